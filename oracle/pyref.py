@@ -1,0 +1,1162 @@
+"""Python big-int ORACLE for the VoteSAVER Groth16/SAVER hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file is a CPU restatement of the reference's algorithms.  It is the *second*, independent
+oracle next to ``oracle/vsp_oracle.c``: slow, obviously-correct Python integers, used to
+(1) pin constants against the reference's own known-answer tests (tests/golden/),
+(2) cross-check the C oracle, and (3) run the self-consistency gate generate -> prove -> verify
+(pairing based) that the reference's own tests use (libs/marshalling/zk/test/r1cs_gg_ppzksnark.cpp:62-164,
+libs/pubkey/test/elgamal_verifiable.cpp:353-506).
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline leg may import it.
+The product path (vote-saver-protocol_b200/) never does.
+
+Authority of each part (paths relative to /root/reference):
+  [SRC]  fft / domains        libs/math/include/nil/crypto3/math/domains/detail/basic_radix2_domain_aux.hpp:46-83
+                              .../domains/basic_radix2_domain.hpp:47-133, step_radix2_domain.hpp:45-247
+                              .../algorithms/make_evaluation_domain.hpp:51-106, type_traits.hpp:56-85
+                              .../algorithms/unity_root.hpp:52-71, coset.hpp:37-43, detail/field_utils.hpp:42-49
+  [SRC]  SAVER                libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp:218-271,322-357,632-667
+  [SRC]  point encodings      libs/marshalling/algebra/include/nil/crypto3/marshalling/algebra/processing/curve_element.hpp:92-173
+                              .../processing/detail/curve_element.hpp:46-92
+  [UPSTREAM-RECALL]           witness_map, BDLO12 multiexp, Groth16 generator/prover/verifier: they live in the
+                              un-vendored submodules crypto3-zk @ d335bb8b and crypto3-algebra @ e4fa2c5e
+                              (/root/reference/.SUBMODULES.json:199,17); restated from the published libsnark /
+                              crypto3 algorithm and anchored on the call sites (elgamal_verifiable.hpp:353,
+                              libs/containers/.../sparse_vector.hpp:258).  PARITY UNPINNED for whole proofs: no test
+                              in the reference fixes r, s or a proof's bytes.
+"""
+from __future__ import annotations
+
+import math
+import random
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence, Tuple
+
+# ----------------------------------------------------------------------------------------------
+# Constants (all [VERIFIED] against the reference's own test vectors)
+# ----------------------------------------------------------------------------------------------
+P = 0x1A0111EA397FE69A4B1BA7B6434BACD764774B84F38512BF6730D2A0F6B0F6241EABFFFEB153FFFFB9FEFFFFFFFFAAAB
+R = 0x73EDA753299D7D483339D80809A1D80553BDA402FFFE5BFEFFFFFFFF00000001
+FR_S = 32  # 2-adicity of r-1
+FR_GENERATOR = 7  # arithmetic_params<Fr>::multiplicative_generator [UPSTREAM-RECALL]
+FR_ROOT_OF_UNITY = pow(FR_GENERATOR, (R - 1) >> FR_S, R)  # order 2^32
+assert FR_ROOT_OF_UNITY == 0x16A2A19EDFE81F20D09B681922C813B4B63683508C2280B93829971F439F0D2B
+BLS_X = 0xD201000000010000  # |x|, x is negative
+G1_B = 4
+# standard generators (used by the oracle's generator/keygen only; prove/encrypt never need them)
+G1_GEN = (
+    0x17F1D3A73197D7942695638C4FA9AC0FC3688C4F9774B905A14E3A3F171BAC586C55E83FF97A1AEFFB3AF00ADB22C6BB,
+    0x08B3F481E3AAA0F1A09E30ED741D8AE4FCF5E095D5D00AF600DB18CB2C04B3EDD03CC744A2888AE40CAA232946C5E7E1,
+)
+G2_GEN = (
+    (0x024AA2B2F08F0A91260805272DC51051C6E47AD4FA403B02B4510B647AE3D1770BAC0326A805BBEFD48056C8C121BDB8,
+     0x13E02B6052719F607DACD3A088274F65596BD0D09920B61AB5DA61BBDC7F5049334CF11213945D57E5AC7D055D042B7E),
+    (0x0CE5D527727D6E118CC9CDC6DA2E351AADFD9BAA8CBDD3A76D429A695160D12C923AC9CC3BACA289E193548608B82801,
+     0x0606C4A02EA734CC32ACD2B02BC28B99CB3E287E85A763AF267492AB572E99AB3F370D275CEC1DA1AAA9075FF05F79BE),
+)
+
+
+# ----------------------------------------------------------------------------------------------
+# Fr helpers
+# ----------------------------------------------------------------------------------------------
+def fr_inv(a: int) -> int:
+    return pow(a, R - 2, R)
+
+
+def ceil_log2(n: int) -> int:
+    """std::ceil(std::log2(n)) as the reference computes it, for n >= 1."""
+    return (n - 1).bit_length() if n > 1 else 0
+
+
+def bitreverse(n: int, l: int) -> int:
+    """detail/field_utils.hpp:42-49"""
+    r = 0
+    for _ in range(l):
+        r = (r << 1) | (n & 1)
+        n >>= 1
+    return r
+
+
+def unity_root(n: int) -> int:
+    """algorithms/unity_root.hpp:52-71"""
+    logn = ceil_log2(n)
+    if n != (1 << logn):
+        raise ValueError("expected n == (1u << logn)")
+    if logn > FR_S:
+        raise ValueError("expected logn <= arithmetic_params<FieldType>::s")
+    omega = FR_ROOT_OF_UNITY
+    for _ in range(FR_S - logn):
+        omega = omega * omega % R
+    return omega
+
+
+def basic_radix2_fft(a: List[int], omega: int) -> None:
+    """domains/detail/basic_radix2_domain_aux.hpp:46-83 — in place, natural in / natural out."""
+    n = len(a)
+    logn = ceil_log2(n) if n > 1 else 0
+    if n != (1 << logn):
+        raise ValueError("expected n == (1u << logn)")
+    for k in range(n):
+        rk = bitreverse(k, logn)
+        if k < rk:
+            a[k], a[rk] = a[rk], a[k]
+    m = 1
+    for _s in range(1, logn + 1):
+        w_m = pow(omega, n // (2 * m), R)
+        for k in range(0, n, 2 * m):
+            w = 1
+            for j in range(m):
+                t = w * a[k + j + m] % R
+                a[k + j + m] = (a[k + j] - t) % R
+                a[k + j] = (a[k + j] + t) % R
+                w = w * w_m % R
+        m *= 2
+
+
+def multiply_by_coset(a: List[int], g: int) -> None:
+    """coset.hpp:37-43 — a[0] untouched, a[i] *= g^i."""
+    u = g
+    for i in range(1, len(a)):
+        a[i] = a[i] * u % R
+        u = u * g % R
+
+
+class BasicRadix2Domain:
+    """domains/basic_radix2_domain.hpp:47-133"""
+
+    kind = "basic_radix2"
+
+    def __init__(self, m: int):
+        if m <= 1:
+            raise ValueError("basic_radix2(): expected m > 1")
+        if ceil_log2(m) > FR_S:
+            raise ValueError("basic_radix2(): expected logm <= s")
+        self.m = m
+        self.omega = unity_root(m)
+
+    def _pad(self, a: List[int]) -> None:
+        if len(a) != self.m:
+            if len(a) < self.m:
+                a.extend([0] * (self.m - len(a)))
+            else:
+                raise ValueError("basic_radix2: expected a.size() == this->m")
+
+    def fft(self, a: List[int]) -> None:
+        self._pad(a)
+        basic_radix2_fft(a, self.omega)
+
+    def inverse_fft(self, a: List[int]) -> None:
+        self._pad(a)
+        basic_radix2_fft(a, fr_inv(self.omega))
+        sconst = fr_inv(len(a) % R)
+        for i in range(len(a)):
+            a[i] = a[i] * sconst % R
+
+    def get_domain_element(self, idx: int) -> int:
+        return pow(self.omega, idx, R)
+
+    def compute_vanishing_polynomial(self, t: int) -> int:
+        return (pow(t, self.m, R) - 1) % R
+
+    def add_poly_z(self, coeff: int, H: List[int]) -> None:
+        if len(H) != self.m + 1:
+            raise ValueError("basic_radix2: expected H.size() == this->m+1")
+        H[self.m] = (H[self.m] + coeff) % R
+        H[0] = (H[0] - coeff) % R
+
+    def divide_by_z_on_coset(self, Pv: List[int]) -> None:
+        zinv = fr_inv(self.compute_vanishing_polynomial(FR_GENERATOR))
+        for i in range(self.m):
+            Pv[i] = Pv[i] * zinv % R
+
+    def evaluate_all_lagrange_polynomials(self, t: int) -> List[int]:
+        return _basic_radix2_lagrange(self.m, t)
+
+
+def _basic_radix2_lagrange(m: int, t: int) -> List[int]:
+    """basic_radix2_domain_aux.hpp:85-140 (Lagrange coefficients over {omega^i} at t)."""
+    if m == 1:
+        return [1]
+    omega = unity_root(m)
+    u = [0] * m
+    if pow(t, m, R) == 1:
+        omega_i = 1
+        for i in range(m):
+            if omega_i == t:
+                u[i] = 1
+                return u
+            omega_i = omega_i * omega % R
+    Z = (pow(t, m, R) - 1) % R
+    l = Z * fr_inv(m % R) % R
+    rr = 1
+    for i in range(m):
+        u[i] = l * fr_inv((t - rr) % R) % R
+        l = l * omega % R
+        rr = rr * omega % R
+    return u
+
+
+class StepRadix2Domain:
+    """domains/step_radix2_domain.hpp:45-247"""
+
+    kind = "step_radix2"
+
+    def __init__(self, m: int):
+        if m <= 1:
+            raise ValueError("step_radix2(): expected m > 1")
+        self.m = m
+        self.big_m = 1 << (ceil_log2(m) - 1)
+        self.small_m = m - self.big_m
+        if self.small_m != (1 << ceil_log2(self.small_m)):
+            raise ValueError("step_radix2(): expected small_m == 1ul<<log2(small_m)")
+        self.omega = unity_root(1 << ceil_log2(m))
+        self.big_omega = self.omega * self.omega % R
+        self.small_omega = unity_root(self.small_m) if self.small_m > 1 else 1
+
+    def _small_root(self) -> int:
+        return unity_root(self.small_m)
+
+    def fft(self, a: List[int]) -> None:
+        if len(a) != self.m:
+            if len(a) < self.m:
+                a.extend([0] * (self.m - len(a)))
+            else:
+                raise ValueError("step_radix2: expected a.size() == this->m")
+        big_m, small_m = self.big_m, self.small_m
+        c = [0] * big_m
+        d = [0] * big_m
+        omega_i = 1
+        for i in range(big_m):
+            if i < small_m:
+                c[i] = (a[i] + a[i + big_m]) % R
+                d[i] = omega_i * ((a[i] - a[i + big_m]) % R) % R
+            else:
+                c[i] = a[i]
+                d[i] = omega_i * a[i] % R
+            omega_i = omega_i * self.omega % R
+        e = [0] * small_m
+        compr = 1 << (ceil_log2(big_m) - ceil_log2(small_m))
+        for i in range(small_m):
+            for j in range(compr):
+                e[i] = (e[i] + d[i + j * small_m]) % R
+        basic_radix2_fft(c, self.big_omega)
+        basic_radix2_fft(e, self._small_root())
+        a[:big_m] = c
+        a[big_m:] = e
+
+    def inverse_fft(self, a: List[int]) -> None:
+        if len(a) != self.m:
+            raise ValueError("step_radix2: expected a.size() == this->m")
+        big_m, small_m = self.big_m, self.small_m
+        U0 = a[:big_m]
+        U1 = a[big_m:]
+        basic_radix2_fft(U0, fr_inv(self.big_omega))
+        basic_radix2_fft(U1, fr_inv(self._small_root()))
+        i0 = fr_inv(big_m % R)
+        U0 = [x * i0 % R for x in U0]
+        i1 = fr_inv(small_m % R)
+        U1 = [x * i1 % R for x in U1]
+        tmp = list(U0)
+        omega_i = 1
+        for i in range(big_m):
+            tmp[i] = tmp[i] * omega_i % R
+            omega_i = omega_i * self.omega % R
+        for i in range(small_m, big_m):
+            a[i] = U0[i]
+        compr = 1 << (ceil_log2(big_m) - ceil_log2(small_m))
+        for i in range(small_m):
+            for j in range(1, compr):
+                U1[i] = (U1[i] - tmp[i + j * small_m]) % R
+        omega_inv = fr_inv(self.omega)
+        omega_inv_i = 1
+        for i in range(small_m):
+            U1[i] = U1[i] * omega_inv_i % R
+            omega_inv_i = omega_inv_i * omega_inv % R
+        over_two = fr_inv(2)
+        for i in range(small_m):
+            a[i] = (U0[i] + U1[i]) * over_two % R
+        for i in range(small_m):
+            a[big_m + i] = (U0[i] - U1[i]) * over_two % R
+
+    def get_domain_element(self, idx: int) -> int:
+        if idx < self.big_m:
+            return pow(self.big_omega, idx, R)
+        return self.omega * pow(self._small_root(), idx - self.big_m, R) % R
+
+    def compute_vanishing_polynomial(self, t: int) -> int:
+        return (pow(t, self.big_m, R) - 1) * (pow(t, self.small_m, R) - pow(self.omega, self.small_m, R)) % R
+
+    def add_poly_z(self, coeff: int, H: List[int]) -> None:
+        w = pow(self.omega, self.small_m, R)
+        H[self.m] = (H[self.m] + coeff) % R
+        H[self.big_m] = (H[self.big_m] - coeff * w) % R
+        H[self.small_m] = (H[self.small_m] - coeff) % R
+        H[0] = (H[0] + coeff * w) % R
+
+    def divide_by_z_on_coset(self, Pv: List[int]) -> None:
+        coset = FR_GENERATOR
+        big_m, small_m = self.big_m, self.small_m
+        Z0 = (pow(coset, big_m, R) - 1) % R
+        c_small_Z0 = pow(coset, small_m, R) * Z0 % R
+        w_small_Z0 = pow(self.omega, small_m, R) * Z0 % R
+        w_2small = pow(self.omega, 2 * small_m, R)
+        elt = 1
+        for i in range(big_m):
+            Pv[i] = Pv[i] * fr_inv((c_small_Z0 * elt - w_small_Z0) % R) % R
+            elt = elt * w_2small % R
+        cw = coset * self.omega % R
+        Z1 = (pow(cw, big_m, R) - 1) * (pow(cw, small_m, R) - pow(self.omega, small_m, R)) % R
+        Z1_inv = fr_inv(Z1)
+        for i in range(small_m):
+            Pv[big_m + i] = Pv[big_m + i] * Z1_inv % R
+
+    def evaluate_all_lagrange_polynomials(self, t: int) -> List[int]:
+        big_m, small_m = self.big_m, self.small_m
+        inner_big = _basic_radix2_lagrange(big_m, t)
+        inner_small = _basic_radix2_lagrange(small_m, t * fr_inv(self.omega) % R)
+        result = [0] * self.m
+        w_small = pow(self.omega, small_m, R)
+        L0 = (pow(t, small_m, R) - w_small) % R
+        bw_small = pow(self.big_omega, small_m, R)
+        elt = 1
+        for i in range(big_m):
+            result[i] = inner_big[i] * L0 % R * fr_inv((elt - w_small) % R) % R
+            elt = elt * bw_small % R
+        L1 = (pow(t, big_m, R) - 1) * fr_inv((pow(self.omega, big_m, R) - 1) % R) % R
+        for i in range(small_m):
+            result[big_m + i] = L1 * inner_small[i] % R
+        return result
+
+
+def is_basic_radix2_domain(m: int) -> bool:
+    """type_traits.hpp:56-61"""
+    log_m = ceil_log2(m) if m >= 1 else 0
+    return m > 1 and log_m <= FR_S and m == (1 << log_m)
+
+
+def is_extended_radix2_domain(m: int) -> bool:
+    """type_traits.hpp:63-72"""
+    if m <= 1:
+        return False
+    log_m = ceil_log2(m)
+    small_m = m // 2
+    log_small = ceil_log2(small_m) if small_m >= 1 else 0
+    return log_m == FR_S + 1 and small_m == (1 << log_small) and log_small <= FR_S
+
+
+def is_step_radix2_domain(m: int) -> bool:
+    """type_traits.hpp:74-85"""
+    if m <= 1:
+        return False
+    log_m = ceil_log2(m)
+    small_m = m - (1 << (log_m - 1))
+    if small_m < 1:
+        return False
+    return small_m == (1 << ceil_log2(small_m)) and log_m <= FR_S
+
+
+def domain_plan(m: int) -> Tuple[str, int]:
+    """algorithms/make_evaluation_domain.hpp:51-106 — (kind, actual size)."""
+    if m <= 1:
+        raise ValueError("make_evaluation_domain: m > 1 expected")
+    big = 1 << (ceil_log2(m) - 1)
+    rounded_small = 1 << ceil_log2(m - big)
+    if is_basic_radix2_domain(m):
+        return "basic_radix2", m
+    if is_extended_radix2_domain(m):
+        return "extended_radix2", m
+    if is_step_radix2_domain(m):
+        return "step_radix2", m
+    if is_basic_radix2_domain(big + rounded_small):
+        return "basic_radix2", big + rounded_small
+    if is_extended_radix2_domain(big + rounded_small):
+        return "extended_radix2", big + rounded_small
+    if is_step_radix2_domain(big + rounded_small):
+        return "step_radix2", big + rounded_small
+    raise ValueError("no radix-2 family domain")  # geometric/arithmetic never reached for Fr here
+
+
+def make_evaluation_domain(m: int):
+    kind, size = domain_plan(m)
+    if kind == "basic_radix2":
+        return BasicRadix2Domain(size)
+    if kind == "step_radix2":
+        return StepRadix2Domain(size)
+    raise ValueError("extended_radix2 needs log m = 33; unsupported in the oracle")
+
+
+# ----------------------------------------------------------------------------------------------
+# Fq2 and curve arithmetic.  G1 points: Jacobian tuples (X, Y, Z) of ints; G2: of (c0, c1) pairs.
+# Group law is the textbook one; the reference's Jacobian (a = 0) formulae live in the missing
+# crypto3-algebra, and any correct law gives the same canonical affine result.
+# ----------------------------------------------------------------------------------------------
+class _Fq:
+    zero = 0
+    one = 1
+
+    @staticmethod
+    def add(a, b):
+        return (a + b) % P
+
+    @staticmethod
+    def sub(a, b):
+        return (a - b) % P
+
+    @staticmethod
+    def mul(a, b):
+        return a * b % P
+
+    @staticmethod
+    def sqr(a):
+        return a * a % P
+
+    @staticmethod
+    def neg(a):
+        return (-a) % P
+
+    @staticmethod
+    def inv(a):
+        return pow(a, P - 2, P)
+
+    @staticmethod
+    def is_zero(a):
+        return a == 0
+
+    @staticmethod
+    def small(k):
+        return k % P
+
+
+class _Fq2:
+    zero = (0, 0)
+    one = (1, 0)
+
+    @staticmethod
+    def add(a, b):
+        return ((a[0] + b[0]) % P, (a[1] + b[1]) % P)
+
+    @staticmethod
+    def sub(a, b):
+        return ((a[0] - b[0]) % P, (a[1] - b[1]) % P)
+
+    @staticmethod
+    def mul(a, b):
+        return ((a[0] * b[0] - a[1] * b[1]) % P, (a[0] * b[1] + a[1] * b[0]) % P)
+
+    @staticmethod
+    def sqr(a):
+        return ((a[0] + a[1]) * (a[0] - a[1]) % P, 2 * a[0] * a[1] % P)
+
+    @staticmethod
+    def neg(a):
+        return ((-a[0]) % P, (-a[1]) % P)
+
+    @staticmethod
+    def inv(a):
+        n = pow(a[0] * a[0] + a[1] * a[1], P - 2, P)
+        return (a[0] * n % P, (-a[1]) * n % P)
+
+    @staticmethod
+    def is_zero(a):
+        return a[0] == 0 and a[1] == 0
+
+    @staticmethod
+    def small(k):
+        return (k % P, 0)
+
+
+class Curve:
+    def __init__(self, F, b):
+        self.F = F
+        self.b = b
+
+    def inf(self):
+        return (self.F.one, self.F.one, self.F.zero)
+
+    def is_inf(self, p):
+        return self.F.is_zero(p[2])
+
+    def from_affine(self, a):
+        if a is None:
+            return self.inf()
+        return (a[0], a[1], self.F.one)
+
+    def to_affine(self, p):
+        F = self.F
+        if self.is_inf(p):
+            return None
+        zi = F.inv(p[2])
+        zi2 = F.sqr(zi)
+        return (F.mul(p[0], zi2), F.mul(p[1], F.mul(zi2, zi)))
+
+    def on_curve_affine(self, a):
+        F = self.F
+        if a is None:
+            return True
+        return F.sqr(a[1]) == F.add(F.mul(F.sqr(a[0]), a[0]), self.b)
+
+    def dbl(self, p):
+        F = self.F
+        if self.is_inf(p):
+            return p
+        X, Y, Z = p
+        A = F.sqr(X)
+        B = F.sqr(Y)
+        C = F.sqr(B)
+        D = F.sub(F.sub(F.sqr(F.add(X, B)), A), C)
+        D = F.add(D, D)
+        E = F.add(F.add(A, A), A)
+        Fv = F.sqr(E)
+        X3 = F.sub(Fv, F.add(D, D))
+        C8 = F.add(C, C)
+        C8 = F.add(C8, C8)
+        C8 = F.add(C8, C8)
+        Y3 = F.sub(F.mul(E, F.sub(D, X3)), C8)
+        Z3 = F.mul(Y, Z)
+        Z3 = F.add(Z3, Z3)
+        return (X3, Y3, Z3)
+
+    def add(self, p, q):
+        F = self.F
+        if self.is_inf(p):
+            return q
+        if self.is_inf(q):
+            return p
+        X1, Y1, Z1 = p
+        X2, Y2, Z2 = q
+        Z1Z1 = F.sqr(Z1)
+        Z2Z2 = F.sqr(Z2)
+        U1 = F.mul(X1, Z2Z2)
+        U2 = F.mul(X2, Z1Z1)
+        S1 = F.mul(Y1, F.mul(Z2, Z2Z2))
+        S2 = F.mul(Y2, F.mul(Z1, Z1Z1))
+        if U1 == U2:
+            if S1 == S2:
+                return self.dbl(p)
+            return self.inf()
+        H = F.sub(U2, U1)
+        Rr = F.sub(S2, S1)
+        HH = F.sqr(H)
+        HHH = F.mul(H, HH)
+        V = F.mul(U1, HH)
+        X3 = F.sub(F.sub(F.sqr(Rr), HHH), F.add(V, V))
+        Y3 = F.sub(F.mul(Rr, F.sub(V, X3)), F.mul(S1, HHH))
+        Z3 = F.mul(F.mul(Z1, Z2), H)
+        return (X3, Y3, Z3)
+
+    def neg(self, p):
+        return (p[0], self.F.neg(p[1]), p[2])
+
+    def mul(self, k: int, p):
+        k %= R
+        acc = self.inf()
+        for bit in bin(k)[2:] if k else "":
+            acc = self.dbl(acc)
+            if bit == "1":
+                acc = self.add(acc, p)
+        return acc
+
+    def eq(self, p, q):
+        return self.to_affine(p) == self.to_affine(q)
+
+
+G1 = Curve(_Fq, 4)
+G2 = Curve(_Fq2, (4, 4))
+
+
+def g1_generator():
+    return G1.from_affine(G1_GEN)
+
+
+def g2_generator():
+    return G2.from_affine(G2_GEN)
+
+
+# --- canonical encodings (processing/curve_element.hpp:92-173; detail/curve_element.hpp:46-92) ---
+def _sign_fq(v: int) -> bool:
+    return v > (P - 1) // 2
+
+
+def g1_compress(p) -> bytes:
+    a = G1.to_affine(p)
+    if a is None:
+        out = bytearray(48)
+        out[0] |= 0x80 | 0x40
+        return bytes(out)
+    out = bytearray(a[0].to_bytes(48, "big"))
+    out[0] |= 0x80 | (0x20 if _sign_fq(a[1]) else 0)
+    return bytes(out)
+
+
+def g2_compress(p) -> bytes:
+    a = G2.to_affine(p)
+    if a is None:
+        out = bytearray(96)
+        out[0] |= 0x80 | 0x40
+        return bytes(out)
+    (x0, x1), (y0, y1) = a
+    out = bytearray(x1.to_bytes(48, "big") + x0.to_bytes(48, "big"))
+    s = _sign_fq(y0) if y1 == 0 else _sign_fq(y1)
+    out[0] |= 0x80 | (0x20 if s else 0)
+    return bytes(out)
+
+
+def g1_uncompressed(p) -> bytes:
+    """point_to_octets: x || y big-endian, no C bit (bls.cpp:167-171 etalon)."""
+    a = G1.to_affine(p)
+    if a is None:
+        out = bytearray(96)
+        out[0] |= 0x40
+        return bytes(out)
+    return a[0].to_bytes(48, "big") + a[1].to_bytes(48, "big")
+
+
+def g2_uncompressed(p) -> bytes:
+    a = G2.to_affine(p)
+    if a is None:
+        out = bytearray(192)
+        out[0] |= 0x40
+        return bytes(out)
+    (x0, x1), (y0, y1) = a
+    return x1.to_bytes(48, "big") + x0.to_bytes(48, "big") + y1.to_bytes(48, "big") + y0.to_bytes(48, "big")
+
+
+# ----------------------------------------------------------------------------------------------
+# multiexp — BDLO12 (Pippenger) as crypto3/libff run it  [UPSTREAM-RECALL]
+# ----------------------------------------------------------------------------------------------
+def bdlo12_window(n: int) -> int:
+    """c = log2(n) - (log2(n)/3 - 2), integer division, libff multiexp_inner<BDLO12>."""
+    log2_length = max(int(math.log2(n)), 0) if n > 0 else 0
+    return max(log2_length - (log2_length // 3 - 2), 1)
+
+
+def multiexp_bdlo12(curve: Curve, bases: Sequence, scalars: Sequence[int]):
+    n = len(bases)
+    assert n == len(scalars)
+    if n == 0:
+        return curve.inf()
+    c = bdlo12_window(n)
+    num_bits = max((s % R).bit_length() for s in scalars)
+    num_groups = (num_bits + c - 1) // c
+    result = curve.inf()
+    result_nonzero = False
+    for k in range(num_groups - 1, -1, -1):
+        if result_nonzero:
+            for _ in range(c):
+                result = curve.dbl(result)
+        buckets = {}
+        for i in range(n):
+            idx = ((scalars[i] % R) >> (k * c)) & ((1 << c) - 1)
+            if idx > 0:
+                buckets[idx] = curve.add(buckets[idx], bases[i]) if idx in buckets else bases[i]
+        running = curve.inf()
+        for idx in range((1 << c) - 1, 0, -1):
+            if idx in buckets:
+                running = curve.add(running, buckets[idx])
+            if not curve.is_inf(running):
+                result = curve.add(result, running)
+                result_nonzero = True
+    return result
+
+
+def multiexp_naive(curve: Curve, bases: Sequence, scalars: Sequence[int]):
+    acc = curve.inf()
+    for b, s in zip(bases, scalars):
+        acc = curve.add(acc, curve.mul(s, b))
+    return acc
+
+
+# ----------------------------------------------------------------------------------------------
+# R1CS, QAP witness map, Groth16  [UPSTREAM-RECALL], data shapes from
+# libs/marshalling/zk/include/nil/crypto3/marshalling/zk/types/r1cs_gg_ppzksnark/{r1cs,fast_proving_key,proof}.hpp
+# ----------------------------------------------------------------------------------------------
+LinComb = List[Tuple[int, int]]  # (variable index, coeff); index 0 is the constant one
+
+
+@dataclass
+class R1CS:
+    primary_input_size: int
+    auxiliary_input_size: int
+    constraints: List[Tuple[LinComb, LinComb, LinComb]] = field(default_factory=list)
+
+    @property
+    def num_variables(self) -> int:
+        return self.primary_input_size + self.auxiliary_input_size
+
+    @property
+    def num_inputs(self) -> int:
+        return self.primary_input_size
+
+    @property
+    def num_constraints(self) -> int:
+        return len(self.constraints)
+
+    @staticmethod
+    def eval_lc(lc: LinComb, full: Sequence[int]) -> int:
+        acc = 0
+        for idx, coeff in lc:
+            acc += coeff * (1 if idx == 0 else full[idx - 1])
+        return acc % R
+
+    def is_satisfied(self, primary: Sequence[int], auxiliary: Sequence[int]) -> bool:
+        full = list(primary) + list(auxiliary)
+        for a, b, c in self.constraints:
+            if self.eval_lc(a, full) * self.eval_lc(b, full) % R != self.eval_lc(c, full):
+                return False
+        return True
+
+
+def r1cs_example_with_field_input(num_constraints: int, num_inputs: int, rng: random.Random):
+    """libs/marshalling/zk/test/detail/r1cs_examples.hpp:75-144 (same constraint shape; seeded values)."""
+    assert num_inputs <= num_constraints + 2
+    cs = R1CS(num_inputs, 2 + num_constraints - num_inputs)
+    a = rng.randrange(R)
+    b = rng.randrange(R)
+    full = [a, b]
+    for i in range(num_constraints - 1):
+        if i % 2:
+            A, B, C = [(i + 1, 1)], [(i + 2, 1)], [(i + 3, 1)]
+            tmp = a * b % R
+        else:
+            B = [(0, 1)]
+            A = [(i + 1, 1), (i + 2, 1)]
+            C = [(i + 3, 1)]
+            tmp = (a + b) % R
+        full.append(tmp)
+        a, b = b, tmp
+        cs.constraints.append((A, B, C))
+    A, B = [], []
+    fin = 0
+    for i in range(1, cs.num_variables):
+        A.append((i, 1))
+        B.append((i, 1))
+        fin = (fin + full[i - 1]) % R
+    cs.constraints.append((A, B, [(cs.num_variables, 1)]))
+    full.append(fin * fin % R)
+    primary, aux = full[:num_inputs], full[num_inputs:]
+    assert cs.num_variables == len(full) and cs.num_constraints == num_constraints
+    assert cs.is_satisfied(primary, aux)
+    return cs, primary, aux
+
+
+def r1cs_example_with_binary_input(num_constraints: int, num_inputs: int, rng: random.Random):
+    """r1cs_examples.hpp:154-210 (XOR chain; witness is all bits)."""
+    assert num_inputs >= 1
+    cs = R1CS(num_inputs, num_constraints)
+    full = [rng.randrange(2) for _ in range(num_inputs)]
+    lastvar = num_inputs - 1
+    for i in range(num_constraints):
+        lastvar += 1
+        u = rng.randrange(num_inputs) if i == 0 else rng.randrange(i)
+        v = rng.randrange(num_inputs) if i == 0 else rng.randrange(i)
+        A = [(u + 1, 2)]
+        B = [(v + 1, 1)]
+        C = [(u + 1, 2)] if u == v else [(u + 1, 1), (v + 1, 1)]
+        C.append((lastvar + 1, R - 1))
+        cs.constraints.append((A, B, C))
+        full.append((full[u] + full[v] - 2 * full[u] * full[v]) % R)
+    primary, aux = full[:num_inputs], full[num_inputs:]
+    assert cs.is_satisfied(primary, aux)
+    return cs, primary, aux
+
+
+def witness_map(cs: R1CS, primary: Sequence[int], auxiliary: Sequence[int]):
+    """r1cs_to_qap::witness_map with d1 = d2 = d3 = 0 (Groth16).  Returns (domain, coefficients_for_H[m+1], full)."""
+    domain = make_evaluation_domain(cs.num_constraints + cs.num_inputs + 1)
+    m = domain.m
+    full = list(primary) + list(auxiliary)
+    nc = cs.num_constraints
+    aA = [0] * m
+    aB = [0] * m
+    for i in range(cs.num_inputs + 1):
+        aA[i + nc] = full[i - 1] if i > 0 else 1
+    for i, (a, b, _c) in enumerate(cs.constraints):
+        aA[i] = (aA[i] + cs.eval_lc(a, full)) % R
+        aB[i] = (aB[i] + cs.eval_lc(b, full)) % R
+    domain.inverse_fft(aA)
+    domain.inverse_fft(aB)
+    g = FR_GENERATOR
+    H = [0] * (m + 1)  # d1=d2=d3=0: the (d2*A + d1*B - d3) + d1*d2*Z part vanishes
+    multiply_by_coset(aA, g)
+    domain.fft(aA)
+    multiply_by_coset(aB, g)
+    domain.fft(aB)
+    H_tmp = [aA[i] * aB[i] % R for i in range(m)]
+    aC = [0] * m
+    for i, (_a, _b, c) in enumerate(cs.constraints):
+        aC[i] = cs.eval_lc(c, full)
+    domain.inverse_fft(aC)
+    multiply_by_coset(aC, g)
+    domain.fft(aC)
+    for i in range(m):
+        H_tmp[i] = (H_tmp[i] - aC[i]) % R
+    domain.divide_by_z_on_coset(H_tmp)
+    domain.inverse_fft(H_tmp)
+    multiply_by_coset(H_tmp, fr_inv(g))
+    for i in range(m):
+        H[i] = (H[i] + H_tmp[i]) % R
+    return domain, H, full
+
+
+@dataclass
+class ProvingKey:
+    """fast_proving_key.hpp:66-103 field order."""
+    alpha_g1: tuple
+    beta_g1: tuple
+    beta_g2: tuple
+    delta_g1: tuple
+    delta_g2: tuple
+    A_query: list  # G1, num_variables + 1
+    B_query: list  # dense list of (G2, G1) or None for zero entries, num_variables + 1 (sparse on the wire)
+    H_query: list  # G1, m - 1
+    L_query: list  # G1, num_variables - num_inputs
+    cs: R1CS
+
+
+@dataclass
+class VerificationKey:
+    alpha_g1: tuple
+    beta_g2: tuple
+    gamma_g2: tuple
+    delta_g2: tuple
+    gamma_g1: tuple  # encrypted_input mode extras used by SAVER keygen (elgamal_verifiable.hpp:233,250-260)
+    delta_g1: tuple
+    gamma_ABC_first: tuple
+    gamma_ABC_rest: list
+
+
+def groth16_generate(cs: R1CS, rng: random.Random):
+    """r1cs_gg_ppzksnark_generator  [UPSTREAM-RECALL] — self-consistency gate only."""
+    t, alpha, beta, gamma, delta = (rng.randrange(1, R) for _ in range(5))
+    domain = make_evaluation_domain(cs.num_constraints + cs.num_inputs + 1)
+    m = domain.m
+    u = domain.evaluate_all_lagrange_polynomials(t)
+    nv = cs.num_variables
+    At = [0] * (nv + 1)
+    Bt = [0] * (nv + 1)
+    Ct = [0] * (nv + 1)
+    for i in range(cs.num_inputs + 1):
+        At[i] = u[cs.num_constraints + i]
+    for i, (a, b, c) in enumerate(cs.constraints):
+        for idx, coeff in a:
+            At[idx] = (At[idx] + u[i] * coeff) % R
+        for idx, coeff in b:
+            Bt[idx] = (Bt[idx] + u[i] * coeff) % R
+        for idx, coeff in c:
+            Ct[idx] = (Ct[idx] + u[i] * coeff) % R
+    Zt = domain.compute_vanishing_polynomial(t)
+    gi, di = fr_inv(gamma), fr_inv(delta)
+    g1, g2 = g1_generator(), g2_generator()
+    gabc = [(beta * At[i] + alpha * Bt[i] + Ct[i]) % R * gi % R for i in range(cs.num_inputs + 1)]
+    Lt = [(beta * At[i] + alpha * Bt[i] + Ct[i]) % R * di % R for i in range(cs.num_inputs + 1, nv + 1)]
+    pk = ProvingKey(
+        alpha_g1=G1.mul(alpha, g1), beta_g1=G1.mul(beta, g1), beta_g2=G2.mul(beta, g2),
+        delta_g1=G1.mul(delta, g1), delta_g2=G2.mul(delta, g2),
+        A_query=[G1.mul(x, g1) for x in At],
+        B_query=[(G2.mul(x, g2), G1.mul(x, g1)) if x else None for x in Bt],
+        H_query=[G1.mul(pow(t, i, R) * Zt % R * di % R, g1) for i in range(m - 1)],
+        L_query=[G1.mul(x, g1) for x in Lt],
+        cs=cs,
+    )
+    gabc_pts = [G1.mul(x, g1) for x in gabc]
+    vk = VerificationKey(pk.alpha_g1, pk.beta_g2, G2.mul(gamma, g2), pk.delta_g2, G1.mul(gamma, g1), pk.delta_g1,
+                         gabc_pts[0], gabc_pts[1:])
+    return pk, vk
+
+
+def groth16_prove(pk: ProvingKey, primary: Sequence[int], auxiliary: Sequence[int], r: int, s: int,
+                  msm=multiexp_bdlo12):
+    """r1cs_gg_ppzksnark_prover::process (basic mode) with explicit r, s  [UPSTREAM-RECALL]."""
+    cs = pk.cs
+    domain, H, full = witness_map(cs, primary, auxiliary)
+    m = domain.m
+    w = [1] + full
+    nv = cs.num_variables
+    ev_A = msm(G1, pk.A_query[: nv + 1], w[: nv + 1])
+    b_idx = [i for i in range(nv + 1) if pk.B_query[i] is not None]
+    ev_B_g2 = msm(G2, [pk.B_query[i][0] for i in b_idx], [w[i] for i in b_idx])
+    ev_B_g1 = msm(G1, [pk.B_query[i][1] for i in b_idx], [w[i] for i in b_idx])
+    ev_H = msm(G1, pk.H_query[: m - 1], H[: m - 1])
+    ev_L = msm(G1, pk.L_query, w[cs.num_inputs + 1:])
+    g1_A = G1.add(G1.add(pk.alpha_g1, ev_A), G1.mul(r, pk.delta_g1))
+    g1_B = G1.add(G1.add(pk.beta_g1, ev_B_g1), G1.mul(s, pk.delta_g1))
+    g2_B = G2.add(G2.add(pk.beta_g2, ev_B_g2), G2.mul(s, pk.delta_g2))
+    g1_C = G1.add(G1.add(ev_H, ev_L), G1.add(G1.mul(s, g1_A), G1.mul(r, g1_B)))
+    g1_C = G1.add(g1_C, G1.neg(G1.mul(r * s % R, pk.delta_g1)))
+    return g1_A, g2_B, g1_C
+
+
+# ----------------------------------------------------------------------------------------------
+# SAVER  [SRC] libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp
+# ----------------------------------------------------------------------------------------------
+@dataclass
+class SaverPublicKey:  # :152-157
+    delta_g1: tuple
+    delta_s_g1: list
+    t_g1: list
+    t_g2: list
+    delta_sum_s_g1: tuple
+    gamma_inverse_sum_s_g1: tuple
+
+
+@dataclass
+class SaverVerificationKey:  # :107-110
+    rho_g2: tuple
+    rho_sv_g2: list
+    rho_rhov_g2: list
+
+
+def saver_keygen(vk: VerificationKey, msg_size: int, rnd: Sequence[int]):
+    """generate_keypair_op::process, elgamal_verifiable.hpp:218-271."""
+    assert len(rnd) >= 3 * msg_size + 2
+    it = iter(rnd)
+    g2 = g2_generator()
+    gamma_inverse_sum_s = vk.gamma_g1
+    rho = next(it)
+    rho_g2 = G2.mul(rho, g2)
+    t = next(it)
+    t_g2 = [G2.mul(t, g2)]
+    delta_sum_s = G1.mul(t, vk.delta_g1)
+    delta_s, t_g1, rho_sv, rho_rhov = [], [], [], []
+    for i in range(msg_size):
+        s = next(it)
+        v = next(it)
+        sv = s * v % R
+        t = next(it)
+        delta_s.append(G1.mul(s, vk.delta_g1))
+        t_g1.append(G1.mul(t, vk.gamma_ABC_rest[i]))
+        t_g2.append(G2.mul(t, g2))
+        delta_sum_s = G1.add(delta_sum_s, G1.mul(s * t % R, vk.delta_g1))
+        gamma_inverse_sum_s = G1.add(gamma_inverse_sum_s, G1.mul(s, vk.gamma_g1))
+        rho_sv.append(G2.mul(sv, g2))
+        rho_rhov.append(G2.mul(v, rho_g2))
+    gamma_inverse_sum_s = G1.neg(gamma_inverse_sum_s)
+    return (SaverPublicKey(vk.delta_g1, delta_s, t_g1, t_g2, delta_sum_s, gamma_inverse_sum_s), rho,
+            SaverVerificationKey(rho_g2, rho_sv, rho_rhov))
+
+
+def saver_ciphertext(pub: SaverPublicKey, gamma_ABC_rest: Sequence, plain: Sequence[int], r: int):
+    """encrypt_op::process ciphertext part, elgamal_verifiable.hpp:341-352."""
+    ct = [G1.mul(r, pub.delta_g1)]
+    sum_tm = G1.mul(r, pub.delta_sum_s_g1)
+    for i, mi in enumerate(plain):
+        ct.append(G1.add(G1.mul(r, pub.delta_s_g1[i]), G1.mul(mi, gamma_ABC_rest[i])))
+        sum_tm = G1.add(sum_tm, G1.mul(mi, pub.t_g1[i]))
+    ct.append(sum_tm)
+    return ct
+
+
+def saver_encrypt(pk: ProvingKey, vk: VerificationKey, pub: SaverPublicKey, plain, primary, auxiliary,
+                  r_saver: int, r: int, s: int, msm=multiexp_bdlo12):
+    """encrypt_op::process :322-357 + zk::prove<encrypted_input> (g_C += r_saver * gamma_inverse_sum_s_g1)."""
+    assert list(primary[: len(plain)]) == list(plain)
+    ct = saver_ciphertext(pub, vk.gamma_ABC_rest, plain, r_saver)
+    gA, gB, gC = groth16_prove(pk, primary, auxiliary, r, s, msm=msm)
+    gC = G1.add(gC, G1.mul(r_saver, pub.gamma_inverse_sum_s_g1))
+    return ct, (gA, gB, gC)
+
+
+def saver_rerandomize(pub: SaverPublicKey, delta_g2, ct, proof, rnd: Sequence[int]):
+    """rerandomize_op::process, elgamal_verifiable.hpp:632-667."""
+    r, z1, z2 = rnd[0], rnd[1], rnd[2]
+    z1_inv = fr_inv(z1)
+    out = [G1.add(ct[0], G1.mul(r, pub.delta_g1))]
+    for i in range(1, len(ct) - 1):
+        out.append(G1.add(ct[i], G1.mul(r, pub.delta_s_g1[i - 1])))
+    out.append(G1.add(ct[-1], G1.mul(r, pub.delta_sum_s_g1)))
+    gA, gB, gC = proof
+    A2 = G1.mul(z1, gA)
+    B2 = G2.add(G2.mul(z1_inv, gB), G2.mul(z2, delta_g2))
+    C2 = G1.add(G1.add(gC, G1.mul(z2, A2)), G1.mul(r, pub.gamma_inverse_sum_s_g1))
+    return out, (A2, B2, C2)
+
+
+# ----------------------------------------------------------------------------------------------
+# Pairing (self-consistency gate only; slow).  Tower Fq2[v]/(v^3 - xi), Fq6[w]/(w^2 - v), xi = 1 + u.
+# ----------------------------------------------------------------------------------------------
+_XI = (1, 1)
+
+
+def _f2mul_xi(a):
+    return ((a[0] - a[1]) % P, (a[0] + a[1]) % P)
+
+
+def _f6add(a, b):
+    return tuple(_Fq2.add(x, y) for x, y in zip(a, b))
+
+
+def _f6sub(a, b):
+    return tuple(_Fq2.sub(x, y) for x, y in zip(a, b))
+
+
+def _f6neg(a):
+    return tuple(_Fq2.neg(x) for x in a)
+
+
+def _f6mul(a, b):
+    m = _Fq2.mul
+    a0, a1, a2 = a
+    b0, b1, b2 = b
+    t0, t1, t2 = m(a0, b0), m(a1, b1), m(a2, b2)
+    c0 = _Fq2.add(t0, _f2mul_xi(_Fq2.add(m(a1, b2), m(a2, b1))))
+    c1 = _Fq2.add(_Fq2.add(m(a0, b1), m(a1, b0)), _f2mul_xi(t2))
+    c2 = _Fq2.add(_Fq2.add(m(a0, b2), m(a2, b0)), t1)
+    return (c0, c1, c2)
+
+
+def _f6mul_v(a):
+    return (_f2mul_xi(a[2]), a[0], a[1])
+
+
+def _f6inv(a):
+    m = _Fq2.mul
+    a0, a1, a2 = a
+    c0 = _Fq2.sub(_Fq2.sqr(a0), _f2mul_xi(m(a1, a2)))
+    c1 = _Fq2.sub(_f2mul_xi(_Fq2.sqr(a2)), m(a0, a1))
+    c2 = _Fq2.sub(_Fq2.sqr(a1), m(a0, a2))
+    t = _Fq2.add(m(a0, c0), _f2mul_xi(_Fq2.add(m(a2, c1), m(a1, c2))))
+    ti = _Fq2.inv(t)
+    return (m(c0, ti), m(c1, ti), m(c2, ti))
+
+
+_F6_ZERO = ((0, 0), (0, 0), (0, 0))
+_F6_ONE = ((1, 0), (0, 0), (0, 0))
+F12_ONE = (_F6_ONE, _F6_ZERO)
+
+
+def f12mul(a, b):
+    a0, a1 = a
+    b0, b1 = b
+    t0 = _f6mul(a0, b0)
+    t1 = _f6mul(a1, b1)
+    c0 = _f6add(t0, _f6mul_v(t1))
+    c1 = _f6sub(_f6sub(_f6mul(_f6add(a0, a1), _f6add(b0, b1)), t0), t1)
+    return (c0, c1)
+
+
+def f12inv(a):
+    a0, a1 = a
+    t = _f6sub(_f6mul(a0, a0), _f6mul_v(_f6mul(a1, a1)))
+    ti = _f6inv(t)
+    return (_f6mul(a0, ti), _f6neg(_f6mul(a1, ti)))
+
+
+def f12conj(a):
+    return (a[0], _f6neg(a[1]))
+
+
+def f12pow(a, e: int):
+    acc = F12_ONE
+    for bit in bin(e)[2:]:
+        acc = f12mul(acc, acc)
+        if bit == "1":
+            acc = f12mul(acc, a)
+    return acc
+
+
+def _f12_from_fq(x: int):
+    return (((x % P, 0), (0, 0), (0, 0)), _F6_ZERO)
+
+
+def _f12_from_fq2_times_w_pow(x, k: int):
+    """x * w^k for k in 0..5, with w^2 = v."""
+    c = [[(0, 0), (0, 0), (0, 0)], [(0, 0), (0, 0), (0, 0)]]
+    c[k % 2][k // 2] = x
+    return (tuple(c[0]), tuple(c[1]))
+
+
+_W2_INV = None
+_W3_INV = None
+
+
+def _untwist(q_aff):
+    """E'(Fq2): y^2 = x^3 + 4 xi  ->  E(Fq12): (x / w^2, y / w^3)."""
+    global _W2_INV, _W3_INV
+    if _W2_INV is None:
+        _W2_INV = f12inv(_f12_from_fq2_times_w_pow((1, 0), 2))
+        _W3_INV = f12inv(_f12_from_fq2_times_w_pow((1, 0), 3))
+    x = f12mul(_f12_from_fq2_times_w_pow(q_aff[0], 0), _W2_INV)
+    y = f12mul(_f12_from_fq2_times_w_pow(q_aff[1], 0), _W3_INV)
+    return x, y
+
+
+def _f12sub(a, b):
+    return (_f6sub(a[0], b[0]), _f6sub(a[1], b[1]))
+
+
+def _f12add(a, b):
+    return (_f6add(a[0], b[0]), _f6add(a[1], b[1]))
+
+
+def miller_loop(p_aff, q_aff):
+    """Textbook ate Miller loop over E(Fq12) with affine steps (slow, simple)."""
+    if p_aff is None or q_aff is None:
+        return F12_ONE
+    px, py = _f12_from_fq(p_aff[0]), _f12_from_fq(p_aff[1])
+    qx, qy = _untwist(q_aff)
+    tx, ty = qx, qy
+    f = F12_ONE
+    three = _f12_from_fq(3)
+    two = _f12_from_fq(2)
+
+    def line(x1, y1, lam):
+        # l(P) = (py - y1) - lam (px - x1)
+        return _f12sub(_f12sub(py, y1), f12mul(lam, _f12sub(px, x1)))
+
+    for bit in bin(BLS_X)[3:]:
+        lam = f12mul(f12mul(three, f12mul(tx, tx)), f12inv(f12mul(two, ty)))
+        f = f12mul(f12mul(f, f), line(tx, ty, lam))
+        nx = _f12sub(f12mul(lam, lam), f12mul(two, tx))
+        ny = _f12sub(f12mul(lam, _f12sub(tx, nx)), ty)
+        tx, ty = nx, ny
+        if bit == "1":
+            lam = f12mul(_f12sub(qy, ty), f12inv(_f12sub(qx, tx)))
+            f = f12mul(f, line(tx, ty, lam))
+            nx = _f12sub(_f12sub(f12mul(lam, lam), tx), qx)
+            ny = _f12sub(f12mul(lam, _f12sub(tx, nx)), ty)
+            tx, ty = nx, ny
+    return f12conj(f)  # x < 0
+
+
+_FINAL_EXP = (P ** 12 - 1) // R
+
+
+def final_exponentiation(f):
+    return f12pow(f, _FINAL_EXP)
+
+
+def pairing_product_is_one(pairs) -> bool:
+    """prod e(P_i, Q_i) == 1, P_i / Q_i Jacobian points of G1 / G2."""
+    f = F12_ONE
+    for p, q in pairs:
+        f = f12mul(f, miller_loop(G1.to_affine(p), G2.to_affine(q)))
+    return final_exponentiation(f) == F12_ONE
+
+
+def groth16_verify(vk: VerificationKey, primary: Sequence[int], proof) -> bool:
+    """e(A,B) = e(alpha,beta) e(acc, gamma) e(C, delta)   (basic mode)."""
+    gA, gB, gC = proof
+    acc = vk.gamma_ABC_first
+    for x, pt in zip(primary, vk.gamma_ABC_rest):
+        acc = G1.add(acc, G1.mul(x, pt))
+    return pairing_product_is_one([
+        (G1.neg(gA), gB), (vk.alpha_g1, vk.beta_g2), (acc, vk.gamma_g2), (gC, vk.delta_g2)])
+
+
+def saver_verify_encryption(vk: VerificationKey, pub: SaverPublicKey, ct, unencrypted_primary, proof) -> bool:
+    """verify_encryption_op (elgamal_verifiable.hpp:486-490) -> zk::verify<encrypted_input>  [UPSTREAM-RECALL]:
+    ciphertext well-formedness  prod e(ct_i, t_g2[i]) = e(ct_last, G2)  and the Groth16 equation with the
+    message slots replaced by the ciphertext elements."""
+    n = len(ct) - 2
+    pairs = [(ct[i], pub.t_g2[i]) for i in range(n + 1)]
+    pairs.append((G1.neg(ct[-1]), g2_generator()))
+    if not pairing_product_is_one(pairs):
+        return False
+    gA, gB, gC = proof
+    acc = vk.gamma_ABC_first
+    for i in range(n + 1):
+        acc = G1.add(acc, ct[i])
+    for x, pt in zip(unencrypted_primary, vk.gamma_ABC_rest[n:]):
+        acc = G1.add(acc, G1.mul(x, pt))
+    return pairing_product_is_one([
+        (G1.neg(gA), gB), (vk.alpha_g1, vk.beta_g2), (acc, vk.gamma_g2), (gC, vk.delta_g2)])
