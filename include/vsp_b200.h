@@ -1,0 +1,173 @@
+/* vsp_b200.h — C ABI of the B200-native VoteSAVER ballot-proof hot path (libvsp_b200.so).
+ *
+ * One shared library, plain pointers and sizes, no C++ or torch types.  Every entry point replaces one
+ * interface of the reference (paths relative to the reference tree NilFoundation/vote-saver-protocol @ ae4f646c):
+ *
+ *   vsp_domain_plan / vsp_fr_fft / vsp_fr_multiply_by_coset / vsp_fr_divide_by_z_on_coset
+ *       math::make_evaluation_domain<Fr>(m)           libs/math/include/nil/crypto3/math/algorithms/make_evaluation_domain.hpp:51-106
+ *       evaluation_domain<Fr>::fft / inverse_fft      libs/math/include/nil/crypto3/math/domains/evaluation_domain.hpp:78,83
+ *                                                     (basic_radix2_domain.hpp:69-96, step_radix2_domain.hpp:73-166)
+ *       math::multiply_by_coset                       libs/math/include/nil/crypto3/math/coset.hpp:37-43
+ *       evaluation_domain<Fr>::divide_by_z_on_coset   basic_radix2_domain.hpp:118-124, step_radix2_domain.hpp:222-246
+ *   vsp_g1_msm / vsp_g2_msm / vsp_g*_bases_*
+ *       algebra::multiexp<multiexp_method_BDLO12>(bases_begin, bases_end, scalars_begin, scalars_end, chunks)
+ *                                                     call site libs/containers/include/nil/crypto3/container/sparse_vector.hpp:258-261
+ *   vsp_pk_load / vsp_witness_map / vsp_prove
+ *       zk::prove<r1cs_gg_ppzksnark<bls12<381>, ..., proving_mode::encrypted_input>>(pk, pubkey, primary, auxiliary, r)
+ *                                                     call site libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp:353-354
+ *       proving-key field order                       libs/marshalling/zk/include/nil/crypto3/marshalling/zk/types/r1cs_gg_ppzksnark/fast_proving_key.hpp:66-103
+ *       R1CS shape                                    .../types/r1cs_gg_ppzksnark/r1cs.hpp:57-113
+ *   vsp_saver_encrypt / vsp_saver_rerandomize
+ *       encrypt_op<elgamal_verifiable<Curve>>::process       elgamal_verifiable.hpp:322-357
+ *       rerandomize_op<elgamal_verifiable<Curve>>::process   elgamal_verifiable.hpp:632-667
+ *
+ * Conventions
+ *   - Every function returns 0 on success and a negative VSP_E_* code on failure; it never aborts and never throws.
+ *     vsp_last_error(ctx) returns the text of the last failure on that context.
+ *   - There is no CPU fallback: without a usable CUDA device vsp_ctx_create fails with VSP_E_NO_DEVICE.
+ *   - A context is bound to one GPU and one CUDA stream and is not thread-safe; distinct contexts are independent.
+ *   - Numbers are canonical (non-Montgomery) little-endian 64-bit limbs:  Fr = 4 limbs (< r), Fq = 6 limbs (< p).
+ *     G1 affine = x | y (12 limbs); G2 affine = x.c0 | x.c1 | y.c0 | y.c1 (24 limbs); the point at infinity is
+ *     all-zero (mirrors fast_curve_element's X | Y | is_infinity, .../marshalling/algebra/types/fast_curve_element.hpp:56-97).
+ *     Outputs are canonical affine, so they compare bit for bit with the reference's to_affine() results.
+ *   - Pointers are host pointers unless the parameter name starts with d_ (device pointer on the context's GPU).
+ *   - Groth16's blinding scalars r, s are explicit inputs (the reference draws them inside zk::prove).
+ */
+#ifndef VSP_B200_H
+#define VSP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VSP_OK 0
+#define VSP_E_INVALID (-1)    /* bad argument (the reference throws std::invalid_argument / asserts) */
+#define VSP_E_NO_DEVICE (-2)  /* no CUDA device / context creation failed */
+#define VSP_E_CUDA (-3)       /* CUDA runtime error, text in vsp_last_error */
+#define VSP_E_DOMAIN (-4)     /* no radix-2 family evaluation domain of that size */
+#define VSP_E_NOMEM (-5)
+
+#define VSP_DOMAIN_BASIC_RADIX2 1
+#define VSP_DOMAIN_EXTENDED_RADIX2 2 /* needs log m = 33 for Fr: reported by vsp_domain_plan, not executable */
+#define VSP_DOMAIN_STEP_RADIX2 3
+
+typedef struct vsp_ctx vsp_ctx;
+typedef struct vsp_g1_bases vsp_g1_bases;
+typedef struct vsp_g2_bases vsp_g2_bases;
+typedef struct vsp_pk vsp_pk;
+
+/* ---- context ------------------------------------------------------------------------------ */
+/* cuda_stream: an existing CUstream / cudaStream_t to launch on (e.g. torch's current stream), or NULL for a
+ * private non-blocking stream. */
+int vsp_ctx_create(int device, void *cuda_stream, vsp_ctx **out);
+void vsp_ctx_destroy(vsp_ctx *ctx);
+const char *vsp_last_error(const vsp_ctx *ctx);
+int vsp_ctx_synchronize(vsp_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t vsp_ctx_launch_count(const vsp_ctx *ctx);
+const char *vsp_version(void);
+
+/* ---- evaluation domains over Fr ------------------------------------------------------------ */
+int vsp_domain_plan(uint64_t min_size, int *kind, uint64_t *m);
+/* fft / inverse_fft of the domain of size m (m as returned by vsp_domain_plan).  n_in <= m values are read; the
+ * basic domain zero-pads short input, the step domain's inverse_fft rejects it (VSP_E_INVALID) as the reference does. */
+int vsp_fr_fft(vsp_ctx *ctx, uint64_t m, int inverse, const uint64_t *in, uint64_t n_in, uint64_t *out);
+int vsp_fr_fft_dev(vsp_ctx *ctx, uint64_t m, int inverse, uint64_t *d_inout);
+int vsp_fr_multiply_by_coset(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *a_inout);
+int vsp_fr_multiply_by_coset_dev(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *d_inout);
+int vsp_fr_divide_by_z_on_coset(vsp_ctx *ctx, uint64_t m, uint64_t *a_inout);
+int vsp_fr_divide_by_z_on_coset_dev(vsp_ctx *ctx, uint64_t m, uint64_t *d_inout);
+
+/* ---- multiexp ------------------------------------------------------------------------------- */
+/* one-shot: sum_i scalars[i] * bases[i] */
+int vsp_g1_msm(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, const uint64_t *scalars, uint64_t *out);
+int vsp_g2_msm(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, const uint64_t *scalars, uint64_t *out);
+/* resident bases (a proving-key query): upload once, run many scalar vectors */
+int vsp_g1_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g1_bases **out);
+void vsp_g1_bases_destroy(vsp_g1_bases *b);
+int vsp_g2_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g2_bases **out);
+void vsp_g2_bases_destroy(vsp_g2_bases *b);
+/* scalars: n_scalars <= n canonical Fr (host, or device when scalars_on_device != 0); out: host affine point */
+int vsp_g1_msm_bases(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *scalars,
+                     int scalars_on_device, uint64_t *out);
+int vsp_g2_msm_bases(vsp_ctx *ctx, const vsp_g2_bases *b, uint64_t n_scalars, const uint64_t *scalars,
+                     int scalars_on_device, uint64_t *out);
+/* same, result left on the device as a canonical affine point (12 / 24 limbs) — no host synchronisation */
+int vsp_g1_msm_bases_dev(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *d_scalars,
+                         uint64_t *d_out);
+/* sum of k affine points (the join step of a point-range sharded MSM after the all-gather) */
+int vsp_g1_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
+int vsp_g2_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
+
+/* ---- R1CS, proving key, prover ------------------------------------------------------------------ */
+typedef struct {
+    uint64_t num_inputs;      /* primary_input_size */
+    uint64_t num_aux;         /* auxiliary_input_size */
+    uint64_t num_constraints;
+    /* CSR per matrix; column 0 is the constant-one variable */
+    const uint64_t *a_row, *b_row, *c_row; /* num_constraints + 1 */
+    const uint32_t *a_col, *b_col, *c_col;
+    const uint64_t *a_val, *b_val, *c_val; /* canonical Fr */
+} vsp_r1cs_t;
+
+typedef struct {
+    vsp_r1cs_t cs;
+    const uint64_t *alpha_g1, *beta_g1, *beta_g2, *delta_g1, *delta_g2;
+    const uint64_t *A_query; /* num_inputs + num_aux + 1 G1 */
+    uint64_t B_count;        /* sparse B_query: sorted variable indices and their (G2, G1) pairs */
+    const uint32_t *B_idx;
+    const uint64_t *B_g2, *B_g1;
+    uint64_t H_count; /* >= m - 1 */
+    const uint64_t *H_query;
+    const uint64_t *L_query; /* num_aux G1 */
+} vsp_proving_key_t;
+
+typedef struct {
+    uint64_t msg_size;
+    const uint64_t *delta_g1;
+    const uint64_t *delta_s_g1; /* msg_size G1 */
+    const uint64_t *t_g1;       /* msg_size G1 */
+    const uint64_t *t_g2;       /* msg_size + 1 G2 (not used by encrypt / rerandomize) */
+    const uint64_t *delta_sum_s_g1;
+    const uint64_t *gamma_inverse_sum_s_g1;
+} vsp_saver_pubkey_t;
+
+int vsp_pk_load(vsp_ctx *ctx, const vsp_proving_key_t *desc, vsp_pk **out);
+void vsp_pk_destroy(vsp_pk *pk);
+uint64_t vsp_pk_domain_size(const vsp_pk *pk);
+
+/* r1cs_to_qap::witness_map(cs, primary, auxiliary, 0, 0, 0): h_out receives coefficients_for_H[0..m] (m + 1 Fr) */
+int vsp_witness_map(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux, uint64_t *h_out);
+
+/* proof = g_A (12 limbs) | g_B (24 limbs) | g_C (12 limbs).  r_saver / gamma_inverse_sum_s_g1 both non-NULL selects
+ * proving_mode::encrypted_input: g_C += r_saver * gamma_inverse_sum_s_g1. */
+int vsp_prove(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux, const uint64_t r[4],
+              const uint64_t s[4], const uint64_t *r_saver, const uint64_t *gamma_inverse_sum_s_g1,
+              uint64_t *out_proof);
+/* k independent ballots on one proving key: witnesses laid out ballot-major; rs = (r, s, r_saver) per ballot
+ * (r_saver ignored when gamma_inverse_sum_s_g1 is NULL).  out_proofs: k * 48 limbs. */
+int vsp_prove_batch(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const uint64_t *primary, const uint64_t *aux,
+                    const uint64_t *rs, const uint64_t *gamma_inverse_sum_s_g1, uint64_t *out_proofs);
+
+/* SAVER: ciphertext (msg_size + 2 G1) and the encrypted_input proof in one call */
+int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
+                      const uint64_t *msg, const uint64_t *primary, const uint64_t *aux, const uint64_t r_saver[4],
+                      const uint64_t r[4], const uint64_t s[4], uint64_t *out_ct, uint64_t *out_proof);
+int vsp_saver_ciphertext(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
+                         const uint64_t *msg, const uint64_t r_saver[4], uint64_t *out_ct);
+/* rnd = r | z1 | z2 */
+int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
+                          const uint64_t *ct_in, const uint64_t *proof_in, uint64_t *ct_out, uint64_t *proof_out);
+
+/* ---- measurement helpers ---------------------------------------------------------------------- */
+/* sustained 32-bit multiply-add issue rate: runs a dependent-free IMAD.WIDE carry-chain kernel on all SMs for
+ * `iters` rounds and returns multiply-adds per second (the P_int roofline denominator). */
+int vsp_measure_imad_rate(vsp_ctx *ctx, uint64_t iters, double *mads_per_second);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSP_B200_H */

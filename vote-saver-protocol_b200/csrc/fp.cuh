@@ -1,0 +1,367 @@
+// fp.cuh — Montgomery prime-field arithmetic on 32-bit limbs for sm_100a (BLS12-381 Fq: 12 limbs, Fr: 8 limbs).
+//
+// Replaces the arithmetic of crypto3-algebra's `fields::bls12_fq<381>` / `bls12_fr<381>` value types (un-vendored
+// submodule crypto3-algebra @ e4fa2c5e, /root/reference/.SUBMODULES.json:17; used through every `*`, `+`,
+// `.inversed()`, `.pow()` in /root/reference/libs/math/include/nil/crypto3/math/domains/*.hpp).
+//
+// Multiplication keeps two partial accumulators (products landing on even / odd 32-bit columns) so every
+// mad.lo.cc / madc.hi.cc pair is a 64-bit-aligned multiply-accumulate that ptxas maps to IMAD.WIDE.U32 with the
+// carry in a predicate; the Montgomery shift by one limb is a role swap of the two accumulators.
+#pragma once
+#include <cstdint>
+
+#include "bls12_381_constants.cuh"
+
+namespace vsp {
+
+#define VSP_DEV __device__ __forceinline__
+
+#ifdef VSP_HOST_EMUL
+// Host emulation of the PTX carry-chain instructions (tests/host_emul: the same templates are compiled with g++ so
+// the limb schedules can be checked against the oracle without a GPU).  CC is the PTX condition-code carry flag.
+namespace ptx {
+static thread_local uint32_t CC = 0;
+inline uint32_t mul_lo(uint32_t a, uint32_t b) { return a * b; }
+inline uint32_t mul_hi(uint32_t a, uint32_t b) { return (uint32_t)((uint64_t(a) * b) >> 32); }
+inline uint32_t acc3(uint64_t x, uint64_t c, uint64_t cin, bool set) {
+    const uint64_t t = x + c + cin;
+    if (set) CC = (uint32_t)(t >> 32);
+    return (uint32_t)t;
+}
+inline uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { return acc3(mul_lo(a, b), c, 0, true); }
+inline uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { return acc3(mul_lo(a, b), c, CC, true); }
+inline uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { return acc3(mul_hi(a, b), c, CC, true); }
+inline uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { return acc3(mul_hi(a, b), c, CC, false); }
+inline uint32_t add_cc(uint32_t a, uint32_t b) { return acc3(a, b, 0, true); }
+inline uint32_t addc_cc(uint32_t a, uint32_t b) { return acc3(a, b, CC, true); }
+inline uint32_t addc(uint32_t a, uint32_t b) { return acc3(a, b, CC, false); }
+inline uint32_t sub3(uint64_t a, uint64_t b, uint64_t bin, bool set) {
+    const uint64_t t = a - b - bin;
+    if (set) CC = (uint32_t)(t >> 63);
+    return (uint32_t)t;
+}
+inline uint32_t sub_cc(uint32_t a, uint32_t b) { return sub3(a, b, 0, true); }
+inline uint32_t subc_cc(uint32_t a, uint32_t b) { return sub3(a, b, CC, true); }
+inline uint32_t subc(uint32_t a, uint32_t b) { return sub3(a, b, CC, false); }
+}  // namespace ptx
+#else
+namespace ptx {
+VSP_DEV uint32_t mul_lo(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("mul.lo.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t mul_hi(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm volatile("mad.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+VSP_DEV uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+VSP_DEV uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+VSP_DEV uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm volatile("madc.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+VSP_DEV uint32_t add_cc(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t addc_cc(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t addc(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("addc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t sub_cc(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t subc_cc(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+VSP_DEV uint32_t subc(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm volatile("subc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+}  // namespace ptx
+#endif
+
+struct FqCfg {
+    static constexpr int N = VSP_FQ_LIMBS;
+    static constexpr uint32_t INV = VSP_FQ_INV;
+    __host__ __device__ static constexpr uint32_t mod(int i) { return VSP_FQ_MOD(i); }
+    __host__ __device__ static constexpr uint32_t r1(int i) { return VSP_FQ_R1(i); }
+    __host__ __device__ static constexpr uint32_t r2(int i) { return VSP_FQ_R2(i); }
+};
+struct FrCfg {
+    static constexpr int N = VSP_FR_LIMBS;
+    static constexpr uint32_t INV = VSP_FR_INV;
+    __host__ __device__ static constexpr uint32_t mod(int i) { return VSP_FR_MOD(i); }
+    __host__ __device__ static constexpr uint32_t r1(int i) { return VSP_FR_R1(i); }
+    __host__ __device__ static constexpr uint32_t r2(int i) { return VSP_FR_R2(i); }
+};
+
+template <class C>
+struct alignas(16) Fp {
+    static constexpr int N = C::N;
+    uint32_t l[C::N];
+
+    VSP_DEV static Fp zero() {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) r.l[i] = 0;
+        return r;
+    }
+    // Montgomery form of 1
+    VSP_DEV static Fp one() {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) r.l[i] = C::r1(i);
+        return r;
+    }
+    VSP_DEV static Fp r2() {
+        Fp r;
+#pragma unroll
+        for (int i = 0; i < N; ++i) r.l[i] = C::r2(i);
+        return r;
+    }
+    VSP_DEV bool is_zero() const {
+        uint32_t x = 0;
+#pragma unroll
+        for (int i = 0; i < N; ++i) x |= l[i];
+        return x == 0;
+    }
+    VSP_DEV bool operator==(const Fp& o) const {
+        uint32_t x = 0;
+#pragma unroll
+        for (int i = 0; i < N; ++i) x |= l[i] ^ o.l[i];
+        return x == 0;
+    }
+    VSP_DEV bool operator!=(const Fp& o) const { return !(*this == o); }
+};
+
+// r = (a >= p) ? a - p : a      (a < 2p)
+template <class C>
+VSP_DEV void fp_reduce_once(Fp<C>& a) {
+    constexpr int N = C::N;
+    uint32_t t[N];
+    t[0] = ptx::sub_cc(a.l[0], C::mod(0));
+#pragma unroll
+    for (int i = 1; i < N; ++i) t[i] = ptx::subc_cc(a.l[i], C::mod(i));
+    uint32_t borrow = ptx::subc(0u, 0u);  // 0xffffffff if a < p
+#pragma unroll
+    for (int i = 0; i < N; ++i) a.l[i] = borrow ? a.l[i] : t[i];
+}
+
+template <class C>
+VSP_DEV Fp<C> fp_add(const Fp<C>& a, const Fp<C>& b) {
+    constexpr int N = C::N;
+    Fp<C> r;
+    r.l[0] = ptx::add_cc(a.l[0], b.l[0]);
+#pragma unroll
+    for (int i = 1; i < N - 1; ++i) r.l[i] = ptx::addc_cc(a.l[i], b.l[i]);
+    r.l[N - 1] = ptx::addc(a.l[N - 1], b.l[N - 1]);  // 2p < 2^(32N): no carry out
+    fp_reduce_once(r);
+    return r;
+}
+
+template <class C>
+VSP_DEV Fp<C> fp_sub(const Fp<C>& a, const Fp<C>& b) {
+    constexpr int N = C::N;
+    Fp<C> r;
+    r.l[0] = ptx::sub_cc(a.l[0], b.l[0]);
+#pragma unroll
+    for (int i = 1; i < N; ++i) r.l[i] = ptx::subc_cc(a.l[i], b.l[i]);
+    uint32_t mask = ptx::subc(0u, 0u);  // all ones on borrow
+    r.l[0] = ptx::add_cc(r.l[0], C::mod(0) & mask);
+#pragma unroll
+    for (int i = 1; i < N - 1; ++i) r.l[i] = ptx::addc_cc(r.l[i], C::mod(i) & mask);
+    r.l[N - 1] = ptx::addc(r.l[N - 1], C::mod(N - 1) & mask);
+    return r;
+}
+
+template <class C>
+VSP_DEV Fp<C> fp_neg(const Fp<C>& a) {
+    constexpr int N = C::N;
+    Fp<C> r;
+    r.l[0] = ptx::sub_cc(C::mod(0), a.l[0]);
+#pragma unroll
+    for (int i = 1; i < N - 1; ++i) r.l[i] = ptx::subc_cc(C::mod(i), a.l[i]);
+    r.l[N - 1] = ptx::subc(C::mod(N - 1), a.l[N - 1]);
+    const bool z = a.is_zero();
+#pragma unroll
+    for (int i = 0; i < N; ++i) r.l[i] = z ? 0u : r.l[i];
+    return r;
+}
+
+template <class C>
+VSP_DEV Fp<C> fp_dbl(const Fp<C>& a) {
+    return fp_add(a, a);
+}
+
+// One Montgomery reduction column: m = E[0] * INV;  O += m * p_odd;  E += m * p_even  (E[0] becomes 0).
+template <class C>
+VSP_DEV void mont_reduce_column(uint32_t (&E)[C::N], uint32_t (&O)[C::N]) {
+    constexpr int N = C::N;
+    const uint32_t m = E[0] * C::INV;
+    O[0] = ptx::mad_lo_cc(C::mod(1), m, O[0]);
+    O[1] = ptx::madc_hi_cc(C::mod(1), m, O[1]);
+#pragma unroll
+    for (int k = 2; k < N - 2; k += 2) {
+        O[k] = ptx::madc_lo_cc(C::mod(k + 1), m, O[k]);
+        O[k + 1] = ptx::madc_hi_cc(C::mod(k + 1), m, O[k + 1]);
+    }
+    O[N - 2] = ptx::madc_lo_cc(C::mod(N - 1), m, O[N - 2]);
+    O[N - 1] = ptx::madc_hi(C::mod(N - 1), m, O[N - 1]);
+    E[0] = ptx::mad_lo_cc(C::mod(0), m, E[0]);
+    E[1] = ptx::madc_hi_cc(C::mod(0), m, E[1]);
+#pragma unroll
+    for (int k = 2; k < N; k += 2) {
+        E[k] = ptx::madc_lo_cc(C::mod(k), m, E[k]);
+        E[k + 1] = ptx::madc_hi_cc(C::mod(k), m, E[k + 1]);
+    }
+    O[N - 1] = ptx::addc(O[N - 1], 0u);
+}
+
+// Montgomery product a * b / 2^(32N) mod p, inputs and output fully reduced.
+template <class C>
+VSP_DEV Fp<C> fp_mul(const Fp<C>& a, const Fp<C>& b) {
+    constexpr int N = C::N;
+    static_assert(N % 2 == 0, "even limb count expected");
+    uint32_t E[N], O[N];
+    {
+        const uint32_t bi = b.l[0];
+#pragma unroll
+        for (int k = 0; k < N; k += 2) {
+            E[k] = ptx::mul_lo(a.l[k], bi);
+            E[k + 1] = ptx::mul_hi(a.l[k], bi);
+            O[k] = ptx::mul_lo(a.l[k + 1], bi);
+            O[k + 1] = ptx::mul_hi(a.l[k + 1], bi);
+        }
+        mont_reduce_column<C>(E, O);
+    }
+#pragma unroll
+    for (int i = 1; i < N; ++i) {
+        const uint32_t bi = b.l[i];
+        uint32_t nO[N];
+        // shift by one limb: new even accumulator = O (+ E[1] at column 0), new odd accumulator = E >> 64
+        O[0] = ptx::add_cc(O[0], E[1]);
+#pragma unroll
+        for (int k = 0; k < N - 2; k += 2) {
+            nO[k] = ptx::madc_lo_cc(a.l[k + 1], bi, E[k + 2]);
+            nO[k + 1] = ptx::madc_hi_cc(a.l[k + 1], bi, E[k + 3]);
+        }
+        nO[N - 2] = ptx::madc_lo_cc(a.l[N - 1], bi, 0u);
+        nO[N - 1] = ptx::madc_hi(a.l[N - 1], bi, 0u);
+        O[0] = ptx::mad_lo_cc(a.l[0], bi, O[0]);
+        O[1] = ptx::madc_hi_cc(a.l[0], bi, O[1]);
+#pragma unroll
+        for (int k = 2; k < N; k += 2) {
+            O[k] = ptx::madc_lo_cc(a.l[k], bi, O[k]);
+            O[k + 1] = ptx::madc_hi_cc(a.l[k], bi, O[k + 1]);
+        }
+        nO[N - 1] = ptx::addc(nO[N - 1], 0u);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+            E[k] = O[k];
+            O[k] = nO[k];
+        }
+        mont_reduce_column<C>(E, O);
+    }
+    Fp<C> r;
+    r.l[0] = ptx::add_cc(O[0], E[1]);
+#pragma unroll
+    for (int k = 1; k < N - 1; ++k) r.l[k] = ptx::addc_cc(O[k], E[k + 1]);
+    r.l[N - 1] = ptx::addc(O[N - 1], 0u);
+    fp_reduce_once(r);
+    return r;
+}
+
+template <class C>
+VSP_DEV Fp<C> fp_sqr(const Fp<C>& a) {
+    return fp_mul(a, a);
+}
+
+template <class C>
+VSP_DEV Fp<C> fp_to_mont(const Fp<C>& a) {
+    return fp_mul(a, Fp<C>::r2());
+}
+template <class C>
+VSP_DEV Fp<C> fp_from_mont(const Fp<C>& a) {
+    Fp<C> one = Fp<C>::zero();
+    one.l[0] = 1;
+    return fp_mul(a, one);
+}
+
+// a^(p-2) by plain square-and-multiply over the constant exponent bits (not on the hot path: batch inversion
+// amortises it).
+template <class C>
+__device__ __noinline__ Fp<C> fp_inv(const Fp<C>& a) {
+    constexpr int N = C::N;
+    Fp<C> acc = Fp<C>::one();
+    Fp<C> base = a;
+    uint32_t borrow = 2;  // exponent = p - 2
+    for (int i = 0; i < N; ++i) {
+        uint32_t limb = C::mod(0);
+        // runtime-indexed modulus limb without a table: select
+#pragma unroll
+        for (int k = 0; k < N; ++k) limb = (i == k) ? C::mod(k) : limb;
+        uint32_t e = limb - borrow;
+        borrow = (limb < borrow) ? 1u : 0u;
+        for (int bit = 0; bit < 32; ++bit) {
+            if ((e >> bit) & 1u) acc = fp_mul(acc, base);
+            base = fp_sqr(base);
+        }
+    }
+    return acc;
+}
+
+using Fq = Fp<FqCfg>;
+using Fr = Fp<FrCfg>;
+
+// 16-byte vector loads/stores of whole elements (global or shared); p must be 16-byte aligned
+template <class C>
+VSP_DEV Fp<C> fp_load(const void* p) {
+    Fp<C> r;
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+#pragma unroll
+    for (int i = 0; i < C::N / 4; ++i) {
+        uint4 v = q[i];
+        r.l[4 * i] = v.x;
+        r.l[4 * i + 1] = v.y;
+        r.l[4 * i + 2] = v.z;
+        r.l[4 * i + 3] = v.w;
+    }
+    return r;
+}
+template <class C>
+VSP_DEV void fp_store(void* p, const Fp<C>& a) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+#pragma unroll
+    for (int i = 0; i < C::N / 4; ++i) q[i] = make_uint4(a.l[4 * i], a.l[4 * i + 1], a.l[4 * i + 2], a.l[4 * i + 3]);
+}
+
+}  // namespace vsp
