@@ -43,6 +43,13 @@
 extern "C" {
 #endif
 
+/* exported from libvsp_b200.so (the library is built with -fvisibility=hidden) */
+#if defined(__GNUC__)
+#define VSP_API __attribute__((visibility("default")))
+#else
+#define VSP_API
+#endif
+
 #define VSP_OK 0
 #define VSP_E_INVALID (-1)    /* bad argument (the reference throws std::invalid_argument / asserts) */
 #define VSP_E_NO_DEVICE (-2)  /* no CUDA device / context creation failed */
@@ -62,45 +69,50 @@ typedef struct vsp_pk vsp_pk;
 /* ---- context ------------------------------------------------------------------------------ */
 /* cuda_stream: an existing CUstream / cudaStream_t to launch on (e.g. torch's current stream), or NULL for a
  * private non-blocking stream. */
-int vsp_ctx_create(int device, void *cuda_stream, vsp_ctx **out);
-void vsp_ctx_destroy(vsp_ctx *ctx);
-const char *vsp_last_error(const vsp_ctx *ctx);
-int vsp_ctx_synchronize(vsp_ctx *ctx);
+VSP_API int vsp_ctx_create(int device, void *cuda_stream, vsp_ctx **out);
+VSP_API void vsp_ctx_destroy(vsp_ctx *ctx);
+VSP_API const char *vsp_last_error(const vsp_ctx *ctx);
+VSP_API int vsp_ctx_synchronize(vsp_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
-uint64_t vsp_ctx_launch_count(const vsp_ctx *ctx);
-const char *vsp_version(void);
+VSP_API uint64_t vsp_ctx_launch_count(const vsp_ctx *ctx);
+VSP_API const char *vsp_version(void);
 
 /* ---- evaluation domains over Fr ------------------------------------------------------------ */
-int vsp_domain_plan(uint64_t min_size, int *kind, uint64_t *m);
+VSP_API int vsp_domain_plan(uint64_t min_size, int *kind, uint64_t *m);
 /* fft / inverse_fft of the domain of size m (m as returned by vsp_domain_plan).  n_in <= m values are read; the
  * basic domain zero-pads short input, the step domain's inverse_fft rejects it (VSP_E_INVALID) as the reference does. */
-int vsp_fr_fft(vsp_ctx *ctx, uint64_t m, int inverse, const uint64_t *in, uint64_t n_in, uint64_t *out);
-int vsp_fr_fft_dev(vsp_ctx *ctx, uint64_t m, int inverse, uint64_t *d_inout);
-int vsp_fr_multiply_by_coset(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *a_inout);
-int vsp_fr_multiply_by_coset_dev(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *d_inout);
-int vsp_fr_divide_by_z_on_coset(vsp_ctx *ctx, uint64_t m, uint64_t *a_inout);
-int vsp_fr_divide_by_z_on_coset_dev(vsp_ctx *ctx, uint64_t m, uint64_t *d_inout);
+VSP_API int vsp_fr_fft(vsp_ctx *ctx, uint64_t m, int inverse, const uint64_t *in, uint64_t n_in, uint64_t *out);
+VSP_API int vsp_fr_fft_dev(vsp_ctx *ctx, uint64_t m, int inverse, uint64_t *d_inout);
+VSP_API int vsp_fr_multiply_by_coset(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *a_inout);
+VSP_API int vsp_fr_multiply_by_coset_dev(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *d_inout);
+VSP_API int vsp_fr_divide_by_z_on_coset(vsp_ctx *ctx, uint64_t m, uint64_t *a_inout);
+VSP_API int vsp_fr_divide_by_z_on_coset_dev(vsp_ctx *ctx, uint64_t m, uint64_t *d_inout);
 
 /* ---- multiexp ------------------------------------------------------------------------------- */
 /* one-shot: sum_i scalars[i] * bases[i] */
-int vsp_g1_msm(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, const uint64_t *scalars, uint64_t *out);
-int vsp_g2_msm(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, const uint64_t *scalars, uint64_t *out);
+VSP_API int vsp_g1_msm(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, const uint64_t *scalars, uint64_t *out);
+VSP_API int vsp_g2_msm(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, const uint64_t *scalars, uint64_t *out);
 /* resident bases (a proving-key query): upload once, run many scalar vectors */
-int vsp_g1_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g1_bases **out);
-void vsp_g1_bases_destroy(vsp_g1_bases *b);
-int vsp_g2_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g2_bases **out);
-void vsp_g2_bases_destroy(vsp_g2_bases *b);
+VSP_API int vsp_g1_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g1_bases **out);
+VSP_API void vsp_g1_bases_destroy(vsp_g1_bases *b);
+VSP_API int vsp_g2_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g2_bases **out);
+VSP_API void vsp_g2_bases_destroy(vsp_g2_bases *b);
+/* synthetic bases for the measurement sweeps, built on the device:
+ * bases[i] = k_i * G1_generator, k_i = splitmix64(seed + i) | 1.  vsp_g1_bases_read copies a range back as canonical
+ * affine points so small cases can be checked against the oracle. */
+VSP_API int vsp_g1_bases_generate(vsp_ctx *ctx, uint64_t n, uint64_t seed, vsp_g1_bases **out);
+VSP_API int vsp_g1_bases_read(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t first, uint64_t count, uint64_t *out);
 /* scalars: n_scalars <= n canonical Fr (host, or device when scalars_on_device != 0); out: host affine point */
-int vsp_g1_msm_bases(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *scalars,
+VSP_API int vsp_g1_msm_bases(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *scalars,
                      int scalars_on_device, uint64_t *out);
-int vsp_g2_msm_bases(vsp_ctx *ctx, const vsp_g2_bases *b, uint64_t n_scalars, const uint64_t *scalars,
+VSP_API int vsp_g2_msm_bases(vsp_ctx *ctx, const vsp_g2_bases *b, uint64_t n_scalars, const uint64_t *scalars,
                      int scalars_on_device, uint64_t *out);
 /* same, result left on the device as a canonical affine point (12 / 24 limbs) — no host synchronisation */
-int vsp_g1_msm_bases_dev(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *d_scalars,
+VSP_API int vsp_g1_msm_bases_dev(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *d_scalars,
                          uint64_t *d_out);
 /* sum of k affine points (the join step of a point-range sharded MSM after the all-gather) */
-int vsp_g1_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
-int vsp_g2_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
+VSP_API int vsp_g1_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
+VSP_API int vsp_g2_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
 
 /* ---- R1CS, proving key, prover ------------------------------------------------------------------ */
 typedef struct {
@@ -135,37 +147,37 @@ typedef struct {
     const uint64_t *gamma_inverse_sum_s_g1;
 } vsp_saver_pubkey_t;
 
-int vsp_pk_load(vsp_ctx *ctx, const vsp_proving_key_t *desc, vsp_pk **out);
-void vsp_pk_destroy(vsp_pk *pk);
-uint64_t vsp_pk_domain_size(const vsp_pk *pk);
+VSP_API int vsp_pk_load(vsp_ctx *ctx, const vsp_proving_key_t *desc, vsp_pk **out);
+VSP_API void vsp_pk_destroy(vsp_pk *pk);
+VSP_API uint64_t vsp_pk_domain_size(const vsp_pk *pk);
 
 /* r1cs_to_qap::witness_map(cs, primary, auxiliary, 0, 0, 0): h_out receives coefficients_for_H[0..m] (m + 1 Fr) */
-int vsp_witness_map(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux, uint64_t *h_out);
+VSP_API int vsp_witness_map(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux, uint64_t *h_out);
 
 /* proof = g_A (12 limbs) | g_B (24 limbs) | g_C (12 limbs).  r_saver / gamma_inverse_sum_s_g1 both non-NULL selects
  * proving_mode::encrypted_input: g_C += r_saver * gamma_inverse_sum_s_g1. */
-int vsp_prove(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux, const uint64_t r[4],
+VSP_API int vsp_prove(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux, const uint64_t r[4],
               const uint64_t s[4], const uint64_t *r_saver, const uint64_t *gamma_inverse_sum_s_g1,
               uint64_t *out_proof);
 /* k independent ballots on one proving key: witnesses laid out ballot-major; rs = (r, s, r_saver) per ballot
  * (r_saver ignored when gamma_inverse_sum_s_g1 is NULL).  out_proofs: k * 48 limbs. */
-int vsp_prove_batch(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const uint64_t *primary, const uint64_t *aux,
+VSP_API int vsp_prove_batch(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const uint64_t *primary, const uint64_t *aux,
                     const uint64_t *rs, const uint64_t *gamma_inverse_sum_s_g1, uint64_t *out_proofs);
 
 /* SAVER: ciphertext (msg_size + 2 G1) and the encrypted_input proof in one call */
-int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
+VSP_API int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
                       const uint64_t *msg, const uint64_t *primary, const uint64_t *aux, const uint64_t r_saver[4],
                       const uint64_t r[4], const uint64_t s[4], uint64_t *out_ct, uint64_t *out_proof);
-int vsp_saver_ciphertext(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
+VSP_API int vsp_saver_ciphertext(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
                          const uint64_t *msg, const uint64_t r_saver[4], uint64_t *out_ct);
 /* rnd = r | z1 | z2 */
-int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
+VSP_API int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
                           const uint64_t *ct_in, const uint64_t *proof_in, uint64_t *ct_out, uint64_t *proof_out);
 
 /* ---- measurement helpers ---------------------------------------------------------------------- */
 /* sustained 32-bit multiply-add issue rate: runs a dependent-free IMAD.WIDE carry-chain kernel on all SMs for
  * `iters` rounds and returns multiply-adds per second (the P_int roofline denominator). */
-int vsp_measure_imad_rate(vsp_ctx *ctx, uint64_t iters, double *mads_per_second);
+VSP_API int vsp_measure_imad_rate(vsp_ctx *ctx, uint64_t iters, double *mads_per_second);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,122 @@
+"""GPU parity: r1cs_to_qap::witness_map, zk::prove (basic and encrypted_input modes), batched proving, and the SAVER
+ciphertext / rerandomisation through the C ABI against the oracle.  Bit-exact (every group element canonical affine).
+
+Whole-proof parity is against the oracle's restatement (PARITY UNPINNED upstream: the reference has no proof-byte
+fixtures); tests/test_oracle.py holds the generate -> prove -> verify self-consistency gate."""
+import random
+
+import numpy as np
+import pytest
+
+from oracle import cref, fixtures as fx, pyref as o
+
+from helpers import synthetic_pk_arrays, synthetic_r1cs, synthetic_saver_pub
+
+pytestmark = pytest.mark.gpu
+
+
+def _instance(nc, ni, seed, binary=False):
+    cs, primary, aux = synthetic_r1cs(nc, ni, seed, binary)
+    arr = synthetic_pk_arrays(cs, seed + 1)
+    return cs, cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4) if aux else np.zeros((0, 4), np.uint64), arr
+
+
+def _oracle_pk(arr):
+    return fx.fill_pk(cref.ProvingKeyDesc(), arr)
+
+
+# (constraints, inputs): m_req = nc + ni + 1 -> 16 basic; 24 step; 128 basic; 1024+64 step (exact); 5000 -> rounds to 5120 step
+CASES = [(10, 5, False), (18, 5, False), (97, 30, False), (1057, 30, False), (4969, 30, True)]
+
+
+@pytest.mark.parametrize("nc,ni,binary", CASES)
+def test_witness_map_matches_oracle(vsp, ctx, nc, ni, binary):
+    cs, primary, aux, arr = _instance(nc, ni, seed=nc, binary=binary)
+    pk = vsp.ProvingKey(ctx, arr)
+    want = cref.witness_map(_oracle_pk(arr).cs, primary, aux)
+    got = pk.witness_map(primary, aux)
+    assert pk.m == want.shape[0] - 1
+    assert np.array_equal(got, want)
+    pk.close()
+
+
+@pytest.mark.parametrize("nc,ni,binary", CASES)
+def test_prove_matches_oracle(vsp, ctx, nc, ni, binary):
+    cs, primary, aux, arr = _instance(nc, ni, seed=nc + 100, binary=binary)
+    pk = vsp.ProvingKey(ctx, arr)
+    rng = random.Random(nc)
+    r, s = rng.randrange(o.R), rng.randrange(o.R)
+    want = cref.groth16_prove(_oracle_pk(arr), primary, aux, r, s)
+    assert np.array_equal(pk.prove(primary, aux, r, s), want)
+    pk.close()
+
+
+def test_prove_encrypted_input_mode_and_degenerate_randomness(vsp, ctx):
+    cs, primary, aux, arr = _instance(97, 30, seed=900)
+    pub_arr, _ = synthetic_saver_pub(25, seed=901)
+    pub = vsp.SaverPublicKey(pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    opk = _oracle_pk(arr)
+    rng = random.Random(5)
+    for r, s, rs in ((rng.randrange(o.R), rng.randrange(o.R), rng.randrange(o.R)), (0, 0, 0), (1, o.R - 1, 1)):
+        want = cref.groth16_prove(opk, primary, aux, r, s, rs, pub_arr["gamma_inverse_sum_s_g1"])
+        assert np.array_equal(pk.prove(primary, aux, r, s, pub, rs), want)
+    with pytest.raises(ValueError):
+        pk.prove(primary, aux, o.R, 1)  # randomness must be reduced mod r
+    pk.close()
+
+
+def test_prove_batch_equals_single_proofs(vsp, ctx):
+    nc, ni, k = 97, 30, 5
+    cs, _, _ = synthetic_r1cs(nc, ni, 0)
+    arr = synthetic_pk_arrays(cs, 3)
+    pub_arr, _ = synthetic_saver_pub(25, seed=4)
+    pub = vsp.SaverPublicKey(pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    opk = _oracle_pk(arr)
+    prim, aux, rs = [], [], []
+    rng = random.Random(9)
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=b)  # same constraint shape, different witness
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4))
+    got = pk.prove_batch(np.stack(prim), np.stack(aux), np.stack(rs), pub)
+    for b in range(k):
+        r, s, rsv = cref.limbs_to_ints(rs[b])
+        want = cref.groth16_prove(opk, prim[b], aux[b], r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"])
+        assert np.array_equal(got[b], want), b
+    pk.close()
+
+
+def test_saver_encrypt_and_rerandomize_match_oracle(vsp, ctx):
+    """elgamal_verifiable.hpp:322-357 and :632-667 with msg_size = 25 (common.hpp:163)"""
+    nc, ni, msg_size = 97, 30, 25
+    cs, primary, aux = synthetic_r1cs(nc, ni, seed=21, binary=True)
+    arr = synthetic_pk_arrays(cs, 22)
+    pub_arr, gamma_abc_rest = synthetic_saver_pub(msg_size, seed=23)
+    gamma_abc_rest = np.ascontiguousarray(gamma_abc_rest[:msg_size])
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    msg = np.ascontiguousarray(P[:msg_size])
+    pub = vsp.SaverPublicKey(pub_arr)
+    opub = fx.fill_struct(cref.SaverPubkeyDesc(), pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    rng = random.Random(31)
+    r_saver, r, s = (rng.randrange(o.R) for _ in range(3))
+    ct, proof = pk.encrypt(pub, gamma_abc_rest, msg, P, A, r_saver, r, s)
+    want_ct = cref.saver_ciphertext(opub, gamma_abc_rest, msg, r_saver)
+    want_proof = cref.groth16_prove(_oracle_pk(arr), P, A, r, s, r_saver, pub_arr["gamma_inverse_sum_s_g1"])
+    assert np.array_equal(ct, want_ct)
+    assert np.array_equal(proof, want_proof)
+    assert np.array_equal(vsp.saver_ciphertext(ctx, pub, gamma_abc_rest, msg, r_saver), want_ct)
+    # "Plain text should be a prefix of primary input" (:336-339)
+    bad = msg.copy()
+    bad[3, 0] ^= 1
+    with pytest.raises(ValueError):
+        pk.encrypt(pub, gamma_abc_rest, bad, P, A, r_saver, r, s)
+    rnd = [rng.randrange(1, o.R) for _ in range(3)]
+    ct2, proof2 = vsp.rerandomize(ctx, pub, arr["delta_g2"], rnd, ct, proof)
+    want_ct2, want_proof2 = cref.saver_rerandomize(opub, arr["delta_g2"], rnd, want_ct, want_proof)
+    assert np.array_equal(ct2, want_ct2)
+    assert np.array_equal(proof2, want_proof2)
+    pk.close()

@@ -1,0 +1,346 @@
+"""vote-saver-protocol_b200 — host-side mirror of the crypto3 entry points of VoteSAVER's ballot-proof hot path,
+running on one B200 through the C ABI of libvsp_b200.so (include/vsp_b200.h).
+
+Reference interfaces mirrored (paths relative to NilFoundation/vote-saver-protocol @ ae4f646c):
+  make_evaluation_domain(m) -> domain.fft / inverse_fft / divide_by_z_on_coset
+        libs/math/include/nil/crypto3/math/algorithms/make_evaluation_domain.hpp:51-106,
+        libs/math/include/nil/crypto3/math/domains/evaluation_domain.hpp:78-118
+  multiply_by_coset(a, g)                       libs/math/include/nil/crypto3/math/coset.hpp:37-43
+  multiexp(bases, scalars)                      call site libs/containers/include/nil/crypto3/container/sparse_vector.hpp:258-261
+  prove(pk, primary, auxiliary, r, s[, pubkey, r_saver])
+        zk::prove<r1cs_gg_ppzksnark<..., encrypted_input>>  call site libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp:353
+  encrypt / rerandomize                         elgamal_verifiable.hpp:322-357, 632-667
+
+Data: numpy uint64 arrays of canonical little-endian limbs — Fr (n, 4); G1 affine (n, 12); G2 affine (n, 24);
+the point at infinity is all-zero.  Error behaviour follows the reference: what throws std::invalid_argument there
+raises ValueError here.  Everything computes on the GPU; without the built library or a CUDA device the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2, ProvingKeyDesc, R1CSDesc,
+                   SaverPubkeyDesc, VspError)
+
+__all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
+           "G2Bases", "ProvingKey", "SaverPublicKey", "domain_plan", "VspError", "library_path"]
+
+FR_MULTIPLICATIVE_GENERATOR = 7
+
+
+def library_path() -> str:
+    return _lib.LIB_PATH
+
+
+def _a(x, cols=None) -> np.ndarray:
+    a = np.ascontiguousarray(x, dtype=np.uint64)
+    if cols is not None and (a.ndim == 0 or a.shape[-1] != cols):
+        a = a.reshape(-1, cols)
+    return a
+
+
+def _p(a: np.ndarray):
+    return C.c_void_p(a.ctypes.data)
+
+
+def _fr(x: int) -> np.ndarray:
+    return np.frombuffer(int(x).to_bytes(32, "little"), dtype=np.uint64).copy()
+
+
+def domain_plan(min_size: int):
+    """(kind, m) of make_evaluation_domain<Fr>(min_size); ValueError where the reference throws."""
+    kind, m = C.c_int(0), C.c_uint64(0)
+    if _lib.load().vsp_domain_plan(int(min_size), C.byref(kind), C.byref(m)) != 0:
+        raise ValueError("no radix-2 family evaluation domain for size %d" % min_size)
+    return kind.value, m.value
+
+
+class Context:
+    """One GPU + one CUDA stream (vsp_ctx).  `stream`: a raw cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        rc = self._lib.vsp_ctx_create(int(device), C.c_void_p(stream) if stream else None, C.byref(h))
+        if rc != 0:
+            raise VspError(rc, "vsp_ctx_create(device=%d) failed — a CUDA device is required, there is no CPU path" % device)
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.vsp_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def check(self, rc: int):
+        if rc == 0:
+            return
+        text = (self._lib.vsp_last_error(self._h) or b"").decode("utf-8", "replace")
+        if rc in (_lib.VSP_E_INVALID, _lib.VSP_E_DOMAIN):
+            raise ValueError(text or "invalid argument")
+        raise VspError(rc, text)
+
+    def synchronize(self):
+        self.check(self._lib.vsp_ctx_synchronize(self._h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.vsp_ctx_launch_count(self._h))
+
+    def measure_imad_rate(self, iters: int = 4096) -> float:
+        out = C.c_double(0)
+        self.check(self._lib.vsp_measure_imad_rate(self._h, iters, C.byref(out)))
+        return out.value
+
+
+class EvaluationDomain:
+    """evaluation_domain<Fr> of size m as make_evaluation_domain selects it (basic_radix2 or step_radix2)."""
+
+    def __init__(self, ctx: Context, min_size: int):
+        self.ctx = ctx
+        self.kind, self.m = domain_plan(min_size)
+        if self.kind == DOMAIN_EXTENDED_RADIX2:
+            raise ValueError("extended_radix2 domain (log m = 33) is not executable")
+
+    def fft(self, a) -> np.ndarray:
+        return self._run(a, 0)
+
+    def inverse_fft(self, a) -> np.ndarray:
+        return self._run(a, 1)
+
+    def _run(self, a, inverse: int) -> np.ndarray:
+        a = _a(a, 4)
+        out = np.empty((self.m, 4), dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_fr_fft(self.ctx._h, self.m, inverse, _p(a), a.shape[0], _p(out)))
+        return out
+
+    def divide_by_z_on_coset(self, a) -> np.ndarray:
+        a = _a(a, 4).copy()
+        if a.shape[0] != self.m:
+            raise ValueError("expected a.size() == m")
+        self.ctx.check(self.ctx._lib.vsp_fr_divide_by_z_on_coset(self.ctx._h, self.m, _p(a)))
+        return a
+
+    # device-resident variants (raw device pointers, e.g. tensor.data_ptr()); stream-ordered, no synchronisation
+    def fft_dev(self, d_ptr: int, inverse: bool = False):
+        self.ctx.check(self.ctx._lib.vsp_fr_fft_dev(self.ctx._h, self.m, int(inverse), C.c_void_p(d_ptr)))
+
+
+def make_evaluation_domain(ctx: Context, min_size: int) -> EvaluationDomain:
+    return EvaluationDomain(ctx, min_size)
+
+
+def multiply_by_coset(ctx: Context, a, g: int = FR_MULTIPLICATIVE_GENERATOR) -> np.ndarray:
+    a = _a(a, 4).copy()
+    gg = _fr(g)
+    ctx.check(ctx._lib.vsp_fr_multiply_by_coset(ctx._h, a.shape[0], _p(gg), _p(a)))
+    return a
+
+
+class _Bases:
+    _G2 = False
+
+    def __init__(self, ctx: Context, bases=None, *, _handle=None, _n=0):
+        self.ctx = ctx
+        lib = ctx._lib
+        if _handle is not None:
+            self._h, self.n = _handle, _n
+            return
+        b = _a(bases, 24 if self._G2 else 12)
+        h = C.c_void_p()
+        create = lib.vsp_g2_bases_create if self._G2 else lib.vsp_g1_bases_create
+        ctx.check(create(ctx._h, b.shape[0], _p(b), C.byref(h)))
+        self._h, self.n = h, b.shape[0]
+
+    def close(self):
+        if getattr(self, "_h", None) and getattr(self.ctx, "_h", None):
+            (self.ctx._lib.vsp_g2_bases_destroy if self._G2 else self.ctx._lib.vsp_g1_bases_destroy)(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def multiexp(self, scalars) -> np.ndarray:
+        s = _a(scalars, 4)
+        out = np.zeros(24 if self._G2 else 12, dtype=np.uint64)
+        fn = self.ctx._lib.vsp_g2_msm_bases if self._G2 else self.ctx._lib.vsp_g1_msm_bases
+        self.ctx.check(fn(self.ctx._h, self._h, s.shape[0], _p(s), 0, _p(out)))
+        return out
+
+
+class G1Bases(_Bases):
+    """Device-resident G1 bases (a proving-key query)."""
+    _G2 = False
+
+    @classmethod
+    def generate(cls, ctx: Context, n: int, seed: int) -> "G1Bases":
+        """Synthetic bases k_i * G with k_i = splitmix64(seed, i) | 1, built on the device."""
+        h = C.c_void_p()
+        ctx.check(ctx._lib.vsp_g1_bases_generate(ctx._h, n, seed, C.byref(h)))
+        return cls(ctx, _handle=h, _n=n)
+
+    def read(self, first: int = 0, count: int | None = None) -> np.ndarray:
+        count = self.n - first if count is None else count
+        out = np.zeros((count, 12), dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_g1_bases_read(self.ctx._h, self._h, first, count, _p(out)))
+        return out
+
+    def multiexp_dev(self, n_scalars: int, d_scalars: int, d_out: int):
+        """scalars and the 12-limb affine result stay on the device; stream-ordered, no synchronisation."""
+        self.ctx.check(self.ctx._lib.vsp_g1_msm_bases_dev(self.ctx._h, self._h, n_scalars, C.c_void_p(d_scalars),
+                                                          C.c_void_p(d_out)))
+
+
+class G2Bases(_Bases):
+    _G2 = True
+
+
+def multiexp(ctx: Context, bases, scalars) -> np.ndarray:
+    """algebra::multiexp<BDLO12>(bases, scalars): G1 if bases are (n, 12), G2 if (n, 24).  Host buffers in, affine out."""
+    b = np.ascontiguousarray(bases, dtype=np.uint64)
+    s = _a(scalars, 4)
+    g2 = b.ndim == 2 and b.shape[1] == 24
+    b = _a(b, 24 if g2 else 12)
+    if b.shape[0] != s.shape[0]:
+        raise ValueError("bases and scalars differ in length")
+    out = np.zeros(24 if g2 else 12, dtype=np.uint64)
+    fn = ctx._lib.vsp_g2_msm if g2 else ctx._lib.vsp_g1_msm
+    ctx.check(fn(ctx._h, b.shape[0], _p(b), _p(s), _p(out)))
+    return out
+
+
+def points_sum(ctx: Context, points) -> np.ndarray:
+    p = np.ascontiguousarray(points, dtype=np.uint64)
+    g2 = p.shape[-1] == 24
+    out = np.zeros(24 if g2 else 12, dtype=np.uint64)
+    fn = ctx._lib.vsp_g2_sum if g2 else ctx._lib.vsp_g1_sum
+    ctx.check(fn(ctx._h, p.shape[0], _p(p), _p(out)))
+    return out
+
+
+def _fill(desc, arr: dict):
+    """populate a ctypes descriptor from a dict of numpy arrays / ints with the same field names"""
+    for name, ftype in desc._fields_:
+        v = arr[name]
+        if isinstance(v, dict):
+            _fill(getattr(desc, name), v)
+        elif isinstance(v, np.ndarray):
+            setattr(desc, name, v.ctypes.data_as(ftype))
+        else:
+            setattr(desc, name, v)
+    return desc
+
+
+class SaverPublicKey:
+    """elgamal_verifiable public key (elgamal_verifiable.hpp:152-157) as flat arrays."""
+
+    def __init__(self, arrays: dict):
+        self.arrays = arrays  # keeps the numpy buffers alive
+        self.desc = _fill(SaverPubkeyDesc(), arrays)
+        self.msg_size = int(arrays["msg_size"])
+
+
+class ProvingKey:
+    """r1cs_gg_ppzksnark proving key resident on the GPU (fast_proving_key.hpp:66-103 field order)."""
+
+    def __init__(self, ctx: Context, arrays: dict):
+        self.ctx = ctx
+        self.arrays = arrays
+        desc = _fill(ProvingKeyDesc(), arrays)
+        h = C.c_void_p()
+        ctx.check(ctx._lib.vsp_pk_load(ctx._h, C.byref(desc), C.byref(h)))
+        self._h = h
+        self.num_inputs = int(arrays["cs"]["num_inputs"])
+        self.num_aux = int(arrays["cs"]["num_aux"])
+        self.m = int(ctx._lib.vsp_pk_domain_size(h))
+
+    def close(self):
+        if getattr(self, "_h", None) and getattr(self.ctx, "_h", None):
+            self.ctx._lib.vsp_pk_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def witness_map(self, primary, auxiliary) -> np.ndarray:
+        """r1cs_to_qap::witness_map(cs, primary, auxiliary, 0, 0, 0).coefficients_for_H  (m + 1 values)"""
+        p, a = _a(primary, 4), _a(auxiliary, 4)
+        out = np.zeros((self.m + 1, 4), dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_witness_map(self.ctx._h, self._h, _p(p), _p(a), _p(out)))
+        return out
+
+    def prove(self, primary, auxiliary, r: int, s: int, pubkey: SaverPublicKey | None = None,
+              r_saver: int | None = None) -> np.ndarray:
+        """proof = g_A | g_B | g_C (48 limbs).  pubkey + r_saver select proving_mode::encrypted_input."""
+        p, a = _a(primary, 4), _a(auxiliary, 4)
+        out = np.zeros(48, dtype=np.uint64)
+        rr, ss = _fr(r), _fr(s)
+        if pubkey is not None:
+            rs = _fr(r_saver)
+            gi = pubkey.arrays["gamma_inverse_sum_s_g1"]
+            rc = self.ctx._lib.vsp_prove(self.ctx._h, self._h, _p(p), _p(a), _p(rr), _p(ss), _p(rs), _p(gi), _p(out))
+        else:
+            rc = self.ctx._lib.vsp_prove(self.ctx._h, self._h, _p(p), _p(a), _p(rr), _p(ss), None, None, _p(out))
+        self.ctx.check(rc)
+        return out
+
+    def prove_batch(self, primary, auxiliary, rs, pubkey: SaverPublicKey | None = None) -> np.ndarray:
+        """k ballots: primary (k, ni, 4), auxiliary (k, na, 4), rs (k, 3, 4) = (r, s, r_saver).  -> (k, 48)"""
+        p = np.ascontiguousarray(primary, dtype=np.uint64)
+        a = np.ascontiguousarray(auxiliary, dtype=np.uint64)
+        q = np.ascontiguousarray(rs, dtype=np.uint64)
+        k = q.shape[0]
+        out = np.zeros((k, 48), dtype=np.uint64)
+        gi = _p(pubkey.arrays["gamma_inverse_sum_s_g1"]) if pubkey is not None else None
+        self.ctx.check(self.ctx._lib.vsp_prove_batch(self.ctx._h, self._h, k, _p(p), _p(a), _p(q), gi, _p(out)))
+        return out
+
+    def encrypt(self, pubkey: SaverPublicKey, gamma_abc_rest, msg, primary, auxiliary, r_saver: int, r: int, s: int):
+        """encrypt_op<elgamal_verifiable>::process -> (cipher_text (msg_size + 2, 12), proof (48,))"""
+        g, mm, p, a = _a(gamma_abc_rest, 12), _a(msg, 4), _a(primary, 4), _a(auxiliary, 4)
+        ct = np.zeros((pubkey.msg_size + 2, 12), dtype=np.uint64)
+        proof = np.zeros(48, dtype=np.uint64)
+        rs, rr, ss = _fr(r_saver), _fr(r), _fr(s)
+        self.ctx.check(self.ctx._lib.vsp_saver_encrypt(self.ctx._h, self._h, C.byref(pubkey.desc), _p(g), _p(mm), _p(p),
+                                                       _p(a), _p(rs), _p(rr), _p(ss), _p(ct), _p(proof)))
+        return ct, proof
+
+
+def saver_ciphertext(ctx: Context, pubkey: SaverPublicKey, gamma_abc_rest, msg, r_saver: int) -> np.ndarray:
+    g, mm = _a(gamma_abc_rest, 12), _a(msg, 4)
+    ct = np.zeros((pubkey.msg_size + 2, 12), dtype=np.uint64)
+    rs = _fr(r_saver)
+    ctx.check(ctx._lib.vsp_saver_ciphertext(ctx._h, C.byref(pubkey.desc), _p(g), _p(mm), _p(rs), _p(ct)))
+    return ct
+
+
+def rerandomize(ctx: Context, pubkey: SaverPublicKey, delta_g2, rnd, ct, proof):
+    """rerandomize_op<elgamal_verifiable>::process; rnd = (r, z1, z2) -> (cipher_text', proof')"""
+    d2, c, pr = _a(delta_g2), _a(ct, 12), _a(proof)
+    q = np.concatenate([_fr(x) for x in rnd])
+    ct_out = np.zeros_like(c)
+    proof_out = np.zeros(48, dtype=np.uint64)
+    ctx.check(ctx._lib.vsp_saver_rerandomize(ctx._h, C.byref(pubkey.desc), _p(d2), _p(q), _p(c), _p(pr), _p(ct_out),
+                                             _p(proof_out)))
+    return ct_out, proof_out

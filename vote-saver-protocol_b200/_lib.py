@@ -1,0 +1,115 @@
+"""ctypes loader for libvsp_b200.so (the C-ABI product library, include/vsp_b200.h).
+
+There is no CPU fallback: if the library is missing, or no CUDA device is usable, the caller gets an exception.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvsp_b200.so")
+
+u64p = C.POINTER(C.c_uint64)
+u32p = C.POINTER(C.c_uint32)
+
+VSP_OK = 0
+VSP_E_INVALID = -1
+VSP_E_NO_DEVICE = -2
+VSP_E_CUDA = -3
+VSP_E_DOMAIN = -4
+VSP_E_NOMEM = -5
+
+DOMAIN_BASIC_RADIX2 = 1
+DOMAIN_EXTENDED_RADIX2 = 2
+DOMAIN_STEP_RADIX2 = 3
+
+
+class R1CSDesc(C.Structure):
+    """vsp_r1cs_t"""
+    _fields_ = [("num_inputs", C.c_uint64), ("num_aux", C.c_uint64), ("num_constraints", C.c_uint64),
+                ("a_row", u64p), ("b_row", u64p), ("c_row", u64p),
+                ("a_col", u32p), ("b_col", u32p), ("c_col", u32p),
+                ("a_val", u64p), ("b_val", u64p), ("c_val", u64p)]
+
+
+class ProvingKeyDesc(C.Structure):
+    """vsp_proving_key_t"""
+    _fields_ = [("cs", R1CSDesc),
+                ("alpha_g1", u64p), ("beta_g1", u64p), ("beta_g2", u64p), ("delta_g1", u64p), ("delta_g2", u64p),
+                ("A_query", u64p), ("B_count", C.c_uint64), ("B_idx", u32p), ("B_g2", u64p), ("B_g1", u64p),
+                ("H_count", C.c_uint64), ("H_query", u64p), ("L_query", u64p)]
+
+
+class SaverPubkeyDesc(C.Structure):
+    """vsp_saver_pubkey_t"""
+    _fields_ = [("msg_size", C.c_uint64), ("delta_g1", u64p), ("delta_s_g1", u64p), ("t_g1", u64p), ("t_g2", u64p),
+                ("delta_sum_s_g1", u64p), ("gamma_inverse_sum_s_g1", u64p)]
+
+
+# every symbol include/vsp_b200.h declares: (name, restype, argtypes)
+_vp = C.c_void_p
+_u64 = C.c_uint64
+_int = C.c_int
+SYMBOLS = [
+    ("vsp_ctx_create", _int, [_int, _vp, C.POINTER(_vp)]),
+    ("vsp_ctx_destroy", None, [_vp]),
+    ("vsp_last_error", C.c_char_p, [_vp]),
+    ("vsp_ctx_synchronize", _int, [_vp]),
+    ("vsp_ctx_launch_count", _u64, [_vp]),
+    ("vsp_version", C.c_char_p, []),
+    ("vsp_domain_plan", _int, [_u64, C.POINTER(_int), C.POINTER(_u64)]),
+    ("vsp_fr_fft", _int, [_vp, _u64, _int, _vp, _u64, _vp]),
+    ("vsp_fr_fft_dev", _int, [_vp, _u64, _int, _vp]),
+    ("vsp_fr_multiply_by_coset", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_fr_multiply_by_coset_dev", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_fr_divide_by_z_on_coset", _int, [_vp, _u64, _vp]),
+    ("vsp_fr_divide_by_z_on_coset_dev", _int, [_vp, _u64, _vp]),
+    ("vsp_g1_msm", _int, [_vp, _u64, _vp, _vp, _vp]),
+    ("vsp_g2_msm", _int, [_vp, _u64, _vp, _vp, _vp]),
+    ("vsp_g1_bases_create", _int, [_vp, _u64, _vp, C.POINTER(_vp)]),
+    ("vsp_g1_bases_destroy", None, [_vp]),
+    ("vsp_g2_bases_create", _int, [_vp, _u64, _vp, C.POINTER(_vp)]),
+    ("vsp_g2_bases_destroy", None, [_vp]),
+    ("vsp_g1_bases_generate", _int, [_vp, _u64, _u64, C.POINTER(_vp)]),
+    ("vsp_g1_bases_read", _int, [_vp, _vp, _u64, _u64, _vp]),
+    ("vsp_g1_msm_bases", _int, [_vp, _vp, _u64, _vp, _int, _vp]),
+    ("vsp_g2_msm_bases", _int, [_vp, _vp, _u64, _vp, _int, _vp]),
+    ("vsp_g1_msm_bases_dev", _int, [_vp, _vp, _u64, _vp, _vp]),
+    ("vsp_g1_sum", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_g2_sum", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_pk_load", _int, [_vp, C.POINTER(ProvingKeyDesc), C.POINTER(_vp)]),
+    ("vsp_pk_destroy", None, [_vp]),
+    ("vsp_pk_domain_size", _u64, [_vp]),
+    ("vsp_witness_map", _int, [_vp, _vp, _vp, _vp, _vp]),
+    ("vsp_prove", _int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_prove_batch", _int, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_saver_encrypt", _int, [_vp, _vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_saver_ciphertext", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp]),
+    ("vsp_saver_rerandomize", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
+]
+
+_LIB = None
+
+
+class VspError(RuntimeError):
+    def __init__(self, code: int, text: str):
+        super().__init__("vsp error %d: %s" % (code, text))
+        self.code = code
+
+
+def load():
+    """dlopen libvsp_b200.so and type every export.  Raises if the library has not been built."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (or make -C "
+                              "vote-saver-protocol_b200/csrc).  There is no CPU fallback." % LIB_PATH)
+        lib = C.CDLL(LIB_PATH)
+        for name, res, args in SYMBOLS:
+            fn = getattr(lib, name)  # AttributeError here = header/library mismatch
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+    return _LIB

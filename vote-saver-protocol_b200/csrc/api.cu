@@ -11,6 +11,8 @@ using namespace vsp;
 
 namespace vsp {
 int domain_plan(uint64_t min_size, int* kind, uint64_t* m);  // ntt.cu
+int bases_generate_g1(vsp_ctx*, cudaStream_t, uint32_t*, uint64_t, uint64_t);  // msm_g1.cu
+int bases_read_g1(vsp_ctx*, cudaStream_t, const uint32_t*, uint64_t, uint64_t, uint64_t*);
 }
 
 struct vsp_g1_bases {
@@ -222,6 +224,45 @@ void vsp_g2_bases_destroy(vsp_g2_bases* b) {
     if (!b) return;
     bases_free(&b->b);
     delete b;
+}
+
+// synthetic bases for the measurement sweeps: bases[i] = k_i * G, k_i = splitmix64(seed + i) | 1
+int vsp_g1_bases_generate(vsp_ctx* ctx, uint64_t n, uint64_t seed, vsp_g1_bases** out) {
+    if (!ctx || !out) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    vsp_g1_bases* h = new (std::nothrow) vsp_g1_bases();
+    if (!h) return VSP_E_NOMEM;
+    h->b.ctx = ctx;
+    h->b.n = n;
+    h->b.g2 = false;
+    cudaError_t e = cudaMalloc(&h->b.d_pts, n ? n * 96 : 16);
+    if (e != cudaSuccess) {
+        delete h;
+        return set_error(ctx, VSP_E_NOMEM, "cudaMalloc(%llu bases) failed: %s", (unsigned long long)n, cudaGetErrorString(e));
+    }
+    int rc = n ? bases_generate_g1(ctx, ctx->stream, h->b.d_pts, n, seed) : VSP_OK;
+    if (rc == VSP_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+        rc = set_error(ctx, VSP_E_CUDA, "bases generation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc) {
+        bases_free(&h->b);
+        delete h;
+        return rc;
+    }
+    *out = h;
+    return VSP_OK;
+}
+// canonical affine copy of bases [first, first + count) to the host
+int vsp_g1_bases_read(vsp_ctx* ctx, const vsp_g1_bases* b, uint64_t first, uint64_t count, uint64_t* out) {
+    if (!ctx || !b || (!out && count)) return VSP_E_INVALID;
+    if (first > b->b.n || count > b->b.n - first) return set_error(ctx, VSP_E_INVALID, "bases range out of bounds");
+    if (count == 0) return VSP_OK;
+    cudaSetDevice(ctx->device);
+    DevBuf d;
+    VSP_TRY(d.alloc(ctx, count * 96, ctx->stream));
+    VSP_TRY(bases_read_g1(ctx, ctx->stream, b->b.d_pts, first, count, d.as<uint64_t>()));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out, d.p, count * 96, cudaMemcpyDeviceToHost, ctx->stream));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSP_OK;
 }
 
 static int msm_bases_host_out(vsp_ctx* ctx, const BasesDev& b, uint64_t n, const uint64_t* scalars, int on_device,

@@ -14,7 +14,21 @@
 
 namespace vsp {
 
+#ifdef VSP_HOST_EMUL
+// g++ build of the same templates (tests/host_emul): CUDA keywords and the few builtins used become plain C++
+#define VSP_DEV inline
+#define __device__
+#define __host__
+#define __noinline__
+#define __forceinline__ inline
+struct uint4 {
+    uint32_t x, y, z, w;
+};
+inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return uint4{x, y, z, w}; }
+inline int __clz(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+#else
 #define VSP_DEV __device__ __forceinline__
+#endif
 
 #ifdef VSP_HOST_EMUL
 // Host emulation of the PTX carry-chain instructions (tests/host_emul: the same templates are compiled with g++ so

@@ -76,9 +76,9 @@ __global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, M
         d += carry;
         uint32_t key = KEY_NONE;
         if (d > half) {
-            const uint32_t mag = (1u << p.c) - d;  // negative digit
+            const uint32_t mag = (1u << p.c) - d;  // negative digit; d == 2^c (all-ones + carry) is digit 0, carry 1
             carry = 1;
-            key = ((w << p.nb_log) + mag - 1u) | 0x80000000u;
+            if (mag) key = ((w << p.nb_log) + mag - 1u) | 0x80000000u;
         } else {
             carry = 0;
             if (d) key = (w << p.nb_log) + d - 1u;
