@@ -1,0 +1,418 @@
+#!/usr/bin/env python3
+"""bench.py — ballot proofs/s of the B200 Groth16 (encrypted_input) prover, one JSON line (contract in DESIGN.md §6).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--ballots B] [--impl b200|reference]
+  torchrun --nproc-per-node N bench.py --gpus N ...        (one rank per GPU; ballots shard proof-per-GPU, no collective)
+
+A step = one pass of the hot path over one batch of B synthetic ballots per GPU (weak scaling).  The workload is
+BASELINE.json configs[3] ("batched ballot proving ... sharded proof-per-GPU") on the depth-16 stand-in circuit of
+configs[2]: 65,505 constraints + 30 primary inputs -> evaluation domain 2^16 (tools/workload.py).
+  value  : proofs/s with the assignments already resident in HBM (vsp_prove_batch_dev), device-timed, max over ranks
+  e2e    : the same through the host-buffer C-ABI call (vsp_prove_batch): pinned host witnesses in, proofs out,
+           H2D/D2H inside the timed region
+  roofline / kernels : per-kernel-class device times measured live with CUDA events inside the library
+  cpu_baseline / --impl reference : the CPU oracle's restatement of the reference prover on the host cores
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+METRIC = "ballot proofs/sec (Groth16 BLS12-381, encrypted_input mode)"
+UNIT = "proofs/s"
+NUM_CONSTRAINTS = (1 << 16) - 31
+NUM_INPUTS = 30
+MSG_SIZE = 25
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--ballots", type=int, default=16, help="ballots per GPU per step")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--constraints", type=int, default=NUM_CONSTRAINTS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the MSM 2^20 / NTT 2^20 side measurements")
+    return ap.parse_args()
+
+
+def workload_config(args, world):
+    return {"workload": "batched encrypted-input ballot proofs (BASELINE configs[3] on the configs[2] depth-16 stand-in "
+                        "circuit), proof-per-GPU",
+            "constraints": args.constraints, "primary_inputs": NUM_INPUTS, "msg_size": MSG_SIZE,
+            "domain": "basic_radix2 2^16" if args.constraints == NUM_CONSTRAINTS else "see constraints",
+            "ballots_per_gpu_per_step": args.ballots, "ballots_per_step": args.ballots * world,
+            "witness": "all-bits XOR chain (r1cs_examples.hpp:154-210 shape), distinct per ballot",
+            "proving_key": "synthetic seeded bases k_i*G (shape-only)",
+            "l2": "per-step working set (5 query tables 36 MiB + per-ballot vectors) streams through L2; inputs of "
+                  "consecutive ballots differ; no explicit flush"}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the B200 arm
+# ---------------------------------------------------------------------------------------------------------
+def dist_setup(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(local)
+    return world, rank, local
+
+
+def max_over_ranks(x: float, world: int) -> float:
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier(world: int):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def run_b200(args):
+    import torch
+    import workload as wl
+    world, rank, local = dist_setup(args)
+    vsp = importlib.import_module("vote-saver-protocol_b200")
+    stream = torch.cuda.Stream()
+    ctx = vsp.Context(local, stream.cuda_stream)
+    B, K, W = args.ballots, args.steps, max(args.warmup, 3)
+
+    # ---- setup (untimed): circuit, proving key, witnesses ----------------------------------------------
+    cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
+    _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
+    pk = vsp.ProvingKey(ctx, wl.proving_key_arrays(vsp, ctx, cs, m, seed=7))
+    pub_arr, _gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
+    pub = vsp.SaverPublicKey(pub_arr)
+    ni, na = cs["num_inputs"], cs["num_aux"]
+    prim = torch.empty((B, ni, 4), dtype=torch.int64).pin_memory()
+    aux = torch.empty((B, na, 4), dtype=torch.int64).pin_memory()
+    proofs_host = torch.empty((B, 48), dtype=torch.int64).pin_memory()
+    prim_np, aux_np = prim.numpy().view(np.uint64), aux.numpy().view(np.uint64)
+    for b in range(B):
+        p, a = wl.ballot_witness(cs, seed=rank * 100003 + b)
+        prim_np[b], aux_np[b] = p, a
+    rs = wl.random_fr(3 * B, seed=rank + 99).reshape(B, 3, 4)
+    assign = torch.zeros((B, ni + na + 1, 4), dtype=torch.int64, device="cuda")
+    assign[:, 0, 0] = 1
+    assign[:, 1:ni + 1] = prim.cuda()
+    assign[:, ni + 1:] = aux.cuda()
+    d_proofs = torch.zeros((B, 48), dtype=torch.int64, device="cuda")
+    lib, h_ctx, h_pk = ctx._lib, ctx._h, pk._h
+
+    def step_dev():
+        pk.prove_batch_dev(B, assign.data_ptr(), rs, d_proofs.data_ptr(), pub)
+
+    def step_e2e():
+        out = pk.prove_batch(prim_np, aux_np, rs, pub)  # host buffers in, host proofs out (synchronises)
+        return out
+
+    # ---- device-resident timing ---------------------------------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            step_dev()
+        barrier(world)
+        ctx.profile_enable(True)
+        launches0 = ctx.launch_count
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(world)
+        e0.record(stream)
+        for _ in range(K):
+            step_dev()
+        e1.record(stream)
+        barrier(world)
+        ms_dev = e0.elapsed_time(e1)
+        clocks = sampler.stop() if rank == 0 else None
+        launches = ctx.launch_count - launches0
+        prof = ctx.profile_read()
+        ctx.profile_enable(False)
+    proofs_dev = d_proofs.cpu().numpy().view(np.uint64)
+    ms_dev = max_over_ranks(ms_dev, world)
+
+    # ---- end-to-end timing through the host-buffer C-ABI call ---------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(2):
+            step_e2e()
+        barrier(world)
+        t0 = time.perf_counter()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(K):
+            proofs_e2e = step_e2e()
+        f1.record(stream)
+        barrier(world)
+        ms_e2e = max(f0.elapsed_time(f1), (time.perf_counter() - t0) * 1e3)
+    ms_e2e = max_over_ranks(ms_e2e, world)
+    same = bool(np.array_equal(proofs_e2e, proofs_dev))
+
+    return dict(world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
+                clocks=clocks, launches=launches, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
+                proofs=proofs_dev, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes), d2h=int(B * 384), stream=stream)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU legs (the only places that touch oracle/): cpu_baseline of the b200 arm and the --impl reference arm
+# ---------------------------------------------------------------------------------------------------------
+def cpu_prover(args, cs_arrays, pk_arrays, prim, aux, rs, pub_arr, n_proofs: int):
+    """Times the oracle's restatement of the reference prover (witness_map + 5 BDLO12 multiexps + assembly, the
+    encrypted_input adjustment) on `n_proofs` ballots with every host core (chunked multiexp as the reference's
+    MULTICORE hook intends, sparse_vector.hpp:224-229).  Returns (seconds, proofs, cores)."""
+    from oracle import cref, fixtures as fx
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        pass
+    cref.lib().orc_set_num_threads(cores)
+    desc = fx.fill_pk(cref.ProvingKeyDesc(), pk_arrays)
+    out = []
+    t0 = time.perf_counter()
+    for b in range(n_proofs):
+        r, s, rsv = cref.limbs_to_ints(rs[b])
+        out.append(cref.groth16_prove(desc, np.ascontiguousarray(prim[b]), np.ascontiguousarray(aux[b]), r, s, rsv,
+                                      pub_arr["gamma_inverse_sum_s_g1"], chunks=cores))
+    return time.perf_counter() - t0, np.stack(out), cores
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path.  crypto3 itself cannot be built here (Boost and the algebra / zk /
+    multiprecision submodules are absent: DESIGN.md), so this times oracle/'s restatement (kind = "port")."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    import workload as wl
+    import torch
+    vsp = importlib.import_module("vote-saver-protocol_b200")
+    # the proving key is synthetic (seeded bases); it is built with the device generator when a GPU is present so both
+    # arms use identical keys
+    ctx = vsp.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
+    _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
+    pk_arr = wl.proving_key_arrays(vsp, ctx, cs, m, seed=7)
+    pub_arr, _ = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
+    ctx.close()
+    n = 1  # one ballot per step: a bounded sample of the B-ballot batch
+    prim, aux = [], []
+    for b in range(n):
+        p, a = wl.ballot_witness(cs, seed=b)
+        prim.append(p)
+        aux.append(a)
+    rs = wl.random_fr(3 * n, seed=99).reshape(n, 3, 4)
+    K, W = args.steps, min(args.warmup, 1)
+    for _ in range(W):
+        cpu_prover(args, cs, pk_arr, prim, aux, rs, pub_arr, n)
+    total = 0.0
+    cores = 1
+    for _ in range(K):
+        sec, _, cores = cpu_prover(args, cs, pk_arr, prim, aux, rs, pub_arr, n)
+        total += sec
+    value = n * K / total
+    sample = "%d ballot per step (of the %d-ballot batch), %d steps" % (n, args.ballots * world, K)
+    return {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": K,
+            "warmup": W, "ms_per_step": total / K * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32 limbs (Fq 12x32, Fr 8x32 Montgomery)" if False else "u64 limbs (CPU)",
+            "data": "synthetic", "config": workload_config(args, world),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "CPU restatement of crypto3's prover (oracle/vsp_oracle.c); crypto3 itself is unbuildable here"}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# side measurements named by BASELINE.json's metric: G1 MSM 2^20 and Fr NTT 2^20 latency, device-resident
+# ---------------------------------------------------------------------------------------------------------
+def msm_reference_mads(n: int) -> float:
+    """W_msm(N) of SURVEY.md 8d: the reference algorithm's adds x 11 Fq mul x 300 multiply-adds"""
+    lg = max(int(np.floor(np.log2(n))), 0)
+    c = max(lg - (lg // 3 - 2), 1)
+    groups = -(-255 // c)
+    adds = groups * n + groups * (1 << (c + 1)) + 255
+    return adds * 11.0 * 300.0
+
+
+def run_extras(res, peaks, p_int):
+    import torch
+    import workload as wl
+    vsp, ctx, stream = res["vsp"], res["ctx"], res["stream"]
+    out = {}
+
+    def timed(fn, iters, warm=3):
+        with torch.cuda.stream(stream):
+            for _ in range(warm):
+                fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(iters):
+                fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / iters
+
+    n = 1 << 20
+    # NTT 2^20: 8 distinct 32 MiB vectors round-robin (256 MiB > 126 MiB L2) so no launch finds its input in L2
+    bufs = [torch.from_numpy(wl.random_fr(n, 2 + i).view(np.int64)).cuda() for i in range(8)]
+    dom = vsp.make_evaluation_domain(ctx, n)
+    it = [0]
+
+    def ntt():
+        dom.fft_dev(bufs[it[0] % 8].data_ptr(), False)
+        it[0] += 1
+
+    ms = timed(ntt, 40)
+    bytes_alg, mads = 2.0 * n * 32, (n / 2) * 20 * 136.0
+    out["ntt_fr_2p20"] = {"ms": ms, "l2": "8 buffers round-robin (256 MiB > L2)",
+                          "roofline_hbm": {"bound": "hbm", "achieved": bytes_alg / ms / 1e6, "peak": peaks["hbm_gbs"],
+                                           "unit": "GB/s", "frac": bytes_alg / ms / 1e6 / peaks["hbm_gbs"]},
+                          "roofline_int": {"bound": "int32-mad", "achieved": mads / ms / 1e9, "peak": p_int / 1e12,
+                                           "unit": "TMAD/s", "frac": mads / ms / 1e9 / (p_int / 1e12)}}
+    del bufs
+    # G1 MSM 2^20: 96 MiB of bases + 32 MiB of scalars, two scalar vectors alternating
+    h = vsp.G1Bases.generate(ctx, n, 1234)
+    sc = [torch.from_numpy(wl.random_fr(n, 1 + i).view(np.int64)).cuda() for i in range(2)]
+    o = torch.zeros(12, dtype=torch.int64, device="cuda")
+    jt = [0]
+
+    def msm():
+        h.multiexp_dev(n, sc[jt[0] % 2].data_ptr(), o.data_ptr())
+        jt[0] += 1
+
+    ms = timed(msm, 10, warm=3)
+    w = msm_reference_mads(n)
+    out["msm_g1_2p20"] = {"ms": ms, "l2": "inputs 128 MiB > L2",
+                          "roofline_int": {"bound": "int32-mad", "achieved": w / ms / 1e9, "peak": p_int / 1e12,
+                                           "unit": "TMAD/s", "frac": w / ms / 1e9 / (p_int / 1e12),
+                                           "work": "reference-algorithm multiply-adds W_msm(2^20) = %.3g" % w}}
+    h.close()
+    return out
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return {"hbm_gbs": float(d["hbm_gbs"]), "source": "MEASURED_PEAKS.json"}
+    return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        line = run_reference(args)
+        if line is not None:
+            print(json.dumps(line))
+        return
+    res = run_b200(args)
+    world, rank, B, K = res["world"], res["rank"], res["B"], res["K"]
+    if rank != 0:
+        return
+    ctx = res["ctx"]
+    peaks = load_peaks()
+    p_int = ctx.measure_imad_rate(4096)  # 32x32->64 multiply-adds per second, measured now on this GPU
+    value = world * B * K / (res["ms_dev"] * 1e-3)
+    e2e = world * B * K / (res["ms_e2e"] * 1e-3)
+    prof = res["prof"]
+    tot_ms = sum(v["ms"] for v in prof.values()) or 1.0
+    kernels = {k: {"launches": v["launches"], "ms_per_step": v["ms"] / K, "share": v["ms"] / tot_ms}
+               for k, v in prof.items() if v["launches"]}
+    acc = prof["msm_accumulate_g1"]
+    ach = acc["units"] / (acc["ms"] * 1e-3) / 1e12 if acc["ms"] else 0.0
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": res["W"],
+            "ms_per_step": res["ms_dev"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32 limbs (Fq 12x32, Fr 8x32, Montgomery)", "data": "synthetic",
+            "config": workload_config(args, world),
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"],
+                    "ms_per_step": res["ms_e2e"] / K, "proofs_equal_device_path": res["same"]},
+            "gpu_launches": res["launches"], "clocks": res["clocks"],
+            "roofline": {"bound": "int32-mad", "kernel": "k_msm_accumulate<G1>", "achieved": ach, "peak": p_int / 1e12,
+                         "unit": "TMAD/s", "frac": ach / (p_int / 1e12) if p_int else None, "traffic": None,
+                         "launches": acc["launches"], "avg_launch_ms": acc["ms"] / max(acc["launches"], 1),
+                         "share_of_kernel_time": acc["ms"] / tot_ms,
+                         "peak_source": "vsp_measure_imad_rate, measured in this run (MEASURED_PEAKS.json has no "
+                                        "integer-pipe figure); HBM peak " + peaks["source"],
+                         "work": "bucket additions scheduled x 11 Fq mul x 300 MAD (SURVEY.md 8d), counted on the device"},
+            "kernels": kernels}
+    if not args.no_extras:
+        line["extras"] = run_extras(res, peaks, p_int)
+    if not args.no_cpu_baseline:
+        pk_arr = res["pk"].arrays
+        sec, cpu_proofs, cores = cpu_prover(args, res["cs"], pk_arr, res["prim"], res["aux"], res["rs"], res["pub_arr"], 1)
+        line["cpu_baseline"] = {"value": 1.0 / sec, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": "ballot 0 of the batch, proved once by oracle/vsp_oracle.c (%.1f s)" % sec,
+                                "gpu_proof_bit_exact": bool(np.array_equal(cpu_proofs[0], res["proofs"][0]))}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -76,6 +76,14 @@ VSP_API int vsp_ctx_synchronize(vsp_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 VSP_API uint64_t vsp_ctx_launch_count(const vsp_ctx *ctx);
 VSP_API const char *vsp_version(void);
+/* live per-kernel-class device timing (CUDA events around every launch, on the launching stream).  Classes:
+ * 0 G1 bucket accumulation, 1 G2 bucket accumulation, 2 multiexp sort (digits/scan/scatter), 3 multiexp reduction,
+ * 4 NTT, 5 QAP (R1CS evaluation, pointwise), 6 fixed-base multiples + proof assembly, 7 other.
+ * enable(on) synchronises, clears the counters and switches recording; read() returns launches, summed device ms and
+ * summed algorithmic work units (32-bit multiply-adds for classes 0/1) since enable. */
+#define VSP_KCLASS_COUNT 8
+VSP_API int vsp_ctx_profile_enable(vsp_ctx *ctx, int on);
+VSP_API int vsp_ctx_profile_read(vsp_ctx *ctx, int kclass, uint64_t *launches, double *total_ms, double *units);
 
 /* ---- evaluation domains over Fr ------------------------------------------------------------ */
 VSP_API int vsp_domain_plan(uint64_t min_size, int *kind, uint64_t *m);
@@ -102,6 +110,8 @@ VSP_API void vsp_g2_bases_destroy(vsp_g2_bases *b);
  * affine points so small cases can be checked against the oracle. */
 VSP_API int vsp_g1_bases_generate(vsp_ctx *ctx, uint64_t n, uint64_t seed, vsp_g1_bases **out);
 VSP_API int vsp_g1_bases_read(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t first, uint64_t count, uint64_t *out);
+/* the same over G2 (k_i * G2_generator), written straight to a host array of n canonical affine points */
+VSP_API int vsp_g2_points_generate(vsp_ctx *ctx, uint64_t n, uint64_t seed, uint64_t *out);
 /* scalars: n_scalars <= n canonical Fr (host, or device when scalars_on_device != 0); out: host affine point */
 VSP_API int vsp_g1_msm_bases(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *scalars,
                      int scalars_on_device, uint64_t *out);
@@ -163,6 +173,11 @@ VSP_API int vsp_prove(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, c
  * (r_saver ignored when gamma_inverse_sum_s_g1 is NULL).  out_proofs: k * 48 limbs. */
 VSP_API int vsp_prove_batch(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const uint64_t *primary, const uint64_t *aux,
                     const uint64_t *rs, const uint64_t *gamma_inverse_sum_s_g1, uint64_t *out_proofs);
+
+/* device-resident variant: d_assignments = k full assignments (1 || primary || auxiliary), num_inputs + num_aux + 1
+ * canonical Fr each; d_proofs = k * 48 limbs on the device.  Stream-ordered, no host synchronisation. */
+VSP_API int vsp_prove_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const uint64_t *d_assignments,
+                                const uint64_t *rs, const uint64_t *gamma_inverse_sum_s_g1, uint64_t *d_proofs);
 
 /* SAVER: ciphertext (msg_size + 2 G1) and the encrypted_input proof in one call */
 VSP_API int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,

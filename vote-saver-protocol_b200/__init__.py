@@ -102,6 +102,20 @@ class Context:
     def launch_count(self) -> int:
         return int(self._lib.vsp_ctx_launch_count(self._h))
 
+    KCLASSES = ("msm_accumulate_g1", "msm_accumulate_g2", "msm_sort", "msm_reduce", "ntt", "qap", "fixed_base", "other")
+
+    def profile_enable(self, on: bool = True):
+        self.check(self._lib.vsp_ctx_profile_enable(self._h, int(on)))
+
+    def profile_read(self) -> dict:
+        """{class: {"launches", "ms", "units"}} of device time per kernel class since profile_enable()"""
+        out = {}
+        for k, name in enumerate(self.KCLASSES):
+            n, ms, u = C.c_uint64(0), C.c_double(0), C.c_double(0)
+            self.check(self._lib.vsp_ctx_profile_read(self._h, k, C.byref(n), C.byref(ms), C.byref(u)))
+            out[name] = {"launches": n.value, "ms": ms.value, "units": u.value}
+        return out
+
     def measure_imad_rate(self, iters: int = 4096) -> float:
         out = C.c_double(0)
         self.check(self._lib.vsp_measure_imad_rate(self._h, iters, C.byref(out)))
@@ -213,6 +227,13 @@ class G2Bases(_Bases):
     _G2 = True
 
 
+def generate_g2_points(ctx: Context, n: int, seed: int) -> np.ndarray:
+    """n synthetic G2 points k_i * G2 (k_i = splitmix64(seed + i) | 1) as canonical affine limbs, built on the device"""
+    out = np.zeros((n, 24), dtype=np.uint64)
+    ctx.check(ctx._lib.vsp_g2_points_generate(ctx._h, n, seed, _p(out)))
+    return out
+
+
 def multiexp(ctx: Context, bases, scalars) -> np.ndarray:
     """algebra::multiexp<BDLO12>(bases, scalars): G1 if bases are (n, 12), G2 if (n, 24).  Host buffers in, affine out."""
     b = np.ascontiguousarray(bases, dtype=np.uint64)
@@ -315,6 +336,14 @@ class ProvingKey:
         gi = _p(pubkey.arrays["gamma_inverse_sum_s_g1"]) if pubkey is not None else None
         self.ctx.check(self.ctx._lib.vsp_prove_batch(self.ctx._h, self._h, k, _p(p), _p(a), _p(q), gi, _p(out)))
         return out
+
+    def prove_batch_dev(self, k: int, d_assignments: int, rs, d_proofs: int, pubkey: SaverPublicKey | None = None):
+        """device-resident ballots: d_assignments -> k x (1 || primary || auxiliary) canonical Fr; d_proofs -> k x 48
+        limbs.  Raw device pointers; stream-ordered, no synchronisation."""
+        q = np.ascontiguousarray(rs, dtype=np.uint64)
+        gi = _p(pubkey.arrays["gamma_inverse_sum_s_g1"]) if pubkey is not None else None
+        self.ctx.check(self.ctx._lib.vsp_prove_batch_dev(self.ctx._h, self._h, k, C.c_void_p(d_assignments), _p(q), gi,
+                                                         C.c_void_p(d_proofs)))
 
     def encrypt(self, pubkey: SaverPublicKey, gamma_abc_rest, msg, primary, auxiliary, r_saver: int, r: int, s: int):
         """encrypt_op<elgamal_verifiable>::process -> (cipher_text (msg_size + 2, 12), proof (48,))"""

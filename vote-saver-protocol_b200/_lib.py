@@ -58,6 +58,8 @@ SYMBOLS = [
     ("vsp_ctx_synchronize", _int, [_vp]),
     ("vsp_ctx_launch_count", _u64, [_vp]),
     ("vsp_version", C.c_char_p, []),
+    ("vsp_ctx_profile_enable", _int, [_vp, _int]),
+    ("vsp_ctx_profile_read", _int, [_vp, _int, C.POINTER(_u64), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     ("vsp_domain_plan", _int, [_u64, C.POINTER(_int), C.POINTER(_u64)]),
     ("vsp_fr_fft", _int, [_vp, _u64, _int, _vp, _u64, _vp]),
     ("vsp_fr_fft_dev", _int, [_vp, _u64, _int, _vp]),
@@ -73,6 +75,7 @@ SYMBOLS = [
     ("vsp_g2_bases_destroy", None, [_vp]),
     ("vsp_g1_bases_generate", _int, [_vp, _u64, _u64, C.POINTER(_vp)]),
     ("vsp_g1_bases_read", _int, [_vp, _vp, _u64, _u64, _vp]),
+    ("vsp_g2_points_generate", _int, [_vp, _u64, _u64, _vp]),
     ("vsp_g1_msm_bases", _int, [_vp, _vp, _u64, _vp, _int, _vp]),
     ("vsp_g2_msm_bases", _int, [_vp, _vp, _u64, _vp, _int, _vp]),
     ("vsp_g1_msm_bases_dev", _int, [_vp, _vp, _u64, _vp, _vp]),
@@ -84,6 +87,7 @@ SYMBOLS = [
     ("vsp_witness_map", _int, [_vp, _vp, _vp, _vp, _vp]),
     ("vsp_prove", _int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_prove_batch", _int, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_prove_batch_dev", _int, [_vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_saver_encrypt", _int, [_vp, _vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_saver_ciphertext", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp]),
     ("vsp_saver_rerandomize", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -13,6 +13,7 @@ namespace vsp {
 int domain_plan(uint64_t min_size, int* kind, uint64_t* m);  // ntt.cu
 int bases_generate_g1(vsp_ctx*, cudaStream_t, uint32_t*, uint64_t, uint64_t);  // msm_g1.cu
 int bases_read_g1(vsp_ctx*, cudaStream_t, const uint32_t*, uint64_t, uint64_t, uint64_t*);
+int points_generate_g2(vsp_ctx*, cudaStream_t, uint64_t*, uint64_t, uint64_t);  // msm_g2.cu
 }
 
 struct vsp_g1_bases {
@@ -21,6 +22,25 @@ struct vsp_g1_bases {
 struct vsp_g2_bases {
     BasesDev b;
 };
+
+// ---- live per-kernel-class timing ------------------------------------------------------------------
+static void prof_drain(vsp_ctx* ctx) {
+    KProf& p = ctx->prof;
+    for (KProfRec& r : p.recs) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+            p.ms[r.kc] += ms;
+            p.n[r.kc] += 1;
+            p.units[r.kc] += r.slot >= 0 ? r.scale * (double)p.pinned[r.slot] : r.scale;
+        }
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    p.recs.clear();
+    p.pinned_used = 0;
+    cudaGetLastError();
+}
+
 
 extern "C" {
 
@@ -79,6 +99,8 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
     for (int i = 0; i < 4; ++i)
         if (ctx->side[i]) cudaStreamSynchronize(ctx->side[i]);
     ntt_tables_free(ctx);
+    prof_drain(ctx);
+    if (ctx->prof.pinned) cudaFreeHost(ctx->prof.pinned);
     for (int i = 0; i < 4; ++i) {
         if (ctx->side[i]) cudaStreamDestroy(ctx->side[i]);
         if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
@@ -97,6 +119,40 @@ int vsp_ctx_synchronize(vsp_ctx* ctx) {
 }
 
 uint64_t vsp_ctx_launch_count(const vsp_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int vsp_ctx_profile_enable(vsp_ctx* ctx, int on) {
+    if (!ctx) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < 4; ++i) cudaStreamSynchronize(ctx->side[i]);
+    prof_drain(ctx);
+    KProf& p = ctx->prof;
+    if (on && !p.pinned) {
+        p.pinned_cap = 1 << 16;
+        if (cudaMallocHost(&p.pinned, (size_t)p.pinned_cap * 4) != cudaSuccess) {
+            p.pinned = nullptr;
+            p.pinned_cap = 0;
+            cudaGetLastError();
+        }
+    }
+    for (int k = 0; k < KC_COUNT; ++k) {
+        p.ms[k] = 0;
+        p.units[k] = 0;
+        p.n[k] = 0;
+    }
+    p.on = on != 0;
+    return VSP_OK;
+}
+
+int vsp_ctx_profile_read(vsp_ctx* ctx, int kclass, uint64_t* launches, double* total_ms, double* units) {
+    if (!ctx || kclass < 0 || kclass >= KC_COUNT) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    prof_drain(ctx);
+    if (launches) *launches = ctx->prof.n[kclass];
+    if (total_ms) *total_ms = ctx->prof.ms[kclass];
+    if (units) *units = ctx->prof.units[kclass];
+    return VSP_OK;
+}
 
 // ---- domains ------------------------------------------------------------------------------------
 int vsp_domain_plan(uint64_t min_size, int* kind, uint64_t* m) {
@@ -261,6 +317,18 @@ int vsp_g1_bases_read(vsp_ctx* ctx, const vsp_g1_bases* b, uint64_t first, uint6
     VSP_TRY(d.alloc(ctx, count * 96, ctx->stream));
     VSP_TRY(bases_read_g1(ctx, ctx->stream, b->b.d_pts, first, count, d.as<uint64_t>()));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out, d.p, count * 96, cudaMemcpyDeviceToHost, ctx->stream));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSP_OK;
+}
+
+int vsp_g2_points_generate(vsp_ctx* ctx, uint64_t n, uint64_t seed, uint64_t* out) {
+    if (!ctx || (!out && n)) return VSP_E_INVALID;
+    if (n == 0) return VSP_OK;
+    cudaSetDevice(ctx->device);
+    DevBuf d;
+    VSP_TRY(d.alloc(ctx, n * 192, ctx->stream));
+    VSP_TRY(points_generate_g2(ctx, ctx->stream, d.as<uint64_t>(), n, seed));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out, d.p, n * 192, cudaMemcpyDeviceToHost, ctx->stream));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return VSP_OK;
 }

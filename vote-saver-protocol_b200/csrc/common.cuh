@@ -12,6 +12,35 @@
 
 namespace vsp {
 struct NttTables;
+
+// kernel classes for the live per-class device timing (vsp_ctx_profile_*): bench.py's roofline leg
+enum KClass {
+    KC_MSM_ACC_G1 = 0,  // bucket accumulation, G1 (the dominant kernel of a proof)
+    KC_MSM_ACC_G2 = 1,  // bucket accumulation, G2
+    KC_MSM_SORT = 2,    // digits, histogram scans, scatter, task list
+    KC_MSM_REDUCE = 3,  // heavy-bucket collapse, bucket running sums, window sums, Horner + to-affine
+    KC_NTT = 4,         // Stockham passes and step-domain kernels
+    KC_QAP = 5,         // R1CS evaluation, pointwise H, coset tables
+    KC_FIXED = 6,       // fixed-base scalar multiples, proof assembly, SAVER ciphertext
+    KC_OTHER = 7,
+    KC_COUNT = 8
+};
+
+struct KProfRec {
+    int kc;
+    cudaEvent_t a, b;
+    int slot;       // index into the pinned counter array, or -1
+    double scale;   // units = counter * scale (slot >= 0) or scale alone
+};
+struct KProf {
+    bool on = false;
+    std::vector<KProfRec> recs;
+    double ms[KC_COUNT] = {0};
+    double units[KC_COUNT] = {0};
+    uint64_t n[KC_COUNT] = {0};
+    uint32_t* pinned = nullptr;  // device-side counters copied back (4 bytes each)
+    int pinned_cap = 0, pinned_used = 0;
+};
 }
 
 struct vsp_ctx {
@@ -26,6 +55,8 @@ struct vsp_ctx {
     cudaStream_t side[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr;
     cudaEvent_t ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+    vsp::KProf prof;
+    int last_prof = -1;  // profile record of the most recent launch (for kprof_units)
 };
 
 namespace vsp {
@@ -54,12 +85,43 @@ inline int set_error(vsp_ctx* ctx, int code, const char* fmt, ...) {
         if (_rc != VSP_OK) return _rc; \
     } while (0)
 
-// counted launch helper: every kernel of this library goes through it so gpu_launches is an exact count
-#define VSP_LAUNCH(ctx, kernel, grid, block, smem, strm, ...)        \
+// live per-class timing: when enabled, every launch is bracketed by two events on its own stream
+inline int kprof_begin(vsp_ctx* ctx, int kc, cudaStream_t s) {
+    if (!ctx->prof.on) return -1;
+    KProfRec r;
+    r.kc = kc;
+    r.slot = -1;
+    r.scale = 0.0;
+    if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return -1;
+    cudaEventRecord(r.a, s);
+    ctx->prof.recs.push_back(r);
+    return (int)ctx->prof.recs.size() - 1;
+}
+inline void kprof_end(vsp_ctx* ctx, int idx, cudaStream_t s) {
+    if (idx >= 0) cudaEventRecord(ctx->prof.recs[idx].b, s);
+}
+// algorithmic work of launch `idx`: `scale` units, times a 32-bit device counter read back after the launch if given
+inline void kprof_units(vsp_ctx* ctx, int idx, double scale, const uint32_t* d_counter, cudaStream_t s) {
+    if (idx < 0) return;
+    KProf& p = ctx->prof;
+    p.recs[idx].scale = scale;
+    if (d_counter && p.pinned && p.pinned_used < p.pinned_cap) {
+        p.recs[idx].slot = p.pinned_used++;
+        cudaMemcpyAsync(p.pinned + p.recs[idx].slot, d_counter, 4, cudaMemcpyDeviceToHost, s);
+    }
+}
+
+// counted launch helpers: every kernel of this library goes through them so gpu_launches is an exact count
+#define VSP_LAUNCH_K(ctx, kc, kernel, grid, block, smem, strm, ...)  \
     do {                                                             \
+        const int _pi = ::vsp::kprof_begin((ctx), (kc), (strm));     \
         kernel<<<(grid), (block), (smem), (strm)>>>(__VA_ARGS__);    \
+        ::vsp::kprof_end((ctx), _pi, (strm));                        \
+        (ctx)->last_prof = _pi;                                      \
         ++(ctx)->launches;                                           \
     } while (0)
+#define VSP_LAUNCH(ctx, kernel, grid, block, smem, strm, ...) \
+    VSP_LAUNCH_K(ctx, ::vsp::KC_OTHER, kernel, grid, block, smem, strm, __VA_ARGS__)
 
 // Stream-ordered device buffer (cudaMallocAsync pool: no device synchronisation, memory reused across calls).
 struct DevBuf {

@@ -18,6 +18,8 @@
 // 0 and 1 scalars need no special path: a zero contributes no digit, a one lands in bucket (window 0, 1), which
 // step 5 reduces in parallel — the reference's `_with_mixed_addition` pre-pass (skip 0, add 1) is subsumed.
 #pragma once
+#include <type_traits>
+
 #include "ec.cuh"
 #include "msm.cuh"
 
@@ -174,9 +176,9 @@ template <int MODE>
 static int exclusive_scan(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint64_t n, uint32_t* d_out,
                           uint32_t* d_tile_scratch) {
     const unsigned tiles = (unsigned)((n + SCAN_TILE - 1) / SCAN_TILE);
-    VSP_LAUNCH(ctx, (k_scan_tile_sums<MODE>), tiles, SCAN_THREADS, 0, s, d_in, n, d_tile_scratch);
-    VSP_LAUNCH(ctx, k_scan_tiles, 1, 1024, 0, s, d_tile_scratch, tiles);
-    VSP_LAUNCH(ctx, (k_scan_apply<MODE>), tiles, SCAN_THREADS, 0, s, d_in, n, d_tile_scratch, d_out);
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, (k_scan_tile_sums<MODE>), tiles, SCAN_THREADS, 0, s, d_in, n, d_tile_scratch);
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_scan_tiles, 1, 1024, 0, s, d_tile_scratch, tiles);
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, (k_scan_apply<MODE>), tiles, SCAN_THREADS, 0, s, d_in, n, d_tile_scratch, d_out);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
 }
@@ -417,13 +419,13 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_CUDA_CHECK(ctx, cudaMemsetAsync(cursors.p, 0, (p.buckets + 1) * 4, s));
     VSP_CUDA_CHECK(ctx, cudaMemsetAsync(heavy_count.p, 0, 4, s));
 
-    VSP_LAUNCH(ctx, k_msm_digits, (unsigned)((n + 127) / 128), 128, 0, s, d_scalars, n, p, keys.as<uint32_t>(),
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_digits, (unsigned)((n + 127) / 128), 128, 0, s, d_scalars, n, p, keys.as<uint32_t>(),
                counts.as<uint32_t>());
     VSP_TRY(exclusive_scan<0>(ctx, s, counts.as<uint32_t>(), p.buckets, offsets.as<uint32_t>(),
                               tile_scratch.as<uint32_t>()));
     VSP_TRY(exclusive_scan<1>(ctx, s, counts.as<uint32_t>(), p.buckets, task_off.as<uint32_t>(),
                               tile_scratch.as<uint32_t>()));
-    VSP_LAUNCH(ctx, k_msm_scatter, (unsigned)((total + 255) / 256), 256, 0, s, keys.as<uint32_t>(), total, n,
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_scatter, (unsigned)((total + 255) / 256), 256, 0, s, keys.as<uint32_t>(), total, n,
                offsets.as<uint32_t>(), cursors.as<uint32_t>(), sorted.as<uint32_t>());
     // upper bound on the number of tasks, known without a device read-back: every bucket contributes
     // ceil(count / T) <= count / T + 1
@@ -431,24 +433,28 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     DevBuf tasks, partial;
     VSP_TRY(tasks.alloc(ctx, max_tasks * sizeof(Task), s));
     VSP_TRY(partial.alloc(ctx, max_tasks * XYZZ<F>::BYTES, s));
-    VSP_LAUNCH(ctx, k_msm_tasks, (unsigned)((p.buckets + 127) / 128), 128, 0, s, offsets.as<uint32_t>(),
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_tasks, (unsigned)((p.buckets + 127) / 128), 128, 0, s, offsets.as<uint32_t>(),
                task_off.as<uint32_t>(), p.buckets, tasks.as<Task>(), heavy.as<uint32_t>(), heavy_count.as<uint32_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     // the exact task count lives on the device (task_off[buckets]); the grid covers the bound and extra threads exit
-    VSP_LAUNCH(ctx, k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
+    VSP_LAUNCH_K(ctx, (std::is_same<F, FqOps>::value ? KC_MSM_ACC_G1 : KC_MSM_ACC_G2), k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
                sorted.as<uint32_t>(), tasks.as<Task>(), task_off.as<uint32_t>() + p.buckets, partial.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_msm_collapse<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
+    // algorithmic work of this launch for the live roofline: bucket additions scheduled (= non-zero digits,
+    // offsets[buckets]) x 11 field multiplications (the reference's mixed Jacobian add) x I_mul(limbs)
+    kprof_units(ctx, ctx->last_prof, 11.0 * (std::is_same<F, FqOps>::value ? 300.0 : 3.0 * 300.0),
+                offsets.as<uint32_t>() + p.buckets, s);
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
                heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>());
     const unsigned segs_per_window = 1u << (p.nb_log - p.seg_log);
     const unsigned n_segs = p.windows * segs_per_window;
     DevBuf seg, win;
     VSP_TRY(seg.alloc(ctx, (size_t)n_segs * XYZZ<F>::BYTES, s));
     VSP_TRY(win.alloc(ctx, (size_t)p.windows * XYZZ<F>::BYTES, s));
-    VSP_LAUNCH(ctx, k_msm_reduce_segments<F>, (n_segs + 63) / 64, 64, 0, s, partial.as<uint32_t>(),
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_segments<F>, (n_segs + 63) / 64, 64, 0, s, partial.as<uint32_t>(),
                task_off.as<uint32_t>(), p, seg.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_msm_window_sums<F>, p.windows, WSUM_THREADS, WSUM_THREADS * XYZZ<F>::BYTES, s, seg.as<uint32_t>(),
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_window_sums<F>, p.windows, WSUM_THREADS, WSUM_THREADS * XYZZ<F>::BYTES, s, seg.as<uint32_t>(),
                p, win.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_msm_final<F>, 1, 32, 0, s, win.as<uint32_t>(), p, d_out, raw ? 1 : 0);
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_final<F>, 1, 32, 0, s, win.as<uint32_t>(), p, d_out, raw ? 1 : 0);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     (void)L;
     return VSP_OK;

@@ -74,7 +74,7 @@ int ntt_tables_ensure(vsp_ctx* ctx, unsigned log_n) {
     const uint64_t half = uint64_t(1) << (want - 1);
     VSP_CUDA_CHECK(ctx, cudaMalloc(&t->d_w, half * 32));
     t->log_w = want;
-    VSP_LAUNCH(ctx, k_build_twiddles, (unsigned)((half + 255) / 256), 256, 0, ctx->stream, t->d_w, want);
+    VSP_LAUNCH_K(ctx, KC_NTT, k_build_twiddles, (unsigned)((half + 255) / 256), 256, 0, ctx->stream, t->d_w, want);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     // side streams may use the table immediately: order them after the build
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -214,7 +214,7 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
     const uint64_t n = uint64_t(1) << log_n;
     if (log_n == 0) {
         if (d_in != d_out || d_pre || d_post) {
-            VSP_LAUNCH(ctx, k_scale_copy, 1, 32, 0, s, d_in, d_out, n, d_pre, d_post);
+            VSP_LAUNCH_K(ctx, KC_NTT, k_scale_copy, 1, 32, 0, s, d_in, d_out, n, d_pre, d_post);
             VSP_CUDA_CHECK(ctx, cudaGetLastError());
         }
         return VSP_OK;
@@ -275,7 +275,7 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
         const unsigned threads = 1u << (k - 1 + g_log);
         const unsigned blocks = 1u << (log_n - k - g_log);
         const size_t smem = (size_t)32 << (k + g_log);
-        VSP_LAUNCH(ctx, k_ntt_pass, blocks, threads, smem, s, a);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, blocks, threads, smem, s, a);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         if (last && dst != d_out) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_out, dst, n * 32, cudaMemcpyDeviceToDevice, s));
         src = dst;
@@ -375,15 +375,15 @@ int domain_fft_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, bool inverse, uint3
     VSP_TRY(e.alloc(ctx, small_m * 32, s));
     const unsigned gb = (unsigned)((big_m + 127) / 128), gs = (unsigned)((small_m + 127) / 128);
     if (!inverse) {
-        VSP_LAUNCH(ctx, k_step_fft_c, gb, 128, 0, s, d, c.as<uint32_t>(), big_m, small_m);
-        VSP_LAUNCH(ctx, k_step_fft_e, gs, 128, 0, s, d, e.as<uint32_t>(), big_m, small_m, tb->d_w, tb->log_w, log_2big);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_step_fft_c, gb, 128, 0, s, d, c.as<uint32_t>(), big_m, small_m);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_step_fft_e, gs, 128, 0, s, d, e.as<uint32_t>(), big_m, small_m, tb->d_w, tb->log_w, log_2big);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         VSP_TRY(ntt_pow2(ctx, s, c.as<uint32_t>(), d, log_big, false, nullptr, nullptr));
         VSP_TRY(ntt_pow2(ctx, s, e.as<uint32_t>(), d + 8 * big_m, log_small, false, nullptr, nullptr));
     } else {
         VSP_TRY(ntt_pow2(ctx, s, d, c.as<uint32_t>(), log_big, true, nullptr, nullptr));
         VSP_TRY(ntt_pow2(ctx, s, d + 8 * big_m, e.as<uint32_t>(), log_small, true, nullptr, nullptr));
-        VSP_LAUNCH(ctx, k_step_ifft_combine, gb, 128, 0, s, c.as<uint32_t>(), e.as<uint32_t>(), d, big_m, small_m,
+        VSP_LAUNCH_K(ctx, KC_NTT, k_step_ifft_combine, gb, 128, 0, s, c.as<uint32_t>(), e.as<uint32_t>(), d, big_m, small_m,
                    tb->d_w, tb->log_w, log_2big);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
     }
@@ -445,7 +445,7 @@ int multiply_by_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t n, const uint64
     memcpy(gg.v, g, 32);
     if (hostfr::geq(gg.v, hostfr::MOD)) return set_error(ctx, VSP_E_INVALID, "coset generator not reduced");
     PowTable t = make_pow_table(gg);
-    VSP_LAUNCH(ctx, k_mul_powers, (unsigned)((n + 127) / 128), 128, 0, s, d, n, t);
+    VSP_LAUNCH_K(ctx, KC_NTT, k_mul_powers, (unsigned)((n + 127) / 128), 128, 0, s, d, n, t);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
 }
@@ -456,7 +456,7 @@ int fill_power_table(vsp_ctx* ctx, cudaStream_t s, uint32_t* d_out, uint64_t n, 
     PowTable t = make_pow_table(g);
     Fr kk;
     fr4_to_limbs(kk.l, hostfr::to_mont(k));
-    VSP_LAUNCH(ctx, k_fill_powers, (unsigned)((n + 127) / 128), 128, 0, s, d_out, n, t, kk);
+    VSP_LAUNCH_K(ctx, KC_NTT, k_fill_powers, (unsigned)((n + 127) / 128), 128, 0, s, d_out, n, t, kk);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
 }
@@ -517,7 +517,7 @@ int divide_by_z_on_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, uint32_t*
         Fr4 z = sub(pow_u64(coset, m), from_u64(1));
         Fr k;
         fr4_to_limbs(k.l, to_mont(inv(z)));
-        VSP_LAUNCH(ctx, k_scale_const, (unsigned)((m + 127) / 128), 128, 0, s, d, m, k);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_scale_const, (unsigned)((m + 127) / 128), 128, 0, s, d, m, k);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         return VSP_OK;
     }
@@ -548,16 +548,16 @@ int divide_by_z_on_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, uint32_t*
         fr4_to_limbs(A.l, to_mont(c_small_Z0));
         fr4_to_limbs(B.l, to_mont(w_small_Z0));
         const uint64_t chunks = (big_m + STEP_INV_CHUNK - 1) / STEP_INV_CHUNK;
-        VSP_LAUNCH(ctx, k_step_div_table, (unsigned)((chunks + 63) / 64), 64, 0, s, tbl->inv_big.as<uint32_t>(), big_m,
+        VSP_LAUNCH_K(ctx, KC_NTT, k_step_div_table, (unsigned)((chunks + 63) / 64), 64, 0, s, tbl->inv_big.as<uint32_t>(), big_m,
                    pt, A, B);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         // the table outlives this stream-ordered call: make it visible to every stream of the context
         VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
     }
-    VSP_LAUNCH(ctx, k_mul_table, (unsigned)((big_m + 127) / 128), 128, 0, s, d, big_m, tbl->inv_big.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_NTT, k_mul_table, (unsigned)((big_m + 127) / 128), 128, 0, s, d, big_m, tbl->inv_big.as<uint32_t>());
     Fr k;
     fr4_to_limbs(k.l, tbl->z1_inv_mont);
-    VSP_LAUNCH(ctx, k_scale_const, (unsigned)((small_m + 127) / 128), 128, 0, s, d + 8 * big_m, small_m, k);
+    VSP_LAUNCH_K(ctx, KC_NTT, k_scale_const, (unsigned)((small_m + 127) / 128), 128, 0, s, d + 8 * big_m, small_m, k);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
 }

@@ -325,7 +325,7 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
         if (nnz) {
             VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(pk->d_col[i], cols[i], nnz * 4, cudaMemcpyHostToDevice, s));
             VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(pk->d_val[i], vals[i], nnz * 32, cudaMemcpyHostToDevice, s));
-            VSP_LAUNCH(ctx, k_vals_to_mont, (unsigned)((nnz + 127) / 128), 128, 0, s, pk->d_val[i], nnz, i == 1 ? 1 : 0);
+            VSP_LAUNCH_K(ctx, KC_QAP, k_vals_to_mont, (unsigned)((nnz + 127) / 128), 128, 0, s, pk->d_val[i], nnz, i == 1 ? 1 : 0);
             VSP_CUDA_CHECK(ctx, cudaGetLastError());
         }
     }
@@ -365,7 +365,7 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
         VSP_CUDA_CHECK(ctx, cudaMalloc(&pk->d_zinv, pk->m * 32));
         Fr one_mont;
         memcpy(one_mont.l, to_mont(from_u64(1)).v, 32);
-        VSP_LAUNCH(ctx, k_fill_const, (unsigned)((pk->m + 127) / 128), 128, 0, s, pk->d_zinv, pk->m, one_mont);
+        VSP_LAUNCH_K(ctx, KC_QAP, k_fill_const, (unsigned)((pk->m + 127) / 128), 128, 0, s, pk->d_zinv, pk->m, one_mont);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         VSP_TRY(divide_by_z_on_coset_dev(ctx, s, pk->m, pk->d_zinv));
     }
@@ -403,7 +403,7 @@ static int coset_lde(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, uint32_t* d
         VSP_TRY(ntt_pow2(ctx, s, d_a, d_a, L, false, nullptr, nullptr));    // fft
     } else {
         VSP_TRY(domain_fft_dev(ctx, s, m, true, d_a));
-        VSP_LAUNCH(ctx, k_mul_table2, (unsigned)((m + 127) / 128), 128, 0, s, d_a, m, pk->d_gpow);
+        VSP_LAUNCH_K(ctx, KC_QAP, k_mul_table2, (unsigned)((m + 127) / 128), 128, 0, s, d_a, m, pk->d_gpow);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         VSP_TRY(domain_fft_dev(ctx, s, m, false, d_a));
     }
@@ -423,7 +423,7 @@ static int witness_map_dev(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_w, 
         csr.val[i] = pk->d_val[i];
     }
     uint32_t* aA = d_h;
-    VSP_LAUNCH(ctx, k_r1cs_eval, (unsigned)((m * 32 + 255) / 256), 256, 0, s, csr, d_w, pk->nc, pk->ni, m, aA,
+    VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval, (unsigned)((m * 32 + 255) / 256), 256, 0, s, csr, d_w, pk->nc, pk->ni, m, aA,
                aB.as<uint32_t>(), aC.as<uint32_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
@@ -436,7 +436,7 @@ static int witness_map_dev(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_w, 
     VSP_TRY(coset_lde(ctx, s, pk, aA));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[0], 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[1], 0));
-    VSP_LAUNCH(ctx, k_h_pointwise, (unsigned)((m + 127) / 128), 128, 0, s, aA, aB.as<uint32_t>(), aC.as<uint32_t>(),
+    VSP_LAUNCH_K(ctx, KC_QAP, k_h_pointwise, (unsigned)((m + 127) / 128), 128, 0, s, aA, aB.as<uint32_t>(), aC.as<uint32_t>(),
                pk->d_zinv, m);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     if (pk->kind == VSP_DOMAIN_BASIC_RADIX2) {
@@ -444,7 +444,7 @@ static int witness_map_dev(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_w, 
         VSP_TRY(ntt_pow2(ctx, s, aA, aA, ceil_log2_u64(m), true, nullptr, pk->d_ginvpow));
     } else {
         VSP_TRY(domain_fft_dev(ctx, s, m, true, aA));
-        VSP_LAUNCH(ctx, k_mul_table2, (unsigned)((m + 127) / 128), 128, 0, s, aA, m, pk->d_ginvpow);
+        VSP_LAUNCH_K(ctx, KC_QAP, k_mul_table2, (unsigned)((m + 127) / 128), 128, 0, s, aA, m, pk->d_ginvpow);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
     }
     return VSP_OK;
@@ -470,17 +470,21 @@ struct ProofScratch {
     DevBuf w, h, aB, aC, bsc, ev, fxpts, fxsc, fx1, fx2, gab, sgpts, sgsc, sg;
 };
 
-static int prove_async(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux, const uint64_t* r,
-                       const uint64_t* sv, const uint64_t* r_saver, const uint64_t* gamma_inv, uint64_t* d_proof,
-                       ProofScratch& k) {
+static int prove_async(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_assignment, const uint64_t* primary,
+                       const uint64_t* aux, const uint64_t* r, const uint64_t* sv, const uint64_t* r_saver,
+                       const uint64_t* gamma_inv, uint64_t* d_proof, ProofScratch& k) {
     using namespace hostfr;
     if (!fr_reduced(r) || !fr_reduced(sv) || (r_saver && !fr_reduced(r_saver)))
         return set_error(ctx, VSP_E_INVALID, "proving randomness not reduced mod r");
     cudaStream_t s = ctx->stream;
     const uint64_t m = pk->m;
     constexpr size_t X1 = G1XYZZ::BYTES, X2 = G2XYZZ::BYTES;
-    VSP_TRY(upload_witness(ctx, pk, primary, aux, k.w));
-    const uint32_t* d_w = k.w.as<uint32_t>();
+    // the full assignment (1 || primary || auxiliary): already on the device, or uploaded from the host buffers
+    const uint32_t* d_w = d_assignment;
+    if (!d_w) {
+        VSP_TRY(upload_witness(ctx, pk, primary, aux, k.w));
+        d_w = k.w.as<uint32_t>();
+    }
 
     // fork: multiexps that only need the witness start now
     VSP_TRY(k.ev.alloc(ctx, 4 * X1 + X2, s));  // evA, evB1, evH, evL (G1) | evB2 (G2)
@@ -533,13 +537,13 @@ static int prove_async(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, 
     VSP_TRY(msm_run(ctx, ctx->side[2], pk->L, pk->na, d_w + 8 * (pk->ni + 1), evL, true));
     VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[2], ctx->side[2]));
     // side 3: fixed-base multiples, B (G2), B (G1)
-    VSP_LAUNCH(ctx, k_scalar_mul_batch<Fq2Ops>, 1, 32, 0, ctx->side[3],
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<Fq2Ops>, 1, 32, 0, ctx->side[3],
                reinterpret_cast<const uint64_t*>(k.fxpts.as<char>() + sizeof(pts1)),
                reinterpret_cast<const uint32_t*>(k.fxsc.as<char>() + sizeof(sc1)), 1u, 0, k.fx2.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_scalar_mul_batch<FqOps>, 4, 32, 0, ctx->side[3], k.fxpts.as<uint64_t>(), k.fxsc.as<uint32_t>(), 4u,
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 4, 32, 0, ctx->side[3], k.fxpts.as<uint64_t>(), k.fxsc.as<uint32_t>(), 4u,
                0, k.fx1.as<uint32_t>());
     if (pk->B_count)
-        VSP_LAUNCH(ctx, k_gather_fr, (unsigned)((pk->B_count + 127) / 128), 128, 0, ctx->side[3], d_w, pk->d_B_idx,
+        VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, (unsigned)((pk->B_count + 127) / 128), 128, 0, ctx->side[3], d_w, pk->d_B_idx,
                    pk->B_count, k.bsc.as<uint32_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_TRY(msm_run(ctx, ctx->side[3], pk->Bg2, pk->B_count, k.bsc.as<uint32_t>(), evB2, true));
@@ -564,10 +568,10 @@ static int prove_async(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, 
     ap.fixed2 = pk->fixed2.d_pts;
     ap.gA_gB1 = k.gab.as<uint64_t>();
     ap.proof = d_proof;
-    VSP_LAUNCH(ctx, k_prove_phase1, 1, 96, 0, s, ap);
-    VSP_LAUNCH(ctx, k_scalar_mul_batch<FqOps>, 2, 32, 0, s, k.gab.as<uint64_t>(), k.sgsc.as<uint32_t>(), 2u, 0,
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, 1, 96, 0, s, ap);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2, 32, 0, s, k.gab.as<uint64_t>(), k.sgsc.as<uint32_t>(), 2u, 0,
                k.sg.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_prove_phase3, 1, 32, 0, s, ap, k.sg.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, 1, 32, 0, s, ap, k.sg.as<uint32_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
 }
@@ -596,10 +600,32 @@ extern "C" int vsp_prove(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary
     ProofScratch k;
     DevBuf d_proof;
     VSP_TRY(d_proof.alloc(ctx, 384, ctx->stream));
-    VSP_TRY(prove_async(ctx, pk, primary, aux, r, s, r_saver, gamma_inverse_sum_s_g1, d_proof.as<uint64_t>(), k));
+    VSP_TRY(prove_async(ctx, pk, nullptr, primary, aux, r, s, r_saver, gamma_inverse_sum_s_g1, d_proof.as<uint64_t>(), k));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_proof, d_proof.p, 384, cudaMemcpyDeviceToHost, ctx->stream));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     for (int i = 0; i < 4; ++i) VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->side[i]));
+    return VSP_OK;
+}
+
+static int prove_batch_impl(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const uint64_t* primary, const uint64_t* aux,
+                            const uint64_t* d_assignments, const uint64_t* rs, const uint64_t* gamma_inverse_sum_s_g1,
+                            uint64_t* d_proofs) {
+    // ballots are enqueued back to back without host synchronisation; scratch of ballot i is released (stream-ordered)
+    // once ballot i + 1 has been enqueued, so the allocator pool recycles it.
+    for (uint64_t i = 0; i < k; ++i) {
+        ProofScratch sc;
+        const uint64_t* rr = rs + 12 * i;
+        const uint32_t* d_w =
+            d_assignments ? reinterpret_cast<const uint32_t*>(d_assignments + 4 * (pk->nv + 1) * i) : nullptr;
+        VSP_TRY(prove_async(ctx, pk, d_w, primary ? primary + 4 * pk->ni * i : nullptr, aux ? aux + 4 * pk->na * i : nullptr,
+                            rr, rr + 4, gamma_inverse_sum_s_g1 ? rr + 8 : nullptr, gamma_inverse_sum_s_g1,
+                            d_proofs + 48 * i, sc));
+        // side streams must finish with this ballot's scratch before it is recycled
+        for (int j = 0; j < 4; ++j) {
+            VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[j], ctx->side[j]));
+            VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[j], 0));
+        }
+    }
     return VSP_OK;
 }
 
@@ -610,23 +636,19 @@ extern "C" int vsp_prove_batch(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const
     if (k == 0) return VSP_OK;
     DevBuf d_proofs;
     VSP_TRY(d_proofs.alloc(ctx, k * 384, ctx->stream));
-    // ballots are enqueued back to back without host synchronisation; scratch of ballot i is released (stream-ordered)
-    // once ballot i + 1 has been enqueued, so the allocator pool recycles it.
-    for (uint64_t i = 0; i < k; ++i) {
-        ProofScratch sc;
-        const uint64_t* rr = rs + 12 * i;
-        VSP_TRY(prove_async(ctx, pk, primary + 4 * pk->ni * i, aux + 4 * pk->na * i, rr, rr + 4,
-                            gamma_inverse_sum_s_g1 ? rr + 8 : nullptr, gamma_inverse_sum_s_g1,
-                            d_proofs.as<uint64_t>() + 48 * i, sc));
-        // side streams must finish with this ballot's scratch before it is recycled
-        for (int j = 0; j < 4; ++j) {
-            VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[j], ctx->side[j]));
-            VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[j], 0));
-        }
-    }
+    VSP_TRY(prove_batch_impl(ctx, pk, k, primary, aux, nullptr, rs, gamma_inverse_sum_s_g1, d_proofs.as<uint64_t>()));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_proofs, d_proofs.p, k * 384, cudaMemcpyDeviceToHost, ctx->stream));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return VSP_OK;
+}
+
+// device-resident variant: d_assignments = k full assignments (1 || primary || auxiliary), (num_inputs + num_aux + 1)
+// canonical Fr each; d_proofs = k * 48 limbs on the device.  Stream-ordered: returns once everything is enqueued.
+extern "C" int vsp_prove_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const uint64_t* d_assignments,
+                                   const uint64_t* rs, const uint64_t* gamma_inverse_sum_s_g1, uint64_t* d_proofs) {
+    if (!ctx || !pk || !rs || !d_proofs || !d_assignments) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return prove_batch_impl(ctx, pk, k, nullptr, nullptr, d_assignments, rs, gamma_inverse_sum_s_g1, d_proofs);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -659,9 +681,9 @@ static int run_mul_jobs_g1(vsp_ctx* ctx, const std::vector<const uint64_t*>& pts
         VSP_TRY(da.alloc(ctx, (size_t)n_groups * 96, s));
         VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(da.p, addend_host, (size_t)n_groups * 96, cudaMemcpyHostToDevice, s));
     }
-    VSP_LAUNCH(ctx, k_scalar_mul_batch<FqOps>, n, 32, 0, s, dp.as<uint64_t>(), ds.as<uint32_t>(), n, 0,
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, n, 32, 0, s, dp.as<uint64_t>(), ds.as<uint32_t>(), n, 0,
                dx.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_group_sum<FqOps>, (n_groups + 31) / 32, 32, 0, s, dx.as<uint32_t>(), dg.as<uint32_t>(), n,
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_group_sum<FqOps>, (n_groups + 31) / 32, 32, 0, s, dx.as<uint32_t>(), dg.as<uint32_t>(), n,
                addend_host ? da.as<uint64_t>() : nullptr, n_groups, dout.as<uint64_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_host, dout.p, (size_t)n_groups * 96, cudaMemcpyDeviceToHost, s));
@@ -749,8 +771,8 @@ extern "C" int vsp_saver_rerandomize(vsp_ctx* ctx, const vsp_saver_pubkey_t* pub
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(dp.p, hp, sizeof(hp), cudaMemcpyHostToDevice, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(ds.p, hs, sizeof(hs), cudaMemcpyHostToDevice, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(dg.p, hg, sizeof(hg), cudaMemcpyHostToDevice, s));
-    VSP_LAUNCH(ctx, k_scalar_mul_batch<Fq2Ops>, 2, 32, 0, s, dp.as<uint64_t>(), ds.as<uint32_t>(), 2u, 0, dx.as<uint32_t>());
-    VSP_LAUNCH(ctx, k_group_sum<Fq2Ops>, 1, 32, 0, s, dx.as<uint32_t>(), dg.as<uint32_t>(), 2u, nullptr, 1u,
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<Fq2Ops>, 2, 32, 0, s, dp.as<uint64_t>(), ds.as<uint32_t>(), 2u, 0, dx.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_group_sum<Fq2Ops>, 1, 32, 0, s, dx.as<uint32_t>(), dg.as<uint32_t>(), 2u, nullptr, 1u,
                dout.as<uint64_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(proof_out + 12, dout.p, 192, cudaMemcpyDeviceToHost, s));
