@@ -239,10 +239,10 @@ int vsp_fr_divide_by_z_on_coset(vsp_ctx* ctx, uint64_t m, uint64_t* a_inout) {
 }
 
 // ---- multiexp -------------------------------------------------------------------------------------
-static int bases_create(vsp_ctx* ctx, bool g2, uint64_t n, const uint64_t* bases, BasesDev* b) {
+static int bases_create(vsp_ctx* ctx, bool g2, uint64_t n, const uint64_t* bases, BasesDev* b, bool table = true) {
     if (!ctx || (!bases && n)) return VSP_E_INVALID;
     cudaSetDevice(ctx->device);
-    return bases_upload(ctx, g2, n, bases, b);
+    return bases_upload(ctx, g2, n, bases, b, table);
 }
 
 int vsp_g1_bases_create(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, vsp_g1_bases** out) {
@@ -297,6 +297,7 @@ int vsp_g1_bases_generate(vsp_ctx* ctx, uint64_t n, uint64_t seed, vsp_g1_bases*
         return set_error(ctx, VSP_E_NOMEM, "cudaMalloc(%llu bases) failed: %s", (unsigned long long)n, cudaGetErrorString(e));
     }
     int rc = n ? bases_generate_g1(ctx, ctx->stream, h->b.d_pts, n, seed) : VSP_OK;
+    if (rc == VSP_OK) rc = bases_finalize(ctx, &h->b, true);
     if (rc == VSP_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
         rc = set_error(ctx, VSP_E_CUDA, "bases generation failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (rc) {
@@ -369,19 +370,19 @@ int vsp_g1_msm_bases_dev(vsp_ctx* ctx, const vsp_g1_bases* b, uint64_t n_scalars
     return msm_run(ctx, ctx->stream, b->b, n_scalars, reinterpret_cast<const uint32_t*>(d_scalars), d_out);
 }
 
-int vsp_g1_msm(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, const uint64_t* scalars, uint64_t* out) {
-    vsp_g1_bases* h = nullptr;
-    VSP_TRY(vsp_g1_bases_create(ctx, n, bases, &h));
-    int rc = vsp_g1_msm_bases(ctx, h, n, scalars, 0, out);
-    vsp_g1_bases_destroy(h);
+// one-shot multiexp: the bases are used once, so no window table is built for them
+static int msm_one_shot(vsp_ctx* ctx, bool g2, uint64_t n, const uint64_t* bases, const uint64_t* scalars, uint64_t* out) {
+    BasesDev b;
+    int rc = bases_create(ctx, g2, n, bases, &b, false);
+    if (rc == VSP_OK) rc = msm_bases_host_out(ctx, b, n, scalars, 0, out);
+    bases_free(&b);
     return rc;
 }
+int vsp_g1_msm(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, const uint64_t* scalars, uint64_t* out) {
+    return msm_one_shot(ctx, false, n, bases, scalars, out);
+}
 int vsp_g2_msm(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, const uint64_t* scalars, uint64_t* out) {
-    vsp_g2_bases* h = nullptr;
-    VSP_TRY(vsp_g2_bases_create(ctx, n, bases, &h));
-    int rc = vsp_g2_msm_bases(ctx, h, n, scalars, 0, out);
-    vsp_g2_bases_destroy(h);
-    return rc;
+    return msm_one_shot(ctx, true, n, bases, scalars, out);
 }
 
 static int points_sum_host(vsp_ctx* ctx, bool g2, uint64_t k, const uint64_t* points, uint64_t* out) {

@@ -1,21 +1,26 @@
-// msm.cu — signed-digit bucket multiexp (Pippenger) over BLS12-381 G1 / G2 on sm_100a.
+// msm_impl.cuh — signed-digit bucket multiexp (Pippenger) over BLS12-381 G1 / G2 on sm_100a, batched over ballots.
 //
 // Replaces algebra::multiexp<policies::multiexp_method_BDLO12> and multiexp_with_mixed_addition (un-vendored
 // crypto3-algebra @ e4fa2c5e; signature from the call site
-// /root/reference/libs/containers/include/nil/crypto3/container/sparse_vector.hpp:258-261) and the four prover
-// multiexps over A/B/H/L_query.  Any correct algorithm yields the same group element; the result
-// is returned as a canonical affine point, which is what the reference's encoders emit
+// /root/reference/libs/containers/include/nil/crypto3/container/sparse_vector.hpp:258-261) and the prover's
+// multiexps over A/B/H/L_query.  Any correct algorithm yields the same group element; results
+// leave as canonical affine points, which is what the reference's encoders emit
 // (libs/marshalling/algebra/.../processing/curve_element.hpp:112-113).
 //
-// Pipeline (all stream-ordered, no host round trip):
-//   1 digits      scalar -> W signed c-bit digits; key = window * 2^(c-1) + |d| - 1; histogram by key
-//   2 scan        exclusive prefix sum of the histogram -> bucket offsets; split buckets into tasks of <= T points
-//   3 scatter     counting sort of (point index | sign) by key
-//   4 accumulate  one thread per task: XYZZ mixed additions of the gathered affine bases
-//   5 collapse    buckets that were split over several tasks (e.g. the bucket of all scalars == 1) are tree-reduced
-//   6 reduce      per window, per segment of buckets: running-sum  sum (k+1) B_k ; segments tree-summed per window
-//   7 final       Horner over the windows, to affine, out of Montgomery form
-// 0 and 1 scalars need no special path: a zero contributes no digit, a one lands in bucket (window 0, 1), which
+// Resident bases (a proving-key query) carry a table of window multiples  T[w][i] = 2^(c w) * P_i  built once at
+// load time, so every window of every scalar drops into ONE bucket set per ballot and no doubling happens at
+// multiexp time.  One-shot bases (vsp_g*_msm) have no table: one bucket set per window, joined by a Horner pass.
+//
+// Pipeline for `batch` scalar vectors over the same bases (all stream-ordered, no host round trip):
+//   1 digits      scalar -> W signed c-bit digits; key = (ballot, set, |d| - 1); histogram by key
+//   2 scan        exclusive prefix sums -> bucket offsets; buckets split into tasks of <= TASK_POINTS points
+//   3 scatter     counting sort of (table index | sign) by key
+//   4 accumulate  one thread per task: XYZZ mixed additions of the gathered affine points      <- the hot kernel
+//   5 collapse    buckets split over several tasks are summed (thread per bucket; block per very heavy bucket)
+//   6 reduce      per bucket set: sum_v v * B_v = sum_j 2^j * (sum of buckets whose value has bit j) — c parallel
+//                 tree sums instead of a serial running sum — then a c-step Horner per set
+//   7 final       Horner over the sets of a ballot (one-shot bases only), to affine, out of Montgomery form
+// 0 and 1 scalars need no special path: a zero contributes no digit, a one lands in bucket (set 0, value 1), which
 // step 5 reduces in parallel — the reference's `_with_mixed_addition` pre-pass (skip 0, add 1) is subsumed.
 #pragma once
 #include <type_traits>
@@ -26,42 +31,32 @@
 namespace vsp {
 namespace {
 
-constexpr unsigned TASK_POINTS = 64;     // max points one accumulate thread sums
+constexpr unsigned TASK_POINTS = 64;  // max points one accumulate thread sums
 constexpr unsigned KEY_NONE = 0xffffffffu;
+constexpr unsigned HEAVY_TASKS = 32;  // buckets with more partials than this are collapsed by a whole block
 
 struct MsmPlan {
     unsigned c;        // window bits
     unsigned windows;  // 255 / c + 1
-    unsigned nb_log;   // c - 1: buckets per window = 2^(c-1)
-    uint64_t buckets;  // windows << nb_log
-    unsigned seg_log;  // buckets per reduce segment = 2^seg_log
+    unsigned nb_log;   // c - 1: buckets per set = 2^(c-1), bucket index v - 1 for digit magnitude v in [1, 2^(c-1)]
+    unsigned sets;     // bucket sets per ballot: 1 with a window table, `windows` without
+    unsigned batch;    // ballots
+    uint64_t stride;   // table stride between windows (bases.n), 0 without a table
+    uint64_t buckets;  // batch * sets << nb_log
 };
-
-static MsmPlan make_plan(uint64_t n) {
-    MsmPlan p;
-    int c = (int)floor_log2_u64(n ? n : 1) - 3;
-    if (c < 2) c = 2;
-    if (c > 16) c = 16;
-    p.c = (unsigned)c;
-    p.windows = 255 / p.c + 1;
-    p.nb_log = p.c - 1;
-    p.buckets = uint64_t(p.windows) << p.nb_log;
-    // ~<= 512 segments per window
-    p.seg_log = p.nb_log > 9 ? p.nb_log - 9 : 0;
-    if (p.seg_log > 6) p.seg_log = 6;
-    return p;
-}
 
 // ---------------------------------------------------------------------------------------------
 // 1. digits + histogram
 // ---------------------------------------------------------------------------------------------
-__global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, MsmPlan p, uint32_t* __restrict__ keys,
-                             uint32_t* __restrict__ counts) {
+__global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t scalar_stride, MsmPlan p,
+                             uint32_t* __restrict__ keys, uint32_t* __restrict__ counts) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const unsigned b = blockIdx.y;
     if (i >= n) return;
+    const uint32_t* sp = scalars + 8 * (uint64_t(b) * scalar_stride + i);
     uint32_t s[9];
-    const uint4 lo = reinterpret_cast<const uint4*>(scalars + 8 * i)[0];
-    const uint4 hi = reinterpret_cast<const uint4*>(scalars + 8 * i)[1];
+    const uint4 lo = reinterpret_cast<const uint4*>(sp)[0];
+    const uint4 hi = reinterpret_cast<const uint4*>(sp)[1];
     s[0] = lo.x; s[1] = lo.y; s[2] = lo.z; s[3] = lo.w;
     s[4] = hi.x; s[5] = hi.y; s[6] = hi.z; s[7] = hi.w;
     s[8] = 0;
@@ -76,16 +71,17 @@ __global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, M
             d = (uint32_t)(two >> sh) & mask;
         }
         d += carry;
+        const uint32_t set = b * p.sets + (p.sets > 1 ? w : 0u);
         uint32_t key = KEY_NONE;
         if (d > half) {
             const uint32_t mag = (1u << p.c) - d;  // negative digit; d == 2^c (all-ones + carry) is digit 0, carry 1
             carry = 1;
-            if (mag) key = ((w << p.nb_log) + mag - 1u) | 0x80000000u;
+            if (mag) key = ((set << p.nb_log) + mag - 1u) | 0x80000000u;
         } else {
             carry = 0;
-            if (d) key = (w << p.nb_log) + d - 1u;
+            if (d) key = (set << p.nb_log) + d - 1u;
         }
-        keys[uint64_t(w) * n + i] = key;
+        keys[(uint64_t(b) * p.windows + w) * n + i] = key;
         if (key != KEY_NONE) atomicAdd(&counts[key & 0x7fffffffu], 1u);
     }
 }
@@ -186,24 +182,26 @@ static int exclusive_scan(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, ui
 // ---------------------------------------------------------------------------------------------
 // 3. scatter (counting sort) and task list
 // ---------------------------------------------------------------------------------------------
-__global__ void k_msm_scatter(const uint32_t* __restrict__ keys, uint64_t total, uint64_t n,
+__global__ void k_msm_scatter(const uint32_t* __restrict__ keys, uint64_t total, uint64_t n, MsmPlan p,
                               const uint32_t* __restrict__ offsets, uint32_t* __restrict__ cursors,
                               uint32_t* __restrict__ sorted) {
     const uint64_t q = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (q >= total) return;
     const uint32_t key = keys[q];
     if (key == KEY_NONE) return;
-    const uint32_t b = key & 0x7fffffffu;
-    const uint32_t pos = offsets[b] + atomicAdd(&cursors[b], 1u);
-    const uint32_t i = (uint32_t)(q % n);
-    sorted[pos] = i | (key & 0x80000000u);
+    const uint32_t bk = key & 0x7fffffffu;
+    const uint32_t pos = offsets[bk] + atomicAdd(&cursors[bk], 1u);
+    const uint64_t row = q / n;  // ballot * windows + window
+    const uint32_t i = (uint32_t)(q - row * n);
+    const uint32_t w = (uint32_t)(row % p.windows);
+    sorted[pos] = (uint32_t)(i + w * p.stride) | (key & 0x80000000u);  // index into the window table
 }
 
 struct Task {
     uint32_t begin, end;  // positions in `sorted`
 };
 
-// one thread per bucket: emit its tasks; buckets split over > 1 task are appended to the heavy list
+// one thread per bucket: emit its tasks
 __global__ void k_msm_tasks(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ task_off, uint64_t buckets,
                             Task* __restrict__ tasks, uint32_t* __restrict__ heavy, uint32_t* __restrict__ heavy_count) {
     const uint64_t b = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -216,14 +214,14 @@ __global__ void k_msm_tasks(const uint32_t* __restrict__ offsets, const uint32_t
         k.end = min(hi, k.begin + TASK_POINTS);
         tasks[t] = k;
     }
-    if (t1 - t0 > 1) heavy[atomicAdd(heavy_count, 1u)] = (uint32_t)b;
+    if (t1 - t0 > HEAVY_TASKS) heavy[atomicAdd(heavy_count, 1u)] = (uint32_t)b;
 }
 
 // ---------------------------------------------------------------------------------------------
 // 4. accumulate
 // ---------------------------------------------------------------------------------------------
 template <class F>
-__global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restrict__ bases, const uint32_t* __restrict__ sorted,
+__global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restrict__ table, const uint32_t* __restrict__ sorted,
                                                         const Task* __restrict__ tasks,
                                                         const uint32_t* __restrict__ n_tasks_ptr,
                                                         uint32_t* __restrict__ partial) {
@@ -234,7 +232,7 @@ __global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restri
     constexpr int PT_LIMBS = Affine<F>::BYTES / 4;
     for (uint32_t pos = k.begin; pos < k.end; ++pos) {
         const uint32_t v = sorted[pos];
-        Affine<F> pt = Affine<F>::load(bases + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
+        Affine<F> pt = Affine<F>::load(table + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
         if (v & 0x80000000u) pt.y = F::neg(pt.y);
         ec_madd<F>(acc, pt);
     }
@@ -244,12 +242,27 @@ __global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restri
 // ---------------------------------------------------------------------------------------------
 // 5. collapse multi-task buckets: partial[task_off[b]] = sum of the bucket's partials
 // ---------------------------------------------------------------------------------------------
+// light buckets (2 .. HEAVY_TASKS partials): one thread each
+template <class F>
+__global__ void __launch_bounds__(64) k_msm_collapse_light(const uint32_t* __restrict__ task_off, uint64_t buckets,
+                                                           uint32_t* __restrict__ partial) {
+    const uint64_t b = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (b >= buckets) return;
+    const uint32_t t0 = task_off[b], t1 = task_off[b + 1];
+    if (t1 - t0 < 2 || t1 - t0 > HEAVY_TASKS) return;
+    constexpr int L = XYZZ<F>::BYTES / 4;
+    XYZZ<F> acc = XYZZ<F>::load(partial + uint64_t(t0) * L);
+    for (uint32_t t = t0 + 1; t < t1; ++t) ec_add<F>(acc, XYZZ<F>::load(partial + uint64_t(t) * L));
+    acc.store(partial + uint64_t(t0) * L);
+}
+
+// heavy buckets (e.g. the bucket of all scalars == 1): one block each, strided sums then a shared-memory tree
 constexpr unsigned COLLAPSE_THREADS = 64;
 template <class F>
-__global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse(const uint32_t* __restrict__ heavy,
-                                                                   const uint32_t* __restrict__ heavy_count,
-                                                                   const uint32_t* __restrict__ task_off,
-                                                                   uint32_t* __restrict__ partial) {
+__global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse_heavy(const uint32_t* __restrict__ heavy,
+                                                                         const uint32_t* __restrict__ heavy_count,
+                                                                         const uint32_t* __restrict__ task_off,
+                                                                         uint32_t* __restrict__ partial) {
     extern __shared__ uint4 sm4[];
     uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
@@ -278,67 +291,67 @@ __global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse(const uint32_
 }
 
 // ---------------------------------------------------------------------------------------------
-// 6. bucket reduction
+// 6. bucket reduction by bit planes:  sum_v v B_v = sum_j 2^j S_j,  S_j = sum of B_v over v with bit j set
 // ---------------------------------------------------------------------------------------------
-// thread = (window, segment): sum over the segment's buckets of (local index + 1) * B, plus lo * sum(B)
-template <class F>
-__global__ void __launch_bounds__(64) k_msm_reduce_segments(const uint32_t* __restrict__ partial,
-                                                            const uint32_t* __restrict__ task_off, MsmPlan p,
-                                                            uint32_t* __restrict__ seg_out) {
-    constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned segs_per_window = 1u << (p.nb_log - p.seg_log);
-    const unsigned gid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= p.windows * segs_per_window) return;
-    const unsigned w = gid / segs_per_window, seg = gid % segs_per_window;
-    const uint32_t lo = seg << p.seg_log, cnt = 1u << p.seg_log;
-    const uint64_t bbase = (uint64_t(w) << p.nb_log) + lo;
-    XYZZ<F> running = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
-    for (int k = (int)cnt - 1; k >= 0; --k) {
-        const uint64_t b = bbase + k;
-        const uint32_t t0 = task_off[b], t1 = task_off[b + 1];
-        if (t1 > t0) {
-            XYZZ<F> q = XYZZ<F>::load(partial + uint64_t(t0) * L);
-            ec_add<F>(running, q);
-        }
-        ec_add<F>(acc, running);
-    }
-    if (lo) {
-        XYZZ<F> shifted = ec_mul_small<F>(running, lo);
-        ec_add<F>(acc, shifted);
-    }
-    acc.store(seg_out + uint64_t(gid) * L);
-}
+constexpr unsigned RED_THREADS = 64, RED_CHUNK = 1024;  // buckets per block of k_msm_reduce_planes
 
-// block = window: tree-sum the window's segment results
-constexpr unsigned WSUM_THREADS = 64;
+// block = (chunk, plane j, set): tree-sum the chunk's buckets whose value v = index + 1 has bit j set
 template <class F>
-__global__ void __launch_bounds__(WSUM_THREADS) k_msm_window_sums(const uint32_t* __restrict__ seg_in, MsmPlan p,
-                                                                  uint32_t* __restrict__ win_out) {
+__global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_t* __restrict__ partial,
+                                                                   const uint32_t* __restrict__ task_off, MsmPlan p,
+                                                                   unsigned chunks, uint32_t* __restrict__ plane_out) {
     extern __shared__ uint4 sm4[];
     uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned segs = 1u << (p.nb_log - p.seg_log);
-    const unsigned w = blockIdx.x;
+    const unsigned chunk = blockIdx.x, j = blockIdx.y, set = blockIdx.z;
+    const uint32_t nb = 1u << p.nb_log;
+    const uint32_t lo = chunk * RED_CHUNK, hi = min(nb, lo + RED_CHUNK);
+    const uint64_t bbase = uint64_t(set) << p.nb_log;
     XYZZ<F> acc = XYZZ<F>::inf();
-    for (unsigned sgi = threadIdx.x; sgi < segs; sgi += WSUM_THREADS) {
-        XYZZ<F> q = XYZZ<F>::load(seg_in + (uint64_t(w) * segs + sgi) * L);
-        ec_add<F>(acc, q);
+    for (uint32_t idx = lo + threadIdx.x; idx < hi; idx += RED_THREADS) {
+        if (!(((idx + 1u) >> j) & 1u)) continue;
+        const uint32_t t0 = task_off[bbase + idx], t1 = task_off[bbase + idx + 1];
+        if (t1 > t0) ec_add<F>(acc, XYZZ<F>::load(partial + uint64_t(t0) * L));
     }
     acc.store(sm + threadIdx.x * L);
     __syncthreads();
-    for (unsigned st = WSUM_THREADS / 2; st > 0; st >>= 1) {
+    for (unsigned st = RED_THREADS / 2; st > 0; st >>= 1) {
         if (threadIdx.x < st) {
-            XYZZ<F> q = XYZZ<F>::load(sm + (threadIdx.x + st) * L);
-            ec_add<F>(acc, q);
+            ec_add<F>(acc, XYZZ<F>::load(sm + (threadIdx.x + st) * L));
             acc.store(sm + threadIdx.x * L);
         }
         __syncthreads();
     }
-    if (threadIdx.x == 0) acc.store(win_out + uint64_t(w) * L);
+    if (threadIdx.x == 0) acc.store(plane_out + ((uint64_t(set) * p.c + j) * chunks + chunk) * L);
+}
+
+// block = set, thread j sums plane j over the chunks; thread 0 then runs the c-step Horner  sum_j 2^j S_j
+template <class F>
+__global__ void __launch_bounds__(32) k_msm_reduce_sets(const uint32_t* __restrict__ plane_in, MsmPlan p, unsigned chunks,
+                                                        uint32_t* __restrict__ set_out) {
+    extern __shared__ uint4 sm4[];
+    uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
+    constexpr int L = XYZZ<F>::BYTES / 4;
+    const unsigned set = blockIdx.x, j = threadIdx.x;
+    if (j < p.c) {
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (unsigned ch = 0; ch < chunks; ++ch)
+            ec_add<F>(acc, XYZZ<F>::load(plane_in + ((uint64_t(set) * p.c + j) * chunks + ch) * L));
+        acc.store(sm + j * L);
+    }
+    __syncthreads();
+    if (j == 0) {
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (int k = (int)p.c - 1; k >= 0; --k) {
+            acc = ec_dbl<F>(acc);
+            ec_add<F>(acc, XYZZ<F>::load(sm + k * L));
+        }
+        acc.store(set_out + uint64_t(set) * L);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
-// 7. final: Horner over windows, affine, canonical
+// 7. final: Horner over a ballot's sets (one-shot bases), affine, canonical
 // ---------------------------------------------------------------------------------------------
 template <class F>
 VSP_DEV void store_canonical_affine(uint64_t* out, const XYZZ<F>& p) {
@@ -348,30 +361,34 @@ VSP_DEV void store_canonical_affine(uint64_t* out, const XYZZ<F>& p) {
     a.store(out);
 }
 
+// block = ballot (lane 0 works): out + ballot * out_stride (u64 limbs)
 template <class F>
-__global__ void k_msm_final(const uint32_t* __restrict__ win, MsmPlan p, uint64_t* __restrict__ out, int raw) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+__global__ void k_msm_final(const uint32_t* __restrict__ set_in, MsmPlan p, uint64_t* __restrict__ out,
+                            uint64_t out_stride, int raw) {
+    if (threadIdx.x != 0) return;
     constexpr int L = XYZZ<F>::BYTES / 4;
+    const unsigned b = blockIdx.x;
     XYZZ<F> acc = XYZZ<F>::inf();
-    for (int w = (int)p.windows - 1; w >= 0; --w) {
-        for (unsigned k = 0; k < p.c; ++k) acc = ec_dbl<F>(acc);
-        XYZZ<F> q = XYZZ<F>::load(win + uint64_t(w) * L);
-        ec_add<F>(acc, q);
+    for (int w = (int)p.sets - 1; w >= 0; --w) {
+        if (w != (int)p.sets - 1)
+            for (unsigned k = 0; k < p.c; ++k) acc = ec_dbl<F>(acc);
+        ec_add<F>(acc, XYZZ<F>::load(set_in + (uint64_t(b) * p.sets + w) * L));
     }
+    uint64_t* o = out + uint64_t(b) * out_stride;
     if (raw)
-        acc.store(out);  // Montgomery-form XYZZ for the prover's assembly kernel: skips the inversion
+        acc.store(o);  // Montgomery-form XYZZ for the prover's assembly kernel: skips the inversion
     else
-        store_canonical_affine<F>(out, acc);
+        store_canonical_affine<F>(o, acc);
 }
 
 template <class F>
-__global__ void k_write_infinity(uint64_t* out, int raw) {
+__global__ void k_write_infinity(uint64_t* out, uint64_t out_stride, int raw) {
     const int n = (raw ? XYZZ<F>::BYTES : Affine<F>::BYTES) / 8;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) out[uint64_t(blockIdx.x) * out_stride + i] = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
-// bases
+// bases: Montgomery conversion and the window table  T[w][i] = 2^(c w) P_i
 // ---------------------------------------------------------------------------------------------
 template <class F>
 __global__ void k_bases_to_mont(uint32_t* pts, uint64_t n) {
@@ -384,25 +401,86 @@ __global__ void k_bases_to_mont(uint32_t* pts, uint64_t n) {
     a.store(pts + i * L);
 }
 
+// level w from level w - 1: c doublings per point, then back to affine with one inversion per TABLE_CH points
+// (Montgomery's trick).  Runs once per proving-key query.
+constexpr int TABLE_CH = 4;
+template <class F>
+__global__ void __launch_bounds__(64) k_table_level(uint32_t* table, uint64_t n, unsigned level, unsigned c) {
+    using E = typename F::T;
+    constexpr int L = Affine<F>::BYTES / 4;
+    const uint64_t base = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) * TABLE_CH;
+    if (base >= n) return;
+    const uint32_t* src = table + uint64_t(level - 1) * n * L;
+    uint32_t* dst = table + uint64_t(level) * n * L;
+    XYZZ<F> r[TABLE_CH];
+    E den[TABLE_CH], pre[TABLE_CH];
+    for (int q = 0; q < TABLE_CH; ++q) {
+        r[q] = XYZZ<F>::inf();
+        if (base + q < n) {
+            Affine<F> pt = Affine<F>::load(src + (base + q) * L);
+            if (!pt.is_inf()) {
+                r[q] = ec_dbl_affine<F>(pt);
+                for (unsigned k = 1; k < c; ++k) r[q] = ec_dbl<F>(r[q]);
+            }
+        }
+        den[q] = r[q].is_inf() ? F::one() : F::mul(r[q].ZZ, r[q].ZZZ);
+        pre[q] = q ? F::mul(pre[q - 1], den[q]) : den[q];
+    }
+    E inv = F::inv(pre[TABLE_CH - 1]);
+    for (int q = TABLE_CH - 1; q >= 0; --q) {
+        const E dinv = q ? F::mul(inv, pre[q - 1]) : inv;  // 1 / (ZZ ZZZ) of point q
+        inv = F::mul(inv, den[q]);
+        if (base + q >= n) continue;
+        Affine<F> a = Affine<F>::inf();
+        if (!r[q].is_inf()) {
+            a.x = F::mul(r[q].X, F::mul(dinv, r[q].ZZZ));
+            a.y = F::mul(r[q].Y, F::mul(dinv, r[q].ZZ));
+        }
+        a.store(dst + (base + q) * L);
+    }
+}
+
+// window width minimising  (bucket additions) + (bit-plane reduction additions, ~1.4x as expensive each)
+static unsigned choose_window(uint64_t n, bool table) {
+    double best = 1e300;
+    unsigned best_c = 4;
+    for (unsigned c = 4; c <= 16; ++c) {
+        const double w = 255 / c + 1, red = 0.7 * c * double(1u << (c - 1));
+        const double cost = table ? w * double(n) + red : w * (double(n) + red);
+        if (cost < best) {
+            best = cost;
+            best_c = c;
+        }
+    }
+    return best_c;
+}
 
 // ---------------------------------------------------------------------------------------------
 // driver
 // ---------------------------------------------------------------------------------------------
 template <class F>
 static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64_t n, const uint32_t* d_scalars,
-                     uint64_t* d_out, bool raw) {
+                     uint64_t scalar_stride, unsigned batch, uint64_t* d_out, uint64_t out_stride, bool raw) {
+    constexpr int KC_ACC = std::is_same<F, FqOps>::value ? KC_MSM_ACC_G1 : KC_MSM_ACC_G2;
     if (n > bases.n) return set_error(ctx, VSP_E_INVALID, "multiexp: %llu scalars for %llu bases", (unsigned long long)n,
                                       (unsigned long long)bases.n);
-    if (n >= (uint64_t(1) << 31)) return set_error(ctx, VSP_E_INVALID, "multiexp: n must be < 2^31");
+    if (batch == 0) return VSP_OK;
     if (n == 0) {
-        VSP_LAUNCH(ctx, k_write_infinity<F>, 1, 32, 0, s, d_out, raw ? 1 : 0);
+        VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_write_infinity<F>, batch, 32, 0, s, d_out, out_stride, raw ? 1 : 0);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         return VSP_OK;
     }
-    const MsmPlan p = make_plan(n);
-    const uint64_t total = n * p.windows;
-    if (total >= (uint64_t(1) << 32)) return set_error(ctx, VSP_E_INVALID, "multiexp: n * windows must be < 2^32");
-    constexpr int L = XYZZ<F>::BYTES / 4;
+    MsmPlan p;
+    p.c = bases.table ? bases.c : choose_window(n, false);
+    p.windows = 255 / p.c + 1;
+    p.nb_log = p.c - 1;
+    p.sets = bases.table ? 1 : p.windows;
+    p.batch = batch;
+    p.stride = bases.table ? bases.n : 0;
+    p.buckets = (uint64_t(batch) * p.sets) << p.nb_log;
+    const uint64_t total = n * p.windows * batch;
+    if (total >= (uint64_t(1) << 32) || p.buckets >= (uint64_t(1) << 31) || batch * p.sets > 65535)
+        return set_error(ctx, VSP_E_INVALID, "multiexp: batch * n * windows must be < 2^32");
     const unsigned tiles = (unsigned)((p.buckets + SCAN_TILE - 1) / SCAN_TILE);
 
     DevBuf keys, counts, offsets, cursors, task_off, tile_scratch, sorted, heavy, heavy_count;
@@ -419,50 +497,78 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_CUDA_CHECK(ctx, cudaMemsetAsync(cursors.p, 0, (p.buckets + 1) * 4, s));
     VSP_CUDA_CHECK(ctx, cudaMemsetAsync(heavy_count.p, 0, 4, s));
 
-    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_digits, (unsigned)((n + 127) / 128), 128, 0, s, d_scalars, n, p, keys.as<uint32_t>(),
-               counts.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_digits, dim3((unsigned)((n + 127) / 128), batch), 128, 0, s, d_scalars, n,
+                 scalar_stride, p, keys.as<uint32_t>(), counts.as<uint32_t>());
     VSP_TRY(exclusive_scan<0>(ctx, s, counts.as<uint32_t>(), p.buckets, offsets.as<uint32_t>(),
                               tile_scratch.as<uint32_t>()));
     VSP_TRY(exclusive_scan<1>(ctx, s, counts.as<uint32_t>(), p.buckets, task_off.as<uint32_t>(),
                               tile_scratch.as<uint32_t>()));
-    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_scatter, (unsigned)((total + 255) / 256), 256, 0, s, keys.as<uint32_t>(), total, n,
-               offsets.as<uint32_t>(), cursors.as<uint32_t>(), sorted.as<uint32_t>());
-    // upper bound on the number of tasks, known without a device read-back: every bucket contributes
-    // ceil(count / T) <= count / T + 1
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_scatter, (unsigned)((total + 255) / 256), 256, 0, s, keys.as<uint32_t>(), total,
+                 n, p, offsets.as<uint32_t>(), cursors.as<uint32_t>(), sorted.as<uint32_t>());
+    // upper bound on the number of tasks, known without a device read-back: ceil(count / T) <= count / T + 1
     const uint64_t max_tasks = total / TASK_POINTS + p.buckets;
     DevBuf tasks, partial;
     VSP_TRY(tasks.alloc(ctx, max_tasks * sizeof(Task), s));
     VSP_TRY(partial.alloc(ctx, max_tasks * XYZZ<F>::BYTES, s));
     VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_tasks, (unsigned)((p.buckets + 127) / 128), 128, 0, s, offsets.as<uint32_t>(),
-               task_off.as<uint32_t>(), p.buckets, tasks.as<Task>(), heavy.as<uint32_t>(), heavy_count.as<uint32_t>());
-    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+                 task_off.as<uint32_t>(), p.buckets, tasks.as<Task>(), heavy.as<uint32_t>(), heavy_count.as<uint32_t>());
     // the exact task count lives on the device (task_off[buckets]); the grid covers the bound and extra threads exit
-    VSP_LAUNCH_K(ctx, (std::is_same<F, FqOps>::value ? KC_MSM_ACC_G1 : KC_MSM_ACC_G2), k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
-               sorted.as<uint32_t>(), tasks.as<Task>(), task_off.as<uint32_t>() + p.buckets, partial.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_ACC, k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
+                 sorted.as<uint32_t>(), tasks.as<Task>(), task_off.as<uint32_t>() + p.buckets, partial.as<uint32_t>());
     // algorithmic work of this launch for the live roofline: bucket additions scheduled (= non-zero digits,
     // offsets[buckets]) x 11 field multiplications (the reference's mixed Jacobian add) x I_mul(limbs)
     kprof_units(ctx, ctx->last_prof, 11.0 * (std::is_same<F, FqOps>::value ? 300.0 : 3.0 * 300.0),
                 offsets.as<uint32_t>() + p.buckets, s);
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
-               heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>());
-    const unsigned segs_per_window = 1u << (p.nb_log - p.seg_log);
-    const unsigned n_segs = p.windows * segs_per_window;
-    DevBuf seg, win;
-    VSP_TRY(seg.alloc(ctx, (size_t)n_segs * XYZZ<F>::BYTES, s));
-    VSP_TRY(win.alloc(ctx, (size_t)p.windows * XYZZ<F>::BYTES, s));
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_segments<F>, (n_segs + 63) / 64, 64, 0, s, partial.as<uint32_t>(),
-               task_off.as<uint32_t>(), p, seg.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_window_sums<F>, p.windows, WSUM_THREADS, WSUM_THREADS * XYZZ<F>::BYTES, s, seg.as<uint32_t>(),
-               p, win.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_final<F>, 1, 32, 0, s, win.as<uint32_t>(), p, d_out, raw ? 1 : 0);
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_light<F>, (unsigned)((p.buckets + 63) / 64), 64, 0, s,
+                 task_off.as<uint32_t>(), p.buckets, partial.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
+                 heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>());
+    const unsigned n_sets = batch * p.sets;
+    const unsigned chunks = (unsigned)(((uint64_t(1) << p.nb_log) + RED_CHUNK - 1) / RED_CHUNK);
+    DevBuf planes, sets;
+    VSP_TRY(planes.alloc(ctx, (size_t)n_sets * p.c * chunks * XYZZ<F>::BYTES, s));
+    VSP_TRY(sets.alloc(ctx, (size_t)n_sets * XYZZ<F>::BYTES, s));
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_planes<F>, dim3(chunks, p.c, n_sets), RED_THREADS,
+                 RED_THREADS * XYZZ<F>::BYTES, s, partial.as<uint32_t>(), task_off.as<uint32_t>(), p, chunks,
+                 planes.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, n_sets, 32, 32 * XYZZ<F>::BYTES, s, planes.as<uint32_t>(), p,
+                 chunks, sets.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_final<F>, batch, 32, 0, s, sets.as<uint32_t>(), p, d_out, out_stride,
+                 raw ? 1 : 0);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    return VSP_OK;
+}
+
+// after d_pts[0, n) holds Montgomery affine points: fix the window width and, for resident bases, build the table
+template <class F>
+static int bases_finalize_t(vsp_ctx* ctx, cudaStream_t s, BasesDev* b, bool table) {
+    constexpr int L = Affine<F>::BYTES / 4;
+    b->c = choose_window(b->n ? b->n : 1, table);
+    b->windows = 255 / b->c + 1;
+    b->table = false;
+    if (!table || b->n == 0) return VSP_OK;
+    if (b->n * b->windows >= (uint64_t(1) << 31)) return VSP_OK;  // too large to index: stay table-less
+    uint32_t* t = nullptr;
+    const size_t bytes = (size_t)b->n * b->windows * Affine<F>::BYTES;
+    if (cudaMalloc(&t, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return VSP_OK;  // not enough memory for the table: the table-less path still works
+    }
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(t, b->d_pts, (size_t)b->n * Affine<F>::BYTES, cudaMemcpyDeviceToDevice, s));
+    const uint64_t threads = (b->n + TABLE_CH - 1) / TABLE_CH;
+    for (unsigned w = 1; w < b->windows; ++w)
+        VSP_LAUNCH_K(ctx, KC_OTHER, k_table_level<F>, (unsigned)((threads + 63) / 64), 64, 0, s, t, b->n, w, b->c);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    cudaFree(b->d_pts);
+    b->d_pts = t;
+    b->table = true;
     (void)L;
     return VSP_OK;
 }
 
-
 // ---------------------------------------------------------------------------------------------
-// sum of k affine points (join step of a sharded multiexp; also Groth16 proof assembly helpers)
+// sum of k affine points (join step of a sharded multiexp)
 // ---------------------------------------------------------------------------------------------
 template <class F>
 __global__ void k_points_sum(const uint64_t* pts, uint64_t k, uint64_t* out) {
@@ -471,31 +577,32 @@ __global__ void k_points_sum(const uint64_t* pts, uint64_t k, uint64_t* out) {
     XYZZ<F> acc = XYZZ<F>::inf();
     for (uint64_t i = 0; i < k; ++i) {
         Affine<F> a = Affine<F>::load(pts + i * L8);
+        if (a.is_inf()) continue;
         a.x = F::to_mont(a.x);
         a.y = F::to_mont(a.y);
-        if (a.is_inf()) continue;
         ec_madd<F>(acc, a);
     }
     store_canonical_affine<F>(out, acc);
 }
-
-
 
 }  // namespace
 
 // one translation unit per curve keeps ptxas time down (msm_g1.cu / msm_g2.cu)
 #define VSP_MSM_INSTANTIATE(SUFFIX, F)                                                                              \
     int msm_run_##SUFFIX(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64_t n, const uint32_t* d_scalars, \
-                         uint64_t* d_out, bool raw) {                                                               \
-        return msm_run_t<F>(ctx, s, bases, n, d_scalars, d_out, raw);                                               \
+                         uint64_t scalar_stride, unsigned batch, uint64_t* d_out, uint64_t out_stride, bool raw) {  \
+        return msm_run_t<F>(ctx, s, bases, n, d_scalars, scalar_stride, batch, d_out, out_stride, raw);             \
+    }                                                                                                               \
+    int bases_finalize_##SUFFIX(vsp_ctx* ctx, cudaStream_t s, BasesDev* b, bool table) {                            \
+        return bases_finalize_t<F>(ctx, s, b, table);                                                               \
     }                                                                                                               \
     int points_sum_##SUFFIX(vsp_ctx* ctx, cudaStream_t s, uint64_t k, const uint64_t* d_points, uint64_t* d_out) {  \
-        VSP_LAUNCH(ctx, k_points_sum<F>, 1, 32, 0, s, d_points, k, d_out);                                          \
+        VSP_LAUNCH_K(ctx, KC_FIXED, k_points_sum<F>, 1, 32, 0, s, d_points, k, d_out);                              \
         VSP_CUDA_CHECK(ctx, cudaGetLastError());                                                                    \
         return VSP_OK;                                                                                              \
     }                                                                                                               \
     int bases_to_mont_##SUFFIX(vsp_ctx* ctx, cudaStream_t s, uint32_t* d_pts, uint64_t n) {                         \
-        VSP_LAUNCH(ctx, k_bases_to_mont<F>, (unsigned)((n + 127) / 128), 128, 0, s, d_pts, n);                      \
+        VSP_LAUNCH_K(ctx, KC_OTHER, k_bases_to_mont<F>, (unsigned)((n + 127) / 128), 128, 0, s, d_pts, n);          \
         VSP_CUDA_CHECK(ctx, cudaGetLastError());                                                                    \
         return VSP_OK;                                                                                              \
     }

@@ -329,11 +329,11 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
             VSP_CUDA_CHECK(ctx, cudaGetLastError());
         }
     }
-    VSP_TRY(bases_upload(ctx, false, pk->nv + 1, d->A_query, &pk->A));
-    VSP_TRY(bases_upload(ctx, false, d->B_count, d->B_g1, &pk->Bg1));
-    VSP_TRY(bases_upload(ctx, true, d->B_count, d->B_g2, &pk->Bg2));
-    VSP_TRY(bases_upload(ctx, false, pk->m - 1, d->H_query, &pk->H));
-    VSP_TRY(bases_upload(ctx, false, pk->na, d->L_query, &pk->L));
+    VSP_TRY(bases_upload(ctx, false, pk->nv + 1, d->A_query, &pk->A, true));
+    VSP_TRY(bases_upload(ctx, false, d->B_count, d->B_g1, &pk->Bg1, true));
+    VSP_TRY(bases_upload(ctx, true, d->B_count, d->B_g2, &pk->Bg2, true));
+    VSP_TRY(bases_upload(ctx, false, pk->m - 1, d->H_query, &pk->H, true));
+    VSP_TRY(bases_upload(ctx, false, pk->na, d->L_query, &pk->L, true));
     pk->B_count = d->B_count;
     for (uint64_t k = 0; k < d->B_count; ++k)
         if (d->B_idx[k] > pk->nv) return set_error(ctx, VSP_E_INVALID, "B_query index out of range");
@@ -348,8 +348,8 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
     memcpy(f2 + 24, d->delta_g2, 192);
     memcpy(pk->h_delta_g1, d->delta_g1, 96);
     memcpy(pk->h_delta_g2, d->delta_g2, 192);
-    VSP_TRY(bases_upload(ctx, false, 3, f1, &pk->fixed1));
-    VSP_TRY(bases_upload(ctx, true, 2, f2, &pk->fixed2));
+    VSP_TRY(bases_upload(ctx, false, 3, f1, &pk->fixed1, false));
+    VSP_TRY(bases_upload(ctx, true, 2, f2, &pk->fixed2, false));
 
     // coset tables (multiplicative_generator = 7)
     const Fr4 g = from_u64(7), ginv = inv(g);
