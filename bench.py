@@ -7,9 +7,10 @@
 A step = one pass of the hot path over one batch of B synthetic ballots per GPU (weak scaling).  The workload is
 BASELINE.json configs[3] ("batched ballot proving ... sharded proof-per-GPU") on the depth-16 stand-in circuit of
 configs[2]: 65,505 constraints + 30 primary inputs -> evaluation domain 2^16 (tools/workload.py).
-  value  : proofs/s with the assignments already resident in HBM (vsp_prove_batch_dev), device-timed, max over ranks
-  e2e    : the same through the host-buffer C-ABI call (vsp_prove_batch): pinned host witnesses in, proofs out,
-           H2D/D2H inside the timed region
+  value  : ballots/s (SAVER ciphertext + encrypted_input proof each) with the assignments already resident in HBM
+           (vsp_saver_encrypt_batch_dev), device-timed, max over ranks
+  e2e    : the same through the host-buffer C-ABI call (vsp_saver_encrypt_batch): pinned host witnesses in,
+           ciphertexts + proofs out, H2D/D2H inside the timed region
   roofline / kernels : per-kernel-class device times measured live with CUDA events inside the library
   cpu_baseline / --impl reference : the CPU oracle's restatement of the reference prover on the host cores
 """
@@ -42,7 +43,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--ballots", type=int, default=16, help="ballots per GPU per step")
+    ap.add_argument("--ballots", type=int, default=256, help="ballots per GPU per step")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--constraints", type=int, default=NUM_CONSTRAINTS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -149,8 +150,10 @@ def run_b200(args):
     cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
     _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
     pk = vsp.ProvingKey(ctx, wl.proving_key_arrays(vsp, ctx, cs, m, seed=7))
-    pub_arr, _gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
+    pub_arr, gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
+    gabc = np.ascontiguousarray(gabc[:MSG_SIZE])
     pub = vsp.SaverPublicKey(pub_arr)
+    key = pub.resident(ctx, gabc)
     ni, na = cs["num_inputs"], cs["num_aux"]
     prim = torch.empty((B, ni, 4), dtype=torch.int64).pin_memory()
     aux = torch.empty((B, na, 4), dtype=torch.int64).pin_memory()
@@ -165,14 +168,14 @@ def run_b200(args):
     assign[:, 1:ni + 1] = prim.cuda()
     assign[:, ni + 1:] = aux.cuda()
     d_proofs = torch.zeros((B, 48), dtype=torch.int64, device="cuda")
-    lib, h_ctx, h_pk = ctx._lib, ctx._h, pk._h
+    d_cts = torch.zeros((B, MSG_SIZE + 2, 12), dtype=torch.int64, device="cuda")
 
+    # one step = B ballots through encrypt_op::process: SAVER ciphertext (27 G1) + encrypted_input Groth16 proof
     def step_dev():
-        pk.prove_batch_dev(B, assign.data_ptr(), rs, d_proofs.data_ptr(), pub)
+        pk.encrypt_batch_dev(key, B, assign.data_ptr(), rs, d_cts.data_ptr(), d_proofs.data_ptr())
 
     def step_e2e():
-        out = pk.prove_batch(prim_np, aux_np, rs, pub)  # host buffers in, host proofs out (synchronises)
-        return out
+        return pk.encrypt_batch(key, prim_np, aux_np, rs)  # host buffers in, host ciphertexts + proofs out (synchronises)
 
     # ---- device-resident timing ---------------------------------------------------------------------
     with torch.cuda.stream(stream):
@@ -208,22 +211,24 @@ def run_b200(args):
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record(stream)
         for _ in range(K):
-            proofs_e2e = step_e2e()
+            cts_e2e, proofs_e2e = step_e2e()
         f1.record(stream)
         barrier(world)
         ms_e2e = max(f0.elapsed_time(f1), (time.perf_counter() - t0) * 1e3)
     ms_e2e = max_over_ranks(ms_e2e, world)
-    same = bool(np.array_equal(proofs_e2e, proofs_dev))
+    cts_dev = d_cts.cpu().numpy().view(np.uint64)
+    same = bool(np.array_equal(proofs_e2e, proofs_dev) and np.array_equal(cts_e2e, cts_dev))
 
     return dict(world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
                 clocks=clocks, launches=launches, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
-                proofs=proofs_dev, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes), d2h=int(B * 384), stream=stream)
+                proofs=proofs_dev, cts=cts_dev, gabc=gabc, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes),
+                d2h=int(B * 384 + cts_dev.nbytes), stream=stream)
 
 
 # ---------------------------------------------------------------------------------------------------------
 # CPU legs (the only places that touch oracle/): cpu_baseline of the b200 arm and the --impl reference arm
 # ---------------------------------------------------------------------------------------------------------
-def cpu_prover(args, cs_arrays, pk_arrays, prim, aux, rs, pub_arr, n_proofs: int):
+def cpu_prover(args, cs_arrays, pk_arrays, prim, aux, rs, pub_arr, gabc, n_proofs: int):
     """Times the oracle's restatement of the reference prover (witness_map + 5 BDLO12 multiexps + assembly, the
     encrypted_input adjustment) on `n_proofs` ballots with every host core (chunked multiexp as the reference's
     MULTICORE hook intends, sparse_vector.hpp:224-229).  Returns (seconds, proofs, cores)."""
@@ -235,13 +240,16 @@ def cpu_prover(args, cs_arrays, pk_arrays, prim, aux, rs, pub_arr, n_proofs: int
         pass
     cref.lib().orc_set_num_threads(cores)
     desc = fx.fill_pk(cref.ProvingKeyDesc(), pk_arrays)
-    out = []
+    opub = fx.fill_struct(cref.SaverPubkeyDesc(), pub_arr)
+    out, cts = [], []
     t0 = time.perf_counter()
     for b in range(n_proofs):
         r, s, rsv = cref.limbs_to_ints(rs[b])
-        out.append(cref.groth16_prove(desc, np.ascontiguousarray(prim[b]), np.ascontiguousarray(aux[b]), r, s, rsv,
+        p = np.ascontiguousarray(prim[b])
+        cts.append(cref.saver_ciphertext(opub, gabc, np.ascontiguousarray(p[:MSG_SIZE]), rsv))
+        out.append(cref.groth16_prove(desc, p, np.ascontiguousarray(aux[b]), r, s, rsv,
                                       pub_arr["gamma_inverse_sum_s_g1"], chunks=cores))
-    return time.perf_counter() - t0, np.stack(out), cores
+    return time.perf_counter() - t0, np.stack(out), np.stack(cts), cores
 
 
 def run_reference(args):
@@ -260,7 +268,8 @@ def run_reference(args):
     cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
     _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
     pk_arr = wl.proving_key_arrays(vsp, ctx, cs, m, seed=7)
-    pub_arr, _ = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
+    pub_arr, gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
+    gabc = np.ascontiguousarray(gabc[:MSG_SIZE])
     ctx.close()
     n = 1  # one ballot per step: a bounded sample of the B-ballot batch
     prim, aux = [], []
@@ -271,11 +280,11 @@ def run_reference(args):
     rs = wl.random_fr(3 * n, seed=99).reshape(n, 3, 4)
     K, W = args.steps, min(args.warmup, 1)
     for _ in range(W):
-        cpu_prover(args, cs, pk_arr, prim, aux, rs, pub_arr, n)
+        cpu_prover(args, cs, pk_arr, prim, aux, rs, pub_arr, gabc, n)
     total = 0.0
     cores = 1
     for _ in range(K):
-        sec, _, cores = cpu_prover(args, cs, pk_arr, prim, aux, rs, pub_arr, n)
+        sec, _, _, cores = cpu_prover(args, cs, pk_arr, prim, aux, rs, pub_arr, gabc, n)
         total += sec
     value = n * K / total
     sample = "%d ballot per step (of the %d-ballot batch), %d steps" % (n, args.ballots * world, K)
@@ -407,10 +416,12 @@ def main():
         line["extras"] = run_extras(res, peaks, p_int)
     if not args.no_cpu_baseline:
         pk_arr = res["pk"].arrays
-        sec, cpu_proofs, cores = cpu_prover(args, res["cs"], pk_arr, res["prim"], res["aux"], res["rs"], res["pub_arr"], 1)
+        sec, cpu_proofs, cpu_cts, cores = cpu_prover(args, res["cs"], pk_arr, res["prim"], res["aux"], res["rs"],
+                                                     res["pub_arr"], res["gabc"], 1)
         line["cpu_baseline"] = {"value": 1.0 / sec, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": "ballot 0 of the batch, proved once by oracle/vsp_oracle.c (%.1f s)" % sec,
-                                "gpu_proof_bit_exact": bool(np.array_equal(cpu_proofs[0], res["proofs"][0]))}
+                                "gpu_proof_bit_exact": bool(np.array_equal(cpu_proofs[0], res["proofs"][0])),
+                                "gpu_ciphertext_bit_exact": bool(np.array_equal(cpu_cts[0], res["cts"][0]))}
     print(json.dumps(line))
 
 

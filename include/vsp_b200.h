@@ -65,6 +65,7 @@ typedef struct vsp_ctx vsp_ctx;
 typedef struct vsp_g1_bases vsp_g1_bases;
 typedef struct vsp_g2_bases vsp_g2_bases;
 typedef struct vsp_pk vsp_pk;
+typedef struct vsp_saver_pub vsp_saver_pub;
 
 /* ---- context ------------------------------------------------------------------------------ */
 /* cuda_stream: an existing CUstream / cudaStream_t to launch on (e.g. torch's current stream), or NULL for a
@@ -185,6 +186,21 @@ VSP_API int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pu
                       const uint64_t r[4], const uint64_t s[4], uint64_t *out_ct, uint64_t *out_proof);
 VSP_API int vsp_saver_ciphertext(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
                          const uint64_t *msg, const uint64_t r_saver[4], uint64_t *out_ct);
+/* Batched SAVER (the 4,096-ballot configuration): the public key's 3 msg_size + 2 G1 bases stay on the GPU as 8-bit
+ * fixed-base tables; k ballots are encrypted and proved in chunks that share every launch.  The message of ballot b
+ * is the first msg_size primary inputs ("plain text should be a prefix of the primary input",
+ * elgamal_verifiable.hpp:336-339).  rs = k x (r, s, r_saver).  out_cts: k x (msg_size + 2) G1; out_proofs: k x 48 limbs.
+ * The _dev variant takes k device-resident assignments (1 || primary || auxiliary) and leaves both results on the
+ * device, stream-ordered. */
+VSP_API int vsp_saver_pub_load(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
+                               vsp_saver_pub **out);
+VSP_API void vsp_saver_pub_destroy(vsp_saver_pub *sp);
+VSP_API int vsp_saver_encrypt_batch(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pub *sp, uint64_t k,
+                                    const uint64_t *primary, const uint64_t *aux, const uint64_t *rs, uint64_t *out_cts,
+                                    uint64_t *out_proofs);
+VSP_API int vsp_saver_encrypt_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pub *sp, uint64_t k,
+                                        const uint64_t *d_assignments, const uint64_t *rs, uint64_t *d_cts,
+                                        uint64_t *d_proofs);
 /* rnd = r | z1 | z2 */
 VSP_API int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
                           const uint64_t *ct_in, const uint64_t *proof_in, uint64_t *ct_out, uint64_t *proof_out);

@@ -120,3 +120,35 @@ def test_saver_encrypt_and_rerandomize_match_oracle(vsp, ctx):
     assert np.array_equal(ct2, want_ct2)
     assert np.array_equal(proof2, want_proof2)
     pk.close()
+
+
+@pytest.mark.parametrize("binary", [True, False])
+def test_encrypt_batch_matches_oracle(vsp, ctx, binary):
+    """vsp_saver_encrypt_batch: k ballots, chunked (VSP_BATCH_CHUNK default 64 -> one chunk; k = 7 exercises ragged
+    lanes), messages with 0 / 1 and general slots, each ciphertext and proof against the oracle"""
+    nc, ni, msg_size, k = 97, 30, 25, 7
+    cs, _, _ = synthetic_r1cs(nc, ni, 0, binary=binary)
+    arr = synthetic_pk_arrays(cs, 41)
+    pub_arr, gamma_abc_rest = synthetic_saver_pub(msg_size, seed=42)
+    gamma_abc_rest = np.ascontiguousarray(gamma_abc_rest[:msg_size])
+    pub = vsp.SaverPublicKey(pub_arr)
+    opub = fx.fill_struct(cref.SaverPubkeyDesc(), pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    opk = _oracle_pk(arr)
+    key = pub.resident(ctx, gamma_abc_rest)
+    rng = random.Random(43)
+    prim, aux, rs = [], [], []
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=b, binary=binary)
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4))
+    cts, proofs = pk.encrypt_batch(key, np.stack(prim), np.stack(aux), np.stack(rs))
+    for b in range(k):
+        r, s, rsv = cref.limbs_to_ints(rs[b])
+        msg = np.ascontiguousarray(prim[b][:msg_size])
+        assert np.array_equal(cts[b], cref.saver_ciphertext(opub, gamma_abc_rest, msg, rsv)), b
+        want = cref.groth16_prove(opk, prim[b], aux[b], r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"])
+        assert np.array_equal(proofs[b], want), b
+    key.close()
+    pk.close()

@@ -26,7 +26,7 @@ from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADI
                    SaverPubkeyDesc, VspError)
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
-           "G2Bases", "ProvingKey", "SaverPublicKey", "domain_plan", "VspError", "library_path"]
+           "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path"]
 
 FR_MULTIPLICATIVE_GENERATOR = 7
 
@@ -277,6 +277,38 @@ class SaverPublicKey:
         self.arrays = arrays  # keeps the numpy buffers alive
         self.desc = _fill(SaverPubkeyDesc(), arrays)
         self.msg_size = int(arrays["msg_size"])
+        self._resident = None
+
+    def resident(self, ctx: "Context", gamma_abc_rest) -> "ResidentSaverKey":
+        """the key's fixed-base tables on the GPU (built once) for the batched encrypt path"""
+        if self._resident is None or self._resident.ctx is not ctx or self._resident._h is None:
+            self._resident = ResidentSaverKey(ctx, self, gamma_abc_rest)
+        return self._resident
+
+
+class ResidentSaverKey:
+    """vsp_saver_pub: delta, delta_s, gamma_ABC rest, t and delta_sum_s as 8-bit fixed-base tables on the GPU."""
+
+    def __init__(self, ctx: "Context", pubkey: SaverPublicKey, gamma_abc_rest):
+        self.ctx, self.pubkey = ctx, pubkey
+        g = _a(gamma_abc_rest, 12)
+        if g.shape[0] < pubkey.msg_size:
+            raise ValueError("gamma_abc_rest shorter than msg_size")
+        h = C.c_void_p()
+        ctx.check(ctx._lib.vsp_saver_pub_load(ctx._h, C.byref(pubkey.desc), _p(g), C.byref(h)))
+        self._h = h
+        self.msg_size = pubkey.msg_size
+
+    def close(self):
+        if getattr(self, "_h", None) and getattr(self.ctx, "_h", None):
+            self.ctx._lib.vsp_saver_pub_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class ProvingKey:
@@ -344,6 +376,25 @@ class ProvingKey:
         gi = _p(pubkey.arrays["gamma_inverse_sum_s_g1"]) if pubkey is not None else None
         self.ctx.check(self.ctx._lib.vsp_prove_batch_dev(self.ctx._h, self._h, k, C.c_void_p(d_assignments), _p(q), gi,
                                                          C.c_void_p(d_proofs)))
+
+    def encrypt_batch(self, key: "ResidentSaverKey", primary, auxiliary, rs):
+        """k ballots through encrypt_op::process: the message is the first msg_size primary inputs of each ballot.
+        primary (k, ni, 4), auxiliary (k, na, 4), rs (k, 3, 4) = (r, s, r_saver) -> (cts (k, msg_size + 2, 12), proofs (k, 48))"""
+        p = np.ascontiguousarray(primary, dtype=np.uint64)
+        a = np.ascontiguousarray(auxiliary, dtype=np.uint64)
+        q = np.ascontiguousarray(rs, dtype=np.uint64)
+        k = q.shape[0]
+        cts = np.zeros((k, key.msg_size + 2, 12), dtype=np.uint64)
+        proofs = np.zeros((k, 48), dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_saver_encrypt_batch(self.ctx._h, self._h, key._h, k, _p(p), _p(a), _p(q), _p(cts),
+                                                             _p(proofs)))
+        return cts, proofs
+
+    def encrypt_batch_dev(self, key: "ResidentSaverKey", k: int, d_assignments: int, rs, d_cts: int, d_proofs: int):
+        """device-resident ballots (k x (1 || primary || auxiliary)); ciphertexts and proofs stay on the device"""
+        q = np.ascontiguousarray(rs, dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_saver_encrypt_batch_dev(self.ctx._h, self._h, key._h, k, C.c_void_p(d_assignments),
+                                                                 _p(q), C.c_void_p(d_cts), C.c_void_p(d_proofs)))
 
     def encrypt(self, pubkey: SaverPublicKey, gamma_abc_rest, msg, primary, auxiliary, r_saver: int, r: int, s: int):
         """encrypt_op<elgamal_verifiable>::process -> (cipher_text (msg_size + 2, 12), proof (48,))"""

@@ -90,6 +90,10 @@ SYMBOLS = [
     ("vsp_prove_batch_dev", _int, [_vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_saver_encrypt", _int, [_vp, _vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_saver_ciphertext", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp]),
+    ("vsp_saver_pub_load", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, C.POINTER(_vp)]),
+    ("vsp_saver_pub_destroy", None, [_vp]),
+    ("vsp_saver_encrypt_batch", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_saver_encrypt_batch_dev", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_saver_rerandomize", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
 ]

@@ -172,9 +172,12 @@ int ntt_tables_ensure(vsp_ctx* ctx, unsigned log_n);
 void ntt_tables_free(vsp_ctx* ctx);
 // power-of-two NTT of 2^log_n canonical/any-form Fr values, out of place (d_in may equal d_out only if a scratch
 // is supplied internally); inverse scales by 2^-log_n.  pre / post: optional per-index multiplier tables.
+// `batch` vectors, vector v at element v * stride (0 = packed); the pre / post tables are shared by the batch.
 int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out, unsigned log_n, bool inverse,
-             const uint32_t* d_pre, const uint32_t* d_post);
-int domain_fft_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, bool inverse, uint32_t* d_inout);
+             const uint32_t* d_pre, const uint32_t* d_post, unsigned batch = 1, uint64_t in_stride = 0,
+             uint64_t out_stride = 0);
+int domain_fft_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, bool inverse, uint32_t* d_inout, unsigned batch = 1,
+                   uint64_t stride = 0);
 int multiply_by_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t n, const uint64_t g[4], uint32_t* d_inout);
 int divide_by_z_on_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, uint32_t* d_inout);
 

@@ -12,6 +12,7 @@ struct BasesDev {
     bool g2 = false;
     bool table = false;
     unsigned c = 0, windows = 0;
+    unsigned force_c = 0;  // non-zero: fixed window width (the 8-bit fixed-base tables of the prover)
     uint32_t* d_pts = nullptr;  // n * (table ? windows : 1) * (24 | 48) limbs
 };
 

@@ -543,7 +543,7 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
 template <class F>
 static int bases_finalize_t(vsp_ctx* ctx, cudaStream_t s, BasesDev* b, bool table) {
     constexpr int L = Affine<F>::BYTES / 4;
-    b->c = choose_window(b->n ? b->n : 1, table);
+    b->c = b->force_c ? b->force_c : choose_window(b->n ? b->n : 1, table);
     b->windows = 255 / b->c + 1;
     b->table = false;
     if (!table || b->n == 0) return VSP_OK;

@@ -110,6 +110,7 @@ struct PassArgs {
     const uint32_t* pre;   // optional per-input-index multiplier (first pass only)
     const uint32_t* post;  // optional per-output-index multiplier (last pass only)
     unsigned log_w, log_n, k, ns_log, g_log;
+    uint64_t in_stride, out_stride;  // elements between consecutive vectors of the batch (blockIdx.y)
     int inverse;
     int scale_log;  // multiply outputs by 2^-scale_log (last pass of an inverse transform), 0 = none
 };
@@ -126,6 +127,8 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
     const uint64_t nj = uint64_t(1) << (a.log_n - a.k);
     const uint64_t j0 = uint64_t(blockIdx.x) << a.g_log;
     const uint64_t ns_mask = (uint64_t(1) << a.ns_log) - 1;
+    const uint32_t* vin = a.in + 8 * (uint64_t(blockIdx.y) * a.in_stride);
+    uint32_t* vout = a.out + 8 * (uint64_t(blockIdx.y) * a.out_stride);
 
     // ---- load (+ coset pre-scale, + inter-pass twiddle), bit-reversed into shared memory
 #pragma unroll
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
         const unsigned jj = q & (G - 1), r = q >> a.g_log;
         const uint64_t j = j0 + jj;
         const uint64_t gidx = j + uint64_t(r) * nj;
-        Fr x = fp_load<FrCfg>(a.in + 8 * gidx);
+        Fr x = fp_load<FrCfg>(vin + 8 * gidx);
         if (a.pre) x = fp_mul(x, fp_load<FrCfg>(a.pre + 8 * gidx));
         if (a.ns_log) {
             // omega_{Ns*R}^{(j mod Ns) * r} = omega_N^{(j mod Ns) * r * N / (Ns * R)}
@@ -196,13 +199,16 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
         y.l[4] = qq.x; y.l[5] = qq.y; y.l[6] = qq.z; y.l[7] = qq.w;
         if (a.scale_log) y = fp_mul(y, scale);
         if (a.post) y = fp_mul(y, fp_load<FrCfg>(a.post + 8 * didx));
-        fp_store(a.out + 8 * didx, y);
+        fp_store(vout + 8 * didx, y);
     }
 }
 
-__global__ void k_scale_copy(const uint32_t* in, uint32_t* out, uint64_t n, const uint32_t* pre, const uint32_t* post) {
+__global__ void k_scale_copy(const uint32_t* in, uint32_t* out, uint64_t n, const uint32_t* pre, const uint32_t* post,
+                             uint64_t in_stride, uint64_t out_stride) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    in += 8 * (uint64_t(blockIdx.y) * in_stride);
+    out += 8 * (uint64_t(blockIdx.y) * out_stride);
     Fr x = fp_load<FrCfg>(in + 8 * i);
     if (pre) x = fp_mul(x, fp_load<FrCfg>(pre + 8 * i));
     if (post) x = fp_mul(x, fp_load<FrCfg>(post + 8 * i));
@@ -210,11 +216,16 @@ __global__ void k_scale_copy(const uint32_t* in, uint32_t* out, uint64_t n, cons
 }
 
 int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out, unsigned log_n, bool inverse,
-             const uint32_t* d_pre, const uint32_t* d_post) {
+             const uint32_t* d_pre, const uint32_t* d_post, unsigned batch, uint64_t in_stride, uint64_t out_stride) {
     const uint64_t n = uint64_t(1) << log_n;
+    if (batch == 0) return VSP_OK;
+    if (batch > 65535) return set_error(ctx, VSP_E_INVALID, "NTT batch too large");
+    if (in_stride == 0) in_stride = n;
+    if (out_stride == 0) out_stride = n;
     if (log_n == 0) {
         if (d_in != d_out || d_pre || d_post) {
-            VSP_LAUNCH_K(ctx, KC_NTT, k_scale_copy, 1, 32, 0, s, d_in, d_out, n, d_pre, d_post);
+            VSP_LAUNCH_K(ctx, KC_NTT, k_scale_copy, dim3(1, batch), 32, 0, s, d_in, d_out, n, d_pre, d_post, in_stride,
+                         out_stride);
             VSP_CUDA_CHECK(ctx, cudaGetLastError());
         }
         return VSP_OK;
@@ -237,6 +248,7 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
     }
     DevBuf tmp_a, tmp_b;
     const uint32_t* src = d_in;
+    uint64_t src_stride = in_stride;
     unsigned ns_log = 0;
     for (unsigned p = 0; p < np; ++p) {
         const unsigned k = ks[p];
@@ -245,18 +257,21 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
         if (g_log > log_n - k) g_log = log_n - k;
         const bool last = (p + 1 == np);
         uint32_t* dst;
+        uint64_t dst_stride = n;
         const bool single_block = (log_n - k - g_log) == 0;
         if (last) {
             dst = d_out;
+            dst_stride = out_stride;
             if (np == 1 && d_in == d_out && !single_block) {
-                VSP_TRY(tmp_a.alloc(ctx, n * 32, s));
+                VSP_TRY(tmp_a.alloc(ctx, n * batch * 32, s));
                 dst = tmp_a.as<uint32_t>();
+                dst_stride = n;
             }
         } else if (p == 0) {
-            VSP_TRY(tmp_a.alloc(ctx, n * 32, s));
+            VSP_TRY(tmp_a.alloc(ctx, n * batch * 32, s));
             dst = tmp_a.as<uint32_t>();
         } else {
-            VSP_TRY(tmp_b.alloc(ctx, n * 32, s));
+            VSP_TRY(tmp_b.alloc(ctx, n * batch * 32, s));
             dst = tmp_b.as<uint32_t>();
         }
         PassArgs a;
@@ -270,15 +285,24 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
         a.k = k;
         a.ns_log = ns_log;
         a.g_log = g_log;
+        a.in_stride = src_stride;
+        a.out_stride = dst_stride;
         a.inverse = inverse ? 1 : 0;
         a.scale_log = (inverse && last) ? (int)log_n : 0;
         const unsigned threads = 1u << (k - 1 + g_log);
         const unsigned blocks = 1u << (log_n - k - g_log);
         const size_t smem = (size_t)32 << (k + g_log);
-        VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, blocks, threads, smem, s, a);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, dim3(blocks, batch), threads, smem, s, a);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
-        if (last && dst != d_out) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_out, dst, n * 32, cudaMemcpyDeviceToDevice, s));
+        if (last && dst != d_out) {
+            if (out_stride == n)
+                VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_out, dst, n * batch * 32, cudaMemcpyDeviceToDevice, s));
+            else
+                VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d_out, out_stride * 32, dst, n * 32, n * 32, batch,
+                                                      cudaMemcpyDeviceToDevice, s));
+        }
         src = dst;
+        src_stride = dst_stride;
         ns_log += k;
     }
     return VSP_OK;
@@ -317,19 +341,25 @@ int domain_plan(uint64_t min_size, int* kind, uint64_t* m) {
 // ---------------------------------------------------------------------------------------------
 // step_radix2_domain kernels (step_radix2_domain.hpp:73-166)
 // ---------------------------------------------------------------------------------------------
+// every kernel below takes the batch in blockIdx.y: vector v of `a` starts at element v * a_stride, the scratch
+// vectors c / u0 (big_m each) and e / u1 (small_m each) are packed
 // c[i] = i < small ? a[i] + a[i + big] : a[i]
-__global__ void k_step_fft_c(const uint32_t* a, uint32_t* c, uint64_t big_m, uint64_t small_m) {
+__global__ void k_step_fft_c(const uint32_t* a, uint32_t* c, uint64_t big_m, uint64_t small_m, uint64_t a_stride) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= big_m) return;
+    a += 8 * (uint64_t(blockIdx.y) * a_stride);
+    c += 8 * (uint64_t(blockIdx.y) * big_m);
     Fr x = fp_load<FrCfg>(a + 8 * i);
     if (i < small_m) x = fp_add(x, fp_load<FrCfg>(a + 8 * (i + big_m)));
     fp_store(c + 8 * i, x);
 }
 // e[i] = sum_j omega^(i + j small) * (idx < small ? a[idx] - a[idx + big] : a[idx]),  idx = i + j small
 __global__ void k_step_fft_e(const uint32_t* a, uint32_t* e, uint64_t big_m, uint64_t small_m, const uint32_t* w,
-                             unsigned log_w, unsigned log_2big) {
+                             unsigned log_w, unsigned log_2big, uint64_t a_stride) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= small_m) return;
+    a += 8 * (uint64_t(blockIdx.y) * a_stride);
+    e += 8 * (uint64_t(blockIdx.y) * small_m);
     Fr acc = Fr::zero();
     for (uint64_t idx = i; idx < big_m; idx += small_m) {
         Fr x = fp_load<FrCfg>(a + 8 * idx);
@@ -341,9 +371,13 @@ __global__ void k_step_fft_e(const uint32_t* a, uint32_t* e, uint64_t big_m, uin
 }
 // inverse: combine U0 (big_m, already scaled) and U1 (small_m, already scaled) into a
 __global__ void k_step_ifft_combine(const uint32_t* u0, const uint32_t* u1, uint32_t* a, uint64_t big_m,
-                                    uint64_t small_m, const uint32_t* w, unsigned log_w, unsigned log_2big) {
+                                    uint64_t small_m, const uint32_t* w, unsigned log_w, unsigned log_2big,
+                                    uint64_t a_stride) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= big_m) return;
+    a += 8 * (uint64_t(blockIdx.y) * a_stride);
+    u0 += 8 * (uint64_t(blockIdx.y) * big_m);
+    u1 += 8 * (uint64_t(blockIdx.y) * small_m);
     Fr x0 = fp_load<FrCfg>(u0 + 8 * i);
     if (i >= small_m) {
         fp_store(a + 8 * i, x0);
@@ -362,8 +396,12 @@ __global__ void k_step_ifft_combine(const uint32_t* u0, const uint32_t* u1, uint
     fp_store(a + 8 * (i + big_m), fp_mul(fp_sub(x0, x1), half));
 }
 
-int domain_fft_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, bool inverse, uint32_t* d) {
-    if (is_basic(m)) return ntt_pow2(ctx, s, d, d, ceil_log2_u64(m), inverse, nullptr, nullptr);
+// fft / inverse_fft of `batch` vectors of the size-m domain, in place; vector v starts at element v * stride
+int domain_fft_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, bool inverse, uint32_t* d, unsigned batch, uint64_t stride) {
+    if (stride == 0) stride = m;
+    if (batch == 0) return VSP_OK;
+    if (batch > 65535) return set_error(ctx, VSP_E_INVALID, "NTT batch too large");
+    if (is_basic(m)) return ntt_pow2(ctx, s, d, d, ceil_log2_u64(m), inverse, nullptr, nullptr, batch, stride, stride);
     if (!is_step(m)) return set_error(ctx, VSP_E_DOMAIN, "no executable radix-2 domain of size %llu", (unsigned long long)m);
     const unsigned log_2big = ceil_log2_u64(m);
     const uint64_t big_m = uint64_t(1) << (log_2big - 1), small_m = m - big_m;
@@ -371,20 +409,21 @@ int domain_fft_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, bool inverse, uint3
     VSP_TRY(ntt_tables_ensure(ctx, log_2big));
     NttTables* tb = ctx->ntt;
     DevBuf c, e;
-    VSP_TRY(c.alloc(ctx, big_m * 32, s));
-    VSP_TRY(e.alloc(ctx, small_m * 32, s));
-    const unsigned gb = (unsigned)((big_m + 127) / 128), gs = (unsigned)((small_m + 127) / 128);
+    VSP_TRY(c.alloc(ctx, big_m * batch * 32, s));
+    VSP_TRY(e.alloc(ctx, small_m * batch * 32, s));
+    const dim3 gb((unsigned)((big_m + 127) / 128), batch), gs((unsigned)((small_m + 127) / 128), batch);
     if (!inverse) {
-        VSP_LAUNCH_K(ctx, KC_NTT, k_step_fft_c, gb, 128, 0, s, d, c.as<uint32_t>(), big_m, small_m);
-        VSP_LAUNCH_K(ctx, KC_NTT, k_step_fft_e, gs, 128, 0, s, d, e.as<uint32_t>(), big_m, small_m, tb->d_w, tb->log_w, log_2big);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_step_fft_c, gb, 128, 0, s, d, c.as<uint32_t>(), big_m, small_m, stride);
+        VSP_LAUNCH_K(ctx, KC_NTT, k_step_fft_e, gs, 128, 0, s, d, e.as<uint32_t>(), big_m, small_m, tb->d_w, tb->log_w,
+                     log_2big, stride);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
-        VSP_TRY(ntt_pow2(ctx, s, c.as<uint32_t>(), d, log_big, false, nullptr, nullptr));
-        VSP_TRY(ntt_pow2(ctx, s, e.as<uint32_t>(), d + 8 * big_m, log_small, false, nullptr, nullptr));
+        VSP_TRY(ntt_pow2(ctx, s, c.as<uint32_t>(), d, log_big, false, nullptr, nullptr, batch, big_m, stride));
+        VSP_TRY(ntt_pow2(ctx, s, e.as<uint32_t>(), d + 8 * big_m, log_small, false, nullptr, nullptr, batch, small_m, stride));
     } else {
-        VSP_TRY(ntt_pow2(ctx, s, d, c.as<uint32_t>(), log_big, true, nullptr, nullptr));
-        VSP_TRY(ntt_pow2(ctx, s, d + 8 * big_m, e.as<uint32_t>(), log_small, true, nullptr, nullptr));
+        VSP_TRY(ntt_pow2(ctx, s, d, c.as<uint32_t>(), log_big, true, nullptr, nullptr, batch, stride, big_m));
+        VSP_TRY(ntt_pow2(ctx, s, d + 8 * big_m, e.as<uint32_t>(), log_small, true, nullptr, nullptr, batch, stride, small_m));
         VSP_LAUNCH_K(ctx, KC_NTT, k_step_ifft_combine, gb, 128, 0, s, c.as<uint32_t>(), e.as<uint32_t>(), d, big_m, small_m,
-                   tb->d_w, tb->log_w, log_2big);
+                     tb->d_w, tb->log_w, log_2big, stride);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
     }
     return VSP_OK;

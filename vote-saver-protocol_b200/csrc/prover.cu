@@ -12,10 +12,12 @@
 //   encrypt_op<elgamal_verifiable>::process      elgamal_verifiable.hpp:322-357
 //   rerandomize_op<elgamal_verifiable>::process  elgamal_verifiable.hpp:632-667
 //
-// Stream plan for one proof (fork after the witness upload, join before assembly):
-//   main   : A w / B w / C w  ->  aA: iNTT+coset, NTT  ->  pointwise H  ->  coset iNTT  ->  multiexp H  ->  assembly
-//   side 0 : aB: iNTT+coset, NTT                         side 1 : aC: iNTT+coset, NTT
-//   side 2 : multiexp A, multiexp L                      side 3 : multiexp B (G2), multiexp B (G1), fixed-base r/s multiples
+// Ballots are proved in chunks of up to `chunk` (VSP_BATCH_CHUNK, default 64) that share every launch: each kernel
+// carries the ballot index in a grid dimension, so one chunk costs the launches of one proof and the serial tails
+// (field inversions, the two variable-base multiples) run for all its ballots at once.
+// Stream plan for one chunk (fork after the witness upload, join before assembly):
+//   main   : A w / B w / C w  ->  3B batched iNTT+coset, NTT  ->  pointwise H  ->  coset iNTT  ->  multiexp H  ->  assembly
+//   side 2 : multiexp A, multiexp L       side 3 : fixed-base r/s multiples, multiexp B (G2), multiexp B (G1)
 #include "common.cuh"
 #include "ec.cuh"
 #include "host_fr.h"
@@ -44,13 +46,25 @@ struct vsp_pk {
     BasesDev A, Bg1, Bg2, H, L;
     BasesDev fixed1;  // alpha_g1, beta_g1, delta_g1 (Montgomery affine)
     BasesDev fixed2;  // beta_g2, delta_g2
+    // 8-bit fixed-base tables T[w][i] = 2^(8 w) P_i:  fx1tab = {delta_g1, gamma_inverse_sum_s_g1}, fx2tab = {delta_g2}
+    BasesDev fx1tab, fx2tab;
+    uint64_t gamma_key[12] = {0};  // the gamma_inverse_sum_s_g1 currently in fx1tab (all-zero: none)
     uint32_t* d_B_idx = nullptr;
     uint64_t B_count = 0;
     uint32_t* d_gpow = nullptr;     // g^i, i < m (Montgomery)
     uint32_t* d_ginvpow = nullptr;  // basic domain: Z(g)^-1 g^-i ; step domain: g^-i
     uint32_t* d_zinv = nullptr;     // step domain only: 1 / Z on the coset, per element (Montgomery)
-    uint64_t h_delta_g1[12];        // canonical copies for the fixed-base scalar multiplications
+    uint64_t h_delta_g1[12];        // canonical copies
     uint64_t h_delta_g2[24];
+};
+
+// SAVER public key resident on the GPU: 8-bit fixed-base tables of its 3 msg_size + 2 G1 bases
+//   order: delta | delta_s[0..n) | gamma_abc_rest[0..n) | t[0..n) | delta_sum_s
+struct vsp_saver_pub {
+    vsp_ctx* ctx = nullptr;
+    unsigned n = 0;  // msg_size
+    BasesDev tab;
+    uint64_t gamma_inv[12];  // canonical gamma_inverse_sum_s_g1
 };
 
 namespace vsp {
@@ -84,21 +98,24 @@ struct CsrDev {
     const uint32_t* val[3];
 };
 
-// one warp per domain row: aA / aB / aC[row] = <matrix row, (1 || primary || aux)>; rows n_c .. n_c + n_in of aA hold
-// the input-consistency values, everything above is zero.  aB comes out in Montgomery form (values carry R^2).
-__global__ void __launch_bounds__(256) k_r1cs_eval(CsrDev csr, const uint32_t* __restrict__ w, uint64_t nc, uint64_t ni,
-                                                   uint64_t m, uint32_t* aA, uint32_t* aB, uint32_t* aC) {
+// one warp per (domain row, ballot = blockIdx.y): aA / aB / aC[row] = <matrix row, (1 || primary || aux)>; rows
+// n_c .. n_c + n_in of aA hold the input-consistency values, everything above is zero.  aB comes out in Montgomery form
+// (its values carry R^2).  abc = [aA: B x m | aB: B x m | aC: B x m]
+__global__ void __launch_bounds__(256) k_r1cs_eval(CsrDev csr, const uint32_t* __restrict__ w_all, uint64_t w_stride,
+                                                   uint64_t nc, uint64_t ni, uint64_t m, uint32_t* abc) {
     const uint64_t row = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31;
     if (row >= m) return;
-    uint32_t* outs[3] = {aA, aB, aC};
+    const uint64_t B = gridDim.y, b = blockIdx.y;
+    const uint32_t* w = w_all + 8 * b * w_stride;
+    uint32_t* outs[3] = {abc + 8 * (b * m), abc + 8 * ((B + b) * m), abc + 8 * ((2 * B + b) * m)};
     if (row >= nc) {
         if (lane == 0) {
             Fr z = Fr::zero();
             Fr a = (row - nc <= ni) ? fp_load<FrCfg>(w + 8 * (row - nc)) : z;
-            fp_store(aA + 8 * row, a);
-            fp_store(aB + 8 * row, z);
-            fp_store(aC + 8 * row, z);
+            fp_store(outs[0] + 8 * row, a);
+            fp_store(outs[1] + 8 * row, z);
+            fp_store(outs[2] + 8 * row, z);
         }
         return;
     }
@@ -116,28 +133,42 @@ __global__ void __launch_bounds__(256) k_r1cs_eval(CsrDev csr, const uint32_t* _
     }
 }
 
-// h[i] = (a[i] * b_mont[i] - c[i]) [* zinv[i]]
+// h[b][i] = (a[b][i] * b_mont[b][i] - c[b][i]) [* zinv[i]]      (ballot b = blockIdx.y, vectors packed B x m)
 __global__ void k_h_pointwise(uint32_t* a, const uint32_t* b, const uint32_t* c, const uint32_t* zinv, uint64_t m) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= m) return;
-    Fr x = fp_sub(fp_mul(fp_load<FrCfg>(a + 8 * i), fp_load<FrCfg>(b + 8 * i)), fp_load<FrCfg>(c + 8 * i));
+    const uint64_t o = 8 * (uint64_t(blockIdx.y) * m + i);
+    Fr x = fp_sub(fp_mul(fp_load<FrCfg>(a + o), fp_load<FrCfg>(b + o)), fp_load<FrCfg>(c + o));
     if (zinv) x = fp_mul(x, fp_load<FrCfg>(zinv + 8 * i));
-    fp_store(a + 8 * i, x);
+    fp_store(a + o, x);
 }
+// a[v][i] *= tbl[i]   (v = blockIdx.y, vectors packed)
 __global__ void k_mul_table2(uint32_t* a, uint64_t n, const uint32_t* tbl) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    fp_store(a + 8 * i, fp_mul(fp_load<FrCfg>(a + 8 * i), fp_load<FrCfg>(tbl + 8 * i)));
+    const uint64_t o = 8 * (uint64_t(blockIdx.y) * n + i);
+    fp_store(a + o, fp_mul(fp_load<FrCfg>(a + o), fp_load<FrCfg>(tbl + 8 * i)));
 }
 __global__ void k_fill_const(uint32_t* a, uint64_t n, Fr v) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
     fp_store(a + 8 * i, v);
 }
-__global__ void k_gather_fr(const uint32_t* __restrict__ w, const uint32_t* __restrict__ idx, uint64_t n, uint32_t* out) {
+// out[b][i] = w[b][idx[i]]
+__global__ void k_gather_fr(const uint32_t* __restrict__ w, uint64_t w_stride, const uint32_t* __restrict__ idx, uint64_t n,
+                            uint32_t* out) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    fp_store(out + 8 * i, fp_load<FrCfg>(w + 8 * uint64_t(idx[i])));
+    const uint64_t b = blockIdx.y;
+    fp_store(out + 8 * (b * n + i), fp_load<FrCfg>(w + 8 * (b * w_stride + idx[i])));
+}
+// w[b][0] = 1 (the constant-one variable of every assignment)
+__global__ void k_set_one(uint32_t* w, uint64_t w_stride, unsigned B) {
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    Fr one = Fr::zero();
+    one.l[0] = 1;
+    fp_store(w + 8 * (uint64_t(b) * w_stride), one);
 }
 
 // k * P, P affine (Montgomery), k canonical 8 x 32-bit: MSB-first double-and-add
@@ -153,12 +184,12 @@ VSP_DEV XYZZ<F> ec_scalar_mul(const Affine<F>& p, const uint32_t* k) {
     return acc;
 }
 
-// out[i] (XYZZ, Montgomery) = scalars[i] * points[i];  points canonical affine (mont == 0) or Montgomery affine
+// out[i] (XYZZ, Montgomery) = scalars[i] * points[i];  points canonical affine (mont == 0) or Montgomery affine.
+// Variable-base multiples (s g_A, r g1_B; rerandomisation): one job per block, lane 0 of one warp — independent
+// scalars diverge at every add step, so jobs sharing a warp would serialise; separate warps run concurrently.
 template <class F>
 __global__ void k_scalar_mul_batch(const uint64_t* __restrict__ points, const uint32_t* __restrict__ scalars, unsigned n,
                                    int mont, uint32_t* __restrict__ out) {
-    // one job per block (lane 0 of one warp): independent scalars diverge at every add step, so jobs sharing a warp
-    // would serialise; separate warps run concurrently on separate schedulers / SMs
     const unsigned i = blockIdx.x;
     if (i >= n || threadIdx.x != 0) return;
     Affine<F> p = Affine<F>::load(points + uint64_t(i) * (Affine<F>::BYTES / 8));
@@ -171,6 +202,54 @@ __global__ void k_scalar_mul_batch(const uint64_t* __restrict__ points, const ui
     for (int q = 0; q < 8; ++q) k[q] = scalars[8 * i + q];
     XYZZ<F> r = ec_scalar_mul<F>(p, k);
     r.store(out + uint64_t(i) * (XYZZ<F>::BYTES / 4));
+}
+
+// Fixed-base multiples from an 8-bit window table T[w][i] = 2^(8 w) P_i (32 levels of n_bases affine points):
+// one warp per job, lane w computes  digit_w * T[w][base]  by an 8-step double-and-add, then the 32 partial results
+// are tree-summed through shared memory: 8 doublings + 5 additions deep instead of 255 + 127.
+//   job j of ballot b:  base = spec[j].base;  scalar = spec[j].sel >= 0 ? host_sc[b][sel] : w[b][-sel]  (canonical Fr)
+struct FixedJob {
+    int base;
+    int sel;
+};
+constexpr int FIXED_WARPS = 2;
+template <class F>
+__global__ void __launch_bounds__(32 * FIXED_WARPS) k_fixed_mul(const uint32_t* __restrict__ table, uint64_t n_bases,
+                                                                const FixedJob* __restrict__ spec, unsigned jobs_per_ballot,
+                                                                unsigned n_jobs, const uint32_t* __restrict__ host_sc,
+                                                                unsigned sc_per_ballot, const uint32_t* __restrict__ w,
+                                                                uint64_t w_stride, uint32_t* __restrict__ out) {
+    extern __shared__ uint4 sm4[];
+    constexpr int L = XYZZ<F>::BYTES / 4, AL = Affine<F>::BYTES / 4;
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t* sm = reinterpret_cast<uint32_t*>(sm4) + warp * 32 * L;
+    const unsigned job = blockIdx.x * FIXED_WARPS + warp;
+    const bool live = job < n_jobs;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    if (live) {
+        const unsigned b = job / jobs_per_ballot, j = job - b * jobs_per_ballot;
+        const FixedJob fj = spec[j];
+        const uint32_t* sp = fj.sel >= 0 ? host_sc + 8 * (uint64_t(b) * sc_per_ballot + fj.sel)
+                                         : w + 8 * (uint64_t(b) * w_stride + uint64_t(-fj.sel));
+        const uint32_t d = (sp[lane >> 2] >> ((lane & 3) * 8)) & 0xffu;
+        if (d) {
+            const Affine<F> p = Affine<F>::load(table + (uint64_t(lane) * n_bases + fj.base) * AL);
+            for (int bit = 31 - __clz(d); bit >= 0; --bit) {
+                acc = ec_dbl<F>(acc);
+                if ((d >> bit) & 1u) ec_madd<F>(acc, p);
+            }
+        }
+    }
+    acc.store(sm + lane * L);
+    __syncwarp();
+    for (unsigned st = 16; st > 0; st >>= 1) {
+        if (lane < st) {
+            ec_add<F>(acc, XYZZ<F>::load(sm + (lane + st) * L));
+            acc.store(sm + lane * L);
+        }
+        __syncwarp();
+    }
+    if (live && lane == 0) acc.store(out + uint64_t(job) * L);
 }
 
 // out[j] (canonical affine) = sum of xyzz[i] with group[i] == j  (+ addend[j], canonical affine, optional)
@@ -199,24 +278,6 @@ __global__ void k_group_sum(const uint32_t* __restrict__ xyzz, const uint32_t* _
     r.store(out + uint64_t(j) * (Affine<F>::BYTES / 8));
 }
 
-// proof assembly, phase 1: three threads (separate warps)
-//   t0: g_A  = alpha + evA  + r delta1      -> out_proof[0..12)  and scratch for phase 2
-//   t1: g1_B = beta1 + evB1 + s delta1      -> scratch
-//   t2: g_B  = beta2 + evB2 + s delta2      -> out_proof[12..36)
-struct AsmPtrs {
-    const uint32_t* evA;    // XYZZ G1
-    const uint32_t* evB1;   // XYZZ G1
-    const uint32_t* evB2;   // XYZZ G2
-    const uint32_t* evH;    // XYZZ G1
-    const uint32_t* evL;    // XYZZ G1
-    const uint32_t* fx1;    // XYZZ G1 x4: r d1, s d1, (-rs) d1, r_saver gamma_inv (or infinity)
-    const uint32_t* fx2;    // XYZZ G2 x1: s d2
-    const uint32_t* fixed1; // affine Montgomery: alpha, beta1, delta1
-    const uint32_t* fixed2; // affine Montgomery: beta2, delta2
-    uint64_t* gA_gB1;       // scratch: canonical affine g_A, g1_B (2 x 12 limbs)
-    uint64_t* proof;        // 48 limbs
-};
-
 template <class F>
 VSP_DEV void write_canonical(uint64_t* out, const XYZZ<F>& p) {
     Affine<F> a = ec_to_affine<F>(p);
@@ -225,40 +286,87 @@ VSP_DEV void write_canonical(uint64_t* out, const XYZZ<F>& p) {
     a.store(out);
 }
 
-__global__ void __launch_bounds__(96) k_prove_phase1(AsmPtrs p) {
-    const unsigned warp = threadIdx.x >> 5;
-    if (threadIdx.x & 31) return;
-    constexpr int L1 = G1XYZZ::BYTES / 4, A1 = G1Affine::BYTES / 4;
-    if (warp == 0) {
-        G1XYZZ acc = G1XYZZ::load(p.evA);
-        ec_madd<FqOps>(acc, G1Affine::load(p.fixed1));
-        ec_add<FqOps>(acc, G1XYZZ::load(p.fx1));
-        write_canonical<FqOps>(p.gA_gB1, acc);
-        write_canonical<FqOps>(p.proof, acc);
-    } else if (warp == 1) {
-        G1XYZZ acc = G1XYZZ::load(p.evB1);
-        ec_madd<FqOps>(acc, G1Affine::load(p.fixed1 + A1));
-        ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + L1));
-        write_canonical<FqOps>(p.gA_gB1 + 12, acc);
+// SAVER ciphertext of ballot b from its 3 n + 2 fixed-base multiples (job order of vsp_saver_pub):
+//   ct[0] = r delta;  ct[1 + i] = r delta_s[i] + m_i gamma_abc[i];  ct[n + 1] = r delta_sum_s + sum_i m_i t[i]
+// thread = (ballot, slot); elgamal_verifiable.hpp:341-352
+__global__ void k_ct_sum(const uint32_t* __restrict__ mul, unsigned n, unsigned B, uint64_t* __restrict__ ct) {
+    const unsigned q = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned slots = n + 2;
+    if (q >= B * slots) return;
+    const unsigned b = q / slots, slot = q - b * slots;
+    constexpr int L = G1XYZZ::BYTES / 4;
+    const uint32_t* jb = mul + uint64_t(b) * (3 * n + 2) * L;
+    G1XYZZ acc;
+    if (slot == 0) {
+        acc = G1XYZZ::load(jb);
+    } else if (slot <= n) {
+        acc = G1XYZZ::load(jb + uint64_t(slot) * L);
+        ec_add<FqOps>(acc, G1XYZZ::load(jb + uint64_t(n + slot) * L));
     } else {
-        G2XYZZ acc = G2XYZZ::load(p.evB2);
+        acc = G1XYZZ::load(jb + uint64_t(3 * n + 1) * L);
+        for (unsigned i = 0; i < n; ++i) ec_add<FqOps>(acc, G1XYZZ::load(jb + uint64_t(2 * n + 1 + i) * L));
+    }
+    write_canonical<FqOps>(ct + uint64_t(q) * 12, acc);
+}
+
+// ---------------------------------------------------------------------------------------------
+// proof assembly for a chunk of B ballots; lane = ballot, so a warp runs one role in lock step
+// ---------------------------------------------------------------------------------------------
+struct AsmPtrs {
+    const uint32_t* evA;    // B x XYZZ G1
+    const uint32_t* evB1;   // B x XYZZ G1
+    const uint32_t* evB2;   // B x XYZZ G2
+    const uint32_t* evH;    // B x XYZZ G1
+    const uint32_t* evL;    // B x XYZZ G1
+    const uint32_t* fx1;    // B x 4 XYZZ G1: r d1, s d1, (-rs) d1, r_saver gamma_inv (or infinity)
+    const uint32_t* fx2;    // B x XYZZ G2: s d2
+    const uint32_t* fixed1; // affine Montgomery: alpha, beta1, delta1
+    const uint32_t* fixed2; // affine Montgomery: beta2, delta2
+    uint64_t* gab;          // scratch: B x (canonical affine g_A, g1_B) (2 x 12 limbs)
+    const uint32_t* sg;     // B x 2 XYZZ G1: s g_A, r g1_B
+    uint64_t* proof;        // B x 48 limbs
+    unsigned B;
+};
+
+// phase 1, role = blockIdx.y:
+//   0: g_A  = alpha + evA  + r delta1      -> proof[b][0..12)  and gab[b][0]
+//   1: g1_B = beta1 + evB1 + s delta1      -> gab[b][1]
+//   2: g_B  = beta2 + evB2 + s delta2      -> proof[b][12..36)
+__global__ void __launch_bounds__(32) k_prove_phase1(AsmPtrs p) {
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.B) return;
+    constexpr int L1 = G1XYZZ::BYTES / 4, L2 = G2XYZZ::BYTES / 4, A1 = G1Affine::BYTES / 4;
+    if (blockIdx.y == 0) {
+        G1XYZZ acc = G1XYZZ::load(p.evA + uint64_t(b) * L1);
+        ec_madd<FqOps>(acc, G1Affine::load(p.fixed1));
+        ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b) * L1));
+        write_canonical<FqOps>(p.gab + uint64_t(b) * 24, acc);
+        for (int i = 0; i < 12; ++i) p.proof[uint64_t(b) * 48 + i] = p.gab[uint64_t(b) * 24 + i];
+    } else if (blockIdx.y == 1) {
+        G1XYZZ acc = G1XYZZ::load(p.evB1 + uint64_t(b) * L1);
+        ec_madd<FqOps>(acc, G1Affine::load(p.fixed1 + A1));
+        ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b + 1) * L1));
+        write_canonical<FqOps>(p.gab + uint64_t(b) * 24 + 12, acc);
+    } else {
+        G2XYZZ acc = G2XYZZ::load(p.evB2 + uint64_t(b) * L2);
         ec_madd<Fq2Ops>(acc, G2Affine::load(p.fixed2));
-        ec_add<Fq2Ops>(acc, G2XYZZ::load(p.fx2));
-        write_canonical<Fq2Ops>(p.proof + 12, acc);
+        ec_add<Fq2Ops>(acc, G2XYZZ::load(p.fx2 + uint64_t(b) * L2));
+        write_canonical<Fq2Ops>(p.proof + uint64_t(b) * 48 + 12, acc);
     }
 }
 
 // phase 3: g_C = evH + evL + s g_A + r g1_B + (-rs) delta1 + r_saver gamma_inv
-__global__ void k_prove_phase3(AsmPtrs p, const uint32_t* sg) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+__global__ void __launch_bounds__(32) k_prove_phase3(AsmPtrs p) {
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.B) return;
     constexpr int L1 = G1XYZZ::BYTES / 4;
-    G1XYZZ acc = G1XYZZ::load(p.evH);
-    ec_add<FqOps>(acc, G1XYZZ::load(p.evL));
-    ec_add<FqOps>(acc, G1XYZZ::load(sg));
-    ec_add<FqOps>(acc, G1XYZZ::load(sg + L1));
-    ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + 2 * L1));
-    ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + 3 * L1));
-    write_canonical<FqOps>(p.proof + 36, acc);
+    G1XYZZ acc = G1XYZZ::load(p.evH + uint64_t(b) * L1);
+    ec_add<FqOps>(acc, G1XYZZ::load(p.evL + uint64_t(b) * L1));
+    ec_add<FqOps>(acc, G1XYZZ::load(p.sg + uint64_t(2 * b) * L1));
+    ec_add<FqOps>(acc, G1XYZZ::load(p.sg + uint64_t(2 * b + 1) * L1));
+    ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b + 2) * L1));
+    ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b + 3) * L1));
+    write_canonical<FqOps>(p.proof + uint64_t(b) * 48 + 36, acc);
 }
 
 static void free_dev(void* p) {
@@ -286,6 +394,8 @@ extern "C" void vsp_pk_destroy(vsp_pk* pk) {
     bases_free(&pk->L);
     bases_free(&pk->fixed1);
     bases_free(&pk->fixed2);
+    bases_free(&pk->fx1tab);
+    bases_free(&pk->fx2tab);
     free_dev(pk->d_B_idx);
     free_dev(pk->d_gpow);
     free_dev(pk->d_ginvpow);
@@ -350,6 +460,15 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
     memcpy(pk->h_delta_g2, d->delta_g2, 192);
     VSP_TRY(bases_upload(ctx, false, 3, f1, &pk->fixed1, false));
     VSP_TRY(bases_upload(ctx, true, 2, f2, &pk->fixed2, false));
+    // 8-bit fixed-base tables for the r / s multiples of delta (gamma_inverse_sum_s_g1 joins fx1tab on first use)
+    uint64_t t1[24];
+    memcpy(t1, d->delta_g1, 96);
+    memset(t1 + 12, 0, 96);
+    pk->fx1tab.force_c = 8;
+    pk->fx2tab.force_c = 8;
+    VSP_TRY(bases_upload(ctx, false, 2, t1, &pk->fx1tab, true));
+    VSP_TRY(bases_upload(ctx, true, 1, d->delta_g2, &pk->fx2tab, true));
+    if (!pk->fx1tab.table || !pk->fx2tab.table) return set_error(ctx, VSP_E_NOMEM, "fixed-base tables not built");
 
     // coset tables (multiplicative_generator = 7)
     const Fr4 g = from_u64(7), ginv = inv(g);
@@ -390,169 +509,182 @@ extern "C" int vsp_pk_load(vsp_ctx* ctx, const vsp_proving_key_t* desc, vsp_pk**
     return VSP_OK;
 }
 
+
 // ---------------------------------------------------------------------------------------------
 // witness map
 // ---------------------------------------------------------------------------------------------
 namespace vsp {
 
-static int coset_lde(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, uint32_t* d_a) {
+// `nvec` packed vectors of m values: inverse_fft, multiply_by_coset(g), fft
+static int coset_lde(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, uint32_t* d_a, unsigned nvec) {
     const uint64_t m = pk->m;
     if (pk->kind == VSP_DOMAIN_BASIC_RADIX2) {
         const unsigned L = ceil_log2_u64(m);
-        VSP_TRY(ntt_pow2(ctx, s, d_a, d_a, L, true, nullptr, pk->d_gpow));  // inverse_fft then multiply_by_coset(g)
-        VSP_TRY(ntt_pow2(ctx, s, d_a, d_a, L, false, nullptr, nullptr));    // fft
+        VSP_TRY(ntt_pow2(ctx, s, d_a, d_a, L, true, nullptr, pk->d_gpow, nvec));  // inverse_fft then multiply_by_coset(g)
+        VSP_TRY(ntt_pow2(ctx, s, d_a, d_a, L, false, nullptr, nullptr, nvec));    // fft
     } else {
-        VSP_TRY(domain_fft_dev(ctx, s, m, true, d_a));
-        VSP_LAUNCH_K(ctx, KC_QAP, k_mul_table2, (unsigned)((m + 127) / 128), 128, 0, s, d_a, m, pk->d_gpow);
+        VSP_TRY(domain_fft_dev(ctx, s, m, true, d_a, nvec));
+        VSP_LAUNCH_K(ctx, KC_QAP, k_mul_table2, dim3((unsigned)((m + 127) / 128), nvec), 128, 0, s, d_a, m, pk->d_gpow);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
-        VSP_TRY(domain_fft_dev(ctx, s, m, false, d_a));
+        VSP_TRY(domain_fft_dev(ctx, s, m, false, d_a, nvec));
     }
     return VSP_OK;
 }
 
-// d_w: (1 || primary || aux) canonical.  d_h: m Fr (coefficients_for_H[0..m)), canonical.  Uses side streams 0 and 1.
-static int witness_map_dev(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_w, uint32_t* d_h, DevBuf& aB, DevBuf& aC) {
-    cudaStream_t s = ctx->stream;
+// d_w: B assignments (1 || primary || aux), canonical, w_stride elements apart.  abc: 3 B m Fr of scratch; on return
+// abc[0 .. B m) holds coefficients_for_H[0..m) of every ballot (canonical).  Everything on stream s.
+static int witness_map_dev(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const uint32_t* d_w, uint64_t w_stride,
+                           unsigned B, uint32_t* abc) {
     const uint64_t m = pk->m;
-    VSP_TRY(aB.alloc(ctx, m * 32, s));
-    VSP_TRY(aC.alloc(ctx, m * 32, s));
     CsrDev csr;
     for (int i = 0; i < 3; ++i) {
         csr.row[i] = pk->d_row[i];
         csr.col[i] = pk->d_col[i];
         csr.val[i] = pk->d_val[i];
     }
-    uint32_t* aA = d_h;
-    VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval, (unsigned)((m * 32 + 255) / 256), 256, 0, s, csr, d_w, pk->nc, pk->ni, m, aA,
-               aB.as<uint32_t>(), aC.as<uint32_t>());
+    uint32_t *aA = abc, *aB = abc + 8 * (uint64_t(B) * m), *aC = abc + 8 * (uint64_t(2 * B) * m);
+    VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval, dim3((unsigned)((m * 32 + 255) / 256), B), 256, 0, s, csr, d_w, w_stride, pk->nc,
+                 pk->ni, m, abc);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[0], ctx->ev_fork, 0));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[1], ctx->ev_fork, 0));
-    VSP_TRY(coset_lde(ctx, ctx->side[0], pk, aB.as<uint32_t>()));
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], ctx->side[0]));
-    VSP_TRY(coset_lde(ctx, ctx->side[1], pk, aC.as<uint32_t>()));
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[1], ctx->side[1]));
-    VSP_TRY(coset_lde(ctx, s, pk, aA));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[0], 0));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[1], 0));
-    VSP_LAUNCH_K(ctx, KC_QAP, k_h_pointwise, (unsigned)((m + 127) / 128), 128, 0, s, aA, aB.as<uint32_t>(), aC.as<uint32_t>(),
-               pk->d_zinv, m);
+    VSP_TRY(coset_lde(ctx, s, pk, abc, 3 * B));
+    VSP_LAUNCH_K(ctx, KC_QAP, k_h_pointwise, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, aA, aB, aC, pk->d_zinv, m);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     if (pk->kind == VSP_DOMAIN_BASIC_RADIX2) {
         // inverse_fft, multiply_by_coset(g^-1) and divide_by_z_on_coset in one pass chain (table = Z^-1 g^-i)
-        VSP_TRY(ntt_pow2(ctx, s, aA, aA, ceil_log2_u64(m), true, nullptr, pk->d_ginvpow));
+        VSP_TRY(ntt_pow2(ctx, s, aA, aA, ceil_log2_u64(m), true, nullptr, pk->d_ginvpow, B));
     } else {
-        VSP_TRY(domain_fft_dev(ctx, s, m, true, aA));
-        VSP_LAUNCH_K(ctx, KC_QAP, k_mul_table2, (unsigned)((m + 127) / 128), 128, 0, s, aA, m, pk->d_ginvpow);
+        VSP_TRY(domain_fft_dev(ctx, s, m, true, aA, B));
+        VSP_LAUNCH_K(ctx, KC_QAP, k_mul_table2, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, aA, m, pk->d_ginvpow);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
     }
     return VSP_OK;
 }
 
-static int upload_witness(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux, DevBuf& d_w) {
+// B host witnesses -> packed device assignments (1 || primary || aux), stride nv + 1
+static int upload_witness(vsp_ctx* ctx, const vsp_pk* pk, unsigned B, const uint64_t* primary, const uint64_t* aux,
+                          DevBuf& d_w) {
     cudaStream_t s = ctx->stream;
-    VSP_TRY(d_w.alloc(ctx, (pk->nv + 1) * 32, s));
-    static const uint64_t one[4] = {1, 0, 0, 0};
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_w.p, one, 32, cudaMemcpyHostToDevice, s));
+    const uint64_t stride = pk->nv + 1;
+    VSP_TRY(d_w.alloc(ctx, uint64_t(B) * stride * 32, s));
+    VSP_LAUNCH_K(ctx, KC_QAP, k_set_one, (B + 127) / 128, 128, 0, s, d_w.as<uint32_t>(), stride, B);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
     if (pk->ni)
-        VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_w.as<char>() + 32, primary, pk->ni * 32, cudaMemcpyHostToDevice, s));
+        VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d_w.as<char>() + 32, stride * 32, primary, pk->ni * 32, pk->ni * 32, B,
+                                              cudaMemcpyHostToDevice, s));
     if (pk->na)
-        VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_w.as<char>() + 32 + pk->ni * 32, aux, pk->na * 32, cudaMemcpyHostToDevice, s));
+        VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d_w.as<char>() + 32 + pk->ni * 32, stride * 32, aux, pk->na * 32, pk->na * 32,
+                                              B, cudaMemcpyHostToDevice, s));
     return VSP_OK;
 }
 
 static bool fr_reduced(const uint64_t* x) { return !hostfr::geq(x, hostfr::MOD); }
 
-// One proof, fully asynchronous: on return everything is enqueued and d_proof (48 limbs) will hold the result once
-// ctx->stream completes.  `keep` owns the scratch so it outlives this function until the caller has synchronised.
-struct ProofScratch {
-    DevBuf w, h, aB, aC, bsc, ev, fxpts, fxsc, fx1, fx2, gab, sgpts, sgsc, sg;
-};
+// make fx1tab = {delta_g1, gamma_inv}: rebuilt only when a different gamma_inverse_sum_s_g1 arrives
+static int ensure_gamma_table(vsp_ctx* ctx, vsp_pk* pk, const uint64_t* gamma_inv) {
+    if (memcmp(pk->gamma_key, gamma_inv, 96) == 0) return VSP_OK;
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 4; ++i) VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->side[i]));
+    uint64_t t1[24];
+    memcpy(t1, pk->h_delta_g1, 96);
+    memcpy(t1 + 12, gamma_inv, 96);
+    BasesDev nb;
+    nb.force_c = 8;
+    VSP_TRY(bases_upload(ctx, false, 2, t1, &nb, true));
+    if (!nb.table) {
+        bases_free(&nb);
+        return set_error(ctx, VSP_E_NOMEM, "fixed-base table not built");
+    }
+    bases_free(&pk->fx1tab);
+    pk->fx1tab = nb;
+    memcpy(pk->gamma_key, gamma_inv, 96);
+    return VSP_OK;
+}
 
-static int prove_async(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_assignment, const uint64_t* primary,
-                       const uint64_t* aux, const uint64_t* r, const uint64_t* sv, const uint64_t* r_saver,
-                       const uint64_t* gamma_inv, uint64_t* d_proof, ProofScratch& k) {
+// device constants of the proof's fixed-base jobs: (base, scalar slot) x 4 over fx1tab, x 1 over fx2tab.
+// per-ballot host scalars: 0 r | 1 s | 2 -rs | 3 r_saver (0 without encrypted_input)
+static const FixedJob PROOF_JOBS_G1[4] = {{0, 0}, {0, 1}, {0, 2}, {1, 3}};
+static const FixedJob PROOF_JOBS_G2[1] = {{0, 1}};
+
+// One chunk of B proofs, fully asynchronous: on return everything is enqueued on ctx->stream / side streams, joined
+// back into ctx->stream, and d_proofs (B x 48 limbs) holds the results once ctx->stream completes.
+//   d_w: B assignments, w_stride apart.  rs: B x (r, s, r_saver) host scalars.
+static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w, uint64_t w_stride, const uint64_t* rs,
+                       const uint64_t* gamma_inv, uint64_t* d_proofs) {
     using namespace hostfr;
-    if (!fr_reduced(r) || !fr_reduced(sv) || (r_saver && !fr_reduced(r_saver)))
-        return set_error(ctx, VSP_E_INVALID, "proving randomness not reduced mod r");
     cudaStream_t s = ctx->stream;
     const uint64_t m = pk->m;
     constexpr size_t X1 = G1XYZZ::BYTES, X2 = G2XYZZ::BYTES;
-    // the full assignment (1 || primary || auxiliary): already on the device, or uploaded from the host buffers
-    const uint32_t* d_w = d_assignment;
-    if (!d_w) {
-        VSP_TRY(upload_witness(ctx, pk, primary, aux, k.w));
-        d_w = k.w.as<uint32_t>();
-    }
+    if (gamma_inv) VSP_TRY(ensure_gamma_table(ctx, pk, gamma_inv));
 
-    // fork: multiexps that only need the witness start now
-    VSP_TRY(k.ev.alloc(ctx, 4 * X1 + X2, s));  // evA, evB1, evH, evL (G1) | evB2 (G2)
-    uint64_t* evA = k.ev.as<uint64_t>();
-    uint64_t* evB1 = evA + X1 / 8;
-    uint64_t* evH = evB1 + X1 / 8;
-    uint64_t* evL = evH + X1 / 8;
-    uint64_t* evB2 = evL + X1 / 8;
-    VSP_TRY(k.bsc.alloc(ctx, (pk->B_count ? pk->B_count : 1) * 32, s));
-    // fixed-base multiples: r d1, s d1, (-rs) d1, r_saver gamma_inv | s d2
-    Fr4 fr, fs, frs;
-    memcpy(fr.v, r, 32);
-    memcpy(fs.v, sv, 32);
-    frs = sub(from_u64(0), mul(fr, fs));
-    uint64_t pts1[4 * 12], sc1[4 * 4];
-    for (int i = 0; i < 3; ++i) memcpy(pts1 + 12 * i, pk->h_delta_g1, 96);
-    memcpy(sc1, r, 32);
-    memcpy(sc1 + 4, sv, 32);
-    memcpy(sc1 + 8, frs.v, 32);
-    if (r_saver && gamma_inv) {
-        memcpy(pts1 + 36, gamma_inv, 96);
-        memcpy(sc1 + 12, r_saver, 32);
-    } else {
-        memset(pts1 + 36, 0, 96);
-        memset(sc1 + 12, 0, 32);
+    // host scalars of the chunk: fixed-base slots (4 per ballot) and the variable-base pair (s, r)
+    std::vector<uint64_t> fsc(size_t(B) * 16), vsc(size_t(B) * 8);
+    for (unsigned b = 0; b < B; ++b) {
+        const uint64_t *r = rs + 12 * b, *sv = r + 4, *rsv = r + 8;
+        if (!fr_reduced(r) || !fr_reduced(sv) || (gamma_inv && !fr_reduced(rsv)))
+            return set_error(ctx, VSP_E_INVALID, "proving randomness not reduced mod r");
+        Fr4 fr, fs;
+        memcpy(fr.v, r, 32);
+        memcpy(fs.v, sv, 32);
+        const Fr4 frs = sub(from_u64(0), mul(fr, fs));
+        uint64_t* f = &fsc[size_t(b) * 16];
+        memcpy(f, r, 32);
+        memcpy(f + 4, sv, 32);
+        memcpy(f + 8, frs.v, 32);
+        if (gamma_inv) memcpy(f + 12, rsv, 32); else memset(f + 12, 0, 32);
+        memcpy(&vsc[size_t(b) * 8], sv, 32);     // s * g_A
+        memcpy(&vsc[size_t(b) * 8 + 4], r, 32);  // r * g1_B
     }
-    VSP_TRY(k.fxpts.alloc(ctx, sizeof(pts1) + 192, s));
-    VSP_TRY(k.fxsc.alloc(ctx, sizeof(sc1) + 32, s));
-    VSP_TRY(k.fx1.alloc(ctx, 4 * X1, s));
-    VSP_TRY(k.fx2.alloc(ctx, X2, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(k.fxpts.p, pts1, sizeof(pts1), cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(k.fxpts.as<char>() + sizeof(pts1), pk->h_delta_g2, 192, cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(k.fxsc.p, sc1, sizeof(sc1), cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(k.fxsc.as<char>() + sizeof(sc1), sv, 32, cudaMemcpyHostToDevice, s));
-    VSP_TRY(k.h.alloc(ctx, m * 32, s));
-    VSP_TRY(k.gab.alloc(ctx, 2 * 96, s));
-    VSP_TRY(k.sgsc.alloc(ctx, 64, s));
-    VSP_TRY(k.sg.alloc(ctx, 2 * X1, s));
-    uint64_t sgs[8];
-    memcpy(sgs, sv, 32);     // s * g_A
-    memcpy(sgs + 4, r, 32);  // r * g1_B
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(k.sgsc.p, sgs, 64, cudaMemcpyHostToDevice, s));
+    DevBuf abc, ev, bsc, d_fsc, d_vsc, jobs, fx1, fx2, gab, sg;
+    VSP_TRY(ev.alloc(ctx, size_t(B) * (4 * X1 + X2), s));  // evA | evB1 | evH | evL (G1) | evB2 (G2), B each
+    uint64_t* evA = ev.as<uint64_t>();
+    uint64_t* evB1 = evA + size_t(B) * X1 / 8;
+    uint64_t* evH = evB1 + size_t(B) * X1 / 8;
+    uint64_t* evL = evH + size_t(B) * X1 / 8;
+    uint64_t* evB2 = evL + size_t(B) * X1 / 8;
+    VSP_TRY(bsc.alloc(ctx, size_t(B) * (pk->B_count ? pk->B_count : 1) * 32, s));
+    VSP_TRY(d_fsc.alloc(ctx, fsc.size() * 8, s));
+    VSP_TRY(d_vsc.alloc(ctx, vsc.size() * 8, s));
+    VSP_TRY(jobs.alloc(ctx, sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), s));
+    VSP_TRY(fx1.alloc(ctx, size_t(B) * 4 * X1, s));
+    VSP_TRY(fx2.alloc(ctx, size_t(B) * X2, s));
+    VSP_TRY(gab.alloc(ctx, size_t(B) * 2 * 96, s));
+    VSP_TRY(sg.alloc(ctx, size_t(B) * 2 * X1, s));
+    VSP_TRY(abc.alloc(ctx, size_t(3) * B * m * 32, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc.data(), fsc.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc.p, vsc.data(), vsc.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.p, PROOF_JOBS_G1, sizeof(PROOF_JOBS_G1), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.as<char>() + sizeof(PROOF_JOBS_G1), PROOF_JOBS_G2, sizeof(PROOF_JOBS_G2),
+                                        cudaMemcpyHostToDevice, s));
+    const FixedJob* jobs1 = jobs.as<FixedJob>();
+    const FixedJob* jobs2 = jobs1 + 4;
 
-    cudaEvent_t ev_w = ctx->ev_join[3];  // reuse as "witness ready" before side 2/3 start (re-recorded below)
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ev_w, s));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[2], ev_w, 0));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[3], ev_w, 0));
+    // fork: everything that only needs the witness and the scalars
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[2], ctx->ev_fork, 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[3], ctx->ev_fork, 0));
     // side 2: A, L
-    VSP_TRY(msm_run(ctx, ctx->side[2], pk->A, pk->nv + 1, d_w, evA, true));
-    VSP_TRY(msm_run(ctx, ctx->side[2], pk->L, pk->na, d_w + 8 * (pk->ni + 1), evL, true));
+    VSP_TRY(msm_run(ctx, ctx->side[2], pk->A, pk->nv + 1, d_w, evA, true, B, w_stride, X1 / 8));
+    VSP_TRY(msm_run(ctx, ctx->side[2], pk->L, pk->na, d_w + 8 * (pk->ni + 1), evL, true, B, w_stride, X1 / 8));
     VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[2], ctx->side[2]));
     // side 3: fixed-base multiples, B (G2), B (G1)
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<Fq2Ops>, 1, 32, 0, ctx->side[3],
-               reinterpret_cast<const uint64_t*>(k.fxpts.as<char>() + sizeof(pts1)),
-               reinterpret_cast<const uint32_t*>(k.fxsc.as<char>() + sizeof(sc1)), 1u, 0, k.fx2.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 4, 32, 0, ctx->side[3], k.fxpts.as<uint64_t>(), k.fxsc.as<uint32_t>(), 4u,
-               0, k.fx1.as<uint32_t>());
+    cudaStream_t s3 = ctx->side[3];
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<Fq2Ops>, (B + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
+                 FIXED_WARPS * 32 * X2, s3, pk->fx2tab.d_pts, pk->fx2tab.n, jobs2, 1u, B, d_fsc.as<uint32_t>(), 4u,
+                 (const uint32_t*)nullptr, uint64_t(0), fx2.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (4 * B + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
+                 FIXED_WARPS * 32 * X1, s3, pk->fx1tab.d_pts, pk->fx1tab.n, jobs1, 4u, 4 * B, d_fsc.as<uint32_t>(), 4u,
+                 (const uint32_t*)nullptr, uint64_t(0), fx1.as<uint32_t>());
     if (pk->B_count)
-        VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, (unsigned)((pk->B_count + 127) / 128), 128, 0, ctx->side[3], d_w, pk->d_B_idx,
-                   pk->B_count, k.bsc.as<uint32_t>());
+        VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, dim3((unsigned)((pk->B_count + 127) / 128), B), 128, 0, s3, d_w, w_stride,
+                     pk->d_B_idx, pk->B_count, bsc.as<uint32_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    VSP_TRY(msm_run(ctx, ctx->side[3], pk->Bg2, pk->B_count, k.bsc.as<uint32_t>(), evB2, true));
-    VSP_TRY(msm_run(ctx, ctx->side[3], pk->Bg1, pk->B_count, k.bsc.as<uint32_t>(), evB1, true));
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[3], ctx->side[3]));
+    VSP_TRY(msm_run(ctx, s3, pk->Bg2, pk->B_count, bsc.as<uint32_t>(), evB2, true, B, pk->B_count, X2 / 8));
+    VSP_TRY(msm_run(ctx, s3, pk->Bg1, pk->B_count, bsc.as<uint32_t>(), evB1, true, B, pk->B_count, X1 / 8));
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[3], s3));
 
     // main: witness map, H multiexp
-    VSP_TRY(witness_map_dev(ctx, pk, d_w, k.h.as<uint32_t>(), k.aB, k.aC));
-    VSP_TRY(msm_run(ctx, s, pk->H, m - 1, k.h.as<uint32_t>(), evH, true));
+    VSP_TRY(witness_map_dev(ctx, s, pk, d_w, w_stride, B, abc.as<uint32_t>()));
+    VSP_TRY(msm_run(ctx, s, pk->H, m - 1, abc.as<uint32_t>(), evH, true, B, m, X1 / 8));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[2], 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[3], 0));
 
@@ -562,18 +694,30 @@ static int prove_async(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* d_assignm
     ap.evB2 = reinterpret_cast<uint32_t*>(evB2);
     ap.evH = reinterpret_cast<uint32_t*>(evH);
     ap.evL = reinterpret_cast<uint32_t*>(evL);
-    ap.fx1 = k.fx1.as<uint32_t>();
-    ap.fx2 = k.fx2.as<uint32_t>();
+    ap.fx1 = fx1.as<uint32_t>();
+    ap.fx2 = fx2.as<uint32_t>();
     ap.fixed1 = pk->fixed1.d_pts;
     ap.fixed2 = pk->fixed2.d_pts;
-    ap.gA_gB1 = k.gab.as<uint64_t>();
-    ap.proof = d_proof;
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, 1, 96, 0, s, ap);
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2, 32, 0, s, k.gab.as<uint64_t>(), k.sgsc.as<uint32_t>(), 2u, 0,
-               k.sg.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, 1, 32, 0, s, ap, k.sg.as<uint32_t>());
+    ap.gab = gab.as<uint64_t>();
+    ap.sg = sg.as<uint32_t>();
+    ap.proof = d_proofs;
+    ap.B = B;
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, dim3((B + 31) / 32, 3), 32, 0, s, ap);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2 * B, 32, 0, s, gab.as<uint64_t>(), d_vsc.as<uint32_t>(), 2 * B, 0,
+                 sg.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, (B + 31) / 32, 32, 0, s, ap);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    return VSP_OK;
+    return VSP_OK;  // scratch is released stream-ordered on s, after the joins above
+}
+
+static unsigned batch_chunk() {
+    static unsigned v = 0;
+    if (!v) {
+        const char* e = getenv("VSP_BATCH_CHUNK");
+        long x = e ? atol(e) : 64;
+        v = (unsigned)(x < 1 ? 1 : (x > 1024 ? 1024 : x));
+    }
+    return v;
 }
 
 }  // namespace vsp
@@ -582,49 +726,35 @@ extern "C" int vsp_witness_map(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* p
                                uint64_t* h_out) {
     if (!ctx || !pk || !h_out || (!primary && pk->ni) || (!aux && pk->na)) return VSP_E_INVALID;
     cudaSetDevice(ctx->device);
-    DevBuf d_w, d_h, aB, aC;
-    VSP_TRY(upload_witness(ctx, pk, primary, aux, d_w));
-    VSP_TRY(d_h.alloc(ctx, pk->m * 32, ctx->stream));
-    VSP_TRY(witness_map_dev(ctx, pk, d_w.as<uint32_t>(), d_h.as<uint32_t>(), aB, aC));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(h_out, d_h.p, pk->m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    DevBuf d_w, abc;
+    VSP_TRY(upload_witness(ctx, pk, 1, primary, aux, d_w));
+    VSP_TRY(abc.alloc(ctx, 3 * pk->m * 32, ctx->stream));
+    VSP_TRY(witness_map_dev(ctx, ctx->stream, pk, d_w.as<uint32_t>(), pk->nv + 1, 1, abc.as<uint32_t>()));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(h_out, abc.p, pk->m * 32, cudaMemcpyDeviceToHost, ctx->stream));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     memset(h_out + 4 * pk->m, 0, 32);  // coefficients_for_H[m] = 0 for d1 = d2 = d3 = 0
     return VSP_OK;
 }
 
-extern "C" int vsp_prove(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux,
-                         const uint64_t r[4], const uint64_t s[4], const uint64_t* r_saver,
-                         const uint64_t* gamma_inverse_sum_s_g1, uint64_t* out_proof) {
-    if (!ctx || !pk || !r || !s || !out_proof || (!primary && pk->ni) || (!aux && pk->na)) return VSP_E_INVALID;
-    cudaSetDevice(ctx->device);
-    ProofScratch k;
-    DevBuf d_proof;
-    VSP_TRY(d_proof.alloc(ctx, 384, ctx->stream));
-    VSP_TRY(prove_async(ctx, pk, nullptr, primary, aux, r, s, r_saver, gamma_inverse_sum_s_g1, d_proof.as<uint64_t>(), k));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_proof, d_proof.p, 384, cudaMemcpyDeviceToHost, ctx->stream));
-    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    for (int i = 0; i < 4; ++i) VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->side[i]));
-    return VSP_OK;
-}
-
-static int prove_batch_impl(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const uint64_t* primary, const uint64_t* aux,
+// k ballots in chunks; witnesses either on the host (primary / aux, ballot-major) or on the device (d_assignments)
+static int prove_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, uint64_t k, const uint64_t* primary, const uint64_t* aux,
                             const uint64_t* d_assignments, const uint64_t* rs, const uint64_t* gamma_inverse_sum_s_g1,
                             uint64_t* d_proofs) {
-    // ballots are enqueued back to back without host synchronisation; scratch of ballot i is released (stream-ordered)
-    // once ballot i + 1 has been enqueued, so the allocator pool recycles it.
-    for (uint64_t i = 0; i < k; ++i) {
-        ProofScratch sc;
-        const uint64_t* rr = rs + 12 * i;
-        const uint32_t* d_w =
-            d_assignments ? reinterpret_cast<const uint32_t*>(d_assignments + 4 * (pk->nv + 1) * i) : nullptr;
-        VSP_TRY(prove_async(ctx, pk, d_w, primary ? primary + 4 * pk->ni * i : nullptr, aux ? aux + 4 * pk->na * i : nullptr,
-                            rr, rr + 4, gamma_inverse_sum_s_g1 ? rr + 8 : nullptr, gamma_inverse_sum_s_g1,
-                            d_proofs + 48 * i, sc));
-        // side streams must finish with this ballot's scratch before it is recycled
-        for (int j = 0; j < 4; ++j) {
-            VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[j], ctx->side[j]));
-            VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[j], 0));
+    vsp_pk* pk = const_cast<vsp_pk*>(cpk);  // the gamma_inv table cache is the only mutable part
+    const uint64_t stride = pk->nv + 1;
+    const unsigned chunk = batch_chunk();
+    for (uint64_t i = 0; i < k; i += chunk) {
+        const unsigned B = (unsigned)((k - i < chunk) ? (k - i) : chunk);
+        DevBuf d_w;
+        const uint32_t* w;
+        if (d_assignments) {
+            w = reinterpret_cast<const uint32_t*>(d_assignments + 4 * stride * i);
+        } else {
+            VSP_TRY(upload_witness(ctx, pk, B, primary ? primary + 4 * pk->ni * i : nullptr,
+                                   aux ? aux + 4 * pk->na * i : nullptr, d_w));
+            w = d_w.as<uint32_t>();
         }
+        VSP_TRY(prove_chunk(ctx, pk, B, w, stride, rs + 12 * i, gamma_inverse_sum_s_g1, d_proofs + 48 * i));
     }
     return VSP_OK;
 }
@@ -642,6 +772,18 @@ extern "C" int vsp_prove_batch(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const
     return VSP_OK;
 }
 
+extern "C" int vsp_prove(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux,
+                         const uint64_t r[4], const uint64_t s[4], const uint64_t* r_saver,
+                         const uint64_t* gamma_inverse_sum_s_g1, uint64_t* out_proof) {
+    if (!ctx || !pk || !r || !s || !out_proof) return VSP_E_INVALID;
+    const bool enc = r_saver && gamma_inverse_sum_s_g1;
+    uint64_t rs[12] = {0};
+    memcpy(rs, r, 32);
+    memcpy(rs + 4, s, 32);
+    if (enc) memcpy(rs + 8, r_saver, 32);
+    return vsp_prove_batch(ctx, pk, 1, primary, aux, rs, enc ? gamma_inverse_sum_s_g1 : nullptr, out_proof);
+}
+
 // device-resident variant: d_assignments = k full assignments (1 || primary || auxiliary), (num_inputs + num_aux + 1)
 // canonical Fr each; d_proofs = k * 48 limbs on the device.  Stream-ordered: returns once everything is enqueued.
 extern "C" int vsp_prove_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const uint64_t* d_assignments,
@@ -650,7 +792,6 @@ extern "C" int vsp_prove_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, c
     cudaSetDevice(ctx->device);
     return prove_batch_impl(ctx, pk, k, nullptr, nullptr, d_assignments, rs, gamma_inverse_sum_s_g1, d_proofs);
 }
-
 // ---------------------------------------------------------------------------------------------
 // SAVER
 // ---------------------------------------------------------------------------------------------
@@ -778,4 +919,139 @@ extern "C" int vsp_saver_rerandomize(vsp_ctx* ctx, const vsp_saver_pubkey_t* pub
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(proof_out + 12, dout.p, 192, cudaMemcpyDeviceToHost, s));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
     return VSP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SAVER, batched: resident public key + ciphertexts and proofs of k ballots in one call
+// ---------------------------------------------------------------------------------------------
+extern "C" void vsp_saver_pub_destroy(vsp_saver_pub* sp) {
+    if (!sp) return;
+    cudaSetDevice(sp->ctx->device);
+    cudaDeviceSynchronize();
+    bases_free(&sp->tab);
+    delete sp;
+}
+
+extern "C" int vsp_saver_pub_load(vsp_ctx* ctx, const vsp_saver_pubkey_t* pub, const uint64_t* gamma_abc_rest,
+                                  vsp_saver_pub** out) {
+    if (!ctx || !pub || !out || !pub->delta_g1 || !pub->delta_sum_s_g1 || !pub->gamma_inverse_sum_s_g1 ||
+        (pub->msg_size && (!pub->delta_s_g1 || !pub->t_g1 || !gamma_abc_rest)))
+        return VSP_E_INVALID;
+    *out = nullptr;
+    if (pub->msg_size > 4096) return set_error(ctx, VSP_E_INVALID, "msg_size too large");
+    cudaSetDevice(ctx->device);
+    vsp_saver_pub* sp = new (std::nothrow) vsp_saver_pub();
+    if (!sp) return VSP_E_NOMEM;
+    sp->ctx = ctx;
+    sp->n = (unsigned)pub->msg_size;
+    const unsigned n = sp->n;
+    std::vector<uint64_t> pts(12 * size_t(3 * n + 2));
+    memcpy(&pts[0], pub->delta_g1, 96);
+    if (n) {
+        memcpy(&pts[12], pub->delta_s_g1, size_t(n) * 96);
+        memcpy(&pts[12 * size_t(1 + n)], gamma_abc_rest, size_t(n) * 96);
+        memcpy(&pts[12 * size_t(1 + 2 * n)], pub->t_g1, size_t(n) * 96);
+    }
+    memcpy(&pts[12 * size_t(1 + 3 * n)], pub->delta_sum_s_g1, 96);
+    memcpy(sp->gamma_inv, pub->gamma_inverse_sum_s_g1, 96);
+    sp->tab.force_c = 8;
+    int rc = bases_upload(ctx, false, 3 * n + 2, pts.data(), &sp->tab, true);
+    if (rc == VSP_OK && !sp->tab.table) rc = set_error(ctx, VSP_E_NOMEM, "fixed-base table not built");
+    if (rc) {
+        bases_free(&sp->tab);
+        delete sp;
+        return rc;
+    }
+    *out = sp;
+    return VSP_OK;
+}
+
+namespace vsp {
+// ciphertexts of B ballots: messages are the first msg_size primary inputs of each assignment (the reference asserts
+// the plain text is a prefix of the primary input, elgamal_verifiable.hpp:336-339); r_saver = rs[b][2]
+static int ciphertext_chunk(vsp_ctx* ctx, const vsp_saver_pub* sp, unsigned B, const uint32_t* d_w, uint64_t w_stride,
+                            const uint64_t* rs, uint64_t* d_cts) {
+    cudaStream_t s = ctx->side[0];
+    const unsigned n = sp->n, J = 3 * n + 2;
+    std::vector<FixedJob> spec(J);
+    spec[0] = FixedJob{0, 0};
+    for (unsigned i = 0; i < n; ++i) {
+        spec[1 + i] = FixedJob{int(1 + i), 0};                      // r delta_s[i]
+        spec[1 + n + i] = FixedJob{int(1 + n + i), -int(1 + i)};    // m_i gamma_abc[i]   (w[1 + i] = primary[i])
+        spec[1 + 2 * n + i] = FixedJob{int(1 + 2 * n + i), -int(1 + i)};  // m_i t[i]
+    }
+    spec[3 * n + 1] = FixedJob{int(3 * n + 1), 0};
+    std::vector<uint64_t> sc(size_t(B) * 4);
+    for (unsigned b = 0; b < B; ++b) {
+        if (!fr_reduced(rs + 12 * b + 8)) return set_error(ctx, VSP_E_INVALID, "r_saver not reduced mod r");
+        memcpy(&sc[size_t(b) * 4], rs + 12 * b + 8, 32);
+    }
+    DevBuf d_spec, d_sc, mul;
+    VSP_TRY(d_spec.alloc(ctx, J * sizeof(FixedJob), s));
+    VSP_TRY(d_sc.alloc(ctx, sc.size() * 8, s));
+    VSP_TRY(mul.alloc(ctx, size_t(B) * J * G1XYZZ::BYTES, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_spec.p, spec.data(), J * sizeof(FixedJob), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_sc.p, sc.data(), sc.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (B * J + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
+                 FIXED_WARPS * 32 * G1XYZZ::BYTES, s, sp->tab.d_pts, sp->tab.n, d_spec.as<FixedJob>(), J, B * J,
+                 d_sc.as<uint32_t>(), 1u, d_w, w_stride, mul.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_ct_sum, (B * (n + 2) + 63) / 64, 64, 0, s, mul.as<uint32_t>(), n, B, d_cts);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    return VSP_OK;
+}
+
+static int saver_encrypt_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, const vsp_saver_pub* sp, uint64_t k,
+                                    const uint64_t* primary, const uint64_t* aux, const uint64_t* d_assignments,
+                                    const uint64_t* rs, uint64_t* d_cts, uint64_t* d_proofs) {
+    vsp_pk* pk = const_cast<vsp_pk*>(cpk);
+    if (sp->n >= pk->ni + 1)
+        return set_error(ctx, VSP_E_INVALID, "plain text should be a proper prefix of the primary input");
+    const uint64_t stride = pk->nv + 1;
+    const unsigned chunk = batch_chunk();
+    const uint64_t ct_limbs = uint64_t(sp->n + 2) * 12;
+    for (uint64_t i = 0; i < k; i += chunk) {
+        const unsigned B = (unsigned)((k - i < chunk) ? (k - i) : chunk);
+        DevBuf d_w;
+        const uint32_t* w;
+        if (d_assignments) {
+            w = reinterpret_cast<const uint32_t*>(d_assignments + 4 * stride * i);
+        } else {
+            VSP_TRY(upload_witness(ctx, pk, B, primary + 4 * pk->ni * i, aux ? aux + 4 * pk->na * i : nullptr, d_w));
+            w = d_w.as<uint32_t>();
+        }
+        // the ciphertext runs on side stream 0 beside the proof
+        VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], ctx->stream));
+        VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[0], ctx->ev_join[0], 0));
+        VSP_TRY(ciphertext_chunk(ctx, sp, B, w, stride, rs + 12 * i, d_cts + ct_limbs * i));
+        VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], ctx->side[0]));
+        VSP_TRY(prove_chunk(ctx, pk, B, w, stride, rs + 12 * i, sp->gamma_inv, d_proofs + 48 * i));
+        VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[0], 0));
+    }
+    return VSP_OK;
+}
+}  // namespace vsp
+
+extern "C" int vsp_saver_encrypt_batch(vsp_ctx* ctx, const vsp_pk* pk, const vsp_saver_pub* sp, uint64_t k,
+                                       const uint64_t* primary, const uint64_t* aux, const uint64_t* rs, uint64_t* out_cts,
+                                       uint64_t* out_proofs) {
+    if (!ctx || !pk || !sp || !rs || !out_cts || !out_proofs || !primary || (!aux && pk->na)) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    if (k == 0) return VSP_OK;
+    const size_t ct_bytes = size_t(sp->n + 2) * 96;
+    DevBuf d_cts, d_proofs;
+    VSP_TRY(d_cts.alloc(ctx, k * ct_bytes, ctx->stream));
+    VSP_TRY(d_proofs.alloc(ctx, k * 384, ctx->stream));
+    VSP_TRY(saver_encrypt_batch_impl(ctx, pk, sp, k, primary, aux, nullptr, rs, d_cts.as<uint64_t>(), d_proofs.as<uint64_t>()));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_cts, d_cts.p, k * ct_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_proofs, d_proofs.p, k * 384, cudaMemcpyDeviceToHost, ctx->stream));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSP_OK;
+}
+
+extern "C" int vsp_saver_encrypt_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, const vsp_saver_pub* sp, uint64_t k,
+                                           const uint64_t* d_assignments, const uint64_t* rs, uint64_t* d_cts,
+                                           uint64_t* d_proofs) {
+    if (!ctx || !pk || !sp || !rs || !d_cts || !d_proofs || !d_assignments) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return saver_encrypt_batch_impl(ctx, pk, sp, k, nullptr, nullptr, d_assignments, rs, d_cts, d_proofs);
 }
