@@ -152,3 +152,15 @@ def test_encrypt_batch_matches_oracle(vsp, ctx, binary):
         assert np.array_equal(proofs[b], want), b
     key.close()
     pk.close()
+
+
+def test_warp_per_row_r1cs_kernel_matches(vsp, ctx, monkeypatch):
+    """the warp-per-row R1CS evaluation (long rows) and the thread-per-row one (short rows) give the same H"""
+    cs, primary, aux, arr = _instance(1057, 30, 3)
+    want = cref.witness_map(_oracle_pk(arr).cs, primary, aux)
+    for force in (None, "1"):
+        if force:
+            monkeypatch.setenv("VSP_R1CS_WARP_ROWS", force)
+        pk = vsp.ProvingKey(ctx, arr)
+        assert np.array_equal(pk.witness_map(primary, aux), want)
+        pk.close()

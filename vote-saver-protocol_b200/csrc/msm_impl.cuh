@@ -291,27 +291,54 @@ __global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse_heavy(const u
 }
 
 // ---------------------------------------------------------------------------------------------
-// 6. bucket reduction by bit planes:  sum_v v B_v = sum_j 2^j S_j,  S_j = sum of B_v over v with bit j set
+// 6. bucket reduction:  S = sum_v v B_v  over the 2^(c-1) buckets of a set (bucket index i holds value v = i + 1)
+//    a) segments of SEG = 2^seg_log buckets, one thread each, top-down running sums (2 additions per bucket):
+//           run_t = sum_{i in seg t} B_i        acc_t = sum_{i in seg t} (i - lo_t + 1) B_i
+//       so  S = sum_t acc_t + SEG * sum_t t run_t
+//    b) the (SEG times smaller) weighted sum over segments by bit planes of t:  sum_t t run_t = sum_j 2^j P_j,
+//       P_j = sum of run_t over t with bit j set — parallel tree sums; plane index nseg_log sums the acc_t
+//    c) per set: Horner over the planes, log2(SEG) doublings, add sum acc_t
 // ---------------------------------------------------------------------------------------------
-constexpr unsigned RED_THREADS = 64, RED_CHUNK = 1024;  // buckets per block of k_msm_reduce_planes
+constexpr unsigned RED_THREADS = 64;
+constexpr unsigned SEG_LOG_MAX = 6;
 
-// block = (chunk, plane j, set): tree-sum the chunk's buckets whose value v = index + 1 has bit j set
 template <class F>
-__global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_t* __restrict__ partial,
-                                                                   const uint32_t* __restrict__ task_off, MsmPlan p,
-                                                                   unsigned chunks, uint32_t* __restrict__ plane_out) {
+__global__ void __launch_bounds__(64) k_msm_reduce_segments(const uint32_t* __restrict__ partial,
+                                                            const uint32_t* __restrict__ task_off, MsmPlan p,
+                                                            unsigned seg_log, uint32_t* __restrict__ seg_out) {
+    constexpr int L = XYZZ<F>::BYTES / 4;
+    const unsigned nseg_log = p.nb_log - seg_log;
+    const uint64_t q = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;  // (set, segment)
+    const uint64_t n_sets = uint64_t(p.batch) * p.sets;
+    if (q >= (n_sets << nseg_log)) return;
+    const uint64_t lo = q << seg_log;  // global bucket index of the segment's first bucket (sets are contiguous)
+    XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
+    for (int i = (1 << seg_log) - 1; i >= 0; --i) {
+        const uint32_t t0 = task_off[lo + i], t1 = task_off[lo + i + 1];
+        if (t1 > t0) ec_add<F>(run, XYZZ<F>::load(partial + uint64_t(t0) * L));
+        ec_add<F>(acc, run);
+    }
+    acc.store(seg_out + (2 * q) * L);
+    run.store(seg_out + (2 * q + 1) * L);
+}
+
+// block = (plane j, set): j < nseg_log sums run_t over t with bit j set; j == nseg_log sums every acc_t
+template <class F>
+__global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_t* __restrict__ seg, unsigned nseg_log,
+                                                                   uint32_t* __restrict__ plane_out) {
     extern __shared__ uint4 sm4[];
     uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned chunk = blockIdx.x, j = blockIdx.y, set = blockIdx.z;
-    const uint32_t nb = 1u << p.nb_log;
-    const uint32_t lo = chunk * RED_CHUNK, hi = min(nb, lo + RED_CHUNK);
-    const uint64_t bbase = uint64_t(set) << p.nb_log;
+    const unsigned j = blockIdx.x, set = blockIdx.y;
+    const uint32_t nseg = 1u << nseg_log;
+    const uint32_t* base = seg + (uint64_t(set) << nseg_log) * 2 * L;
     XYZZ<F> acc = XYZZ<F>::inf();
-    for (uint32_t idx = lo + threadIdx.x; idx < hi; idx += RED_THREADS) {
-        if (!(((idx + 1u) >> j) & 1u)) continue;
-        const uint32_t t0 = task_off[bbase + idx], t1 = task_off[bbase + idx + 1];
-        if (t1 > t0) ec_add<F>(acc, XYZZ<F>::load(partial + uint64_t(t0) * L));
+    for (uint32_t t = threadIdx.x; t < nseg; t += RED_THREADS) {
+        if (j < nseg_log) {
+            if ((t >> j) & 1u) ec_add<F>(acc, XYZZ<F>::load(base + (2 * uint64_t(t) + 1) * L));
+        } else {
+            ec_add<F>(acc, XYZZ<F>::load(base + (2 * uint64_t(t)) * L));
+        }
     }
     acc.store(sm + threadIdx.x * L);
     __syncthreads();
@@ -322,32 +349,25 @@ __global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_
         }
         __syncthreads();
     }
-    if (threadIdx.x == 0) acc.store(plane_out + ((uint64_t(set) * p.c + j) * chunks + chunk) * L);
+    if (threadIdx.x == 0) acc.store(plane_out + (uint64_t(set) * (nseg_log + 1) + j) * L);
 }
 
-// block = set, thread j sums plane j over the chunks; thread 0 then runs the c-step Horner  sum_j 2^j S_j
+// thread = set: Horner over the planes, times SEG, plus the acc plane
 template <class F>
-__global__ void __launch_bounds__(32) k_msm_reduce_sets(const uint32_t* __restrict__ plane_in, MsmPlan p, unsigned chunks,
-                                                        uint32_t* __restrict__ set_out) {
-    extern __shared__ uint4 sm4[];
-    uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
+__global__ void __launch_bounds__(32) k_msm_reduce_sets(const uint32_t* __restrict__ plane_in, unsigned nseg_log,
+                                                        unsigned seg_log, unsigned n_sets, uint32_t* __restrict__ set_out) {
     constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned set = blockIdx.x, j = threadIdx.x;
-    if (j < p.c) {
-        XYZZ<F> acc = XYZZ<F>::inf();
-        for (unsigned ch = 0; ch < chunks; ++ch)
-            ec_add<F>(acc, XYZZ<F>::load(plane_in + ((uint64_t(set) * p.c + j) * chunks + ch) * L));
-        acc.store(sm + j * L);
+    const unsigned set = blockIdx.x * blockDim.x + threadIdx.x;
+    if (set >= n_sets) return;
+    const uint32_t* pl = plane_in + uint64_t(set) * (nseg_log + 1) * L;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (int k = (int)nseg_log - 1; k >= 0; --k) {
+        acc = ec_dbl<F>(acc);
+        ec_add<F>(acc, XYZZ<F>::load(pl + uint64_t(k) * L));
     }
-    __syncthreads();
-    if (j == 0) {
-        XYZZ<F> acc = XYZZ<F>::inf();
-        for (int k = (int)p.c - 1; k >= 0; --k) {
-            acc = ec_dbl<F>(acc);
-            ec_add<F>(acc, XYZZ<F>::load(sm + k * L));
-        }
-        acc.store(set_out + uint64_t(set) * L);
-    }
+    for (unsigned k = 0; k < seg_log; ++k) acc = ec_dbl<F>(acc);
+    ec_add<F>(acc, XYZZ<F>::load(pl + uint64_t(nseg_log) * L));
+    acc.store(set_out + uint64_t(set) * L);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -440,12 +460,12 @@ __global__ void __launch_bounds__(64) k_table_level(uint32_t* table, uint64_t n,
     }
 }
 
-// window width minimising  (bucket additions) + (bit-plane reduction additions, ~1.4x as expensive each)
+// window width minimising  (bucket additions) + (reduction: 2 full additions per bucket, ~1.4x a mixed one each)
 static unsigned choose_window(uint64_t n, bool table) {
     double best = 1e300;
     unsigned best_c = 4;
-    for (unsigned c = 4; c <= 16; ++c) {
-        const double w = 255 / c + 1, red = 0.7 * c * double(1u << (c - 1));
+    for (unsigned c = 4; c <= 22; ++c) {
+        const double w = 255 / c + 1, red = 2.8 * double(1u << (c - 1));
         const double cost = table ? w * double(n) + red : w * (double(n) + red);
         if (cost < best) {
             best = cost;
@@ -524,15 +544,18 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
                  heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>());
     const unsigned n_sets = batch * p.sets;
-    const unsigned chunks = (unsigned)(((uint64_t(1) << p.nb_log) + RED_CHUNK - 1) / RED_CHUNK);
-    DevBuf planes, sets;
-    VSP_TRY(planes.alloc(ctx, (size_t)n_sets * p.c * chunks * XYZZ<F>::BYTES, s));
+    const unsigned seg_log = p.nb_log < SEG_LOG_MAX ? p.nb_log : SEG_LOG_MAX, nseg_log = p.nb_log - seg_log;
+    const uint64_t n_seg = uint64_t(n_sets) << nseg_log;
+    DevBuf segs, planes, sets;
+    VSP_TRY(segs.alloc(ctx, (size_t)n_seg * 2 * XYZZ<F>::BYTES, s));
+    VSP_TRY(planes.alloc(ctx, (size_t)n_sets * (nseg_log + 1) * XYZZ<F>::BYTES, s));
     VSP_TRY(sets.alloc(ctx, (size_t)n_sets * XYZZ<F>::BYTES, s));
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_planes<F>, dim3(chunks, p.c, n_sets), RED_THREADS,
-                 RED_THREADS * XYZZ<F>::BYTES, s, partial.as<uint32_t>(), task_off.as<uint32_t>(), p, chunks,
-                 planes.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, n_sets, 32, 32 * XYZZ<F>::BYTES, s, planes.as<uint32_t>(), p,
-                 chunks, sets.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_segments<F>, (unsigned)((n_seg + 63) / 64), 64, 0, s,
+                 partial.as<uint32_t>(), task_off.as<uint32_t>(), p, seg_log, segs.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_planes<F>, dim3(nseg_log + 1, n_sets), RED_THREADS,
+                 RED_THREADS * XYZZ<F>::BYTES, s, segs.as<uint32_t>(), nseg_log, planes.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, (n_sets + 31) / 32, 32, 0, s, planes.as<uint32_t>(), nseg_log,
+                 seg_log, n_sets, sets.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_final<F>, batch, 32, 0, s, sets.as<uint32_t>(), p, d_out, out_stride,
                  raw ? 1 : 0);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());

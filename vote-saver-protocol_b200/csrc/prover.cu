@@ -39,6 +39,7 @@ struct vsp_pk {
     vsp_ctx* ctx = nullptr;
     uint64_t ni = 0, na = 0, nc = 0, nv = 0, m = 0;
     int kind = 0;
+    bool short_rows = false;  // average row has <= 8 terms per matrix: thread-per-row R1CS evaluation
     // CSR (device): rows u64, cols u32, values Montgomery (A, C: v R;  B: v R^2 so that B w comes out in Montgomery form)
     uint64_t* d_row[3] = {nullptr, nullptr, nullptr};
     uint32_t* d_col[3] = {nullptr, nullptr, nullptr};
@@ -130,6 +131,36 @@ __global__ void __launch_bounds__(256) k_r1cs_eval(CsrDev csr, const uint32_t* _
         }
         acc = warp_sum(acc);
         if (lane == 0) fp_store(outs[mtx] + 8 * row, acc);
+    }
+}
+
+// the same with one thread per (row, ballot): the ballot circuits' rows hold a handful of terms (booleanity, XOR and
+// packing constraints), where a warp per row leaves 29+ lanes idle
+__global__ void __launch_bounds__(128) k_r1cs_eval_rows(CsrDev csr, const uint32_t* __restrict__ w_all, uint64_t w_stride,
+                                                        uint64_t nc, uint64_t ni, uint64_t m, uint32_t* abc) {
+    const uint64_t row = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (row >= m) return;
+    const uint64_t B = gridDim.y, b = blockIdx.y;
+    const uint32_t* w = w_all + 8 * b * w_stride;
+    uint32_t* outs[3] = {abc + 8 * (b * m), abc + 8 * ((B + b) * m), abc + 8 * ((2 * B + b) * m)};
+    if (row >= nc) {
+        Fr z = Fr::zero();
+        Fr a = (row - nc <= ni) ? fp_load<FrCfg>(w + 8 * (row - nc)) : z;
+        fp_store(outs[0] + 8 * row, a);
+        fp_store(outs[1] + 8 * row, z);
+        fp_store(outs[2] + 8 * row, z);
+        return;
+    }
+#pragma unroll 1
+    for (int mtx = 0; mtx < 3; ++mtx) {
+        const uint64_t lo = csr.row[mtx][row], hi = csr.row[mtx][row + 1];
+        Fr acc = Fr::zero();
+        for (uint64_t k = lo; k < hi; ++k) {
+            Fr v = fp_load<FrCfg>(csr.val[mtx] + 8 * k);
+            Fr x = fp_load<FrCfg>(w + 8 * uint64_t(csr.col[mtx][k]));
+            acc = fp_add(acc, fp_mul(v, x));
+        }
+        fp_store(outs[mtx] + 8 * row, acc);
     }
 }
 
@@ -422,9 +453,11 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
     const uint64_t* rows[3] = {cs.a_row, cs.b_row, cs.c_row};
     const uint32_t* cols[3] = {cs.a_col, cs.b_col, cs.c_col};
     const uint64_t* vals[3] = {cs.a_val, cs.b_val, cs.c_val};
+    uint64_t nnz_total = 0;
     for (int i = 0; i < 3; ++i) {
         if (!rows[i]) return set_error(ctx, VSP_E_INVALID, "null CSR row pointer");
         const uint64_t nnz = rows[i][pk->nc];
+        nnz_total += nnz;
         for (uint64_t k = 0; k < nnz; ++k)
             if (cols[i][k] > pk->nv) return set_error(ctx, VSP_E_INVALID, "constraint refers to variable %u > %llu",
                                                       cols[i][k], (unsigned long long)pk->nv);
@@ -439,6 +472,7 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
             VSP_CUDA_CHECK(ctx, cudaGetLastError());
         }
     }
+    pk->short_rows = nnz_total <= 24 * pk->nc && !getenv("VSP_R1CS_WARP_ROWS");  // env: force the warp-per-row kernel (tests)
     VSP_TRY(bases_upload(ctx, false, pk->nv + 1, d->A_query, &pk->A, true));
     VSP_TRY(bases_upload(ctx, false, d->B_count, d->B_g1, &pk->Bg1, true));
     VSP_TRY(bases_upload(ctx, true, d->B_count, d->B_g2, &pk->Bg2, true));
@@ -543,8 +577,12 @@ static int witness_map_dev(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const
         csr.val[i] = pk->d_val[i];
     }
     uint32_t *aA = abc, *aB = abc + 8 * (uint64_t(B) * m), *aC = abc + 8 * (uint64_t(2 * B) * m);
-    VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval, dim3((unsigned)((m * 32 + 255) / 256), B), 256, 0, s, csr, d_w, w_stride, pk->nc,
-                 pk->ni, m, abc);
+    if (pk->short_rows)
+        VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval_rows, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, csr, d_w, w_stride,
+                     pk->nc, pk->ni, m, abc);
+    else
+        VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval, dim3((unsigned)((m * 32 + 255) / 256), B), 256, 0, s, csr, d_w, w_stride,
+                     pk->nc, pk->ni, m, abc);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_TRY(coset_lde(ctx, s, pk, abc, 3 * B));
     VSP_LAUNCH_K(ctx, KC_QAP, k_h_pointwise, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, aA, aB, aC, pk->d_zinv, m);
