@@ -9,9 +9,9 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 vsp = importlib.import_module("vote-saver-protocol_b200")
-from oracle import fixtures as fx  # noqa: E402  (input generation only)
+import workload as fx  # noqa: E402  (seeded input generation)
 
 
 def timeit(fn, iters=5, warm=2):
@@ -62,7 +62,12 @@ def main():
             s = torch.from_numpy(fx.random_fr(n, 1).view(np.int64)).cuda()
             out = torch.zeros(12, dtype=torch.int64, device="cuda")
             ms = wall(lambda: h.multiexp_dev(n, s.data_ptr(), out.data_ptr()), iters=3, warm=1)
-            print("g1 msm 2^%d: %.3f ms" % (lg, ms))
+            ctx.profile_enable(True)
+            h.multiexp_dev(n, s.data_ptr(), out.data_ptr())
+            prof = ctx.profile_read()
+            ctx.profile_enable(False)
+            print("g1 msm 2^%d (VSP_MSM_C=%s): %.3f ms  | %s" % (lg, os.environ.get("VSP_MSM_C", "auto"), ms, "  ".join(
+                "%s %.2f" % (k, v["ms"]) for k, v in prof.items() if v["launches"])))
             h.close()
 
 

@@ -78,6 +78,8 @@ int vsp_ctx_create(int device, void* cuda_stream, vsp_ctx** out) {
         cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming);
     }
     cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming);
+    for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->tail[i].done, cudaEventDisableTiming);
     // keep freed scratch in the pool: repeated calls then allocate without touching the driver
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -106,6 +108,11 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
         if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
     }
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_main) cudaEventDestroy(ctx->ev_main);
+    for (int i = 0; i < 2; ++i) {
+        if (ctx->tail[i].done) cudaEventDestroy(ctx->tail[i].done);
+        if (ctx->tail[i].p) cudaFree(ctx->tail[i].p);
+    }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -55,6 +56,16 @@ struct vsp_ctx {
     cudaStream_t side[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr;
     cudaEvent_t ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+    // double-buffered scratch of the proof-assembly tail (prover.cu): the tail of chunk i runs on side[1] while the
+    // main stream already works on chunk i + 1
+    struct TailSlot {
+        void* p = nullptr;
+        size_t cap = 0;
+        cudaEvent_t done = nullptr;
+        bool pending = false;
+    } tail[2];
+    unsigned tail_next = 0;
+    cudaEvent_t ev_main = nullptr;
     vsp::KProf prof;
     int last_prof = -1;  // profile record of the most recent launch (for kprof_units)
 };

@@ -23,6 +23,7 @@
 // 0 and 1 scalars need no special path: a zero contributes no digit, a one lands in bucket (set 0, value 1), which
 // step 5 reduces in parallel — the reference's `_with_mixed_addition` pre-pass (skip 0, add 1) is subsumed.
 #pragma once
+#include <algorithm>
 #include <type_traits>
 
 #include "ec.cuh"
@@ -217,16 +218,66 @@ __global__ void k_msm_tasks(const uint32_t* __restrict__ offsets, const uint32_t
     if (t1 - t0 > HEAVY_TASKS) heavy[atomicAdd(heavy_count, 1u)] = (uint32_t)b;
 }
 
+// Tasks are handed to threads in order of decreasing length (a counting sort on the 1..TASK_POINTS lengths), so the
+// 32 lanes of a warp run the same number of additions: with ~30 points per bucket the lengths are Poisson-spread
+// and bucket order would leave a third of the lanes idle.  Only the assignment of tasks to threads changes; every
+// task still sums its points in the same order into partial[task], so results are unaffected.
+constexpr unsigned LEN_BINS = TASK_POINTS + 1;
+__global__ void __launch_bounds__(256) k_task_hist(const Task* __restrict__ tasks, const uint32_t* __restrict__ n_tasks_ptr,
+                                                   uint32_t* __restrict__ bins) {
+    __shared__ uint32_t h[LEN_BINS];
+    for (unsigned i = threadIdx.x; i < LEN_BINS; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    const uint32_t n = *n_tasks_ptr;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x)
+        atomicAdd(&h[tasks[t].end - tasks[t].begin], 1u);
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < LEN_BINS; i += blockDim.x)
+        if (h[i]) atomicAdd(&bins[i], h[i]);
+}
+// bins[len] -> start position of that length class, longest first; cursors follow at bins[LEN_BINS + len]
+__global__ void k_task_bin_offsets(uint32_t* bins) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint32_t run = 0;
+    for (int len = (int)LEN_BINS - 1; len >= 0; --len) {
+        const uint32_t c = bins[len];
+        bins[LEN_BINS + len] = run;
+        run += c;
+    }
+}
+__global__ void __launch_bounds__(256) k_task_order(const Task* __restrict__ tasks, const uint32_t* __restrict__ n_tasks_ptr,
+                                                    uint32_t* __restrict__ bins, uint32_t* __restrict__ order) {
+    __shared__ uint32_t h[LEN_BINS], base[LEN_BINS];
+    const uint32_t n = *n_tasks_ptr;
+    const uint32_t per_block = (n + gridDim.x - 1) / gridDim.x;
+    const uint32_t lo = blockIdx.x * per_block, hi = min(n, lo + per_block);
+    for (unsigned i = threadIdx.x; i < LEN_BINS; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    for (uint32_t t = lo + threadIdx.x; t < hi; t += blockDim.x) atomicAdd(&h[tasks[t].end - tasks[t].begin], 1u);
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < LEN_BINS; i += blockDim.x) {
+        base[i] = h[i] ? atomicAdd(&bins[LEN_BINS + i], h[i]) : 0u;
+        h[i] = 0;
+    }
+    __syncthreads();
+    for (uint32_t t = lo + threadIdx.x; t < hi; t += blockDim.x) {
+        const uint32_t len = tasks[t].end - tasks[t].begin;
+        order[base[len] + atomicAdd(&h[len], 1u)] = t;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // 4. accumulate
 // ---------------------------------------------------------------------------------------------
 template <class F>
 __global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restrict__ table, const uint32_t* __restrict__ sorted,
                                                         const Task* __restrict__ tasks,
+                                                        const uint32_t* __restrict__ order,
                                                         const uint32_t* __restrict__ n_tasks_ptr,
                                                         uint32_t* __restrict__ partial) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= *n_tasks_ptr) return;  // exact task count is device-resident (task_off[buckets]): no host round trip
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= *n_tasks_ptr) return;  // exact task count is device-resident (task_off[buckets]): no host round trip
+    const uint32_t t = order[tid];
     const Task k = tasks[t];
     XYZZ<F> acc = XYZZ<F>::inf();
     constexpr int PT_LIMBS = Affine<F>::BYTES / 4;
@@ -322,18 +373,21 @@ __global__ void __launch_bounds__(64) k_msm_reduce_segments(const uint32_t* __re
     run.store(seg_out + (2 * q + 1) * L);
 }
 
-// block = (plane j, set): j < nseg_log sums run_t over t with bit j set; j == nseg_log sums every acc_t
+// block = (chunk, plane j, set): over the chunk's RED_CHUNK segments, j < nseg_log sums run_t over t with bit j set;
+// j == nseg_log sums every acc_t
+constexpr unsigned RED_CHUNK = 1024;
 template <class F>
 __global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_t* __restrict__ seg, unsigned nseg_log,
-                                                                   uint32_t* __restrict__ plane_out) {
+                                                                   unsigned chunks, uint32_t* __restrict__ plane_out) {
     extern __shared__ uint4 sm4[];
     uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned j = blockIdx.x, set = blockIdx.y;
+    const unsigned chunk = blockIdx.x, j = blockIdx.y, set = blockIdx.z;
     const uint32_t nseg = 1u << nseg_log;
+    const uint32_t lo = chunk * RED_CHUNK, hi = min(nseg, lo + RED_CHUNK);
     const uint32_t* base = seg + (uint64_t(set) << nseg_log) * 2 * L;
     XYZZ<F> acc = XYZZ<F>::inf();
-    for (uint32_t t = threadIdx.x; t < nseg; t += RED_THREADS) {
+    for (uint32_t t = lo + threadIdx.x; t < hi; t += RED_THREADS) {
         if (j < nseg_log) {
             if ((t >> j) & 1u) ec_add<F>(acc, XYZZ<F>::load(base + (2 * uint64_t(t) + 1) * L));
         } else {
@@ -349,25 +403,35 @@ __global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_
         }
         __syncthreads();
     }
-    if (threadIdx.x == 0) acc.store(plane_out + (uint64_t(set) * (nseg_log + 1) + j) * L);
+    if (threadIdx.x == 0) acc.store(plane_out + ((uint64_t(set) * (nseg_log + 1) + j) * chunks + chunk) * L);
 }
 
-// thread = set: Horner over the planes, times SEG, plus the acc plane
+// block = set, thread j sums plane j over the chunks; thread 0 then runs the Horner over the planes, times SEG, plus
+// the acc plane
 template <class F>
 __global__ void __launch_bounds__(32) k_msm_reduce_sets(const uint32_t* __restrict__ plane_in, unsigned nseg_log,
-                                                        unsigned seg_log, unsigned n_sets, uint32_t* __restrict__ set_out) {
+                                                        unsigned seg_log, unsigned chunks, uint32_t* __restrict__ set_out) {
+    extern __shared__ uint4 sm4[];
+    uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned set = blockIdx.x * blockDim.x + threadIdx.x;
-    if (set >= n_sets) return;
-    const uint32_t* pl = plane_in + uint64_t(set) * (nseg_log + 1) * L;
-    XYZZ<F> acc = XYZZ<F>::inf();
-    for (int k = (int)nseg_log - 1; k >= 0; --k) {
-        acc = ec_dbl<F>(acc);
-        ec_add<F>(acc, XYZZ<F>::load(pl + uint64_t(k) * L));
+    const unsigned set = blockIdx.x, j = threadIdx.x;
+    if (j <= nseg_log) {
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (unsigned ch = 0; ch < chunks; ++ch)
+            ec_add<F>(acc, XYZZ<F>::load(plane_in + ((uint64_t(set) * (nseg_log + 1) + j) * chunks + ch) * L));
+        acc.store(sm + j * L);
     }
-    for (unsigned k = 0; k < seg_log; ++k) acc = ec_dbl<F>(acc);
-    ec_add<F>(acc, XYZZ<F>::load(pl + uint64_t(nseg_log) * L));
-    acc.store(set_out + uint64_t(set) * L);
+    __syncthreads();
+    if (j == 0) {
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (int k = (int)nseg_log - 1; k >= 0; --k) {
+            acc = ec_dbl<F>(acc);
+            ec_add<F>(acc, XYZZ<F>::load(sm + k * L));
+        }
+        for (unsigned k = 0; k < seg_log; ++k) acc = ec_dbl<F>(acc);
+        ec_add<F>(acc, XYZZ<F>::load(sm + nseg_log * L));
+        acc.store(set_out + uint64_t(set) * L);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -462,6 +526,10 @@ __global__ void __launch_bounds__(64) k_table_level(uint32_t* table, uint64_t n,
 
 // window width minimising  (bucket additions) + (reduction: 2 full additions per bucket, ~1.4x a mixed one each)
 static unsigned choose_window(uint64_t n, bool table) {
+    if (const char* e = getenv("VSP_MSM_C")) {  // tuning override
+        const int c = atoi(e);
+        if (c >= 2 && c <= 24) return (unsigned)c;
+    }
     double best = 1e300;
     unsigned best_c = 4;
     for (unsigned c = 4; c <= 22; ++c) {
@@ -533,8 +601,18 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_tasks, (unsigned)((p.buckets + 127) / 128), 128, 0, s, offsets.as<uint32_t>(),
                  task_off.as<uint32_t>(), p.buckets, tasks.as<Task>(), heavy.as<uint32_t>(), heavy_count.as<uint32_t>());
     // the exact task count lives on the device (task_off[buckets]); the grid covers the bound and extra threads exit
+    DevBuf bins, order;
+    VSP_TRY(bins.alloc(ctx, 2 * LEN_BINS * 4, s));
+    VSP_TRY(order.alloc(ctx, max_tasks * 4, s));
+    VSP_CUDA_CHECK(ctx, cudaMemsetAsync(bins.p, 0, 2 * LEN_BINS * 4, s));
+    const uint32_t* d_n_tasks = task_off.as<uint32_t>() + p.buckets;
+    const unsigned order_blocks = (unsigned)std::min<uint64_t>((max_tasks + 2047) / 2048, 1184);
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_task_hist, order_blocks, 256, 0, s, tasks.as<Task>(), d_n_tasks, bins.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_task_bin_offsets, 1, 32, 0, s, bins.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_task_order, order_blocks, 256, 0, s, tasks.as<Task>(), d_n_tasks, bins.as<uint32_t>(),
+                 order.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_ACC, k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
-                 sorted.as<uint32_t>(), tasks.as<Task>(), task_off.as<uint32_t>() + p.buckets, partial.as<uint32_t>());
+                 sorted.as<uint32_t>(), tasks.as<Task>(), order.as<uint32_t>(), d_n_tasks, partial.as<uint32_t>());
     // algorithmic work of this launch for the live roofline: bucket additions scheduled (= non-zero digits,
     // offsets[buckets]) x 11 field multiplications (the reference's mixed Jacobian add) x I_mul(limbs)
     kprof_units(ctx, ctx->last_prof, 11.0 * (std::is_same<F, FqOps>::value ? 300.0 : 3.0 * 300.0),
@@ -544,18 +622,27 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
                  heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>());
     const unsigned n_sets = batch * p.sets;
-    const unsigned seg_log = p.nb_log < SEG_LOG_MAX ? p.nb_log : SEG_LOG_MAX, nseg_log = p.nb_log - seg_log;
+    // segment length: keep ~2^15 segment threads in flight (each runs a serial chain of 2 * SEG additions)
+    unsigned seg_log = 1;
+    {
+        const unsigned total_log = p.nb_log + floor_log2_u64(n_sets);
+        if (total_log > 15 + 1) seg_log = total_log - 15;
+        if (seg_log > SEG_LOG_MAX) seg_log = SEG_LOG_MAX;
+        if (seg_log > p.nb_log) seg_log = p.nb_log;
+    }
+    const unsigned nseg_log = p.nb_log - seg_log;
     const uint64_t n_seg = uint64_t(n_sets) << nseg_log;
+    const unsigned chunks = (unsigned)(((uint64_t(1) << nseg_log) + RED_CHUNK - 1) / RED_CHUNK);
     DevBuf segs, planes, sets;
     VSP_TRY(segs.alloc(ctx, (size_t)n_seg * 2 * XYZZ<F>::BYTES, s));
-    VSP_TRY(planes.alloc(ctx, (size_t)n_sets * (nseg_log + 1) * XYZZ<F>::BYTES, s));
+    VSP_TRY(planes.alloc(ctx, (size_t)n_sets * (nseg_log + 1) * chunks * XYZZ<F>::BYTES, s));
     VSP_TRY(sets.alloc(ctx, (size_t)n_sets * XYZZ<F>::BYTES, s));
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_segments<F>, (unsigned)((n_seg + 63) / 64), 64, 0, s,
                  partial.as<uint32_t>(), task_off.as<uint32_t>(), p, seg_log, segs.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_planes<F>, dim3(nseg_log + 1, n_sets), RED_THREADS,
-                 RED_THREADS * XYZZ<F>::BYTES, s, segs.as<uint32_t>(), nseg_log, planes.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, (n_sets + 31) / 32, 32, 0, s, planes.as<uint32_t>(), nseg_log,
-                 seg_log, n_sets, sets.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_planes<F>, dim3(chunks, nseg_log + 1, n_sets), RED_THREADS,
+                 RED_THREADS * XYZZ<F>::BYTES, s, segs.as<uint32_t>(), nseg_log, chunks, planes.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, n_sets, 32, 32 * XYZZ<F>::BYTES, s, planes.as<uint32_t>(), nseg_log,
+                 seg_log, chunks, sets.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_final<F>, batch, 32, 0, s, sets.as<uint32_t>(), p, d_out, out_stride,
                  raw ? 1 : 0);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());

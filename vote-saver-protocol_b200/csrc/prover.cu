@@ -638,6 +638,9 @@ static int ensure_gamma_table(vsp_ctx* ctx, vsp_pk* pk, const uint64_t* gamma_in
     return VSP_OK;
 }
 
+// side stream i — or the main stream while per-launch profiling is on, so that timed launches do not overlap
+static cudaStream_t side_stream(vsp_ctx* ctx, int i) { return ctx->prof.on ? ctx->stream : ctx->side[i]; }
+
 // device constants of the proof's fixed-base jobs: (base, scalar slot) x 4 over fx1tab, x 1 over fx2tab.
 // per-ballot host scalars: 0 r | 1 s | 2 -rs | 3 r_saver (0 without encrypted_input)
 static const FixedJob PROOF_JOBS_G1[4] = {{0, 0}, {0, 1}, {0, 2}, {1, 3}};
@@ -672,24 +675,42 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
         memcpy(&vsc[size_t(b) * 8], sv, 32);     // s * g_A
         memcpy(&vsc[size_t(b) * 8 + 4], r, 32);  // r * g1_B
     }
-    DevBuf abc, ev, bsc, d_fsc, d_vsc, jobs, fx1, fx2, gab, sg;
-    VSP_TRY(ev.alloc(ctx, size_t(B) * (4 * X1 + X2), s));  // evA | evB1 | evH | evL (G1) | evB2 (G2), B each
-    uint64_t* evA = ev.as<uint64_t>();
+    // tail scratch (MSM results, fixed-base multiples, g_A / g1_B, their multiples, the variable-base scalars): one of
+    // two persistent slots, so this chunk's assembly tail can still be running while the next chunk is enqueued
+    vsp_ctx::TailSlot& slot = ctx->tail[ctx->tail_next++ & 1];
+    const size_t per_ballot = (4 * X1 + X2) + 4 * X1 + X2 + 192 + 2 * X1 + 64;
+    if (slot.pending) VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, slot.done, 0));  // the slot's previous tail
+    if (slot.cap < per_ballot * B) {
+        if (slot.pending) VSP_CUDA_CHECK(ctx, cudaEventSynchronize(slot.done));
+        if (slot.p) cudaFree(slot.p);
+        slot.p = nullptr;
+        slot.cap = 0;
+        VSP_CUDA_CHECK(ctx, cudaMalloc(&slot.p, per_ballot * B));
+        slot.cap = per_ballot * B;
+    }
+    char* tp = reinterpret_cast<char*>(slot.p);
+    uint64_t* evA = reinterpret_cast<uint64_t*>(tp);  // evA | evB1 | evH | evL (G1) | evB2 (G2), B each
     uint64_t* evB1 = evA + size_t(B) * X1 / 8;
     uint64_t* evH = evB1 + size_t(B) * X1 / 8;
     uint64_t* evL = evH + size_t(B) * X1 / 8;
     uint64_t* evB2 = evL + size_t(B) * X1 / 8;
+    tp += size_t(B) * (4 * X1 + X2);
+    uint32_t* fx1 = reinterpret_cast<uint32_t*>(tp);
+    tp += size_t(B) * 4 * X1;
+    uint32_t* fx2 = reinterpret_cast<uint32_t*>(tp);
+    tp += size_t(B) * X2;
+    uint64_t* gab = reinterpret_cast<uint64_t*>(tp);
+    tp += size_t(B) * 192;
+    uint32_t* sg = reinterpret_cast<uint32_t*>(tp);
+    tp += size_t(B) * 2 * X1;
+    uint32_t* d_vsc = reinterpret_cast<uint32_t*>(tp);
+    DevBuf abc, bsc, d_fsc, jobs;
     VSP_TRY(bsc.alloc(ctx, size_t(B) * (pk->B_count ? pk->B_count : 1) * 32, s));
     VSP_TRY(d_fsc.alloc(ctx, fsc.size() * 8, s));
-    VSP_TRY(d_vsc.alloc(ctx, vsc.size() * 8, s));
     VSP_TRY(jobs.alloc(ctx, sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), s));
-    VSP_TRY(fx1.alloc(ctx, size_t(B) * 4 * X1, s));
-    VSP_TRY(fx2.alloc(ctx, size_t(B) * X2, s));
-    VSP_TRY(gab.alloc(ctx, size_t(B) * 2 * 96, s));
-    VSP_TRY(sg.alloc(ctx, size_t(B) * 2 * X1, s));
     VSP_TRY(abc.alloc(ctx, size_t(3) * B * m * 32, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc.data(), fsc.size() * 8, cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc.p, vsc.data(), vsc.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc, vsc.data(), vsc.size() * 8, cudaMemcpyHostToDevice, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.p, PROOF_JOBS_G1, sizeof(PROOF_JOBS_G1), cudaMemcpyHostToDevice, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.as<char>() + sizeof(PROOF_JOBS_G1), PROOF_JOBS_G2, sizeof(PROOF_JOBS_G2),
                                         cudaMemcpyHostToDevice, s));
@@ -698,20 +719,20 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
 
     // fork: everything that only needs the witness and the scalars
     VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[2], ctx->ev_fork, 0));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[3], ctx->ev_fork, 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 2), ctx->ev_fork, 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 3), ctx->ev_fork, 0));
     // side 2: A, L
-    VSP_TRY(msm_run(ctx, ctx->side[2], pk->A, pk->nv + 1, d_w, evA, true, B, w_stride, X1 / 8));
-    VSP_TRY(msm_run(ctx, ctx->side[2], pk->L, pk->na, d_w + 8 * (pk->ni + 1), evL, true, B, w_stride, X1 / 8));
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[2], ctx->side[2]));
+    VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->A, pk->nv + 1, d_w, evA, true, B, w_stride, X1 / 8));
+    VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->L, pk->na, d_w + 8 * (pk->ni + 1), evL, true, B, w_stride, X1 / 8));
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[2], side_stream(ctx, 2)));
     // side 3: fixed-base multiples, B (G2), B (G1)
-    cudaStream_t s3 = ctx->side[3];
+    cudaStream_t s3 = side_stream(ctx, 3);
     VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<Fq2Ops>, (B + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
                  FIXED_WARPS * 32 * X2, s3, pk->fx2tab.d_pts, pk->fx2tab.n, jobs2, 1u, B, d_fsc.as<uint32_t>(), 4u,
-                 (const uint32_t*)nullptr, uint64_t(0), fx2.as<uint32_t>());
+                 (const uint32_t*)nullptr, uint64_t(0), fx2);
     VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (4 * B + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
                  FIXED_WARPS * 32 * X1, s3, pk->fx1tab.d_pts, pk->fx1tab.n, jobs1, 4u, 4 * B, d_fsc.as<uint32_t>(), 4u,
-                 (const uint32_t*)nullptr, uint64_t(0), fx1.as<uint32_t>());
+                 (const uint32_t*)nullptr, uint64_t(0), fx1);
     if (pk->B_count)
         VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, dim3((unsigned)((pk->B_count + 127) / 128), B), 128, 0, s3, d_w, w_stride,
                      pk->d_B_idx, pk->B_count, bsc.as<uint32_t>());
@@ -723,6 +744,13 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
     // main: witness map, H multiexp
     VSP_TRY(witness_map_dev(ctx, s, pk, d_w, w_stride, B, abc.as<uint32_t>()));
     VSP_TRY(msm_run(ctx, s, pk->H, m - 1, abc.as<uint32_t>(), evH, true, B, m, X1 / 8));
+    // the assembly tail runs on side[1] once the five multiexps are done; the main stream only joins the side
+    // streams (whose scratch it owns) and moves on to the next chunk
+    cudaStream_t st = side_stream(ctx, 1);
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_main, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(st, ctx->ev_main, 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(st, ctx->ev_join[2], 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(st, ctx->ev_join[3], 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[2], 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[3], 0));
 
@@ -732,20 +760,28 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
     ap.evB2 = reinterpret_cast<uint32_t*>(evB2);
     ap.evH = reinterpret_cast<uint32_t*>(evH);
     ap.evL = reinterpret_cast<uint32_t*>(evL);
-    ap.fx1 = fx1.as<uint32_t>();
-    ap.fx2 = fx2.as<uint32_t>();
+    ap.fx1 = fx1;
+    ap.fx2 = fx2;
     ap.fixed1 = pk->fixed1.d_pts;
     ap.fixed2 = pk->fixed2.d_pts;
-    ap.gab = gab.as<uint64_t>();
-    ap.sg = sg.as<uint32_t>();
+    ap.gab = gab;
+    ap.sg = sg;
     ap.proof = d_proofs;
     ap.B = B;
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, dim3((B + 31) / 32, 3), 32, 0, s, ap);
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2 * B, 32, 0, s, gab.as<uint64_t>(), d_vsc.as<uint32_t>(), 2 * B, 0,
-                 sg.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, (B + 31) / 32, 32, 0, s, ap);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, dim3((B + 31) / 32, 3), 32, 0, st, ap);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2 * B, 32, 0, st, gab, d_vsc, 2 * B, 0, sg);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, (B + 31) / 32, 32, 0, st, ap);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    return VSP_OK;  // scratch is released stream-ordered on s, after the joins above
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(slot.done, st));
+    slot.pending = true;
+    return VSP_OK;  // the caller joins the tails (join_tails) before it hands results back
+}
+
+// make ctx->stream wait for every assembly tail still in flight
+static int join_tails(vsp_ctx* ctx) {
+    for (int i = 0; i < 2; ++i)
+        if (ctx->tail[i].pending) VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->tail[i].done, 0));
+    return VSP_OK;
 }
 
 static unsigned batch_chunk() {
@@ -794,7 +830,7 @@ static int prove_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, uint64_t k, const u
         }
         VSP_TRY(prove_chunk(ctx, pk, B, w, stride, rs + 12 * i, gamma_inverse_sum_s_g1, d_proofs + 48 * i));
     }
-    return VSP_OK;
+    return join_tails(ctx);
 }
 
 extern "C" int vsp_prove_batch(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, const uint64_t* primary, const uint64_t* aux,
@@ -1009,7 +1045,7 @@ namespace vsp {
 // the plain text is a prefix of the primary input, elgamal_verifiable.hpp:336-339); r_saver = rs[b][2]
 static int ciphertext_chunk(vsp_ctx* ctx, const vsp_saver_pub* sp, unsigned B, const uint32_t* d_w, uint64_t w_stride,
                             const uint64_t* rs, uint64_t* d_cts) {
-    cudaStream_t s = ctx->side[0];
+    cudaStream_t s = side_stream(ctx, 0);
     const unsigned n = sp->n, J = 3 * n + 2;
     std::vector<FixedJob> spec(J);
     spec[0] = FixedJob{0, 0};
@@ -1059,13 +1095,13 @@ static int saver_encrypt_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, const vsp_s
         }
         // the ciphertext runs on side stream 0 beside the proof
         VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], ctx->stream));
-        VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->side[0], ctx->ev_join[0], 0));
+        VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 0), ctx->ev_join[0], 0));
         VSP_TRY(ciphertext_chunk(ctx, sp, B, w, stride, rs + 12 * i, d_cts + ct_limbs * i));
-        VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], ctx->side[0]));
+        VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], side_stream(ctx, 0)));
         VSP_TRY(prove_chunk(ctx, pk, B, w, stride, rs + 12 * i, sp->gamma_inv, d_proofs + 48 * i));
         VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[0], 0));
     }
-    return VSP_OK;
+    return join_tails(ctx);
 }
 }  // namespace vsp
 
