@@ -209,3 +209,26 @@ def test_saver_c_agrees_with_python():
                            J(pub_arr["delta_sum_s_g1"])[0], J(pub_arr["gamma_inverse_sum_s_g1"])[0])
     want = o.saver_ciphertext(pub, J(gabc), msg_i, r)
     assert cref.g1_from_limbs(got) == [o.G1.to_affine(p) for p in want]
+
+
+def test_saver_encrypt_verifies_and_survives_rerandomisation():
+    """elgamal_verifiable.cpp:353-489 style round trip on the oracle: keygen -> encrypt (ciphertext + encrypted_input
+    proof, g_C += r_saver * gamma_inverse_sum_s_g1) -> verify_encryption true; a tampered ciphertext is rejected; the
+    same after rerandomize.  This is the gate for the UPSTREAM-RECALL encrypted_input adjustment."""
+    rng = random.Random(31)
+    msg_size = 3
+    cs, primary, aux = o.r1cs_example_with_field_input(12, 5, rng)
+    pk, vk = o.groth16_generate(cs, rng)
+    pub, _sk, _svk = o.saver_keygen(vk, msg_size, [rng.randrange(1, o.R) for _ in range(3 * msg_size + 2)])
+    r_saver, r, s = (rng.randrange(o.R) for _ in range(3))
+    plain = list(primary[:msg_size])
+    ct, proof = o.saver_encrypt(pk, vk, pub, plain, primary, aux, r_saver, r, s)
+    rest = list(primary[msg_size:])
+    assert o.saver_verify_encryption(vk, pub, ct, rest, proof)
+    bad = list(ct)
+    bad[1] = o.G1.add(bad[1], o.g1_generator())
+    assert not o.saver_verify_encryption(vk, pub, bad, rest, proof)
+    rnd = [rng.randrange(1, o.R) for _ in range(3)]
+    ct2, proof2 = o.saver_rerandomize(pub, pk.delta_g2, ct, proof, rnd)
+    assert ct2 != ct
+    assert o.saver_verify_encryption(vk, pub, ct2, rest, proof2)
