@@ -47,7 +47,8 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--constraints", type=int, default=NUM_CONSTRAINTS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the MSM 2^20 / NTT 2^20 side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip the MSM 2^20 / NTT 2^20 / sharded MSM side measurements")
+    ap.add_argument("--sharded-log-n", type=int, default=24, help="total points of the point-range sharded G1 multiexp")
     return ap.parse_args()
 
 
@@ -372,6 +373,55 @@ def run_extras(res, peaks, p_int):
     return out
 
 
+def run_sharded_msm(res, log_n_total: int, p_int_holder):
+    """BASELINE configs[4]'s exchange step: one G1 multiexp of 2^log_n_total points sharded by contiguous point range
+    over all ranks (each rank holds its range's window table), one all_gather of the partial affine points over
+    NCCL/NVLink, local join.  Collective: every rank must call this.  Device-timed, max over ranks."""
+    import torch
+    import workload as wl
+    sharded = importlib.import_module("vote-saver-protocol_b200.sharded")
+    vsp, ctx, stream, world, rank = res["vsp"], res["ctx"], res["stream"], res["world"], res["rank"]
+    n_total = 1 << log_n_total
+    sb = sharded.ShardedBases(vsp, ctx, n_total, seed=4321)
+    n_loc = sb.hi - sb.lo
+    sc = torch.from_numpy(wl.random_fr(n_loc, 77 + rank).view(np.int64)).cuda()
+    part = torch.zeros(12, dtype=torch.int64, device="cuda")
+    gathered = torch.zeros((world, 12), dtype=torch.int64, device="cuda")
+    out = torch.zeros(12, dtype=torch.int64, device="cuda")
+    lib = ctx._lib
+    import ctypes as C
+
+    def once():
+        sb.handle.multiexp_dev(n_loc, sc.data_ptr(), part.data_ptr())
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(gathered.view(-1), part)
+        else:
+            gathered[0].copy_(part)
+        # join: sum of the world partial points, on the device (vsp_g1_sum takes host points; the device path is the
+        # same kernel through the multiexp library's resident-point entry)
+        ctx.check(lib.vsp_g1_sum_dev(ctx._h, world, C.c_void_p(gathered.data_ptr()), C.c_void_p(out.data_ptr())))
+
+    with torch.cuda.stream(stream):
+        for _ in range(2):
+            once()
+        barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        iters = 5
+        for _ in range(iters):
+            once()
+        e1.record(stream)
+        barrier(world)
+        ms = e0.elapsed_time(e1) / iters
+    ms = max_over_ranks(ms, world)
+    result = out.cpu().numpy().view(np.uint64)
+    sb.close()
+    return {"log_n_total": log_n_total, "points_per_gpu": n_loc, "ms": ms, "n_gpus": world,
+            "exchange": "all_gather of %d x 96 B affine points + %d point additions" % (world, max(world - 1, 0)),
+            "result_x_limb0": int(result[0])}
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -389,6 +439,7 @@ def main():
         return
     res = run_b200(args)
     world, rank, B, K = res["world"], res["rank"], res["B"], res["K"]
+    sharded_msm = None if args.no_extras else run_sharded_msm(res, args.sharded_log_n, None)  # collective: all ranks
     if rank != 0:
         return
     ctx = res["ctx"]
@@ -419,6 +470,12 @@ def main():
             "kernels": kernels}
     if not args.no_extras:
         line["extras"] = run_extras(res, peaks, p_int)
+        w = msm_reference_mads(1 << args.sharded_log_n)
+        sharded_msm["roofline_int"] = {"bound": "int32-mad", "achieved": w / sharded_msm["ms"] / 1e9,
+                                       "peak": world * p_int / 1e12, "unit": "TMAD/s",
+                                       "frac": w / sharded_msm["ms"] / 1e9 / (world * p_int / 1e12),
+                                       "work": "reference-algorithm multiply-adds W_msm(N_total) = %.3g" % w}
+        line["extras"]["msm_g1_sharded_by_point_range"] = sharded_msm
     if not args.no_cpu_baseline:
         pk_arr = res["pk"].arrays
         sec, cpu_proofs, cpu_cts, cores = cpu_prover(args, res["cs"], pk_arr, res["prim"], res["aux"], res["rs"],

@@ -124,6 +124,9 @@ VSP_API int vsp_g1_msm_bases_dev(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n
 /* sum of k affine points (the join step of a point-range sharded MSM after the all-gather) */
 VSP_API int vsp_g1_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
 VSP_API int vsp_g2_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
+/* the same with the k points and the result on the device (e.g. the all_gather output buffer); stream-ordered */
+VSP_API int vsp_g1_sum_dev(vsp_ctx *ctx, uint64_t k, const uint64_t *d_points, uint64_t *d_out);
+VSP_API int vsp_g2_sum_dev(vsp_ctx *ctx, uint64_t k, const uint64_t *d_points, uint64_t *d_out);
 
 /* ---- R1CS, proving key, prover ------------------------------------------------------------------ */
 typedef struct {

@@ -81,6 +81,8 @@ SYMBOLS = [
     ("vsp_g1_msm_bases_dev", _int, [_vp, _vp, _u64, _vp, _vp]),
     ("vsp_g1_sum", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_g2_sum", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_g1_sum_dev", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_g2_sum_dev", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_pk_load", _int, [_vp, C.POINTER(ProvingKeyDesc), C.POINTER(_vp)]),
     ("vsp_pk_destroy", None, [_vp]),
     ("vsp_pk_domain_size", _u64, [_vp]),

@@ -411,6 +411,16 @@ int vsp_g1_sum(vsp_ctx* ctx, uint64_t k, const uint64_t* points, uint64_t* out) 
 int vsp_g2_sum(vsp_ctx* ctx, uint64_t k, const uint64_t* points, uint64_t* out) {
     return points_sum_host(ctx, true, k, points, out);
 }
+int vsp_g1_sum_dev(vsp_ctx* ctx, uint64_t k, const uint64_t* d_points, uint64_t* d_out) {
+    if (!ctx || (!d_points && k) || !d_out) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return points_sum_dev(ctx, ctx->stream, false, k, d_points, d_out);
+}
+int vsp_g2_sum_dev(vsp_ctx* ctx, uint64_t k, const uint64_t* d_points, uint64_t* d_out) {
+    if (!ctx || (!d_points && k) || !d_out) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return points_sum_dev(ctx, ctx->stream, true, k, d_points, d_out);
+}
 
 }  // extern "C"
 

@@ -1,0 +1,123 @@
+"""Multi-GPU sharding of the ballot-proof path over torch.distributed (one process per GPU; NCCL over NVLink 5 /
+NVSwitch on the GPU box, gloo in the CPU tests).  SURVEY.md 8e / DESIGN.md 7:
+
+  * batched ballots shard proof-per-GPU: ballot i -> rank i mod G, proving key replicated, no data-path collective;
+    proofs (48 limbs) and ciphertexts are gathered at the end if the caller wants them in one place;
+  * one large multiexp shards by contiguous point range: rank g runs the whole bucket pipeline on bases
+    [g N / G, (g + 1) N / G) and emits ONE affine point; the G points are exchanged by a single all_gather and summed
+    locally (NCCL has no elliptic-curve reduction, so this cannot be an all_reduce).
+
+The local multiexp and the point sum are injectable so the partition / exchange / join logic is testable on CPU with
+world_size 2 (tests/test_sharding.py supplies the oracle's functions there; the product default is the CUDA library).
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import numpy as np
+
+
+def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
+    """contiguous point range [lo, hi) of rank `rank`: sizes differ by at most one, earlier ranks take the remainder"""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank / world size")
+    q, r = divmod(n, world)
+    lo = rank * q + min(rank, r)
+    return lo, lo + q + (1 if rank < r else 0)
+
+
+def ballot_indices(k: int, rank: int, world: int) -> np.ndarray:
+    """ballots of rank `rank` under proof-per-GPU sharding: i = rank (mod world)"""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank / world size")
+    return np.arange(rank, k, world, dtype=np.int64)
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def _world(group=None) -> Tuple[int, int]:
+    dist = _dist()
+    if not (dist.is_available() and dist.is_initialized()):
+        return 0, 1
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def all_gather_rows(local: np.ndarray, group=None, device: Optional[str] = None) -> np.ndarray:
+    """all_gather of one fixed-shape uint64 array per rank -> array of shape (world,) + local.shape.
+    `device`: "cuda" moves the payload through the GPU (required by NCCL); None picks it from the backend."""
+    import torch
+    dist = _dist()
+    rank, world = _world(group)
+    local = np.ascontiguousarray(local, dtype=np.uint64)
+    if world == 1:
+        return local[None].copy()
+    if device is None:
+        device = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    t = torch.from_numpy(local.view(np.int64).copy()).to(device)
+    out = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(out, t, group=group)
+    return np.stack([o.cpu().numpy().view(np.uint64) for o in out])
+
+
+def sharded_multiexp(local_multiexp: Callable[[], np.ndarray], point_sum: Callable[[np.ndarray], np.ndarray],
+                     group=None, device: Optional[str] = None) -> np.ndarray:
+    """Point-range sharded multiexp.  local_multiexp() -> this rank's partial result as a canonical affine point
+    (12 limbs G1 / 24 limbs G2, all-zero = infinity); point_sum(points (world, L)) -> their sum, same format.
+    Every rank returns the full result (the join is replicated: G - 1 point additions)."""
+    part = np.ascontiguousarray(local_multiexp(), dtype=np.uint64).reshape(-1)
+    if part.shape[0] not in (12, 24):
+        raise ValueError("a partial multiexp result must be one affine G1 (12 limbs) or G2 (24 limbs) point")
+    parts = all_gather_rows(part, group, device)
+    return np.ascontiguousarray(point_sum(parts), dtype=np.uint64).reshape(-1)
+
+
+class ShardedBases:
+    """This rank's contiguous slice of a large bases vector, resident on its GPU with its window table."""
+
+    def __init__(self, vsp, ctx, n_total: int, *, bases_local: Optional[np.ndarray] = None, seed: Optional[int] = None,
+                 group=None):
+        self.vsp, self.ctx, self.group = vsp, ctx, group
+        self.rank, self.world = _world(group)
+        self.n_total = n_total
+        self.lo, self.hi = shard_range(n_total, self.rank, self.world)
+        if bases_local is not None:
+            b = np.ascontiguousarray(bases_local, dtype=np.uint64)
+            if b.shape[0] != self.hi - self.lo:
+                raise ValueError("bases_local must hold exactly this rank's range")
+            self.g2 = b.ndim == 2 and b.shape[1] == 24
+            self.handle = (vsp.G2Bases if self.g2 else vsp.G1Bases)(ctx, b)
+        else:
+            # synthetic sweep bases: k_i * G with k_i = splitmix64(seed + i); every rank
+            # generates only its own range, with the global index as the stream position
+            self.g2 = False
+            self.handle = vsp.G1Bases.generate(ctx, self.hi - self.lo, int(seed) + self.lo)
+
+    def multiexp(self, scalars_local) -> np.ndarray:
+        """scalars_local: this rank's (hi - lo, 4) canonical Fr.  Returns the full sum on every rank."""
+        s = np.ascontiguousarray(scalars_local, dtype=np.uint64).reshape(-1, 4)
+        if s.shape[0] != self.hi - self.lo:
+            raise ValueError("scalars_local must hold exactly this rank's range")
+        return sharded_multiexp(lambda: self.handle.multiexp(s), lambda pts: self.vsp.points_sum(self.ctx, pts),
+                                self.group)
+
+    def close(self):
+        self.handle.close()
+
+
+def gather_ballot_results(local: np.ndarray, k: int, group=None, device: Optional[str] = None) -> np.ndarray:
+    """Inverse of ballot_indices: every rank passes the results of its ballots (rows in its own order); returns the
+    (k, ...) array in ballot order on every rank.  Ranks with fewer ballots are padded for the exchange."""
+    rank, world = _world(group)
+    local = np.ascontiguousarray(local, dtype=np.uint64)
+    per = -(-k // world)
+    pad = np.zeros((per,) + local.shape[1:], dtype=np.uint64)
+    pad[: local.shape[0]] = local
+    allr = all_gather_rows(pad, group, device)
+    out = np.zeros((k,) + local.shape[1:], dtype=np.uint64)
+    for g in range(world):
+        idx = ballot_indices(k, g, world)
+        out[idx] = allr[g][: len(idx)]
+    return out
