@@ -60,8 +60,8 @@ def workload_config(args, world):
             "ballots_per_gpu_per_step": args.ballots, "ballots_per_step": args.ballots * world,
             "witness": "all-bits XOR chain (r1cs_examples.hpp:154-210 shape), distinct per ballot",
             "proving_key": "synthetic seeded bases k_i*G (shape-only)",
-            "l2": "per-step working set (5 query tables 36 MiB + per-ballot vectors) streams through L2; inputs of "
-                  "consecutive ballots differ; no explicit flush"}
+            "l2": "inputs larger than L2: 2 MiB of witness + ~30 MiB of scratch per ballot x %d ballots per step, window "
+                  "tables ~200 MiB; every ballot's witness differs; no explicit flush" % args.ballots}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -258,6 +258,11 @@ def cpu_prover(args, cs_arrays, pk_arrays, prim, aux, rs, pub_arr, gabc, n_proof
     return time.perf_counter() - t0, np.stack(out), np.stack(cts), cores
 
 
+def cref_generator(group: str):
+    from oracle import pyref as o
+    return o.G1_GEN if group == "G1" else o.G2_GEN
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path.  crypto3 itself cannot be built here (Boost and the algebra / zk /
     multiprecision submodules are absent: DESIGN.md), so this times oracle/'s restatement (kind = "port")."""
@@ -266,17 +271,53 @@ def run_reference(args):
     if rank != 0:
         return None
     import workload as wl
-    import torch
-    vsp = importlib.import_module("vote-saver-protocol_b200")
-    # the proving key is synthetic (seeded bases); it is built with the device generator when a GPU is present so both
-    # arms use identical keys
-    ctx = vsp.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    from oracle import cref
+
+    # the same synthetic key as the B200 arm (bases k_i * G, k_i = splitmix64(seed + i) | 1), built on the host by the
+    # oracle's fixed-base multiplier: nothing of the CUDA library is on this arm's path
+    def _k(n, seed):
+        with np.errstate(over="ignore"):
+            z = np.arange(n, dtype=np.uint64) + np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15)
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            return (z ^ (z >> np.uint64(31))) | np.uint64(1)
+
+    g1_gen = cref.g1_to_limbs([cref_generator("G1")])
+    g2_gen = cref.g2_to_limbs([cref_generator("G2")])
+
+    class _Handle:
+        def __init__(self, pts):
+            self.pts = pts
+
+        def read(self):
+            return self.pts
+
+        def close(self):
+            pass
+
+    class _CpuKeyGen:
+        class G1Bases:
+            @staticmethod
+            def generate(_ctx, n, seed):
+                return _Handle(cref.g1_fixed_base_mul64(g1_gen, _k(n, seed)))
+
+        @staticmethod
+        def generate_g2_points(_ctx, n, seed):
+            return cref.g2_fixed_base_mul64(g2_gen, _k(n, seed))
+
+        @staticmethod
+        def domain_plan(m):
+            kind, mm = cref.domain_plan(m)
+            return kind, mm
+
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cref.lib().orc_set_num_threads(cores)
+    vsp, ctx = _CpuKeyGen, None
     cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
     _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
     pk_arr = wl.proving_key_arrays(vsp, ctx, cs, m, seed=7)
     pub_arr, gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
     gabc = np.ascontiguousarray(gabc[:MSG_SIZE])
-    ctx.close()
     n = 1  # one ballot per step: a bounded sample of the B-ballot batch
     prim, aux = [], []
     for b in range(n):
@@ -422,6 +463,10 @@ def run_sharded_msm(res, log_n_total: int, p_int_holder):
             "result_x_limb0": int(result[0])}
 
 
+def batch_chunk_env() -> int:
+    return int(os.environ.get("VSP_BATCH_CHUNK", "64"))
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -430,17 +475,32 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def emit(line: dict):
+    """the one JSON line goes to the process's ORIGINAL stdout; everything else native code prints on fd 1 (e.g. NCCL's
+    version banner) has been rerouted to stderr by main()"""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         line = run_reference(args)
         if line is not None:
-            print(json.dumps(line))
+            emit(line)
         return
     res = run_b200(args)
     world, rank, B, K = res["world"], res["rank"], res["B"], res["K"]
     sharded_msm = None if args.no_extras else run_sharded_msm(res, args.sharded_log_n, None)  # collective: all ranks
     if rank != 0:
+        import torch.distributed as dist
+        dist.destroy_process_group()
         return
     ctx = res["ctx"]
     peaks = load_peaks()
@@ -461,7 +521,10 @@ def main():
                     "ms_per_step": res["ms_e2e"] / K, "proofs_equal_device_path": res["same"]},
             "gpu_launches": res["launches"], "clocks": res["clocks"],
             "roofline": {"bound": "int32-mad", "kernel": "k_msm_accumulate<G1>", "achieved": ach, "peak": p_int / 1e12,
-                         "unit": "TMAD/s", "frac": ach / (p_int / 1e12) if p_int else None, "traffic": None,
+                         "unit": "TMAD/s", "frac": ach / (p_int / 1e12) if p_int else None,
+                         "traffic": 5.738e9 if batch_chunk_env() == 64 and args.constraints == NUM_CONSTRAINTS else None,
+                         "traffic_note": "dram read+write bytes of the H_query launch of one 64-ballot chunk, ncu --set full "
+                                         "(profiles/r01d_ncu_full_msm_accumulate.txt)",
                          "launches": acc["launches"], "avg_launch_ms": acc["ms"] / max(acc["launches"], 1),
                          "share_of_kernel_time": acc["ms"] / tot_ms,
                          "peak_source": "vsp_measure_imad_rate, measured in this run (MEASURED_PEAKS.json has no "
@@ -484,7 +547,10 @@ def main():
                                 "sample": "ballot 0 of the batch, proved once by oracle/vsp_oracle.c (%.1f s)" % sec,
                                 "gpu_proof_bit_exact": bool(np.array_equal(cpu_proofs[0], res["proofs"][0])),
                                 "gpu_ciphertext_bit_exact": bool(np.array_equal(cpu_cts[0], res["cts"][0]))}
-    print(json.dumps(line))
+    emit(line)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
