@@ -183,6 +183,26 @@ VSP_API int vsp_prove_batch(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const ui
 VSP_API int vsp_prove_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, uint64_t k, const uint64_t *d_assignments,
                                 const uint64_t *rs, const uint64_t *gamma_inverse_sum_s_g1, uint64_t *d_proofs);
 
+/* Point-range sharded proving (one proof over G GPUs; BASELINE configs[4]).  A sliced key holds, for each of the five
+ * queries, only a contiguous range: desc->A_query / B_* / H_query / L_query point at the slices (B_idx: the slice's
+ * global variable indices, B_count = B_hi - B_lo; H_count = H_hi - H_lo), the constraint system is replicated.
+ * vsp_prove_partial returns this rank's share of the five multiexps as canonical affine points
+ *   out_partials = A(w) | B1(w) | H(h) | L(w_aux)  (G1, 12 limbs each) | B2(w) (G2, 24 limbs)  = 72 limbs;
+ * the shares are summed per component across ranks (one all_gather + vsp_g1_sum / vsp_g2_sum) and vsp_prove_assemble
+ * builds the proof from the sums (it only needs alpha/beta/delta, so any key of the same circuit serves). */
+typedef struct {
+    uint64_t A_lo, A_hi; /* within [0, num_inputs + num_aux + 1) */
+    uint64_t B_lo, B_hi; /* within the sparse B_query's entries */
+    uint64_t H_lo, H_hi; /* within [0, m - 1) */
+    uint64_t L_lo, L_hi; /* within [0, num_aux) */
+} vsp_pk_slice_t;
+VSP_API int vsp_pk_load_slice(vsp_ctx *ctx, const vsp_proving_key_t *desc, const vsp_pk_slice_t *slice, vsp_pk **out);
+VSP_API int vsp_prove_partial(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *primary, const uint64_t *aux,
+                              uint64_t *out_partials);
+VSP_API int vsp_prove_assemble(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *sums, const uint64_t r[4],
+                               const uint64_t s[4], const uint64_t *r_saver, const uint64_t *gamma_inverse_sum_s_g1,
+                               uint64_t *out_proof);
+
 /* SAVER: ciphertext (msg_size + 2 G1) and the encrypted_input proof in one call */
 VSP_API int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
                       const uint64_t *msg, const uint64_t *primary, const uint64_t *aux, const uint64_t r_saver[4],

@@ -1,0 +1,47 @@
+"""Point-range sharded proving through the C ABI (vsp_pk_load_slice / vsp_prove_partial / vsp_prove_assemble): the G
+ranks of BASELINE configs[4] are emulated one after another on the one GPU the test tier has; the exchange is the
+all_gather's identity (stacking).  Proofs must equal the oracle's single-prover proof bit for bit."""
+import importlib
+import random
+
+import numpy as np
+import pytest
+
+from oracle import cref, fixtures as fx, pyref as o
+
+from helpers import synthetic_pk_arrays, synthetic_r1cs, synthetic_saver_pub
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("nc,ni,world", [(97, 30, 2), (1057, 30, 3), (18, 5, 8)])
+def test_sharded_proof_equals_single_prover(vsp, ctx, nc, ni, world):
+    sh = importlib.import_module("vote-saver-protocol_b200.sharded")
+    cs, primary, aux = synthetic_r1cs(nc, ni, seed=nc)
+    arr = synthetic_pk_arrays(cs, nc + 1)
+    pub_arr, _ = synthetic_saver_pub(5, seed=9)
+    pub = vsp.SaverPublicKey(pub_arr)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    _, m = vsp.domain_plan(nc + ni + 1)
+    parts, keys = [], []
+    for rank in range(world):
+        sliced, rng = sh.slice_proving_key(arr, m, rank, world)
+        pk = vsp.ProvingKey(ctx, sliced, slice=rng)
+        parts.append(pk.prove_partial(P, A))
+        keys.append(pk)
+    sums = sh.sum_partials(np.stack(parts), lambda p: vsp.points_sum(ctx, p), lambda p: vsp.points_sum(ctx, p))
+    rng_ = random.Random(5)
+    r, s, rsv = (rng_.randrange(o.R) for _ in range(3))
+    opk = fx.fill_pk(cref.ProvingKeyDesc(), arr)
+    assert np.array_equal(keys[0].prove_assemble(sums, r, s), cref.groth16_prove(opk, P, A, r, s))
+    assert np.array_equal(keys[-1].prove_assemble(sums, r, s, pub, rsv),
+                          cref.groth16_prove(opk, P, A, r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"]))
+    # a sliced key refuses the whole-proof entry point
+    with pytest.raises(ValueError):
+        keys[0].prove(P, A, r, s)
+    # a full key's partial is the whole multiexp: assembling it alone gives the same proof
+    full = vsp.ProvingKey(ctx, arr)
+    assert np.array_equal(full.prove_assemble(full.prove_partial(P, A), r, s), cref.groth16_prove(opk, P, A, r, s))
+    full.close()
+    for k in keys:
+        k.close()

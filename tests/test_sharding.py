@@ -95,3 +95,43 @@ def test_sharded_multiexp_and_ballot_gather_world2_gloo(tmp_path):
     world = 2
     mp.spawn(_worker, args=(world, _free_port(), 301, str(tmp_path)), nprocs=world, join=True)
     assert all((tmp_path / ("ok%d" % r)).exists() for r in range(world))
+
+
+def test_slice_proving_key_partitions_every_query_and_shares_sum_to_the_whole():
+    """point-range slicing of a proving key (sharded.slice_proving_key): the slices tile A / B / H / L exactly, and the
+    oracle's multiexps over the slices (with the scalar ranges vsp_prove_partial uses) sum to the full multiexps"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import cref, fixtures as fx
+    import helpers as h
+    sh = _sharded()
+    cs, primary, aux = h.synthetic_r1cs(61, 6, seed=3)
+    arr = h.synthetic_pk_arrays(cs, 4)
+    _, m = cref.domain_plan(cs.num_constraints + cs.num_inputs + 1)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    w = np.concatenate([cref.ints_to_limbs([1], 4), P, A])
+    H = cref.witness_map(fx.fill_pk(cref.ProvingKeyDesc(), arr).cs, P, A)
+    ni = cs.num_inputs
+    full = {"A": cref.msm_g1(arr["A_query"], w), "H": cref.msm_g1(np.ascontiguousarray(arr["H_query"][:m - 1]), H[:m - 1].copy()),
+            "L": cref.msm_g1(arr["L_query"], A), "B": cref.msm_g1(arr["B_g1"], np.ascontiguousarray(w[arr["B_idx"]]))}
+    for world in (1, 2, 3, 5):
+        acc = {k: np.zeros(12, dtype=np.uint64) for k in full}
+        seen = {k: [] for k in "ABHL"}
+        for rank in range(world):
+            sl, rng = sh.slice_proving_key(arr, m, rank, world)
+            for k in "ABHL":
+                seen[k].append(rng[k])
+            a_lo, a_hi = rng["A"]
+            h_lo, h_hi = rng["H"]
+            l_lo, l_hi = rng["L"]
+            parts = {"A": (sl["A_query"][:a_hi - a_lo], w[a_lo:a_hi]),
+                     "H": (sl["H_query"][:h_hi - h_lo], H[h_lo:h_hi]),
+                     "L": (sl["L_query"][:l_hi - l_lo], w[ni + 1 + l_lo: ni + 1 + l_hi]),
+                     "B": (sl["B_g1"][:sl["B_count"]], w[sl["B_idx"][:sl["B_count"]]])}
+            for k, (b, s) in parts.items():
+                if len(s):
+                    acc[k] = cref.g1_add(acc[k], cref.msm_g1(np.ascontiguousarray(b), np.ascontiguousarray(s)))
+        for k in "ABHL":
+            assert seen[k][0][0] == 0 and all(seen[k][i][1] == seen[k][i + 1][0] for i in range(world - 1))
+        assert seen["A"][-1][1] == cs.num_variables + 1 and seen["H"][-1][1] == m - 1
+        for k in full:
+            assert np.array_equal(acc[k], full[k]), (world, k)

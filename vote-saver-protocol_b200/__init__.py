@@ -22,7 +22,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2, ProvingKeyDesc, R1CSDesc,
+from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2, PkSliceDesc, ProvingKeyDesc, R1CSDesc,
                    SaverPubkeyDesc, VspError)
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
@@ -314,12 +314,20 @@ class ResidentSaverKey:
 class ProvingKey:
     """r1cs_gg_ppzksnark proving key resident on the GPU (fast_proving_key.hpp:66-103 field order)."""
 
-    def __init__(self, ctx: Context, arrays: dict):
+    def __init__(self, ctx: Context, arrays: dict, slice: dict | None = None):
+        """`slice`: {"A": (lo, hi), "B": ..., "H": ..., "L": ...} when `arrays` holds only a contiguous range of each
+        query (point-range sharded proving, sharded.slice_proving_key); such a key serves prove_partial /
+        prove_assemble only."""
         self.ctx = ctx
         self.arrays = arrays
+        self.slice = slice
         desc = _fill(ProvingKeyDesc(), arrays)
         h = C.c_void_p()
-        ctx.check(ctx._lib.vsp_pk_load(ctx._h, C.byref(desc), C.byref(h)))
+        if slice is None:
+            ctx.check(ctx._lib.vsp_pk_load(ctx._h, C.byref(desc), C.byref(h)))
+        else:
+            sd = PkSliceDesc(*[int(v) for q in "ABHL" for v in slice[q]])
+            ctx.check(ctx._lib.vsp_pk_load_slice(ctx._h, C.byref(desc), C.byref(sd), C.byref(h)))
         self._h = h
         self.num_inputs = int(arrays["cs"]["num_inputs"])
         self.num_aux = int(arrays["cs"]["num_aux"])
@@ -355,6 +363,30 @@ class ProvingKey:
             rc = self.ctx._lib.vsp_prove(self.ctx._h, self._h, _p(p), _p(a), _p(rr), _p(ss), _p(rs), _p(gi), _p(out))
         else:
             rc = self.ctx._lib.vsp_prove(self.ctx._h, self._h, _p(p), _p(a), _p(rr), _p(ss), None, None, _p(out))
+        self.ctx.check(rc)
+        return out
+
+    def prove_partial(self, primary, auxiliary) -> np.ndarray:
+        """this key's (slice's) share of the five multiexps: A | B1 | H | L (G1) | B2 (G2) as 72 canonical limbs"""
+        p, a = _a(primary, 4), _a(auxiliary, 4)
+        out = np.zeros(72, dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_prove_partial(self.ctx._h, self._h, _p(p), _p(a), _p(out)))
+        return out
+
+    def prove_assemble(self, sums, r: int, s: int, pubkey: SaverPublicKey | None = None,
+                       r_saver: int | None = None) -> np.ndarray:
+        """the proof from the five multiexp results summed over all slices (layout of prove_partial)"""
+        q = np.ascontiguousarray(sums, dtype=np.uint64).reshape(-1)
+        if q.shape[0] != 72:
+            raise ValueError("sums must be 72 limbs: A | B1 | H | L | B2")
+        out = np.zeros(48, dtype=np.uint64)
+        rr, ss = _fr(r), _fr(s)
+        if pubkey is not None:
+            rs = _fr(r_saver)
+            gi = pubkey.arrays["gamma_inverse_sum_s_g1"]
+            rc = self.ctx._lib.vsp_prove_assemble(self.ctx._h, self._h, _p(q), _p(rr), _p(ss), _p(rs), _p(gi), _p(out))
+        else:
+            rc = self.ctx._lib.vsp_prove_assemble(self.ctx._h, self._h, _p(q), _p(rr), _p(ss), None, None, _p(out))
         self.ctx.check(rc)
         return out
 

@@ -41,6 +41,11 @@ class ProvingKeyDesc(C.Structure):
                 ("H_count", C.c_uint64), ("H_query", u64p), ("L_query", u64p)]
 
 
+class PkSliceDesc(C.Structure):
+    """vsp_pk_slice_t"""
+    _fields_ = [(n, C.c_uint64) for n in ("A_lo", "A_hi", "B_lo", "B_hi", "H_lo", "H_hi", "L_lo", "L_hi")]
+
+
 class SaverPubkeyDesc(C.Structure):
     """vsp_saver_pubkey_t"""
     _fields_ = [("msg_size", C.c_uint64), ("delta_g1", u64p), ("delta_s_g1", u64p), ("t_g1", u64p), ("t_g2", u64p),
@@ -84,6 +89,9 @@ SYMBOLS = [
     ("vsp_g1_sum_dev", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_g2_sum_dev", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_pk_load", _int, [_vp, C.POINTER(ProvingKeyDesc), C.POINTER(_vp)]),
+    ("vsp_pk_load_slice", _int, [_vp, C.POINTER(ProvingKeyDesc), C.POINTER(PkSliceDesc), C.POINTER(_vp)]),
+    ("vsp_prove_partial", _int, [_vp, _vp, _vp, _vp, _vp]),
+    ("vsp_prove_assemble", _int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_pk_destroy", None, [_vp]),
     ("vsp_pk_domain_size", _u64, [_vp]),
     ("vsp_witness_map", _int, [_vp, _vp, _vp, _vp, _vp]),

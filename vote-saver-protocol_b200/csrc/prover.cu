@@ -39,6 +39,9 @@ struct vsp_pk {
     vsp_ctx* ctx = nullptr;
     uint64_t ni = 0, na = 0, nc = 0, nv = 0, m = 0;
     int kind = 0;
+    // point-range slice of the five queries held by this key (full key: lo = 0, n = whole query)
+    bool sliced = false;
+    uint64_t A_lo = 0, A_n = 0, B_lo = 0, H_lo = 0, H_n = 0, L_lo = 0, L_n = 0;
     bool short_rows = false;  // average row has <= 8 terms per matrix: thread-per-row R1CS evaluation
     // CSR (device): rows u64, cols u32, values Montgomery (A, C: v R;  B: v R^2 so that B w comes out in Montgomery form)
     uint64_t* d_row[3] = {nullptr, nullptr, nullptr};
@@ -436,7 +439,7 @@ extern "C" void vsp_pk_destroy(vsp_pk* pk) {
 
 extern "C" uint64_t vsp_pk_domain_size(const vsp_pk* pk) { return pk ? pk->m : 0; }
 
-static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
+static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, const vsp_pk_slice_t* sl, vsp_pk* pk) {
     using namespace hostfr;
     const vsp_r1cs_t& cs = d->cs;
     pk->ctx = ctx;
@@ -448,7 +451,23 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
     if (domain_plan(pk->nc + pk->ni + 1, &pk->kind, &pk->m) != VSP_OK || pk->kind == VSP_DOMAIN_EXTENDED_RADIX2)
         return set_error(ctx, VSP_E_DOMAIN, "no executable evaluation domain for %llu constraints",
                          (unsigned long long)pk->nc);
-    if (d->H_count + 1 < pk->m) return set_error(ctx, VSP_E_INVALID, "H_query shorter than m - 1");
+    // the slice of each query this key holds: everything for a full key
+    pk->sliced = sl != nullptr;
+    pk->A_lo = sl ? sl->A_lo : 0;
+    pk->A_n = sl ? sl->A_hi - sl->A_lo : pk->nv + 1;
+    pk->B_lo = sl ? sl->B_lo : 0;
+    pk->H_lo = sl ? sl->H_lo : 0;
+    pk->H_n = sl ? sl->H_hi - sl->H_lo : pk->m - 1;
+    pk->L_lo = sl ? sl->L_lo : 0;
+    pk->L_n = sl ? sl->L_hi - sl->L_lo : pk->na;
+    if (sl) {
+        if (sl->A_lo > sl->A_hi || sl->A_hi > pk->nv + 1 || sl->H_lo > sl->H_hi || sl->H_hi > pk->m - 1 ||
+            sl->L_lo > sl->L_hi || sl->L_hi > pk->na || sl->B_lo > sl->B_hi || sl->B_hi - sl->B_lo != d->B_count)
+            return set_error(ctx, VSP_E_INVALID, "proving-key slice out of range");
+        if (d->H_count != pk->H_n) return set_error(ctx, VSP_E_INVALID, "H_query slice length differs from H_hi - H_lo");
+    } else if (d->H_count + 1 < pk->m) {
+        return set_error(ctx, VSP_E_INVALID, "H_query shorter than m - 1");
+    }
     cudaStream_t s = ctx->stream;
     const uint64_t* rows[3] = {cs.a_row, cs.b_row, cs.c_row};
     const uint32_t* cols[3] = {cs.a_col, cs.b_col, cs.c_col};
@@ -473,11 +492,11 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, vsp_pk* pk) {
         }
     }
     pk->short_rows = nnz_total <= 24 * pk->nc && !getenv("VSP_R1CS_WARP_ROWS");  // env: force the warp-per-row kernel (tests)
-    VSP_TRY(bases_upload(ctx, false, pk->nv + 1, d->A_query, &pk->A, true));
+    VSP_TRY(bases_upload(ctx, false, pk->A_n, d->A_query, &pk->A, true));
     VSP_TRY(bases_upload(ctx, false, d->B_count, d->B_g1, &pk->Bg1, true));
     VSP_TRY(bases_upload(ctx, true, d->B_count, d->B_g2, &pk->Bg2, true));
-    VSP_TRY(bases_upload(ctx, false, pk->m - 1, d->H_query, &pk->H, true));
-    VSP_TRY(bases_upload(ctx, false, pk->na, d->L_query, &pk->L, true));
+    VSP_TRY(bases_upload(ctx, false, pk->H_n, d->H_query, &pk->H, true));
+    VSP_TRY(bases_upload(ctx, false, pk->L_n, d->L_query, &pk->L, true));
     pk->B_count = d->B_count;
     for (uint64_t k = 0; k < d->B_count; ++k)
         if (d->B_idx[k] > pk->nv) return set_error(ctx, VSP_E_INVALID, "B_query index out of range");
@@ -533,7 +552,23 @@ extern "C" int vsp_pk_load(vsp_ctx* ctx, const vsp_proving_key_t* desc, vsp_pk**
     cudaSetDevice(ctx->device);
     vsp_pk* pk = new (std::nothrow) vsp_pk();
     if (!pk) return VSP_E_NOMEM;
-    int rc = pk_load_impl(ctx, desc, pk);
+    int rc = pk_load_impl(ctx, desc, nullptr, pk);
+    if (rc) {
+        pk->ctx = ctx;
+        vsp_pk_destroy(pk);
+        return rc;
+    }
+    *out = pk;
+    return VSP_OK;
+}
+
+extern "C" int vsp_pk_load_slice(vsp_ctx* ctx, const vsp_proving_key_t* desc, const vsp_pk_slice_t* slice, vsp_pk** out) {
+    if (!ctx || !desc || !slice || !out) return VSP_E_INVALID;
+    *out = nullptr;
+    cudaSetDevice(ctx->device);
+    vsp_pk* pk = new (std::nothrow) vsp_pk();
+    if (!pk) return VSP_E_NOMEM;
+    int rc = pk_load_impl(ctx, desc, slice, pk);
     if (rc) {
         pk->ctx = ctx;
         vsp_pk_destroy(pk);
@@ -655,6 +690,8 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
     cudaStream_t s = ctx->stream;
     const uint64_t m = pk->m;
     constexpr size_t X1 = G1XYZZ::BYTES, X2 = G2XYZZ::BYTES;
+    if (pk->sliced)
+        return set_error(ctx, VSP_E_INVALID, "this key holds a point-range slice: use vsp_prove_partial / vsp_prove_assemble");
     if (gamma_inv) VSP_TRY(ensure_gamma_table(ctx, pk, gamma_inv));
 
     // host scalars of the chunk: fixed-base slots (4 per ballot) and the variable-base pair (s, r)
@@ -866,6 +903,140 @@ extern "C" int vsp_prove_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, uint64_t k, c
     cudaSetDevice(ctx->device);
     return prove_batch_impl(ctx, pk, k, nullptr, nullptr, d_assignments, rs, gamma_inverse_sum_s_g1, d_proofs);
 }
+// ---------------------------------------------------------------------------------------------
+// point-range sharded proving (BASELINE configs[4]): every rank holds a contiguous slice of each query,
+// computes its share of the five multiexps (vsp_prove_partial), the shares are summed after one all_gather
+// (sharded.py), and the proof is assembled from the sums (vsp_prove_assemble)
+// ---------------------------------------------------------------------------------------------
+namespace vsp {
+template <class F>
+__global__ void k_affine_to_xyzz(const uint64_t* __restrict__ in, unsigned n, uint32_t* __restrict__ out) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Affine<F> a = Affine<F>::load(in + uint64_t(i) * (Affine<F>::BYTES / 8));
+    if (!a.is_inf()) {
+        a.x = F::to_mont(a.x);
+        a.y = F::to_mont(a.y);
+    }
+    XYZZ<F>::from_affine(a).store(out + uint64_t(i) * (XYZZ<F>::BYTES / 4));
+}
+}  // namespace vsp
+
+// out_partials: evA | evB1 | evH | evL (G1 affine) | evB2 (G2 affine) = 4 * 12 + 24 = 72 limbs, canonical
+extern "C" int vsp_prove_partial(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux,
+                                 uint64_t* out_partials) {
+    if (!ctx || !pk || !out_partials || (!primary && pk->ni) || (!aux && pk->na)) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStream_t s = ctx->stream;
+    const uint64_t m = pk->m, stride = pk->nv + 1;
+    DevBuf d_w, abc, bsc, out;
+    VSP_TRY(upload_witness(ctx, pk, 1, primary, aux, d_w));
+    const uint32_t* w = d_w.as<uint32_t>();
+    VSP_TRY(out.alloc(ctx, 72 * 8, s));
+    VSP_TRY(bsc.alloc(ctx, (pk->B_count ? pk->B_count : 1) * 32, s));
+    VSP_TRY(abc.alloc(ctx, size_t(3) * m * 32, s));
+    uint64_t* o = out.as<uint64_t>();
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 2), ctx->ev_fork, 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 3), ctx->ev_fork, 0));
+    VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->A, pk->A_n, w + 8 * pk->A_lo, o, false));
+    VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->L, pk->L_n, w + 8 * (pk->ni + 1 + pk->L_lo), o + 36, false));
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[2], side_stream(ctx, 2)));
+    cudaStream_t s3 = side_stream(ctx, 3);
+    if (pk->B_count)
+        VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, dim3((unsigned)((pk->B_count + 127) / 128), 1), 128, 0, s3, w, stride,
+                     pk->d_B_idx, pk->B_count, bsc.as<uint32_t>());
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_TRY(msm_run(ctx, s3, pk->Bg2, pk->B_count, bsc.as<uint32_t>(), o + 48, false));
+    VSP_TRY(msm_run(ctx, s3, pk->Bg1, pk->B_count, bsc.as<uint32_t>(), o + 12, false));
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[3], s3));
+    // the witness map is replicated: every rank needs its slice of coefficients_for_H
+    VSP_TRY(witness_map_dev(ctx, s, pk, w, stride, 1, abc.as<uint32_t>()));
+    VSP_TRY(msm_run(ctx, s, pk->H, pk->H_n, abc.as<uint32_t>() + 8 * pk->H_lo, o + 24, false));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[2], 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[3], 0));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_partials, o, 72 * 8, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    return VSP_OK;
+}
+
+// sums: the five multiexp results summed over all ranks, same layout as out_partials
+extern "C" int vsp_prove_assemble(vsp_ctx* ctx, const vsp_pk* cpk, const uint64_t* sums, const uint64_t r[4],
+                                  const uint64_t sv[4], const uint64_t* r_saver, const uint64_t* gamma_inverse_sum_s_g1,
+                                  uint64_t* out_proof) {
+    using namespace hostfr;
+    if (!ctx || !cpk || !sums || !r || !sv || !out_proof) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    vsp_pk* pk = const_cast<vsp_pk*>(cpk);
+    const bool enc = r_saver && gamma_inverse_sum_s_g1;
+    if (!fr_reduced(r) || !fr_reduced(sv) || (enc && !fr_reduced(r_saver)))
+        return set_error(ctx, VSP_E_INVALID, "proving randomness not reduced mod r");
+    if (enc) VSP_TRY(ensure_gamma_table(ctx, pk, gamma_inverse_sum_s_g1));
+    cudaStream_t s = ctx->stream;
+    constexpr size_t X1 = G1XYZZ::BYTES, X2 = G2XYZZ::BYTES;
+    Fr4 fr, fs;
+    memcpy(fr.v, r, 32);
+    memcpy(fs.v, sv, 32);
+    const Fr4 frs = sub(from_u64(0), mul(fr, fs));
+    uint64_t fsc[16] = {0}, vsc[8];
+    memcpy(fsc, r, 32);
+    memcpy(fsc + 4, sv, 32);
+    memcpy(fsc + 8, frs.v, 32);
+    if (enc) memcpy(fsc + 12, r_saver, 32);
+    memcpy(vsc, sv, 32);
+    memcpy(vsc + 4, r, 32);
+    DevBuf d_sums, ev, d_fsc, d_vsc, jobs, fx1, fx2, gab, sg, proof;
+    VSP_TRY(d_sums.alloc(ctx, 72 * 8, s));
+    VSP_TRY(ev.alloc(ctx, 4 * X1 + X2, s));
+    VSP_TRY(d_fsc.alloc(ctx, sizeof(fsc), s));
+    VSP_TRY(d_vsc.alloc(ctx, sizeof(vsc), s));
+    VSP_TRY(jobs.alloc(ctx, sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), s));
+    VSP_TRY(fx1.alloc(ctx, 4 * X1, s));
+    VSP_TRY(fx2.alloc(ctx, X2, s));
+    VSP_TRY(gab.alloc(ctx, 192, s));
+    VSP_TRY(sg.alloc(ctx, 2 * X1, s));
+    VSP_TRY(proof.alloc(ctx, 384, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_sums.p, sums, 72 * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc, sizeof(fsc), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc.p, vsc, sizeof(vsc), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.p, PROOF_JOBS_G1, sizeof(PROOF_JOBS_G1), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.as<char>() + sizeof(PROOF_JOBS_G1), PROOF_JOBS_G2, sizeof(PROOF_JOBS_G2),
+                                        cudaMemcpyHostToDevice, s));
+    // sums (evA | evB1 | evH | evL | evB2, affine canonical) -> the XYZZ Montgomery layout of the assembly kernels
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_affine_to_xyzz<FqOps>, 1, 32, 0, s, d_sums.as<uint64_t>(), 4u, ev.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_affine_to_xyzz<Fq2Ops>, 1, 32, 0, s, d_sums.as<uint64_t>() + 48, 1u,
+                 ev.as<uint32_t>() + 4 * X1 / 4);
+    const FixedJob* jobs1 = jobs.as<FixedJob>();
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<Fq2Ops>, 1, 32 * FIXED_WARPS, FIXED_WARPS * 32 * X2, s, pk->fx2tab.d_pts,
+                 pk->fx2tab.n, jobs1 + 4, 1u, 1u, d_fsc.as<uint32_t>(), 4u, (const uint32_t*)nullptr, uint64_t(0),
+                 fx2.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (4 + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
+                 FIXED_WARPS * 32 * X1, s, pk->fx1tab.d_pts, pk->fx1tab.n, jobs1, 4u, 4u, d_fsc.as<uint32_t>(), 4u,
+                 (const uint32_t*)nullptr, uint64_t(0), fx1.as<uint32_t>());
+    AsmPtrs ap;
+    ap.evA = ev.as<uint32_t>();
+    ap.evB1 = ap.evA + X1 / 4;
+    ap.evH = ap.evB1 + X1 / 4;
+    ap.evL = ap.evH + X1 / 4;
+    ap.evB2 = ap.evL + X1 / 4;
+    ap.fx1 = fx1.as<uint32_t>();
+    ap.fx2 = fx2.as<uint32_t>();
+    ap.fixed1 = pk->fixed1.d_pts;
+    ap.fixed2 = pk->fixed2.d_pts;
+    ap.gab = gab.as<uint64_t>();
+    ap.sg = sg.as<uint32_t>();
+    ap.proof = proof.as<uint64_t>();
+    ap.B = 1;
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, dim3(1, 3), 32, 0, s, ap);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2, 32, 0, s, gab.as<uint64_t>(), d_vsc.as<uint32_t>(), 2u, 0,
+                 sg.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, 1, 32, 0, s, ap);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_proof, proof.p, 384, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    return VSP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // SAVER
 // ---------------------------------------------------------------------------------------------

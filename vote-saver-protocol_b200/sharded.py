@@ -121,3 +121,72 @@ def gather_ballot_results(local: np.ndarray, k: int, group=None, device: Optiona
         idx = ballot_indices(k, g, world)
         out[idx] = allr[g][: len(idx)]
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# one proof over G GPUs: every query sharded by contiguous point range (BASELINE configs[4])
+# ---------------------------------------------------------------------------------------------------------------------
+PARTIAL_G1 = ((0, 12), (12, 24), (24, 36), (36, 48))  # A | B1 | H | L inside the 72-limb partial vector
+PARTIAL_G2 = (48, 72)  # B2
+
+
+def slice_proving_key(arrays: dict, m: int, rank: int, world: int):
+    """(arrays', slice) for rank `rank`: the same proving key with each of A_query, B_query, H_query, L_query cut to
+    this rank's contiguous range (constraint system and the fixed elements replicated).  `arrays` follows
+    vsp_proving_key_t's field names; m is the evaluation-domain size (H_query has m - 1 points)."""
+    cs = arrays["cs"]
+    nv, na = int(cs["num_inputs"]) + int(cs["num_aux"]), int(cs["num_aux"])
+    nb = int(arrays["B_count"])
+    rng = {"A": shard_range(nv + 1, rank, world), "B": shard_range(nb, rank, world),
+           "H": shard_range(m - 1, rank, world), "L": shard_range(na, rank, world)}
+
+    def cut(name, lo, hi, width):
+        a = np.ascontiguousarray(arrays[name], dtype=np.uint64).reshape(-1, width)[lo:hi]
+        return np.ascontiguousarray(a) if hi > lo else np.zeros((1, width), dtype=np.uint64)
+
+    out = dict(arrays)
+    out["A_query"] = cut("A_query", *rng["A"], 12)
+    out["H_query"] = cut("H_query", *rng["H"], 12)
+    out["H_count"] = rng["H"][1] - rng["H"][0]
+    out["L_query"] = cut("L_query", *rng["L"], 12)
+    lo, hi = rng["B"]
+    out["B_count"] = hi - lo
+    out["B_g1"] = cut("B_g1", lo, hi, 12)
+    out["B_g2"] = cut("B_g2", lo, hi, 24)
+    idx = np.ascontiguousarray(arrays["B_idx"], dtype=np.uint32)[lo:hi]
+    out["B_idx"] = np.ascontiguousarray(idx) if hi > lo else np.zeros(1, dtype=np.uint32)
+    return out, rng
+
+
+def sum_partials(parts: np.ndarray, sum_g1: Callable[[np.ndarray], np.ndarray],
+                 sum_g2: Callable[[np.ndarray], np.ndarray]) -> np.ndarray:
+    """component-wise sum of the (world, 72) partial vectors -> 72 limbs"""
+    parts = np.ascontiguousarray(parts, dtype=np.uint64).reshape(-1, 72)
+    out = np.zeros(72, dtype=np.uint64)
+    for lo, hi in PARTIAL_G1:
+        out[lo:hi] = sum_g1(np.ascontiguousarray(parts[:, lo:hi]))
+    lo, hi = PARTIAL_G2
+    out[lo:hi] = sum_g2(np.ascontiguousarray(parts[:, lo:hi]))
+    return out
+
+
+class ShardedProver:
+    """Groth16 prover for one large circuit over all ranks of `group`: this rank loads its slice of the proving key,
+    proves its share, the shares meet in one all_gather of 72 limbs per rank, every rank assembles the proof."""
+
+    def __init__(self, vsp, ctx, arrays: dict, group=None):
+        self.vsp, self.ctx, self.group = vsp, ctx, group
+        self.rank, self.world = _world(group)
+        cs = arrays["cs"]
+        _, self.m = vsp.domain_plan(int(cs["num_constraints"]) + int(cs["num_inputs"]) + 1)
+        sliced, self.ranges = slice_proving_key(arrays, self.m, self.rank, self.world)
+        self.pk = vsp.ProvingKey(ctx, sliced, slice=self.ranges)
+
+    def prove(self, primary, auxiliary, r: int, s: int, pubkey=None, r_saver=None) -> np.ndarray:
+        part = self.pk.prove_partial(primary, auxiliary)
+        parts = all_gather_rows(part, self.group)
+        sums = sum_partials(parts, lambda p: self.vsp.points_sum(self.ctx, p), lambda p: self.vsp.points_sum(self.ctx, p))
+        return self.pk.prove_assemble(sums, r, s, pubkey, r_saver)
+
+    def close(self):
+        self.pk.close()
