@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the MSM 2^20 / NTT 2^20 / sharded MSM side measurements")
     ap.add_argument("--sharded-log-n", type=int, default=24, help="total points of the point-range sharded G1 multiexp")
+    ap.add_argument("--sharded-prove-log", type=int, default=20, help="log2 domain size of the point-range sharded proof")
     return ap.parse_args()
 
 
@@ -227,7 +228,7 @@ def run_b200(args):
 
     return dict(world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
                 clocks=clocks, launches=launches, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
-                proofs=proofs_dev, cts=cts_dev, gabc=gabc, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes),
+                proofs=proofs_dev, cts=cts_dev, gabc=gabc, key=key, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes),
                 d2h=int(B * 384 + cts_dev.nbytes), stream=stream)
 
 
@@ -376,6 +377,16 @@ def run_extras(res, peaks, p_int):
             torch.cuda.synchronize()
             return e0.elapsed_time(e1) / iters
 
+    # BASELINE configs[2]: ONE encrypted-input ballot (ciphertext + proof) on the depth-16 stand-in circuit, host buffers in
+    # and out, wall clock around the synchronising C-ABI call (vsp_saver_encrypt_batch with k = 1)
+    if "key" in res:
+        lat = []
+        for i in range(7):
+            t0 = time.perf_counter()
+            res["pk"].encrypt_batch(res["key"], res["prim"][i:i + 1], res["aux"][i:i + 1], res["rs"][i:i + 1])
+            lat.append((time.perf_counter() - t0) * 1e3)
+        out["single_ballot_latency"] = {"ms_median": sorted(lat[2:])[len(lat[2:]) // 2], "ms_all": [round(x, 3) for x in lat],
+                                        "what": "one ballot, host -> host, 2 warm-up calls dropped"}
     n = 1 << 20
     # NTT 2^20: 8 distinct 32 MiB vectors round-robin (256 MiB > 126 MiB L2) so no launch finds its input in L2
     bufs = [torch.from_numpy(wl.random_fr(n, 2 + i).view(np.int64)).cuda() for i in range(8)]
@@ -467,6 +478,35 @@ def batch_chunk_env() -> int:
     return int(os.environ.get("VSP_BATCH_CHUNK", "64"))
 
 
+def run_sharded_prove(res, log_m: int):
+    """BASELINE configs[4] at a bench-sized domain: ONE Groth16 proof of a 2^log_m-constraint synthetic R1CS with every
+    query sharded by contiguous point range over all ranks (sharded.ShardedProver): replicated witness map, local
+    multiexps on each rank's slices, one all_gather of 72 limbs per rank, local join + assembly.  Collective."""
+    import workload as wl
+    sharded = importlib.import_module("vote-saver-protocol_b200.sharded")
+    vsp, ctx, world, rank = res["vsp"], res["ctx"], res["world"], res["rank"]
+    nc = (1 << log_m) - NUM_INPUTS - 1
+    cs = wl.ballot_r1cs(nc, NUM_INPUTS, seed=1)
+    _, m = vsp.domain_plan(nc + NUM_INPUTS + 1)
+    arr = wl.proving_key_arrays(vsp, ctx, cs, m, seed=17)
+    prover = sharded.ShardedProver(vsp, ctx, arr)
+    del arr
+    prim, aux = wl.ballot_witness(cs, seed=5)
+    r, s = 0x1234567, 0x7654321
+    prover.prove(prim, aux, r, s)  # warm-up (also builds nothing new: tables are built at load)
+    barrier(world)
+    t0 = time.perf_counter()
+    iters = 3
+    for _ in range(iters):
+        proof = prover.prove(prim, aux, r, s)
+    barrier(world)
+    ms = max_over_ranks((time.perf_counter() - t0) / iters * 1e3, world)
+    prover.close()
+    return {"constraints": nc, "domain": m, "n_gpus": world, "ms_per_proof": ms,
+            "timing": "host wall clock around prove_partial + all_gather + join + assemble (each call synchronises), "
+                      "max over ranks", "proof_g_A_limb0": int(proof[0])}
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -498,6 +538,7 @@ def main():
     res = run_b200(args)
     world, rank, B, K = res["world"], res["rank"], res["B"], res["K"]
     sharded_msm = None if args.no_extras else run_sharded_msm(res, args.sharded_log_n, None)  # collective: all ranks
+    sharded_prove = None if args.no_extras else run_sharded_prove(res, args.sharded_prove_log)
     if rank != 0:
         import torch.distributed as dist
         dist.destroy_process_group()
@@ -539,6 +580,7 @@ def main():
                                        "frac": w / sharded_msm["ms"] / 1e9 / (world * p_int / 1e12),
                                        "work": "reference-algorithm multiply-adds W_msm(N_total) = %.3g" % w}
         line["extras"]["msm_g1_sharded_by_point_range"] = sharded_msm
+        line["extras"]["prove_sharded_by_point_range"] = sharded_prove
     if not args.no_cpu_baseline:
         pk_arr = res["pk"].arrays
         sec, cpu_proofs, cpu_cts, cores = cpu_prover(args, res["cs"], pk_arr, res["prim"], res["aux"], res["rs"],
