@@ -228,6 +228,33 @@ VSP_API int vsp_saver_encrypt_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, const vs
 VSP_API int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
                           const uint64_t *ct_in, const uint64_t *proof_in, uint64_t *ct_out, uint64_t *proof_out);
 
+/* ---- wire codecs: the reference's byte formats either side of the path (host only, no GPU work) ------------- */
+/* Formats (relative to libs/marshalling): big-endian fixed-width integers (Fr 32 B, Fq 48 B, size_t 8 B), sequences
+ * with an 8-byte count prefix; compressed points as processing/curve_element.hpp:93-174 writes them (G1 48 B,
+ * G2 96 B = x.c1 | x.c0, flag bits 0x80 compressed / 0x40 infinity / 0x20 y > (p-1)/2); "fast" points X | Y |
+ * is_infinity (types/fast_curve_element.hpp:56-97).  These are what bin/cli's vote phase reads (common.hpp:1004-1006)
+ * and writes (common.hpp:1154-1160). */
+VSP_API int vsp_codec_g1_compress(const uint64_t *point, uint8_t *out48);
+VSP_API int vsp_codec_g2_compress(const uint64_t *point, uint8_t *out96);
+/* proof g_A | g_B | g_C (48 limbs) -> 192 bytes (zk/.../r1cs_gg_ppzksnark/proof.hpp:63-71) */
+VSP_API int vsp_codec_proof_write(const uint64_t *proof, uint8_t *out192);
+/* n cipher-text G1 points -> 8 + 48 n bytes; n Fr -> 8 + 32 n bytes (zk/.../r1cs_gg_ppzksnark/primary_input.hpp:61-97) */
+VSP_API int vsp_codec_ciphertext_write(const uint64_t *ct, uint64_t n, uint8_t *out);
+VSP_API int vsp_codec_primary_input_write(const uint64_t *values, uint64_t n, uint8_t *out);
+VSP_API int vsp_codec_primary_input_read(const uint8_t *in, size_t len, uint64_t *n, uint64_t *values, uint64_t capacity);
+/* r1cs_gg_ppzksnark_fast_proving_key (zk/.../r1cs_gg_ppzksnark/fast_proving_key.hpp:66-103): parse in two steps —
+ * sizes, then fill caller-allocated arrays addressed by a vsp_proving_key_t (rows: num_constraints + 1; cols / vals:
+ * nnz_*; A_query: A_count; B_idx / B_g2 / B_g1: B_count; H_query: H_count; L_query: L_count).  The filled descriptor
+ * goes straight into vsp_pk_load.  vsp_codec_fast_pk_write is the inverse (out == NULL: size only). */
+typedef struct {
+    uint64_t num_inputs, num_aux, num_constraints, nnz_a, nnz_b, nnz_c;
+    uint64_t A_count, B_count, B_domain_size, H_count, L_count;
+    uint64_t bytes; /* length of the serialised key inside the blob */
+} vsp_fast_pk_sizes_t;
+VSP_API int vsp_codec_fast_pk_sizes(const uint8_t *blob, size_t len, vsp_fast_pk_sizes_t *out);
+VSP_API int vsp_codec_fast_pk_read(const uint8_t *blob, size_t len, vsp_proving_key_t *desc);
+VSP_API int vsp_codec_fast_pk_write(const vsp_proving_key_t *desc, uint8_t *out, size_t capacity, size_t *written);
+
 /* ---- measurement helpers ---------------------------------------------------------------------- */
 /* sustained 32-bit multiply-add issue rate: runs a dependent-free IMAD.WIDE carry-chain kernel on all SMs for
  * `iters` rounds and returns multiply-adds per second (the P_int roofline denominator). */

@@ -164,3 +164,22 @@ def test_warp_per_row_r1cs_kernel_matches(vsp, ctx, monkeypatch):
         pk = vsp.ProvingKey(ctx, arr)
         assert np.array_equal(pk.witness_map(primary, aux), want)
         pk.close()
+
+
+def test_prove_from_fast_proving_key_blob_to_proof_bytes(vsp, ctx):
+    """the drop-in data path of the vote phase: r1cs_proving_key.bin bytes -> vsp_codec_fast_pk_read -> vsp_pk_load ->
+    vsp_prove -> 192-byte proof.bin body, equal to the oracle's proof in the reference's compressed encoding"""
+    import importlib
+    codec = importlib.import_module("vote-saver-protocol_b200.codec")
+    cs, primary, aux, arr = _instance(97, 30, seed=8, binary=True)
+    blob = codec.write_fast_proving_key(arr)
+    pk = vsp.ProvingKey(ctx, codec.read_fast_proving_key(blob))
+    r, s = 0x1234567890abcdef, o.R - 5
+    proof = pk.prove(primary, aux, r, s)
+    want = cref.groth16_prove(_oracle_pk(arr), primary, aux, r, s)
+    assert np.array_equal(proof, want)
+    gA, gB, gC = cref.g1_from_limbs(want[None, 0:12])[0], cref.g2_from_limbs(want[None, 12:36])[0], \
+        cref.g1_from_limbs(want[None, 36:48])[0]
+    assert codec.proof_bytes(proof) == (o.g1_compress(o.G1.from_affine(gA)) + o.g2_compress(o.G2.from_affine(gB)) +
+                                        o.g1_compress(o.G1.from_affine(gC)))
+    pk.close()

@@ -46,6 +46,12 @@ class PkSliceDesc(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("A_lo", "A_hi", "B_lo", "B_hi", "H_lo", "H_hi", "L_lo", "L_hi")]
 
 
+class FastPkSizes(C.Structure):
+    """vsp_fast_pk_sizes_t"""
+    _fields_ = [(n, C.c_uint64) for n in ("num_inputs", "num_aux", "num_constraints", "nnz_a", "nnz_b", "nnz_c", "A_count",
+                                          "B_count", "B_domain_size", "H_count", "L_count", "bytes")]
+
+
 class SaverPubkeyDesc(C.Structure):
     """vsp_saver_pubkey_t"""
     _fields_ = [("msg_size", C.c_uint64), ("delta_g1", u64p), ("delta_s_g1", u64p), ("t_g1", u64p), ("t_g2", u64p),
@@ -105,6 +111,15 @@ SYMBOLS = [
     ("vsp_saver_encrypt_batch", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_saver_encrypt_batch_dev", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_saver_rerandomize", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_codec_g1_compress", _int, [_vp, _vp]),
+    ("vsp_codec_g2_compress", _int, [_vp, _vp]),
+    ("vsp_codec_proof_write", _int, [_vp, _vp]),
+    ("vsp_codec_ciphertext_write", _int, [_vp, _u64, _vp]),
+    ("vsp_codec_primary_input_write", _int, [_vp, _u64, _vp]),
+    ("vsp_codec_primary_input_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), _vp, _u64]),
+    ("vsp_codec_fast_pk_sizes", _int, [_vp, C.c_size_t, C.POINTER(FastPkSizes)]),
+    ("vsp_codec_fast_pk_read", _int, [_vp, C.c_size_t, C.POINTER(ProvingKeyDesc)]),
+    ("vsp_codec_fast_pk_write", _int, [C.POINTER(ProvingKeyDesc), _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
 ]
 

@@ -1,0 +1,365 @@
+// codec.cpp — the reference's wire formats either side of the hot path (host only, no GPU work): what
+// process_encrypted_input_mode_vote_phase reads (the "fast" uncompressed proving key) and writes (compressed proof,
+// cipher text, primary-input slices).  SURVEY.md 8f rank 1.
+//
+// Formats restated from (paths relative to /root/reference/libs/marshalling):
+//   integers            fixed width, big-endian (bin/cli/include/nil/vote_saver/common.hpp:180), width = ceil(bits / 8):
+//                       Fr 32 B, Fq 48 B  (multiprecision/.../detail/integral/basic_fixed_precision_type.hpp:84-95);
+//                       std::size_t 8 B
+//   sequences           8-byte count prefix, then the elements (option::sequence_size_field_prefix<integral<size_t>>)
+//   field_element       Fq2 = c0 | c1   (algebra/.../types/field_element.hpp:343-390: data[0], data[1])
+//   fast_curve_element  X | Y | is_infinity:u8, rebuilt as (X, Y, 1)   (algebra/.../types/fast_curve_element.hpp:56-97)
+//   curve_element       compressed: G1 48 B big-endian x; G2 96 B x.c1 | x.c0; top bits of byte 0: C = 0x80, I = 0x40,
+//                       S = 0x20 set iff y > (p - 1) / 2, for G2 decided on y.c1 unless it is zero, then y.c0
+//                       (algebra/.../processing/curve_element.hpp:93-174, processing/detail/curve_element.hpp:46-92)
+//   proof               g_A | g_B | g_C compressed = 192 B   (zk/.../r1cs_gg_ppzksnark/proof.hpp:63-71)
+//   primary input       count | Fr...;  encrypted primary input (cipher text) count | compressed G1...
+//                       (zk/.../r1cs_gg_ppzksnark/primary_input.hpp:61-97)
+//   fast proving key    alpha_g1 beta_g1 beta_g2 delta_g1 delta_g2 | A_query | B_query (indices, (g: G2, h: G1) pairs,
+//                       domain_size) | H_query | L_query | constraint system
+//                       (zk/.../r1cs_gg_ppzksnark/fast_proving_key.hpp:66-103, sparse_vector.hpp:103-115,
+//                        fast_knowledge_commitment.hpp:62-68, r1cs.hpp:57-113: linear term = index:size_t | coeff:Fr)
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../../include/vsp_b200.h"
+
+namespace {
+
+constexpr size_t FR_BYTES = 32, FQ_BYTES = 48, G1_FAST = 2 * FQ_BYTES + 1, G2_FAST = 4 * FQ_BYTES + 1;
+
+// (p - 1) / 2, little-endian 64-bit limbs
+const uint64_t HALF_P[6] = {0xdcff7fffffffd555ull, 0x0f55ffff58a9ffffull, 0xb39869507b587b12ull,
+                            0xb23ba5c279c2895full, 0x258dd3db21a5d66bull, 0x0d0088f51cbff34dull};
+
+// big-endian bytes <-> little-endian limbs
+void put_be(uint8_t* out, const uint64_t* limbs, size_t bytes) {
+    for (size_t k = 0; k < bytes; ++k) {
+        const size_t bit = 8 * (bytes - 1 - k);
+        out[k] = (uint8_t)(limbs[bit / 64] >> (bit % 64));
+    }
+}
+void get_be(const uint8_t* in, uint64_t* limbs, size_t bytes) {
+    for (size_t i = 0; i < bytes / 8; ++i) limbs[i] = 0;
+    for (size_t k = 0; k < bytes; ++k) {
+        const size_t bit = 8 * (bytes - 1 - k);
+        limbs[bit / 64] |= (uint64_t)in[k] << (bit % 64);
+    }
+}
+void put_u64(uint8_t* out, uint64_t v) { put_be(out, &v, 8); }
+uint64_t get_u64(const uint8_t* in) {
+    uint64_t v;
+    get_be(in, &v, 8);
+    return v;
+}
+bool is_zero(const uint64_t* x, int n) {
+    uint64_t a = 0;
+    for (int i = 0; i < n; ++i) a |= x[i];
+    return a == 0;
+}
+// y > (p - 1) / 2
+bool fq_is_high(const uint64_t* y) {
+    for (int i = 5; i >= 0; --i) {
+        if (y[i] > HALF_P[i]) return true;
+        if (y[i] < HALF_P[i]) return false;
+    }
+    return false;
+}
+
+void g1_compress(const uint64_t* p, uint8_t* out) {
+    if (is_zero(p, 12)) {
+        memset(out, 0, FQ_BYTES);
+        out[0] = 0x80 | 0x40;
+        return;
+    }
+    put_be(out, p, FQ_BYTES);
+    out[0] |= 0x80 | (fq_is_high(p + 6) ? 0x20 : 0);
+}
+void g2_compress(const uint64_t* p, uint8_t* out) {
+    if (is_zero(p, 24)) {
+        memset(out, 0, 2 * FQ_BYTES);
+        out[0] = 0x80 | 0x40;
+        return;
+    }
+    put_be(out, p + 6, FQ_BYTES);        // x.c1
+    put_be(out + FQ_BYTES, p, FQ_BYTES);  // x.c0
+    const uint64_t *y0 = p + 12, *y1 = p + 18;
+    const bool high = is_zero(y1, 6) ? fq_is_high(y0) : fq_is_high(y1);
+    out[0] |= 0x80 | (high ? 0x20 : 0);
+}
+
+// fast_curve_element: X | Y | is_infinity
+void fast_write(uint8_t* out, const uint64_t* p, int fq_count) {  // fq_count = 2 (G1) or 4 (G2)
+    const bool inf = is_zero(p, 6 * fq_count);
+    if (inf) {
+        // the zero point's affine form is (0, 1) in Jacobian conventions; readers ignore X, Y when the flag is set
+        memset(out, 0, FQ_BYTES * fq_count);
+        out[FQ_BYTES * (fq_count / 2) + FQ_BYTES - 1] = 1;
+    } else {
+        for (int i = 0; i < fq_count; ++i) put_be(out + FQ_BYTES * i, p + 6 * i, FQ_BYTES);
+    }
+    out[FQ_BYTES * fq_count] = inf ? 1 : 0;
+}
+void fast_read(const uint8_t* in, uint64_t* p, int fq_count) {
+    if (in[FQ_BYTES * fq_count]) {
+        memset(p, 0, 48 * fq_count);
+        return;
+    }
+    for (int i = 0; i < fq_count; ++i) get_be(in + FQ_BYTES * i, p + 6 * i, FQ_BYTES);
+}
+
+struct Reader {
+    const uint8_t* p;
+    size_t left;
+    bool ok = true;
+    const uint8_t* take(size_t n) {
+        if (!ok || left < n) {
+            ok = false;
+            return nullptr;
+        }
+        const uint8_t* r = p;
+        p += n;
+        left -= n;
+        return r;
+    }
+    uint64_t u64() {
+        const uint8_t* q = take(8);
+        return q ? get_u64(q) : 0;
+    }
+};
+
+}  // namespace
+
+extern "C" {
+
+int vsp_codec_g1_compress(const uint64_t* point, uint8_t* out48) {
+    if (!point || !out48) return VSP_E_INVALID;
+    g1_compress(point, out48);
+    return VSP_OK;
+}
+int vsp_codec_g2_compress(const uint64_t* point, uint8_t* out96) {
+    if (!point || !out96) return VSP_E_INVALID;
+    g2_compress(point, out96);
+    return VSP_OK;
+}
+// proof (g_A | g_B | g_C as 48 limbs) -> 192 bytes
+int vsp_codec_proof_write(const uint64_t* proof, uint8_t* out192) {
+    if (!proof || !out192) return VSP_E_INVALID;
+    g1_compress(proof, out192);
+    g2_compress(proof + 12, out192 + 48);
+    g1_compress(proof + 36, out192 + 144);
+    return VSP_OK;
+}
+// cipher text of n G1 points -> 8 + 48 n bytes
+int vsp_codec_ciphertext_write(const uint64_t* ct, uint64_t n, uint8_t* out) {
+    if ((!ct && n) || !out) return VSP_E_INVALID;
+    put_u64(out, n);
+    for (uint64_t i = 0; i < n; ++i) g1_compress(ct + 12 * i, out + 8 + 48 * i);
+    return VSP_OK;
+}
+// n Fr -> 8 + 32 n bytes
+int vsp_codec_primary_input_write(const uint64_t* values, uint64_t n, uint8_t* out) {
+    if ((!values && n) || !out) return VSP_E_INVALID;
+    put_u64(out, n);
+    for (uint64_t i = 0; i < n; ++i) put_be(out + 8 + FR_BYTES * i, values + 4 * i, FR_BYTES);
+    return VSP_OK;
+}
+// 8 + 32 n bytes -> n Fr; *n receives the count; values may be NULL to query it; capacity in elements
+int vsp_codec_primary_input_read(const uint8_t* in, size_t len, uint64_t* n, uint64_t* values, uint64_t capacity) {
+    if (!in || !n || len < 8) return VSP_E_INVALID;
+    const uint64_t cnt = get_u64(in);
+    if (cnt > (len - 8) / FR_BYTES) return VSP_E_INVALID;
+    *n = cnt;
+    if (!values) return VSP_OK;
+    if (capacity < cnt) return VSP_E_INVALID;
+    for (uint64_t i = 0; i < cnt; ++i) get_be(in + 8 + FR_BYTES * i, values + 4 * i, FR_BYTES);
+    return VSP_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fast proving key  (r1cs_proving_key.bin as bin/cli reads it: common.hpp:1004-1006)
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+// walks one linear combination; with cols/vals non-null also stores it at position *pos
+bool walk_lc(Reader& r, uint64_t* nnz, uint32_t* cols, uint64_t* vals, uint64_t n_vars) {
+    const uint64_t terms = r.u64();
+    if (!r.ok || terms > r.left / (8 + FR_BYTES)) return r.ok = false;
+    for (uint64_t t = 0; t < terms; ++t) {
+        const uint64_t idx = r.u64();
+        const uint8_t* c = r.take(FR_BYTES);
+        if (!c) return false;
+        if (cols) {
+            if (idx > n_vars) return r.ok = false;
+            cols[*nnz] = (uint32_t)idx;
+            get_be(c, vals + 4 * *nnz, FR_BYTES);
+        }
+        ++*nnz;
+    }
+    return true;
+}
+
+// one pass over the blob: sizes only (desc == nullptr) or fill the caller's arrays
+int fast_pk_walk(const uint8_t* blob, size_t len, vsp_fast_pk_sizes_t* sz, vsp_proving_key_t* d) {
+    Reader r {blob, len};
+    auto g1 = [&](const uint64_t* dst) {
+        const uint8_t* q = r.take(G1_FAST);
+        if (q && dst) fast_read(q, const_cast<uint64_t*>(dst), 2);
+    };
+    auto g2 = [&](const uint64_t* dst) {
+        const uint8_t* q = r.take(G2_FAST);
+        if (q && dst) fast_read(q, const_cast<uint64_t*>(dst), 4);
+    };
+    auto g1_list = [&](const uint64_t* dst, uint64_t* count) {
+        const uint64_t n = r.u64();
+        if (!r.ok || n > r.left / G1_FAST) {
+            r.ok = false;
+            return;
+        }
+        *count = n;
+        for (uint64_t i = 0; i < n; ++i) g1(dst ? dst + 12 * i : nullptr);
+    };
+    g1(d ? d->alpha_g1 : nullptr);
+    g1(d ? d->beta_g1 : nullptr);
+    g2(d ? d->beta_g2 : nullptr);
+    g1(d ? d->delta_g1 : nullptr);
+    g2(d ? d->delta_g2 : nullptr);
+    vsp_fast_pk_sizes_t s;
+    memset(&s, 0, sizeof(s));
+    g1_list(d ? d->A_query : nullptr, &s.A_count);
+    // B_query: indices | (g: G2, h: G1) pairs | domain_size
+    const uint64_t n_idx = r.u64();
+    if (!r.ok || n_idx > r.left / 8) return VSP_E_INVALID;
+    for (uint64_t i = 0; i < n_idx; ++i) {
+        const uint64_t v = r.u64();
+        if (d) {
+            if (v > 0xffffffffull) return VSP_E_INVALID;
+            const_cast<uint32_t*>(d->B_idx)[i] = (uint32_t)v;
+        }
+    }
+    const uint64_t n_val = r.u64();
+    if (!r.ok || n_val != n_idx || n_val > r.left / (G1_FAST + G2_FAST)) return VSP_E_INVALID;
+    for (uint64_t i = 0; i < n_val; ++i) {
+        g2(d ? d->B_g2 + 24 * i : nullptr);
+        g1(d ? d->B_g1 + 12 * i : nullptr);
+    }
+    s.B_count = n_val;
+    s.B_domain_size = r.u64();
+    g1_list(d ? d->H_query : nullptr, &s.H_count);
+    g1_list(d ? d->L_query : nullptr, &s.L_count);
+    // constraint system: primary_input_size | auxiliary_input_size | constraints
+    s.num_inputs = r.u64();
+    s.num_aux = r.u64();
+    s.num_constraints = r.u64();
+    if (!r.ok || s.num_constraints > r.left / 24) return VSP_E_INVALID;
+    const uint64_t n_vars = s.num_inputs + s.num_aux;
+    uint64_t nnz[3] = {0, 0, 0};
+    for (uint64_t i = 0; i < s.num_constraints; ++i) {
+        for (int k = 0; k < 3; ++k) {
+            uint64_t* row = nullptr;
+            uint32_t* col = nullptr;
+            uint64_t* val = nullptr;
+            if (d) {
+                row = const_cast<uint64_t*>(k == 0 ? d->cs.a_row : k == 1 ? d->cs.b_row : d->cs.c_row);
+                col = const_cast<uint32_t*>(k == 0 ? d->cs.a_col : k == 1 ? d->cs.b_col : d->cs.c_col);
+                val = const_cast<uint64_t*>(k == 0 ? d->cs.a_val : k == 1 ? d->cs.b_val : d->cs.c_val);
+                row[i] = nnz[k];
+            }
+            if (!walk_lc(r, &nnz[k], col, val, n_vars)) return VSP_E_INVALID;
+            if (d) row[i + 1] = nnz[k];
+        }
+    }
+    if (!r.ok) return VSP_E_INVALID;
+    s.nnz_a = nnz[0];
+    s.nnz_b = nnz[1];
+    s.nnz_c = nnz[2];
+    s.bytes = len - r.left;
+    if (d) {
+        if (s.num_constraints == 0) {
+            const_cast<uint64_t*>(d->cs.a_row)[0] = const_cast<uint64_t*>(d->cs.b_row)[0] = 0;
+            const_cast<uint64_t*>(d->cs.c_row)[0] = 0;
+        }
+        d->cs.num_inputs = s.num_inputs;
+        d->cs.num_aux = s.num_aux;
+        d->cs.num_constraints = s.num_constraints;
+        d->B_count = s.B_count;
+        d->H_count = s.H_count;
+    }
+    if (sz) *sz = s;
+    return VSP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int vsp_codec_fast_pk_sizes(const uint8_t* blob, size_t len, vsp_fast_pk_sizes_t* out) {
+    if (!blob || !out) return VSP_E_INVALID;
+    return fast_pk_walk(blob, len, out, nullptr);
+}
+
+// desc's array pointers must address caller-allocated writable memory of the sizes vsp_codec_fast_pk_sizes reported
+// (rows: num_constraints + 1; cols / vals: nnz; A_query: A_count G1; B_*: B_count; H_query: H_count; L_query: L_count);
+// the scalar fields of desc are filled in
+int vsp_codec_fast_pk_read(const uint8_t* blob, size_t len, vsp_proving_key_t* desc) {
+    if (!blob || !desc) return VSP_E_INVALID;
+    return fast_pk_walk(blob, len, nullptr, desc);
+}
+
+// serialised size of a key / write it (the inverse of vsp_codec_fast_pk_read); A_query holds num_inputs + num_aux + 1
+// points, L_query num_aux, H_query H_count; B's domain_size is written as num_inputs + num_aux + 1
+int vsp_codec_fast_pk_write(const vsp_proving_key_t* d, uint8_t* out, size_t capacity, size_t* written) {
+    if (!d || !written) return VSP_E_INVALID;
+    const uint64_t nv1 = d->cs.num_inputs + d->cs.num_aux + 1, nc = d->cs.num_constraints;
+    const uint64_t nnz = d->cs.a_row[nc] + d->cs.b_row[nc] + d->cs.c_row[nc];
+    const size_t need = 3 * G1_FAST + 2 * G2_FAST + 8 + nv1 * G1_FAST + 8 + d->B_count * 8 + 8 +
+                        d->B_count * (G1_FAST + G2_FAST) + 8 + 8 + d->H_count * G1_FAST + 8 + d->cs.num_aux * G1_FAST +
+                        24 + nc * 24 + nnz * (8 + FR_BYTES);
+    *written = need;
+    if (!out) return VSP_OK;
+    if (capacity < need) return VSP_E_INVALID;
+    uint8_t* p = out;
+    auto g1 = [&](const uint64_t* src) { fast_write(p, src, 2); p += G1_FAST; };
+    auto g2 = [&](const uint64_t* src) { fast_write(p, src, 4); p += G2_FAST; };
+    auto u64 = [&](uint64_t v) { put_u64(p, v); p += 8; };
+    g1(d->alpha_g1);
+    g1(d->beta_g1);
+    g2(d->beta_g2);
+    g1(d->delta_g1);
+    g2(d->delta_g2);
+    u64(nv1);
+    for (uint64_t i = 0; i < nv1; ++i) g1(d->A_query + 12 * i);
+    u64(d->B_count);
+    for (uint64_t i = 0; i < d->B_count; ++i) u64(d->B_idx[i]);
+    u64(d->B_count);
+    for (uint64_t i = 0; i < d->B_count; ++i) {
+        g2(d->B_g2 + 24 * i);
+        g1(d->B_g1 + 12 * i);
+    }
+    u64(nv1);
+    u64(d->H_count);
+    for (uint64_t i = 0; i < d->H_count; ++i) g1(d->H_query + 12 * i);
+    u64(d->cs.num_aux);
+    for (uint64_t i = 0; i < d->cs.num_aux; ++i) g1(d->L_query + 12 * i);
+    u64(d->cs.num_inputs);
+    u64(d->cs.num_aux);
+    u64(nc);
+    const uint64_t* rows[3] = {d->cs.a_row, d->cs.b_row, d->cs.c_row};
+    const uint32_t* cols[3] = {d->cs.a_col, d->cs.b_col, d->cs.c_col};
+    const uint64_t* vals[3] = {d->cs.a_val, d->cs.b_val, d->cs.c_val};
+    for (uint64_t i = 0; i < nc; ++i)
+        for (int k = 0; k < 3; ++k) {
+            u64(rows[k][i + 1] - rows[k][i]);
+            for (uint64_t q = rows[k][i]; q < rows[k][i + 1]; ++q) {
+                u64(cols[k][q]);
+                put_be(p, vals[k] + 4 * q, FR_BYTES);
+                p += FR_BYTES;
+            }
+        }
+    return (size_t)(p - out) == need ? VSP_OK : VSP_E_INVALID;
+}
+
+}  // extern "C"
