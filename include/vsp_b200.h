@@ -228,6 +228,53 @@ VSP_API int vsp_saver_encrypt_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, const vs
 VSP_API int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
                           const uint64_t *ct_in, const uint64_t *proof_in, uint64_t *ct_out, uint64_t *proof_out);
 
+/* ---- key generation: the callers that produce the keys the path consumes ------------------ */
+/* zk::generate<r1cs_gg_ppzksnark<bls12<381>, ..., proving_mode::encrypted_input>>(constraint_system)
+ *     call site bin/cli/include/nil/vote_saver/common.hpp:916-917 (generator source in un-vendored crypto3-zk @ d335bb8b).
+ * toxic = t | alpha | beta | gamma | delta (5 canonical Fr; the reference draws them inside generate — explicit here so
+ * the key pair is reproducible bit for bit).  Every array of `out` is caller-allocated:
+ *   A_query (n_v + 1) G1; B_idx / B_g2 / B_g1 capacity n_v + 1 (B_count is written: the sparse B_query's non-zero
+ *   entries); H_query (m - 1) G1, m from vsp_domain_plan(num_constraints + num_inputs + 1); L_query num_aux G1;
+ *   gamma_ABC_g1 (num_inputs + 1) G1 = first | rest; the rest single points.  gamma_g1 / delta_g1 are the
+ *   encrypted_input-mode verification-key extras SAVER key generation reads (elgamal_verifiable.hpp:233, 250-260).
+ * The filled proving-key half maps field for field onto vsp_proving_key_t / vsp_pk_load. */
+typedef struct {
+    uint64_t *alpha_g1, *beta_g1, *beta_g2, *delta_g1, *delta_g2;
+    uint64_t *A_query;
+    uint64_t B_count; /* out */
+    uint32_t *B_idx;
+    uint64_t *B_g2, *B_g1;
+    uint64_t H_count; /* out: m - 1 */
+    uint64_t *H_query;
+    uint64_t *L_query;
+    uint64_t *gamma_g2, *gamma_g1, *gamma_ABC_g1;
+} vsp_keypair_t;
+VSP_API int vsp_groth16_generate(vsp_ctx *ctx, const vsp_r1cs_t *cs, const uint64_t *toxic, vsp_keypair_t *out);
+
+/* generate_keypair_op<elgamal_verifiable<Curve>>::process (elgamal_verifiable.hpp:218-271).
+ * rnd = rho | t_0 | (s_i, v_i, t_i) for i < msg_size: 3 msg_size + 2 canonical Fr, consumed in the reference's order.
+ * Public key = (delta_g1 [the caller's], delta_s_g1, t_g1, t_g2, delta_sum_s_g1, gamma_inverse_sum_s_g1),
+ * secret key = rho, verification key = (rho_g2, rho_sv_g2, rho_rhov_g2); all arrays caller-allocated. */
+typedef struct {
+    uint64_t *delta_s_g1;             /* msg_size G1 */
+    uint64_t *t_g1;                   /* msg_size G1 */
+    uint64_t *t_g2;                   /* msg_size + 1 G2 */
+    uint64_t *delta_sum_s_g1;         /* 1 G1 */
+    uint64_t *gamma_inverse_sum_s_g1; /* 1 G1 */
+    uint64_t *rho_g2;                 /* 1 G2 */
+    uint64_t *rho_sv_g2;              /* msg_size G2 */
+    uint64_t *rho_rhov_g2;            /* msg_size G2 */
+    uint64_t *rho;                    /* 4 limbs */
+} vsp_saver_keypair_t;
+VSP_API int vsp_saver_keygen(vsp_ctx *ctx, uint64_t msg_size, const uint64_t *delta_g1, const uint64_t *gamma_g1,
+                             const uint64_t *gamma_abc_rest, const uint64_t *rnd, vsp_saver_keypair_t *out);
+
+/* building blocks: out[i] = scalars[i] * points[i] (variable base), and fixed-base multiples of the group generators
+ * (`scalar * g1_type::value_type::one()`, e.g. elgamal_verifiable.hpp:233-249) from an 8-bit table, one thread per scalar */
+VSP_API int vsp_g1_mul_batch(vsp_ctx *ctx, uint64_t n, const uint64_t *points, const uint64_t *scalars, uint64_t *out);
+VSP_API int vsp_g1_generator_mul_batch(vsp_ctx *ctx, uint64_t n, const uint64_t *scalars, uint64_t *out);
+VSP_API int vsp_g2_generator_mul_batch(vsp_ctx *ctx, uint64_t n, const uint64_t *scalars, uint64_t *out);
+
 /* ---- wire codecs: the reference's byte formats either side of the path (host only, no GPU work) ------------- */
 /* Formats (relative to libs/marshalling): big-endian fixed-width integers (Fr 32 B, Fq 48 B, size_t 8 B), sequences
  * with an 8-byte count prefix; compressed points as processing/curve_element.hpp:93-174 writes them (G1 48 B,

@@ -825,9 +825,10 @@ class VerificationKey:
     gamma_ABC_rest: list
 
 
-def groth16_generate(cs: R1CS, rng: random.Random):
-    """r1cs_gg_ppzksnark_generator  [UPSTREAM-RECALL] — self-consistency gate only."""
-    t, alpha, beta, gamma, delta = (rng.randrange(1, R) for _ in range(5))
+def groth16_generate(cs: R1CS, rng: random.Random, toxic=None):
+    """r1cs_gg_ppzksnark_generator  [UPSTREAM-RECALL] — self-consistency gate only.  toxic = (t, alpha, beta, gamma,
+    delta) overrides the draw from rng."""
+    t, alpha, beta, gamma, delta = toxic if toxic is not None else (rng.randrange(1, R) for _ in range(5))
     domain = make_evaluation_domain(cs.num_constraints + cs.num_inputs + 1)
     m = domain.m
     u = domain.evaluate_all_lagrange_polynomials(t)

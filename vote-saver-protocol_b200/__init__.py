@@ -10,6 +10,8 @@ Reference interfaces mirrored (paths relative to NilFoundation/vote-saver-protoc
   prove(pk, primary, auxiliary, r, s[, pubkey, r_saver])
         zk::prove<r1cs_gg_ppzksnark<..., encrypted_input>>  call site libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp:353
   encrypt / rerandomize                         elgamal_verifiable.hpp:322-357, 632-667
+  generate(cs, toxic)                           zk::generate<...>  call site bin/cli/include/nil/vote_saver/common.hpp:916-917
+  saver_generate_keypair(vk, msg_size, rnd)     generate_keypair_op::process, elgamal_verifiable.hpp:218-271
 
 Data: numpy uint64 arrays of canonical little-endian limbs — Fr (n, 4); G1 affine (n, 12); G2 affine (n, 24);
 the point at infinity is all-zero.  Error behaviour follows the reference: what throws std::invalid_argument there
@@ -22,11 +24,12 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2, PkSliceDesc, ProvingKeyDesc, R1CSDesc,
-                   SaverPubkeyDesc, VspError)
+from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2, KeypairDesc, PkSliceDesc,
+                   ProvingKeyDesc, R1CSDesc, SaverKeypairDesc, SaverPubkeyDesc, VspError)
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
-           "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path"]
+           "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path",
+           "generate", "saver_generate_keypair", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
 
 FR_MULTIPLICATIVE_GENERATOR = 7
 
@@ -456,3 +459,86 @@ def rerandomize(ctx: Context, pubkey: SaverPublicKey, delta_g2, rnd, ct, proof):
     ctx.check(ctx._lib.vsp_saver_rerandomize(ctx._h, C.byref(pubkey.desc), _p(d2), _p(q), _p(c), _p(pr), _p(ct_out),
                                              _p(proof_out)))
     return ct_out, proof_out
+
+
+# ---- key generation --------------------------------------------------------------
+def g1_mul_batch(ctx: Context, points, scalars) -> np.ndarray:
+    """out[i] = scalars[i] * points[i] (variable base)"""
+    p, sc = _a(points, 12), _a(scalars, 4)
+    if p.shape[0] != sc.shape[0]:
+        raise ValueError("points / scalars length mismatch")
+    out = np.zeros((p.shape[0], 12), dtype=np.uint64)
+    ctx.check(ctx._lib.vsp_g1_mul_batch(ctx._h, p.shape[0], _p(p), _p(sc), _p(out)))
+    return out
+
+
+def g1_generator_mul_batch(ctx: Context, scalars) -> np.ndarray:
+    """out[i] = scalars[i] * G1::one()"""
+    sc = _a(scalars, 4)
+    out = np.zeros((sc.shape[0], 12), dtype=np.uint64)
+    ctx.check(ctx._lib.vsp_g1_generator_mul_batch(ctx._h, sc.shape[0], _p(sc), _p(out)))
+    return out
+
+
+def g2_generator_mul_batch(ctx: Context, scalars) -> np.ndarray:
+    """out[i] = scalars[i] * G2::one()"""
+    sc = _a(scalars, 4)
+    out = np.zeros((sc.shape[0], 24), dtype=np.uint64)
+    ctx.check(ctx._lib.vsp_g2_generator_mul_batch(ctx._h, sc.shape[0], _p(sc), _p(out)))
+    return out
+
+
+def generate(ctx: Context, cs: dict, toxic):
+    """zk::generate<r1cs_gg_ppzksnark<..., encrypted_input>>(constraint_system) with the generator's randomness
+    toxic = (t, alpha, beta, gamma, delta) passed in.  `cs`: the R1CS arrays dict (vsp_r1cs_t field names).
+    Returns (pk_arrays, vk_arrays): pk_arrays goes straight into ProvingKey(ctx, pk_arrays); vk_arrays holds
+    alpha_g1, beta_g2, gamma_g2, delta_g2, gamma_g1, delta_g1, gamma_ABC_g1 (first | rest)."""
+    ni, na, nc = int(cs["num_inputs"]), int(cs["num_aux"]), int(cs["num_constraints"])
+    nvp1 = ni + na + 1
+    _kind, m = domain_plan(nc + ni + 1)
+    tox = np.concatenate([_fr(int(x)) for x in toxic])
+    if tox.shape[0] != 20:
+        raise ValueError("toxic = (t, alpha, beta, gamma, delta)")
+    z1, z2 = (lambda n: np.zeros((max(n, 1), 12), np.uint64)), (lambda n: np.zeros((max(n, 1), 24), np.uint64))
+    arr = {"alpha_g1": z1(1), "beta_g1": z1(1), "beta_g2": z2(1), "delta_g1": z1(1), "delta_g2": z2(1),
+           "A_query": z1(nvp1), "B_count": 0, "B_idx": np.zeros(nvp1, np.uint32), "B_g2": z2(nvp1), "B_g1": z1(nvp1),
+           "H_count": 0, "H_query": z1(m - 1), "L_query": z1(na),
+           "gamma_g2": z2(1), "gamma_g1": z1(1), "gamma_ABC_g1": z1(ni + 1)}
+    desc = _fill(KeypairDesc(), arr)
+    csd = _fill(R1CSDesc(), cs)
+    ctx.check(ctx._lib.vsp_groth16_generate(ctx._h, C.byref(csd), _p(tox), C.byref(desc)))
+    nb = int(desc.B_count)
+    pk = {"cs": cs, "alpha_g1": arr["alpha_g1"], "beta_g1": arr["beta_g1"], "beta_g2": arr["beta_g2"],
+          "delta_g1": arr["delta_g1"], "delta_g2": arr["delta_g2"], "A_query": arr["A_query"], "B_count": nb,
+          "B_idx": np.ascontiguousarray(arr["B_idx"][:max(nb, 1)]), "B_g2": np.ascontiguousarray(arr["B_g2"][:max(nb, 1)]),
+          "B_g1": np.ascontiguousarray(arr["B_g1"][:max(nb, 1)]), "H_count": int(desc.H_count), "H_query": arr["H_query"],
+          "L_query": arr["L_query"]}
+    vk = {"alpha_g1": arr["alpha_g1"], "beta_g2": arr["beta_g2"], "gamma_g2": arr["gamma_g2"], "delta_g2": arr["delta_g2"],
+          "gamma_g1": arr["gamma_g1"], "delta_g1": arr["delta_g1"], "gamma_ABC_g1": arr["gamma_ABC_g1"]}
+    return pk, vk
+
+
+def saver_generate_keypair(ctx: Context, vk: dict, msg_size: int, rnd):
+    """generate_keypair_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:218-271): rnd = 3 msg_size + 2 scalars
+    (rho, t_0, then s_i, v_i, t_i).  Returns (public-key arrays for SaverPublicKey, rho, verification-key arrays)."""
+    n = int(msg_size)
+    rnd = [int(x) for x in rnd]
+    if len(rnd) < 3 * n + 2:
+        raise ValueError("Too few numbers in the source of randomness.")  # the reference's assertion text (:221)
+    r = np.concatenate([_fr(x) for x in rnd[:3 * n + 2]])
+    gabc = _a(vk["gamma_ABC_g1"], 12)
+    if gabc.shape[0] < n + 1:
+        raise ValueError("gamma_ABC_g1 shorter than msg_size + 1")
+    rest = np.ascontiguousarray(gabc[1:])
+    z1, z2 = (lambda k: np.zeros((max(k, 1), 12), np.uint64)), (lambda k: np.zeros((max(k, 1), 24), np.uint64))
+    arr = {"delta_s_g1": z1(n), "t_g1": z1(n), "t_g2": z2(n + 1), "delta_sum_s_g1": z1(1), "gamma_inverse_sum_s_g1": z1(1),
+           "rho_g2": z2(1), "rho_sv_g2": z2(n), "rho_rhov_g2": z2(n), "rho": np.zeros(4, np.uint64)}
+    desc = _fill(SaverKeypairDesc(), arr)
+    ctx.check(ctx._lib.vsp_saver_keygen(ctx._h, n, _p(_a(vk["delta_g1"], 12)), _p(_a(vk["gamma_g1"], 12)), _p(rest), _p(r),
+                                        C.byref(desc)))
+    pub = {"msg_size": n, "delta_g1": _a(vk["delta_g1"], 12).copy(), "delta_s_g1": arr["delta_s_g1"], "t_g1": arr["t_g1"],
+           "t_g2": arr["t_g2"], "delta_sum_s_g1": arr["delta_sum_s_g1"],
+           "gamma_inverse_sum_s_g1": arr["gamma_inverse_sum_s_g1"]}
+    svk = {"rho_g2": arr["rho_g2"], "rho_sv_g2": arr["rho_sv_g2"], "rho_rhov_g2": arr["rho_rhov_g2"]}
+    rho = int.from_bytes(arr["rho"].tobytes(), "little")
+    return pub, rho, svk

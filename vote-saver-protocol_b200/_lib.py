@@ -58,6 +58,20 @@ class SaverPubkeyDesc(C.Structure):
                 ("delta_sum_s_g1", u64p), ("gamma_inverse_sum_s_g1", u64p)]
 
 
+class KeypairDesc(C.Structure):
+    """vsp_keypair_t"""
+    _fields_ = [("alpha_g1", u64p), ("beta_g1", u64p), ("beta_g2", u64p), ("delta_g1", u64p), ("delta_g2", u64p),
+                ("A_query", u64p), ("B_count", C.c_uint64), ("B_idx", u32p), ("B_g2", u64p), ("B_g1", u64p),
+                ("H_count", C.c_uint64), ("H_query", u64p), ("L_query", u64p),
+                ("gamma_g2", u64p), ("gamma_g1", u64p), ("gamma_ABC_g1", u64p)]
+
+
+class SaverKeypairDesc(C.Structure):
+    """vsp_saver_keypair_t"""
+    _fields_ = [(n, u64p) for n in ("delta_s_g1", "t_g1", "t_g2", "delta_sum_s_g1", "gamma_inverse_sum_s_g1", "rho_g2",
+                                    "rho_sv_g2", "rho_rhov_g2", "rho")]
+
+
 # every symbol include/vsp_b200.h declares: (name, restype, argtypes)
 _vp = C.c_void_p
 _u64 = C.c_uint64
@@ -111,6 +125,11 @@ SYMBOLS = [
     ("vsp_saver_encrypt_batch", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_saver_encrypt_batch_dev", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_saver_rerandomize", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_groth16_generate", _int, [_vp, C.POINTER(R1CSDesc), _vp, C.POINTER(KeypairDesc)]),
+    ("vsp_saver_keygen", _int, [_vp, _u64, _vp, _vp, _vp, _vp, C.POINTER(SaverKeypairDesc)]),
+    ("vsp_g1_mul_batch", _int, [_vp, _u64, _vp, _vp, _vp]),
+    ("vsp_g1_generator_mul_batch", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_g2_generator_mul_batch", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_codec_g1_compress", _int, [_vp, _vp]),
     ("vsp_codec_g2_compress", _int, [_vp, _vp]),
     ("vsp_codec_proof_write", _int, [_vp, _vp]),

@@ -489,12 +489,12 @@ int multiply_by_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t n, const uint64
     return VSP_OK;
 }
 
-// table[i] = k * g^i, i < n, Montgomery form (k, g canonical)
+// table[i] = k * g^i, i < n (k, g canonical): Montgomery form, or canonical values with canonical_out
 int fill_power_table(vsp_ctx* ctx, cudaStream_t s, uint32_t* d_out, uint64_t n, const hostfr::Fr4& g,
-                     const hostfr::Fr4& k) {
+                     const hostfr::Fr4& k, bool canonical_out) {
     PowTable t = make_pow_table(g);
     Fr kk;
-    fr4_to_limbs(kk.l, hostfr::to_mont(k));
+    fr4_to_limbs(kk.l, canonical_out ? k : hostfr::to_mont(k));
     VSP_LAUNCH_K(ctx, KC_NTT, k_fill_powers, (unsigned)((n + 127) / 128), 128, 0, s, d_out, n, t, kk);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
@@ -547,6 +547,21 @@ __global__ void k_step_div_table(uint32_t* out, uint64_t n, PowTable elt_pows, F
         fp_store(out + 8 * (base + i), fp_mul(inv, prev));
         inv = fp_mul(inv, den[i]);
     }
+}
+
+// out[i] = 1 / (A * elt^i - B), i < n, Montgomery form (A, B, elt canonical); a zero denominator poisons its chunk,
+// so callers rule that case out first (the generator does: t outside the domain)
+int inv_affine_table_dev(vsp_ctx* ctx, cudaStream_t s, uint32_t* d_out, uint64_t n, const hostfr::Fr4& elt,
+                         const hostfr::Fr4& A, const hostfr::Fr4& B) {
+    if (n == 0) return VSP_OK;
+    PowTable pt = make_pow_table(elt);
+    Fr a, b;
+    fr4_to_limbs(a.l, hostfr::to_mont(A));
+    fr4_to_limbs(b.l, hostfr::to_mont(B));
+    const uint64_t chunks = (n + STEP_INV_CHUNK - 1) / STEP_INV_CHUNK;
+    VSP_LAUNCH_K(ctx, KC_NTT, k_step_div_table, (unsigned)((chunks + 63) / 64), 64, 0, s, d_out, n, pt, a, b);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    return VSP_OK;
 }
 
 int divide_by_z_on_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, uint32_t* d) {

@@ -30,7 +30,7 @@
 namespace vsp {
 int domain_plan(uint64_t min_size, int* kind, uint64_t* m);
 int fill_power_table(vsp_ctx* ctx, cudaStream_t s, uint32_t* d_out, uint64_t n, const hostfr::Fr4& g,
-                     const hostfr::Fr4& k);
+                     const hostfr::Fr4& k, bool canonical_out = false);
 }  // namespace vsp
 
 using namespace vsp;
@@ -1078,6 +1078,21 @@ static int run_mul_jobs_g1(vsp_ctx* ctx, const std::vector<const uint64_t*>& pts
 }
 
 }  // namespace vsp
+
+extern "C" int vsp_g1_mul_batch(vsp_ctx* ctx, uint64_t n, const uint64_t* points, const uint64_t* scalars, uint64_t* out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (n == 0) return VSP_OK;
+    if (!points || !scalars || !out || n > (1u << 20)) return set_error(ctx, VSP_E_INVALID, "vsp_g1_mul_batch: bad argument");
+    cudaSetDevice(ctx->device);
+    std::vector<const uint64_t*> pts(n), scs(n);
+    std::vector<uint32_t> grp(n);
+    for (uint64_t i = 0; i < n; ++i) {
+        pts[i] = points + 12 * i;
+        scs[i] = scalars + 4 * i;
+        grp[i] = (uint32_t)i;
+    }
+    return run_mul_jobs_g1(ctx, pts, scs, grp, (unsigned)n, nullptr, out);
+}
 
 extern "C" int vsp_saver_ciphertext(vsp_ctx* ctx, const vsp_saver_pubkey_t* pub, const uint64_t* gamma_abc_rest,
                                     const uint64_t* msg, const uint64_t r_saver[4], uint64_t* out_ct) {
