@@ -259,6 +259,19 @@ def cpu_prover(args, cs_arrays, pk_arrays, prim, aux, rs, pub_arr, gabc, n_proof
     return time.perf_counter() - t0, np.stack(out), np.stack(cts), cores
 
 
+def oracle_verify(vk_arr, proof, primary) -> bool:
+    """the oracle's pairing check (r1cs_gg_ppzksnark verifier restated in oracle/pyref.py) on a proof the GPU made with a
+    key the GPU generated: e(A, B) = e(alpha, beta) e(sum x_i gamma_ABC_i, gamma) e(C, delta)"""
+    from oracle import cref, pyref as o
+    J1 = lambda a: [o.G1.from_affine(p) if p else o.G1.inf() for p in cref.g1_from_limbs(np.ascontiguousarray(a).reshape(-1, 12))]
+    J2 = lambda a: [o.G2.from_affine(p) if p else o.G2.inf() for p in cref.g2_from_limbs(np.ascontiguousarray(a).reshape(-1, 24))]
+    gabc = J1(vk_arr["gamma_ABC_g1"])
+    vk = o.VerificationKey(J1(vk_arr["alpha_g1"])[0], J2(vk_arr["beta_g2"])[0], J2(vk_arr["gamma_g2"])[0],
+                           J2(vk_arr["delta_g2"])[0], J1(vk_arr["gamma_g1"])[0], J1(vk_arr["delta_g1"])[0], gabc[0], gabc[1:])
+    pr = (J1(proof[:12])[0], J2(proof[12:36])[0], J1(proof[36:])[0])
+    return bool(o.groth16_verify(vk, cref.limbs_to_ints(np.ascontiguousarray(primary)), pr))
+
+
 def cref_generator(group: str):
     from oracle import pyref as o
     return o.G1_GEN if group == "G1" else o.G2_GEN
@@ -387,6 +400,25 @@ def run_extras(res, peaks, p_int):
             lat.append((time.perf_counter() - t0) * 1e3)
         out["single_ballot_latency"] = {"ms_median": sorted(lat[2:])[len(lat[2:]) // 2], "ms_all": [round(x, 3) for x in lat],
                                         "what": "one ballot, host -> host, 2 warm-up calls dropped"}
+    # key generation for the bench circuit on the GPU, host arrays in and out; the key is then loaded and
+    # ballot 0 proved with it, so the cpu_baseline leg can put that proof through the oracle's pairing check
+    if "key" in res:
+        tox = [int.from_bytes(x.tobytes(), "little") | 1 for x in wl.random_fr(5, 77)]
+        gen_ms = []
+        for _ in range(2):
+            t0 = time.perf_counter()
+            pk_arr, vk_arr = vsp.generate(ctx, res["cs"], tox)
+            gen_ms.append((time.perf_counter() - t0) * 1e3)
+        nvp1 = res["cs"]["num_inputs"] + res["cs"]["num_aux"] + 1
+        out["groth16_generate"] = {"ms": min(gen_ms), "ms_all": [round(x, 1) for x in gen_ms],
+                                   "constraints": res["cs"]["num_constraints"],
+                                   "g1_elements": 3 * nvp1 + res["m"] - 1 + 4, "g2_elements": nvp1 + 3,
+                                   "what": "vsp_groth16_generate, host R1CS in, host key pair out (wall clock)"}
+        pk2 = vsp.ProvingKey(ctx, pk_arr)
+        r_, s_ = (int.from_bytes(x.tobytes(), "little") for x in res["rs"][0][:2])
+        res["generated"] = (vk_arr, pk2.prove(res["prim"][0], res["aux"][0], r_, s_), res["prim"][0])
+        pk2.close()
+        del pk_arr
     n = 1 << 20
     # NTT 2^20: 8 distinct 32 MiB vectors round-robin (256 MiB > 126 MiB L2) so no launch finds its input in L2
     bufs = [torch.from_numpy(wl.random_fr(n, 2 + i).view(np.int64)).cuda() for i in range(8)]
@@ -589,6 +621,8 @@ def main():
                                 "sample": "ballot 0 of the batch, proved once by oracle/vsp_oracle.c (%.1f s)" % sec,
                                 "gpu_proof_bit_exact": bool(np.array_equal(cpu_proofs[0], res["proofs"][0])),
                                 "gpu_ciphertext_bit_exact": bool(np.array_equal(cpu_cts[0], res["cts"][0]))}
+        if "generated" in res:
+            line["cpu_baseline"]["gpu_generated_key_proof_verifies"] = oracle_verify(*res["generated"])
     emit(line)
     if world > 1:
         import torch.distributed as dist

@@ -34,6 +34,8 @@
 #include <utility>
 #include <vector>
 
+#include <tuple>
+
 #include "vsp_b200.h"
 
 namespace nil {
@@ -392,7 +394,11 @@ namespace zk {
             std::vector<T> rest;
         };
         template<typename CurveType>
-        struct r1cs_gg_ppzksnark_verification_key {    // only the members the prover-side path reads
+        struct r1cs_gg_ppzksnark_verification_key {    // the extended (encrypted_input) key's group members; the GT element
+                                                       // alpha_g1_beta_g2 = e(alpha_g1, beta_g2) belongs to the pairing-side
+                                                       // verifier and is kept as its two preimages here
+            typename CurveType::template g1_type<>::value_type alpha_g1;
+            typename CurveType::template g2_type<>::value_type beta_g2;
             typename CurveType::template g2_type<>::value_type gamma_g2, delta_g2;
             typename CurveType::template g1_type<>::value_type delta_g1, gamma_g1;
             accumulation_vector<typename CurveType::template g1_type<>::value_type> gamma_ABC_g1;
@@ -452,6 +458,22 @@ namespace pubkey {
         }
     };
 
+    template<typename Scheme>
+    struct private_key;
+    template<typename CurveType, std::size_t BlockBits>
+    struct private_key<elgamal_verifiable<CurveType, BlockBits>> {    // elgamal_verifiable.hpp:131-139
+        typename CurveType::scalar_field_type::value_type rho;
+    };
+    template<typename Scheme>
+    struct verification_key;
+    template<typename CurveType, std::size_t BlockBits>
+    struct verification_key<elgamal_verifiable<CurveType, BlockBits>> {    // elgamal_verifiable.hpp:85-113
+        typedef elgamal_verifiable<CurveType, BlockBits> scheme_type;
+        typename scheme_type::g2_value_type rho_g2;
+        std::vector<typename scheme_type::g2_value_type> rho_sv_g2;
+        std::vector<typename scheme_type::g2_value_type> rho_rhov_g2;
+    };
+
     namespace modes {
         template<typename Scheme>
         struct verifiable_encryption {};
@@ -489,6 +511,97 @@ namespace zk {
             return eng;
         }
     }    // namespace detail
+
+    // generate<ProofSystem>(constraint_system) -> keypair   (bin/cli/include/nil/vote_saver/common.hpp:916-917).
+    // The reference draws t, alpha, beta, gamma, delta inside; the overload taking them makes key pairs reproducible.
+    struct generator_randomness {
+        b200::fr_value t, alpha, beta, gamma, delta;
+    };
+    template<typename ProofSystem>
+    typename ProofSystem::keypair_type
+        generate(const snark::r1cs_constraint_system<typename ProofSystem::curve_type::scalar_field_type> &cs,
+                 const generator_randomness &rnd) {
+        typedef typename ProofSystem::curve_type curve_type;
+        typedef typename curve_type::scalar_field_type field_type;
+        typedef typename curve_type::template g1_type<>::value_type g1;
+        typedef typename curve_type::template g2_type<>::value_type g2;
+        const std::size_t nc = cs.num_constraints(), nv = cs.num_variables(), ni = cs.primary_input_size;
+        std::vector<std::uint64_t> row[3], val[3];
+        std::vector<std::uint32_t> col[3];
+        for (int k = 0; k < 3; ++k) row[k].assign(nc + 1, 0);
+        for (std::size_t i = 0; i < nc; ++i) {
+            const std::vector<snark::linear_term<field_type>> *lc[3] = {&cs.constraints[i].a, &cs.constraints[i].b,
+                                                                        &cs.constraints[i].c};
+            for (int k = 0; k < 3; ++k) {
+                for (const auto &t : *lc[k]) {
+                    col[k].push_back(static_cast<std::uint32_t>(t.index));
+                    val[k].insert(val[k].end(), t.coeff.l.begin(), t.coeff.l.end());
+                }
+                row[k][i + 1] = col[k].size();
+            }
+        }
+        vsp_r1cs_t d;
+        std::memset(&d, 0, sizeof(d));
+        d.num_inputs = ni;
+        d.num_aux = cs.auxiliary_input_size;
+        d.num_constraints = nc;
+        d.a_row = row[0].data(); d.b_row = row[1].data(); d.c_row = row[2].data();
+        d.a_col = col[0].data(); d.b_col = col[1].data(); d.c_col = col[2].data();
+        d.a_val = val[0].data(); d.b_val = val[1].data(); d.c_val = val[2].data();
+        int kind = 0;
+        std::uint64_t m = 0;
+        if (vsp_domain_plan(nc + ni + 1, &kind, &m) != VSP_OK)
+            throw std::invalid_argument("generate: no evaluation domain for this constraint system");
+        typename ProofSystem::keypair_type kp;
+        auto &pk = kp.first;
+        auto &vk = kp.second;
+        pk.A_query.resize(nv + 1);
+        pk.H_query.resize(m - 1);
+        pk.L_query.resize(cs.auxiliary_input_size);
+        std::vector<g1> b_g1(nv + 1), gabc(ni + 1);
+        std::vector<g2> b_g2(nv + 1);
+        std::vector<std::uint32_t> b_idx(nv + 1);
+        g1 scratch_g1;
+        vsp_keypair_t out;
+        std::memset(&out, 0, sizeof(out));
+        out.alpha_g1 = pk.alpha_g1.l.data(); out.beta_g1 = pk.beta_g1.l.data(); out.beta_g2 = pk.beta_g2.l.data();
+        out.delta_g1 = pk.delta_g1.l.data(); out.delta_g2 = pk.delta_g2.l.data();
+        out.A_query = pk.A_query[0].l.data();
+        out.B_idx = b_idx.data(); out.B_g2 = b_g2[0].l.data(); out.B_g1 = b_g1[0].l.data();
+        out.H_query = pk.H_query.empty() ? scratch_g1.l.data() : pk.H_query[0].l.data();
+        out.L_query = pk.L_query.empty() ? nullptr : pk.L_query[0].l.data();
+        out.gamma_g2 = vk.gamma_g2.l.data(); out.gamma_g1 = vk.gamma_g1.l.data();
+        out.gamma_ABC_g1 = gabc[0].l.data();
+        const std::uint64_t toxic[20] = {rnd.t.l[0], rnd.t.l[1], rnd.t.l[2], rnd.t.l[3],
+                                         rnd.alpha.l[0], rnd.alpha.l[1], rnd.alpha.l[2], rnd.alpha.l[3],
+                                         rnd.beta.l[0], rnd.beta.l[1], rnd.beta.l[2], rnd.beta.l[3],
+                                         rnd.gamma.l[0], rnd.gamma.l[1], rnd.gamma.l[2], rnd.gamma.l[3],
+                                         rnd.delta.l[0], rnd.delta.l[1], rnd.delta.l[2], rnd.delta.l[3]};
+        auto &dev = b200::device::instance();
+        dev.check(vsp_groth16_generate(dev.ctx(), &d, toxic, &out), "generate");
+        for (std::uint64_t i = 0; i < out.B_count; ++i) {
+            pk.B_query.indices.push_back(b_idx[i]);
+            pk.B_query.values.push_back({b_g2[i], b_g1[i]});
+        }
+        pk.constraint_system = cs;
+        vk.alpha_g1 = pk.alpha_g1;
+        vk.beta_g2 = pk.beta_g2;
+        vk.delta_g2 = pk.delta_g2;
+        vk.delta_g1 = pk.delta_g1;
+        vk.gamma_ABC_g1.first = gabc[0];
+        vk.gamma_ABC_g1.rest.assign(gabc.begin() + 1, gabc.end());
+        return kp;
+    }
+    template<typename ProofSystem>
+    typename ProofSystem::keypair_type
+        generate(const snark::r1cs_constraint_system<typename ProofSystem::curve_type::scalar_field_type> &cs) {
+        auto &e = detail::blinding_engine();
+        generator_randomness rnd;
+        for (b200::fr_value *x : {&rnd.t, &rnd.alpha, &rnd.beta, &rnd.gamma, &rnd.delta})
+            do *x = b200::random_fr(e);
+            while (x->is_zero());
+        return generate<ProofSystem>(cs, rnd);
+    }
 
     // basic mode: prove<ProofSystem>(pk, primary, auxiliary)  (libs/marshalling/zk/test/r1cs_gg_ppzksnark.cpp:84).
     // The reference draws Groth16's blinding scalars r, s inside; the overloads with explicit (r, s) make proofs
@@ -534,6 +647,51 @@ namespace zk {
 // pubkey::encrypt / pubkey::rerandomize for elgamal_verifiable
 // =====================================================================================================================
 namespace pubkey {
+    template<typename Scheme>
+    struct generate_keypair_init_params {    // generate_keypair_op::init_params_type, elgamal_verifiable.hpp:189-192
+        const typename Scheme::proof_system_type::keypair_type &gg_keypair;
+        std::size_t msg_size;
+    };
+    // generate_keypair<Scheme, modes::verifiable_encryption<Scheme>>(rnd, {gg_keypair, msg_size})
+    //   -> (public key, private key, verification key)     generate_keypair_op::process, elgamal_verifiable.hpp:218-271
+    // as bin/cli/include/nil/vote_saver/common.hpp:928-931 calls it
+    template<typename Scheme, typename Mode, typename RandomRange>
+    std::tuple<public_key<Scheme>, private_key<Scheme>, verification_key<Scheme>>
+        generate_keypair(const RandomRange &rnd, const generate_keypair_init_params<Scheme> &p) {
+        typedef typename Scheme::scalar_field_type::value_type fr;
+        const std::vector<fr> rr(std::begin(rnd), std::end(rnd));
+        const auto &vk = p.gg_keypair.second;
+        const std::size_t n = p.msg_size;
+        // the reference's BOOST_ASSERT_MSG checks, elgamal_verifiable.hpp:199-201, 220-221
+        if (!(vk.gamma_ABC_g1.rest.size() > n))
+            throw std::invalid_argument("Array of gammas in vk should be longer than the message.");
+        if (rr.size() < 3 * n + 2) throw std::invalid_argument("Too few numbers in the source of randomness.");
+        std::tuple<public_key<Scheme>, private_key<Scheme>, verification_key<Scheme>> out;
+        auto &pub = std::get<0>(out);
+        auto &svk = std::get<2>(out);
+        pub.delta_g1 = vk.delta_g1;
+        pub.delta_s_g1.resize(n);
+        pub.t_g1.resize(n);
+        pub.t_g2.resize(n + 1);
+        svk.rho_sv_g2.resize(n);
+        svk.rho_rhov_g2.resize(n);
+        vsp_saver_keypair_t d;
+        d.delta_s_g1 = n ? pub.delta_s_g1[0].l.data() : nullptr;
+        d.t_g1 = n ? pub.t_g1[0].l.data() : nullptr;
+        d.t_g2 = pub.t_g2[0].l.data();
+        d.delta_sum_s_g1 = pub.delta_sum_s_g1.l.data();
+        d.gamma_inverse_sum_s_g1 = pub.gamma_inverse_sum_s_g1.l.data();
+        d.rho_g2 = svk.rho_g2.l.data();
+        d.rho_sv_g2 = n ? svk.rho_sv_g2[0].l.data() : nullptr;
+        d.rho_rhov_g2 = n ? svk.rho_rhov_g2[0].l.data() : nullptr;
+        d.rho = std::get<1>(out).rho.l.data();
+        auto &dev = b200::device::instance();
+        dev.check(vsp_saver_keygen(dev.ctx(), n, vk.delta_g1.l.data(), vk.gamma_g1.l.data(), vk.gamma_ABC_g1.rest[0].l.data(),
+                                   rr[0].l.data(), &d),
+                  "generate_keypair");
+        return out;
+    }
+
     template<typename Scheme>
     struct encrypt_init_params {    // encrypt_op::init_params_type, elgamal_verifiable.hpp:283-290
         typename Scheme::scalar_field_type::value_type r;

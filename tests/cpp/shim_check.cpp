@@ -192,6 +192,64 @@ int main(int argc, char **argv) {
                 },
                 "encrypt: plain text not a prefix of primary input throws");
         }
+        // ---- zk::generate / pubkey::generate_keypair, as common.hpp:916-931 calls them ------------------------------------------
+        if (F.count("kg_num_constraints")) {
+            zk::snark::r1cs_constraint_system<fr_type> cs;
+            cs.primary_input_size = F.at("kg_num_inputs")[0];
+            cs.auxiliary_input_size = F.at("kg_num_aux")[0];
+            const std::size_t nc = F.at("kg_num_constraints")[0];
+            cs.constraints.resize(nc);
+            const char *mn[3] = {"a", "b", "c"};
+            for (int k = 0; k < 3; ++k) {
+                const auto &row = F.at(std::string("kg_") + mn[k] + "_row"), &col = F.at(std::string("kg_") + mn[k] + "_col");
+                auto val = vec<fr>(std::string("kg_") + mn[k] + "_val");
+                for (std::size_t i = 0; i < nc; ++i)
+                    for (std::uint64_t q = row[i]; q < row[i + 1]; ++q) {
+                        zk::snark::linear_term<fr_type> t {static_cast<std::size_t>(col[q]), val[q]};
+                        (k == 0 ? cs.constraints[i].a : k == 1 ? cs.constraints[i].b : cs.constraints[i].c).push_back(t);
+                    }
+            }
+            auto tox = vec<fr>("kg_toxic");
+            auto kp = zk::generate<proof_system_type>(cs, {tox[0], tox[1], tox[2], tox[3], tox[4]});
+            expect(kp.first.alpha_g1 == one<g1>("kg_alpha_g1") && kp.first.beta_g1 == one<g1>("kg_beta_g1") &&
+                       kp.first.beta_g2 == one<g2>("kg_beta_g2") && kp.first.delta_g1 == one<g1>("kg_delta_g1") &&
+                       kp.first.delta_g2 == one<g2>("kg_delta_g2"),
+                   "zk::generate alpha / beta / delta");
+            expect(kp.first.A_query == vec<g1>("kg_A_query"), "zk::generate A_query");
+            expect(kp.first.H_query == vec<g1>("kg_H_query"), "zk::generate H_query");
+            expect(kp.first.L_query == vec<g1>("kg_L_query"), "zk::generate L_query");
+            bool b_ok = kp.first.B_query.indices.size() == F.at("kg_B_count")[0];
+            auto bg1 = vec<g1>("kg_B_g1");
+            auto bg2 = vec<g2>("kg_B_g2");
+            for (std::size_t i = 0; b_ok && i < kp.first.B_query.indices.size(); ++i)
+                b_ok = kp.first.B_query.indices[i] == F.at("kg_B_idx")[i] && kp.first.B_query.values[i].g == bg2[i] &&
+                       kp.first.B_query.values[i].h == bg1[i];
+            expect(b_ok, "zk::generate B_query (sparse)");
+            auto gabc = vec<g1>("kg_gamma_ABC_g1");
+            expect(kp.second.gamma_ABC_g1.first == gabc[0] &&
+                       kp.second.gamma_ABC_g1.rest == std::vector<g1>(gabc.begin() + 1, gabc.end()) &&
+                       kp.second.gamma_g2 == one<g2>("kg_gamma_g2") && kp.second.gamma_g1 == one<g1>("kg_gamma_g1"),
+                   "zk::generate verification key");
+            auto rnd = vec<fr>("kg_rnd");
+            const std::size_t msg = F.at("kg_msg_size")[0];
+            auto keys = pubkey::generate_keypair<scheme_type, pubkey::modes::verifiable_encryption<scheme_type>>(rnd, {kp, msg});
+            const auto &spub = std::get<0>(keys);
+            expect(spub.delta_g1 == kp.second.delta_g1 && spub.delta_s_g1 == vec<g1>("kg_pub_delta_s_g1") &&
+                       spub.t_g1 == vec<g1>("kg_pub_t_g1") && spub.t_g2 == vec<g2>("kg_pub_t_g2") &&
+                       spub.delta_sum_s_g1 == one<g1>("kg_pub_delta_sum_s_g1") &&
+                       spub.gamma_inverse_sum_s_g1 == one<g1>("kg_pub_gamma_inverse_sum_s_g1"),
+                   "pubkey::generate_keypair public key");
+            expect(std::get<1>(keys).rho == rnd[0], "pubkey::generate_keypair private key");
+            expect(std::get<2>(keys).rho_g2 == one<g2>("kg_rho_g2") && std::get<2>(keys).rho_sv_g2 == vec<g2>("kg_rho_sv_g2") &&
+                       std::get<2>(keys).rho_rhov_g2 == vec<g2>("kg_rho_rhov_g2"),
+                   "pubkey::generate_keypair verification key");
+            rnd.pop_back();
+            expect_invalid(
+                [&] {
+                    pubkey::generate_keypair<scheme_type, pubkey::modes::verifiable_encryption<scheme_type>>(rnd, {kp, msg});
+                },
+                "generate_keypair: too few random numbers throws");
+        }
     } catch (const std::exception &e) {
         std::fprintf(stderr, "shim_check: exception: %s\n", e.what());
         return 3;

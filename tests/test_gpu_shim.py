@@ -70,6 +70,33 @@ def write_fixture(path: str):
     rnd = [rng.randrange(1, o.R) for _ in range(3)]
     rec["rnd"] = cref.ints_to_limbs(rnd, 4)
     rec["rerand_ct"], rec["rerand_proof"] = cref.saver_rerandomize(opub, arr["delta_g2"], rnd, ct, rec["proof_enc"])
+    # key generation (zk::generate, pubkey::generate_keypair) on a small circuit, expected values from the Python oracle
+    kcs, _kp, _ka = synthetic_r1cs(12, 5, seed=31)
+    tox = [rng.randrange(1, o.R) for _ in range(5)]
+    opk, ovk = o.groth16_generate(kcs, None, toxic=tox)
+    karr = fx.pk_arrays(opk)
+    kcsa = karr["cs"]
+    rec["kg_num_inputs"], rec["kg_num_aux"], rec["kg_num_constraints"] = ([kcsa["num_inputs"]], [kcsa["num_aux"]],
+                                                                         [kcsa["num_constraints"]])
+    for k in "abc":
+        rec["kg_" + k + "_row"], rec["kg_" + k + "_col"], rec["kg_" + k + "_val"] = (
+            kcsa[k + "_row"], kcsa[k + "_col"].astype(np.uint64), kcsa[k + "_val"])
+    rec["kg_toxic"] = cref.ints_to_limbs(tox, 4)
+    for k in ("alpha_g1", "beta_g1", "beta_g2", "delta_g1", "delta_g2", "A_query", "H_query", "L_query", "B_g1", "B_g2"):
+        rec["kg_" + k] = karr[k]
+    rec["kg_B_count"], rec["kg_B_idx"] = [karr["B_count"]], karr["B_idx"].astype(np.uint64)
+    A1 = lambda pts: cref.g1_to_limbs([o.G1.to_affine(p) for p in pts])
+    A2 = lambda pts: cref.g2_to_limbs([o.G2.to_affine(p) for p in pts])
+    rec["kg_gamma_ABC_g1"] = A1([ovk.gamma_ABC_first] + ovk.gamma_ABC_rest)
+    rec["kg_gamma_g2"], rec["kg_gamma_g1"] = A2([ovk.gamma_g2]), A1([ovk.gamma_g1])
+    kmsg = 3
+    krnd = [rng.randrange(1, o.R) for _ in range(3 * kmsg + 2)]
+    kpub, _rho, ksvk = o.saver_keygen(ovk, kmsg, krnd)
+    rec["kg_msg_size"], rec["kg_rnd"] = [kmsg], cref.ints_to_limbs(krnd, 4)
+    kpa = fx.saver_pub_arrays(kpub)
+    for k in ("delta_s_g1", "t_g1", "t_g2", "delta_sum_s_g1", "gamma_inverse_sum_s_g1"):
+        rec["kg_pub_" + k] = kpa[k]
+    rec["kg_rho_g2"], rec["kg_rho_sv_g2"], rec["kg_rho_rhov_g2"] = A2([ksvk.rho_g2]), A2(ksvk.rho_sv_g2), A2(ksvk.rho_rhov_g2)
     with open(path, "wb") as f:
         for name, v in rec.items():
             data = np.ascontiguousarray(np.asarray(v, dtype=np.uint64)).reshape(-1)
