@@ -275,6 +275,38 @@ VSP_API int vsp_g1_mul_batch(vsp_ctx *ctx, uint64_t n, const uint64_t *points, c
 VSP_API int vsp_g1_generator_mul_batch(vsp_ctx *ctx, uint64_t n, const uint64_t *scalars, uint64_t *out);
 VSP_API int vsp_g2_generator_mul_batch(vsp_ctx *ctx, uint64_t n, const uint64_t *scalars, uint64_t *out);
 
+/* ---- pairing side: the verifiers that consume what the path produces ------------------------- */
+/* r1cs_gg_ppzksnark verification key, group members only: the reference stores e(alpha_g1, beta_g2) as the GT element
+ * alpha_g1_beta_g2 (libs/marshalling/zk/.../r1cs_gg_ppzksnark/verification_key.hpp:69); here its two preimages are
+ * passed and the pairing joins the product.  gamma_ABC_g1 = first | rest, gamma_ABC_count points. */
+typedef struct {
+    const uint64_t *alpha_g1, *beta_g2, *gamma_g2, *delta_g2;
+    uint64_t gamma_ABC_count;
+    const uint64_t *gamma_ABC_g1;
+} vsp_verification_key_t;
+/* algebra::pair_reduced<Curve>(P, Q) (call sites elgamal_verifiable.hpp:415-424, 559-571), batched as n_checks products
+ * of `pairs` pairings: g1 / g2 hold n_checks x pairs canonical affine points; gt_out[c] = prod_j e(g1[c][j], g2[c][j])
+ * as a canonical Fq12 (72 limbs, tower order c0.c0 | c0.c1 | c0.c2 | c1.c0 | c1.c1 | c1.c2 over Fq2 = c0 | c1,
+ * Fq12 = Fq6[w]/(w^2 - v), Fq6 = Fq2[v]/(v^3 - (1 + u))); is_one[c] = 1 iff the product is the identity.  Either
+ * output may be NULL.  A pair with a point at infinity contributes 1. */
+VSP_API int vsp_pairing_products(vsp_ctx *ctx, uint64_t n_checks, uint64_t pairs, const uint64_t *g1, const uint64_t *g2,
+                                 uint64_t *gt_out, uint8_t *is_one);
+/* zk::verify<r1cs_gg_ppzksnark<...>>(vk, primary_input, proof) for k proofs on one key (basic mode;
+ * libs/marshalling/zk/test/r1cs_gg_ppzksnark.cpp:160-163): ok_out[b] = 1 iff
+ *   e(A, B) = e(alpha, beta) e(gamma_ABC.first + sum_i x_i gamma_ABC.rest[i], gamma) e(C, delta).
+ * primary: k x n_primary canonical Fr; vk->gamma_ABC_count must be n_primary + 1; proofs: k x 48 limbs. */
+VSP_API int vsp_groth16_verify_batch(vsp_ctx *ctx, const vsp_verification_key_t *vk, uint64_t k, const uint64_t *primary,
+                                     uint64_t n_primary, const uint64_t *proofs, uint8_t *ok_out);
+/* verify_encryption_op<elgamal_verifiable>::process -> zk::verify<..., encrypted_input>(ct, vk, pubkey,
+ * unencrypted_primary_input, proof) (elgamal_verifiable.hpp:486-490) for k ballots: ok_out[b] = 1 iff
+ *   prod_{i <= n} e(ct_i, t_g2[i]) = e(ct_{n+1}, G2)   and
+ *   e(A, B) = e(alpha, beta) e(gamma_ABC.first + sum_{i<=n} ct_i + sum_j x_j gamma_ABC.rest[n + j], gamma) e(C, delta),
+ * n = pub->msg_size.  cts: k x (n + 2) G1; unencrypted_primary: k x n_unencrypted Fr (the primary input after the
+ * message slots); vk->gamma_ABC_count must be 1 + n + n_unencrypted. */
+VSP_API int vsp_saver_verify_encryption_batch(vsp_ctx *ctx, const vsp_verification_key_t *vk, const vsp_saver_pubkey_t *pub,
+                                              uint64_t k, const uint64_t *cts, const uint64_t *unencrypted_primary,
+                                              uint64_t n_unencrypted, const uint64_t *proofs, uint8_t *ok_out);
+
 /* ---- wire codecs: the reference's byte formats either side of the path (host only, no GPU work) ------------- */
 /* Formats (relative to libs/marshalling): big-endian fixed-width integers (Fr 32 B, Fq 48 B, size_t 8 B), sequences
  * with an 8-byte count prefix; compressed points as processing/curve_element.hpp:93-174 writes them (G1 48 B,

@@ -1,0 +1,146 @@
+"""GPU pairing side against the oracle: reduced pairings as bit-exact Fq12 values
+(algebra::pair_reduced, call sites libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp:415-424), bilinearity at
+sizes the oracle cannot reach, and the two verifiers (zk::verify, libs/marshalling/zk/test/r1cs_gg_ppzksnark.cpp:160-163;
+verify_encryption_op::process, elgamal_verifiable.hpp:486-490) deciding exactly as the oracle does on honest, tampered
+and rerandomised ballots (the flow of libs/pubkey/test/elgamal_verifiable.cpp:442-489)."""
+import importlib
+import random
+
+import numpy as np
+import pytest
+
+from helpers import synthetic_r1cs
+from oracle import cref, fixtures as fx, pyref as o
+
+pytestmark = pytest.mark.gpu
+vsp = importlib.import_module("vote-saver-protocol_b200")
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    with vsp.Context(0) as c:
+        yield c
+
+
+def _gt_limbs(f):
+    """pyref Fq12 ((a0, a1, a2), (b0, b1, b2)) -> 72 limbs in the ABI's tower order"""
+    flat = [c for half in f for e2 in half for c in e2]
+    return cref.ints_to_limbs(flat, 6).reshape(-1)
+
+
+G1L = lambda pts: cref.g1_to_limbs([o.G1.to_affine(p) for p in pts])
+G2L = lambda pts: cref.g2_to_limbs([o.G2.to_affine(p) for p in pts])
+
+
+def test_reduced_pairing_matches_oracle_bit_for_bit(ctx):
+    rng = random.Random(3)
+    ps = [o.G1.mul(rng.randrange(1, o.R), o.g1_generator()) for _ in range(3)]
+    qs = [o.G2.mul(rng.randrange(1, o.R), o.g2_generator()) for _ in range(3)]
+    gt, one = vsp.pairing_products(ctx, G1L(ps), G2L(qs))
+    for i in range(3):
+        want = o.final_exponentiation(o.miller_loop(o.G1.to_affine(ps[i]), o.G2.to_affine(qs[i])))
+        assert np.array_equal(gt[i], _gt_limbs(want)), i
+    assert not one.any()
+    # a product of three pairings in one check
+    gt3, _ = vsp.pairing_products(ctx, G1L(ps), G2L(qs), pairs=3)
+    f = o.F12_ONE
+    for p, q in zip(ps, qs):
+        f = o.f12mul(f, o.miller_loop(o.G1.to_affine(p), o.G2.to_affine(q)))
+    assert np.array_equal(gt3[0], _gt_limbs(o.final_exponentiation(f)))
+
+
+def test_pairing_bilinearity_and_infinity(ctx):
+    """e(aP, bQ) e(-abP, Q) = 1 for many random (a, b); a pair with a point at infinity contributes 1"""
+    n = 64
+    a, b = fx.random_fr(n, seed=1), fx.random_fr(n, seed=2)
+    ai, bi = cref.limbs_to_ints(a), cref.limbs_to_ints(b)
+    ab = cref.ints_to_limbs([(-x * y) % o.R for x, y in zip(ai, bi)], 4)
+    g2 = G2L([o.g2_generator()])[0]
+    aP, abP = vsp.g1_generator_mul_batch(ctx, a), vsp.g1_generator_mul_batch(ctx, ab)
+    bQ = vsp.g2_generator_mul_batch(ctx, b)
+    g1 = np.stack([aP, abP], axis=1).reshape(-1, 12)
+    q = np.stack([bQ, np.tile(g2, (n, 1))], axis=1).reshape(-1, 24)
+    _gt, one = vsp.pairing_products(ctx, g1, q, pairs=2)
+    assert one.all()
+    g1[1] = vsp.g1_generator_mul_batch(ctx, a[:1])[0]  # break check 0
+    _gt, one = vsp.pairing_products(ctx, g1, q, pairs=2)
+    assert not one[0] and one[1:].all()
+    z1, z2 = np.zeros((1, 12), np.uint64), np.zeros((1, 24), np.uint64)
+    _gt, one = vsp.pairing_products(ctx, np.concatenate([z1, aP[:1]]), np.concatenate([bQ[:1], z2]))
+    assert one.all()
+
+
+def _keys_and_ballots(ctx, nc, ni, msg_size, k, seed):
+    cs, _p, _a = synthetic_r1cs(nc, ni, seed=seed)
+    rng = random.Random(seed)
+    arr, vk = vsp.generate(ctx, fx.r1cs_arrays(cs), [rng.randrange(1, o.R) for _ in range(5)])
+    pub_arr, _rho, _svk = vsp.saver_generate_keypair(ctx, vk, msg_size, [rng.randrange(1, o.R) for _ in range(3 * msg_size + 2)])
+    return cs, arr, vk, pub_arr, rng
+
+
+def test_verify_batch_decides_like_the_oracle(ctx):
+    nc, ni, k = 40, 6, 5
+    cs, arr, vk, _pub, rng = _keys_and_ballots(ctx, nc, ni, 2, k, seed=5)
+    pk = vsp.ProvingKey(ctx, arr)
+    prim, proofs = [], []
+    for b in range(k):
+        _cs, primary, aux = synthetic_r1cs(nc, ni, seed=5)  # same circuit, same satisfying assignment
+        proofs.append(pk.prove(cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4), rng.randrange(o.R), rng.randrange(o.R)))
+        prim.append(cref.ints_to_limbs(primary, 4))
+    pk.close()
+    prim, proofs = np.stack(prim), np.stack(proofs)
+    assert vsp.verify_batch(ctx, vk, prim, proofs).all()
+    prim[1, 0, 0] ^= np.uint64(1)            # wrong primary input
+    proofs[2, 36:48] = proofs[3, 0:12]       # C replaced by another valid G1 point
+    proofs[4, 12:36] = proofs[0, 12:36]      # B from another proof
+    got = vsp.verify_batch(ctx, vk, prim, proofs)
+    assert got.tolist() == [True, False, False, True, False]
+    # the oracle agrees on one accept and one reject
+    from test_gpu_keygen import _vk_from_arrays
+    ovk = _vk_from_arrays(vk)
+    J1 = lambda a: o.G1.from_affine(cref.g1_from_limbs(a.reshape(1, 12))[0])
+    J2 = lambda a: o.G2.from_affine(cref.g2_from_limbs(a.reshape(1, 24))[0])
+    for b in (0, 1):
+        pr = (J1(proofs[b, :12]), J2(proofs[b, 12:36]), J1(proofs[b, 36:]))
+        assert o.groth16_verify(ovk, cref.limbs_to_ints(prim[b]), pr) == bool(got[b])
+
+
+def test_verify_encryption_batch_decides_like_the_oracle(ctx):
+    nc, ni, msg_size, k = 33, 7, 4, 6
+    cs, arr, vk, pub_arr, rng = _keys_and_ballots(ctx, nc, ni, msg_size, k, seed=9)
+    pk = vsp.ProvingKey(ctx, arr)
+    pub = vsp.SaverPublicKey(pub_arr)
+    _cs, primary, aux = synthetic_r1cs(nc, ni, seed=9)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    gabc_rest = np.ascontiguousarray(vk["gamma_ABC_g1"][1:1 + msg_size])
+    cts, proofs = [], []
+    for b in range(k):
+        r_saver, r, s = (rng.randrange(o.R) for _ in range(3))
+        ct, proof = pk.encrypt(pub, gabc_rest, np.ascontiguousarray(P[:msg_size]), P, A, r_saver, r, s)
+        cts.append(ct)
+        proofs.append(proof)
+    # ballot 5: a rerandomised copy of ballot 0 (rerandomize_op, elgamal_verifiable.hpp:632-667) still verifies
+    rnd = [rng.randrange(1, o.R) for _ in range(3)]
+    cts[5], proofs[5] = vsp.rerandomize(ctx, pub, arr["delta_g2"], rnd, cts[0], proofs[0])
+    pk.close()
+    cts, proofs = np.stack(cts), np.stack(proofs)
+    rest = np.tile(P[msg_size:], (k, 1, 1))
+    assert vsp.verify_encryption_batch(ctx, vk, pub, cts, rest, proofs).all()
+    g = G1L([o.g1_generator()])[0]
+    cts[1, 1] = cref.g1_add(cts[1, 1], g)        # tampered message slot
+    cts[2, msg_size + 1] = cts[3, msg_size + 1]  # sum element of another ballot
+    rest[4, 0, 0] ^= np.uint64(1)                # wrong public part of the primary input
+    got = vsp.verify_encryption_batch(ctx, vk, pub, cts, rest, proofs)
+    assert got.tolist() == [True, False, False, True, False, True]
+    from test_gpu_keygen import _vk_from_arrays
+    ovk = _vk_from_arrays(vk)
+    J1s = lambda a: [o.G1.from_affine(p) if p else o.G1.inf() for p in cref.g1_from_limbs(a)]
+    J2s = lambda a: [o.G2.from_affine(p) if p else o.G2.inf() for p in cref.g2_from_limbs(a)]
+    opub = o.SaverPublicKey(J1s(pub_arr["delta_g1"])[0], J1s(pub_arr["delta_s_g1"]), J1s(pub_arr["t_g1"]), J2s(pub_arr["t_g2"]),
+                            J1s(pub_arr["delta_sum_s_g1"])[0], J1s(pub_arr["gamma_inverse_sum_s_g1"])[0])
+    for b in (0, 1, 5):
+        pr = (J1s(proofs[b, :12].reshape(1, 12))[0], J2s(proofs[b, 12:36].reshape(1, 24))[0], J1s(proofs[b, 36:].reshape(1, 12))[0])
+        want = o.saver_verify_encryption(ovk, opub, J1s(cts[b]), cref.limbs_to_ints(rest[b]), pr)
+        assert want == bool(got[b]), b
+    with pytest.raises(ValueError):
+        vsp.verify_encryption_batch(ctx, vk, pub, cts, rest[:, :1], proofs)  # gamma_ABC count mismatch

@@ -12,6 +12,8 @@ Reference interfaces mirrored (paths relative to NilFoundation/vote-saver-protoc
   encrypt / rerandomize                         elgamal_verifiable.hpp:322-357, 632-667
   generate(cs, toxic)                           zk::generate<...>  call site bin/cli/include/nil/vote_saver/common.hpp:916-917
   saver_generate_keypair(vk, msg_size, rnd)     generate_keypair_op::process, elgamal_verifiable.hpp:218-271
+  pairing_products / verify_batch / verify_encryption_batch
+        algebra::pair_reduced (elgamal_verifiable.hpp:415-424), zk::verify, verify_encryption_op::process (:486-490)
 
 Data: numpy uint64 arrays of canonical little-endian limbs — Fr (n, 4); G1 affine (n, 12); G2 affine (n, 24);
 the point at infinity is all-zero.  Error behaviour follows the reference: what throws std::invalid_argument there
@@ -25,11 +27,11 @@ import numpy as np
 
 from . import _lib
 from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2, KeypairDesc, PkSliceDesc,
-                   ProvingKeyDesc, R1CSDesc, SaverKeypairDesc, SaverPubkeyDesc, VspError)
+                   ProvingKeyDesc, R1CSDesc, SaverKeypairDesc, SaverPubkeyDesc, VerificationKeyDesc, VspError)
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
            "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path",
-           "generate", "saver_generate_keypair", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
+           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_encryption_batch", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
 
 FR_MULTIPLICATIVE_GENERATOR = 7
 
@@ -542,3 +544,49 @@ def saver_generate_keypair(ctx: Context, vk: dict, msg_size: int, rnd):
     svk = {"rho_g2": arr["rho_g2"], "rho_sv_g2": arr["rho_sv_g2"], "rho_rhov_g2": arr["rho_rhov_g2"]}
     rho = int.from_bytes(arr["rho"].tobytes(), "little")
     return pub, rho, svk
+
+
+# ---- pairing side ----------------------------------------------------------------
+def pairing_products(ctx: Context, g1, g2, pairs: int = 1):
+    """prod_j e(g1[c][j], g2[c][j]) for every check c: returns (gt, is_one) with gt (n_checks, 72) canonical Fq12 limbs in
+    tower order and is_one (n_checks,) bool.  algebra::pair_reduced, batched."""
+    p1, p2 = _a(g1, 12), _a(g2, 24)
+    if p1.shape[0] != p2.shape[0] or pairs < 1 or p1.shape[0] % pairs:
+        raise ValueError("g1 / g2 must hold n_checks * pairs points each")
+    n = p1.shape[0] // pairs
+    gt = np.zeros((n, 72), dtype=np.uint64)
+    one = np.zeros(n, dtype=np.uint8)
+    ctx.check(ctx._lib.vsp_pairing_products(ctx._h, n, pairs, _p(p1), _p(p2), _p(gt), _p(one)))
+    return gt, one.astype(bool)
+
+
+def _vk_desc(vk: dict):
+    keep = {k: _a(vk[k], 24 if k.endswith("g2") else 12) for k in ("alpha_g1", "beta_g2", "gamma_g2", "delta_g2", "gamma_ABC_g1")}
+    keep["gamma_ABC_count"] = keep["gamma_ABC_g1"].shape[0]
+    return _fill(VerificationKeyDesc(), keep), keep
+
+
+def verify_batch(ctx: Context, vk: dict, primary, proofs) -> np.ndarray:
+    """zk::verify<r1cs_gg_ppzksnark<...>>(vk, primary_input, proof) for k proofs (basic mode): bool per proof.
+    primary: (k, n_primary, 4); proofs: (k, 48)."""
+    desc, keep = _vk_desc(vk)
+    pr = _a(proofs, 48)
+    k = pr.shape[0]
+    x = np.ascontiguousarray(primary, dtype=np.uint64).reshape(k, -1, 4) if k else np.zeros((0, 0, 4), np.uint64)
+    ok = np.zeros(k, dtype=np.uint8)
+    ctx.check(ctx._lib.vsp_groth16_verify_batch(ctx._h, C.byref(desc), k, _p(x), x.shape[1], _p(pr), _p(ok)))
+    return ok.astype(bool)
+
+
+def verify_encryption_batch(ctx: Context, vk: dict, pubkey: SaverPublicKey, cts, unencrypted_primary, proofs) -> np.ndarray:
+    """verify_encryption_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:486-490) for k ballots: bool per ballot.
+    cts: (k, msg_size + 2, 12); unencrypted_primary: (k, n_rest, 4) — the primary input after the message slots."""
+    desc, keep = _vk_desc(vk)
+    pr = _a(proofs, 48)
+    k = pr.shape[0]
+    ct = np.ascontiguousarray(cts, dtype=np.uint64).reshape(k, pubkey.msg_size + 2, 12)
+    x = np.ascontiguousarray(unencrypted_primary, dtype=np.uint64).reshape(k, -1, 4)
+    ok = np.zeros(k, dtype=np.uint8)
+    ctx.check(ctx._lib.vsp_saver_verify_encryption_batch(ctx._h, C.byref(desc), C.byref(pubkey.desc), k, _p(ct), _p(x),
+                                                         x.shape[1], _p(pr), _p(ok)))
+    return ok.astype(bool)

@@ -72,6 +72,12 @@ class SaverKeypairDesc(C.Structure):
                                     "rho_sv_g2", "rho_rhov_g2", "rho")]
 
 
+class VerificationKeyDesc(C.Structure):
+    """vsp_verification_key_t"""
+    _fields_ = [("alpha_g1", u64p), ("beta_g2", u64p), ("gamma_g2", u64p), ("delta_g2", u64p),
+                ("gamma_ABC_count", C.c_uint64), ("gamma_ABC_g1", u64p)]
+
+
 # every symbol include/vsp_b200.h declares: (name, restype, argtypes)
 _vp = C.c_void_p
 _u64 = C.c_uint64
@@ -130,6 +136,10 @@ SYMBOLS = [
     ("vsp_g1_mul_batch", _int, [_vp, _u64, _vp, _vp, _vp]),
     ("vsp_g1_generator_mul_batch", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_g2_generator_mul_batch", _int, [_vp, _u64, _vp, _vp]),
+    ("vsp_pairing_products", _int, [_vp, _u64, _u64, _vp, _vp, _vp, _vp]),
+    ("vsp_groth16_verify_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), _u64, _vp, _u64, _vp, _vp]),
+    ("vsp_saver_verify_encryption_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), C.POINTER(SaverPubkeyDesc), _u64, _vp,
+                                                 _vp, _u64, _vp, _vp]),
     ("vsp_codec_g1_compress", _int, [_vp, _vp]),
     ("vsp_codec_g2_compress", _int, [_vp, _vp]),
     ("vsp_codec_proof_write", _int, [_vp, _vp]),

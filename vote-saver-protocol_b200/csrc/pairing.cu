@@ -1,0 +1,494 @@
+// pairing.cu — the pairing side of the ballot path: BLS12-381 optimal ate pairing products on the GPU
+// and the verifiers built on them.
+//
+// Replaces (paths relative to /root/reference):
+//   algebra::pair_reduced<Curve>(P, Q)            call sites libs/pubkey/include/nil/crypto3/pubkey/elgamal_verifiable.hpp:415-424,
+//                                                 559-571 (source in the un-vendored crypto3-algebra @ e4fa2c5e)
+//   verify_encryption_op<elgamal_verifiable>::process -> zk::verify<r1cs_gg_ppzksnark<..., encrypted_input>>
+//                                                 elgamal_verifiable.hpp:486-490 (verifier in un-vendored crypto3-zk @ d335bb8b),
+//                                                 restated [UPSTREAM-RECALL, SURVEY.md 8c] as:
+//        prod_{i <= n} e(ct_i, t_g2[i]) = e(ct_{n+1}, G2)                               (ciphertext well-formedness)
+//        e(A, B) = e(alpha, beta) e(gamma_ABC.first + sum_{i<=n} ct_i + sum_j x_j gamma_ABC.rest[n+j], gamma) e(C, delta)
+//   zk::verify<r1cs_gg_ppzksnark<...>> (basic mode) libs/marshalling/zk/test/r1cs_gg_ppzksnark.cpp:160-163
+//
+// Tower: Fq2 = Fq[u]/(u^2 + 1), Fq6 = Fq2[v]/(v^3 - xi), Fq12 = Fq6[w]/(w^2 - v), xi = 1 + u.
+// Miller loop: T runs over the twist E'(Fq2) in affine coordinates; the line through T (slope lambda) evaluated at
+// P = (px, py), scaled by w^3 (a factor in the proper subfield Fq4 that the final exponentiation removes), is the
+// sparse element  (lambda Tx - Ty) + (-lambda px) w^2 + py w^3.  The slopes depend on Q only, so each G2 argument is
+// expanded ONCE into a table of its 68 (lambda, lambda Tx - Ty) pairs (63 doublings + 5 additions of the loop over
+// |x| = 0xd201000000010000); after that a pairing costs no inversion, and a product of pairings shares the 63 squarings
+// (one thread per product).  In the verifiers all but one G2 argument per ballot (the proof's B) are key material whose
+// tables are built once per call.  Final exponentiation: f^((p^12-1)/r) = (conj(f)/f)^((p^6+1)/r).
+#include "common.cuh"
+#include "ec.cuh"
+#include "host_fr.h"
+#include "pairing_constants.cuh"
+
+#include <cstring>
+#include <vector>
+
+namespace vsp {
+namespace {
+
+using E2 = Fq2;
+using O2 = Fq2Ops;
+
+struct Fq6 {
+    E2 c0, c1, c2;
+};
+struct Fq12 {
+    Fq6 c0, c1;
+};
+
+VSP_DEV E2 mul_xi(const E2& a) { return E2{fp_sub(a.c0, a.c1), fp_add(a.c0, a.c1)}; }
+VSP_DEV E2 mul_fq(const E2& a, const Fq& b) { return E2{fp_mul(a.c0, b), fp_mul(a.c1, b)}; }
+
+VSP_DEV Fq6 f6_add(const Fq6& a, const Fq6& b) { return Fq6{O2::add(a.c0, b.c0), O2::add(a.c1, b.c1), O2::add(a.c2, b.c2)}; }
+VSP_DEV Fq6 f6_sub(const Fq6& a, const Fq6& b) { return Fq6{O2::sub(a.c0, b.c0), O2::sub(a.c1, b.c1), O2::sub(a.c2, b.c2)}; }
+VSP_DEV Fq6 f6_neg(const Fq6& a) { return Fq6{O2::neg(a.c0), O2::neg(a.c1), O2::neg(a.c2)}; }
+VSP_DEV Fq6 f6_mul_v(const Fq6& a) { return Fq6{mul_xi(a.c2), a.c0, a.c1}; }
+VSP_DEV Fq6 f6_zero() { return Fq6{O2::zero(), O2::zero(), O2::zero()}; }
+VSP_DEV Fq12 f12_one() { return Fq12{Fq6{O2::one(), O2::zero(), O2::zero()}, f6_zero()}; }
+
+// Karatsuba over Fq2: 6 multiplications
+__device__ __noinline__ Fq6 f6_mul(const Fq6& a, const Fq6& b) {
+    const E2 t0 = O2::mul(a.c0, b.c0), t1 = O2::mul(a.c1, b.c1), t2 = O2::mul(a.c2, b.c2);
+    const E2 s12 = O2::sub(O2::sub(O2::mul(O2::add(a.c1, a.c2), O2::add(b.c1, b.c2)), t1), t2);
+    const E2 s01 = O2::sub(O2::sub(O2::mul(O2::add(a.c0, a.c1), O2::add(b.c0, b.c1)), t0), t1);
+    const E2 s02 = O2::sub(O2::sub(O2::mul(O2::add(a.c0, a.c2), O2::add(b.c0, b.c2)), t0), t2);
+    return Fq6{O2::add(t0, mul_xi(s12)), O2::add(s01, mul_xi(t2)), O2::add(s02, t1)};
+}
+// a * (b0 + b1 v): 5 multiplications
+__device__ __noinline__ Fq6 f6_mul_01(const Fq6& a, const E2& b0, const E2& b1) {
+    const E2 t0 = O2::mul(a.c0, b0), t1 = O2::mul(a.c1, b1);
+    const E2 s01 = O2::sub(O2::sub(O2::mul(O2::add(a.c0, a.c1), O2::add(b0, b1)), t0), t1);
+    return Fq6{O2::add(t0, mul_xi(O2::mul(a.c2, b1))), s01, O2::add(O2::mul(a.c2, b0), t1)};
+}
+// a * (b v), b in Fq
+VSP_DEV Fq6 f6_mul_1fq(const Fq6& a, const Fq& b) { return Fq6{mul_xi(mul_fq(a.c2, b)), mul_fq(a.c0, b), mul_fq(a.c1, b)}; }
+
+__device__ __noinline__ Fq6 f6_inv(const Fq6& a) {
+    const E2 c0 = O2::sub(O2::sqr(a.c0), mul_xi(O2::mul(a.c1, a.c2)));
+    const E2 c1 = O2::sub(mul_xi(O2::sqr(a.c2)), O2::mul(a.c0, a.c1));
+    const E2 c2 = O2::sub(O2::sqr(a.c1), O2::mul(a.c0, a.c2));
+    const E2 t = O2::add(O2::mul(a.c0, c0), mul_xi(O2::add(O2::mul(a.c2, c1), O2::mul(a.c1, c2))));
+    const E2 ti = O2::inv(t);
+    return Fq6{O2::mul(c0, ti), O2::mul(c1, ti), O2::mul(c2, ti)};
+}
+
+__device__ __noinline__ void f12_mul(Fq12& a, const Fq12& b) {
+    const Fq6 t0 = f6_mul(a.c0, b.c0), t1 = f6_mul(a.c1, b.c1);
+    const Fq6 m = f6_mul(f6_add(a.c0, a.c1), f6_add(b.c0, b.c1));
+    a.c0 = f6_add(t0, f6_mul_v(t1));
+    a.c1 = f6_sub(f6_sub(m, t0), t1);
+}
+// complex squaring: 2 Fq6 multiplications
+__device__ __noinline__ void f12_sqr(Fq12& a) {
+    const Fq6 t = f6_mul(a.c0, a.c1);
+    const Fq6 m = f6_mul(f6_add(a.c0, a.c1), f6_add(a.c0, f6_mul_v(a.c1)));
+    a.c0 = f6_sub(f6_sub(m, t), f6_mul_v(t));
+    a.c1 = f6_add(t, t);
+}
+// a *= l0 + l1 v + py v w   (the scaled line; l0, l1 in Fq2, py in Fq)
+__device__ __noinline__ void f12_mul_line(Fq12& a, const E2& l0, const E2& l1, const Fq& py) {
+    const Fq6 t0 = f6_mul_01(a.c0, l0, l1);
+    const Fq6 t1 = f6_mul_1fq(a.c1, py);
+    const E2 l1p = E2{fp_add(l1.c0, py), l1.c1};
+    const Fq6 m = f6_mul_01(f6_add(a.c0, a.c1), l0, l1p);
+    a.c0 = f6_add(t0, f6_mul_v(t1));
+    a.c1 = f6_sub(f6_sub(m, t0), t1);
+}
+__device__ __noinline__ Fq12 f12_inv(const Fq12& a) {
+    const Fq6 t = f6_sub(f6_mul(a.c0, a.c0), f6_mul_v(f6_mul(a.c1, a.c1)));
+    const Fq6 ti = f6_inv(t);
+    return Fq12{f6_mul(a.c0, ti), f6_neg(f6_mul(a.c1, ti))};
+}
+VSP_DEV bool f12_is_one(const Fq12& a) {
+    const E2 one = O2::one();
+    return O2::eq(a.c0.c0, one) && O2::is_zero(a.c0.c1) && O2::is_zero(a.c0.c2) && O2::is_zero(a.c1.c0) &&
+           O2::is_zero(a.c1.c1) && O2::is_zero(a.c1.c2);
+}
+VSP_DEV void f12_store(uint32_t* p, const Fq12& a) {
+    char* q = reinterpret_cast<char*>(p);
+    O2::store(q, a.c0.c0); O2::store(q + 96, a.c0.c1); O2::store(q + 192, a.c0.c2);
+    O2::store(q + 288, a.c1.c0); O2::store(q + 384, a.c1.c1); O2::store(q + 480, a.c1.c2);
+}
+VSP_DEV Fq12 f12_load(const uint32_t* p) {
+    const char* q = reinterpret_cast<const char*>(p);
+    return Fq12{Fq6{O2::load(q), O2::load(q + 96), O2::load(q + 192)}, Fq6{O2::load(q + 288), O2::load(q + 384), O2::load(q + 480)}};
+}
+
+constexpr int STEPS = VSP_MILLER_STEPS;
+constexpr int LINE_LIMBS = 48;                  // (lambda, lambda Tx - Ty): 2 Fq2, 192 bytes
+constexpr int TABLE_LIMBS = STEPS * LINE_LIMBS;  // 13,056 bytes per G2 argument
+
+// one thread per G2 point (canonical affine in): the slope table of its Miller loop; valid[i] = 0 for the point at infinity
+__global__ void __launch_bounds__(64) k_g2_line_table(const uint64_t* __restrict__ q_in, unsigned n, uint32_t* __restrict__ tables,
+                                                      uint8_t* __restrict__ valid) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    G2Affine q = G2Affine::load(q_in + uint64_t(i) * 24);
+    if (q.is_inf()) {
+        valid[i] = 0;
+        return;
+    }
+    valid[i] = 1;
+    q.x = O2::to_mont(q.x);
+    q.y = O2::to_mont(q.y);
+    E2 tx = q.x, ty = q.y;
+    uint32_t* out = tables + uint64_t(i) * TABLE_LIMBS;
+    int k = 0;
+#pragma unroll 1
+    for (int bit = 62; bit >= 0; --bit) {
+        const E2 xx = O2::sqr(tx);
+        E2 lam = O2::mul(O2::add(O2::dbl(xx), xx), O2::inv(O2::dbl(ty)));
+        O2::store(out + k * LINE_LIMBS, lam);
+        O2::store(out + k * LINE_LIMBS + 24, O2::sub(O2::mul(lam, tx), ty));
+        ++k;
+        E2 nx = O2::sub(O2::sqr(lam), O2::dbl(tx));
+        ty = O2::sub(O2::mul(lam, O2::sub(tx, nx)), ty);
+        tx = nx;
+        if ((VSP_BLS_X_ABS >> bit) & 1ULL) {
+            lam = O2::mul(O2::sub(q.y, ty), O2::inv(O2::sub(q.x, tx)));
+            O2::store(out + k * LINE_LIMBS, lam);
+            O2::store(out + k * LINE_LIMBS + 24, O2::sub(O2::mul(lam, tx), ty));
+            ++k;
+            nx = O2::sub(O2::sub(O2::sqr(lam), tx), q.x);
+            ty = O2::sub(O2::mul(lam, O2::sub(tx, nx)), ty);
+            tx = nx;
+        }
+    }
+}
+
+// one thread per product: f = conj( prod_j miller(P_j, table_j) ) with the squarings shared.
+//   pts: n_checks x pairs G1 affine (Montgomery); tidx: n_checks x pairs table index (0xffffffff or an invalid table or
+//   an infinite P: the pair contributes 1)
+__global__ void __launch_bounds__(64) k_multi_miller(const uint32_t* __restrict__ pts, const uint32_t* __restrict__ tidx,
+                                                     unsigned pairs, unsigned n_checks, const uint32_t* __restrict__ tables,
+                                                     const uint8_t* __restrict__ valid, uint32_t* __restrict__ f_out) {
+    const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_checks) return;
+    const uint32_t* my_pts = pts + uint64_t(c) * pairs * 24;
+    const uint32_t* my_idx = tidx + uint64_t(c) * pairs;
+    Fq12 f = f12_one();
+    int k = 0;
+#pragma unroll 1
+    for (int bit = 62; bit >= 0; --bit) {
+        f12_sqr(f);
+        const int lines = ((VSP_BLS_X_ABS >> bit) & 1ULL) ? 2 : 1;
+#pragma unroll 1
+        for (int l = 0; l < lines; ++l, ++k) {
+#pragma unroll 1
+            for (unsigned j = 0; j < pairs; ++j) {
+                const uint32_t t = my_idx[j];
+                if (t == 0xffffffffu || !valid[t]) continue;
+                const G1Affine p = G1Affine::load(my_pts + j * 24);
+                if (p.is_inf()) continue;
+                const uint32_t* e = tables + uint64_t(t) * TABLE_LIMBS + k * LINE_LIMBS;
+                const E2 lam = O2::load(e);
+                f12_mul_line(f, O2::load(e + 24), O2::neg(mul_fq(lam, p.x)), p.y);
+            }
+        }
+    }
+    f.c1 = f6_neg(f.c1);  // x < 0
+    f12_store(f_out + uint64_t(c) * 144, f);
+}
+
+// one thread per product: g = (conj(f) / f)^((p^6+1)/r); gt_out (optional): canonical Fq12, 72 u64 limbs in tower order
+__global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f_in, unsigned n, uint64_t* __restrict__ gt_out,
+                                                  uint8_t* __restrict__ is_one) {
+    const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    const Fq12 f = f12_load(f_in + uint64_t(c) * 144);
+    Fq12 base = f12_inv(f);
+    {
+        Fq12 cj = f;
+        cj.c1 = f6_neg(cj.c1);
+        f12_mul(base, cj);
+    }
+    Fq12 acc = base;  // leading bit
+#pragma unroll 1
+    for (int bit = VSP_PAIRING_E2_BITS - 2; bit >= 0; --bit) {
+        f12_sqr(acc);
+        if ((VSP_PAIRING_E2[bit >> 5] >> (bit & 31)) & 1u) f12_mul(acc, base);
+    }
+    if (is_one) is_one[c] = f12_is_one(acc) ? 1 : 0;
+    if (gt_out) {
+        const E2* co[6] = {&acc.c0.c0, &acc.c0.c1, &acc.c0.c2, &acc.c1.c0, &acc.c1.c1, &acc.c1.c2};
+        for (int q = 0; q < 6; ++q) O2::store(gt_out + uint64_t(c) * 72 + q * 12, O2::from_mont(*co[q]));
+    }
+}
+
+// G1 points canonical -> Montgomery (optionally negated), laid out for k_multi_miller
+__global__ void k_g1_prepare(const uint64_t* __restrict__ in, uint64_t n, uint32_t* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    G1Affine p = G1Affine::load(in + i * 12);
+    if (!p.is_inf()) {
+        p.x = fp_to_mont(p.x);
+        p.y = fp_to_mont(p.y);
+    }
+    p.store(out + i * 24);
+}
+
+// verifier preparation, one thread per ballot b:
+//   check 1 (only with a ciphertext): P = ct_0 .. ct_n, -ct_{n+1};  tables t_g2[0..n], G2
+//   check 2: P = -A, alpha, acc, C;  tables B_b, beta, gamma, delta
+//   acc = gamma_ABC.first + sum_{i<=n} ct_i + sum_j x_j gamma_ABC.rest[n_ct_slots + j]
+struct VerifyArgs {
+    const uint64_t* cts;     // k x (n + 2) canonical G1, or null (basic mode)
+    const uint64_t* proofs;  // k x 48 limbs
+    const uint32_t* xs;      // k x n_x canonical Fr
+    const uint64_t* gabc;    // (1 + n + n_x) canonical G1: first | rest   (n = msg_size; 0 slots in basic mode)
+    const uint64_t* alpha;   // canonical G1
+    unsigned k, n, n_x;
+    int has_ct;
+    uint32_t fixed_base;     // table index of t_g2[0]; then G2 | beta | gamma | delta follow the t_g2 block
+    uint32_t* pts1;          // k x (n + 2) G1 Montgomery
+    uint32_t* idx1;
+    uint32_t* pts2;          // k x 4
+    uint32_t* idx2;
+};
+__global__ void __launch_bounds__(64) k_verify_prepare(VerifyArgs a) {
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= a.k) return;
+    const unsigned slots = a.has_ct ? a.n + 1 : 0;  // ciphertext elements folded into acc
+    G1XYZZ acc = G1XYZZ::inf();
+    {
+        G1Affine g = G1Affine::load(a.gabc);
+        if (!g.is_inf()) {
+            g.x = fp_to_mont(g.x);
+            g.y = fp_to_mont(g.y);
+            ec_madd<FqOps>(acc, g);
+        }
+    }
+    if (a.has_ct) {
+        const uint64_t* ct = a.cts + uint64_t(b) * (a.n + 2) * 12;
+        for (unsigned i = 0; i < a.n + 2; ++i) {
+            G1Affine p = G1Affine::load(ct + uint64_t(i) * 12);
+            if (!p.is_inf()) {
+                p.x = fp_to_mont(p.x);
+                p.y = fp_to_mont(p.y);
+                if (i <= a.n) ec_madd<FqOps>(acc, p);
+                if (i == a.n + 1) p.y = fp_neg(p.y);
+            }
+            p.store(a.pts1 + (uint64_t(b) * (a.n + 2) + i) * 24);
+            a.idx1[uint64_t(b) * (a.n + 2) + i] = a.fixed_base + i;  // t_g2[0..n], then G2 at n + 1
+        }
+    }
+    for (unsigned j = 0; j < a.n_x; ++j) {
+        G1Affine g = G1Affine::load(a.gabc + uint64_t(1 + (a.has_ct ? a.n : 0) + j) * 12);
+        if (g.is_inf()) continue;
+        g.x = fp_to_mont(g.x);
+        g.y = fp_to_mont(g.y);
+        const uint32_t* x = a.xs + 8 * (uint64_t(b) * a.n_x + j);
+        G1XYZZ t = G1XYZZ::inf();
+        int top = 255;
+        while (top >= 0 && !((x[top >> 5] >> (top & 31)) & 1u)) --top;
+        for (int bit = top; bit >= 0; --bit) {
+            t = ec_dbl<FqOps>(t);
+            if ((x[bit >> 5] >> (bit & 31)) & 1u) ec_madd<FqOps>(t, g);
+        }
+        ec_add<FqOps>(acc, t);
+    }
+    (void)slots;
+    const uint64_t* pr = a.proofs + uint64_t(b) * 48;
+    G1Affine A = G1Affine::load(pr), C = G1Affine::load(pr + 36), al = G1Affine::load(a.alpha);
+    if (!A.is_inf()) {
+        A.x = fp_to_mont(A.x);
+        A.y = fp_neg(fp_to_mont(A.y));
+    }
+    if (!C.is_inf()) {
+        C.x = fp_to_mont(C.x);
+        C.y = fp_to_mont(C.y);
+    }
+    if (!al.is_inf()) {
+        al.x = fp_to_mont(al.x);
+        al.y = fp_to_mont(al.y);
+    }
+    uint32_t* p2 = a.pts2 + uint64_t(b) * 4 * 24;
+    A.store(p2);
+    al.store(p2 + 24);
+    ec_to_affine<FqOps>(acc).store(p2 + 48);
+    C.store(p2 + 72);
+    const uint32_t fixed_tail = a.fixed_base + (a.has_ct ? a.n + 2 : 0);  // beta | gamma | delta
+    uint32_t* i2 = a.idx2 + uint64_t(b) * 4;
+    i2[0] = b;  // the proof's own B: tables 0 .. k-1
+    i2[1] = fixed_tail;
+    i2[2] = fixed_tail + 1;
+    i2[3] = fixed_tail + 2;
+}
+
+__global__ void k_and_flags(const uint8_t* a, const uint8_t* b, unsigned n, uint8_t* out) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = (a[i] && (!b || b[i])) ? 1 : 0;
+}
+
+const uint64_t G2_GENERATOR[24] = {
+    0xd48056c8c121bdb8ULL, 0x0bac0326a805bbefULL, 0xb4510b647ae3d177ULL, 0xc6e47ad4fa403b02ULL, 0x260805272dc51051ULL, 0x024aa2b2f08f0a91ULL,
+    0xe5ac7d055d042b7eULL, 0x334cf11213945d57ULL, 0xb5da61bbdc7f5049ULL, 0x596bd0d09920b61aULL, 0x7dacd3a088274f65ULL, 0x13e02b6052719f60ULL,
+    0xe193548608b82801ULL, 0x923ac9cc3baca289ULL, 0x6d429a695160d12cULL, 0xadfd9baa8cbdd3a7ULL, 0x8cc9cdc6da2e351aULL, 0x0ce5d527727d6e11ULL,
+    0xaaa9075ff05f79beULL, 0x3f370d275cec1da1ULL, 0x267492ab572e99abULL, 0xcb3e287e85a763afULL, 0x32acd2b02bc28b99ULL, 0x0606c4a02ea734ccULL};
+
+int run_products(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_pts, const uint32_t* d_idx, unsigned pairs, unsigned n_checks,
+                 const uint32_t* d_tables, const uint8_t* d_valid, uint64_t* d_gt, uint8_t* d_one) {
+    if (!n_checks) return VSP_OK;
+    DevBuf f;
+    VSP_TRY(f.alloc(ctx, size_t(n_checks) * 576, s));
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_multi_miller, (n_checks + 63) / 64, 64, 0, s, d_pts, d_idx, pairs, n_checks, d_tables, d_valid,
+                 f.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_final_exp, (n_checks + 63) / 64, 64, 0, s, f.as<uint32_t>(), n_checks, d_gt, d_one);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    return VSP_OK;
+}
+
+int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* t_g2, uint64_t msg_size, uint64_t k,
+                const uint64_t* cts, const uint64_t* xs, uint64_t n_x, const uint64_t* proofs, uint8_t* ok) {
+    if (k == 0) return VSP_OK;
+    if (k > (1u << 24) || msg_size > 4096 || n_x > (1u << 20)) return set_error(ctx, VSP_E_INVALID, "verify: batch too large");
+    const bool has_ct = cts != nullptr;
+    const unsigned n = has_ct ? (unsigned)msg_size : 0, K = (unsigned)k;
+    if (vk->gamma_ABC_count != 1 + uint64_t(n) + n_x)
+        return set_error(ctx, VSP_E_INVALID, "verify: gamma_ABC_g1 holds %llu points, expected 1 + %u + %llu",
+                         (unsigned long long)vk->gamma_ABC_count, n, (unsigned long long)n_x);
+    for (uint64_t i = 0; i < k * n_x; ++i)
+        if (hostfr::geq(xs + 4 * i, hostfr::MOD)) return set_error(ctx, VSP_E_INVALID, "primary input not reduced mod r");
+    cudaStream_t s = ctx->stream;
+    // G2 arguments: k proofs' B | t_g2[0..n] | G2 | beta | gamma | delta
+    const unsigned n_fixed = (has_ct ? n + 2 : 0) + 3, n_q = K + n_fixed;
+    std::vector<uint64_t> hq(size_t(n_q) * 24);
+    for (unsigned b = 0; b < K; ++b) memcpy(&hq[size_t(b) * 24], proofs + size_t(b) * 48 + 12, 192);
+    size_t pos = size_t(K) * 24;
+    if (has_ct) {
+        memcpy(&hq[pos], t_g2, size_t(n + 1) * 192);
+        pos += size_t(n + 1) * 24;
+        memcpy(&hq[pos], G2_GENERATOR, 192);
+        pos += 24;
+    }
+    memcpy(&hq[pos], vk->beta_g2, 192);
+    memcpy(&hq[pos + 24], vk->gamma_g2, 192);
+    memcpy(&hq[pos + 48], vk->delta_g2, 192);
+    DevBuf d_q, d_tab, d_valid, d_ct, d_pr, d_x, d_gabc, d_alpha, d_p1, d_i1, d_p2, d_i2, d_one;
+    VSP_TRY(d_q.alloc(ctx, hq.size() * 8, s));
+    VSP_TRY(d_tab.alloc(ctx, size_t(n_q) * TABLE_LIMBS * 4, s));
+    VSP_TRY(d_valid.alloc(ctx, n_q, s));
+    VSP_TRY(d_pr.alloc(ctx, size_t(K) * 384, s));
+    VSP_TRY(d_x.alloc(ctx, size_t(K) * n_x * 32, s));
+    VSP_TRY(d_gabc.alloc(ctx, size_t(vk->gamma_ABC_count) * 96, s));
+    VSP_TRY(d_alpha.alloc(ctx, 96, s));
+    VSP_TRY(d_p2.alloc(ctx, size_t(K) * 4 * 96, s));
+    VSP_TRY(d_i2.alloc(ctx, size_t(K) * 4 * 4, s));
+    VSP_TRY(d_one.alloc(ctx, size_t(K) * 3, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_q.p, hq.data(), hq.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_pr.p, proofs, size_t(K) * 384, cudaMemcpyHostToDevice, s));
+    if (n_x) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_x.p, xs, size_t(K) * n_x * 32, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_gabc.p, vk->gamma_ABC_g1, size_t(vk->gamma_ABC_count) * 96, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_alpha.p, vk->alpha_g1, 96, cudaMemcpyHostToDevice, s));
+    if (has_ct) {
+        VSP_TRY(d_ct.alloc(ctx, size_t(K) * (n + 2) * 96, s));
+        VSP_TRY(d_p1.alloc(ctx, size_t(K) * (n + 2) * 96, s));
+        VSP_TRY(d_i1.alloc(ctx, size_t(K) * (n + 2) * 4, s));
+        VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_ct.p, cts, size_t(K) * (n + 2) * 96, cudaMemcpyHostToDevice, s));
+    }
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_g2_line_table, (n_q + 63) / 64, 64, 0, s, d_q.as<uint64_t>(), n_q, d_tab.as<uint32_t>(),
+                 d_valid.as<uint8_t>());
+    VerifyArgs a;
+    a.cts = has_ct ? d_ct.as<uint64_t>() : nullptr;
+    a.proofs = d_pr.as<uint64_t>();
+    a.xs = d_x.as<uint32_t>();
+    a.gabc = d_gabc.as<uint64_t>();
+    a.alpha = d_alpha.as<uint64_t>();
+    a.k = K;
+    a.n = n;
+    a.n_x = (unsigned)n_x;
+    a.has_ct = has_ct ? 1 : 0;
+    a.fixed_base = K;
+    a.pts1 = has_ct ? d_p1.as<uint32_t>() : nullptr;
+    a.idx1 = has_ct ? d_i1.as<uint32_t>() : nullptr;
+    a.pts2 = d_p2.as<uint32_t>();
+    a.idx2 = d_i2.as<uint32_t>();
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_verify_prepare, (K + 63) / 64, 64, 0, s, a);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    uint8_t* one = d_one.as<uint8_t>();
+    VSP_TRY(run_products(ctx, s, d_p2.as<uint32_t>(), d_i2.as<uint32_t>(), 4, K, d_tab.as<uint32_t>(), d_valid.as<uint8_t>(), nullptr,
+                         one));
+    if (has_ct)
+        VSP_TRY(run_products(ctx, s, d_p1.as<uint32_t>(), d_i1.as<uint32_t>(), n + 2, K, d_tab.as<uint32_t>(),
+                             d_valid.as<uint8_t>(), nullptr, one + K));
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_and_flags, (K + 127) / 128, 128, 0, s, one, has_ct ? one + K : nullptr, K, one + 2 * K);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(ok, one + 2 * K, K, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    return VSP_OK;
+}
+
+}  // namespace
+}  // namespace vsp
+
+using namespace vsp;
+
+// n_checks products of `pairs` pairings each: gt_out[c] = prod_j e(g1[c][j], g2[c][j]) as a canonical Fq12 (72 limbs, tower
+// order c0.c0 | c0.c1 | c0.c2 | c1.c0 | c1.c1 | c1.c2, each Fq2 = c0 | c1), is_one[c] = (product == 1); either may be null
+extern "C" int vsp_pairing_products(vsp_ctx* ctx, uint64_t n_checks, uint64_t pairs, const uint64_t* g1, const uint64_t* g2,
+                                    uint64_t* gt_out, uint8_t* is_one) {
+    if (!ctx) return VSP_E_INVALID;
+    if (n_checks == 0) return VSP_OK;
+    if (!g1 || !g2 || pairs == 0 || n_checks * pairs > (1u << 22)) return set_error(ctx, VSP_E_INVALID, "vsp_pairing_products: bad argument");
+    cudaSetDevice(ctx->device);
+    cudaStream_t s = ctx->stream;
+    const uint64_t n = n_checks * pairs;
+    DevBuf d_g1, d_g2, d_pts, d_idx, d_tab, d_valid, d_gt, d_one;
+    VSP_TRY(d_g1.alloc(ctx, n * 96, s));
+    VSP_TRY(d_g2.alloc(ctx, n * 192, s));
+    VSP_TRY(d_pts.alloc(ctx, n * 96, s));
+    VSP_TRY(d_idx.alloc(ctx, n * 4, s));
+    VSP_TRY(d_tab.alloc(ctx, n * TABLE_LIMBS * 4, s));
+    VSP_TRY(d_valid.alloc(ctx, n, s));
+    VSP_TRY(d_gt.alloc(ctx, n_checks * 576, s));
+    VSP_TRY(d_one.alloc(ctx, n_checks, s));
+    std::vector<uint32_t> idx(n);
+    for (uint64_t i = 0; i < n; ++i) idx[i] = (uint32_t)i;
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_g1.p, g1, n * 96, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_g2.p, g2, n * 192, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_idx.p, idx.data(), n * 4, cudaMemcpyHostToDevice, s));
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_g1_prepare, (unsigned)((n + 127) / 128), 128, 0, s, d_g1.as<uint64_t>(), n, d_pts.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_g2_line_table, (unsigned)((n + 63) / 64), 64, 0, s, d_g2.as<uint64_t>(), (unsigned)n,
+                 d_tab.as<uint32_t>(), d_valid.as<uint8_t>());
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_TRY(run_products(ctx, s, d_pts.as<uint32_t>(), d_idx.as<uint32_t>(), (unsigned)pairs, (unsigned)n_checks, d_tab.as<uint32_t>(),
+                         d_valid.as<uint8_t>(), d_gt.as<uint64_t>(), d_one.as<uint8_t>()));
+    if (gt_out) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(gt_out, d_gt.p, n_checks * 576, cudaMemcpyDeviceToHost, s));
+    if (is_one) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(is_one, d_one.p, n_checks, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    return VSP_OK;
+}
+
+extern "C" int vsp_groth16_verify_batch(vsp_ctx* ctx, const vsp_verification_key_t* vk, uint64_t k, const uint64_t* primary,
+                                        uint64_t n_primary, const uint64_t* proofs, uint8_t* ok_out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (!vk || !vk->alpha_g1 || !vk->beta_g2 || !vk->gamma_g2 || !vk->delta_g2 || !vk->gamma_ABC_g1 || (k && (!proofs || !ok_out)) ||
+        (k && n_primary && !primary))
+        return set_error(ctx, VSP_E_INVALID, "vsp_groth16_verify_batch: null argument");
+    cudaSetDevice(ctx->device);
+    try {
+        return verify_impl(ctx, vk, nullptr, 0, k, nullptr, primary, n_primary, proofs, ok_out);
+    } catch (const std::bad_alloc&) {
+        return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
+    }
+}
+
+extern "C" int vsp_saver_verify_encryption_batch(vsp_ctx* ctx, const vsp_verification_key_t* vk, const vsp_saver_pubkey_t* pub,
+                                                 uint64_t k, const uint64_t* cts, const uint64_t* unencrypted_primary,
+                                                 uint64_t n_unencrypted, const uint64_t* proofs, uint8_t* ok_out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (!vk || !pub || !pub->t_g2 || !vk->alpha_g1 || !vk->beta_g2 || !vk->gamma_g2 || !vk->delta_g2 || !vk->gamma_ABC_g1 ||
+        (k && (!cts || !proofs || !ok_out)) || (k && n_unencrypted && !unencrypted_primary))
+        return set_error(ctx, VSP_E_INVALID, "vsp_saver_verify_encryption_batch: null argument");
+    cudaSetDevice(ctx->device);
+    try {
+        return verify_impl(ctx, vk, pub->t_g2, pub->msg_size, k, cts, unencrypted_primary, n_unencrypted, proofs, ok_out);
+    } catch (const std::bad_alloc&) {
+        return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
+    }
+}
