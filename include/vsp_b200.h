@@ -307,6 +307,19 @@ VSP_API int vsp_saver_verify_encryption_batch(vsp_ctx *ctx, const vsp_verificati
                                               uint64_t k, const uint64_t *cts, const uint64_t *unencrypted_primary,
                                               uint64_t n_unencrypted, const uint64_t *proofs, uint8_t *ok_out);
 
+/* decrypt_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:401-441): ct = msg_size + 2 G1 (e.g. the tally's sum of
+ * ballots' ciphertexts), rho the secret key, (rho_sv_g2, rho_rhov_g2) from the SAVER verification key, gamma_abc_rest the
+ * first msg_size points of gamma_ABC_g1.rest.  m_out: msg_size Fr, each the discrete log found by the reference's search
+ * over exp = 0 .. 2^block_bits (scheme_type::block_bits, default 4); verify_c0_out = rho * ct[0], the decryption proof.
+ * VSP_E_INVALID with text "Decryption failed." where the reference asserts. */
+VSP_API int vsp_saver_decrypt(vsp_ctx *ctx, uint64_t msg_size, const uint64_t *ct, const uint64_t rho[4],
+                              const uint64_t *rho_sv_g2, const uint64_t *rho_rhov_g2, const uint64_t *gamma_abc_rest,
+                              unsigned block_bits, uint64_t *m_out, uint64_t *verify_c0_out);
+/* verify_decryption_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:548-575): proof = verify_c0 of decrypt */
+VSP_API int vsp_saver_verify_decryption(vsp_ctx *ctx, uint64_t msg_size, const uint64_t *ct, const uint64_t *plain,
+                                        const uint64_t *rho_g2, const uint64_t *rho_sv_g2, const uint64_t *rho_rhov_g2,
+                                        const uint64_t *gamma_abc_rest, const uint64_t *proof, uint8_t *ok_out);
+
 /* ---- wire codecs: the reference's byte formats either side of the path (host only, no GPU work) ------------- */
 /* Formats (relative to libs/marshalling): big-endian fixed-width integers (Fr 32 B, Fq 48 B, size_t 8 B), sequences
  * with an 8-byte count prefix; compressed points as processing/curve_element.hpp:93-174 writes them (G1 48 B,

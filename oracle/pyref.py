@@ -1161,3 +1161,49 @@ def saver_verify_encryption(vk: VerificationKey, pub: SaverPublicKey, ct, unencr
         acc = G1.add(acc, G1.mul(x, pt))
     return pairing_product_is_one([
         (G1.neg(gA), gB), (vk.alpha_g1, vk.beta_g2), (acc, vk.gamma_g2), (gC, vk.delta_g2)])
+
+
+def pair_reduced(p, q):
+    """algebra::pair_reduced<Curve>(P, Q): Jacobian points in, reduced pairing (Fq12 tuple) out."""
+    return final_exponentiation(miller_loop(G1.to_affine(p), G2.to_affine(q)))
+
+
+def saver_decrypt(ct, rho: int, svk: SaverVerificationKey, gamma_ABC_rest: Sequence, block_bits: int = 4):
+    """decrypt_op::process, elgamal_verifiable.hpp:401-441 [SRC]: returns (m_new, verify_c0); raises where the
+    reference asserts 'Decryption failed.'"""
+    n = len(ct) - 2
+    assert len(gamma_ABC_rest) > n and n == len(svk.rho_sv_g2) == len(svk.rho_rhov_g2)
+    m_new = []
+    for j in range(1, len(ct) - 1):
+        ci_sk_i = pair_reduced(ct[j], svk.rho_rhov_g2[j - 1])
+        c0_sk_0 = f12pow(pair_reduced(ct[0], svk.rho_sv_g2[j - 1]), rho)
+        dec_tmp = f12mul(ci_sk_i, f12inv(c0_sk_0))
+        discrete_log = F12_ONE
+        bruteforce = pair_reduced(gamma_ABC_rest[j - 1], svk.rho_rhov_g2[j - 1])
+        exp = 0
+        deciphered = False
+        while True:
+            if dec_tmp == discrete_log:
+                m_new.append(exp)
+                deciphered = True
+                break
+            discrete_log = f12mul(discrete_log, bruteforce)
+            exp += 1
+            if not (exp - 1 < (1 << block_bits)):  # do { ... } while (exp++ < 1 << block_bits)
+                break
+        if not deciphered:
+            raise ValueError("Decryption failed.")
+    return m_new, G1.mul(rho, ct[0])
+
+
+def saver_verify_decryption(ct, plain: Sequence[int], svk: SaverVerificationKey, gamma_ABC_rest: Sequence, proof) -> bool:
+    """verify_decryption_op::process, elgamal_verifiable.hpp:548-575 [SRC]; proof = verify_c0 of decrypt."""
+    assert len(plain) + 2 == len(ct) and len(gamma_ABC_rest) > len(plain)
+    ans = pair_reduced(proof, g2_generator()) == pair_reduced(ct[0], svk.rho_g2)
+    for i in range(1, len(ct) - 1):
+        ci_v_nj = pair_reduced(ct[i], svk.rho_rhov_g2[i - 1])
+        v_vj = pair_reduced(proof, svk.rho_sv_g2[i - 1])
+        verify_tmp = f12mul(ci_v_nj, f12inv(v_vj))
+        verify_msg = f12pow(pair_reduced(gamma_ABC_rest[i - 1], svk.rho_rhov_g2[i - 1]), plain[i - 1] % R)
+        ans = ans and (verify_tmp == verify_msg)
+    return ans

@@ -144,3 +144,40 @@ def test_verify_encryption_batch_decides_like_the_oracle(ctx):
         assert want == bool(got[b]), b
     with pytest.raises(ValueError):
         vsp.verify_encryption_batch(ctx, vk, pub, cts, rest[:, :1], proofs)  # gamma_ABC count mismatch
+
+
+def test_tally_decrypt_and_verify_decryption(ctx):
+    """the tally flow of bin/cli (common.hpp: sum the ballots' ciphertexts, decrypt_op, verify_decryption_op): keys, ballots
+    and the tally on the GPU; small case cross-checked against the oracle's restatement of elgamal_verifiable.hpp:401-441,
+    548-575"""
+    msg_size, voters = 3, 5
+    cs, arr, vk, pub_arr, rng = _keys_and_ballots(ctx, 20, 5, msg_size, voters, seed=13)
+    rnd = [rng.randrange(1, o.R) for _ in range(3 * msg_size + 2)]
+    pub_arr, rho, svk = vsp.saver_generate_keypair(ctx, vk, msg_size, rnd)
+    pub = vsp.SaverPublicKey(pub_arr)
+    gabc_rest = np.ascontiguousarray(vk["gamma_ABC_g1"][1:1 + msg_size])
+    votes = [[1, 0, 0], [0, 1, 0], [1, 0, 0], [1, 0, 0], [0, 0, 1]]
+    total = None
+    for v in votes:
+        ct = vsp.saver_ciphertext(ctx, pub, gabc_rest, cref.ints_to_limbs(v, 4), rng.randrange(1, o.R))
+        total = ct if total is None else np.stack([cref.g1_add(total[i], ct[i]) for i in range(msg_size + 2)])
+    m, c0 = vsp.decrypt(ctx, total, rho, svk, gabc_rest, block_bits=3)
+    assert m == [3, 1, 1]
+    assert vsp.verify_decryption(ctx, total, m, svk, gabc_rest, c0)
+    assert not vsp.verify_decryption(ctx, total, [3, 1, 0], svk, gabc_rest, c0)
+    assert not vsp.verify_decryption(ctx, total, m, svk, gabc_rest, cref.g1_add(c0, G1L([o.g1_generator()])[0]))
+    with pytest.raises(ValueError, match="Decryption failed"):
+        vsp.decrypt(ctx, total, rho, svk, gabc_rest, block_bits=1)  # 3 votes do not fit exp <= 2
+    # the oracle agrees on a two-slot ciphertext (one Python pairing costs about a second)
+    from test_gpu_keygen import _vk_from_arrays
+    ovk = _vk_from_arrays(vk)
+    J1s = lambda a: [o.G1.from_affine(p) if p else o.G1.inf() for p in cref.g1_from_limbs(a)]
+    J2s = lambda a: [o.G2.from_affine(p) if p else o.G2.inf() for p in cref.g2_from_limbs(a)]
+    osvk = o.SaverVerificationKey(J2s(svk["rho_g2"])[0], J2s(svk["rho_sv_g2"])[:1], J2s(svk["rho_rhov_g2"])[:1])
+    small = np.concatenate([total[:2], total[-1:]])  # slot 0 only: ct_0, ct_1, (sum element unused by decrypt)
+    om, oc0 = o.saver_decrypt(J1s(small), rho, osvk, ovk.gamma_ABC_rest, block_bits=2)
+    gm, gc0 = vsp.decrypt(ctx, small, rho, svk, gabc_rest, block_bits=2)
+    assert om == gm == [3]
+    assert np.array_equal(gc0, G1L([oc0])[0])
+    assert o.saver_verify_decryption(J1s(small), om, osvk, ovk.gamma_ABC_rest, oc0)
+    assert vsp.verify_decryption(ctx, small, gm, svk, gabc_rest, gc0)

@@ -232,3 +232,24 @@ def test_saver_encrypt_verifies_and_survives_rerandomisation():
     ct2, proof2 = o.saver_rerandomize(pub, pk.delta_g2, ct, proof, rnd)
     assert ct2 != ct
     assert o.saver_verify_encryption(vk, pub, ct2, rest, proof2)
+
+
+def test_saver_decrypt_round_trip_on_the_oracle():
+    """elgamal_verifiable.cpp:442-489 style on the oracle: keygen -> ciphertext -> decrypt recovers the message and
+    verify_decryption accepts it (elgamal_verifiable.hpp:401-441, 548-575 restated from source); a wrong message or a
+    wrong decryption proof is rejected, and a message outside the brute-force range fails like the reference asserts."""
+    rng = random.Random(41)
+    msg_size = 2
+    cs, primary, aux = o.r1cs_example_with_field_input(8, 3, rng)
+    _pk, vk = o.groth16_generate(cs, rng)
+    pub, rho, svk = o.saver_keygen(vk, msg_size, [rng.randrange(1, o.R) for _ in range(3 * msg_size + 2)])
+    plain = [3, 0]
+    ct = o.saver_ciphertext(pub, vk.gamma_ABC_rest, plain, rng.randrange(1, o.R))
+    m, c0 = o.saver_decrypt(ct, rho, svk, vk.gamma_ABC_rest, block_bits=2)
+    assert m == plain
+    assert o.saver_verify_decryption(ct, plain, svk, vk.gamma_ABC_rest, c0)
+    assert not o.saver_verify_decryption(ct, [2, 0], svk, vk.gamma_ABC_rest, c0)
+    assert not o.saver_verify_decryption(ct, plain, svk, vk.gamma_ABC_rest, o.G1.add(c0, o.g1_generator()))
+    ct6 = o.saver_ciphertext(pub, vk.gamma_ABC_rest, [6, 0], rng.randrange(1, o.R))
+    with pytest.raises(ValueError):
+        o.saver_decrypt(ct6, rho, svk, vk.gamma_ABC_rest, block_bits=2)

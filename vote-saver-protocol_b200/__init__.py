@@ -31,7 +31,7 @@ from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADI
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
            "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path",
-           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_encryption_batch", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
+           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_encryption_batch", "decrypt", "verify_decryption", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
 
 FR_MULTIPLICATIVE_GENERATOR = 7
 
@@ -590,3 +590,32 @@ def verify_encryption_batch(ctx: Context, vk: dict, pubkey: SaverPublicKey, cts,
     ctx.check(ctx._lib.vsp_saver_verify_encryption_batch(ctx._h, C.byref(desc), C.byref(pubkey.desc), k, _p(ct), _p(x),
                                                          x.shape[1], _p(pr), _p(ok)))
     return ok.astype(bool)
+
+
+def decrypt(ctx: Context, ct, rho: int, svk: dict, gamma_abc_rest, block_bits: int = 4):
+    """decrypt_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:401-441): (message ints, verify_c0 point).
+    svk: the SAVER verification-key arrays (rho_g2, rho_sv_g2, rho_rhov_g2).  ValueError("Decryption failed.") where the
+    reference asserts."""
+    c = _a(ct, 12)
+    n = c.shape[0] - 2
+    sv, rv, g = _a(svk["rho_sv_g2"], 24), _a(svk["rho_rhov_g2"], 24), _a(gamma_abc_rest, 12)
+    if n < 0 or sv.shape[0] < n or rv.shape[0] < n or g.shape[0] < n:
+        raise ValueError("Cipher text size should match the verification key (exclusive of 2 elements in CT).")
+    m = np.zeros((max(n, 1), 4), dtype=np.uint64)
+    c0 = np.zeros(12, dtype=np.uint64)
+    ctx.check(ctx._lib.vsp_saver_decrypt(ctx._h, n, _p(c), _p(_fr(rho)), _p(sv), _p(rv), _p(g), int(block_bits), _p(m), _p(c0)))
+    return [int(x) for x in m[:n, 0]], c0
+
+
+def verify_decryption(ctx: Context, ct, plain, svk: dict, gamma_abc_rest, proof) -> bool:
+    """verify_decryption_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:548-575); proof = decrypt's verify_c0."""
+    c = _a(ct, 12)
+    n = c.shape[0] - 2
+    pl = np.concatenate([_fr(int(x)) for x in plain]).reshape(-1, 4) if len(plain) else np.zeros((1, 4), np.uint64)
+    if len(plain) != n:
+        raise ValueError("Cipher text size should be equal to the plain text size (exclusive of 2 element in CT).")
+    ok = np.zeros(1, dtype=np.uint8)
+    ctx.check(ctx._lib.vsp_saver_verify_decryption(ctx._h, n, _p(c), _p(pl), _p(_a(svk["rho_g2"], 24)), _p(_a(svk["rho_sv_g2"], 24)),
+                                                   _p(_a(svk["rho_rhov_g2"], 24)), _p(_a(gamma_abc_rest, 12)), _p(_a(proof, 12)),
+                                                   _p(ok)))
+    return bool(ok[0])

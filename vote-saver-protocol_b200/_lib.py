@@ -140,6 +140,8 @@ SYMBOLS = [
     ("vsp_groth16_verify_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), _u64, _vp, _u64, _vp, _vp]),
     ("vsp_saver_verify_encryption_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), C.POINTER(SaverPubkeyDesc), _u64, _vp,
                                                  _vp, _u64, _vp, _vp]),
+    ("vsp_saver_decrypt", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp]),
+    ("vsp_saver_verify_decryption", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_codec_g1_compress", _int, [_vp, _vp]),
     ("vsp_codec_g2_compress", _int, [_vp, _vp]),
     ("vsp_codec_proof_write", _int, [_vp, _vp]),

@@ -331,6 +331,25 @@ const uint64_t G2_GENERATOR[24] = {
     0xe193548608b82801ULL, 0x923ac9cc3baca289ULL, 0x6d429a695160d12cULL, 0xadfd9baa8cbdd3a7ULL, 0x8cc9cdc6da2e351aULL, 0x0ce5d527727d6e11ULL,
     0xaaa9075ff05f79beULL, 0x3f370d275cec1da1ULL, 0x267492ab572e99abULL, 0xcb3e287e85a763afULL, 0x32acd2b02bc28b99ULL, 0x0606c4a02ea734ccULL};
 
+// -P for a canonical affine G1 point (host): y -> p - y
+const uint64_t FQ_MOD64[6] = {0xb9feffffffffaaabULL, 0x1eabfffeb153ffffULL, 0x6730d2a0f6b0f624ULL,
+                              0x64774b84f38512bfULL, 0x4b1ba7b6434bacd7ULL, 0x1a0111ea397fe69aULL};
+void g1_negate_host(uint64_t* out, const uint64_t* in) {
+    memcpy(out, in, 96);
+    bool zero = true;
+    for (int i = 0; i < 12; ++i) zero = zero && in[i] == 0;
+    if (zero) return;
+    unsigned __int128 borrow = 0;
+    for (int i = 0; i < 6; ++i) {
+        const unsigned __int128 d = (unsigned __int128)FQ_MOD64[i] - in[6 + i] - (uint64_t)borrow;
+        out[6 + i] = (uint64_t)d;
+        borrow = (d >> 64) & 1;
+    }
+    bool yzero = true;
+    for (int i = 0; i < 6; ++i) yzero = yzero && in[6 + i] == 0;
+    if (yzero) memset(out + 6, 0, 48);
+}
+
 int run_products(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_pts, const uint32_t* d_idx, unsigned pairs, unsigned n_checks,
                  const uint32_t* d_tables, const uint8_t* d_valid, uint64_t* d_gt, uint8_t* d_one) {
     if (!n_checks) return VSP_OK;
@@ -488,6 +507,123 @@ extern "C" int vsp_saver_verify_encryption_batch(vsp_ctx* ctx, const vsp_verific
     cudaSetDevice(ctx->device);
     try {
         return verify_impl(ctx, vk, pub->t_g2, pub->msg_size, k, cts, unencrypted_primary, n_unencrypted, proofs, ok_out);
+    } catch (const std::bad_alloc&) {
+        return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
+    }
+}
+
+extern "C" int vsp_g1_mul_batch(vsp_ctx* ctx, uint64_t n, const uint64_t* points, const uint64_t* scalars, uint64_t* out);
+
+// decrypt_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:401-441).  For every message slot j:
+//   dec_j = e(ct_j, rho_rhov_{j-1}) * e(ct_0, rho_sv_{j-1})^(-rho)  =  e(ct_j, rho_rhov_{j-1}) e(-rho ct_0, rho_sv_{j-1})
+//   m_j   = the exp in [0, 2^block_bits] with  dec_j == e(gamma_ABC.rest[j-1], rho_rhov_{j-1})^exp
+//                                                   == e(exp gamma_ABC.rest[j-1], rho_rhov_{j-1})
+// (bilinearity moves the GT powers onto G1, where they are small multiples; reduced pairings are canonical field
+// elements, so the equalities are the reference's).  verify_c0 = rho ct_0.  All pairings of a call run as one batch.
+extern "C" int vsp_saver_decrypt(vsp_ctx* ctx, uint64_t msg_size, const uint64_t* ct, const uint64_t rho[4],
+                                 const uint64_t* rho_sv_g2, const uint64_t* rho_rhov_g2, const uint64_t* gamma_abc_rest,
+                                 unsigned block_bits, uint64_t* m_out, uint64_t* verify_c0_out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (!ct || !rho || !verify_c0_out || (msg_size && (!rho_sv_g2 || !rho_rhov_g2 || !gamma_abc_rest || !m_out)))
+        return set_error(ctx, VSP_E_INVALID, "vsp_saver_decrypt: null argument");
+    if (block_bits == 0 || block_bits > 16 || msg_size > 4096) return set_error(ctx, VSP_E_INVALID, "vsp_saver_decrypt: bad size");
+    if (hostfr::geq(rho, hostfr::MOD)) return set_error(ctx, VSP_E_INVALID, "rho not reduced mod r");
+    try {
+        const uint64_t n = msg_size, E = (uint64_t(1) << block_bits);  // candidates exp = 0 .. E
+        // G1 multiples: rho ct_0, then exp * gamma_ABC.rest[j] for exp = 1 .. E
+        std::vector<uint64_t> pts(12 * (1 + n * E)), scs(4 * (1 + n * E), 0), mul(12 * (1 + n * E));
+        memcpy(&pts[0], ct, 96);
+        memcpy(&scs[0], rho, 32);
+        for (uint64_t j = 0; j < n; ++j)
+            for (uint64_t e = 1; e <= E; ++e) {
+                memcpy(&pts[12 * (1 + j * E + e - 1)], gamma_abc_rest + 12 * j, 96);
+                scs[4 * (1 + j * E + e - 1)] = e;
+            }
+        VSP_TRY(vsp_g1_mul_batch(ctx, 1 + n * E, pts.data(), scs.data(), mul.data()));
+        memcpy(verify_c0_out, &mul[0], 96);
+        if (n == 0) return VSP_OK;
+        uint64_t neg_c0[12];
+        g1_negate_host(neg_c0, &mul[0]);
+        // checks of 2 pairs: [dec_j] then [candidate (j, exp), exp = 1 .. E] (second pair at infinity)
+        const uint64_t checks = n * (1 + E);
+        std::vector<uint64_t> g1(checks * 2 * 12, 0), g2(checks * 2 * 24, 0), gt(checks * 72);
+        for (uint64_t j = 0; j < n; ++j) {
+            memcpy(&g1[(j * 2) * 12], ct + 12 * (j + 1), 96);
+            memcpy(&g2[(j * 2) * 24], rho_rhov_g2 + 24 * j, 192);
+            memcpy(&g1[(j * 2 + 1) * 12], neg_c0, 96);
+            memcpy(&g2[(j * 2 + 1) * 24], rho_sv_g2 + 24 * j, 192);
+            for (uint64_t e = 1; e <= E; ++e) {
+                const uint64_t c = n + j * E + e - 1;
+                memcpy(&g1[(c * 2) * 12], &mul[12 * (1 + j * E + e - 1)], 96);
+                memcpy(&g2[(c * 2) * 24], rho_rhov_g2 + 24 * j, 192);
+            }
+        }
+        VSP_TRY(vsp_pairing_products(ctx, checks, 2, g1.data(), g2.data(), gt.data(), nullptr));
+        uint64_t gt_one[72] = {0};
+        gt_one[0] = 1;
+        for (uint64_t j = 0; j < n; ++j) {
+            const uint64_t* dec = &gt[j * 72];
+            int64_t found = -1;
+            if (!memcmp(dec, gt_one, 576)) found = 0;
+            for (uint64_t e = 1; e <= E && found < 0; ++e)
+                if (!memcmp(dec, &gt[(n + j * E + e - 1) * 72], 576)) found = (int64_t)e;
+            if (found < 0) return set_error(ctx, VSP_E_INVALID, "Decryption failed.");  // the reference's assertion text (:435)
+            m_out[4 * j] = (uint64_t)found;
+            m_out[4 * j + 1] = m_out[4 * j + 2] = m_out[4 * j + 3] = 0;
+        }
+        return VSP_OK;
+    } catch (const std::bad_alloc&) {
+        return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
+    }
+}
+
+// verify_decryption_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:548-575): *ok_out = 1 iff
+//   e(proof, G2) == e(ct_0, rho_g2)   and for every slot i
+//   e(ct_i, rho_rhov_{i-1}) e(proof, rho_sv_{i-1})^-1 == e(gamma_ABC.rest[i-1], rho_rhov_{i-1})^(m_{i-1}),
+// each as a product that must be 1 (powers and inverses moved onto G1).
+extern "C" int vsp_saver_verify_decryption(vsp_ctx* ctx, uint64_t msg_size, const uint64_t* ct, const uint64_t* plain,
+                                           const uint64_t* rho_g2, const uint64_t* rho_sv_g2, const uint64_t* rho_rhov_g2,
+                                           const uint64_t* gamma_abc_rest, const uint64_t* proof, uint8_t* ok_out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (!ct || !rho_g2 || !proof || !ok_out || (msg_size && (!plain || !rho_sv_g2 || !rho_rhov_g2 || !gamma_abc_rest)))
+        return set_error(ctx, VSP_E_INVALID, "vsp_saver_verify_decryption: null argument");
+    if (msg_size > 4096) return set_error(ctx, VSP_E_INVALID, "msg_size too large");
+    for (uint64_t i = 0; i < msg_size; ++i)
+        if (hostfr::geq(plain + 4 * i, hostfr::MOD)) return set_error(ctx, VSP_E_INVALID, "plain text not reduced mod r");
+    try {
+        const uint64_t n = msg_size;
+        // -m_i gamma_ABC.rest[i]: scalars r - m_i
+        std::vector<uint64_t> sc(4 * (n ? n : 1)), mg(12 * (n ? n : 1));
+        for (uint64_t i = 0; i < n; ++i) {
+            hostfr::Fr4 m, z = hostfr::from_u64(0);
+            memcpy(m.v, plain + 4 * i, 32);
+            memcpy(&sc[4 * i], hostfr::sub(z, m).v, 32);
+        }
+        if (n) VSP_TRY(vsp_g1_mul_batch(ctx, n, gamma_abc_rest, sc.data(), mg.data()));
+        uint64_t neg_proof[12], neg_c0[12];
+        g1_negate_host(neg_proof, proof);
+        g1_negate_host(neg_c0, ct);
+        const uint64_t checks = n + 1;
+        std::vector<uint64_t> g1(checks * 3 * 12, 0), g2(checks * 3 * 24, 0);
+        std::vector<uint8_t> one(checks);
+        memcpy(&g1[0], proof, 96);
+        memcpy(&g2[0], G2_GENERATOR, 192);
+        memcpy(&g1[12], neg_c0, 96);
+        memcpy(&g2[24], rho_g2, 192);
+        for (uint64_t i = 0; i < n; ++i) {
+            const uint64_t c = (i + 1) * 3;
+            memcpy(&g1[c * 12], ct + 12 * (i + 1), 96);
+            memcpy(&g2[c * 24], rho_rhov_g2 + 24 * i, 192);
+            memcpy(&g1[(c + 1) * 12], neg_proof, 96);
+            memcpy(&g2[(c + 1) * 24], rho_sv_g2 + 24 * i, 192);
+            memcpy(&g1[(c + 2) * 12], &mg[12 * i], 96);
+            memcpy(&g2[(c + 2) * 24], rho_rhov_g2 + 24 * i, 192);
+        }
+        VSP_TRY(vsp_pairing_products(ctx, checks, 3, g1.data(), g2.data(), nullptr, one.data()));
+        uint8_t ok = 1;
+        for (uint64_t c = 0; c < checks; ++c) ok = ok && one[c];
+        *ok_out = ok;
+        return VSP_OK;
     } catch (const std::bad_alloc&) {
         return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
     }
