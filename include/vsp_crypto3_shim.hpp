@@ -641,6 +641,34 @@ namespace zk {
         const b200::fr_value r = b200::random_fr(e), s = b200::random_fr(e);
         return prove<ProofSystem>(pk, pubkey, primary_input, auxiliary_input, r_saver, r, s);
     }
+
+    // verify<ProofSystem>(vk, primary_input, proof) -> bool   (libs/marshalling/zk/test/r1cs_gg_ppzksnark.cpp:160-163)
+    template<typename ProofSystem>
+    bool verify(const typename ProofSystem::verification_key_type &vk,
+                const typename ProofSystem::primary_input_type &primary_input, const typename ProofSystem::proof_type &proof) {
+        if (vk.gamma_ABC_g1.rest.size() != primary_input.size())
+            throw std::invalid_argument("verify: primary input size does not match the verification key");
+        std::vector<b200::g1_value> gabc;
+        gabc.push_back(vk.gamma_ABC_g1.first);
+        gabc.insert(gabc.end(), vk.gamma_ABC_g1.rest.begin(), vk.gamma_ABC_g1.rest.end());
+        vsp_verification_key_t d;
+        d.alpha_g1 = vk.alpha_g1.l.data();
+        d.beta_g2 = vk.beta_g2.l.data();
+        d.gamma_g2 = vk.gamma_g2.l.data();
+        d.delta_g2 = vk.delta_g2.l.data();
+        d.gamma_ABC_count = gabc.size();
+        d.gamma_ABC_g1 = gabc[0].l.data();
+        std::uint64_t pr[48];
+        std::memcpy(pr, proof.g_A.l.data(), 96);
+        std::memcpy(pr + 12, proof.g_B.l.data(), 192);
+        std::memcpy(pr + 36, proof.g_C.l.data(), 96);
+        std::uint8_t ok = 0;
+        auto &dev = b200::device::instance();
+        dev.check(vsp_groth16_verify_batch(dev.ctx(), &d, 1, primary_input.empty() ? nullptr : primary_input[0].l.data(),
+                                           primary_input.size(), pr, &ok),
+                  "verify");
+        return ok != 0;
+    }
 }    // namespace zk
 
 // =====================================================================================================================
@@ -775,6 +803,119 @@ namespace pubkey {
         std::memcpy(out.second.g_B.l.data(), proof_out + 12, 192);
         std::memcpy(out.second.g_C.l.data(), proof_out + 36, 96);
         return out;
+    }
+
+    // ---- pairing side: verify_encryption / decrypt / verify_decryption ---------------------------------
+    namespace detail {
+        template<typename VK>
+        inline vsp_verification_key_t vk_descriptor(const VK &vk, std::vector<b200::g1_value> &gabc) {
+            gabc.clear();
+            gabc.push_back(vk.gamma_ABC_g1.first);
+            gabc.insert(gabc.end(), vk.gamma_ABC_g1.rest.begin(), vk.gamma_ABC_g1.rest.end());
+            vsp_verification_key_t d;
+            d.alpha_g1 = vk.alpha_g1.l.data();
+            d.beta_g2 = vk.beta_g2.l.data();
+            d.gamma_g2 = vk.gamma_g2.l.data();
+            d.delta_g2 = vk.delta_g2.l.data();
+            d.gamma_ABC_count = gabc.size();
+            d.gamma_ABC_g1 = gabc[0].l.data();
+            return d;
+        }
+        template<typename Proof>
+        inline void proof_limbs(const Proof &p, std::uint64_t out[48]) {
+            std::memcpy(out, p.g_A.l.data(), 96);
+            std::memcpy(out + 12, p.g_B.l.data(), 192);
+            std::memcpy(out + 36, p.g_C.l.data(), 96);
+        }
+    }    // namespace detail
+
+    template<typename Scheme>
+    struct verify_encryption_init_params {    // verify_encryption_op::init_params_type, elgamal_verifiable.hpp:453-458
+        const public_key<Scheme> &pubkey;
+        const typename Scheme::proof_system_type::verification_key_type &gg_vk;
+        const typename Scheme::proof_system_type::proof_type &proof;
+        const typename Scheme::proof_system_type::primary_input_type &unencrypted_primary_input;
+    };
+    // verify_encryption<Scheme>(cipher_text, {pubkey, gg_vk, proof, unencrypted_primary_input}) -> bool
+    //   verify_encryption_op::process, elgamal_verifiable.hpp:486-490; called at bin/cli common.hpp:1164-1168
+    template<typename Scheme, typename CipherRange>
+    bool verify_encryption(const CipherRange &cipher_text, const verify_encryption_init_params<Scheme> &p) {
+        const std::vector<typename Scheme::g1_value_type> ct(std::begin(cipher_text), std::end(cipher_text));
+        if (ct.size() != p.pubkey.delta_s_g1.size() + 2 || p.pubkey.t_g2.size() + 1 != ct.size())
+            throw std::invalid_argument("Cipher text size should match the public key (exclusive of 2 elements in CT).");
+        std::vector<b200::g1_value> gabc;
+        const vsp_verification_key_t vk = detail::vk_descriptor(p.gg_vk, gabc);
+        const vsp_saver_pubkey_t desc = p.pubkey.descriptor();
+        std::uint64_t proof[48];
+        detail::proof_limbs(p.proof, proof);
+        std::uint8_t ok = 0;
+        auto &d = b200::device::instance();
+        const auto &x = p.unencrypted_primary_input;
+        d.check(vsp_saver_verify_encryption_batch(d.ctx(), &vk, &desc, 1, ct[0].l.data(), x.empty() ? nullptr : x[0].l.data(),
+                                                  x.size(), proof, &ok),
+                "verify_encryption");
+        return ok != 0;
+    }
+
+    template<typename Scheme>
+    struct decrypt_init_params {    // decrypt_op::init_params_type, elgamal_verifiable.hpp:371-375
+        const private_key<Scheme> &privkey;
+        const verification_key<Scheme> &vk;
+        const typename Scheme::proof_system_type::keypair_type &gg_keypair;
+    };
+    // decrypt<Scheme, modes::verifiable_encryption<Scheme>>(cipher_text, {privkey, vk, gg_keypair})
+    //   -> (plain text, decryption proof = rho * ct[0])    decrypt_op::process, elgamal_verifiable.hpp:401-441;
+    //   called on the tally's aggregated cipher text at bin/cli common.hpp:1221-1223.  BlockBits: scheme_type::block_bits.
+    template<typename Scheme, typename Mode, std::size_t BlockBits = 4, typename CipherRange>
+    std::pair<std::vector<typename Scheme::scalar_field_type::value_type>, typename Scheme::g1_value_type>
+        decrypt(const CipherRange &cipher_text, const decrypt_init_params<Scheme> &p) {
+        typedef typename Scheme::scalar_field_type::value_type fr;
+        const std::vector<typename Scheme::g1_value_type> ct(std::begin(cipher_text), std::end(cipher_text));
+        const auto &gabc = p.gg_keypair.second.gamma_ABC_g1.rest;
+        // the reference's BOOST_ASSERT_MSG checks, elgamal_verifiable.hpp:403-412
+        if (ct.size() < 2 || !(gabc.size() > ct.size() - 2))
+            throw std::invalid_argument("Array of gammas in vk should be longer than the cipher text (exclusive of 2 element in CT).");
+        if (ct.size() - 2 != p.vk.rho_sv_g2.size() || ct.size() - 2 != p.vk.rho_rhov_g2.size())
+            throw std::invalid_argument("Cipher text size should be equal to the rho_sv_g2 / rho_rhov_g2 array size from vk.");
+        const std::size_t n = ct.size() - 2;
+        std::pair<std::vector<fr>, typename Scheme::g1_value_type> out;
+        out.first.resize(n);
+        auto &d = b200::device::instance();
+        d.check(vsp_saver_decrypt(d.ctx(), n, ct[0].l.data(), p.privkey.rho.l.data(), n ? p.vk.rho_sv_g2[0].l.data() : nullptr,
+                                  n ? p.vk.rho_rhov_g2[0].l.data() : nullptr, n ? gabc[0].l.data() : nullptr,
+                                  static_cast<unsigned>(BlockBits), n ? out.first[0].l.data() : nullptr, out.second.l.data()),
+                "decrypt");
+        return out;
+    }
+
+    template<typename Scheme>
+    struct verify_decryption_init_params {    // verify_decryption_op::init_params_type, elgamal_verifiable.hpp:506-510
+        const verification_key<Scheme> &vk;
+        const typename Scheme::proof_system_type::keypair_type &gg_keypair;
+        const typename Scheme::g1_value_type &proof;
+    };
+    // verify_decryption<Scheme>(cipher_text, plain_text, {vk, gg_keypair, proof}) -> bool
+    //   verify_decryption_op::process, elgamal_verifiable.hpp:548-575; called at bin/cli common.hpp:1282-1283
+    template<typename Scheme, typename CipherRange, typename PlainRange>
+    bool verify_decryption(const CipherRange &cipher_text, const PlainRange &plain_text,
+                           const verify_decryption_init_params<Scheme> &p) {
+        typedef typename Scheme::scalar_field_type::value_type fr;
+        const std::vector<typename Scheme::g1_value_type> ct(std::begin(cipher_text), std::end(cipher_text));
+        const std::vector<fr> m(std::begin(plain_text), std::end(plain_text));
+        const auto &gabc = p.gg_keypair.second.gamma_ABC_g1.rest;
+        if (m.size() + 2 != ct.size())
+            throw std::invalid_argument("Cipher text size should be equal to the plain text size (exclusive of 2 element in CT).");
+        if (!(gabc.size() > m.size())) throw std::invalid_argument("Array of gammas in vk should be longer than the plain text.");
+        if (p.vk.rho_sv_g2.size() < m.size() || p.vk.rho_rhov_g2.size() < m.size())
+            throw std::invalid_argument("verification key shorter than the plain text");
+        std::uint8_t ok = 0;
+        auto &d = b200::device::instance();
+        const std::size_t n = m.size();
+        d.check(vsp_saver_verify_decryption(d.ctx(), n, ct[0].l.data(), n ? m[0].l.data() : nullptr, p.vk.rho_g2.l.data(),
+                                            n ? p.vk.rho_sv_g2[0].l.data() : nullptr, n ? p.vk.rho_rhov_g2[0].l.data() : nullptr,
+                                            n ? gabc[0].l.data() : nullptr, p.proof.l.data(), &ok),
+                "verify_decryption");
+        return ok != 0;
     }
 }    // namespace pubkey
 

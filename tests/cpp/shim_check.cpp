@@ -243,6 +243,34 @@ int main(int argc, char **argv) {
             expect(std::get<2>(keys).rho_g2 == one<g2>("kg_rho_g2") && std::get<2>(keys).rho_sv_g2 == vec<g2>("kg_rho_sv_g2") &&
                        std::get<2>(keys).rho_rhov_g2 == vec<g2>("kg_rho_rhov_g2"),
                    "pubkey::generate_keypair verification key");
+            // the rest of the protocol on those keys (common.hpp:1132-1168, 1221-1223, 1282-1283): encrypt, verify_encryption,
+            // decrypt, verify_decryption
+            {
+                auto kprim = vec<fr>("kg_primary"), kaux = vec<fr>("kg_aux");
+                std::vector<fr> m_field(kprim.begin(), kprim.begin() + msg);
+                const fr rs = one<fr>("r_saver");
+                auto ct = pubkey::encrypt<scheme_type, pubkey::modes::verifiable_encryption<scheme_type>>(
+                    m_field, {rs, spub, kp, kprim, kaux, nullptr, nullptr});
+                proof_system_type::primary_input_type rest(kprim.begin() + msg, kprim.end());
+                expect(pubkey::verify_encryption<scheme_type>(ct.first, {spub, kp.second, ct.second, rest}),
+                       "pubkey::verify_encryption accepts the ballot");
+                auto bad_ct = ct.first;
+                bad_ct[1] = bad_ct[2];
+                expect(!pubkey::verify_encryption<scheme_type>(bad_ct, {spub, kp.second, ct.second, rest}),
+                       "pubkey::verify_encryption rejects a tampered cipher text");
+                typedef zk::snark::r1cs_gg_ppzksnark<curve_type> basic_system;
+                auto bp = zk::prove<basic_system>(kp.first, kprim, kaux);
+                expect(zk::verify<basic_system>(kp.second, kprim, bp), "zk::verify accepts a basic-mode proof");
+                auto dec = pubkey::decrypt<scheme_type, pubkey::modes::verifiable_encryption<scheme_type>, 4>(
+                    ct.first, {std::get<1>(keys), std::get<2>(keys), kp});
+                expect(dec.first == m_field, "pubkey::decrypt recovers the plain text");
+                expect(pubkey::verify_decryption<scheme_type>(ct.first, dec.first, {std::get<2>(keys), kp, dec.second}),
+                       "pubkey::verify_decryption accepts");
+                auto wrong = dec.first;
+                wrong[0].l[0] ^= 1;
+                expect(!pubkey::verify_decryption<scheme_type>(ct.first, wrong, {std::get<2>(keys), kp, dec.second}),
+                       "pubkey::verify_decryption rejects a wrong plain text");
+            }
             rnd.pop_back();
             expect_invalid(
                 [&] {

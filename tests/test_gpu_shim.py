@@ -71,7 +71,8 @@ def write_fixture(path: str):
     rec["rnd"] = cref.ints_to_limbs(rnd, 4)
     rec["rerand_ct"], rec["rerand_proof"] = cref.saver_rerandomize(opub, arr["delta_g2"], rnd, ct, rec["proof_enc"])
     # key generation (zk::generate, pubkey::generate_keypair) on a small circuit, expected values from the Python oracle
-    kcs, _kp, _ka = synthetic_r1cs(12, 5, seed=31)
+    kcs, _kp, _ka = synthetic_r1cs(12, 5, seed=31, binary=True)  # bit witness: message slots within decrypt's search range
+    rec["kg_primary"], rec["kg_aux"] = cref.ints_to_limbs(_kp, 4), cref.ints_to_limbs(_ka, 4)
     tox = [rng.randrange(1, o.R) for _ in range(5)]
     opk, ovk = o.groth16_generate(kcs, None, toxic=tox)
     karr = fx.pk_arrays(opk)

@@ -160,16 +160,26 @@ __global__ void __launch_bounds__(64) k_g2_line_table(const uint64_t* __restrict
     }
 }
 
-// one thread per product: f = conj( prod_j miller(P_j, table_j) ) with the squarings shared.
-//   pts: n_checks x pairs G1 affine (Montgomery); tidx: n_checks x pairs table index (0xffffffff or an invalid table or
-//   an infinite P: the pair contributes 1)
+// A product of pairings is cut into segments of at most SEG_PAIRS pairs; one thread runs the Miller loop of one segment
+// (squarings shared inside it) and the final exponentiation multiplies a check's segments together, so a 27-pairing
+// ciphertext check occupies four threads instead of one.
+struct Span {
+    uint32_t first, count;
+};
+constexpr unsigned SEG_PAIRS = 7;
+
+// one thread per segment: f = conj( prod_j miller(P_j, table_j) ) over the segment's pairs.
+//   pts: flat G1 affine (Montgomery); tidx: flat table index (0xffffffff, an invalid table or an infinite P: the pair
+//   contributes 1)
 __global__ void __launch_bounds__(64) k_multi_miller(const uint32_t* __restrict__ pts, const uint32_t* __restrict__ tidx,
-                                                     unsigned pairs, unsigned n_checks, const uint32_t* __restrict__ tables,
-                                                     const uint8_t* __restrict__ valid, uint32_t* __restrict__ f_out) {
+                                                     const Span* __restrict__ segs, unsigned n_segs,
+                                                     const uint32_t* __restrict__ tables, const uint8_t* __restrict__ valid,
+                                                     uint32_t* __restrict__ f_out) {
     const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n_checks) return;
-    const uint32_t* my_pts = pts + uint64_t(c) * pairs * 24;
-    const uint32_t* my_idx = tidx + uint64_t(c) * pairs;
+    if (c >= n_segs) return;
+    const Span sg = segs[c];
+    const uint32_t* my_pts = pts + uint64_t(sg.first) * 24;
+    const uint32_t* my_idx = tidx + sg.first;
     Fq12 f = f12_one();
     int k = 0;
 #pragma unroll 1
@@ -179,7 +189,7 @@ __global__ void __launch_bounds__(64) k_multi_miller(const uint32_t* __restrict_
 #pragma unroll 1
         for (int l = 0; l < lines; ++l, ++k) {
 #pragma unroll 1
-            for (unsigned j = 0; j < pairs; ++j) {
+            for (unsigned j = 0; j < sg.count; ++j) {
                 const uint32_t t = my_idx[j];
                 if (t == 0xffffffffu || !valid[t]) continue;
                 const G1Affine p = G1Affine::load(my_pts + j * 24);
@@ -195,11 +205,13 @@ __global__ void __launch_bounds__(64) k_multi_miller(const uint32_t* __restrict_
 }
 
 // one thread per product: g = (conj(f) / f)^((p^6+1)/r); gt_out (optional): canonical Fq12, 72 u64 limbs in tower order
-__global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f_in, unsigned n, uint64_t* __restrict__ gt_out,
-                                                  uint8_t* __restrict__ is_one) {
+__global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f_in, const Span* __restrict__ checks, unsigned n,
+                                                  uint64_t* __restrict__ gt_out, uint8_t* __restrict__ is_one) {
     const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n) return;
-    const Fq12 f = f12_load(f_in + uint64_t(c) * 144);
+    const Span ck = checks[c];
+    Fq12 f = f12_load(f_in + uint64_t(ck.first) * 144);
+    for (unsigned q = 1; q < ck.count; ++q) f12_mul(f, f12_load(f_in + uint64_t(ck.first + q) * 144));
     Fq12 base = f12_inv(f);
     {
         Fq12 cj = f;
@@ -350,22 +362,43 @@ void g1_negate_host(uint64_t* out, const uint64_t* in) {
     if (yzero) memset(out + 6, 0, 48);
 }
 
-int run_products(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_pts, const uint32_t* d_idx, unsigned pairs, unsigned n_checks,
+// spans of a batch of checks over a flat pair array: check c covers pairs [first[c], first[c] + count[c])
+struct ProductPlan {
+    std::vector<Span> segs, checks;
+    void add_check(uint32_t first, uint32_t count) {
+        Span ck{(uint32_t)segs.size(), 0};
+        for (uint32_t o = 0; o < count || o == 0; o += SEG_PAIRS) {
+            segs.push_back(Span{first + o, count - o < SEG_PAIRS ? count - o : SEG_PAIRS});
+            ++ck.count;
+            if (count == 0) break;
+        }
+        checks.push_back(ck);
+    }
+};
+
+int run_products(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_pts, const uint32_t* d_idx, const ProductPlan& plan,
                  const uint32_t* d_tables, const uint8_t* d_valid, uint64_t* d_gt, uint8_t* d_one) {
+    const unsigned n_segs = (unsigned)plan.segs.size(), n_checks = (unsigned)plan.checks.size();
     if (!n_checks) return VSP_OK;
-    DevBuf f;
-    VSP_TRY(f.alloc(ctx, size_t(n_checks) * 576, s));
-    VSP_LAUNCH_K(ctx, KC_OTHER, k_multi_miller, (n_checks + 63) / 64, 64, 0, s, d_pts, d_idx, pairs, n_checks, d_tables, d_valid,
-                 f.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_OTHER, k_final_exp, (n_checks + 63) / 64, 64, 0, s, f.as<uint32_t>(), n_checks, d_gt, d_one);
+    DevBuf f, d_segs, d_checks;
+    VSP_TRY(f.alloc(ctx, size_t(n_segs) * 576, s));
+    VSP_TRY(d_segs.alloc(ctx, size_t(n_segs) * sizeof(Span), s));
+    VSP_TRY(d_checks.alloc(ctx, size_t(n_checks) * sizeof(Span), s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_segs.p, plan.segs.data(), size_t(n_segs) * sizeof(Span), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_checks.p, plan.checks.data(), size_t(n_checks) * sizeof(Span), cudaMemcpyHostToDevice, s));
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_multi_miller, (n_segs + 63) / 64, 64, 0, s, d_pts, d_idx, d_segs.as<Span>(), n_segs, d_tables,
+                 d_valid, f.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_final_exp, (n_checks + 63) / 64, 64, 0, s, f.as<uint32_t>(), d_checks.as<Span>(), n_checks, d_gt,
+                 d_one);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));  // the plan's host vectors are the copies' source
     return VSP_OK;
 }
 
 int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* t_g2, uint64_t msg_size, uint64_t k,
                 const uint64_t* cts, const uint64_t* xs, uint64_t n_x, const uint64_t* proofs, uint8_t* ok) {
     if (k == 0) return VSP_OK;
-    if (k > (1u << 24) || msg_size > 4096 || n_x > (1u << 20)) return set_error(ctx, VSP_E_INVALID, "verify: batch too large");
+    if (k > (1u << 20) || msg_size > 1024 || n_x > (1u << 20)) return set_error(ctx, VSP_E_INVALID, "verify: batch too large");
     const bool has_ct = cts != nullptr;
     const unsigned n = has_ct ? (unsigned)msg_size : 0, K = (unsigned)k;
     if (vk->gamma_ABC_count != 1 + uint64_t(n) + n_x)
@@ -388,7 +421,7 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
     memcpy(&hq[pos], vk->beta_g2, 192);
     memcpy(&hq[pos + 24], vk->gamma_g2, 192);
     memcpy(&hq[pos + 48], vk->delta_g2, 192);
-    DevBuf d_q, d_tab, d_valid, d_ct, d_pr, d_x, d_gabc, d_alpha, d_p1, d_i1, d_p2, d_i2, d_one;
+    DevBuf d_q, d_tab, d_valid, d_ct, d_pr, d_x, d_gabc, d_alpha, d_p2, d_i2, d_one;
     VSP_TRY(d_q.alloc(ctx, hq.size() * 8, s));
     VSP_TRY(d_tab.alloc(ctx, size_t(n_q) * TABLE_LIMBS * 4, s));
     VSP_TRY(d_valid.alloc(ctx, n_q, s));
@@ -396,8 +429,10 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
     VSP_TRY(d_x.alloc(ctx, size_t(K) * n_x * 32, s));
     VSP_TRY(d_gabc.alloc(ctx, size_t(vk->gamma_ABC_count) * 96, s));
     VSP_TRY(d_alpha.alloc(ctx, 96, s));
-    VSP_TRY(d_p2.alloc(ctx, size_t(K) * 4 * 96, s));
-    VSP_TRY(d_i2.alloc(ctx, size_t(K) * 4 * 4, s));
+    // flat pair arrays: K x 4 pairs of the Groth16 checks, then K x (n + 2) pairs of the ciphertext checks
+    const size_t n_pairs = size_t(K) * 4 + (has_ct ? size_t(K) * (n + 2) : 0);
+    VSP_TRY(d_p2.alloc(ctx, n_pairs * 96, s));
+    VSP_TRY(d_i2.alloc(ctx, n_pairs * 4, s));
     VSP_TRY(d_one.alloc(ctx, size_t(K) * 3, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_q.p, hq.data(), hq.size() * 8, cudaMemcpyHostToDevice, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_pr.p, proofs, size_t(K) * 384, cudaMemcpyHostToDevice, s));
@@ -406,8 +441,6 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_alpha.p, vk->alpha_g1, 96, cudaMemcpyHostToDevice, s));
     if (has_ct) {
         VSP_TRY(d_ct.alloc(ctx, size_t(K) * (n + 2) * 96, s));
-        VSP_TRY(d_p1.alloc(ctx, size_t(K) * (n + 2) * 96, s));
-        VSP_TRY(d_i1.alloc(ctx, size_t(K) * (n + 2) * 4, s));
         VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_ct.p, cts, size_t(K) * (n + 2) * 96, cudaMemcpyHostToDevice, s));
     }
     VSP_LAUNCH_K(ctx, KC_OTHER, k_g2_line_table, (n_q + 63) / 64, 64, 0, s, d_q.as<uint64_t>(), n_q, d_tab.as<uint32_t>(),
@@ -423,18 +456,19 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
     a.n_x = (unsigned)n_x;
     a.has_ct = has_ct ? 1 : 0;
     a.fixed_base = K;
-    a.pts1 = has_ct ? d_p1.as<uint32_t>() : nullptr;
-    a.idx1 = has_ct ? d_i1.as<uint32_t>() : nullptr;
+    a.pts1 = has_ct ? d_p2.as<uint32_t>() + size_t(K) * 4 * 24 : nullptr;
+    a.idx1 = has_ct ? d_i2.as<uint32_t>() + size_t(K) * 4 : nullptr;
     a.pts2 = d_p2.as<uint32_t>();
     a.idx2 = d_i2.as<uint32_t>();
     VSP_LAUNCH_K(ctx, KC_OTHER, k_verify_prepare, (K + 63) / 64, 64, 0, s, a);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     uint8_t* one = d_one.as<uint8_t>();
-    VSP_TRY(run_products(ctx, s, d_p2.as<uint32_t>(), d_i2.as<uint32_t>(), 4, K, d_tab.as<uint32_t>(), d_valid.as<uint8_t>(), nullptr,
-                         one));
+    ProductPlan plan;  // checks [0, K): Groth16 equation; [K, 2K): ciphertext well-formedness
+    for (unsigned b = 0; b < K; ++b) plan.add_check(b * 4, 4);
     if (has_ct)
-        VSP_TRY(run_products(ctx, s, d_p1.as<uint32_t>(), d_i1.as<uint32_t>(), n + 2, K, d_tab.as<uint32_t>(),
-                             d_valid.as<uint8_t>(), nullptr, one + K));
+        for (unsigned b = 0; b < K; ++b) plan.add_check(K * 4 + b * (n + 2), n + 2);
+    VSP_TRY(run_products(ctx, s, d_p2.as<uint32_t>(), d_i2.as<uint32_t>(), plan, d_tab.as<uint32_t>(), d_valid.as<uint8_t>(),
+                         nullptr, one));
     VSP_LAUNCH_K(ctx, KC_OTHER, k_and_flags, (K + 127) / 128, 128, 0, s, one, has_ct ? one + K : nullptr, K, one + 2 * K);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(ok, one + 2 * K, K, cudaMemcpyDeviceToHost, s));
@@ -475,8 +509,10 @@ extern "C" int vsp_pairing_products(vsp_ctx* ctx, uint64_t n_checks, uint64_t pa
     VSP_LAUNCH_K(ctx, KC_OTHER, k_g2_line_table, (unsigned)((n + 63) / 64), 64, 0, s, d_g2.as<uint64_t>(), (unsigned)n,
                  d_tab.as<uint32_t>(), d_valid.as<uint8_t>());
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    VSP_TRY(run_products(ctx, s, d_pts.as<uint32_t>(), d_idx.as<uint32_t>(), (unsigned)pairs, (unsigned)n_checks, d_tab.as<uint32_t>(),
-                         d_valid.as<uint8_t>(), d_gt.as<uint64_t>(), d_one.as<uint8_t>()));
+    ProductPlan plan;
+    for (uint64_t c = 0; c < n_checks; ++c) plan.add_check((uint32_t)(c * pairs), (uint32_t)pairs);
+    VSP_TRY(run_products(ctx, s, d_pts.as<uint32_t>(), d_idx.as<uint32_t>(), plan, d_tab.as<uint32_t>(), d_valid.as<uint8_t>(),
+                         d_gt.as<uint64_t>(), d_one.as<uint8_t>()));
     if (gt_out) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(gt_out, d_gt.p, n_checks * 576, cudaMemcpyDeviceToHost, s));
     if (is_one) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(is_one, d_one.p, n_checks, cudaMemcpyDeviceToHost, s));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
