@@ -107,6 +107,11 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
         if (ctx->side[i]) cudaStreamDestroy(ctx->side[i]);
         if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
     }
+    if (ctx->copy) {
+        cudaStreamSynchronize(ctx->copy);
+        cudaStreamDestroy(ctx->copy);
+        ctx->copy = nullptr;
+    }
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_main) cudaEventDestroy(ctx->ev_main);
     for (int i = 0; i < 2; ++i) {

@@ -54,6 +54,7 @@ struct vsp_ctx {
     vsp::NttTables* ntt = nullptr;  // lazily built twiddle tables (ntt.cu)
     // side streams + events for overlapping independent multiexps inside vsp_prove
     cudaStream_t side[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t copy = nullptr;  // host -> device witness prefetch of the next chunk (prover.cu), created on first use
     cudaEvent_t ev_fork = nullptr;
     cudaEvent_t ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
     // double-buffered scratch of the proof-assembly tail (prover.cu): the tail of chunk i runs on side[1] while the

@@ -650,6 +650,81 @@ static int upload_witness(vsp_ctx* ctx, const vsp_pk* pk, unsigned B, const uint
     return VSP_OK;
 }
 
+// Host witnesses of a batch, one chunk ahead: chunk c + 1 is copied on the context's copy stream into the other of two
+// device buffers while chunk c is being proved, so the H2D transfer (2 MB per ballot at m = 2^16) leaves the critical
+// path of the host-buffer entry points.  acquire(c) returns chunk c's assignments once main-stream work may read them
+// (the wait is a stream dependency, not a host block); release(c) marks the buffer reusable after main-stream order.
+struct WitnessPrefetch {
+    vsp_ctx* ctx;
+    const vsp_pk* pk;
+    const uint64_t *primary, *aux;
+    uint64_t k;
+    unsigned chunk;
+    DevBuf buf[2];
+    cudaEvent_t up[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr};
+    bool used[2] = {false, false};
+    cudaStream_t cs = nullptr;
+    uint64_t issued = 0;  // chunks whose upload has been enqueued
+
+    WitnessPrefetch(vsp_ctx* c, const vsp_pk* p, const uint64_t* pr, const uint64_t* ax, uint64_t kk, unsigned ch)
+        : ctx(c), pk(p), primary(pr), aux(ax), k(kk), chunk(ch) {}
+    ~WitnessPrefetch() {
+        for (int i = 0; i < 2; ++i) {
+            if (up[i]) cudaEventDestroy(up[i]);
+            if (freed[i]) cudaEventDestroy(freed[i]);
+        }
+    }
+    uint64_t n_chunks() const { return (k + chunk - 1) / chunk; }
+    int init() {
+        if (!ctx->copy && cudaStreamCreateWithFlags(&ctx->copy, cudaStreamNonBlocking) != cudaSuccess)
+            return set_error(ctx, VSP_E_CUDA, "cudaStreamCreate(copy) failed");
+        cs = ctx->prof.on ? ctx->stream : ctx->copy;
+        const uint64_t stride = pk->nv + 1;
+        const unsigned nbuf = n_chunks() > 1 ? 2 : 1;
+        for (unsigned i = 0; i < nbuf; ++i) {
+            const uint64_t B = (i == 0) ? (k < chunk ? k : chunk) : chunk;
+            VSP_TRY(buf[i].alloc(ctx, B * stride * 32, ctx->stream));
+            VSP_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&up[i], cudaEventDisableTiming));
+            VSP_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming));
+        }
+        // the buffers come from the main stream's pool: order the copy stream after the allocation
+        VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_main, ctx->stream));
+        VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(cs, ctx->ev_main, 0));
+        return issue();
+    }
+    int issue() {
+        if (issued >= n_chunks()) return VSP_OK;
+        const uint64_t c = issued, i0 = c * chunk;
+        const unsigned slot = (unsigned)(c & 1), B = (unsigned)((k - i0 < chunk) ? (k - i0) : chunk);
+        const uint64_t stride = pk->nv + 1;
+        if (used[slot]) VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(cs, freed[slot], 0));
+        char* d = buf[slot].as<char>();
+        VSP_LAUNCH_K(ctx, KC_QAP, k_set_one, (B + 127) / 128, 128, 0, cs, buf[slot].as<uint32_t>(), stride, B);
+        VSP_CUDA_CHECK(ctx, cudaGetLastError());
+        if (pk->ni)
+            VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d + 32, stride * 32, primary + 4 * pk->ni * i0, pk->ni * 32, pk->ni * 32, B,
+                                                  cudaMemcpyHostToDevice, cs));
+        if (pk->na)
+            VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d + 32 + pk->ni * 32, stride * 32, aux + 4 * pk->na * i0, pk->na * 32,
+                                                  pk->na * 32, B, cudaMemcpyHostToDevice, cs));
+        VSP_CUDA_CHECK(ctx, cudaEventRecord(up[slot], cs));
+        used[slot] = true;
+        ++issued;
+        return VSP_OK;
+    }
+    // chunk c's assignments; also enqueues the upload of chunk c + 1
+    int acquire(uint64_t c, const uint32_t** w) {
+        const unsigned slot = (unsigned)(c & 1);
+        VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, up[slot], 0));
+        *w = buf[slot].as<uint32_t>();
+        return VSP_OK;
+    }
+    int release(uint64_t c) {
+        VSP_CUDA_CHECK(ctx, cudaEventRecord(freed[c & 1], ctx->stream));
+        return issue();  // the next-but-one chunk reuses this buffer
+    }
+};
+
 static bool fr_reduced(const uint64_t* x) { return !hostfr::geq(x, hostfr::MOD); }
 
 // make fx1tab = {delta_g1, gamma_inv}: rebuilt only when a different gamma_inverse_sum_s_g1 arrives
@@ -854,18 +929,17 @@ static int prove_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, uint64_t k, const u
     vsp_pk* pk = const_cast<vsp_pk*>(cpk);  // the gamma_inv table cache is the only mutable part
     const uint64_t stride = pk->nv + 1;
     const unsigned chunk = batch_chunk();
-    for (uint64_t i = 0; i < k; i += chunk) {
+    WitnessPrefetch pre(ctx, pk, primary, aux, k, chunk);
+    if (!d_assignments) VSP_TRY(pre.init());
+    for (uint64_t i = 0, c = 0; i < k; i += chunk, ++c) {
         const unsigned B = (unsigned)((k - i < chunk) ? (k - i) : chunk);
-        DevBuf d_w;
         const uint32_t* w;
-        if (d_assignments) {
+        if (d_assignments)
             w = reinterpret_cast<const uint32_t*>(d_assignments + 4 * stride * i);
-        } else {
-            VSP_TRY(upload_witness(ctx, pk, B, primary ? primary + 4 * pk->ni * i : nullptr,
-                                   aux ? aux + 4 * pk->na * i : nullptr, d_w));
-            w = d_w.as<uint32_t>();
-        }
+        else
+            VSP_TRY(pre.acquire(c, &w));
         VSP_TRY(prove_chunk(ctx, pk, B, w, stride, rs + 12 * i, gamma_inverse_sum_s_g1, d_proofs + 48 * i));
+        if (!d_assignments) VSP_TRY(pre.release(c));
     }
     return join_tails(ctx);
 }
@@ -1269,16 +1343,15 @@ static int saver_encrypt_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, const vsp_s
     const uint64_t stride = pk->nv + 1;
     const unsigned chunk = batch_chunk();
     const uint64_t ct_limbs = uint64_t(sp->n + 2) * 12;
-    for (uint64_t i = 0; i < k; i += chunk) {
+    WitnessPrefetch pre(ctx, pk, primary, aux, k, chunk);
+    if (!d_assignments) VSP_TRY(pre.init());
+    for (uint64_t i = 0, c = 0; i < k; i += chunk, ++c) {
         const unsigned B = (unsigned)((k - i < chunk) ? (k - i) : chunk);
-        DevBuf d_w;
         const uint32_t* w;
-        if (d_assignments) {
+        if (d_assignments)
             w = reinterpret_cast<const uint32_t*>(d_assignments + 4 * stride * i);
-        } else {
-            VSP_TRY(upload_witness(ctx, pk, B, primary + 4 * pk->ni * i, aux ? aux + 4 * pk->na * i : nullptr, d_w));
-            w = d_w.as<uint32_t>();
-        }
+        else
+            VSP_TRY(pre.acquire(c, &w));
         // the ciphertext runs on side stream 0 beside the proof
         VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], ctx->stream));
         VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 0), ctx->ev_join[0], 0));
@@ -1286,6 +1359,7 @@ static int saver_encrypt_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, const vsp_s
         VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[0], side_stream(ctx, 0)));
         VSP_TRY(prove_chunk(ctx, pk, B, w, stride, rs + 12 * i, sp->gamma_inv, d_proofs + 48 * i));
         VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[0], 0));
+        if (!d_assignments) VSP_TRY(pre.release(c));
     }
     return join_tails(ctx);
 }
