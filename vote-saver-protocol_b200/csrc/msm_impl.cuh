@@ -50,7 +50,7 @@ struct MsmPlan {
 // 1. digits + histogram
 // ---------------------------------------------------------------------------------------------
 __global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t scalar_stride, MsmPlan p,
-                             uint32_t* __restrict__ keys, uint32_t* __restrict__ counts) {
+                             uint32_t* __restrict__ keys, uint32_t* __restrict__ counts, int count_here) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const unsigned b = blockIdx.y;
     if (i >= n) return;
@@ -83,7 +83,7 @@ __global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, u
             if (d) key = (set << p.nb_log) + d - 1u;
         }
         keys[(uint64_t(b) * p.windows + w) * n + i] = key;
-        if (key != KEY_NONE) atomicAdd(&counts[key & 0x7fffffffu], 1u);
+        if (count_here && key != KEY_NONE) atomicAdd(&counts[key & 0x7fffffffu], 1u);
     }
 }
 
@@ -197,6 +197,91 @@ __global__ void k_msm_scatter(const uint32_t* __restrict__ keys, uint64_t total,
     const uint32_t w = (uint32_t)(row % p.windows);
     sorted[pos] = (uint32_t)(i + w * p.stride) | (key & 0x80000000u);  // index into the window table
 }
+
+// Counting sort with the counters in shared memory.  With a window table a ballot owns ONE bucket set of 2^(c-1) <=
+// 32,768 buckets, i.e. <= 128 KB of 32-bit counters: a CTA keeps them on chip, so the two passes over the keys
+// (histogram, then scatter with running cursors) cost shared-memory atomics instead of one L2 atomic round trip per
+// key (k_msm_scatter: 173 cycles of long-scoreboard stall per issue in the round-1 ncu capture).  The keys of ballot b
+// are the contiguous range [b W n, (b + 1) W n); `split` CTAs share a ballot, each taking a contiguous slice, and
+// leave their slice's histogram in hist_split so the scatter pass can start each slice's cursors after the slices
+// before it.  Order inside a bucket is arbitrary, as it already was: bucket sums do not depend on it.
+constexpr unsigned SET_SORT_THREADS = 1024, SET_SORT_UNROLL = 8;
+__global__ void __launch_bounds__(SET_SORT_THREADS) k_msm_hist_set(const uint32_t* __restrict__ keys, uint64_t per_set,
+                                                                   unsigned nb_log, unsigned split,
+                                                                   uint32_t* __restrict__ hist_split,
+                                                                   uint32_t* __restrict__ counts) {
+    extern __shared__ uint32_t sh_cnt[];
+    const unsigned nb = 1u << nb_log, set = blockIdx.y, sp = blockIdx.x;
+    for (unsigned j = threadIdx.x; j < nb; j += blockDim.x) sh_cnt[j] = 0;
+    __syncthreads();
+    const uint64_t slice = (per_set + split - 1) / split;
+    const uint64_t lo = uint64_t(sp) * slice, hi = (lo + slice < per_set) ? lo + slice : per_set;
+    const uint32_t* kp = keys + uint64_t(set) * per_set;
+    // SET_SORT_UNROLL independent loads in flight per thread: the loop is latency-bound otherwise (one CTA per SM)
+    for (uint64_t q0 = lo + threadIdx.x; q0 < hi; q0 += uint64_t(SET_SORT_UNROLL) * blockDim.x) {
+        uint32_t k[SET_SORT_UNROLL];
+#pragma unroll
+        for (unsigned u = 0; u < SET_SORT_UNROLL; ++u) {
+            const uint64_t q = q0 + uint64_t(u) * blockDim.x;
+            k[u] = q < hi ? kp[q] : KEY_NONE;
+        }
+#pragma unroll
+        for (unsigned u = 0; u < SET_SORT_UNROLL; ++u)
+            if (k[u] != KEY_NONE) atomicAdd(&sh_cnt[k[u] & (nb - 1u)], 1u);
+    }
+    __syncthreads();
+    uint32_t* hs = hist_split + (uint64_t(set) * split + sp) * nb;
+    for (unsigned j = threadIdx.x; j < nb; j += blockDim.x) hs[j] = sh_cnt[j];
+    (void)counts;
+}
+// counts[set][j] = sum over the set's slices of hist_split[set][slice][j]
+__global__ void k_msm_sum_split(const uint32_t* __restrict__ hist_split, unsigned nb_log, unsigned split, uint64_t buckets,
+                                uint32_t* __restrict__ counts) {
+    const uint64_t g = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (g >= buckets) return;
+    const uint64_t set = g >> nb_log, j = g & ((uint64_t(1) << nb_log) - 1);
+    uint32_t c = 0;
+    for (unsigned q = 0; q < split; ++q) c += hist_split[((set * split + q) << nb_log) + j];
+    counts[g] = c;
+}
+__global__ void __launch_bounds__(SET_SORT_THREADS) k_msm_scatter_set(const uint32_t* __restrict__ keys, uint64_t per_set,
+                                                                      uint64_t n, MsmPlan p, unsigned split,
+                                                                      const uint32_t* __restrict__ hist_split,
+                                                                      const uint32_t* __restrict__ offsets,
+                                                                      uint32_t* __restrict__ sorted) {
+    extern __shared__ uint32_t sh_cur[];
+    const unsigned nb = 1u << p.nb_log, set = blockIdx.y, sp = blockIdx.x;
+    const uint32_t* og = offsets + (uint64_t(set) << p.nb_log);
+    for (unsigned j = threadIdx.x; j < nb; j += blockDim.x) {
+        uint32_t c = og[j];
+        for (unsigned q = 0; q < sp; ++q) c += hist_split[(uint64_t(set) * split + q) * nb + j];
+        sh_cur[j] = c;
+    }
+    __syncthreads();
+    const uint64_t slice = (per_set + split - 1) / split;
+    const uint64_t lo = uint64_t(sp) * slice, hi = (lo + slice < per_set) ? lo + slice : per_set;
+    const uint32_t* kp = keys + uint64_t(set) * per_set;
+    // per_set < 2^32 (checked by the caller): 32-bit index arithmetic, one 32-bit division per key
+    const uint32_t lo32 = (uint32_t)lo, hi32 = (uint32_t)hi, n32 = (uint32_t)n, stride32 = (uint32_t)p.stride;
+    for (uint32_t q0 = lo32 + threadIdx.x; q0 < hi32; q0 += SET_SORT_UNROLL * SET_SORT_THREADS) {
+        uint32_t k[SET_SORT_UNROLL];
+#pragma unroll
+        for (unsigned u = 0; u < SET_SORT_UNROLL; ++u) {
+            const uint32_t q = q0 + u * SET_SORT_THREADS;
+            k[u] = (q < hi32 && q >= q0) ? kp[q] : KEY_NONE;
+        }
+#pragma unroll
+        for (unsigned u = 0; u < SET_SORT_UNROLL; ++u) {
+            if (k[u] == KEY_NONE) continue;
+            const uint32_t q = q0 + u * SET_SORT_THREADS;
+            const uint32_t pos = atomicAdd(&sh_cur[k[u] & (nb - 1u)], 1u);
+            const uint32_t w = q / n32;
+            sorted[pos] = (q - w * n32 + w * stride32) | (k[u] & 0x80000000u);
+        }
+        if (q0 + SET_SORT_UNROLL * SET_SORT_THREADS < q0) break;  // 32-bit wrap
+    }
+}
+
 
 struct Task {
     uint32_t begin, end;  // positions in `sorted`
@@ -585,14 +670,37 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_CUDA_CHECK(ctx, cudaMemsetAsync(cursors.p, 0, (p.buckets + 1) * 4, s));
     VSP_CUDA_CHECK(ctx, cudaMemsetAsync(heavy_count.p, 0, 4, s));
 
+    // counters in shared memory when a ballot's bucket set fits one CTA (window tables, c <= 16) and the batch fills the
+    // SMs; otherwise global atomics
+    const bool set_sort = p.sets == 1 && p.nb_log <= 15 && batch >= 8 && !getenv("VSP_MSM_GLOBAL_SORT");
     VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_digits, dim3((unsigned)((n + 127) / 128), batch), 128, 0, s, d_scalars, n,
-                 scalar_stride, p, keys.as<uint32_t>(), counts.as<uint32_t>());
+                 scalar_stride, p, keys.as<uint32_t>(), counts.as<uint32_t>(), set_sort ? 0 : 1);
+    DevBuf hist_split;
+    unsigned split = 1;
+    const size_t set_smem = (size_t)4 << p.nb_log;
+    if (set_sort) {
+        VSP_CUDA_CHECK(ctx, cudaFuncSetAttribute(k_msm_hist_set, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+        VSP_CUDA_CHECK(ctx, cudaFuncSetAttribute(k_msm_scatter_set, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+        split = (2u * (unsigned)ctx->sm_count + batch - 1) / batch;
+        if (split < 1) split = 1;
+        if (split > 8) split = 8;
+        VSP_TRY(hist_split.alloc(ctx, ((size_t)batch * split << p.nb_log) * 4, s));
+        VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_hist_set, dim3(split, batch), SET_SORT_THREADS, set_smem, s, keys.as<uint32_t>(),
+                     n * p.windows, p.nb_log, split, hist_split.as<uint32_t>(), counts.as<uint32_t>());
+        VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_sum_split, (unsigned)((p.buckets + 255) / 256), 256, 0, s,
+                     hist_split.as<uint32_t>(), p.nb_log, split, p.buckets, counts.as<uint32_t>());
+    }
     VSP_TRY(exclusive_scan<0>(ctx, s, counts.as<uint32_t>(), p.buckets, offsets.as<uint32_t>(),
                               tile_scratch.as<uint32_t>()));
     VSP_TRY(exclusive_scan<1>(ctx, s, counts.as<uint32_t>(), p.buckets, task_off.as<uint32_t>(),
                               tile_scratch.as<uint32_t>()));
-    VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_scatter, (unsigned)((total + 255) / 256), 256, 0, s, keys.as<uint32_t>(), total,
-                 n, p, offsets.as<uint32_t>(), cursors.as<uint32_t>(), sorted.as<uint32_t>());
+    if (set_sort)
+        VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_scatter_set, dim3(split, batch), SET_SORT_THREADS, set_smem, s,
+                     keys.as<uint32_t>(), n * p.windows, n, p, split, hist_split.as<uint32_t>(), offsets.as<uint32_t>(),
+                     sorted.as<uint32_t>());
+    else
+        VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_msm_scatter, (unsigned)((total + 255) / 256), 256, 0, s, keys.as<uint32_t>(), total,
+                     n, p, offsets.as<uint32_t>(), cursors.as<uint32_t>(), sorted.as<uint32_t>());
     // upper bound on the number of tasks, known without a device read-back: ceil(count / T) <= count / T + 1
     const uint64_t max_tasks = total / TASK_POINTS + p.buckets;
     DevBuf tasks, partial;
