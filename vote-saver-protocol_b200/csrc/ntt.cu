@@ -122,6 +122,8 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
     const unsigned R = 1u << a.k, G = 1u << a.g_log;
     uint4* lo = smem;
     uint4* hi = smem + (size_t)G * R;
+    uint4* tw_lo = smem + (size_t)2 * G * R;  // omega_R^e, e < R/2: every stage's butterfly twiddles, staged once
+    uint4* tw_hi = tw_lo + (R >> 1);
     const unsigned T = blockDim.x;  // G * R / 2 (or 1 when R == 1... R >= 2 here)
     const unsigned t = threadIdx.x;
     const uint64_t nj = uint64_t(1) << (a.log_n - a.k);
@@ -148,6 +150,11 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
         lo[jj * R + rr] = make_uint4(x.l[0], x.l[1], x.l[2], x.l[3]);
         hi[jj * R + rr] = make_uint4(x.l[4], x.l[5], x.l[6], x.l[7]);
     }
+    for (unsigned e = t; e < (R >> 1); e += T) {
+        const Fr w = twiddle(a.w, a.log_w, a.log_n, e << (a.log_n - a.k), a.inverse);
+        tw_lo[e] = make_uint4(w.l[0], w.l[1], w.l[2], w.l[3]);
+        tw_hi[e] = make_uint4(w.l[4], w.l[5], w.l[6], w.l[7]);
+    }
     __syncthreads();
 
     // ---- k radix-2 DIT stages in shared memory
@@ -165,7 +172,13 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
             v.l[0] = p.x; v.l[1] = p.y; v.l[2] = p.z; v.l[3] = p.w;
             v.l[4] = q.x; v.l[5] = q.y; v.l[6] = q.z; v.l[7] = q.w;
         }
-        if (jpos) v = fp_mul(v, twiddle(a.w, a.log_w, a.log_n, jpos << (a.log_n - s), a.inverse));
+        if (jpos) {  // omega_{2^s}^jpos = omega_R^(jpos << (k - s))
+            const uint4 p = tw_lo[jpos << (a.k - s)], q = tw_hi[jpos << (a.k - s)];
+            Fr w;
+            w.l[0] = p.x; w.l[1] = p.y; w.l[2] = p.z; w.l[3] = p.w;
+            w.l[4] = q.x; w.l[5] = q.y; w.l[6] = q.z; w.l[7] = q.w;
+            v = fp_mul(v, w);
+        }
         Fr x = fp_add(u, v), y = fp_sub(u, v);
         lo[i0] = make_uint4(x.l[0], x.l[1], x.l[2], x.l[3]);
         hi[i0] = make_uint4(x.l[4], x.l[5], x.l[6], x.l[7]);
@@ -291,7 +304,7 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
         a.scale_log = (inverse && last) ? (int)log_n : 0;
         const unsigned threads = 1u << (k - 1 + g_log);
         const unsigned blocks = 1u << (log_n - k - g_log);
-        const size_t smem = (size_t)32 << (k + g_log);
+        const size_t smem = ((size_t)32 << (k + g_log)) + ((size_t)16 << k);
         VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, dim3(blocks, batch), threads, smem, s, a);
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         if (last && dst != d_out) {
