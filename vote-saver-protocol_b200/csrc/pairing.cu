@@ -18,7 +18,8 @@
 // expanded ONCE into a table of its 68 (lambda, lambda Tx - Ty) pairs (63 doublings + 5 additions of the loop over
 // |x| = 0xd201000000010000); after that a pairing costs no inversion, and a product of pairings shares the 63 squarings
 // (one thread per product).  In the verifiers all but one G2 argument per ballot (the proof's B) are key material whose
-// tables are built once per call.  Final exponentiation: f^((p^12-1)/r) = (conj(f)/f)^((p^6+1)/r).
+// tables are built once per call.  Final exponentiation: easy part by conjugation / inversion / Frobenius, hard part by the
+// exact x-chain (p^4-p^2+1)/r = ((x-1)^2/3)(x+p)(x^2+p^2-1) + 1 (see k_final_exp).
 #include "common.cuh"
 #include "ec.cuh"
 #include "host_fr.h"
@@ -204,7 +205,48 @@ __global__ void __launch_bounds__(64) k_multi_miller(const uint32_t* __restrict_
     f12_store(f_out + uint64_t(c) * 144, f);
 }
 
-// one thread per product: g = (conj(f) / f)^((p^6+1)/r); gt_out (optional): canonical Fq12, 72 u64 limbs in tower order
+// ---- final exponentiation ------------------------------------------------------------------------------------
+// f^((p^12-1)/r) = easy * hard:  t = conj(f) / f = f^(p^6-1);  f1 = frob^2(t) t = t^(p^2+1);
+// hard exponent (p^4 - p^2 + 1)/r = e0 (x + p)(x^2 + p^2 - 1) + 1 with e0 = (x-1)^2/3 (an exact identity, checked
+// when tools/gen_constants.py writes pairing_constants.cuh), so the result is the same field element the plain
+// 4,314-bit power gives:  a = f1^e0;  b = a^x frob(a);  c = (b^x)^x frob^2(b) conj(b);  result = c f1.
+// After the easy part the value is in the cyclotomic subgroup, where inversion is conjugation; x < 0.
+VSP_DEV Fq fq_const(const uint32_t* p) {
+    Fq r;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) r.l[i] = p[i];
+    return r;
+}
+// frob(sum a_i w^i) = sum conj(a_i) g1_i w^i;  tower slots: w^0 c0.c0, w^1 c1.c0, w^2 c0.c1, w^3 c1.c1, w^4 c0.c2, w^5 c1.c2
+__device__ __noinline__ void f12_frob(Fq12& a) {
+    E2* slot[6] = {&a.c0.c0, &a.c1.c0, &a.c0.c1, &a.c1.c1, &a.c0.c2, &a.c1.c2};
+#pragma unroll 1
+    for (int i = 0; i < 6; ++i) {
+        E2 v = E2{slot[i]->c0, fp_neg(slot[i]->c1)};
+        if (i) v = O2::mul(v, E2{fq_const(VSP_FROB1[i - 1][0]), fq_const(VSP_FROB1[i - 1][1])});
+        *slot[i] = v;
+    }
+}
+__device__ __noinline__ void f12_frob2(Fq12& a) {
+    E2* slot[6] = {&a.c0.c0, &a.c1.c0, &a.c0.c1, &a.c1.c1, &a.c0.c2, &a.c1.c2};
+#pragma unroll 1
+    for (int i = 1; i < 6; ++i) *slot[i] = mul_fq(*slot[i], fq_const(VSP_FROB2[i - 1]));
+}
+VSP_DEV void f12_conj(Fq12& a) { a.c1 = f6_neg(a.c1); }
+// a^x for cyclotomic a (x = -|x|): conj(a^|x|)
+__device__ __noinline__ Fq12 f12_pow_x(const Fq12& a) {
+    Fq12 acc = a;
+#pragma unroll 1
+    for (int bit = 62; bit >= 0; --bit) {
+        f12_sqr(acc);
+        if ((VSP_BLS_X_ABS >> bit) & 1ULL) f12_mul(acc, a);
+    }
+    f12_conj(acc);
+    return acc;
+}
+
+// one thread per check: product of the check's segment values, then the final exponentiation; gt_out (optional):
+// canonical Fq12, 72 u64 limbs in tower order
 __global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f_in, const Span* __restrict__ checks, unsigned n,
                                                   uint64_t* __restrict__ gt_out, uint8_t* __restrict__ is_one) {
     const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -212,18 +254,33 @@ __global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f
     const Span ck = checks[c];
     Fq12 f = f12_load(f_in + uint64_t(ck.first) * 144);
     for (unsigned q = 1; q < ck.count; ++q) f12_mul(f, f12_load(f_in + uint64_t(ck.first + q) * 144));
-    Fq12 base = f12_inv(f);
+    Fq12 f1 = f12_inv(f);
+    f12_conj(f);
+    f12_mul(f1, f);  // t = conj(f) / f
     {
-        Fq12 cj = f;
-        cj.c1 = f6_neg(cj.c1);
-        f12_mul(base, cj);
+        Fq12 t2 = f1;
+        f12_frob2(t2);
+        f12_mul(f1, t2);  // f1 = t^(p^2 + 1)
     }
-    Fq12 acc = base;  // leading bit
+    Fq12 a = f1;  // a = f1^e0, leading bit consumed
 #pragma unroll 1
-    for (int bit = VSP_PAIRING_E2_BITS - 2; bit >= 0; --bit) {
-        f12_sqr(acc);
-        if ((VSP_PAIRING_E2[bit >> 5] >> (bit & 31)) & 1u) f12_mul(acc, base);
+    for (int bit = VSP_PAIRING_E0_BITS - 2; bit >= 0; --bit) {
+        f12_sqr(a);
+        if ((VSP_PAIRING_E0[bit >> 5] >> (bit & 31)) & 1u) f12_mul(a, f1);
     }
+    Fq12 b = f12_pow_x(a);
+    f12_frob(a);
+    f12_mul(b, a);  // b = a^(x + p)
+    Fq12 acc = f12_pow_x(b);
+    acc = f12_pow_x(acc);
+    {
+        Fq12 t = b;
+        f12_frob2(t);
+        f12_mul(acc, t);
+        f12_conj(b);
+        f12_mul(acc, b);  // acc = b^(x^2 + p^2 - 1)
+    }
+    f12_mul(acc, f1);
     if (is_one) is_one[c] = f12_is_one(acc) ? 1 : 0;
     if (gt_out) {
         const E2* co[6] = {&acc.c0.c0, &acc.c0.c1, &acc.c0.c2, &acc.c1.c0, &acc.c1.c1, &acc.c1.c2};
