@@ -181,3 +181,31 @@ def test_tally_decrypt_and_verify_decryption(ctx):
     assert np.array_equal(gc0, G1L([oc0])[0])
     assert o.saver_verify_decryption(J1s(small), om, osvk, ovk.gamma_ABC_rest, oc0)
     assert vsp.verify_decryption(ctx, small, gm, svk, gabc_rest, gc0)
+
+
+def test_empty_batches_and_infinity_proof_elements(ctx):
+    """empty inputs are no-ops; a proof whose A is the point at infinity drops e(A, B) from the product exactly as the
+    oracle's pairing does (miller_loop of an infinite argument is 1), so the check fails unless the rest is 1 too"""
+    cs, arr, vk, pub_arr, rng = _keys_and_ballots(ctx, 14, 3, 1, 1, seed=21)
+    assert vsp.verify_batch(ctx, vk, np.zeros((0, 3, 4), np.uint64), np.zeros((0, 48), np.uint64)).shape == (0,)
+    gt, one = vsp.pairing_products(ctx, np.zeros((0, 12), np.uint64), np.zeros((0, 24), np.uint64))
+    assert gt.shape == (0, 72) and one.shape == (0,)
+    pk = vsp.ProvingKey(ctx, arr)
+    _cs, primary, aux = synthetic_r1cs(14, 3, seed=21)
+    proof = pk.prove(cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4), 5, 6)
+    pk.close()
+    P = cref.ints_to_limbs(primary, 4)[None]
+    assert vsp.verify_batch(ctx, vk, P, proof[None]).tolist() == [True]
+    bad = proof.copy()
+    bad[:12] = 0
+    assert vsp.verify_batch(ctx, vk, P, bad[None]).tolist() == [False]
+    from test_gpu_keygen import _vk_from_arrays
+    J2 = lambda a: o.G2.from_affine(cref.g2_from_limbs(a.reshape(1, 24))[0])
+    J1 = lambda a: o.G1.from_affine(cref.g1_from_limbs(a.reshape(1, 12))[0])
+    assert not o.groth16_verify(_vk_from_arrays(vk), primary, (o.G1.inf(), J2(bad[12:36]), J1(bad[36:])))
+    # SAVER key pair and decryption with an empty message
+    pub0, rho0, svk0 = vsp.saver_generate_keypair(ctx, vk, 0, [7, 9])
+    assert pub0["t_g2"].shape[0] == 1 and rho0 == 7
+    ct0 = vsp.saver_ciphertext(ctx, vsp.SaverPublicKey(pub0), np.zeros((1, 12), np.uint64), np.zeros((0, 4), np.uint64), 11)
+    m0, c0 = vsp.decrypt(ctx, ct0, rho0, svk0, np.zeros((1, 12), np.uint64))
+    assert m0 == [] and vsp.verify_decryption(ctx, ct0, [], svk0, np.zeros((1, 12), np.uint64), c0)
