@@ -216,6 +216,129 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
     }
 }
 
+// The same pass with radix-4 butterflies: a thread owns four elements and runs TWO stages on them in registers between
+// shared-memory exchanges (half the shared traffic and barriers of the radix-2 kernel); an odd k ends with one radix-2
+// stage.  Launched with G * R / 4 threads; k >= 2.
+VSP_DEV Fr sm_load(const uint4* lo, const uint4* hi, unsigned i) {
+    const uint4 p = lo[i], q = hi[i];
+    Fr x;
+    x.l[0] = p.x; x.l[1] = p.y; x.l[2] = p.z; x.l[3] = p.w;
+    x.l[4] = q.x; x.l[5] = q.y; x.l[6] = q.z; x.l[7] = q.w;
+    return x;
+}
+VSP_DEV void sm_store(uint4* lo, uint4* hi, unsigned i, const Fr& x) {
+    lo[i] = make_uint4(x.l[0], x.l[1], x.l[2], x.l[3]);
+    hi[i] = make_uint4(x.l[4], x.l[5], x.l[6], x.l[7]);
+}
+__global__ void __launch_bounds__(256) k_ntt_pass4(PassArgs a) {
+    extern __shared__ uint4 smem[];
+    const unsigned R = 1u << a.k, G = 1u << a.g_log;
+    uint4* lo = smem;
+    uint4* hi = smem + (size_t)G * R;
+    uint4* tw_lo = smem + (size_t)2 * G * R;
+    uint4* tw_hi = tw_lo + (R >> 1);
+    const unsigned T = blockDim.x;  // G * R / 4
+    const unsigned t = threadIdx.x;
+    const uint64_t nj = uint64_t(1) << (a.log_n - a.k);
+    const uint64_t j0 = uint64_t(blockIdx.x) << a.g_log;
+    const uint64_t ns_mask = (uint64_t(1) << a.ns_log) - 1;
+    const uint32_t* vin = a.in + 8 * (uint64_t(blockIdx.y) * a.in_stride);
+    uint32_t* vout = a.out + 8 * (uint64_t(blockIdx.y) * a.out_stride);
+
+#pragma unroll
+    for (unsigned h = 0; h < 4; ++h) {
+        const unsigned q = t + h * T;
+        const unsigned jj = q & (G - 1), r = q >> a.g_log;
+        const uint64_t j = j0 + jj;
+        const uint64_t gidx = j + uint64_t(r) * nj;
+        Fr x = fp_load<FrCfg>(vin + 8 * gidx);
+        if (a.pre) x = fp_mul(x, fp_load<FrCfg>(a.pre + 8 * gidx));
+        if (a.ns_log) {
+            const uint32_t e = (uint32_t)(((j & ns_mask) * r) << (a.log_n - a.ns_log - a.k));
+            if (e) x = fp_mul(x, twiddle(a.w, a.log_w, a.log_n, e, a.inverse));
+        }
+        sm_store(lo, hi, jj * R + (__brev(r) >> (32 - a.k)), x);
+    }
+    for (unsigned e = t; e < (R >> 1); e += T) {
+        const Fr w = twiddle(a.w, a.log_w, a.log_n, e << (a.log_n - a.k), a.inverse);
+        sm_store(tw_lo, tw_hi, e, w);
+    }
+    __syncthreads();
+
+    const unsigned jj4 = t >> (a.k - 2), g = t & ((R >> 2) - 1);
+    unsigned s = 1;
+    for (; s + 1 <= a.k; s += 2) {
+        const unsigned m = 1u << (s - 1);
+        const unsigned jpos = g & (m - 1);
+        const unsigned base = jj4 * R + ((g >> (s - 1)) << (s + 1)) + jpos;
+        Fr e0 = sm_load(lo, hi, base), e1 = sm_load(lo, hi, base + m), e2 = sm_load(lo, hi, base + 2 * m),
+           e3 = sm_load(lo, hi, base + 3 * m);
+        if (jpos) {  // stage s: omega_{2^s}^jpos on both pairs
+            const Fr w1 = sm_load(tw_lo, tw_hi, jpos << (a.k - s));
+            e1 = fp_mul(e1, w1);
+            e3 = fp_mul(e3, w1);
+        }
+        Fr x = fp_add(e0, e1);
+        e1 = fp_sub(e0, e1);
+        e0 = x;
+        x = fp_add(e2, e3);
+        e3 = fp_sub(e2, e3);
+        e2 = x;
+        // stage s + 1: pairs (e0, e2) with omega_{2^(s+1)}^jpos and (e1, e3) with omega_{2^(s+1)}^(jpos + m)
+        if (jpos) e2 = fp_mul(e2, sm_load(tw_lo, tw_hi, jpos << (a.k - s - 1)));
+        e3 = fp_mul(e3, sm_load(tw_lo, tw_hi, (jpos + m) << (a.k - s - 1)));
+        x = fp_add(e0, e2);
+        e2 = fp_sub(e0, e2);
+        e0 = x;
+        x = fp_add(e1, e3);
+        e3 = fp_sub(e1, e3);
+        e1 = x;
+        sm_store(lo, hi, base, e0);
+        sm_store(lo, hi, base + m, e1);
+        sm_store(lo, hi, base + 2 * m, e2);
+        sm_store(lo, hi, base + 3 * m, e3);
+        __syncthreads();
+    }
+    if (s == a.k) {  // odd k: the last stage as two radix-2 butterflies per thread
+        const unsigned m = 1u << (s - 1);
+#pragma unroll
+        for (unsigned h = 0; h < 2; ++h) {
+            const unsigned b = t + h * T;  // butterfly index over G * R / 2
+            const unsigned jj = b >> (a.k - 1), i = b & ((R >> 1) - 1);
+            const unsigned i0 = jj * R + i, i1 = i0 + m;  // s == k: one group per sub-transform, jpos = i
+            Fr u = sm_load(lo, hi, i0), v = sm_load(lo, hi, i1);
+            if (i) v = fp_mul(v, sm_load(tw_lo, tw_hi, i));
+            sm_store(lo, hi, i0, fp_add(u, v));
+            sm_store(lo, hi, i1, fp_sub(u, v));
+        }
+        __syncthreads();
+    }
+
+    Fr scale;
+    if (a.scale_log) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) scale.l[i] = FR_INV_POW2[a.scale_log][i];
+    }
+#pragma unroll
+    for (unsigned h = 0; h < 4; ++h) {
+        const unsigned q = t + h * T;
+        unsigned jj, r;
+        if (a.ns_log == 0) {
+            r = q & (R - 1);
+            jj = q >> a.k;
+        } else {
+            jj = q & (G - 1);
+            r = q >> a.g_log;
+        }
+        const uint64_t j = j0 + jj;
+        const uint64_t didx = ((j >> a.ns_log) << (a.ns_log + a.k)) + (j & ns_mask) + (uint64_t(r) << a.ns_log);
+        Fr y = sm_load(lo, hi, jj * R + r);
+        if (a.scale_log) y = fp_mul(y, scale);
+        if (a.post) y = fp_mul(y, fp_load<FrCfg>(a.post + 8 * didx));
+        fp_store(vout + 8 * didx, y);
+    }
+}
+
 __global__ void k_scale_copy(const uint32_t* in, uint32_t* out, uint64_t n, const uint32_t* pre, const uint32_t* post,
                              uint64_t in_stride, uint64_t out_stride) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -302,10 +425,13 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
         a.out_stride = dst_stride;
         a.inverse = inverse ? 1 : 0;
         a.scale_log = (inverse && last) ? (int)log_n : 0;
-        const unsigned threads = 1u << (k - 1 + g_log);
         const unsigned blocks = 1u << (log_n - k - g_log);
         const size_t smem = ((size_t)32 << (k + g_log)) + ((size_t)16 << k);
-        VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, dim3(blocks, batch), threads, smem, s, a);
+        if (k >= 2 && !getenv("VSP_NTT_RADIX2")) {
+            VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass4, dim3(blocks, batch), 1u << (k - 2 + g_log), smem, s, a);
+        } else {
+            VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, dim3(blocks, batch), 1u << (k - 1 + g_log), smem, s, a);
+        }
         VSP_CUDA_CHECK(ctx, cudaGetLastError());
         if (last && dst != d_out) {
             if (out_stride == n)
