@@ -230,7 +230,7 @@ VSP_DEV void sm_store(uint4* lo, uint4* hi, unsigned i, const Fr& x) {
     lo[i] = make_uint4(x.l[0], x.l[1], x.l[2], x.l[3]);
     hi[i] = make_uint4(x.l[4], x.l[5], x.l[6], x.l[7]);
 }
-__global__ void __launch_bounds__(256) k_ntt_pass4(PassArgs a) {
+__global__ void __launch_bounds__(512) k_ntt_pass4(PassArgs a) {
     extern __shared__ uint4 smem[];
     const unsigned R = 1u << a.k, G = 1u << a.g_log;
     uint4* lo = smem;
@@ -388,8 +388,9 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
     unsigned ns_log = 0;
     for (unsigned p = 0; p < np; ++p) {
         const unsigned k = ks[p];
-        // G sub-transforms per block: 512 threads when possible
-        unsigned g_log = (k - 1 >= 9) ? 0 : (9 - (k - 1));
+        // G sub-transforms per block: 2^block_log values (128 threads on four values each); 9 measured best of 9/10/11
+        static const unsigned block_log = getenv("VSP_NTT_BLOCK_LOG") ? (unsigned)atoi(getenv("VSP_NTT_BLOCK_LOG")) : 9u;
+        unsigned g_log = (k >= block_log) ? 0 : (block_log - k);
         if (g_log > log_n - k) g_log = log_n - k;
         const bool last = (p + 1 == np);
         uint32_t* dst;
@@ -428,6 +429,7 @@ int ntt_pow2(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_in, uint32_t* d_out
         const unsigned blocks = 1u << (log_n - k - g_log);
         const size_t smem = ((size_t)32 << (k + g_log)) + ((size_t)16 << k);
         if (k >= 2 && !getenv("VSP_NTT_RADIX2")) {
+            if (smem > 48 * 1024) cudaFuncSetAttribute(k_ntt_pass4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass4, dim3(blocks, batch), 1u << (k - 2 + g_log), smem, s, a);
         } else {
             VSP_LAUNCH_K(ctx, KC_NTT, k_ntt_pass, dim3(blocks, batch), 1u << (k - 1 + g_log), smem, s, a);
