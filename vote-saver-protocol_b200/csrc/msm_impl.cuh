@@ -392,13 +392,18 @@ __global__ void __launch_bounds__(64) k_msm_collapse_light(const uint32_t* __res
     acc.store(partial + uint64_t(t0) * L);
 }
 
-// heavy buckets (e.g. the bucket of all scalars == 1): one block each, strided sums then a shared-memory tree
+// heavy buckets (e.g. the bucket of all scalars == 1), two launches: the bucket's T tasks are cut into slices of
+// `per` = max(COLLAPSE_SLICE_MIN, ceil(T / COLLAPSE_SLICES)) tasks; block (h, slice) sums its slice (strided sums then a
+// shared-memory tree) into the slice's first slot, then (second launch, slices == 0) one block per bucket sums the
+// slice heads into partial[t0].  A 2^22-point all-ones bucket is 65,536 tasks: 16 + 6 + 6 additions deep instead of 1,030.
 constexpr unsigned COLLAPSE_THREADS = 64;
+constexpr unsigned COLLAPSE_SLICES = 64;
+constexpr unsigned COLLAPSE_SLICE_MIN = 256;
 template <class F>
 __global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse_heavy(const uint32_t* __restrict__ heavy,
                                                                          const uint32_t* __restrict__ heavy_count,
                                                                          const uint32_t* __restrict__ task_off,
-                                                                         uint32_t* __restrict__ partial) {
+                                                                         uint32_t* __restrict__ partial, int heads) {
     extern __shared__ uint4 sm4[];
     uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
@@ -406,9 +411,21 @@ __global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse_heavy(const u
     for (uint32_t h = blockIdx.x; h < nh; h += gridDim.x) {
         const uint32_t b = heavy[h];
         const uint32_t t0 = task_off[b], t1 = task_off[b + 1];
+        const uint32_t per = max(COLLAPSE_SLICE_MIN, (t1 - t0 + COLLAPSE_SLICES - 1) / COLLAPSE_SLICES);
+        uint32_t lo, hi, step;
+        if (heads) {  // the slice heads t0, t0 + per, ...
+            lo = t0;
+            hi = t1;
+            step = per;
+        } else {
+            lo = t0 + blockIdx.y * per;
+            hi = min(t1, lo + per);
+            step = 1;
+            if (lo >= t1) continue;  // block-uniform
+        }
         XYZZ<F> acc = XYZZ<F>::inf();
-        for (uint32_t t = t0 + threadIdx.x; t < t1; t += COLLAPSE_THREADS) {
-            XYZZ<F> q = XYZZ<F>::load(partial + uint64_t(t) * L);
+        for (uint64_t t = lo + uint64_t(threadIdx.x) * step; t < hi; t += uint64_t(COLLAPSE_THREADS) * step) {
+            XYZZ<F> q = XYZZ<F>::load(partial + t * L);
             ec_add<F>(acc, q);
         }
         acc.store(sm + threadIdx.x * L);
@@ -421,7 +438,7 @@ __global__ void __launch_bounds__(COLLAPSE_THREADS) k_msm_collapse_heavy(const u
             }
             __syncthreads();
         }
-        if (threadIdx.x == 0) acc.store(partial + uint64_t(t0) * L);
+        if (threadIdx.x == 0) acc.store(partial + uint64_t(lo) * L);
         __syncthreads();
     }
 }
@@ -727,8 +744,11 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
                 offsets.as<uint32_t>() + p.buckets, s);
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_light<F>, (unsigned)((p.buckets + 63) / 64), 64, 0, s,
                  task_off.as<uint32_t>(), p.buckets, partial.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, dim3(256, COLLAPSE_SLICES), COLLAPSE_THREADS,
+                 COLLAPSE_THREADS * XYZZ<F>::BYTES, s, heavy.as<uint32_t>(), heavy_count.as<uint32_t>(),
+                 task_off.as<uint32_t>(), partial.as<uint32_t>(), 0);
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
-                 heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>());
+                 heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>(), 1);
     const unsigned n_sets = batch * p.sets;
     // segment length: keep ~2^15 segment threads in flight (each runs a serial chain of 2 * SEG additions)
     unsigned seg_log = 1;
