@@ -219,7 +219,12 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
 // The same pass with radix-4 butterflies: a thread owns four elements and runs TWO stages on them in registers between
 // shared-memory exchanges (half the shared traffic and barriers of the radix-2 kernel); an odd k ends with one radix-2
 // stage.  Launched with G * R / 4 threads; k >= 2.
+// 16-byte slot i of a shared vector lives at swz(i): the radix-4 stages read slots 4 apart (stage pair 1) and runs of 4
+// slots 16 apart (stage pair 2); XOR-ing bits 2..4 into bits 0..2 spreads both patterns (and contiguous runs) over all
+// eight 16-byte bank groups of a quarter-warp
+VSP_DEV unsigned swz(unsigned i) { return i ^ ((i >> 2) & 7u); }
 VSP_DEV Fr sm_load(const uint4* lo, const uint4* hi, unsigned i) {
+    i = swz(i);
     const uint4 p = lo[i], q = hi[i];
     Fr x;
     x.l[0] = p.x; x.l[1] = p.y; x.l[2] = p.z; x.l[3] = p.w;
@@ -227,6 +232,7 @@ VSP_DEV Fr sm_load(const uint4* lo, const uint4* hi, unsigned i) {
     return x;
 }
 VSP_DEV void sm_store(uint4* lo, uint4* hi, unsigned i, const Fr& x) {
+    i = swz(i);
     lo[i] = make_uint4(x.l[0], x.l[1], x.l[2], x.l[3]);
     hi[i] = make_uint4(x.l[4], x.l[5], x.l[6], x.l[7]);
 }
