@@ -31,8 +31,9 @@ def test_field_ops(emul, name, mod, limbs):
     pairs = [(a, b) for a in edge for b in edge] + [(rng.randrange(mod), rng.randrange(mod)) for _ in range(400)]
     for i, (a, b) in enumerate(pairs):
         A, B, O = ints_to_limbs([a], limbs), ints_to_limbs([b], limbs), np.zeros((1, limbs), np.uint64)
-        want = [a * b % mod, (a + b) % mod, (a - b) % mod, (-a) % mod, pow(a, mod - 2, mod), a * a % mod]
-        for op in range(6):
+        want = [a * b % mod, (a + b) % mod, (a - b) % mod, (-a) % mod, pow(a, mod - 2, mod), a * a % mod,
+                pow(a, mod - 2, mod)]  # op 6: the binary-Euclid inverse (fp_inv_gcd), every pair
+        for op in range(7):
             if op == 4 and i % 40:
                 continue
             fn(op, P(A), P(B), P(O))

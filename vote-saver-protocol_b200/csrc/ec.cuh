@@ -26,6 +26,7 @@ struct FqOps {
     VSP_DEV static bool is_zero(const T& a) { return a.is_zero(); }
     VSP_DEV static bool eq(const T& a, const T& b) { return a == b; }
     static __device__ __noinline__ T inv(const T& a) { return fp_inv(a); }
+    static __device__ __noinline__ T inv_lowlat(const T& a) { return fp_inv_gcd(a); }
     VSP_DEV static T to_mont(const T& a) { return fp_to_mont(a); }
     VSP_DEV static T from_mont(const T& a) { return fp_from_mont(a); }
     VSP_DEV static T load(const void* p) { return fp_load<FqCfg>(p); }
@@ -61,6 +62,10 @@ struct Fq2Ops {
     VSP_DEV static bool eq(const T& a, const T& b) { return a.c0 == b.c0 && a.c1 == b.c1; }
     static __device__ __noinline__ T inv(const T& a) {
         Fq n = fp_inv(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
+        return T{fp_mul(a.c0, n), fp_neg(fp_mul(a.c1, n))};
+    }
+    static __device__ __noinline__ T inv_lowlat(const T& a) {
+        Fq n = fp_inv_gcd(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
         return T{fp_mul(a.c0, n), fp_neg(fp_mul(a.c1, n))};
     }
     VSP_DEV static T to_mont(const T& a) { return T{fp_to_mont(a.c0), fp_to_mont(a.c1)}; }
@@ -222,10 +227,11 @@ __device__ __noinline__ void ec_add(XYZZ<F>& acc, const XYZZ<F>& q) {
 
 // canonical affine (Montgomery form) of an XYZZ point: one field inversion
 template <class F>
-__device__ __noinline__ Affine<F> ec_to_affine(const XYZZ<F>& p) {
+__device__ __noinline__ Affine<F> ec_to_affine(const XYZZ<F>& p, bool lowlat = false) {
     using E = typename F::T;
     if (p.is_inf()) return Affine<F>::inf();
-    E i = F::inv(F::mul(p.ZZ, p.ZZZ));
+    // lowlat: the caller is the only working lane of its warp (fp_inv_gcd's branches cost nothing then)
+    E i = lowlat ? F::inv_lowlat(F::mul(p.ZZ, p.ZZZ)) : F::inv(F::mul(p.ZZ, p.ZZZ));
     E zz_inv = F::mul(i, p.ZZZ);
     E zzz_inv = F::mul(i, p.ZZ);
     return Affine<F>{F::mul(p.X, zz_inv), F::mul(p.Y, zzz_inv)};

@@ -353,6 +353,97 @@ __device__ __noinline__ Fp<C> fp_inv(const Fp<C>& a) {
     return acc;
 }
 
+// The same inverse by the binary extended Euclid (right shifts and subtractions on the limbs, ~45k plain integer
+// instructions against ~190k multiply-adds for the power): the branches follow the data, so it only pays where ONE
+// thread of a warp is working — the serial tails of a single multiexp or proof — and the uniform power above stays
+// the choice wherever the lanes of a warp invert different values.  In: a R (Montgomery); out: a^-1 R; 0 -> 0.
+namespace gcd_detail {
+template <int N>
+VSP_DEV void shr1(uint32_t (&u)[N], uint32_t top) {
+#pragma unroll
+    for (int k = 0; k < N - 1; ++k) u[k] = (u[k] >> 1) | (u[k + 1] << 31);
+    u[N - 1] = (u[N - 1] >> 1) | (top << 31);
+}
+template <int N>
+VSP_DEV uint32_t sub_to(uint32_t (&u)[N], const uint32_t (&v)[N]) {  // u -= v, returns the borrow
+    uint32_t r[N];
+    r[0] = ptx::sub_cc(u[0], v[0]);
+#pragma unroll
+    for (int k = 1; k < N; ++k) r[k] = ptx::subc_cc(u[k], v[k]);
+    const uint32_t borrow = ptx::subc(0u, 0u);
+#pragma unroll
+    for (int k = 0; k < N; ++k) u[k] = r[k];
+    return borrow;  // 0 or 0xffffffff
+}
+template <class C>
+VSP_DEV uint32_t add_mod_to(uint32_t (&x)[C::N]) {  // x += p, returns the carry
+    x[0] = ptx::add_cc(x[0], C::mod(0));
+#pragma unroll
+    for (int k = 1; k < C::N; ++k) x[k] = ptx::addc_cc(x[k], C::mod(k));
+    return ptx::addc(0u, 0u);
+}
+template <int N>
+VSP_DEV bool geq(const uint32_t (&u)[N], const uint32_t (&v)[N]) {
+    uint32_t t = ptx::sub_cc(u[0], v[0]);
+#pragma unroll
+    for (int k = 1; k < N; ++k) t = ptx::subc_cc(u[k], v[k]);
+    (void)t;
+    return ptx::subc(0u, 0u) == 0u;
+}
+template <int N>
+VSP_DEV bool is_one(const uint32_t (&u)[N]) {
+    uint32_t acc = u[0] ^ 1u;
+#pragma unroll
+    for (int k = 1; k < N; ++k) acc |= u[k];
+    return acc == 0u;
+}
+}  // namespace gcd_detail
+
+template <class C>
+#ifdef __CUDACC__
+__device__ __noinline__
+#else
+inline
+#endif
+Fp<C> fp_inv_gcd(const Fp<C>& a) {
+    using namespace gcd_detail;
+    constexpr int N = C::N;
+    if (a.is_zero()) return a;
+    // invariants: u = a x1, v = a x2 (mod p); u, v > 0; gcd(u, v) = 1
+    uint32_t u[N], v[N], x1[N], x2[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        u[k] = a.l[k];
+        v[k] = C::mod(k);
+        x1[k] = k == 0 ? 1u : 0u;
+        x2[k] = 0u;
+    }
+    while (!is_one<N>(u) && !is_one<N>(v)) {
+        if (!(u[0] & 1u)) {
+            shr1<N>(u, 0u);
+            const uint32_t c = (x1[0] & 1u) ? add_mod_to<C>(x1) : 0u;
+            shr1<N>(x1, c);
+        } else if (!(v[0] & 1u)) {
+            shr1<N>(v, 0u);
+            const uint32_t c = (x2[0] & 1u) ? add_mod_to<C>(x2) : 0u;
+            shr1<N>(x2, c);
+        } else if (geq<N>(u, v)) {
+            sub_to<N>(u, v);
+            if (sub_to<N>(x1, x2)) add_mod_to<C>(x1);
+        } else {
+            sub_to<N>(v, u);
+            if (sub_to<N>(x2, x1)) add_mod_to<C>(x2);
+        }
+    }
+    Fp<C> r;
+    const bool from_u = is_one<N>(u);
+#pragma unroll
+    for (int k = 0; k < N; ++k) r.l[k] = from_u ? x1[k] : x2[k];
+    // r = (a R)^-1 = a^-1 R^-1; one Montgomery product with R^3 puts it back in Montgomery form
+    const Fp<C> r2 = Fp<C>::r2();
+    return fp_mul(r, fp_mul(r2, r2));
+}
+
 using Fq = Fp<FqCfg>;
 using Fr = Fp<FrCfg>;
 

@@ -508,30 +508,51 @@ __global__ void __launch_bounds__(RED_THREADS) k_msm_reduce_planes(const uint32_
     if (threadIdx.x == 0) acc.store(plane_out + ((uint64_t(set) * (nseg_log + 1) + j) * chunks + chunk) * L);
 }
 
-// block = set, thread j sums plane j over the chunks; thread 0 then runs the Horner over the planes, times SEG, plus
-// the acc plane
+// block = set: LP lanes per plane sum the plane's chunks (strided, then a shared-memory tree), the planes are combined
+// as sum_j 2^j P_j by a pairing tree (level d: P_j += 2^d P_(j+d), so nseg_log - 1 doublings and log2 additions deep
+// instead of a serial Horner), then times SEG plus the acc plane.  Everything here is latency of one thread's
+// additions (~10 us each), which is what a single large multiexp waits on.
 template <class F>
-__global__ void __launch_bounds__(32) k_msm_reduce_sets(const uint32_t* __restrict__ plane_in, unsigned nseg_log,
-                                                        unsigned seg_log, unsigned chunks, uint32_t* __restrict__ set_out) {
+struct RedSets {
+    static constexpr unsigned LP = 1536 / XYZZ<F>::BYTES;  // 8 lanes per plane in G1, 4 in G2 (48 KB of shared memory)
+    static_assert((LP & (LP - 1)) == 0, "the lane tree needs a power of two");
+    static constexpr unsigned THREADS = 32 * LP;
+};
+template <class F>
+__global__ void __launch_bounds__(256) k_msm_reduce_sets(const uint32_t* __restrict__ plane_in, unsigned nseg_log,
+                                                         unsigned seg_log, unsigned chunks, uint32_t* __restrict__ set_out) {
     extern __shared__ uint4 sm4[];
     uint32_t* sm = reinterpret_cast<uint32_t*>(sm4);
     constexpr int L = XYZZ<F>::BYTES / 4;
-    const unsigned set = blockIdx.x, j = threadIdx.x;
-    if (j <= nseg_log) {
-        XYZZ<F> acc = XYZZ<F>::inf();
-        for (unsigned ch = 0; ch < chunks; ++ch)
+    constexpr unsigned LP = RedSets<F>::LP;
+    const unsigned set = blockIdx.x, tid = threadIdx.x, j = tid / LP, l = tid % LP;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    if (j <= nseg_log)
+        for (unsigned ch = l; ch < chunks; ch += LP)
             ec_add<F>(acc, XYZZ<F>::load(plane_in + ((uint64_t(set) * (nseg_log + 1) + j) * chunks + ch) * L));
-        acc.store(sm + j * L);
-    }
+    acc.store(sm + tid * L);
     __syncthreads();
-    if (j == 0) {
-        XYZZ<F> acc = XYZZ<F>::inf();
-        for (int k = (int)nseg_log - 1; k >= 0; --k) {
-            acc = ec_dbl<F>(acc);
-            ec_add<F>(acc, XYZZ<F>::load(sm + k * L));
+    for (unsigned st = LP / 2; st > 0; st >>= 1) {
+        if (l < st && j <= nseg_log) {
+            ec_add<F>(acc, XYZZ<F>::load(sm + (tid + st) * L));
+            acc.store(sm + tid * L);
         }
+        __syncthreads();
+    }
+    // plane j now sits at sm[j * LP]; pair them up
+    for (unsigned d = 1; d < nseg_log; d <<= 1) {
+        if (l == 0 && (j & (2 * d - 1)) == 0 && j + d < nseg_log) {
+            XYZZ<F> q = XYZZ<F>::load(sm + (j + d) * LP * L);
+            for (unsigned k = 0; k < d; ++k) q = ec_dbl<F>(q);
+            ec_add<F>(acc, q);
+            acc.store(sm + tid * L);
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (nseg_log == 0) acc = XYZZ<F>::inf();  // no run planes: only the acc plane below
         for (unsigned k = 0; k < seg_log; ++k) acc = ec_dbl<F>(acc);
-        ec_add<F>(acc, XYZZ<F>::load(sm + nseg_log * L));
+        ec_add<F>(acc, XYZZ<F>::load(sm + nseg_log * LP * L));
         acc.store(set_out + uint64_t(set) * L);
     }
 }
@@ -540,8 +561,8 @@ __global__ void __launch_bounds__(32) k_msm_reduce_sets(const uint32_t* __restri
 // 7. final: Horner over a ballot's sets (one-shot bases), affine, canonical
 // ---------------------------------------------------------------------------------------------
 template <class F>
-VSP_DEV void store_canonical_affine(uint64_t* out, const XYZZ<F>& p) {
-    Affine<F> a = ec_to_affine<F>(p);
+VSP_DEV void store_canonical_affine(uint64_t* out, const XYZZ<F>& p, bool lowlat = false) {
+    Affine<F> a = ec_to_affine<F>(p, lowlat);
     a.x = F::from_mont(a.x);
     a.y = F::from_mont(a.y);
     a.store(out);
@@ -564,7 +585,7 @@ __global__ void k_msm_final(const uint32_t* __restrict__ set_in, MsmPlan p, uint
     if (raw)
         acc.store(o);  // Montgomery-form XYZZ for the prover's assembly kernel: skips the inversion
     else
-        store_canonical_affine<F>(o, acc);
+        store_canonical_affine<F>(o, acc, true);  // lane 0 of the block works alone
 }
 
 template <class F>
@@ -771,8 +792,9 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
                  partial.as<uint32_t>(), task_off.as<uint32_t>(), p, seg_log, segs.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_planes<F>, dim3(chunks, nseg_log + 1, n_sets), RED_THREADS,
                  RED_THREADS * XYZZ<F>::BYTES, s, segs.as<uint32_t>(), nseg_log, chunks, planes.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, n_sets, 32, 32 * XYZZ<F>::BYTES, s, planes.as<uint32_t>(), nseg_log,
-                 seg_log, chunks, sets.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_reduce_sets<F>, n_sets, RedSets<F>::THREADS,
+                 RedSets<F>::THREADS * XYZZ<F>::BYTES, s, planes.as<uint32_t>(), nseg_log, seg_log, chunks,
+                 sets.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_final<F>, batch, 32, 0, s, sets.as<uint32_t>(), p, d_out, out_stride,
                  raw ? 1 : 0);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
@@ -822,7 +844,7 @@ __global__ void k_points_sum(const uint64_t* pts, uint64_t k, uint64_t* out) {
         a.y = F::to_mont(a.y);
         ec_madd<F>(acc, a);
     }
-    store_canonical_affine<F>(out, acc);
+    store_canonical_affine<F>(out, acc, true);
 }
 
 }  // namespace

@@ -313,8 +313,8 @@ __global__ void k_group_sum(const uint32_t* __restrict__ xyzz, const uint32_t* _
 }
 
 template <class F>
-VSP_DEV void write_canonical(uint64_t* out, const XYZZ<F>& p) {
-    Affine<F> a = ec_to_affine<F>(p);
+VSP_DEV void write_canonical(uint64_t* out, const XYZZ<F>& p, bool lowlat = false) {
+    Affine<F> a = ec_to_affine<F>(p, lowlat);
     a.x = F::from_mont(a.x);
     a.y = F::from_mont(a.y);
     a.store(out);
@@ -374,18 +374,18 @@ __global__ void __launch_bounds__(32) k_prove_phase1(AsmPtrs p) {
         G1XYZZ acc = G1XYZZ::load(p.evA + uint64_t(b) * L1);
         ec_madd<FqOps>(acc, G1Affine::load(p.fixed1));
         ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b) * L1));
-        write_canonical<FqOps>(p.gab + uint64_t(b) * 24, acc);
+        write_canonical<FqOps>(p.gab + uint64_t(b) * 24, acc, p.B == 1);
         for (int i = 0; i < 12; ++i) p.proof[uint64_t(b) * 48 + i] = p.gab[uint64_t(b) * 24 + i];
     } else if (blockIdx.y == 1) {
         G1XYZZ acc = G1XYZZ::load(p.evB1 + uint64_t(b) * L1);
         ec_madd<FqOps>(acc, G1Affine::load(p.fixed1 + A1));
         ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b + 1) * L1));
-        write_canonical<FqOps>(p.gab + uint64_t(b) * 24 + 12, acc);
+        write_canonical<FqOps>(p.gab + uint64_t(b) * 24 + 12, acc, p.B == 1);
     } else {
         G2XYZZ acc = G2XYZZ::load(p.evB2 + uint64_t(b) * L2);
         ec_madd<Fq2Ops>(acc, G2Affine::load(p.fixed2));
         ec_add<Fq2Ops>(acc, G2XYZZ::load(p.fx2 + uint64_t(b) * L2));
-        write_canonical<Fq2Ops>(p.proof + uint64_t(b) * 48 + 12, acc);
+        write_canonical<Fq2Ops>(p.proof + uint64_t(b) * 48 + 12, acc, p.B == 1);
     }
 }
 
@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(32) k_prove_phase3(AsmPtrs p) {
     ec_add<FqOps>(acc, G1XYZZ::load(p.sg + uint64_t(2 * b + 1) * L1));
     ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b + 2) * L1));
     ec_add<FqOps>(acc, G1XYZZ::load(p.fx1 + uint64_t(4 * b + 3) * L1));
-    write_canonical<FqOps>(p.proof + uint64_t(b) * 48 + 36, acc);
+    write_canonical<FqOps>(p.proof + uint64_t(b) * 48 + 36, acc, p.B == 1);
 }
 
 static void free_dev(void* p) {
