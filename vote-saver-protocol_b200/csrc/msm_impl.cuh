@@ -49,6 +49,7 @@ struct MsmPlan {
 // ---------------------------------------------------------------------------------------------
 // 1. digits + histogram
 // ---------------------------------------------------------------------------------------------
+constexpr uint32_t AGG_BUCKETS = 32;
 __global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t scalar_stride, MsmPlan p,
                              uint32_t* __restrict__ keys, uint32_t* __restrict__ counts, int count_here) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -83,7 +84,17 @@ __global__ void k_msm_digits(const uint32_t* __restrict__ scalars, uint64_t n, u
             if (d) key = (set << p.nb_log) + d - 1u;
         }
         keys[(uint64_t(b) * p.windows + w) * n + i] = key;
-        if (count_here && key != KEY_NONE) atomicAdd(&counts[key & 0x7fffffffu], 1u);
+        // a 0/1 (or small-valued) witness sends every lane to the same few counters: for the lowest AGG_BUCKETS
+        // buckets of a set, one atomic per distinct bucket in the warp; uniform digits take the plain atomic
+        if (count_here && key != KEY_NONE) {
+            const uint32_t bk = key & 0x7fffffffu;
+            if ((bk & ((1u << p.nb_log) - 1u)) < AGG_BUCKETS) {
+                const unsigned grp = __match_any_sync(__activemask(), bk);
+                if ((threadIdx.x & 31u) == unsigned(__ffs(grp) - 1)) atomicAdd(&counts[bk], (uint32_t)__popc(grp));
+            } else {
+                atomicAdd(&counts[bk], 1u);
+            }
+        }
     }
 }
 
@@ -191,7 +202,18 @@ __global__ void k_msm_scatter(const uint32_t* __restrict__ keys, uint64_t total,
     const uint32_t key = keys[q];
     if (key == KEY_NONE) return;
     const uint32_t bk = key & 0x7fffffffu;
-    const uint32_t pos = offsets[bk] + atomicAdd(&cursors[bk], 1u);
+    uint32_t pos;
+    if ((bk & ((1u << p.nb_log) - 1u)) < AGG_BUCKETS) {
+        // warp-aggregated cursor (see k_msm_digits): lanes holding the same bucket take consecutive slots from one atomic
+        const unsigned grp = __match_any_sync(__activemask(), bk);
+        const unsigned lane = threadIdx.x & 31u, leader = unsigned(__ffs(grp) - 1);
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&cursors[bk], (uint32_t)__popc(grp));
+        base = __shfl_sync(grp, base, leader);
+        pos = offsets[bk] + base + (uint32_t)__popc(grp & ((1u << lane) - 1u));
+    } else {
+        pos = offsets[bk] + atomicAdd(&cursors[bk], 1u);
+    }
     const uint64_t row = q / n;  // ballot * windows + window
     const uint32_t i = (uint32_t)(q - row * n);
     const uint32_t w = (uint32_t)(row % p.windows);
