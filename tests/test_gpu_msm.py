@@ -120,3 +120,21 @@ def test_g1_multiexp_checksum_full_size(vsp, ctx, log_n):
         ab = cref.ints_to_limbs([(x + y) % o.R for x, y in zip(cref.limbs_to_ints(scalars), cref.limbs_to_ints(b))], 4)
         lhs = vsp.points_sum(ctx, np.stack([h.multiexp(scalars), h.multiexp(b)]))
         assert np.array_equal(lhs, h.multiexp(ab))
+
+
+def test_g1_multiexp_one_hot_bucket_at_scale(vsp, ctx):
+    """2^21 points under a 0/1 witness: every non-zero digit lands in ONE bucket (32,768 tasks), which exercises the
+    sliced two-level collapse beyond its minimum slice length and the warp-aggregated counters of the global sort;
+    then the same points with small scalars (values 1..8: a handful of hot buckets).  Checksum as above."""
+    n, seed = 1 << 21, 77
+    h = vsp.G1Bases.generate(ctx, n, seed)
+    k = generated_base_scalars(n, seed).astype(object)
+    rng = np.random.default_rng(5)
+    bits = np.zeros((n, 4), dtype=np.uint64)
+    bits[:, 0] = rng.integers(0, 2, size=n, dtype=np.uint64)
+    small = np.zeros((n, 4), dtype=np.uint64)
+    small[:, 0] = rng.integers(1, 9, size=n, dtype=np.uint64)
+    for sc in (bits, _ones(n), small):
+        acc = int((k * sc[:, 0].astype(object)).sum()) % o.R
+        assert np.array_equal(h.multiexp(sc), cref.g1_mul(acc, G1_GEN_LIMBS))
+    h.close()
