@@ -62,6 +62,16 @@ def test_variable_base_multiples_match_oracle(ctx):
     got = vsp.g1_mul_batch(ctx, pts, sc)
     for i, k in enumerate(fr_ints(sc)):
         assert np.array_equal(got[i], cref.g1_mul(k, pts[i]))
+    # the G1 jobs split k = k1 + k2 * lambda, lambda = z^2 - 1 (endomorphism): scalars around every boundary of the split
+    z2 = 0xd201000000010000 ** 2
+    lam = z2 - 1
+    assert (lam * lam + lam + 1) % o.R == 0
+    edge = [0, 1, 2, lam, z2, z2 - 2, z2 + 1, 2 * z2 - 1, (1 << 128) - 1, 1 << 128, (1 << 128) + 1, (o.R - 1) // z2 * z2,
+            (o.R - 1) // z2 * z2 - 1, o.R - 1, o.R - 2, (o.R - 1) // 2, lam * lam % o.R, (1 << 254) + 12345]
+    epts = random_g1(len(edge), seed=6)
+    got = vsp.g1_mul_batch(ctx, epts, cref.ints_to_limbs(edge, 4))
+    for i, k in enumerate(edge):
+        assert np.array_equal(got[i], cref.g1_mul(k, epts[i])), hex(k)
 
 
 def _check_keypair(ctx, cs, toxic):

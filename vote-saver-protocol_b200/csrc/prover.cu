@@ -19,6 +19,7 @@
 //   main   : A w / B w / C w  ->  3B batched iNTT+coset, NTT  ->  pointwise H  ->  coset iNTT  ->  multiexp H  ->  assembly
 //   side 2 : multiexp A, multiexp L       side 3 : fixed-base r/s multiples, multiexp B (G2), multiexp B (G1)
 #include "common.cuh"
+#include <type_traits>
 #include "ec.cuh"
 #include "host_fr.h"
 #include "msm.cuh"
@@ -218,9 +219,69 @@ VSP_DEV XYZZ<F> ec_scalar_mul(const Affine<F>& p, const uint32_t* k) {
     return acc;
 }
 
+// G1 endomorphism (GLV): phi(x, y) = (beta x, y) = lambda (x, y) with lambda = z^2 - 1 (z the BLS parameter), since
+// lambda^2 + lambda + 1 = z^4 - z^2 + 1 = r.  A scalar k < r splits as k = q (lambda + 1) + rem = (q + rem) + q lambda
+// with q = floor(k / z^2) < 2^128, so k P = k1 P + k2 phi(P) with k1 = q + rem < 2^129, k2 = q: one joint
+// double-and-add over 129 bits with the table {P, phi P, P + phi P} instead of 255 doublings.  beta is the cube root of
+// unity matching this lambda (checked against the CPU restatement's lambda * G in tests/test_gpu_keygen.py through
+// vsp_g1_mul_batch); canonical limbs here, converted once per thread.
+__device__ const uint32_t GLV_BETA[12] = {0x0000aaacu, 0x8bfd0000u, 0x4f49fffdu, 0x409427ebu, 0x0fb85f9bu, 0x897d2965u, 0x89759ad4u, 0xaa0d857du, 0x63d4de85u, 0xec024086u, 0x397fe699u, 0x1a0111eau};
+VSP_DEV void glv_split(const uint32_t* k, uint32_t (&k1)[5], uint32_t (&k2)[4]) {
+    const uint64_t Lhi = 0xac45a4010001a402ULL, Llo = 0x0000000100000000ULL;  // z^2
+    uint64_t rh = 0, rl = 0, qh = 0, ql = 0;
+    for (int bit = 255; bit >= 0; --bit) {
+        const uint64_t carry = rh >> 63;
+        rh = (rh << 1) | (rl >> 63);
+        rl = (rl << 1) | ((k[bit >> 5] >> (bit & 31)) & 1u);
+        if (carry || rh > Lhi || (rh == Lhi && rl >= Llo)) {
+            const uint64_t borrow = rl < Llo ? 1u : 0u;
+            rl -= Llo;
+            rh = rh - Lhi - borrow;
+            if (bit < 64)
+                ql |= uint64_t(1) << bit;
+            else if (bit < 128)
+                qh |= uint64_t(1) << (bit - 64);
+        }
+    }
+    const uint64_t sl = ql + rl, c0 = sl < ql ? 1u : 0u;
+    const uint64_t t = qh + rh, c1 = t < qh ? 1u : 0u;
+    const uint64_t sh = t + c0, c2 = sh < t ? 1u : 0u;
+    k1[0] = (uint32_t)sl; k1[1] = (uint32_t)(sl >> 32); k1[2] = (uint32_t)sh; k1[3] = (uint32_t)(sh >> 32);
+    k1[4] = (uint32_t)(c1 + c2);
+    k2[0] = (uint32_t)ql; k2[1] = (uint32_t)(ql >> 32); k2[2] = (uint32_t)qh; k2[3] = (uint32_t)(qh >> 32);
+}
+// k * P on G1 by the split above; P Montgomery affine, not infinity; k canonical < r
+VSP_DEV G1XYZZ ec_scalar_mul_glv(const G1Affine& p, const uint32_t* k) {
+    uint32_t k1[5], k2[4];
+    glv_split(k, k1, k2);
+    Fq beta;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) beta.l[i] = GLV_BETA[i];
+    G1Affine ph = p;
+    ph.x = fp_mul(p.x, fp_to_mont(beta));
+    G1XYZZ both = G1XYZZ::from_affine(p);
+    ec_madd<FqOps>(both, ph);  // P + phi(P): distinct points, neither the other's negative (lambda != +-1)
+    G1XYZZ acc = G1XYZZ::inf();
+    int top = 128;
+    while (top >= 0 && !(((k1[top >> 5] >> (top & 31)) | (top < 128 ? k2[top >> 5] >> (top & 31) : 0u)) & 1u)) --top;
+    for (int bit = top; bit >= 0; --bit) {
+        acc = ec_dbl<FqOps>(acc);
+        const uint32_t b1 = (k1[bit >> 5] >> (bit & 31)) & 1u;
+        const uint32_t b2 = bit < 128 ? (k2[bit >> 5] >> (bit & 31)) & 1u : 0u;
+        if (b1 & b2)
+            ec_add<FqOps>(acc, both);
+        else if (b1)
+            ec_madd<FqOps>(acc, p);
+        else if (b2)
+            ec_madd<FqOps>(acc, ph);
+    }
+    return acc;
+}
+
 // out[i] (XYZZ, Montgomery) = scalars[i] * points[i];  points canonical affine (mont == 0) or Montgomery affine.
 // Variable-base multiples (s g_A, r g1_B; rerandomisation): one job per block, lane 0 of one warp — independent
 // scalars diverge at every add step, so jobs sharing a warp would serialise; separate warps run concurrently.
+// G1 jobs take the endomorphism split above; G2 jobs the plain double-and-add.
 template <class F>
 __global__ void k_scalar_mul_batch(const uint64_t* __restrict__ points, const uint32_t* __restrict__ scalars, unsigned n,
                                    int mont, uint32_t* __restrict__ out) {
@@ -234,7 +295,12 @@ __global__ void k_scalar_mul_batch(const uint64_t* __restrict__ points, const ui
     uint32_t k[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) k[q] = scalars[8 * i + q];
-    XYZZ<F> r = ec_scalar_mul<F>(p, k);
+    XYZZ<F> r;
+    if constexpr (std::is_same<F, FqOps>::value) {
+        r = p.is_inf() ? XYZZ<F>::inf() : ec_scalar_mul_glv(p, k);
+    } else {
+        r = ec_scalar_mul<F>(p, k);
+    }
     r.store(out + uint64_t(i) * (XYZZ<F>::BYTES / 4));
 }
 
