@@ -183,3 +183,34 @@ def test_prove_from_fast_proving_key_blob_to_proof_bytes(vsp, ctx):
     assert codec.proof_bytes(proof) == (o.g1_compress(o.G1.from_affine(gA)) + o.g2_compress(o.G2.from_affine(gB)) +
                                         o.g1_compress(o.G1.from_affine(gC)))
     pk.close()
+
+
+def test_tuning_switches_do_not_change_results(vsp, ctx, monkeypatch):
+    """DESIGN.md 4 'tuning switches': a 12-ballot batch (shared-memory sort, radix-4 NTT passes by default) proved again
+    under the global-counter sort, the radix-2 pass kernel, another reduction segment length and another window width;
+    every proof identical, and ballot 0 equal to the oracle's"""
+    nc, ni, k = 1000, 30, 12
+    cs, _, _ = synthetic_r1cs(nc, ni, 0, binary=True)
+    arr = synthetic_pk_arrays(cs, 5)
+    prim, aux, rs = [], [], []
+    rng = random.Random(19)
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=b, binary=True)
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R), rng.randrange(o.R), 0], 4))
+    prim, aux, rs = np.stack(prim), np.stack(aux), np.stack(rs)
+
+    def run():
+        pk = vsp.ProvingKey(ctx, arr)
+        out = pk.prove_batch(prim, aux, rs)
+        pk.close()
+        return out
+
+    base = run()
+    r, s, _ = cref.limbs_to_ints(rs[0])
+    assert np.array_equal(base[0], cref.groth16_prove(_oracle_pk(arr), prim[0], aux[0], r, s))
+    for name, val in (("VSP_MSM_GLOBAL_SORT", "1"), ("VSP_NTT_RADIX2", "1"), ("VSP_MSM_SEG_LOG", "2"), ("VSP_MSM_C", "9")):
+        monkeypatch.setenv(name, val)
+        assert np.array_equal(run(), base), name
+        monkeypatch.delenv(name)
