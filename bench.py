@@ -632,9 +632,9 @@ def main():
             "gpu_launches": res["launches"], "clocks": res["clocks"],
             "roofline": {"bound": "int32-mad", "kernel": "k_msm_accumulate<G1>", "achieved": ach, "peak": p_int / 1e12,
                          "unit": "TMAD/s", "frac": ach / (p_int / 1e12) if p_int else None,
-                         "traffic": 5.738e9 if batch_chunk_env() == 64 and args.constraints == NUM_CONSTRAINTS else None,
+                         "traffic": 5.750e9 if batch_chunk_env() == 64 and args.constraints == NUM_CONSTRAINTS else None,
                          "traffic_note": "dram read+write bytes of the H_query launch of one 64-ballot chunk, ncu --set full "
-                                         "(profiles/r01d_ncu_full_msm_accumulate.txt)",
+                                         "(profiles/r01l_ncu_full_msm_accumulate.txt: 5.351 GB read + 0.399 GB written; 5.738 GB in r01d)",
                          "launches": acc["launches"], "avg_launch_ms": acc["ms"] / max(acc["launches"], 1),
                          "share_of_kernel_time": acc["ms"] / tot_ms,
                          "peak_source": "vsp_measure_imad_rate, measured in this run (MEASURED_PEAKS.json has no "
