@@ -88,4 +88,7 @@ void emul_g2_op(int op, const uint64_t* a, const uint64_t* b, uint32_t k, uint64
 // raw Montgomery product of unreduced-domain limbs (checks fp_mul on arbitrary < p inputs without conversions)
 void emul_fq_montmul_raw(const uint64_t* a, const uint64_t* b, uint64_t* out) { st<FqCfg>(out, fp_mul(ld<FqCfg>(a), ld<FqCfg>(b))); }
 void emul_fr_montmul_raw(const uint64_t* a, const uint64_t* b, uint64_t* out) { st<FrCfg>(out, fp_mul(ld<FrCfg>(a), ld<FrCfg>(b))); }
+// raw Montgomery square (fp_sqr's own schedule: doubled cross products + diagonal, then the sliding-frame reduction)
+void emul_fq_montsqr_raw(const uint64_t* a, uint64_t* out) { st<FqCfg>(out, fp_sqr(ld<FqCfg>(a))); }
+void emul_fr_montsqr_raw(const uint64_t* a, uint64_t* out) { st<FrCfg>(out, fp_sqr(ld<FrCfg>(a))); }
 }

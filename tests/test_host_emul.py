@@ -52,6 +52,27 @@ def test_raw_montgomery_product(emul, name, mod, limbs):
         assert limbs_to_ints(O)[0] == a * b * rinv % mod
 
 
+@pytest.mark.parametrize("name,mod,limbs", [("fr", o.R, 4), ("fq", o.P, 6)])
+def test_raw_montgomery_square(emul, name, mod, limbs):
+    """fp_sqr has its own limb schedule (cross products once, doubled; sliding-frame reduction): raw < p inputs whose
+    32-bit limbs are biased to all-ones / zero / one so every carry path of the chains fires"""
+    fn = getattr(emul, "emul_%s_montsqr_raw" % name)
+    rinv = pow(1 << (64 * limbs), -1, mod)
+    rng = random.Random(11)
+    pool = [0xffffffff, 0, 1, 0x80000000, 0x7fffffff, 0xfffffffe]
+    vals = [0, 1, mod - 1, mod - 2, mod >> 1, (1 << (32 * limbs)) % mod]
+    while len(vals) < 1500:
+        ws = [rng.choice(pool) if rng.random() < 0.7 else rng.getrandbits(32) for _ in range(2 * limbs)]
+        v = sum(w << (32 * i) for i, w in enumerate(ws))
+        if len(vals) % 3 == 0:
+            v = rng.randrange(mod)
+        vals.append(v % mod if v >= mod and rng.random() < 0.5 else (v if v < mod else v & ((1 << (mod.bit_length() - 1)) - 1)))
+    for a in vals:
+        A, O = ints_to_limbs([a], limbs), np.zeros((1, limbs), np.uint64)
+        fn(P(A), P(O))
+        assert limbs_to_ints(O)[0] == a * a * rinv % mod, (name, hex(a))
+
+
 @pytest.mark.parametrize("grp", ["g1", "g2"])
 def test_curve_ops(emul, grp):
     fn = getattr(emul, "emul_%s_op" % grp)

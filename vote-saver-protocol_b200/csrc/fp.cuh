@@ -314,9 +314,94 @@ VSP_DEV Fp<C> fp_mul(const Fp<C>& a, const Fp<C>& b) {
     return r;
 }
 
+// Montgomery square a^2 / 2^(32N) mod p.  The N(N-1)/2 cross products a_i a_j (i < j) are formed once and doubled, so a
+// square costs N(N-1)/2 + N + N^2 + N multiply-adds (Fq: 234, Fr: 108) against the product's 2N^2 + N (300 / 136).
+// Same two-accumulator discipline as fp_mul so every lo/hi pair is one IMAD.WIDE: a product landing on an even 32-bit
+// column goes to Ev (pair Ev[c], Ev[c+1]), on an odd column to Od (Od[k] is column k + 1), rows i in increasing order so
+// the limb above a row's chain has only ever held carries.  Then T = 2 (Ev + Od 2^32) + sum a_i^2 2^(64 i) as a flat
+// 2N-limb integer, reduced column by column on the sliding (E, O) frame of mont_reduce_column; the frame's shift is a
+// role swap plus one carry ripple, and limb N + i of T enters the frame's top as row i leaves.
 template <class C>
 VSP_DEV Fp<C> fp_sqr(const Fp<C>& a) {
-    return fp_mul(a, a);
+    constexpr int N = C::N;
+    static_assert(N % 2 == 0 && N >= 4, "even limb count expected");
+    uint32_t Ev[2 * N], Od[2 * N];
+#pragma unroll
+    for (int k = 0; k < 2 * N; ++k) Ev[k] = Od[k] = 0u;
+#pragma unroll
+    for (int i = 0; i < N - 1; ++i) {
+        // partners j = i + 1, i + 3, ...: odd columns i + j -> Od[i + j - 1], Od[i + j]
+        {
+            const int jl = ((N - 1 - (i + 1)) & 1) ? N - 2 : N - 1;  // last partner of this parity
+#pragma unroll
+            for (int j = i + 1; j < N; j += 2) {
+                const int c = i + j - 1;
+                Od[c] = (j == i + 1) ? ptx::mad_lo_cc(a.l[i], a.l[j], Od[c]) : ptx::madc_lo_cc(a.l[i], a.l[j], Od[c]);
+                Od[c + 1] = ptx::madc_hi_cc(a.l[i], a.l[j], Od[c + 1]);
+            }
+            Od[i + jl + 1] = ptx::addc(Od[i + jl + 1], 0u);
+        }
+        // partners j = i + 2, i + 4, ...: even columns i + j -> Ev[i + j], Ev[i + j + 1]
+        if (i + 2 < N) {
+            const int jl = ((N - 1 - (i + 2)) & 1) ? N - 2 : N - 1;
+#pragma unroll
+            for (int j = i + 2; j < N; j += 2) {
+                const int c = i + j;
+                Ev[c] = (j == i + 2) ? ptx::mad_lo_cc(a.l[i], a.l[j], Ev[c]) : ptx::madc_lo_cc(a.l[i], a.l[j], Ev[c]);
+                Ev[c + 1] = ptx::madc_hi_cc(a.l[i], a.l[j], Ev[c + 1]);
+            }
+            Ev[i + jl + 2] = ptx::addc(Ev[i + jl + 2], 0u);
+        }
+    }
+    // T = Ev + Od 2^32 (the cross sum is < 2^(64N - 1): no carry out), doubled, plus the diagonal
+    uint32_t T[2 * N];
+    T[0] = Ev[0];
+    T[1] = ptx::add_cc(Ev[1], Od[0]);
+#pragma unroll
+    for (int k = 2; k < 2 * N - 1; ++k) T[k] = ptx::addc_cc(Ev[k], Od[k - 1]);
+    T[2 * N - 1] = ptx::addc(Ev[2 * N - 1], Od[2 * N - 2]);
+#pragma unroll
+    for (int k = 2 * N - 1; k > 0; --k) T[k] = (T[k] << 1) | (T[k - 1] >> 31);
+    T[0] <<= 1;
+    T[0] = ptx::mad_lo_cc(a.l[0], a.l[0], T[0]);
+    T[1] = ptx::madc_hi_cc(a.l[0], a.l[0], T[1]);
+#pragma unroll
+    for (int i = 1; i < N - 1; ++i) {
+        T[2 * i] = ptx::madc_lo_cc(a.l[i], a.l[i], T[2 * i]);
+        T[2 * i + 1] = ptx::madc_hi_cc(a.l[i], a.l[i], T[2 * i + 1]);
+    }
+    T[2 * N - 2] = ptx::madc_lo_cc(a.l[N - 1], a.l[N - 1], T[2 * N - 2]);
+    T[2 * N - 1] = ptx::madc_hi(a.l[N - 1], a.l[N - 1], T[2 * N - 1]);
+    // reduction: frame value = E + O 2^32 over limbs [i, i + N]
+    uint32_t E[N], O[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        E[k] = T[k];
+        O[k] = 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < N - 1; ++i) {
+        mont_reduce_column<C>(E, O);  // E[0] = 0 now
+        uint32_t nO[N];
+        O[0] = ptx::add_cc(O[0], E[1]);
+#pragma unroll
+        for (int k = 0; k < N - 2; ++k) nO[k] = ptx::addc_cc(E[k + 2], 0u);
+        nO[N - 2] = ptx::addc_cc(T[N + i], 0u);
+        nO[N - 1] = ptx::addc(0u, 0u);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+            E[k] = O[k];
+            O[k] = nO[k];
+        }
+    }
+    mont_reduce_column<C>(E, O);
+    Fp<C> r;
+    r.l[0] = ptx::add_cc(O[0], E[1]);
+#pragma unroll
+    for (int k = 1; k < N - 1; ++k) r.l[k] = ptx::addc_cc(O[k], E[k + 1]);
+    r.l[N - 1] = ptx::addc(O[N - 1], T[2 * N - 1]);
+    fp_reduce_once(r);
+    return r;
 }
 
 template <class C>
