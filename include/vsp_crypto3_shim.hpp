@@ -33,6 +33,11 @@
 #include <string>
 #include <utility>
 #include <vector>
+#if defined(__linux__)
+#include <cerrno>
+#include <sys/random.h>
+#include <sys/types.h>
+#endif
 
 #include <tuple>
 
@@ -82,10 +87,10 @@ namespace b200 {
     // uniform element of Fr by rejection sampling (stands in for random::algebraic_random_device, common.hpp:1131)
     template<typename Engine>
     fr_value random_fr(Engine &eng) {
-        std::uniform_int_distribution<std::uint64_t> d;
+        static_assert(Engine::min() == 0 && Engine::max() == ~std::uint64_t(0), "64 uniform bits per draw expected");
         for (;;) {
             fr_value x;
-            for (auto &v : x.l) v = d(eng);
+            for (auto &v : x.l) v = eng();
             x.l[3] &= 0x7fffffffffffffffull;
             if (fr_is_reduced(x)) return x;
         }
@@ -506,8 +511,36 @@ namespace zk {
             std::memcpy(proof.g_C.l.data(), out + 36, 96);
             return proof;
         }
-        inline std::mt19937_64 &blinding_engine() {
-            static std::mt19937_64 eng {std::random_device {}()};
+        // Every secret scalar (the generator's toxic waste, Groth16 r and s, SAVER's encryption and rerandomisation
+        // randomness) comes from the operating system's CSPRNG, 64 bits per call, as the reference draws them from
+        // random::algebraic_random_device (common.hpp:923, 1131): getrandom(2) on Linux, std::random_device (one call per
+        // 32-bit half) elsewhere.  No seeded PRNG sits between the OS and a secret; a short read or an error throws.
+        struct os_entropy_engine {
+            typedef std::uint64_t result_type;
+            static constexpr result_type min() { return 0; }
+            static constexpr result_type max() { return ~result_type(0); }
+            result_type operator()() {
+                result_type v = 0;
+#if defined(__linux__)
+                unsigned char *p = reinterpret_cast<unsigned char *>(&v);
+                std::size_t got = 0;
+                while (got < sizeof(v)) {
+                    const ssize_t n = ::getrandom(p + got, sizeof(v) - got, 0);
+                    if (n < 0) {
+                        if (errno == EINTR) continue;
+                        throw std::runtime_error("getrandom failed: no OS entropy for a secret scalar");
+                    }
+                    got += static_cast<std::size_t>(n);
+                }
+#else
+                std::random_device rd;
+                v = (result_type(rd()) << 32) | result_type(rd() & 0xffffffffu);
+#endif
+                return v;
+            }
+        };
+        inline os_entropy_engine &blinding_engine() {
+            static os_entropy_engine eng;
             return eng;
         }
     }    // namespace detail

@@ -237,11 +237,13 @@ VSP_DEV Fp<C> fp_dbl(const Fp<C>& a) {
 }
 
 // One Montgomery reduction column: m = E[0] * INV;  O += m * p_odd;  E += m * p_even  (E[0] becomes 0).
-template <class C>
+// CARRY_IN: the O chain starts from the carry flag left by the caller's last .cc instruction (a carry into column 1 of
+// the frame, which is where O[0] sits), so a frame shift needs no ripple of its own.
+template <class C, bool CARRY_IN = false>
 VSP_DEV void mont_reduce_column(uint32_t (&E)[C::N], uint32_t (&O)[C::N]) {
     constexpr int N = C::N;
     const uint32_t m = E[0] * C::INV;
-    O[0] = ptx::mad_lo_cc(C::mod(1), m, O[0]);
+    O[0] = CARRY_IN ? ptx::madc_lo_cc(C::mod(1), m, O[0]) : ptx::mad_lo_cc(C::mod(1), m, O[0]);
     O[1] = ptx::madc_hi_cc(C::mod(1), m, O[1]);
 #pragma unroll
     for (int k = 2; k < N - 2; k += 2) {
@@ -379,22 +381,25 @@ VSP_DEV Fp<C> fp_sqr(const Fp<C>& a) {
         E[k] = T[k];
         O[k] = 0u;
     }
+    mont_reduce_column<C>(E, O);  // E[0] = 0 now
 #pragma unroll
     for (int i = 0; i < N - 1; ++i) {
-        mont_reduce_column<C>(E, O);  // E[0] = 0 now
+        // frame shift by one limb: the old O becomes the even accumulator, the old E >> 64 (topped up with limb N + i of
+        // T) the odd one; the carry of O[0] + E[1] belongs to column 1 of the new frame and rides into the next
+        // column's O chain (its last addc cannot overflow: the frame value stays below 2^(32 (N + 1)))
         uint32_t nO[N];
-        O[0] = ptx::add_cc(O[0], E[1]);
 #pragma unroll
-        for (int k = 0; k < N - 2; ++k) nO[k] = ptx::addc_cc(E[k + 2], 0u);
-        nO[N - 2] = ptx::addc_cc(T[N + i], 0u);
-        nO[N - 1] = ptx::addc(0u, 0u);
+        for (int k = 0; k < N - 2; ++k) nO[k] = E[k + 2];
+        nO[N - 2] = T[N + i];
+        nO[N - 1] = 0u;
+        const uint32_t e0 = ptx::add_cc(O[0], E[1]);
 #pragma unroll
-        for (int k = 0; k < N; ++k) {
-            E[k] = O[k];
-            O[k] = nO[k];
-        }
+        for (int k = 1; k < N; ++k) E[k] = O[k];
+        E[0] = e0;
+#pragma unroll
+        for (int k = 0; k < N; ++k) O[k] = nO[k];
+        mont_reduce_column<C, true>(E, O);
     }
-    mont_reduce_column<C>(E, O);
     Fp<C> r;
     r.l[0] = ptx::add_cc(O[0], E[1]);
 #pragma unroll
