@@ -288,7 +288,9 @@ typedef struct {
  * of `pairs` pairings: g1 / g2 hold n_checks x pairs canonical affine points; gt_out[c] = prod_j e(g1[c][j], g2[c][j])
  * as a canonical Fq12 (72 limbs, tower order c0.c0 | c0.c1 | c0.c2 | c1.c0 | c1.c1 | c1.c2 over Fq2 = c0 | c1,
  * Fq12 = Fq6[w]/(w^2 - v), Fq6 = Fq2[v]/(v^3 - (1 + u))); is_one[c] = 1 iff the product is the identity.  Either
- * output may be NULL.  A pair with a point at infinity contributes 1. */
+ * output may be NULL.  A pair with a point at infinity contributes 1.  The value is crypto3's pair_reduced, i.e. the
+ * Miller value to the power 3 (p^12 - 1) / r (the cube of the textbook reduced pairing; pinned on the alpha_g1_beta_g2
+ * stored in the reference's bin/cli/src/data.bin). */
 VSP_API int vsp_pairing_products(vsp_ctx *ctx, uint64_t n_checks, uint64_t pairs, const uint64_t *g1, const uint64_t *g2,
                                  uint64_t *gt_out, uint8_t *is_one);
 /* zk::verify<r1cs_gg_ppzksnark<...>>(vk, primary_input, proof) for k proofs on one key (basic mode;
@@ -297,6 +299,18 @@ VSP_API int vsp_pairing_products(vsp_ctx *ctx, uint64_t n_checks, uint64_t pairs
  * primary: k x n_primary canonical Fr; vk->gamma_ABC_count must be n_primary + 1; proofs: k x 48 limbs. */
 VSP_API int vsp_groth16_verify_batch(vsp_ctx *ctx, const vsp_verification_key_t *vk, uint64_t k, const uint64_t *primary,
                                      uint64_t n_primary, const uint64_t *proofs, uint8_t *ok_out);
+/* The same with the verification key in the reference's own form (libs/marshalling/zk/.../verification_key.hpp:69-75:
+ * alpha_g1_beta_g2 = pair_reduced(alpha_g1, beta_g2) as an Fq12 value, not alpha and beta): ok_out[b] = 1 iff
+ *   e(A, B) = alpha_g1_beta_g2 * e(gamma_ABC.first + sum_i x_i gamma_ABC.rest[i], gamma) * e(C, delta)
+ * compared as canonical Fq12 values.  alpha_g1_beta_g2: 72 limbs in the order vsp_pairing_products writes, which is the
+ * order the reference serialises (pinned on bin/cli/src/data.bin, tests/golden/databin_groth16.json). */
+VSP_API int vsp_groth16_verify_gt_batch(vsp_ctx *ctx, const uint64_t *alpha_g1_beta_g2, const uint64_t *gamma_g2,
+                                        const uint64_t *delta_g2, uint64_t gamma_ABC_count, const uint64_t *gamma_ABC_g1,
+                                        uint64_t k, const uint64_t *primary, uint64_t n_primary, const uint64_t *proofs,
+                                        uint8_t *ok_out);
+/* Both verifiers first check what the prover sent (A, B, C, the cipher text): coordinates reduced mod p, on the curve /
+ * twist, in the order-r subgroup (proof.is_well_formed() and the decoders' guarantees in the reference); an ill-formed
+ * element gives ok_out[b] = 0.  The point at infinity is well formed. */
 /* verify_encryption_op<elgamal_verifiable>::process -> zk::verify<..., encrypted_input>(ct, vk, pubkey,
  * unencrypted_primary_input, proof) (elgamal_verifiable.hpp:486-490) for k ballots: ok_out[b] = 1 iff
  *   prod_{i <= n} e(ct_i, t_g2[i]) = e(ct_{n+1}, G2)   and
@@ -330,6 +344,11 @@ VSP_API int vsp_codec_g1_compress(const uint64_t *point, uint8_t *out48);
 VSP_API int vsp_codec_g2_compress(const uint64_t *point, uint8_t *out96);
 /* proof g_A | g_B | g_C (48 limbs) -> 192 bytes (zk/.../r1cs_gg_ppzksnark/proof.hpp:63-71) */
 VSP_API int vsp_codec_proof_write(const uint64_t *proof, uint8_t *out192);
+/* the decoders (processing/curve_element.hpp:176-395, proof.hpp:86-102): compressed octets -> canonical affine limbs;
+ * VSP_E_INVALID for a malformed encoding (C bit clear, non-canonical infinity, x >= p) or an x with no curve point */
+VSP_API int vsp_codec_g1_decompress(const uint8_t *in48, uint64_t *point);
+VSP_API int vsp_codec_g2_decompress(const uint8_t *in96, uint64_t *point);
+VSP_API int vsp_codec_proof_read(const uint8_t *in192, uint64_t *proof);
 /* n cipher-text G1 points -> 8 + 48 n bytes; n Fr -> 8 + 32 n bytes (zk/.../r1cs_gg_ppzksnark/primary_input.hpp:61-97) */
 VSP_API int vsp_codec_ciphertext_write(const uint64_t *ct, uint64_t n, uint8_t *out);
 VSP_API int vsp_codec_primary_input_write(const uint64_t *values, uint64_t n, uint8_t *out);

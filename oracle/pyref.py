@@ -556,6 +556,18 @@ class Curve:
                 acc = self.add(acc, p)
         return acc
 
+    def mul_raw(self, k: int, p):
+        """k * p with k taken as it is (mul reduces k mod r, which is only right for points of order r): the subgroup check"""
+        acc = self.inf()
+        for bit in bin(k)[2:] if k else "":
+            acc = self.dbl(acc)
+            if bit == "1":
+                acc = self.add(acc, p)
+        return acc
+
+    def in_subgroup(self, p) -> bool:
+        return self.is_inf(self.mul_raw(R, p))
+
     def eq(self, p, q):
         return self.to_affine(p) == self.to_affine(q)
 
@@ -599,6 +611,77 @@ def g2_compress(p) -> bytes:
     s = _sign_fq(y0) if y1 == 0 else _sign_fq(y1)
     out[0] |= 0x80 | (0x20 if s else 0)
     return bytes(out)
+
+
+def fq_sqrt(a: int):
+    """square root in Fq (p = 3 mod 4) or None"""
+    r = pow(a % P, (P + 1) // 4, P)
+    return r if r * r % P == a % P else None
+
+
+def fq2_sqrt(a):
+    """a square root of a = (a0, a1) in Fq2 = Fq[u]/(u^2 + 1), or None"""
+    a0, a1 = a[0] % P, a[1] % P
+    if a1 == 0:
+        r = fq_sqrt(a0)
+        if r is not None:
+            return (r, 0)
+        r = fq_sqrt(-a0 % P)
+        return None if r is None else (0, r)
+    n = fq_sqrt((a0 * a0 + a1 * a1) % P)
+    if n is None:
+        return None
+    inv2 = pow(2, P - 2, P)
+    for nn in (n, -n % P):
+        x0 = fq_sqrt((a0 + nn) * inv2 % P)
+        if not x0:
+            continue
+        r = (x0, a1 * pow(2 * x0, P - 2, P) % P)
+        if _Fq2.sqr(r) == (a0, a1):
+            return r
+    return None
+
+
+def g1_decompress(b: bytes):
+    """octets -> affine point or None for infinity (processing/curve_element.hpp:176-255: the C bit must be set, the I bit
+    means infinity, x big-endian, y = the root whose sign matches the S bit).  ValueError where the reference fails."""
+    if len(b) != 48 or not b[0] & 0x80:
+        raise ValueError("not a compressed G1 encoding")
+    if b[0] & 0x40:
+        if any(b[1:]) or b[0] & 0x3f:
+            raise ValueError("non-canonical infinity")
+        return None
+    x = int.from_bytes(bytes([b[0] & 0x1f]) + b[1:], "big")
+    if x >= P:
+        raise ValueError("x not reduced")
+    y = fq_sqrt((x * x * x + 4) % P)
+    if y is None:
+        raise ValueError("x is not on the curve")
+    if _sign_fq(y) != bool(b[0] & 0x20):
+        y = -y % P
+    return (x, y)
+
+
+def g2_decompress(b: bytes):
+    """96 octets x.c1 | x.c0 -> affine twist point or None (processing/curve_element.hpp:257-395)"""
+    if len(b) != 96 or not b[0] & 0x80:
+        raise ValueError("not a compressed G2 encoding")
+    if b[0] & 0x40:
+        if any(b[1:]) or b[0] & 0x3f:
+            raise ValueError("non-canonical infinity")
+        return None
+    x1 = int.from_bytes(bytes([b[0] & 0x1f]) + b[1:48], "big")
+    x0 = int.from_bytes(b[48:], "big")
+    if x0 >= P or x1 >= P:
+        raise ValueError("x not reduced")
+    x = (x0, x1)
+    y = fq2_sqrt(_Fq2.add(_Fq2.mul(_Fq2.sqr(x), x), (4, 4)))
+    if y is None:
+        raise ValueError("x is not on the twist")
+    s = _sign_fq(y[0]) if y[1] == 0 else _sign_fq(y[1])
+    if s != bool(b[0] & 0x20):
+        y = _Fq2.neg(y)
+    return (x, y)
 
 
 def g1_uncompressed(p) -> bytes:
@@ -1119,11 +1202,22 @@ def miller_loop(p_aff, q_aff):
     return f12conj(f)  # x < 0
 
 
-_FINAL_EXP = (P ** 12 - 1) // R
+# crypto3's reduced pairing is the CUBE of the textbook one: its final exponentiation is the usual BLS12 chain
+# (x - 1)^2 (x + p)(x^2 + p^2 - 1) + 3 = 3 (p^4 - p^2 + 1) / r for the hard part.  Pinned on the reference's own artefact
+# bin/cli/src/data.bin (a Groth16 proof followed by its verification key, tests/golden/databin_groth16.json): the stored
+# alpha_g1_beta_g2 equals e(A, B) / (e(gamma_ABC[0], gamma) e(C, delta)) coefficient for coefficient under this exponent
+# and not under (p^12 - 1) / r.  gcd(3, r) = 1, so every accept / reject decision is the same either way.
+_FINAL_EXP_EXACT = (P ** 12 - 1) // R
+_FINAL_EXP = 3 * _FINAL_EXP_EXACT
 
 
 def final_exponentiation(f):
     return f12pow(f, _FINAL_EXP)
+
+
+def final_exponentiation_exact(f):
+    """f^((p^12 - 1) / r), the textbook reduced pairing (not what crypto3 stores in alpha_g1_beta_g2)"""
+    return f12pow(f, _FINAL_EXP_EXACT)
 
 
 def pairing_product_is_one(pairs) -> bool:
@@ -1134,8 +1228,23 @@ def pairing_product_is_one(pairs) -> bool:
     return final_exponentiation(f) == F12_ONE
 
 
+def _well_formed(curve: Curve, p) -> bool:
+    """what the reference guarantees before it pairs a prover-supplied element (proof.is_well_formed(), and its decoders
+    only produce curve points): on the curve and in the order-r subgroup; infinity is a group element"""
+    if curve.is_inf(p):
+        return True
+    return curve.on_curve_affine(curve.to_affine(p)) and curve.in_subgroup(p)
+
+
+def proof_is_well_formed(proof) -> bool:
+    gA, gB, gC = proof
+    return _well_formed(G1, gA) and _well_formed(G2, gB) and _well_formed(G1, gC)
+
+
 def groth16_verify(vk: VerificationKey, primary: Sequence[int], proof) -> bool:
     """e(A,B) = e(alpha,beta) e(acc, gamma) e(C, delta)   (basic mode)."""
+    if not proof_is_well_formed(proof):
+        return False
     gA, gB, gC = proof
     acc = vk.gamma_ABC_first
     for x, pt in zip(primary, vk.gamma_ABC_rest):
@@ -1144,11 +1253,36 @@ def groth16_verify(vk: VerificationKey, primary: Sequence[int], proof) -> bool:
         (G1.neg(gA), gB), (vk.alpha_g1, vk.beta_g2), (acc, vk.gamma_g2), (gC, vk.delta_g2)])
 
 
+def groth16_verify_gt(alpha_g1_beta_g2, gamma_g2, delta_g2, gamma_ABC_first, gamma_ABC_rest, primary: Sequence[int],
+                      proof) -> bool:
+    """zk::verify with the verification key as the reference stores it (verification_key.hpp:69-75: the GT element
+    alpha_g1_beta_g2, not alpha and beta):  e(A, B) = alpha_g1_beta_g2 * e(acc, gamma) * e(C, delta), compared as Fq12
+    values of pair_reduced.  Pinned on bin/cli/src/data.bin (tests/test_oracle.py)."""
+    if not proof_is_well_formed(proof):
+        return False
+    gA, gB, gC = proof
+    acc = gamma_ABC_first
+    for x, pt in zip(primary, gamma_ABC_rest):
+        acc = G1.add(acc, G1.mul(x, pt))
+    f = F12_ONE
+    for p, q in ((gA, gB), (G1.neg(acc), gamma_g2), (G1.neg(gC), delta_g2)):
+        f = f12mul(f, miller_loop(G1.to_affine(p), G2.to_affine(q)))
+    return final_exponentiation(f) == alpha_g1_beta_g2
+
+
+def gt_from_coeffs(c: Sequence[int]):
+    """12 Fq coefficients in tower order c0.c0.c0, c0.c0.c1, c0.c1.c0, ... -> Fq12 tuple"""
+    c = [int(x) % P for x in c]
+    return tuple(tuple((c[6 * i + 2 * j], c[6 * i + 2 * j + 1]) for j in range(3)) for i in range(2))
+
+
 def saver_verify_encryption(vk: VerificationKey, pub: SaverPublicKey, ct, unencrypted_primary, proof) -> bool:
     """verify_encryption_op (elgamal_verifiable.hpp:486-490) -> zk::verify<encrypted_input>  [UPSTREAM-RECALL]:
     ciphertext well-formedness  prod e(ct_i, t_g2[i]) = e(ct_last, G2)  and the Groth16 equation with the
     message slots replaced by the ciphertext elements."""
     n = len(ct) - 2
+    if not proof_is_well_formed(proof) or not all(_well_formed(G1, c) for c in ct):
+        return False
     pairs = [(ct[i], pub.t_g2[i]) for i in range(n + 1)]
     pairs.append((G1.neg(ct[-1]), g2_generator()))
     if not pairing_product_is_one(pairs):

@@ -172,14 +172,36 @@ def curve_vectors():
     return out
 
 
+def databin():
+    """bin/cli/src/data.bin (1,072 bytes, the only crypto3-made proof in the tree): the blob share/tvm/voting_voter.sol:94
+    hands to tvm.vergrth16 = proof | primary-input count | verification key.  Layout found by decoding it:
+      [0, 192)      proof, compressed g_A | g_B | g_C           (marshalling .../r1cs_gg_ppzksnark/proof.hpp:63-71)
+      [192, 196)    00 00 00 00: number of primary inputs (none)
+      [196, 772)    alpha_g1_beta_g2: 12 Fq coefficients, 48 bytes each, LITTLE-endian, tower order
+                    c0.c0.c0 | c0.c0.c1 | c0.c1.c0 | ... | c1.c2.c1   (verification_key.hpp:69)
+      [772, 964)    gamma_g2 | delta_g2 compressed               (verification_key.hpp:71-73)
+      [964, 1012)   gamma_ABC_g1.first compressed; [1012, 1072) zero: empty rest, padding
+    Every point decodes on its curve and lies in the order-r subgroup, and (tests/test_oracle.py)
+      e(g_A, g_B) = alpha_g1_beta_g2 * e(gamma_ABC.first, gamma_g2) * e(g_C, delta_g2)
+    holds coefficient for coefficient when the reduced pairing is f^(3 (p^12 - 1) / r)."""
+    with open(os.path.join(REF, "bin/cli/src/data.bin"), "rb") as f:
+        d = f.read()
+    assert len(d) == 1072 and d[192:196] == bytes(4) and not any(d[1012:])
+    return {"source": "bin/cli/src/data.bin", "proof": d[0:192].hex(), "n_primary": 0,
+            "alpha_g1_beta_g2": ["%096x" % int.from_bytes(d[196 + 48 * i:196 + 48 * (i + 1)], "little") for i in range(12)],
+            "gamma_g2": d[772:868].hex(), "delta_g2": d[868:964].hex(), "gamma_ABC_first": d[964:1012].hex()}
+
+
 def main():
     if not os.path.isdir(REF):
         sys.exit("needs /root/reference (build container only)")
+    with open(os.path.join(OUT, "databin_groth16.json"), "w") as f:
+        json.dump(databin(), f, indent=1)
     with open(os.path.join(OUT, "fr_fft_kat.json"), "w") as f:
         json.dump(fr_vectors(), f, indent=1)
     with open(os.path.join(OUT, "curve_kat.json"), "w") as f:
         json.dump(curve_vectors(), f, indent=1)
-    print("wrote fr_fft_kat.json, curve_kat.json")
+    print("wrote fr_fft_kat.json, curve_kat.json, databin_groth16.json")
 
 
 if __name__ == "__main__":

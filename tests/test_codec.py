@@ -159,3 +159,56 @@ def test_fast_proving_key_reader_and_writer_match_the_spec_serialiser(nc, ni, bi
         with pytest.raises(ValueError):
             codec.read_fast_proving_key(blob[:cut])
     assert codec.read_fast_proving_key(blob + b"trailing")["_sizes"]["bytes"] == len(blob)
+
+
+def test_decoders_invert_the_encoders_and_match_the_oracle():
+    """processing/curve_element.hpp:176-395: compressed octets -> points.  Known answers (the reference's blst encodings of
+    p4), round trips over random points of both curves against the oracle's decoder, the infinity encoding, and the
+    failure cases the reference's decoder has (C bit clear, x with no curve point, non-canonical infinity, x >= p)."""
+    k1 = golden("curve_kat.json")["g1_serialization"]
+    p4 = cref.g1_to_limbs([tuple(hexlist(k1["p4_affine"])[:2])])
+    assert np.array_equal(codec.g1_decompress(bytes.fromhex(k1["p4_octets_compressed"])), p4.reshape(-1))
+    k2 = golden("curve_kat.json")["g2_serialization"]
+    v = hexlist(k2["p4_affine"])
+    q4 = cref.g2_to_limbs([((v[0], v[1]), (v[2], v[3]))])
+    assert np.array_equal(codec.g2_decompress(bytes.fromhex(k2["p4_octets_compressed"])), q4.reshape(-1))
+    for pt in random_g1(16, seed=41):
+        enc = codec.g1_compress(pt)
+        assert np.array_equal(codec.g1_decompress(enc), pt)
+        assert cref.g1_to_limbs([o.g1_decompress(enc)]).reshape(-1).tolist() == pt.tolist()
+        neg = bytearray(enc)
+        neg[0] ^= 0x20  # the other root
+        got = codec.g1_decompress(bytes(neg))
+        assert np.array_equal(got[:6], pt[:6]) and cref.limbs_to_ints(got[6:12].reshape(1, 6))[0] == o.P - cref.limbs_to_ints(pt[6:12].reshape(1, 6))[0]
+    for pt in random_g2(12, seed=42):
+        enc = codec.g2_compress(pt)
+        assert np.array_equal(codec.g2_decompress(enc), pt)
+        assert cref.g2_to_limbs([o.g2_decompress(enc)]).reshape(-1).tolist() == pt.tolist()
+    assert not codec.g1_decompress(bytes([0xc0]) + bytes(47)).any()
+    assert not codec.g2_decompress(bytes([0xc0]) + bytes(95)).any()
+    good = codec.g1_compress(random_g1(1, seed=43)[0])
+    bad = [bytes([good[0] & 0x7f]) + good[1:],            # C bit clear
+           bytes([0xc0]) + bytes(46) + b"\x01",           # infinity with payload
+           bytes([0x9f]) + b"\xff" * 47]                  # x >= p
+    x = 5
+    while o.fq_sqrt((x ** 3 + 4) % o.P) is not None:
+        x += 1
+    bad.append(bytes([0x80 | (x.to_bytes(48, "big")[0])]) + x.to_bytes(48, "big")[1:])  # no point with this x
+    for b in bad:
+        with pytest.raises(ValueError):
+            codec.g1_decompress(b)
+        with pytest.raises(ValueError):
+            o.g1_decompress(b)
+
+
+def test_reference_made_proof_decodes():
+    """bin/cli/src/data.bin's proof (tests/golden/databin_groth16.json) through vsp_codec_proof_read: the same points the
+    oracle's decoder gives, and re-encoding reproduces the reference's bytes"""
+    g = golden("databin_groth16.json")
+    raw = bytes.fromhex(g["proof"])
+    proof = codec.proof_from_bytes(raw)
+    want = np.concatenate([cref.g1_to_limbs([o.g1_decompress(raw[:48])]).reshape(-1),
+                           cref.g2_to_limbs([o.g2_decompress(raw[48:144])]).reshape(-1),
+                           cref.g1_to_limbs([o.g1_decompress(raw[144:])]).reshape(-1)])
+    assert np.array_equal(proof, want)
+    assert codec.proof_bytes(proof) == raw

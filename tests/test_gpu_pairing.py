@@ -209,3 +209,79 @@ def test_empty_batches_and_infinity_proof_elements(ctx):
     ct0 = vsp.saver_ciphertext(ctx, vsp.SaverPublicKey(pub0), np.zeros((1, 12), np.uint64), np.zeros((0, 4), np.uint64), 11)
     m0, c0 = vsp.decrypt(ctx, ct0, rho0, svk0, np.zeros((1, 12), np.uint64))
     assert m0 == [] and vsp.verify_decryption(ctx, ct0, [], svk0, np.zeros((1, 12), np.uint64), c0)
+
+
+def test_reference_made_proof_verifies_on_the_gpu(ctx):
+    """bin/cli/src/data.bin (tests/golden/databin_groth16.json): the reference's own proof, decoded by the product codec,
+    is accepted under the reference's own verification key (alpha_g1_beta_g2 as a GT value) — and the GPU's pair_reduced
+    product reproduces that stored Fq12 element limb for limb, which pins its value convention on crypto3's."""
+    from helpers import golden
+    codec = importlib.import_module("vote-saver-protocol_b200.codec")
+    g = golden("databin_groth16.json")
+    proof = codec.proof_from_bytes(bytes.fromhex(g["proof"]))
+    gamma, delta = codec.g2_decompress(bytes.fromhex(g["gamma_g2"])), codec.g2_decompress(bytes.fromhex(g["delta_g2"]))
+    first = codec.g1_decompress(bytes.fromhex(g["gamma_ABC_first"]))
+    gt = cref.ints_to_limbs([int(x, 16) for x in g["alpha_g1_beta_g2"]], 6).reshape(-1)
+    none = np.zeros((1, 0, 4), np.uint64)
+    assert vsp.verify_gt_batch(ctx, gt, gamma, delta, first, none, proof[None]).tolist() == [True]
+    swapped = proof.copy()
+    swapped[0:12], swapped[36:48] = proof[36:48], proof[0:12]
+    assert vsp.verify_gt_batch(ctx, gt, gamma, delta, first, none, swapped[None]).tolist() == [False]
+    bad_gt = gt.copy()
+    bad_gt[0] ^= np.uint64(1)
+    assert vsp.verify_gt_batch(ctx, bad_gt, gamma, delta, first, none, proof[None]).tolist() == [False]
+    # e(A, B) e(-first, gamma) e(-C, delta) as a value
+    neg = lambda p: cref.g1_to_limbs([o.G1.to_affine(o.G1.neg(o.G1.from_affine(cref.g1_from_limbs(p.reshape(1, 12))[0])))])[0]
+    g1 = np.stack([proof[:12], neg(first), neg(proof[36:])])
+    g2 = np.stack([proof[12:36], gamma, delta])
+    got, _ = vsp.pairing_products(ctx, g1, g2, pairs=3)
+    assert np.array_equal(got[0], gt)
+
+
+def test_ill_formed_proof_elements_are_rejected(ctx):
+    """proof.is_well_formed() / the decoders' guarantees: an element off the curve, outside the order-r subgroup or with an
+    unreduced coordinate makes the ballot invalid, whatever the pairing of such limbs would give; the oracle agrees"""
+    nc, ni, k = 24, 4, 7
+    cs, arr, vk, _pub, rng = _keys_and_ballots(ctx, nc, ni, 2, k, seed=21)
+    pk = vsp.ProvingKey(ctx, arr)
+    _cs, primary, aux = synthetic_r1cs(nc, ni, seed=21)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    proofs = np.stack([pk.prove(P, A, rng.randrange(o.R), rng.randrange(o.R)) for _ in range(k)])
+    pk.close()
+    prim = np.tile(P, (k, 1, 1))
+    assert vsp.verify_batch(ctx, vk, prim, proofs).all()
+    proofs[1, 6] ^= np.uint64(1)                       # A.y off the curve
+    proofs[2, 12] ^= np.uint64(2)                      # B.x.c0 off the twist
+    pmod = cref.ints_to_limbs([o.P], 6)[0]
+    with np.errstate(over="ignore"):
+        carry, t = 0, proofs[3, 36:42].copy()          # C.x + p: same residue, unreduced limbs
+        for i in range(6):
+            v = int(t[i]) + int(pmod[i]) + carry
+            t[i], carry = np.uint64(v & (2 ** 64 - 1)), v >> 64
+    if carry == 0:
+        proofs[3, 36:42] = t
+    # a curve point outside G1: the cofactor is not 1, so a random x with a square x^3 + 4 almost never lands in the subgroup
+    x = 7
+    while True:
+        y = o.fq_sqrt((x ** 3 + 4) % o.P)
+        if y is not None and not o.G1.in_subgroup(o.G1.from_affine((x, y))):
+            break
+        x += 1
+    proofs[4, 0:12] = cref.g1_to_limbs([(x, y)])[0]
+    # the same on the twist for B
+    x0 = 1
+    while True:
+        yy = o.fq2_sqrt(o._Fq2.add(o._Fq2.mul(o._Fq2.sqr((x0, 0)), (x0, 0)), (4, 4)))
+        if yy is not None and not o.G2.in_subgroup(o.G2.from_affine(((x0, 0), yy))):
+            break
+        x0 += 1
+    proofs[5, 12:36] = cref.g2_to_limbs([((x0, 0), yy)])[0]
+    got = vsp.verify_batch(ctx, vk, prim, proofs)
+    assert got.tolist() == [True, False, False, carry != 0, False, False, True]
+    from test_gpu_keygen import _vk_from_arrays
+    ovk = _vk_from_arrays(vk)
+    J1 = lambda a: o.G1.from_affine(cref.g1_from_limbs(a.reshape(1, 12))[0])
+    J2 = lambda a: o.G2.from_affine(cref.g2_from_limbs(a.reshape(1, 24))[0])
+    for b in (1, 4, 5, 6):
+        pr = (J1(proofs[b, :12]), J2(proofs[b, 12:36]), J1(proofs[b, 36:]))
+        assert o.groth16_verify(ovk, primary, pr) == bool(got[b])

@@ -175,6 +175,35 @@ def test_generate_prove_verify_and_c_prover_agrees():
     assert np.array_equal(got, fx.proof_to_limbs(proof))
 
 
+def test_reference_made_proof_in_data_bin_verifies():
+    """bin/cli/src/data.bin holds the one crypto3-made Groth16 proof of the tree, followed by its verification key
+    (tests/golden/make_golden.py::databin).  It pins, against bytes the reference wrote: the compressed point decoders, the
+    192-byte proof layout, the verification key's field order, the orientation of the verification equation and the value
+    convention of pair_reduced (alpha_g1_beta_g2 is compared coefficient for coefficient, not through a decision)."""
+    g = golden("databin_groth16.json")
+    pr = bytes.fromhex(g["proof"])
+    A, B, C = o.g1_decompress(pr[:48]), o.g2_decompress(pr[48:144]), o.g1_decompress(pr[144:])
+    gamma, delta = o.g2_decompress(bytes.fromhex(g["gamma_g2"])), o.g2_decompress(bytes.fromhex(g["delta_g2"]))
+    first = o.g1_decompress(bytes.fromhex(g["gamma_ABC_first"]))
+    J1, J2 = o.G1.from_affine, o.G2.from_affine
+    for pt in (A, C, first):
+        assert o.G1.on_curve_affine(pt) and o.G1.in_subgroup(J1(pt))
+    for pt in (B, gamma, delta):
+        assert o.G2.on_curve_affine(pt) and o.G2.in_subgroup(J2(pt))
+    # the decoders invert the encoders bit for bit
+    assert o.g1_compress(J1(A)) + o.g2_compress(J2(B)) + o.g1_compress(J1(C)) == pr
+    gt = o.gt_from_coeffs([int(x, 16) for x in g["alpha_g1_beta_g2"]])
+    proof = (J1(A), J2(B), J1(C))
+    assert o.groth16_verify_gt(gt, J2(gamma), J2(delta), J1(first), [], [], proof)
+    assert not o.groth16_verify_gt(gt, J2(gamma), J2(delta), J1(first), [], [], (J1(C), J2(B), J1(A)))
+    # the exact (p^12 - 1) / r power does NOT reproduce the stored element: crypto3's reduced pairing is its cube
+    f = o.F12_ONE
+    for p_, q_ in ((A, B), (o.G1.to_affine(o.G1.neg(J1(first))), gamma), (o.G1.to_affine(o.G1.neg(J1(C))), delta)):
+        f = o.f12mul(f, o.miller_loop(p_, q_))
+    x = o.final_exponentiation_exact(f)
+    assert x != gt and o.f12mul(o.f12mul(x, x), x) == gt
+
+
 def test_step_domain_prover_verifies():
     rng = random.Random(12)
     cs, primary, aux = o.r1cs_example_with_field_input(19, 4, rng)  # m_req = 24 -> step_radix2

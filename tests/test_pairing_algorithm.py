@@ -84,9 +84,10 @@ def _final_exp_x_chain(f):
     t = o.f12mul(o.f12conj(f), o.f12inv(f))
     f1 = o.f12mul(_frob2(t), t)
     a = o.f12pow(f1, e0)
+    a = o.f12mul(o.f12mul(a, a), a)  # f1^((x - 1)^2): crypto3's exponent is 3 x the exact one (oracle/pyref.py)
     b = o.f12mul(powx(a), _frob(a))
     c = o.f12mul(o.f12mul(powx(powx(b)), _frob2(b)), o.f12conj(b))
-    return o.f12mul(c, f1)
+    return o.f12mul(c, o.f12mul(o.f12mul(f1, f1), f1))
 
 
 def test_hard_part_identity_and_frobenius_constants():

@@ -31,7 +31,7 @@ from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADI
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
            "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path",
-           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_encryption_batch", "decrypt", "verify_decryption", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
+           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_gt_batch", "verify_encryption_batch", "decrypt", "verify_decryption", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
 
 FR_MULTIPLICATIVE_GENERATOR = 7
 
@@ -575,6 +575,21 @@ def verify_batch(ctx: Context, vk: dict, primary, proofs) -> np.ndarray:
     x = np.ascontiguousarray(primary, dtype=np.uint64).reshape(k, -1, 4) if k else np.zeros((0, 0, 4), np.uint64)
     ok = np.zeros(k, dtype=np.uint8)
     ctx.check(ctx._lib.vsp_groth16_verify_batch(ctx._h, C.byref(desc), k, _p(x), x.shape[1], _p(pr), _p(ok)))
+    return ok.astype(bool)
+
+
+def verify_gt_batch(ctx: Context, alpha_g1_beta_g2, gamma_g2, delta_g2, gamma_ABC_g1, primary, proofs) -> np.ndarray:
+    """zk::verify with the verification key as the reference stores it (alpha_g1_beta_g2 as a GT value, 72 limbs)."""
+    gt, g2, d2 = _a(alpha_g1_beta_g2).reshape(-1), _a(gamma_g2).reshape(-1, 24), _a(delta_g2).reshape(-1, 24)
+    gabc = _a(gamma_ABC_g1).reshape(-1, 12)
+    if gt.shape[0] != 72:
+        raise ValueError("alpha_g1_beta_g2 must be 72 limbs")
+    pr = _a(proofs, 48)
+    k = pr.shape[0]
+    x = np.ascontiguousarray(primary, dtype=np.uint64).reshape(k, -1, 4) if k else np.zeros((0, 0, 4), np.uint64)
+    ok = np.zeros(k, dtype=np.uint8)
+    ctx.check(ctx._lib.vsp_groth16_verify_gt_batch(ctx._h, _p(gt), _p(g2), _p(d2), gabc.shape[0], _p(gabc), k, _p(x), x.shape[1],
+                                                   _p(pr), _p(ok)))
     return ok.astype(bool)
 
 

@@ -138,6 +138,7 @@ SYMBOLS = [
     ("vsp_g2_generator_mul_batch", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_pairing_products", _int, [_vp, _u64, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_groth16_verify_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), _u64, _vp, _u64, _vp, _vp]),
+    ("vsp_groth16_verify_gt_batch", _int, [_vp, _vp, _vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _vp]),
     ("vsp_saver_verify_encryption_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), C.POINTER(SaverPubkeyDesc), _u64, _vp,
                                                  _vp, _u64, _vp, _vp]),
     ("vsp_saver_decrypt", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp]),
@@ -145,6 +146,9 @@ SYMBOLS = [
     ("vsp_codec_g1_compress", _int, [_vp, _vp]),
     ("vsp_codec_g2_compress", _int, [_vp, _vp]),
     ("vsp_codec_proof_write", _int, [_vp, _vp]),
+    ("vsp_codec_g1_decompress", _int, [_vp, _vp]),
+    ("vsp_codec_g2_decompress", _int, [_vp, _vp]),
+    ("vsp_codec_proof_read", _int, [_vp, _vp]),
     ("vsp_codec_ciphertext_write", _int, [_vp, _u64, _vp]),
     ("vsp_codec_primary_input_write", _int, [_vp, _u64, _vp]),
     ("vsp_codec_primary_input_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), _vp, _u64]),

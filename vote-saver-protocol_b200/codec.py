@@ -46,6 +46,32 @@ def proof_bytes(proof) -> bytes:
     return bytes(out)
 
 
+def g1_decompress(octets: bytes) -> np.ndarray:
+    """48 compressed octets -> 12 canonical affine limbs (all-zero = infinity); ValueError where the reference's decoder fails"""
+    if len(octets) != 48:
+        raise ValueError("a compressed G1 point is 48 bytes")
+    out = np.zeros(12, dtype=np.uint64)
+    _check(_lib.load().vsp_codec_g1_decompress(bytes(octets), out.ctypes.data), "g1_decompress")
+    return out
+
+
+def g2_decompress(octets: bytes) -> np.ndarray:
+    if len(octets) != 96:
+        raise ValueError("a compressed G2 point is 96 bytes")
+    out = np.zeros(24, dtype=np.uint64)
+    _check(_lib.load().vsp_codec_g2_decompress(bytes(octets), out.ctypes.data), "g2_decompress")
+    return out
+
+
+def proof_from_bytes(octets: bytes) -> np.ndarray:
+    """the 192-byte proof.bin body -> g_A | g_B | g_C (48 limbs)"""
+    if len(octets) != 192:
+        raise ValueError("a proof is 192 bytes")
+    out = np.zeros(48, dtype=np.uint64)
+    _check(_lib.load().vsp_codec_proof_read(bytes(octets), out.ctypes.data), "proof_read")
+    return out
+
+
 def ciphertext_bytes(ct) -> bytes:
     c = _u64(ct, 12)
     out = _out(8 + 48 * c.shape[0])

@@ -109,6 +109,240 @@ void fast_read(const uint8_t* in, uint64_t* p, int fq_count) {
     for (int i = 0; i < fq_count; ++i) get_be(in + FQ_BYTES * i, p + 6 * i, FQ_BYTES);
 }
 
+// ---- host Fq / Fq2 for the decoders: y from x (processing/curve_element.hpp:176-395 take the square root of x^3 + b
+// and pick the root whose sign matches the S bit).  Plain 6 x 64-bit limbs, schoolbook product + shift-subtract-free
+// Montgomery reduction; decoding is a few points per ballot, nowhere near the hot path.
+typedef unsigned __int128 u128;
+const uint64_t P64[6] = {0xb9feffffffffaaabull, 0x1eabfffeb153ffffull, 0x6730d2a0f6b0f624ull,
+                         0x64774b84f38512bfull, 0x4b1ba7b6434bacd7ull, 0x1a0111ea397fe69aull};
+const uint64_t P_INV64 = 0x89f3fffcfffcfffdull;  // -p^-1 mod 2^64
+struct HFq {
+    uint64_t l[6];
+};
+bool hfq_geq_p(const uint64_t* x) {
+    for (int i = 5; i >= 0; --i) {
+        if (x[i] > P64[i]) return true;
+        if (x[i] < P64[i]) return false;
+    }
+    return true;
+}
+bool hfq_is_zero(const HFq& a) { return is_zero(a.l, 6); }
+bool hfq_eq(const HFq& a, const HFq& b) { return memcmp(a.l, b.l, 48) == 0; }
+HFq hfq_add(const HFq& a, const HFq& b) {
+    HFq r;
+    u128 c = 0;
+    for (int i = 0; i < 6; ++i) {
+        c += (u128)a.l[i] + b.l[i];
+        r.l[i] = (uint64_t)c;
+        c >>= 64;
+    }
+    if (hfq_geq_p(r.l)) {
+        u128 br = 0;
+        for (int i = 0; i < 6; ++i) {
+            const u128 d = (u128)r.l[i] - P64[i] - (uint64_t)br;
+            r.l[i] = (uint64_t)d;
+            br = (d >> 64) & 1;
+        }
+    }
+    return r;
+}
+HFq hfq_neg(const HFq& a) {
+    if (hfq_is_zero(a)) return a;
+    HFq r;
+    u128 br = 0;
+    for (int i = 0; i < 6; ++i) {
+        const u128 d = (u128)P64[i] - a.l[i] - (uint64_t)br;
+        r.l[i] = (uint64_t)d;
+        br = (d >> 64) & 1;
+    }
+    return r;
+}
+HFq hfq_sub(const HFq& a, const HFq& b) { return hfq_add(a, hfq_neg(b)); }
+// Montgomery product a b / 2^384 mod p (CIOS)
+HFq hfq_mmul(const HFq& a, const HFq& b) {
+    uint64_t t[8] = {0};
+    for (int i = 0; i < 6; ++i) {
+        u128 c = 0;
+        for (int j = 0; j < 6; ++j) {
+            c += (u128)a.l[j] * b.l[i] + t[j];
+            t[j] = (uint64_t)c;
+            c >>= 64;
+        }
+        c += t[6];
+        t[6] = (uint64_t)c;
+        t[7] = (uint64_t)(c >> 64);
+        const uint64_t m = t[0] * P_INV64;
+        c = (u128)m * P64[0] + t[0];
+        c >>= 64;
+        for (int j = 1; j < 6; ++j) {
+            c += (u128)m * P64[j] + t[j];
+            t[j - 1] = (uint64_t)c;
+            c >>= 64;
+        }
+        c += t[6];
+        t[5] = (uint64_t)c;
+        t[6] = t[7] + (uint64_t)(c >> 64);
+    }
+    HFq r;
+    memcpy(r.l, t, 48);
+    if (t[6] || hfq_geq_p(r.l)) {
+        u128 br = 0;
+        for (int i = 0; i < 6; ++i) {
+            const u128 d = (u128)r.l[i] - P64[i] - (uint64_t)br;
+            r.l[i] = (uint64_t)d;
+            br = (d >> 64) & 1;
+        }
+    }
+    return r;
+}
+// R^2 mod p by doubling 1 -> 2^768 mod p
+HFq hfq_r2() {
+    static HFq r2;
+    static bool have = false;
+    if (!have) {
+        HFq x = {{1, 0, 0, 0, 0, 0}};
+        for (int i = 0; i < 768; ++i) x = hfq_add(x, x);
+        r2 = x;
+        have = true;
+    }
+    return r2;
+}
+HFq hfq_to_mont(const HFq& a) { return hfq_mmul(a, hfq_r2()); }
+HFq hfq_from_mont(const HFq& a) {
+    const HFq one = {{1, 0, 0, 0, 0, 0}};
+    return hfq_mmul(a, one);
+}
+// a^e (Montgomery form in and out), e little-endian limbs
+HFq hfq_pow(const HFq& a, const uint64_t* e, int limbs) {
+    HFq acc = hfq_to_mont(HFq{{1, 0, 0, 0, 0, 0}});
+    for (int bit = 64 * limbs - 1; bit >= 0; --bit) {
+        acc = hfq_mmul(acc, acc);
+        if ((e[bit / 64] >> (bit % 64)) & 1) acc = hfq_mmul(acc, a);
+    }
+    return acc;
+}
+// square root (p = 3 mod 4: a^((p + 1) / 4)); false if a is not a square
+bool hfq_sqrt(const HFq& a, HFq* out) {
+    uint64_t e[6];
+    u128 c = 1;
+    for (int i = 0; i < 6; ++i) {  // p + 1
+        c += P64[i];
+        e[i] = (uint64_t)c;
+        c >>= 64;
+    }
+    for (int i = 0; i < 6; ++i) e[i] = (e[i] >> 2) | (i < 5 ? e[i + 1] << 62 : 0);
+    const HFq r = hfq_pow(a, e, 6);
+    if (!hfq_eq(hfq_mmul(r, r), a)) return false;
+    *out = r;
+    return true;
+}
+HFq hfq_inv(const HFq& a) {
+    uint64_t e[6];
+    memcpy(e, P64, 48);
+    e[0] -= 2;  // p - 2 (no borrow: the low limb ends in ...aaab)
+    return hfq_pow(a, e, 6);
+}
+struct HFq2 {
+    HFq c0, c1;
+};
+HFq2 hfq2_mul(const HFq2& a, const HFq2& b) {
+    const HFq t0 = hfq_mmul(a.c0, b.c0), t1 = hfq_mmul(a.c1, b.c1);
+    return HFq2{hfq_sub(t0, t1), hfq_add(hfq_mmul(a.c0, b.c1), hfq_mmul(a.c1, b.c0))};
+}
+// a square root in Fq2 = Fq[u] / (u^2 + 1) by the norm: x0^2 = (a0 +- sqrt(a0^2 + a1^2)) / 2, x1 = a1 / (2 x0)
+bool hfq2_sqrt(const HFq2& a, HFq2* out) {
+    const HFq zero = {{0, 0, 0, 0, 0, 0}};
+    if (hfq_is_zero(a.c1)) {
+        HFq r;
+        if (hfq_sqrt(a.c0, &r)) {
+            *out = HFq2{r, zero};
+            return true;
+        }
+        if (hfq_sqrt(hfq_neg(a.c0), &r)) {
+            *out = HFq2{zero, r};
+            return true;
+        }
+        return false;
+    }
+    HFq n;
+    if (!hfq_sqrt(hfq_add(hfq_mmul(a.c0, a.c0), hfq_mmul(a.c1, a.c1)), &n)) return false;
+    const HFq two = hfq_to_mont(HFq{{2, 0, 0, 0, 0, 0}}), inv2 = hfq_inv(two);
+    for (int sgn = 0; sgn < 2; ++sgn) {
+        const HFq nn = sgn ? hfq_neg(n) : n;
+        HFq x0;
+        if (!hfq_sqrt(hfq_mmul(hfq_add(a.c0, nn), inv2), &x0) || hfq_is_zero(x0)) continue;
+        const HFq x1 = hfq_mmul(a.c1, hfq_inv(hfq_add(x0, x0)));
+        const HFq2 r = {x0, x1}, rr = hfq2_mul(r, r);
+        if (hfq_eq(rr.c0, a.c0) && hfq_eq(rr.c1, a.c1)) {
+            *out = r;
+            return true;
+        }
+    }
+    return false;
+}
+
+// compressed octets -> canonical affine limbs.  VSP_E_INVALID where the reference's decoder fails: C bit clear, a
+// non-canonical infinity, x >= p, x not on the curve.
+int g1_decompress(const uint8_t* in, uint64_t* p) {
+    if (!(in[0] & 0x80)) return VSP_E_INVALID;
+    if (in[0] & 0x40) {
+        if (in[0] & 0x3f) return VSP_E_INVALID;
+        for (size_t i = 1; i < FQ_BYTES; ++i)
+            if (in[i]) return VSP_E_INVALID;
+        memset(p, 0, 96);
+        return VSP_OK;
+    }
+    uint8_t xb[FQ_BYTES];
+    memcpy(xb, in, FQ_BYTES);
+    xb[0] &= 0x1f;
+    HFq x;
+    get_be(xb, x.l, FQ_BYTES);
+    if (hfq_geq_p(x.l)) return VSP_E_INVALID;
+    const HFq xm = hfq_to_mont(x), b = hfq_to_mont(HFq{{4, 0, 0, 0, 0, 0}});
+    HFq ym;
+    if (!hfq_sqrt(hfq_add(hfq_mmul(hfq_mmul(xm, xm), xm), b), &ym)) return VSP_E_INVALID;
+    HFq y = hfq_from_mont(ym);
+    if (fq_is_high(y.l) != bool(in[0] & 0x20)) y = hfq_neg(y);
+    memcpy(p, x.l, 48);
+    memcpy(p + 6, y.l, 48);
+    return VSP_OK;
+}
+int g2_decompress(const uint8_t* in, uint64_t* p) {
+    if (!(in[0] & 0x80)) return VSP_E_INVALID;
+    if (in[0] & 0x40) {
+        if (in[0] & 0x3f) return VSP_E_INVALID;
+        for (size_t i = 1; i < 2 * FQ_BYTES; ++i)
+            if (in[i]) return VSP_E_INVALID;
+        memset(p, 0, 192);
+        return VSP_OK;
+    }
+    uint8_t xb[FQ_BYTES];
+    memcpy(xb, in, FQ_BYTES);
+    xb[0] &= 0x1f;
+    HFq x1, x0;
+    get_be(xb, x1.l, FQ_BYTES);
+    get_be(in + FQ_BYTES, x0.l, FQ_BYTES);
+    if (hfq_geq_p(x0.l) || hfq_geq_p(x1.l)) return VSP_E_INVALID;
+    const HFq2 xm = {hfq_to_mont(x0), hfq_to_mont(x1)};
+    const HFq four = hfq_to_mont(HFq{{4, 0, 0, 0, 0, 0}});
+    HFq2 rhs = hfq2_mul(hfq2_mul(xm, xm), xm);
+    rhs.c0 = hfq_add(rhs.c0, four);
+    rhs.c1 = hfq_add(rhs.c1, four);
+    HFq2 ym;
+    if (!hfq2_sqrt(rhs, &ym)) return VSP_E_INVALID;
+    HFq y0 = hfq_from_mont(ym.c0), y1 = hfq_from_mont(ym.c1);
+    const bool high = hfq_is_zero(y1) ? fq_is_high(y0.l) : fq_is_high(y1.l);
+    if (high != bool(in[0] & 0x20)) {
+        y0 = hfq_neg(y0);
+        y1 = hfq_neg(y1);
+    }
+    memcpy(p, x0.l, 48);
+    memcpy(p + 6, x1.l, 48);
+    memcpy(p + 12, y0.l, 48);
+    memcpy(p + 18, y1.l, 48);
+    return VSP_OK;
+}
+
 struct Reader {
     const uint8_t* p;
     size_t left;
@@ -142,6 +376,24 @@ int vsp_codec_g2_compress(const uint64_t* point, uint8_t* out96) {
     if (!point || !out96) return VSP_E_INVALID;
     g2_compress(point, out96);
     return VSP_OK;
+}
+// compressed octets -> canonical affine limbs (processing/curve_element.hpp:176-395); VSP_E_INVALID for a malformed
+// encoding or an x with no point on the curve.  Subgroup membership is the verifier's check, as in the reference.
+int vsp_codec_g1_decompress(const uint8_t* in48, uint64_t* point) {
+    if (!in48 || !point) return VSP_E_INVALID;
+    return g1_decompress(in48, point);
+}
+int vsp_codec_g2_decompress(const uint8_t* in96, uint64_t* point) {
+    if (!in96 || !point) return VSP_E_INVALID;
+    return g2_decompress(in96, point);
+}
+// 192 bytes -> proof (g_A | g_B | g_C as 48 limbs)   (proof.hpp:86-102)
+int vsp_codec_proof_read(const uint8_t* in192, uint64_t* proof) {
+    if (!in192 || !proof) return VSP_E_INVALID;
+    int rc = g1_decompress(in192, proof);
+    if (rc == VSP_OK) rc = g2_decompress(in192 + 48, proof + 12);
+    if (rc == VSP_OK) rc = g1_decompress(in192 + 144, proof + 36);
+    return rc;
 }
 // proof (g_A | g_B | g_C as 48 limbs) -> 192 bytes
 int vsp_codec_proof_write(const uint64_t* proof, uint8_t* out192) {

@@ -19,7 +19,8 @@
 // |x| = 0xd201000000010000); after that a pairing costs no inversion, and a product of pairings shares the 63 squarings
 // (one thread per product).  In the verifiers all but one G2 argument per ballot (the proof's B) are key material whose
 // tables are built once per call.  Final exponentiation: easy part by conjugation / inversion / Frobenius, hard part by the
-// exact x-chain (p^4-p^2+1)/r = ((x-1)^2/3)(x+p)(x^2+p^2-1) + 1 (see k_final_exp).
+// x-chain 3 (p^4-p^2+1)/r = (x-1)^2 (x+p)(x^2+p^2-1) + 3 (see k_final_exp): crypto3's reduced pairing is the cube of the
+// textbook one, pinned on the reference's bin/cli/src/data.bin (tests/golden/databin_groth16.json).
 #include "common.cuh"
 #include "ec.cuh"
 #include "host_fr.h"
@@ -206,10 +207,11 @@ __global__ void __launch_bounds__(64) k_multi_miller(const uint32_t* __restrict_
 }
 
 // ---- final exponentiation ------------------------------------------------------------------------------------
-// f^((p^12-1)/r) = easy * hard:  t = conj(f) / f = f^(p^6-1);  f1 = frob^2(t) t = t^(p^2+1);
-// hard exponent (p^4 - p^2 + 1)/r = e0 (x + p)(x^2 + p^2 - 1) + 1 with e0 = (x-1)^2/3 (an exact identity, checked
+// f^(3 (p^12-1)/r) = easy * hard:  t = conj(f) / f = f^(p^6-1);  f1 = frob^2(t) t = t^(p^2+1);
+// hard exponent 3 (p^4 - p^2 + 1)/r = 3 e0 (x + p)(x^2 + p^2 - 1) + 3 with e0 = (x-1)^2/3 (an exact identity, checked
 // when tools/gen_constants.py writes pairing_constants.cuh), so the result is the same field element the plain
-// 4,314-bit power gives:  a = f1^e0;  b = a^x frob(a);  c = (b^x)^x frob^2(b) conj(b);  result = c f1.
+// power gives:  a = (f1^e0)^3;  b = a^x frob(a);  c = (b^x)^x frob^2(b) conj(b);  result = c f1^3.
+// The factor 3 is crypto3's convention for pair_reduced (evidence: tests/golden/databin_groth16.json).
 // After the easy part the value is in the cyclotomic subgroup, where inversion is conjugation; x < 0.
 VSP_DEV Fq fq_const(const uint32_t* p) {
     Fq r;
@@ -268,6 +270,11 @@ __global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f
         f12_sqr(a);
         if ((VSP_PAIRING_E0[bit >> 5] >> (bit & 31)) & 1u) f12_mul(a, f1);
     }
+    {
+        Fq12 a2 = a;  // crypto3's hard part is 3 (p^4 - p^2 + 1) / r: a = f1^((x - 1)^2) = (f1^e0)^3
+        f12_sqr(a2);
+        f12_mul(a, a2);
+    }
     Fq12 b = f12_pow_x(a);
     f12_frob(a);
     f12_mul(b, a);  // b = a^(x + p)
@@ -280,7 +287,12 @@ __global__ void __launch_bounds__(64) k_final_exp(const uint32_t* __restrict__ f
         f12_conj(b);
         f12_mul(acc, b);  // acc = b^(x^2 + p^2 - 1)
     }
-    f12_mul(acc, f1);
+    {
+        Fq12 f3 = f1;
+        f12_sqr(f3);
+        f12_mul(f3, f1);
+        f12_mul(acc, f3);  // ... + 3
+    }
     if (is_one) is_one[c] = f12_is_one(acc) ? 1 : 0;
     if (gt_out) {
         const E2* co[6] = {&acc.c0.c0, &acc.c0.c1, &acc.c0.c2, &acc.c1.c0, &acc.c1.c1, &acc.c1.c2};
@@ -388,10 +400,88 @@ __global__ void __launch_bounds__(64) k_verify_prepare(VerifyArgs a) {
     i2[3] = fixed_tail + 2;
 }
 
-__global__ void k_and_flags(const uint8_t* a, const uint8_t* b, unsigned n, uint8_t* out) {
+// ---- well-formedness of the untrusted inputs (proof elements, cipher text) ------------------------------------
+// The reference rejects ill-formed proofs before pairing (proof.is_well_formed()) and its compressed decoders only ever
+// yield curve points; this ABI takes raw affine limbs, so the verifier checks them itself: every coordinate reduced
+// mod p, the point on y^2 = x^3 + 4 (G1) / y^2 = x^3 + 4 (1 + u) (the twist), and in the order-r subgroup ([r] P = O by
+// double-and-add over the bits of r: both curves have cofactors, so an on-curve point need not be in G1 / G2).  The
+// point at infinity (all-zero) is a group element and passes.  One thread per point.
+VSP_DEV bool limbs_below_p(const uint64_t* x) {
+    for (int i = 5; i >= 0; --i) {
+        const uint64_t m = (uint64_t(VSP_FQ_MOD(2 * i + 1)) << 32) | VSP_FQ_MOD(2 * i);
+        if (x[i] < m) return true;
+        if (x[i] > m) return false;
+    }
+    return false;
+}
+template <class F>
+VSP_DEV typename F::T curve_b_mont();
+template <>
+VSP_DEV Fq curve_b_mont<FqOps>() {
+    Fq four = Fq::zero();
+    four.l[0] = 4;
+    return fp_to_mont(four);
+}
+template <>
+VSP_DEV Fq2 curve_b_mont<Fq2Ops>() {
+    const Fq f = curve_b_mont<FqOps>();
+    return Fq2{f, f};
+}
+// pts + i * stride (u64 limbs) holds a canonical affine point; ok[i] = 1 iff well formed
+template <class F>
+__global__ void __launch_bounds__(64) k_points_well_formed(const uint64_t* __restrict__ pts, uint64_t stride, unsigned n,
+                                                           uint8_t* __restrict__ ok) {
     const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = (a[i] && (!b || b[i])) ? 1 : 0;
+    const uint64_t* q = pts + uint64_t(i) * stride;
+    constexpr int NFQ = Affine<F>::BYTES / 48;
+    bool reduced = true, zero = true;
+    for (int k = 0; k < NFQ; ++k) reduced = reduced && limbs_below_p(q + 6 * k);
+    for (int k = 0; k < 6 * NFQ; ++k) zero = zero && q[k] == 0;
+    if (zero || !reduced) {
+        ok[i] = zero ? 1 : 0;
+        return;
+    }
+    Affine<F> a = Affine<F>::load(q);
+    a.x = F::to_mont(a.x);
+    a.y = F::to_mont(a.y);
+    const typename F::T rhs = F::add(F::mul(F::sqr(a.x), a.x), curve_b_mont<F>());
+    if (!F::eq(F::sqr(a.y), rhs)) {
+        ok[i] = 0;
+        return;
+    }
+    XYZZ<F> acc = XYZZ<F>::inf();
+#pragma unroll 1
+    for (int bit = 254; bit >= 0; --bit) {
+        acc = ec_dbl<F>(acc);
+        uint32_t limb = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) limb = ((bit >> 5) == k) ? VSP_FR_MOD(k) : limb;
+        if ((limb >> (bit & 31)) & 1u) ec_madd<F>(acc, a);
+    }
+    ok[i] = acc.is_inf() ? 1 : 0;
+}
+
+// out[b] = a[b] && b_[b] (if given) && every well-formedness flag of ballot b: wf_ab (A, C interleaved 2 per ballot),
+// wf_b (one per ballot), wf_ct (per_ct per ballot, optional)
+__global__ void k_and_flags(const uint8_t* a, const uint8_t* b, unsigned n, const uint8_t* wf_ac, const uint8_t* wf_b,
+                            const uint8_t* wf_ct, unsigned per_ct, uint8_t* out) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bool ok = a[i] && (!b || b[i]);
+    if (wf_ac) ok = ok && wf_ac[2 * i] && wf_ac[2 * i + 1];
+    if (wf_b) ok = ok && wf_b[i];
+    if (wf_ct)
+        for (unsigned j = 0; j < per_ct; ++j) ok = ok && wf_ct[uint64_t(i) * per_ct + j];
+    out[i] = ok ? 1 : 0;
+}
+// one[c] = (gt[c] == want) over 72 limbs (the verification key's alpha_g1_beta_g2 form)
+__global__ void k_gt_equal(const uint64_t* __restrict__ gt, const uint64_t* __restrict__ want, unsigned n, uint8_t* one) {
+    const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    uint64_t d = 0;
+    for (int k = 0; k < 72; ++k) d |= gt[uint64_t(c) * 72 + k] ^ want[k];
+    one[c] = d == 0 ? 1 : 0;
 }
 
 const uint64_t G2_GENERATOR[24] = {
@@ -452,8 +542,11 @@ int run_products(vsp_ctx* ctx, cudaStream_t s, const uint32_t* d_pts, const uint
     return VSP_OK;
 }
 
+// gt_alpha_beta (optional, 72 limbs): the key carries alpha_g1_beta_g2 = pair_reduced(alpha, beta) instead of alpha and
+// beta, as the reference's verification key does (verification_key.hpp:69); vk->alpha_g1 / beta_g2 are then unused.
 int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* t_g2, uint64_t msg_size, uint64_t k,
-                const uint64_t* cts, const uint64_t* xs, uint64_t n_x, const uint64_t* proofs, uint8_t* ok) {
+                const uint64_t* cts, const uint64_t* xs, uint64_t n_x, const uint64_t* proofs, uint8_t* ok,
+                const uint64_t* gt_alpha_beta = nullptr) {
     if (k == 0) return VSP_OK;
     if (k > (1u << 20) || msg_size > 1024 || n_x > (1u << 20)) return set_error(ctx, VSP_E_INVALID, "verify: batch too large");
     const bool has_ct = cts != nullptr;
@@ -475,7 +568,7 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
         memcpy(&hq[pos], G2_GENERATOR, 192);
         pos += 24;
     }
-    memcpy(&hq[pos], vk->beta_g2, 192);
+    memcpy(&hq[pos], gt_alpha_beta ? vk->gamma_g2 : vk->beta_g2, 192);  // GT form: the pair's G1 side is infinity
     memcpy(&hq[pos + 24], vk->gamma_g2, 192);
     memcpy(&hq[pos + 48], vk->delta_g2, 192);
     DevBuf d_q, d_tab, d_valid, d_ct, d_pr, d_x, d_gabc, d_alpha, d_p2, d_i2, d_one;
@@ -495,7 +588,10 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_pr.p, proofs, size_t(K) * 384, cudaMemcpyHostToDevice, s));
     if (n_x) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_x.p, xs, size_t(K) * n_x * 32, cudaMemcpyHostToDevice, s));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_gabc.p, vk->gamma_ABC_g1, size_t(vk->gamma_ABC_count) * 96, cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_alpha.p, vk->alpha_g1, 96, cudaMemcpyHostToDevice, s));
+    if (gt_alpha_beta)
+        VSP_CUDA_CHECK(ctx, cudaMemsetAsync(d_alpha.p, 0, 96, s));
+    else
+        VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_alpha.p, vk->alpha_g1, 96, cudaMemcpyHostToDevice, s));
     if (has_ct) {
         VSP_TRY(d_ct.alloc(ctx, size_t(K) * (n + 2) * 96, s));
         VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_ct.p, cts, size_t(K) * (n + 2) * 96, cudaMemcpyHostToDevice, s));
@@ -524,9 +620,50 @@ int verify_impl(vsp_ctx* ctx, const vsp_verification_key_t* vk, const uint64_t* 
     for (unsigned b = 0; b < K; ++b) plan.add_check(b * 4, 4);
     if (has_ct)
         for (unsigned b = 0; b < K; ++b) plan.add_check(K * 4 + b * (n + 2), n + 2);
+    DevBuf d_gt, d_want, d_wf;
+    if (gt_alpha_beta) {
+        // e(-A, B) e(acc, gamma) e(C, delta) = 1 / alpha_g1_beta_g2, and inversion in the cyclotomic subgroup is conjugation
+        uint64_t want[72];
+        memcpy(want, gt_alpha_beta, 576);
+        for (int q = 36; q < 72; q += 6) {  // the c1 half, one Fq at a time: x -> p - x (0 stays 0)
+            uint64_t any = 0;
+            for (int i = 0; i < 6; ++i) any |= want[q + i];
+            if (!any) continue;
+            unsigned __int128 borrow = 0;
+            for (int i = 0; i < 6; ++i) {
+                const unsigned __int128 d = (unsigned __int128)FQ_MOD64[i] - want[q + i] - (uint64_t)borrow;
+                want[q + i] = (uint64_t)d;
+                borrow = (d >> 64) & 1;
+            }
+        }
+        VSP_TRY(d_gt.alloc(ctx, (size_t(K) * (has_ct ? 2 : 1)) * 576, s));
+        VSP_TRY(d_want.alloc(ctx, 576, s));
+        VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_want.p, want, 576, cudaMemcpyHostToDevice, s));
+        VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));  // `want` is a stack buffer
+    }
     VSP_TRY(run_products(ctx, s, d_p2.as<uint32_t>(), d_i2.as<uint32_t>(), plan, d_tab.as<uint32_t>(), d_valid.as<uint8_t>(),
-                         nullptr, one));
-    VSP_LAUNCH_K(ctx, KC_OTHER, k_and_flags, (K + 127) / 128, 128, 0, s, one, has_ct ? one + K : nullptr, K, one + 2 * K);
+                         gt_alpha_beta ? d_gt.as<uint64_t>() : nullptr, one));
+    if (gt_alpha_beta)
+        VSP_LAUNCH_K(ctx, KC_OTHER, k_gt_equal, (K + 127) / 128, 128, 0, s, d_gt.as<uint64_t>(), d_want.as<uint64_t>(), K, one);
+    // well-formedness of what the prover sent: A, C (2 K), B (K), the cipher text (K (n + 2))
+    const unsigned per_ct = has_ct ? n + 2 : 0;
+    VSP_TRY(d_wf.alloc(ctx, size_t(K) * (3 + per_ct), s));
+    uint8_t *wf_ac = d_wf.as<uint8_t>(), *wf_b = wf_ac + 2 * size_t(K), *wf_ct = wf_b + K;
+    // A and C sit 36 limbs apart inside a proof and proofs 48 apart: one launch with stride 36 over 2 K "points" would
+    // misplace every second one, so A and C take a launch each into interleaved flags via a 2-element stride trick
+    DevBuf d_ac;
+    VSP_TRY(d_ac.alloc(ctx, size_t(K) * 2 * 96, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d_ac.p, 192, d_pr.as<char>(), 384, 96, K, cudaMemcpyDeviceToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpy2DAsync(d_ac.as<char>() + 96, 192, d_pr.as<char>() + 288, 384, 96, K, cudaMemcpyDeviceToDevice, s));
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_points_well_formed<FqOps>, (2 * K + 63) / 64, 64, 0, s, d_ac.as<uint64_t>(), uint64_t(12), 2 * K,
+                 wf_ac);
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_points_well_formed<Fq2Ops>, (K + 63) / 64, 64, 0, s, d_pr.as<uint64_t>() + 12, uint64_t(48), K,
+                 wf_b);
+    if (has_ct)
+        VSP_LAUNCH_K(ctx, KC_OTHER, k_points_well_formed<FqOps>, (K * per_ct + 63) / 64, 64, 0, s, d_ct.as<uint64_t>(),
+                     uint64_t(12), K * per_ct, wf_ct);
+    VSP_LAUNCH_K(ctx, KC_OTHER, k_and_flags, (K + 127) / 128, 128, 0, s, one, has_ct ? one + K : nullptr, K, wf_ac, wf_b,
+                 has_ct ? wf_ct : nullptr, per_ct, one + 2 * K);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(ok, one + 2 * K, K, cudaMemcpyDeviceToHost, s));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
@@ -585,6 +722,27 @@ extern "C" int vsp_groth16_verify_batch(vsp_ctx* ctx, const vsp_verification_key
     cudaSetDevice(ctx->device);
     try {
         return verify_impl(ctx, vk, nullptr, 0, k, nullptr, primary, n_primary, proofs, ok_out);
+    } catch (const std::bad_alloc&) {
+        return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
+    }
+}
+
+extern "C" int vsp_groth16_verify_gt_batch(vsp_ctx* ctx, const uint64_t* alpha_g1_beta_g2, const uint64_t* gamma_g2,
+                                           const uint64_t* delta_g2, uint64_t gamma_ABC_count, const uint64_t* gamma_ABC_g1,
+                                           uint64_t k, const uint64_t* primary, uint64_t n_primary, const uint64_t* proofs,
+                                           uint8_t* ok_out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (!alpha_g1_beta_g2 || !gamma_g2 || !delta_g2 || !gamma_ABC_g1 || (k && (!proofs || !ok_out)) || (k && n_primary && !primary))
+        return set_error(ctx, VSP_E_INVALID, "vsp_groth16_verify_gt_batch: null argument");
+    cudaSetDevice(ctx->device);
+    vsp_verification_key_t vk;
+    memset(&vk, 0, sizeof(vk));
+    vk.gamma_g2 = gamma_g2;
+    vk.delta_g2 = delta_g2;
+    vk.gamma_ABC_count = gamma_ABC_count;
+    vk.gamma_ABC_g1 = gamma_ABC_g1;
+    try {
+        return verify_impl(ctx, &vk, nullptr, 0, k, nullptr, primary, n_primary, proofs, ok_out, alpha_g1_beta_g2);
     } catch (const std::bad_alloc&) {
         return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
     }
