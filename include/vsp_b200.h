@@ -73,6 +73,14 @@ typedef struct vsp_saver_pub vsp_saver_pub;
 VSP_API int vsp_ctx_create(int device, void *cuda_stream, vsp_ctx **out);
 VSP_API void vsp_ctx_destroy(vsp_ctx *ctx);
 VSP_API const char *vsp_last_error(const vsp_ctx *ctx);
+/* text of the last non-fatal degradation on this context ("" if none): today only "a window table did not fit in
+ * device memory, multiexps over these bases run table-less" (same results, slower for small queries) */
+VSP_API const char *vsp_last_warning(const vsp_ctx *ctx);
+/* ballots per chunk of the batched entry points (vsp_prove_batch*, vsp_saver_encrypt_batch*): 0 restores the default
+ * (environment VSP_BATCH_CHUNK, else 64).  The library further clamps it by the circuit's domain size m to
+ * max(1, 2^23 / m), so a batch of any size over any circuit runs in bounded scratch; inside a chunk a multiexp whose
+ * ballots x points x windows would pass 2^32 keys is itself run in sub-batches.  Results do not depend on it. */
+VSP_API int vsp_ctx_set_batch_chunk(vsp_ctx *ctx, int ballots);
 VSP_API int vsp_ctx_synchronize(vsp_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 VSP_API uint64_t vsp_ctx_launch_count(const vsp_ctx *ctx);
@@ -106,10 +114,17 @@ VSP_API int vsp_g1_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases,
 VSP_API void vsp_g1_bases_destroy(vsp_g1_bases *b);
 VSP_API int vsp_g2_bases_create(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, vsp_g2_bases **out);
 VSP_API void vsp_g2_bases_destroy(vsp_g2_bases *b);
+/* the same with the choice of building the window table (table = 0: the points only, multiexps over the handle take the
+ * one-shot path with the bases already resident — what algebra::multiexp costs without the upload) */
+VSP_API int vsp_g1_bases_create_ex(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, int table, vsp_g1_bases **out);
+VSP_API int vsp_g2_bases_create_ex(vsp_ctx *ctx, uint64_t n, const uint64_t *bases, int table, vsp_g2_bases **out);
 /* synthetic bases for the measurement sweeps, built on the device:
  * bases[i] = k_i * G1_generator, k_i = splitmix64(seed + i) | 1.  vsp_g1_bases_read copies a range back as canonical
  * affine points so small cases can be checked against the oracle. */
 VSP_API int vsp_g1_bases_generate(vsp_ctx *ctx, uint64_t n, uint64_t seed, vsp_g1_bases **out);
+/* the same with the choice of building the window table (table = 0: points only; multiexps over the handle then take the
+ * one-shot path of vsp_g1_msm with the bases already resident) */
+VSP_API int vsp_g1_bases_generate_ex(vsp_ctx *ctx, uint64_t n, uint64_t seed, int table, vsp_g1_bases **out);
 VSP_API int vsp_g1_bases_read(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t first, uint64_t count, uint64_t *out);
 /* the same over G2 (k_i * G2_generator), written straight to a host array of n canonical affine points */
 VSP_API int vsp_g2_points_generate(vsp_ctx *ctx, uint64_t n, uint64_t seed, uint64_t *out);
@@ -120,6 +135,8 @@ VSP_API int vsp_g2_msm_bases(vsp_ctx *ctx, const vsp_g2_bases *b, uint64_t n_sca
                      int scalars_on_device, uint64_t *out);
 /* same, result left on the device as a canonical affine point (12 / 24 limbs) — no host synchronisation */
 VSP_API int vsp_g1_msm_bases_dev(vsp_ctx *ctx, const vsp_g1_bases *b, uint64_t n_scalars, const uint64_t *d_scalars,
+                         uint64_t *d_out);
+VSP_API int vsp_g2_msm_bases_dev(vsp_ctx *ctx, const vsp_g2_bases *b, uint64_t n_scalars, const uint64_t *d_scalars,
                          uint64_t *d_out);
 /* sum of k affine points (the join step of a point-range sharded MSM after the all-gather) */
 VSP_API int vsp_g1_sum(vsp_ctx *ctx, uint64_t k, const uint64_t *points, uint64_t *out);
@@ -202,6 +219,16 @@ VSP_API int vsp_prove_partial(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *pr
 VSP_API int vsp_prove_assemble(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *sums, const uint64_t r[4],
                                const uint64_t s[4], const uint64_t *r_saver, const uint64_t *gamma_inverse_sum_s_g1,
                                uint64_t *out_proof);
+/* Device-resident forms of the two calls above, for one process per GPU under torch.distributed / NCCL:
+ * vsp_prove_partial_dev leaves this rank's five shares as 144 limbs of raw Montgomery XYZZ at d_partials
+ * (evA | evB1 | evH | evL: 24 limbs each; evB2: 48), the ranks exchange them with ONE all_gather straight out of and into
+ * device memory, and vsp_prove_assemble_dev sums the world x 144 gathered limbs on the device and leaves the proof
+ * (48 limbs) at d_proof.  Both are stream-ordered on the context's stream and never block the host; d_assignment is
+ * (1 || primary || auxiliary) canonical Fr. */
+VSP_API int vsp_prove_partial_dev(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *d_assignment, uint64_t *d_partials);
+VSP_API int vsp_prove_assemble_dev(vsp_ctx *ctx, const vsp_pk *pk, uint64_t world, const uint64_t *d_gathered,
+                                   const uint64_t r[4], const uint64_t s[4], const uint64_t *r_saver,
+                                   const uint64_t *gamma_inverse_sum_s_g1, uint64_t *d_proof);
 
 /* SAVER: ciphertext (msg_size + 2 G1) and the encrypted_input proof in one call */
 VSP_API int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,
@@ -367,6 +394,9 @@ VSP_API int vsp_codec_fast_pk_read(const uint8_t *blob, size_t len, vsp_proving_
 VSP_API int vsp_codec_fast_pk_write(const vsp_proving_key_t *desc, uint8_t *out, size_t capacity, size_t *written);
 
 /* ---- measurement helpers ---------------------------------------------------------------------- */
+/* 32x32->64 multiply-adds the G1 bucket-accumulation kernel of this build issues per bucket addition (the reference
+ * algorithm's mixed Jacobian addition is 11 x 300 = 3,300): lets a roofline in reference units be read as pipe use */
+VSP_API int vsp_accumulate_mads_per_add(vsp_ctx *ctx, double *out);
 /* sustained 32-bit multiply-add issue rate: runs a dependent-free IMAD.WIDE carry-chain kernel on all SMs for
  * `iters` rounds and returns multiply-adds per second (the P_int roofline denominator). */
 VSP_API int vsp_measure_imad_rate(vsp_ctx *ctx, uint64_t iters, double *mads_per_second);

@@ -214,3 +214,77 @@ def test_tuning_switches_do_not_change_results(vsp, ctx, monkeypatch):
         monkeypatch.setenv(name, val)
         assert np.array_equal(run(), base), name
         monkeypatch.delenv(name)
+
+
+@pytest.mark.parametrize("chunk", [2, 3])
+def test_multi_chunk_batches_match_oracle(vsp, ctx, chunk):
+    """k = 7 ballots in chunks of 2 and 3 (vsp_ctx_set_batch_chunk): the double-buffered assembly tails, the witness
+    prefetch's slot reuse, the ragged last chunk and join_tails, on the host-buffer and the device-resident entry points
+    of prove_batch and encrypt_batch, every proof and cipher text against the oracle"""
+    import torch
+    nc, ni, msg_size, k = 97, 30, 25, 7
+    cs, _, _ = synthetic_r1cs(nc, ni, 0, binary=True)
+    arr = synthetic_pk_arrays(cs, 61)
+    pub_arr, gamma_abc_rest = synthetic_saver_pub(msg_size, seed=62)
+    gamma_abc_rest = np.ascontiguousarray(gamma_abc_rest[:msg_size])
+    pub = vsp.SaverPublicKey(pub_arr)
+    opub = fx.fill_struct(cref.SaverPubkeyDesc(), pub_arr)
+    opk = _oracle_pk(arr)
+    rng = random.Random(63)
+    prim, aux, rs = [], [], []
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=100 + b, binary=True)
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4))
+    prim, aux, rs = np.stack(prim), np.stack(aux), np.stack(rs)
+    want_plain, want_enc, want_ct = [], [], []
+    for b in range(k):
+        r, s, rsv = cref.limbs_to_ints(rs[b])
+        want_plain.append(cref.groth16_prove(opk, prim[b], aux[b], r, s))
+        want_enc.append(cref.groth16_prove(opk, prim[b], aux[b], r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"]))
+        want_ct.append(cref.saver_ciphertext(opub, gamma_abc_rest, np.ascontiguousarray(prim[b][:msg_size]), rsv))
+    want_plain, want_enc, want_ct = np.stack(want_plain), np.stack(want_enc), np.stack(want_ct)
+    ctx.set_batch_chunk(chunk)
+    try:
+        pk = vsp.ProvingKey(ctx, arr)
+        key = pub.resident(ctx, gamma_abc_rest)
+        assert np.array_equal(pk.prove_batch(prim, aux, rs), want_plain)
+        cts, proofs = pk.encrypt_batch(key, prim, aux, rs)
+        assert np.array_equal(cts, want_ct) and np.array_equal(proofs, want_enc)
+        # device-resident: (1 || primary || auxiliary) per ballot
+        assign = np.zeros((k, ni + cs.num_variables - ni + 1, 4), dtype=np.uint64)
+        assign[:, 0, 0] = 1
+        assign[:, 1:ni + 1] = prim
+        assign[:, ni + 1:] = aux
+        d_assign = torch.from_numpy(assign.view(np.int64)).cuda()
+        d_proofs = torch.zeros((k, 48), dtype=torch.int64, device="cuda")
+        d_cts = torch.zeros((k, msg_size + 2, 12), dtype=torch.int64, device="cuda")
+        pk.prove_batch_dev(k, d_assign.data_ptr(), rs, d_proofs.data_ptr())
+        ctx.synchronize()
+        assert np.array_equal(d_proofs.cpu().numpy().view(np.uint64), want_plain)
+        pk.encrypt_batch_dev(key, k, d_assign.data_ptr(), rs, d_cts.data_ptr(), d_proofs.data_ptr())
+        ctx.synchronize()
+        assert np.array_equal(d_proofs.cpu().numpy().view(np.uint64), want_enc)
+        assert np.array_equal(d_cts.cpu().numpy().view(np.uint64), want_ct)
+        key.close()
+        pk.close()
+    finally:
+        ctx.set_batch_chunk(0)
+
+
+def test_long_constraint_rows_and_table_less_key(vsp, ctx, monkeypatch):
+    """the reference's field-input example closes with one constraint over every variable (r1cs_examples.hpp:116-126):
+    5,000 constraints put ~5,000 terms in that row, which the prover cuts over many blocks (k_r1cs_long_*); and the same
+    key loaded without window tables (VSP_TABLE_MAX_LOG = 0, the policy of 2^23+ point queries) proves identically"""
+    cs, primary, aux, arr = _instance(5000, 4, seed=12)
+    want_h = cref.witness_map(_oracle_pk(arr).cs, primary, aux)
+    r, s = 0xabcdef, o.R - 7
+    want = cref.groth16_prove(_oracle_pk(arr), primary, aux, r, s)
+    for table_max in (None, "0"):
+        if table_max is not None:
+            monkeypatch.setenv("VSP_TABLE_MAX_LOG", table_max)
+        pk = vsp.ProvingKey(ctx, arr)
+        assert np.array_equal(pk.witness_map(primary, aux), want_h)
+        assert np.array_equal(pk.prove(primary, aux, r, s), want)
+        pk.close()

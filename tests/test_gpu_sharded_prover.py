@@ -45,3 +45,57 @@ def test_sharded_proof_equals_single_prover(vsp, ctx, nc, ni, world):
     full.close()
     for k in keys:
         k.close()
+
+
+@pytest.mark.parametrize("nc,ni,world,binary", [(97, 30, 2, True), (4500, 6, 3, False)])
+def test_device_resident_sharded_proof(vsp, ctx, nc, ni, world, binary):
+    """the path bench.py times (sharded.ShardedProver.prove_dev): vsp_prove_partial_dev leaves raw XYZZ shares on the
+    device, the all_gather is emulated by writing every rank's 144 limbs into one device tensor, vsp_prove_assemble_dev
+    sums them on the device.  Slices generated per rank exactly as the bench does.  Equal to the oracle's single prover."""
+    import torch
+    sh = importlib.import_module("vote-saver-protocol_b200.sharded")
+    cs, primary, aux = synthetic_r1cs(nc, ni, seed=nc, binary=binary)
+    arr = synthetic_pk_arrays(cs, nc + 2)
+    pub_arr, _ = synthetic_saver_pub(5, seed=9)
+    pub = vsp.SaverPublicKey(pub_arr)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    _, m = vsp.domain_plan(nc + ni + 1)
+    assign = np.concatenate([cref.ints_to_limbs([1], 4), P, A])
+    d_assign = torch.from_numpy(assign.view(np.int64)).cuda()
+    gathered = torch.zeros((world, sh.PARTIAL_LIMBS), dtype=torch.int64, device="cuda")
+    d_proof = torch.zeros(48, dtype=torch.int64, device="cuda")
+    keys = []
+    for rank in range(world):
+        sliced, rng = sh.slice_proving_key(arr, m, rank, world)
+        assert rng == sh.key_ranges(arr["cs"], m, int(arr["B_count"]), rank, world)
+        pk = vsp.ProvingKey(ctx, sliced, slice=rng)
+        pk.prove_partial_dev(d_assign.data_ptr(), gathered[rank].data_ptr())
+        keys.append(pk)
+    rng_ = random.Random(6)
+    r, s, rsv = (rng_.randrange(o.R) for _ in range(3))
+    opk = fx.fill_pk(cref.ProvingKeyDesc(), arr)
+    keys[0].prove_assemble_dev(world, gathered.data_ptr(), r, s, d_proof.data_ptr())
+    ctx.synchronize()
+    assert np.array_equal(d_proof.cpu().numpy().view(np.uint64), cref.groth16_prove(opk, P, A, r, s))
+    keys[-1].prove_assemble_dev(world, gathered.data_ptr(), r, s, d_proof.data_ptr(), pub, rsv)
+    ctx.synchronize()
+    assert np.array_equal(d_proof.cpu().numpy().view(np.uint64),
+                          cref.groth16_prove(opk, P, A, r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"]))
+    for k in keys:
+        k.close()
+
+
+def test_sharded_prover_over_nccl_two_gpus():
+    """real NCCL, two processes, two GPUs (skipped on a one-GPU box): tests/dist_sharded_check.py proves one circuit with
+    sharded.ShardedProver.prove_dev on both ranks and compares with the oracle's single prover on rank 0"""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29611", os.path.join(here, "dist_sharded_check.py")],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "SHARDED_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

@@ -100,6 +100,14 @@ class Context:
             raise ValueError(text or "invalid argument")
         raise VspError(rc, text)
 
+    def set_batch_chunk(self, ballots: int):
+        """ballots per chunk of the batched prover (0 = default); results do not depend on it"""
+        self.check(self._lib.vsp_ctx_set_batch_chunk(self._h, int(ballots)))
+
+    @property
+    def last_warning(self) -> str:
+        return (self._lib.vsp_last_warning(self._h) or b"").decode("utf-8", "replace")
+
     def synchronize(self):
         self.check(self._lib.vsp_ctx_synchronize(self._h))
 
@@ -120,6 +128,12 @@ class Context:
             self.check(self._lib.vsp_ctx_profile_read(self._h, k, C.byref(n), C.byref(ms), C.byref(u)))
             out[name] = {"launches": n.value, "ms": ms.value, "units": u.value}
         return out
+
+    def accumulate_mads_per_add(self) -> float:
+        """32x32->64 multiply-adds the G1 bucket-accumulation kernel issues per bucket addition (a property of the build)"""
+        out = C.c_double(0)
+        self.check(self._lib.vsp_accumulate_mads_per_add(self._h, C.byref(out)))
+        return out.value
 
     def measure_imad_rate(self, iters: int = 4096) -> float:
         out = C.c_double(0)
@@ -174,7 +188,8 @@ def multiply_by_coset(ctx: Context, a, g: int = FR_MULTIPLICATIVE_GENERATOR) -> 
 class _Bases:
     _G2 = False
 
-    def __init__(self, ctx: Context, bases=None, *, _handle=None, _n=0):
+    def __init__(self, ctx: Context, bases=None, *, table: bool = True, _handle=None, _n=0):
+        """table=False: the points only — multiexps take the one-shot path with the bases already resident"""
         self.ctx = ctx
         lib = ctx._lib
         if _handle is not None:
@@ -182,8 +197,8 @@ class _Bases:
             return
         b = _a(bases, 24 if self._G2 else 12)
         h = C.c_void_p()
-        create = lib.vsp_g2_bases_create if self._G2 else lib.vsp_g1_bases_create
-        ctx.check(create(ctx._h, b.shape[0], _p(b), C.byref(h)))
+        create = lib.vsp_g2_bases_create_ex if self._G2 else lib.vsp_g1_bases_create_ex
+        ctx.check(create(ctx._h, b.shape[0], _p(b), int(table), C.byref(h)))
         self._h, self.n = h, b.shape[0]
 
     def close(self):
@@ -196,6 +211,11 @@ class _Bases:
             self.close()
         except Exception:
             pass
+
+    def multiexp_dev(self, n_scalars: int, d_scalars: int, d_out: int):
+        """scalars and the affine result (12 / 24 limbs) stay on the device; stream-ordered, no synchronisation."""
+        fn = self.ctx._lib.vsp_g2_msm_bases_dev if self._G2 else self.ctx._lib.vsp_g1_msm_bases_dev
+        self.ctx.check(fn(self.ctx._h, self._h, n_scalars, C.c_void_p(d_scalars), C.c_void_p(d_out)))
 
     def multiexp(self, scalars) -> np.ndarray:
         s = _a(scalars, 4)
@@ -210,10 +230,11 @@ class G1Bases(_Bases):
     _G2 = False
 
     @classmethod
-    def generate(cls, ctx: Context, n: int, seed: int) -> "G1Bases":
-        """Synthetic bases k_i * G with k_i = splitmix64(seed, i) | 1, built on the device."""
+    def generate(cls, ctx: Context, n: int, seed: int, table: bool = True) -> "G1Bases":
+        """Synthetic bases k_i * G with k_i = splitmix64(seed + i) | 1, built on the device.
+        table=False keeps the points only: multiexps over them run the one-shot (table-less) path."""
         h = C.c_void_p()
-        ctx.check(ctx._lib.vsp_g1_bases_generate(ctx._h, n, seed, C.byref(h)))
+        ctx.check(ctx._lib.vsp_g1_bases_generate_ex(ctx._h, n, seed, int(table), C.byref(h)))
         return cls(ctx, _handle=h, _n=n)
 
     def read(self, first: int = 0, count: int | None = None) -> np.ndarray:
@@ -222,10 +243,6 @@ class G1Bases(_Bases):
         self.ctx.check(self.ctx._lib.vsp_g1_bases_read(self.ctx._h, self._h, first, count, _p(out)))
         return out
 
-    def multiexp_dev(self, n_scalars: int, d_scalars: int, d_out: int):
-        """scalars and the 12-limb affine result stay on the device; stream-ordered, no synchronisation."""
-        self.ctx.check(self.ctx._lib.vsp_g1_msm_bases_dev(self.ctx._h, self._h, n_scalars, C.c_void_p(d_scalars),
-                                                          C.c_void_p(d_out)))
 
 
 class G2Bases(_Bases):
@@ -394,6 +411,24 @@ class ProvingKey:
             rc = self.ctx._lib.vsp_prove_assemble(self.ctx._h, self._h, _p(q), _p(rr), _p(ss), None, None, _p(out))
         self.ctx.check(rc)
         return out
+
+    def prove_partial_dev(self, d_assignment: int, d_partials: int):
+        """device pointers: (1 || primary || auxiliary) in, 144 limbs of raw XYZZ shares out; stream-ordered"""
+        self.ctx.check(self.ctx._lib.vsp_prove_partial_dev(self.ctx._h, self._h, C.c_void_p(d_assignment),
+                                                           C.c_void_p(d_partials)))
+
+    def prove_assemble_dev(self, world: int, d_gathered: int, r: int, s: int, d_proof: int,
+                           pubkey: SaverPublicKey | None = None, r_saver: int | None = None):
+        """d_gathered: world x 144 limbs (the all_gather of every rank's prove_partial_dev); proof left at d_proof"""
+        rr, ss = _fr(r), _fr(s)
+        if pubkey is not None:
+            rs, gi = _fr(r_saver), pubkey.arrays["gamma_inverse_sum_s_g1"]
+            rc = self.ctx._lib.vsp_prove_assemble_dev(self.ctx._h, self._h, world, C.c_void_p(d_gathered), _p(rr), _p(ss),
+                                                      _p(rs), _p(gi), C.c_void_p(d_proof))
+        else:
+            rc = self.ctx._lib.vsp_prove_assemble_dev(self.ctx._h, self._h, world, C.c_void_p(d_gathered), _p(rr), _p(ss),
+                                                      None, None, C.c_void_p(d_proof))
+        self.ctx.check(rc)
 
     def prove_batch(self, primary, auxiliary, rs, pubkey: SaverPublicKey | None = None) -> np.ndarray:
         """k ballots: primary (k, ni, 4), auxiliary (k, na, 4), rs (k, 3, 4) = (r, s, r_saver).  -> (k, 48)"""

@@ -86,6 +86,8 @@ SYMBOLS = [
     ("vsp_ctx_create", _int, [_int, _vp, C.POINTER(_vp)]),
     ("vsp_ctx_destroy", None, [_vp]),
     ("vsp_last_error", C.c_char_p, [_vp]),
+    ("vsp_last_warning", C.c_char_p, [_vp]),
+    ("vsp_ctx_set_batch_chunk", _int, [_vp, _int]),
     ("vsp_ctx_synchronize", _int, [_vp]),
     ("vsp_ctx_launch_count", _u64, [_vp]),
     ("vsp_version", C.c_char_p, []),
@@ -103,13 +105,17 @@ SYMBOLS = [
     ("vsp_g1_bases_create", _int, [_vp, _u64, _vp, C.POINTER(_vp)]),
     ("vsp_g1_bases_destroy", None, [_vp]),
     ("vsp_g2_bases_create", _int, [_vp, _u64, _vp, C.POINTER(_vp)]),
+    ("vsp_g1_bases_create_ex", _int, [_vp, _u64, _vp, _int, C.POINTER(_vp)]),
+    ("vsp_g2_bases_create_ex", _int, [_vp, _u64, _vp, _int, C.POINTER(_vp)]),
     ("vsp_g2_bases_destroy", None, [_vp]),
     ("vsp_g1_bases_generate", _int, [_vp, _u64, _u64, C.POINTER(_vp)]),
+    ("vsp_g1_bases_generate_ex", _int, [_vp, _u64, _u64, _int, C.POINTER(_vp)]),
     ("vsp_g1_bases_read", _int, [_vp, _vp, _u64, _u64, _vp]),
     ("vsp_g2_points_generate", _int, [_vp, _u64, _u64, _vp]),
     ("vsp_g1_msm_bases", _int, [_vp, _vp, _u64, _vp, _int, _vp]),
     ("vsp_g2_msm_bases", _int, [_vp, _vp, _u64, _vp, _int, _vp]),
     ("vsp_g1_msm_bases_dev", _int, [_vp, _vp, _u64, _vp, _vp]),
+    ("vsp_g2_msm_bases_dev", _int, [_vp, _vp, _u64, _vp, _vp]),
     ("vsp_g1_sum", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_g2_sum", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_g1_sum_dev", _int, [_vp, _u64, _vp, _vp]),
@@ -118,6 +124,8 @@ SYMBOLS = [
     ("vsp_pk_load_slice", _int, [_vp, C.POINTER(ProvingKeyDesc), C.POINTER(PkSliceDesc), C.POINTER(_vp)]),
     ("vsp_prove_partial", _int, [_vp, _vp, _vp, _vp, _vp]),
     ("vsp_prove_assemble", _int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_prove_partial_dev", _int, [_vp, _vp, _vp, _vp]),
+    ("vsp_prove_assemble_dev", _int, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_pk_destroy", None, [_vp]),
     ("vsp_pk_domain_size", _u64, [_vp]),
     ("vsp_witness_map", _int, [_vp, _vp, _vp, _vp, _vp]),
@@ -156,6 +164,7 @@ SYMBOLS = [
     ("vsp_codec_fast_pk_read", _int, [_vp, C.c_size_t, C.POINTER(ProvingKeyDesc)]),
     ("vsp_codec_fast_pk_write", _int, [C.POINTER(ProvingKeyDesc), _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
+    ("vsp_accumulate_mads_per_add", _int, [_vp, C.POINTER(C.c_double)]),
 ]
 
 _LIB = None

@@ -123,6 +123,12 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
 }
 
 const char* vsp_last_error(const vsp_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+const char* vsp_last_warning(const vsp_ctx* ctx) { return ctx ? ctx->warn.c_str() : ""; }
+int vsp_ctx_set_batch_chunk(vsp_ctx* ctx, int ballots) {
+    if (!ctx || ballots < 0 || ballots > 1024) return VSP_E_INVALID;
+    ctx->batch_chunk = ballots;
+    return VSP_OK;
+}
 
 int vsp_ctx_synchronize(vsp_ctx* ctx) {
     if (!ctx) return VSP_E_INVALID;
@@ -257,11 +263,19 @@ static int bases_create(vsp_ctx* ctx, bool g2, uint64_t n, const uint64_t* bases
     return bases_upload(ctx, g2, n, bases, b, table);
 }
 
+int vsp_g1_bases_create_ex(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, int table, vsp_g1_bases** out);
+int vsp_g2_bases_create_ex(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, int table, vsp_g2_bases** out);
 int vsp_g1_bases_create(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, vsp_g1_bases** out) {
+    return vsp_g1_bases_create_ex(ctx, n, bases, 1, out);
+}
+int vsp_g2_bases_create(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, vsp_g2_bases** out) {
+    return vsp_g2_bases_create_ex(ctx, n, bases, 1, out);
+}
+int vsp_g1_bases_create_ex(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, int table, vsp_g1_bases** out) {
     if (!out) return VSP_E_INVALID;
     vsp_g1_bases* h = new (std::nothrow) vsp_g1_bases();
     if (!h) return VSP_E_NOMEM;
-    int rc = bases_create(ctx, false, n, bases, &h->b);
+    int rc = bases_create(ctx, false, n, bases, &h->b, table != 0);
     if (rc) {
         bases_free(&h->b);
         delete h;
@@ -275,11 +289,11 @@ void vsp_g1_bases_destroy(vsp_g1_bases* b) {
     bases_free(&b->b);
     delete b;
 }
-int vsp_g2_bases_create(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, vsp_g2_bases** out) {
+int vsp_g2_bases_create_ex(vsp_ctx* ctx, uint64_t n, const uint64_t* bases, int table, vsp_g2_bases** out) {
     if (!out) return VSP_E_INVALID;
     vsp_g2_bases* h = new (std::nothrow) vsp_g2_bases();
     if (!h) return VSP_E_NOMEM;
-    int rc = bases_create(ctx, true, n, bases, &h->b);
+    int rc = bases_create(ctx, true, n, bases, &h->b, table != 0);
     if (rc) {
         bases_free(&h->b);
         delete h;
@@ -295,7 +309,12 @@ void vsp_g2_bases_destroy(vsp_g2_bases* b) {
 }
 
 // synthetic bases for the measurement sweeps: bases[i] = k_i * G, k_i = splitmix64(seed + i) | 1
+int vsp_g1_bases_generate_ex(vsp_ctx* ctx, uint64_t n, uint64_t seed, int table, vsp_g1_bases** out);
 int vsp_g1_bases_generate(vsp_ctx* ctx, uint64_t n, uint64_t seed, vsp_g1_bases** out) {
+    return vsp_g1_bases_generate_ex(ctx, n, seed, 1, out);
+}
+// table = 0: the points only (multiexps over the handle take the one-shot, table-less path)
+int vsp_g1_bases_generate_ex(vsp_ctx* ctx, uint64_t n, uint64_t seed, int table, vsp_g1_bases** out) {
     if (!ctx || !out) return VSP_E_INVALID;
     cudaSetDevice(ctx->device);
     vsp_g1_bases* h = new (std::nothrow) vsp_g1_bases();
@@ -309,7 +328,7 @@ int vsp_g1_bases_generate(vsp_ctx* ctx, uint64_t n, uint64_t seed, vsp_g1_bases*
         return set_error(ctx, VSP_E_NOMEM, "cudaMalloc(%llu bases) failed: %s", (unsigned long long)n, cudaGetErrorString(e));
     }
     int rc = n ? bases_generate_g1(ctx, ctx->stream, h->b.d_pts, n, seed) : VSP_OK;
-    if (rc == VSP_OK) rc = bases_finalize(ctx, &h->b, true);
+    if (rc == VSP_OK) rc = bases_finalize(ctx, &h->b, table != 0);
     if (rc == VSP_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
         rc = set_error(ctx, VSP_E_CUDA, "bases generation failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (rc) {
@@ -376,6 +395,13 @@ int vsp_g2_msm_bases(vsp_ctx* ctx, const vsp_g2_bases* b, uint64_t n_scalars, co
     return msm_bases_host_out(ctx, b->b, n_scalars, scalars, scalars_on_device, out);
 }
 int vsp_g1_msm_bases_dev(vsp_ctx* ctx, const vsp_g1_bases* b, uint64_t n_scalars, const uint64_t* d_scalars,
+                         uint64_t* d_out) {
+    if (!ctx || !b || !d_out || (!d_scalars && n_scalars)) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return msm_run(ctx, ctx->stream, b->b, n_scalars, reinterpret_cast<const uint32_t*>(d_scalars), d_out);
+}
+
+int vsp_g2_msm_bases_dev(vsp_ctx* ctx, const vsp_g2_bases* b, uint64_t n_scalars, const uint64_t* d_scalars,
                          uint64_t* d_out) {
     if (!ctx || !b || !d_out || (!d_scalars && n_scalars)) return VSP_E_INVALID;
     cudaSetDevice(ctx->device);
@@ -456,6 +482,12 @@ __global__ void __launch_bounds__(256) k_imad_rate(uint32_t* sink, uint32_t iter
 #pragma unroll
     for (int i = 0; i < 8; ++i) x ^= lo[i] ^ hi[i];
     if (x == 0x12345678u) sink[0] = x;  // keep the chains live
+}
+
+extern "C" int vsp_accumulate_mads_per_add(vsp_ctx* ctx, double* out) {
+    if (!ctx || !out) return VSP_E_INVALID;
+    *out = ACC_G1_MADS_PER_ADD;
+    return VSP_OK;
 }
 
 extern "C" int vsp_measure_imad_rate(vsp_ctx* ctx, uint64_t iters, double* mads_per_second) {

@@ -49,6 +49,7 @@ struct vsp_ctx {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string err;
+    std::string warn;  // last non-fatal degradation (e.g. a window table that did not fit); vsp_last_warning
     uint64_t launches = 0;
     int sm_count = 148;
     vsp::NttTables* ntt = nullptr;  // lazily built twiddle tables (ntt.cu)
@@ -66,6 +67,7 @@ struct vsp_ctx {
         bool pending = false;
     } tail[2];
     unsigned tail_next = 0;
+    int batch_chunk = 0;  // ballots per chunk of the batched prover (0: VSP_BATCH_CHUNK or 64); vsp_ctx_set_batch_chunk
     cudaEvent_t ev_main = nullptr;
     vsp::KProf prof;
     int last_prof = -1;  // profile record of the most recent launch (for kprof_units)
@@ -81,6 +83,15 @@ inline int set_error(vsp_ctx* ctx, int code, const char* fmt, ...) {
     va_end(ap);
     if (ctx) ctx->err = buf;
     return code;
+}
+
+inline void set_warning(vsp_ctx* ctx, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->warn = buf;
 }
 
 #define VSP_CUDA_CHECK(ctx, expr)                                                                          \

@@ -712,8 +712,22 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     p.stride = bases.table ? bases.n : 0;
     p.buckets = (uint64_t(batch) * p.sets) << p.nb_log;
     const uint64_t total = n * p.windows * batch;
-    if (total >= (uint64_t(1) << 32) || p.buckets >= (uint64_t(1) << 31) || batch * p.sets > 65535)
-        return set_error(ctx, VSP_E_INVALID, "multiexp: batch * n * windows must be < 2^32");
+    if (total >= (uint64_t(1) << 32) || p.buckets >= (uint64_t(1) << 31) || uint64_t(batch) * p.sets > 65535) {
+        // keys and sorted positions are 32-bit: a batch too large for one pass runs as consecutive sub-batches on the same
+        // stream (same results; the scratch of one sub-batch is released, stream-ordered, before the next allocates)
+        const uint64_t per = n * p.windows, sets_buckets = uint64_t(p.sets) << p.nb_log;
+        uint64_t sub = std::min<uint64_t>({((uint64_t(1) << 32) - 1) / per, ((uint64_t(1) << 31) - 1) / sets_buckets,
+                                           65535 / p.sets});
+        if (sub == 0 || batch == 1)
+            return set_error(ctx, VSP_E_INVALID, "multiexp: n * windows must be < 2^32 (n = %llu, %u windows)",
+                             (unsigned long long)n, p.windows);
+        for (unsigned b0 = 0; b0 < batch; b0 += (unsigned)sub) {
+            const unsigned bn = (unsigned)std::min<uint64_t>(sub, batch - b0);
+            VSP_TRY(msm_run_t<F>(ctx, s, bases, n, d_scalars + 8 * uint64_t(b0) * scalar_stride, scalar_stride, bn,
+                                 d_out + uint64_t(b0) * out_stride, out_stride, raw));
+        }
+        return VSP_OK;
+    }
     const unsigned tiles = (unsigned)((p.buckets + SCAN_TILE - 1) / SCAN_TILE);
 
     DevBuf keys, counts, offsets, cursors, task_off, tile_scratch, sorted, heavy, heavy_count;
@@ -836,7 +850,11 @@ static int bases_finalize_t(vsp_ctx* ctx, cudaStream_t s, BasesDev* b, bool tabl
     const size_t bytes = (size_t)b->n * b->windows * Affine<F>::BYTES;
     if (cudaMalloc(&t, bytes) != cudaSuccess) {
         cudaGetLastError();
-        return VSP_OK;  // not enough memory for the table: the table-less path still works
+        // not enough memory for the table: the table-less path still works (same results), but a small-n multiexp is an
+        // order of magnitude slower without it, so the caller is told (vsp_last_warning)
+        set_warning(ctx, "window table of %llu points x %u windows (%.1f GB) did not fit: multiexps over these bases run table-less",
+                    (unsigned long long)b->n, b->windows, bytes / 1e9);
+        return VSP_OK;
     }
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(t, b->d_pts, (size_t)b->n * Affine<F>::BYTES, cudaMemcpyDeviceToDevice, s));
     const uint64_t threads = (b->n + TABLE_CH - 1) / TABLE_CH;

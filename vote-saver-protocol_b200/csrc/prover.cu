@@ -24,6 +24,7 @@
 #include "host_fr.h"
 #include "msm.cuh"
 
+#include <algorithm>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -44,6 +45,10 @@ struct vsp_pk {
     bool sliced = false;
     uint64_t A_lo = 0, A_n = 0, B_lo = 0, H_lo = 0, H_n = 0, L_lo = 0, L_n = 0;
     bool short_rows = false;  // average row has <= 8 terms per matrix: thread-per-row R1CS evaluation
+    // constraints with more than LONG_ROW_TERMS terms in one matrix (e.g. the closing "sum of everything, squared"
+    // constraint of the reference's synthetic examples, r1cs_examples.hpp:116-126) are cut over many blocks
+    uint32_t* d_long_rows = nullptr;
+    unsigned n_long = 0;
     // CSR (device): rows u64, cols u32, values Montgomery (A, C: v R;  B: v R^2 so that B w comes out in Montgomery form)
     uint64_t* d_row[3] = {nullptr, nullptr, nullptr};
     uint32_t* d_col[3] = {nullptr, nullptr, nullptr};
@@ -103,6 +108,9 @@ struct CsrDev {
     const uint32_t* val[3];
 };
 
+constexpr uint64_t LONG_ROW_TERMS = 4096;
+constexpr unsigned LONG_SLICES = 512;
+
 // one warp per (domain row, ballot = blockIdx.y): aA / aB / aC[row] = <matrix row, (1 || primary || aux)>; rows
 // n_c .. n_c + n_in of aA hold the input-consistency values, everything above is zero.  aB comes out in Montgomery form
 // (its values carry R^2).  abc = [aA: B x m | aB: B x m | aC: B x m]
@@ -127,6 +135,7 @@ __global__ void __launch_bounds__(256) k_r1cs_eval(CsrDev csr, const uint32_t* _
 #pragma unroll
     for (int mtx = 0; mtx < 3; ++mtx) {
         const uint64_t lo = csr.row[mtx][row], hi = csr.row[mtx][row + 1];
+        if (hi - lo > LONG_ROW_TERMS) continue;  // k_r1cs_long_* writes it (warp-uniform)
         Fr acc = Fr::zero();
         for (uint64_t k = lo + lane; k < hi; k += 32) {
             Fr v = fp_load<FrCfg>(csr.val[mtx] + 8 * k);
@@ -158,6 +167,7 @@ __global__ void __launch_bounds__(128) k_r1cs_eval_rows(CsrDev csr, const uint32
 #pragma unroll 1
     for (int mtx = 0; mtx < 3; ++mtx) {
         const uint64_t lo = csr.row[mtx][row], hi = csr.row[mtx][row + 1];
+        if (hi - lo > LONG_ROW_TERMS) continue;  // k_r1cs_long_* writes it
         Fr acc = Fr::zero();
         for (uint64_t k = lo; k < hi; ++k) {
             Fr v = fp_load<FrCfg>(csr.val[mtx] + 8 * k);
@@ -166,6 +176,46 @@ __global__ void __launch_bounds__(128) k_r1cs_eval_rows(CsrDev csr, const uint32
         }
         fp_store(outs[mtx] + 8 * row, acc);
     }
+}
+
+// long rows: block (slice, long row * 3 + matrix, ballot) sums its slice of the row's terms into part[...][slice];
+// k_r1cs_long_final adds the slices up and writes the value (rows short in this matrix are left to the row kernels)
+__global__ void __launch_bounds__(256) k_r1cs_long_partial(CsrDev csr, const uint32_t* __restrict__ long_rows,
+                                                           const uint32_t* __restrict__ w_all, uint64_t w_stride,
+                                                           uint32_t* __restrict__ part) {
+    __shared__ uint32_t sm[8 * 8];
+    const unsigned lr = blockIdx.y / 3, mtx = blockIdx.y % 3, b = blockIdx.z;
+    const uint64_t row = long_rows[lr];
+    const uint64_t lo = csr.row[mtx][row], hi = csr.row[mtx][row + 1];
+    Fr acc = Fr::zero();
+    if (hi - lo > LONG_ROW_TERMS) {
+        const uint64_t per = (hi - lo + LONG_SLICES - 1) / LONG_SLICES;
+        const uint64_t s0 = lo + per * blockIdx.x, s1 = s0 + per < hi ? s0 + per : hi;
+        const uint32_t* w = w_all + 8 * uint64_t(b) * w_stride;
+        for (uint64_t k = s0 + threadIdx.x; k < s1; k += blockDim.x) {
+            Fr v = fp_load<FrCfg>(csr.val[mtx] + 8 * k);
+            Fr x = fp_load<FrCfg>(w + 8 * uint64_t(csr.col[mtx][k]));
+            acc = fp_add(acc, fp_mul(v, x));
+        }
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) fp_store(sm + 8 * (threadIdx.x >> 5), acc);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (unsigned q = 1; q < blockDim.x / 32; ++q) acc = fp_add(acc, fp_load<FrCfg>(sm + 8 * q));
+        fp_store(part + 8 * ((uint64_t(b) * gridDim.y + blockIdx.y) * LONG_SLICES + blockIdx.x), acc);
+    }
+}
+__global__ void k_r1cs_long_final(CsrDev csr, const uint32_t* __restrict__ long_rows, unsigned n_long, unsigned B, uint64_t m,
+                                  const uint32_t* __restrict__ part, uint32_t* abc) {
+    const unsigned q = blockIdx.x * blockDim.x + threadIdx.x;  // (ballot, long row, matrix)
+    if (q >= B * n_long * 3) return;
+    const unsigned b = q / (n_long * 3), rm = q % (n_long * 3), lr = rm / 3, mtx = rm % 3;
+    const uint64_t row = long_rows[lr];
+    if (csr.row[mtx][row + 1] - csr.row[mtx][row] <= LONG_ROW_TERMS) return;
+    Fr acc = Fr::zero();
+    for (unsigned sl = 0; sl < LONG_SLICES; ++sl) acc = fp_add(acc, fp_load<FrCfg>(part + 8 * (uint64_t(q) * LONG_SLICES + sl)));
+    fp_store(abc + 8 * ((uint64_t(mtx) * B + b) * m + row), acc);
 }
 
 // h[b][i] = (a[b][i] * b_mont[b][i] - c[b][i]) [* zinv[i]]      (ballot b = blockIdx.y, vectors packed B x m)
@@ -497,6 +547,7 @@ extern "C" void vsp_pk_destroy(vsp_pk* pk) {
     bases_free(&pk->fx1tab);
     bases_free(&pk->fx2tab);
     free_dev(pk->d_B_idx);
+    free_dev(pk->d_long_rows);
     free_dev(pk->d_gpow);
     free_dev(pk->d_ginvpow);
     free_dev(pk->d_zinv);
@@ -557,12 +608,34 @@ static int pk_load_impl(vsp_ctx* ctx, const vsp_proving_key_t* d, const vsp_pk_s
             VSP_CUDA_CHECK(ctx, cudaGetLastError());
         }
     }
+    {
+        std::vector<uint32_t> lr;
+        for (uint64_t r = 0; r < pk->nc; ++r)
+            for (int i = 0; i < 3; ++i)
+                if (rows[i][r + 1] - rows[i][r] > LONG_ROW_TERMS) {
+                    lr.push_back((uint32_t)r);
+                    break;
+                }
+        pk->n_long = (unsigned)lr.size();
+        if (pk->n_long > 4096) return set_error(ctx, VSP_E_INVALID, "too many constraints with more than %llu terms",
+                                                (unsigned long long)LONG_ROW_TERMS);
+        if (pk->n_long) {
+            VSP_CUDA_CHECK(ctx, cudaMalloc(&pk->d_long_rows, lr.size() * 4));
+            VSP_CUDA_CHECK(ctx, cudaMemcpy(pk->d_long_rows, lr.data(), lr.size() * 4, cudaMemcpyHostToDevice));
+        }
+    }
     pk->short_rows = nnz_total <= 24 * pk->nc && !getenv("VSP_R1CS_WARP_ROWS");  // env: force the warp-per-row kernel (tests)
-    VSP_TRY(bases_upload(ctx, false, pk->A_n, d->A_query, &pk->A, true));
-    VSP_TRY(bases_upload(ctx, false, d->B_count, d->B_g1, &pk->Bg1, true));
-    VSP_TRY(bases_upload(ctx, true, d->B_count, d->B_g2, &pk->Bg2, true));
-    VSP_TRY(bases_upload(ctx, false, pk->H_n, d->H_query, &pk->H, true));
-    VSP_TRY(bases_upload(ctx, false, pk->L_n, d->L_query, &pk->L, true));
+    // window tables pay while a query is small enough that the bucket reduction would otherwise rival the bucket
+    // additions (a ballot circuit: 2^16 points); from VSP_TABLE_MAX_LOG (default 2^22) points up a query stays table-less:
+    // 13+ levels of a 2^24-point table are 20+ GB and half a minute of doublings for a few percent of multiexp time
+    unsigned table_max_log = 22;
+    if (const char* e = getenv("VSP_TABLE_MAX_LOG")) table_max_log = (unsigned)atoi(e);
+    auto want_table = [&](uint64_t n) { return table_max_log < 63 && n <= (uint64_t(1) << table_max_log); };
+    VSP_TRY(bases_upload(ctx, false, pk->A_n, d->A_query, &pk->A, want_table(pk->A_n)));
+    VSP_TRY(bases_upload(ctx, false, d->B_count, d->B_g1, &pk->Bg1, want_table(d->B_count)));
+    VSP_TRY(bases_upload(ctx, true, d->B_count, d->B_g2, &pk->Bg2, want_table(d->B_count)));
+    VSP_TRY(bases_upload(ctx, false, pk->H_n, d->H_query, &pk->H, want_table(pk->H_n)));
+    VSP_TRY(bases_upload(ctx, false, pk->L_n, d->L_query, &pk->L, want_table(pk->L_n)));
     pk->B_count = d->B_count;
     for (uint64_t k = 0; k < d->B_count; ++k)
         if (d->B_idx[k] > pk->nv) return set_error(ctx, VSP_E_INVALID, "B_query index out of range");
@@ -684,6 +757,14 @@ static int witness_map_dev(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const
     else
         VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval, dim3((unsigned)((m * 32 + 255) / 256), B), 256, 0, s, csr, d_w, w_stride,
                      pk->nc, pk->ni, m, abc);
+    DevBuf long_part;
+    if (pk->n_long) {
+        VSP_TRY(long_part.alloc(ctx, size_t(B) * pk->n_long * 3 * LONG_SLICES * 32, s));
+        VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_long_partial, dim3(LONG_SLICES, pk->n_long * 3, B), 256, 0, s, csr, pk->d_long_rows, d_w,
+                     w_stride, long_part.as<uint32_t>());
+        VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_long_final, (B * pk->n_long * 3 + 63) / 64, 64, 0, s, csr, pk->d_long_rows, pk->n_long, B,
+                     m, long_part.as<uint32_t>(), abc);
+    }
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     VSP_TRY(coset_lde(ctx, s, pk, abc, 3 * B));
     VSP_LAUNCH_K(ctx, KC_QAP, k_h_pointwise, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, aA, aB, aC, pk->d_zinv, m);
@@ -962,14 +1043,18 @@ static int join_tails(vsp_ctx* ctx) {
     return VSP_OK;
 }
 
-static unsigned batch_chunk() {
-    static unsigned v = 0;
-    if (!v) {
+// ballots per chunk: vsp_ctx_set_batch_chunk, else VSP_BATCH_CHUNK (read on every call), else 64; then clamped by the
+// domain size so that a chunk's scratch (about 100 B per ballot and domain element, plus the multiexp keys) stays a few
+// GB whatever the circuit: 128 ballots at m = 2^16, 8 at 2^20, 1 from 2^23 up
+static unsigned batch_chunk(const vsp_ctx* ctx, const vsp_pk* pk) {
+    long x = ctx->batch_chunk;
+    if (x <= 0) {
         const char* e = getenv("VSP_BATCH_CHUNK");
-        long x = e ? atol(e) : 64;
-        v = (unsigned)(x < 1 ? 1 : (x > 1024 ? 1024 : x));
+        x = e ? atol(e) : 64;
     }
-    return v;
+    x = x < 1 ? 1 : (x > 1024 ? 1024 : x);
+    const uint64_t cap = std::max<uint64_t>(1, (uint64_t(1) << 23) / (pk->m ? pk->m : 1));
+    return (unsigned)std::min<uint64_t>((uint64_t)x, cap);
 }
 
 }  // namespace vsp
@@ -994,7 +1079,7 @@ static int prove_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, uint64_t k, const u
                             uint64_t* d_proofs) {
     vsp_pk* pk = const_cast<vsp_pk*>(cpk);  // the gamma_inv table cache is the only mutable part
     const uint64_t stride = pk->nv + 1;
-    const unsigned chunk = batch_chunk();
+    const unsigned chunk = batch_chunk(ctx, pk);
     WitnessPrefetch pre(ctx, pk, primary, aux, k, chunk);
     if (!d_assignments) VSP_TRY(pre.init());
     for (uint64_t i = 0, c = 0; i < k; i += chunk, ++c) {
@@ -1062,52 +1147,84 @@ __global__ void k_affine_to_xyzz(const uint64_t* __restrict__ in, unsigned n, ui
 }
 }  // namespace vsp
 
-// out_partials: evA | evB1 | evH | evL (G1 affine) | evB2 (G2 affine) = 4 * 12 + 24 = 72 limbs, canonical
-extern "C" int vsp_prove_partial(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux,
-                                 uint64_t* out_partials) {
-    if (!ctx || !pk || !out_partials || (!primary && pk->ni) || (!aux && pk->na)) return VSP_E_INVALID;
-    cudaSetDevice(ctx->device);
+namespace vsp {
+// the five multiexp shares of this key (slice) for ONE assignment already on the device, as raw Montgomery XYZZ:
+//   d_o (144 u64) = evA | evB1 | evH | evL (G1, 24 limbs each) | evB2 (G2, 48 limbs).  Stream-ordered, no host wait.
+constexpr int PARTIAL_LIMBS = 4 * 24 + 48;
+static int prove_partial_impl(vsp_ctx* ctx, const vsp_pk* pk, const uint32_t* w, uint64_t* o) {
     cudaStream_t s = ctx->stream;
     const uint64_t m = pk->m, stride = pk->nv + 1;
-    DevBuf d_w, abc, bsc, out;
-    VSP_TRY(upload_witness(ctx, pk, 1, primary, aux, d_w));
-    const uint32_t* w = d_w.as<uint32_t>();
-    VSP_TRY(out.alloc(ctx, 72 * 8, s));
+    DevBuf abc, bsc;
     VSP_TRY(bsc.alloc(ctx, (pk->B_count ? pk->B_count : 1) * 32, s));
     VSP_TRY(abc.alloc(ctx, size_t(3) * m * 32, s));
-    uint64_t* o = out.as<uint64_t>();
     VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 2), ctx->ev_fork, 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 3), ctx->ev_fork, 0));
-    VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->A, pk->A_n, w + 8 * pk->A_lo, o, false));
-    VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->L, pk->L_n, w + 8 * (pk->ni + 1 + pk->L_lo), o + 36, false));
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[2], side_stream(ctx, 2)));
+    int rc = msm_run(ctx, side_stream(ctx, 2), pk->A, pk->A_n, w + 8 * pk->A_lo, o, true);
+    if (rc == VSP_OK) rc = msm_run(ctx, side_stream(ctx, 2), pk->L, pk->L_n, w + 8 * (pk->ni + 1 + pk->L_lo), o + 72, true);
+    cudaEventRecord(ctx->ev_join[2], side_stream(ctx, 2));
     cudaStream_t s3 = side_stream(ctx, 3);
-    if (pk->B_count)
+    if (rc == VSP_OK && pk->B_count)
         VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, dim3((unsigned)((pk->B_count + 127) / 128), 1), 128, 0, s3, w, stride,
                      pk->d_B_idx, pk->B_count, bsc.as<uint32_t>());
-    VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    VSP_TRY(msm_run(ctx, s3, pk->Bg2, pk->B_count, bsc.as<uint32_t>(), o + 48, false));
-    VSP_TRY(msm_run(ctx, s3, pk->Bg1, pk->B_count, bsc.as<uint32_t>(), o + 12, false));
-    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_join[3], s3));
+    if (rc == VSP_OK) rc = msm_run(ctx, s3, pk->Bg2, pk->B_count, bsc.as<uint32_t>(), o + 96, true);
+    if (rc == VSP_OK) rc = msm_run(ctx, s3, pk->Bg1, pk->B_count, bsc.as<uint32_t>(), o + 24, true);
+    cudaEventRecord(ctx->ev_join[3], s3);
     // the witness map is replicated: every rank needs its slice of coefficients_for_H
-    VSP_TRY(witness_map_dev(ctx, s, pk, w, stride, 1, abc.as<uint32_t>()));
-    VSP_TRY(msm_run(ctx, s, pk->H, pk->H_n, abc.as<uint32_t>() + 8 * pk->H_lo, o + 24, false));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[2], 0));
-    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[3], 0));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_partials, o, 72 * 8, cudaMemcpyDeviceToHost, s));
-    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    if (rc == VSP_OK) rc = witness_map_dev(ctx, s, pk, w, stride, 1, abc.as<uint32_t>());
+    if (rc == VSP_OK) rc = msm_run(ctx, s, pk->H, pk->H_n, abc.as<uint32_t>() + 8 * pk->H_lo, o + 48, true);
+    // join on every path, so that scratch owned by this call is not released under a side stream still reading it
+    cudaStreamWaitEvent(s, ctx->ev_join[2], 0);
+    cudaStreamWaitEvent(s, ctx->ev_join[3], 0);
+    if (rc != VSP_OK) return rc;
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
     return VSP_OK;
 }
 
-// sums: the five multiexp results summed over all ranks, same layout as out_partials
-extern "C" int vsp_prove_assemble(vsp_ctx* ctx, const vsp_pk* cpk, const uint64_t* sums, const uint64_t r[4],
-                                  const uint64_t sv[4], const uint64_t* r_saver, const uint64_t* gamma_inverse_sum_s_g1,
-                                  uint64_t* out_proof) {
+// sums[j] = sum over `world` ranks of gathered[rank][j-th point]   (thread j: 0..3 G1, 4 G2)
+__global__ void k_sum_partials(const uint64_t* __restrict__ gathered, unsigned world, uint32_t* __restrict__ ev) {
+    const unsigned j = blockIdx.x;
+    if (threadIdx.x != 0) return;
+    if (j < 4) {
+        G1XYZZ acc = G1XYZZ::inf();
+        for (unsigned g = 0; g < world; ++g) ec_add<FqOps>(acc, G1XYZZ::load(gathered + uint64_t(g) * PARTIAL_LIMBS + 24 * j));
+        acc.store(ev + 48 * j);
+    } else {
+        G2XYZZ acc = G2XYZZ::inf();
+        for (unsigned g = 0; g < world; ++g) ec_add<Fq2Ops>(acc, G2XYZZ::load(gathered + uint64_t(g) * PARTIAL_LIMBS + 96));
+        acc.store(ev + 48 * 4);
+    }
+}
+// XYZZ shares -> canonical affine (the host-facing form of vsp_prove_partial)
+__global__ void k_partials_to_affine(const uint64_t* __restrict__ xyzz, uint64_t* __restrict__ out) {
+    const unsigned j = blockIdx.x;
+    if (threadIdx.x != 0) return;
+    if (j < 4)
+        write_canonical<FqOps>(out + 12 * j, G1XYZZ::load(xyzz + 24 * j), true);
+    else
+        write_canonical<Fq2Ops>(out + 48, G2XYZZ::load(xyzz + 96), true);
+}
+struct AsmScalars {
+    uint64_t fsc[16];  // r | s | -rs | r_saver
+    uint64_t vsc[8];   // s | r
+};
+__global__ void k_store_scalars(AsmScalars v, uint64_t* fsc, uint64_t* vsc, FixedJob* jobs) {
+    if (threadIdx.x < 16) fsc[threadIdx.x] = v.fsc[threadIdx.x];
+    if (threadIdx.x < 8) vsc[threadIdx.x] = v.vsc[threadIdx.x];
+    if (threadIdx.x == 0) {
+        jobs[0] = FixedJob{0, 0};
+        jobs[1] = FixedJob{0, 1};
+        jobs[2] = FixedJob{0, 2};
+        jobs[3] = FixedJob{1, 3};
+        jobs[4] = FixedJob{0, 1};
+    }
+}
+
+// ev: evA | evB1 | evH | evL | evB2 summed over all ranks (device, XYZZ Montgomery); d_proof: 48 limbs on the device.
+// Stream-ordered: the host scalars travel as kernel arguments.
+static int assemble_impl(vsp_ctx* ctx, vsp_pk* pk, const uint32_t* ev, const uint64_t r[4], const uint64_t sv[4],
+                         const uint64_t* r_saver, const uint64_t* gamma_inverse_sum_s_g1, uint64_t* d_proof, DevBuf* keep) {
     using namespace hostfr;
-    if (!ctx || !cpk || !sums || !r || !sv || !out_proof) return VSP_E_INVALID;
-    cudaSetDevice(ctx->device);
-    vsp_pk* pk = const_cast<vsp_pk*>(cpk);
     const bool enc = r_saver && gamma_inverse_sum_s_g1;
     if (!fr_reduced(r) || !fr_reduced(sv) || (enc && !fr_reduced(r_saver)))
         return set_error(ctx, VSP_E_INVALID, "proving randomness not reduced mod r");
@@ -1118,63 +1235,117 @@ extern "C" int vsp_prove_assemble(vsp_ctx* ctx, const vsp_pk* cpk, const uint64_
     memcpy(fr.v, r, 32);
     memcpy(fs.v, sv, 32);
     const Fr4 frs = sub(from_u64(0), mul(fr, fs));
-    uint64_t fsc[16] = {0}, vsc[8];
-    memcpy(fsc, r, 32);
-    memcpy(fsc + 4, sv, 32);
-    memcpy(fsc + 8, frs.v, 32);
-    if (enc) memcpy(fsc + 12, r_saver, 32);
-    memcpy(vsc, sv, 32);
-    memcpy(vsc + 4, r, 32);
-    DevBuf d_sums, ev, d_fsc, d_vsc, jobs, fx1, fx2, gab, sg, proof;
-    VSP_TRY(d_sums.alloc(ctx, 72 * 8, s));
-    VSP_TRY(ev.alloc(ctx, 4 * X1 + X2, s));
-    VSP_TRY(d_fsc.alloc(ctx, sizeof(fsc), s));
-    VSP_TRY(d_vsc.alloc(ctx, sizeof(vsc), s));
-    VSP_TRY(jobs.alloc(ctx, sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), s));
-    VSP_TRY(fx1.alloc(ctx, 4 * X1, s));
-    VSP_TRY(fx2.alloc(ctx, X2, s));
-    VSP_TRY(gab.alloc(ctx, 192, s));
-    VSP_TRY(sg.alloc(ctx, 2 * X1, s));
-    VSP_TRY(proof.alloc(ctx, 384, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_sums.p, sums, 72 * 8, cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc, sizeof(fsc), cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc.p, vsc, sizeof(vsc), cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.p, PROOF_JOBS_G1, sizeof(PROOF_JOBS_G1), cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.as<char>() + sizeof(PROOF_JOBS_G1), PROOF_JOBS_G2, sizeof(PROOF_JOBS_G2),
-                                        cudaMemcpyHostToDevice, s));
-    // sums (evA | evB1 | evH | evL | evB2, affine canonical) -> the XYZZ Montgomery layout of the assembly kernels
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_affine_to_xyzz<FqOps>, 1, 32, 0, s, d_sums.as<uint64_t>(), 4u, ev.as<uint32_t>());
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_affine_to_xyzz<Fq2Ops>, 1, 32, 0, s, d_sums.as<uint64_t>() + 48, 1u,
-                 ev.as<uint32_t>() + 4 * X1 / 4);
-    const FixedJob* jobs1 = jobs.as<FixedJob>();
+    AsmScalars sc;
+    memset(&sc, 0, sizeof(sc));
+    memcpy(sc.fsc, r, 32);
+    memcpy(sc.fsc + 4, sv, 32);
+    memcpy(sc.fsc + 8, frs.v, 32);
+    if (enc) memcpy(sc.fsc + 12, r_saver, 32);
+    memcpy(sc.vsc, sv, 32);
+    memcpy(sc.vsc + 4, r, 32);
+    // one scratch block: fsc 128 | vsc 64 | jobs 64 | fx1 4 X1 | fx2 X2 | gab 192 | sg 2 X1
+    DevBuf& buf = *keep;
+    VSP_TRY(buf.alloc(ctx, 256 + 4 * X1 + X2 + 192 + 2 * X1, s));
+    char* bp = buf.as<char>();
+    uint64_t* d_fsc = reinterpret_cast<uint64_t*>(bp);
+    uint64_t* d_vsc = reinterpret_cast<uint64_t*>(bp + 128);
+    FixedJob* jobs1 = reinterpret_cast<FixedJob*>(bp + 192);
+    uint32_t* fx1 = reinterpret_cast<uint32_t*>(bp + 256);
+    uint32_t* fx2 = reinterpret_cast<uint32_t*>(bp + 256 + 4 * X1);
+    uint64_t* gab = reinterpret_cast<uint64_t*>(bp + 256 + 4 * X1 + X2);
+    uint32_t* sg = reinterpret_cast<uint32_t*>(bp + 256 + 4 * X1 + X2 + 192);
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_store_scalars, 1, 32, 0, s, sc, d_fsc, d_vsc, jobs1);
     VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<Fq2Ops>, 1, 32 * FIXED_WARPS, FIXED_WARPS * 32 * X2, s, pk->fx2tab.d_pts,
-                 pk->fx2tab.n, jobs1 + 4, 1u, 1u, d_fsc.as<uint32_t>(), 4u, (const uint32_t*)nullptr, uint64_t(0),
-                 fx2.as<uint32_t>());
+                 pk->fx2tab.n, jobs1 + 4, 1u, 1u, reinterpret_cast<uint32_t*>(d_fsc), 4u, (const uint32_t*)nullptr, uint64_t(0),
+                 fx2);
     VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (4 + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
-                 FIXED_WARPS * 32 * X1, s, pk->fx1tab.d_pts, pk->fx1tab.n, jobs1, 4u, 4u, d_fsc.as<uint32_t>(), 4u,
-                 (const uint32_t*)nullptr, uint64_t(0), fx1.as<uint32_t>());
+                 FIXED_WARPS * 32 * X1, s, pk->fx1tab.d_pts, pk->fx1tab.n, jobs1, 4u, 4u, reinterpret_cast<uint32_t*>(d_fsc), 4u,
+                 (const uint32_t*)nullptr, uint64_t(0), fx1);
     AsmPtrs ap;
-    ap.evA = ev.as<uint32_t>();
+    ap.evA = ev;
     ap.evB1 = ap.evA + X1 / 4;
     ap.evH = ap.evB1 + X1 / 4;
     ap.evL = ap.evH + X1 / 4;
     ap.evB2 = ap.evL + X1 / 4;
-    ap.fx1 = fx1.as<uint32_t>();
-    ap.fx2 = fx2.as<uint32_t>();
+    ap.fx1 = fx1;
+    ap.fx2 = fx2;
     ap.fixed1 = pk->fixed1.d_pts;
     ap.fixed2 = pk->fixed2.d_pts;
-    ap.gab = gab.as<uint64_t>();
-    ap.sg = sg.as<uint32_t>();
-    ap.proof = proof.as<uint64_t>();
+    ap.gab = gab;
+    ap.sg = sg;
+    ap.proof = d_proof;
     ap.B = 1;
     VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase1, dim3(1, 3), 32, 0, s, ap);
-    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2, 32, 0, s, gab.as<uint64_t>(), d_vsc.as<uint32_t>(), 2u, 0,
-                 sg.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2, 32, 0, s, gab, reinterpret_cast<uint32_t*>(d_vsc), 2u, 0, sg);
     VSP_LAUNCH_K(ctx, KC_FIXED, k_prove_phase3, 1, 32, 0, s, ap);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    return VSP_OK;
+}
+}  // namespace vsp
+
+// out_partials: evA | evB1 | evH | evL (G1 affine) | evB2 (G2 affine) = 4 * 12 + 24 = 72 limbs, canonical
+extern "C" int vsp_prove_partial(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux,
+                                 uint64_t* out_partials) {
+    if (!ctx || !pk || !out_partials || (!primary && pk->ni) || (!aux && pk->na)) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStream_t s = ctx->stream;
+    DevBuf d_w, raw, out;
+    VSP_TRY(upload_witness(ctx, pk, 1, primary, aux, d_w));
+    VSP_TRY(raw.alloc(ctx, PARTIAL_LIMBS * 8, s));
+    VSP_TRY(out.alloc(ctx, 72 * 8, s));
+    VSP_TRY(prove_partial_impl(ctx, pk, d_w.as<uint32_t>(), raw.as<uint64_t>()));
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_partials_to_affine, 5, 32, 0, s, raw.as<uint64_t>(), out.as<uint64_t>());
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_partials, out.p, 72 * 8, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    return VSP_OK;
+}
+
+// device-resident variant: d_assignment = (1 || primary || auxiliary) canonical Fr; d_partials = 144 limbs of raw
+// Montgomery XYZZ shares (evA | evB1 | evH | evL | evB2) for vsp_prove_assemble_dev.  Stream-ordered, no host wait.
+extern "C" int vsp_prove_partial_dev(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* d_assignment, uint64_t* d_partials) {
+    if (!ctx || !pk || !d_assignment || !d_partials) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return prove_partial_impl(ctx, pk, reinterpret_cast<const uint32_t*>(d_assignment), d_partials);
+}
+
+// sums: the five multiexp results summed over all ranks, same layout as out_partials
+extern "C" int vsp_prove_assemble(vsp_ctx* ctx, const vsp_pk* cpk, const uint64_t* sums, const uint64_t r[4],
+                                  const uint64_t sv[4], const uint64_t* r_saver, const uint64_t* gamma_inverse_sum_s_g1,
+                                  uint64_t* out_proof) {
+    if (!ctx || !cpk || !sums || !r || !sv || !out_proof) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    vsp_pk* pk = const_cast<vsp_pk*>(cpk);
+    cudaStream_t s = ctx->stream;
+    constexpr size_t X1 = G1XYZZ::BYTES, X2 = G2XYZZ::BYTES;
+    DevBuf d_sums, ev, proof, scratch;
+    VSP_TRY(d_sums.alloc(ctx, 72 * 8, s));
+    VSP_TRY(ev.alloc(ctx, 4 * X1 + X2, s));
+    VSP_TRY(proof.alloc(ctx, 384, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_sums.p, sums, 72 * 8, cudaMemcpyHostToDevice, s));
+    // sums (evA | evB1 | evH | evL | evB2, affine canonical) -> the XYZZ Montgomery layout of the assembly kernels
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_affine_to_xyzz<FqOps>, 1, 32, 0, s, d_sums.as<uint64_t>(), 4u, ev.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_affine_to_xyzz<Fq2Ops>, 1, 32, 0, s, d_sums.as<uint64_t>() + 48, 1u,
+                 ev.as<uint32_t>() + 4 * X1 / 4);
+    VSP_TRY(assemble_impl(ctx, pk, ev.as<uint32_t>(), r, sv, r_saver, gamma_inverse_sum_s_g1, proof.as<uint64_t>(), &scratch));
     VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(out_proof, proof.p, 384, cudaMemcpyDeviceToHost, s));
     VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
     return VSP_OK;
+}
+
+// device-resident variant: d_gathered = world x 144 limbs (every rank's vsp_prove_partial_dev output, e.g. straight out
+// of an all_gather); the shares are summed on the device and the proof (48 limbs) is left at d_proof.  Stream-ordered.
+extern "C" int vsp_prove_assemble_dev(vsp_ctx* ctx, const vsp_pk* cpk, uint64_t world, const uint64_t* d_gathered,
+                                      const uint64_t r[4], const uint64_t sv[4], const uint64_t* r_saver,
+                                      const uint64_t* gamma_inverse_sum_s_g1, uint64_t* d_proof) {
+    if (!ctx || !cpk || !d_gathered || !r || !sv || !d_proof || world == 0 || world > 4096) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    vsp_pk* pk = const_cast<vsp_pk*>(cpk);
+    cudaStream_t s = ctx->stream;
+    DevBuf ev, scratch;
+    VSP_TRY(ev.alloc(ctx, 4 * G1XYZZ::BYTES + G2XYZZ::BYTES, s));
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_sum_partials, 5, 32, 0, s, d_gathered, (unsigned)world, ev.as<uint32_t>());
+    return assemble_impl(ctx, pk, ev.as<uint32_t>(), r, sv, r_saver, gamma_inverse_sum_s_g1, d_proof, &scratch);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1407,7 +1578,7 @@ static int saver_encrypt_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, const vsp_s
     if (sp->n >= pk->ni + 1)
         return set_error(ctx, VSP_E_INVALID, "plain text should be a proper prefix of the primary input");
     const uint64_t stride = pk->nv + 1;
-    const unsigned chunk = batch_chunk();
+    const unsigned chunk = batch_chunk(ctx, pk);
     const uint64_t ct_limbs = uint64_t(sp->n + 2) * 12;
     WitnessPrefetch pre(ctx, pk, primary, aux, k, chunk);
     if (!d_assignments) VSP_TRY(pre.init());

@@ -170,17 +170,57 @@ def sum_partials(parts: np.ndarray, sum_g1: Callable[[np.ndarray], np.ndarray],
     return out
 
 
-class ShardedProver:
-    """Groth16 prover for one large circuit over all ranks of `group`: this rank loads its slice of the proving key,
-    proves its share, the shares meet in one all_gather of 72 limbs per rank, every rank assembles the proof."""
+def key_ranges(cs: dict, m: int, n_b: int, rank: int, world: int) -> dict:
+    """the contiguous range of each query rank `rank` holds (what slice_proving_key cuts)"""
+    nv, na = int(cs["num_inputs"]) + int(cs["num_aux"]), int(cs["num_aux"])
+    return {"A": shard_range(nv + 1, rank, world), "B": shard_range(n_b, rank, world),
+            "H": shard_range(m - 1, rank, world), "L": shard_range(na, rank, world)}
 
-    def __init__(self, vsp, ctx, arrays: dict, group=None):
+
+PARTIAL_LIMBS = 144  # raw XYZZ shares of vsp_prove_partial_dev: evA | evB1 | evH | evL (24 limbs each) | evB2 (48)
+
+
+class ShardedProver:
+    """Groth16 prover for one large circuit over all ranks of `group`: this rank loads its slice of the proving key and
+    proves its share; the shares meet in ONE all_gather, every rank sums them and assembles the proof.
+
+    prove()      host arrays in and out, canonical affine shares (72 limbs) over the host — the portable form the CPU
+                 tests drive over gloo;
+    prove_dev()  everything stays on the GPU: vsp_prove_partial_dev leaves 144 limbs of raw XYZZ shares in device memory,
+                 one all_gather_into_tensor (NCCL over NVLink) moves world x 1,152 bytes, vsp_prove_assemble_dev sums
+                 them and writes the proof to device memory.  No host round trip, nothing synchronises."""
+
+    def __init__(self, vsp, ctx, arrays: dict, group=None, sliced: bool = False, ranges: Optional[dict] = None):
+        """`arrays`: the whole proving key (cut here), or with sliced=True this rank's slice already (`ranges` as
+        key_ranges gives them) so that no rank ever has to hold the whole key."""
         self.vsp, self.ctx, self.group = vsp, ctx, group
         self.rank, self.world = _world(group)
         cs = arrays["cs"]
         _, self.m = vsp.domain_plan(int(cs["num_constraints"]) + int(cs["num_inputs"]) + 1)
-        sliced, self.ranges = slice_proving_key(arrays, self.m, self.rank, self.world)
-        self.pk = vsp.ProvingKey(ctx, sliced, slice=self.ranges)
+        if sliced:
+            self.ranges = ranges
+        else:
+            arrays, self.ranges = slice_proving_key(arrays, self.m, self.rank, self.world)
+        self.pk = vsp.ProvingKey(ctx, arrays, slice=self.ranges)
+        self._bufs = None
+
+    def prove_dev(self, d_assignment, r: int, s: int, pubkey=None, r_saver=None):
+        """d_assignment: torch int64 CUDA tensor holding (1 || primary || auxiliary) as canonical Fr limbs.  Returns the
+        proof as a torch int64 CUDA tensor of 48 limbs (valid in stream order on the context's stream)."""
+        import torch
+        if self._bufs is None:
+            dev = d_assignment.device
+            self._bufs = (torch.zeros(PARTIAL_LIMBS, dtype=torch.int64, device=dev),
+                          torch.zeros(self.world * PARTIAL_LIMBS, dtype=torch.int64, device=dev),
+                          torch.zeros(48, dtype=torch.int64, device=dev))
+        part, gathered, proof = self._bufs
+        self.pk.prove_partial_dev(d_assignment.data_ptr(), part.data_ptr())
+        if self.world > 1:
+            _dist().all_gather_into_tensor(gathered, part, group=self.group)
+        else:
+            gathered.copy_(part)
+        self.pk.prove_assemble_dev(self.world, gathered.data_ptr(), r, s, proof.data_ptr(), pubkey, r_saver)
+        return proof
 
     def prove(self, primary, auxiliary, r: int, s: int, pubkey=None, r_saver=None) -> np.ndarray:
         part = self.pk.prove_partial(primary, auxiliary)
