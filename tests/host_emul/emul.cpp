@@ -32,6 +32,7 @@ static void binop(int op, const uint64_t* a, const uint64_t* b, uint64_t* out) {
         case 4: r = fp_inv(x); break;
         case 5: r = fp_sqr(x); break;
         case 6: r = fp_inv_gcd(x); break;
+        case 7: r = fp_inv_safegcd(x); break;
         default: r = Fp<C>::zero();
     }
     st<C>(out, fp_from_mont(r));

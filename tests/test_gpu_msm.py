@@ -138,3 +138,53 @@ def test_g1_multiexp_one_hot_bucket_at_scale(vsp, ctx):
         acc = int((k * sc[:, 0].astype(object)).sum()) % o.R
         assert np.array_equal(h.multiexp(sc), cref.g1_mul(acc, G1_GEN_LIMBS))
     h.close()
+
+
+@pytest.mark.parametrize("affine", ["1", "0"])
+def test_both_accumulate_kernels_match_oracle(vsp, ctx, monkeypatch, affine):
+    """VSP_MSM_AFFINE forces the batched-affine bucket accumulation (1: shared division-step inversions, lanes walking
+    their task queues) or the XYZZ one (0) whatever the launch size; by default the device-resident task count picks.
+    Random G1 / G2 multiexps, the exceptional additions (the same base ten times, P and -P, infinite bases, a finite base
+    with x = 0), witness-like scalars and a 2^16-point checksum, each against the oracle."""
+    monkeypatch.setenv("VSP_MSM_AFFINE", affine)
+    for n in (1, 2, 17, 1000, (1 << 14) + 5):
+        bases, scalars = random_g1(n, seed=n + 11), fx.random_fr(n, seed=n + 12)
+        assert np.array_equal(vsp.multiexp(ctx, bases, scalars), cref.msm_g1(bases, scalars)), n
+    for n in (1, 9, 300, 1 << 10):
+        bases, scalars = random_g2(n, seed=n + 13), fx.random_fr(n, seed=n + 14)
+        assert np.array_equal(vsp.multiexp(ctx, bases, scalars), cref.msm_g2(bases, scalars)), n
+    n = 700
+    bases = random_g1(n, seed=81)
+    bases[10:20] = bases[10]
+    bases[31] = cref.g1_mul(o.R - 1, bases[30])
+    bases[40] = 0
+    bases[41] = cref.g1_to_limbs([(0, 2)])[0]   # on y^2 = x^3 + 4 with x = 0: finite, though all-zero x looks like infinity
+    bases[42] = cref.g1_to_limbs([(0, o.P - 2)])[0]
+    scalars = fx.random_fr(n, seed=82)
+    scalars[0:5] = 0
+    scalars[5:10] = _ones(5)
+    scalars[10:20] = scalars[10]
+    scalars[30] = scalars[31] = scalars[32]
+    scalars[41] = scalars[42] = scalars[43]     # (0, 2) and (0, -2) meet each other and a third point in every bucket
+    small = scalars.copy()
+    small[:, 1:] = 0
+    small[:, 0] &= np.uint64(3)                  # a handful of crowded buckets: long lane queues, many equal-point meetings
+    for sc in (scalars, small, _ones(n)):
+        assert np.array_equal(vsp.multiexp(ctx, bases, sc), cref.msm_g1(bases, sc))
+        h = vsp.G1Bases(ctx, bases)              # the window-table path over the same inputs
+        assert np.array_equal(h.multiexp(sc), cref.msm_g1(bases, sc))
+        h.close()
+    g2 = random_g2(64, seed=83)
+    g2[3:9] = g2[3]
+    g2[20] = 0
+    s2 = fx.random_fr(64, seed=84)
+    s2[3:9] = s2[3]
+    assert np.array_equal(vsp.multiexp(ctx, g2, s2), cref.msm_g2(g2, s2))
+    nb = 1 << 15
+    bases, scalars = random_g1(nb, seed=5), fx.witness_like_fr(nb, seed=6)
+    assert np.array_equal(vsp.multiexp(ctx, bases, scalars), cref.msm_g1(bases, scalars, mixed=True))
+    n, seed = 1 << 16, 4321
+    h = vsp.G1Bases.generate(ctx, n, seed)
+    scalars = fx.random_fr(n, seed=3)
+    assert np.array_equal(h.multiexp(scalars), expected_generated_msm(n, seed, scalars))
+    h.close()

@@ -288,3 +288,31 @@ def test_long_constraint_rows_and_table_less_key(vsp, ctx, monkeypatch):
         assert np.array_equal(pk.witness_map(primary, aux), want_h)
         assert np.array_equal(pk.prove(primary, aux, r, s), want)
         pk.close()
+
+
+@pytest.mark.parametrize("affine", ["1", "0"])
+def test_batch_proofs_under_either_accumulate_kernel(vsp, ctx, monkeypatch, affine):
+    """a 9-ballot encrypt batch with the bucket accumulation forced onto the batched-affine kernel and onto the XYZZ one"""
+    monkeypatch.setenv("VSP_MSM_AFFINE", affine)
+    nc, ni, msg_size, k = 1000, 30, 25, 9
+    cs, _, _ = synthetic_r1cs(nc, ni, 0, binary=False)
+    arr = synthetic_pk_arrays(cs, 71)
+    pub_arr, gamma_abc_rest = synthetic_saver_pub(msg_size, seed=72)
+    gamma_abc_rest = np.ascontiguousarray(gamma_abc_rest[:msg_size])
+    pub = vsp.SaverPublicKey(pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    opk = _oracle_pk(arr)
+    key = pub.resident(ctx, gamma_abc_rest)
+    rng = random.Random(73)
+    prim, aux, rs = [], [], []
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=b, binary=False)
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4))
+    _cts, proofs = pk.encrypt_batch(key, np.stack(prim), np.stack(aux), np.stack(rs))
+    for b in (0, 4, 8):
+        r, s, rsv = cref.limbs_to_ints(rs[b])
+        assert np.array_equal(proofs[b], cref.groth16_prove(opk, prim[b], aux[b], r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"])), b
+    key.close()
+    pk.close()

@@ -32,8 +32,9 @@ def test_field_ops(emul, name, mod, limbs):
     for i, (a, b) in enumerate(pairs):
         A, B, O = ints_to_limbs([a], limbs), ints_to_limbs([b], limbs), np.zeros((1, limbs), np.uint64)
         want = [a * b % mod, (a + b) % mod, (a - b) % mod, (-a) % mod, pow(a, mod - 2, mod), a * a % mod,
-                pow(a, mod - 2, mod)]  # op 6: the binary-Euclid inverse (fp_inv_gcd), every pair
-        for op in range(7):
+                pow(a, mod - 2, mod),  # op 6: the binary-Euclid inverse (fp_inv_gcd), every pair
+                pow(a, mod - 2, mod)]  # op 7: the constant-time division-step inverse (fp_inv_safegcd), every pair
+        for op in range(8):
             if op == 4 and i % 40:
                 continue
             fn(op, P(A), P(B), P(O))
@@ -93,3 +94,20 @@ def test_curve_ops(emul, grp):
             want = {0: cv.add(ja, jb), 1: cv.add(ja, jb), 2: cv.dbl(ja), 3: cv.mul(k, ja), 4: cv.dbl(ja)}[op]
             want = None if cv.is_inf(want) else cv.to_affine(want)
             assert fl(O)[0] == want, (grp, op)
+
+
+@pytest.mark.parametrize("name,mod,limbs", [("fr", o.R, 4), ("fq", o.P, 6)])
+def test_division_step_inverse_stress(emul, name, mod, limbs):
+    """fp_inv_safegcd (the inverse shared by a batch of affine bucket additions): powers of two, values next to 0 and p,
+    sparse and dense bit patterns, and a few thousand random elements, against pow(a, -1, p)"""
+    fn = getattr(emul, "emul_%s_op" % name)
+    rng = random.Random(99 + limbs)
+    vals = [pow(2, k, mod) for k in range(0, 64 * limbs + 3, 7)] + [mod - pow(2, k, mod) for k in range(0, 64 * limbs, 29)]
+    vals += [(1 << k) - 1 for k in range(1, 64 * limbs - 3, 31)] + [rng.getrandbits(rng.randrange(1, 64 * limbs)) % mod for _ in range(500)]
+    vals += [rng.randrange(mod) for _ in range(2500)]
+    A, O = np.zeros((1, limbs), np.uint64), np.zeros((1, limbs), np.uint64)
+    for a in vals:
+        a %= mod
+        A[:] = ints_to_limbs([a], limbs)
+        fn(7, P(A), P(A), P(O))
+        assert limbs_to_ints(O)[0] == (pow(a, -1, mod) if a else 0), hex(a)

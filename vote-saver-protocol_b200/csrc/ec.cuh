@@ -25,8 +25,11 @@ struct FqOps {
     VSP_DEV static T dbl(const T& a) { return fp_dbl(a); }
     VSP_DEV static bool is_zero(const T& a) { return a.is_zero(); }
     VSP_DEV static bool eq(const T& a, const T& b) { return a == b; }
-    static __device__ __noinline__ T inv(const T& a) { return fp_inv(a); }
+    // the constant-time division-step inverse (fp.cuh): ~30x fewer multiplies than the power a^(p-2), same result
+    static __device__ __noinline__ T inv(const T& a) { return fp_inv_safegcd(a); }
     static __device__ __noinline__ T inv_lowlat(const T& a) { return fp_inv_gcd(a); }
+    // constant-time division-step inverse: ~30x fewer multiplies than the power, no divergence between lanes
+    VSP_DEV static T inv_fast(const T& a) { return fp_inv_safegcd(a); }
     VSP_DEV static T to_mont(const T& a) { return fp_to_mont(a); }
     VSP_DEV static T from_mont(const T& a) { return fp_from_mont(a); }
     VSP_DEV static T load(const void* p) { return fp_load<FqCfg>(p); }
@@ -61,11 +64,15 @@ struct Fq2Ops {
     VSP_DEV static bool is_zero(const T& a) { return a.c0.is_zero() && a.c1.is_zero(); }
     VSP_DEV static bool eq(const T& a, const T& b) { return a.c0 == b.c0 && a.c1 == b.c1; }
     static __device__ __noinline__ T inv(const T& a) {
-        Fq n = fp_inv(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
+        Fq n = fp_inv_safegcd(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
         return T{fp_mul(a.c0, n), fp_neg(fp_mul(a.c1, n))};
     }
     static __device__ __noinline__ T inv_lowlat(const T& a) {
         Fq n = fp_inv_gcd(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
+        return T{fp_mul(a.c0, n), fp_neg(fp_mul(a.c1, n))};
+    }
+    static __device__ __noinline__ T inv_fast(const T& a) {
+        Fq n = fp_inv_safegcd(fp_add(fp_sqr(a.c0), fp_sqr(a.c1)));
         return T{fp_mul(a.c0, n), fp_neg(fp_mul(a.c1, n))};
     }
     VSP_DEV static T to_mont(const T& a) { return T{fp_to_mont(a.c0), fp_to_mont(a.c1)}; }
@@ -173,6 +180,34 @@ VSP_DEV void ec_madd(XYZZ<F>& acc, const Affine<F>& q) {
     acc.Y = Y3;
     acc.ZZ = F::mul(acc.ZZ, PP);
     acc.ZZZ = F::mul(acc.ZZZ, PPP);
+}
+
+// ---------------------------------------------------------------------------------------------
+// affine additions on a shared inversion (the bucket accumulation of msm_impl.cuh)
+//   P + Q, P != +-Q:  lambda = (y2 - y1) / (x2 - x1);  x3 = lambda^2 - x1 - x2;  y3 = lambda (x1 - x3) - y1
+// With 1 / (x2 - x1) supplied, that is 2 products + 1 square; Montgomery's trick supplies it for 3 more products per
+// addition and one inversion per batch: 5M + 1S against the 8M + 2S of the XYZZ mixed addition.
+// ---------------------------------------------------------------------------------------------
+template <class F>
+VSP_DEV void ec_affine_add_with_inverse(typename F::T& x1, typename F::T& y1, const typename F::T& x2, const typename F::T& y2,
+                                        const typename F::T& dinv) {
+    using E = typename F::T;
+    const E lam = F::mul(F::sub(y2, y1), dinv);
+    const E x3 = F::sub(F::sub(F::sqr(lam), x1), x2);
+    y1 = F::sub(F::mul(lam, F::sub(x1, x3)), y1);
+    x1 = x3;
+}
+// 2 P in affine coordinates with its own inversion (the rare "same point twice in one bucket" case); false: 2 P = O
+template <class F>
+__device__ __noinline__ bool ec_affine_dbl(typename F::T& x, typename F::T& y) {
+    using E = typename F::T;
+    if (F::is_zero(y)) return false;
+    const E xx = F::sqr(x);
+    const E lam = F::mul(F::add(F::dbl(xx), xx), F::inv_fast(F::dbl(y)));
+    const E x3 = F::sub(F::sqr(lam), F::dbl(x));
+    y = F::sub(F::mul(lam, F::sub(x, x3)), y);
+    x = x3;
+    return true;
 }
 
 // dbl-2008-s-1, a = 0   (not inlined: only the cold reduction kernels use it, and sharing one copy keeps ptxas fast)

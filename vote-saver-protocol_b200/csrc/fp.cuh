@@ -534,6 +534,168 @@ Fp<C> fp_inv_gcd(const Fp<C>& a) {
     return fp_mul(r, fp_mul(r2, r2));
 }
 
+// The inverse by Bernstein-Yang division steps ("safegcd", eprint 2019/266), constant time: the same instruction stream
+// for every input, so the 32 lanes of a warp invert 32 different values in lock step.  Layout after libsecp256k1's
+// modinv32 (signed 30-bit limbs; 30 division steps at a time on the low words, collected in a 2x2 transition matrix that
+// is then applied to the full-width f, g and — modulo p — to d, e).  Number of steps: the paper's bound for the delta = 1
+// start, floor((49 d + 57) / 17) for a d-bit modulus (d >= 46): 1,101 for Fq, 746 for Fr; groups of 30.
+// Cost for Fq: 37 groups x (130 signed 32x32->64 products + ~700 plain integer instructions) — about 4.8k heavy-pipe
+// multiplies against ~146k for the Fermat power, which is what makes a shared inversion per few dozen affine additions
+// pay (msm_impl.cuh).  In: a R (Montgomery form); out: a^-1 R; 0 -> 0.
+namespace safegcd {
+constexpr int32_t M30 = 0x3fffffff;
+struct Trans {
+    int32_t u, v, q, r;
+};
+// 30 division steps on the low 30+ bits; eta = -delta
+VSP_DEV int32_t divsteps_30(int32_t eta, uint32_t f0, uint32_t g0, Trans& t) {
+    uint32_t u = 1, v = 0, q = 0, r = 1, f = f0, g = g0;
+#pragma unroll 6
+    for (int i = 0; i < 30; ++i) {
+        uint32_t c1 = (uint32_t)(eta >> 31);  // delta > 0
+        const uint32_t c2 = 0u - (g & 1u);    // g odd
+        const uint32_t x = (f ^ c1) - c1, y = (u ^ c1) - c1, z = (v ^ c1) - c1;
+        g += x & c2;
+        q += y & c2;
+        r += z & c2;
+        c1 &= c2;
+        eta = (int32_t)(((uint32_t)eta ^ c1) - (c1 + 1u));
+        f += g & c1;
+        u += q & c1;
+        v += r & c1;
+        g >>= 1;
+        u <<= 1;
+        v <<= 1;
+    }
+    t.u = (int32_t)u;
+    t.v = (int32_t)v;
+    t.q = (int32_t)q;
+    t.r = (int32_t)r;
+    return eta;
+}
+// limb j (30 bits) of the modulus
+template <class C>
+__host__ __device__ constexpr uint32_t mod30(int j) {
+    return (uint32_t)(((((30 * j) / 32 + 1 < C::N ? (uint64_t)C::mod((30 * j) / 32 + 1) : 0ull) << 32 |
+                        ((30 * j) / 32 < C::N ? (uint64_t)C::mod((30 * j) / 32) : 0ull)) >>
+                       ((30 * j) % 32)) &
+                      0x3fffffffull);
+}
+}  // namespace safegcd
+
+template <class C>
+#ifdef __CUDACC__
+__device__ __noinline__
+#else
+inline
+#endif
+Fp<C> fp_inv_safegcd(const Fp<C>& a) {
+    using namespace safegcd;
+    constexpr int N = C::N;
+    constexpr int L = (32 * N + 29) / 30 + ((32 * N) % 30 == 0 ? 1 : 0);  // 30-bit limbs, at least 2 spare bits: Fq 13, Fr 9
+    static_assert(30 * L >= 32 * N + 2, "headroom for values in (-2p, p)");
+    constexpr int BITS = 32 * N - (C::mod(N - 1) >> 31 ? 0 : (C::mod(N - 1) >> 30 ? 1 : (C::mod(N - 1) >> 29 ? 2 : 3)));
+    static_assert((C::mod(N - 1) >> 28) != 0, "modulus top limb expected to have at least 29 bits");
+    constexpr int STEPS = (49 * BITS + 57) / 17;
+    constexpr int GROUPS = (STEPS + 29) / 30;
+    constexpr uint32_t PINV30 = (0u - C::INV) & 0x3fffffffu;  // p^-1 mod 2^30 (C::INV = -p^-1 mod 2^32)
+    int32_t d[L], e[L], f[L], g[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+        const int k = (30 * j) / 32, s = (30 * j) % 32;
+        const uint64_t two = ((k + 1 < N ? (uint64_t)a.l[k + 1] : 0ull) << 32) | (k < N ? (uint64_t)a.l[k] : 0ull);
+        g[j] = (int32_t)((two >> s) & 0x3fffffffull);
+        f[j] = (int32_t)mod30<C>(j);
+        d[j] = 0;
+        e[j] = j == 0 ? 1 : 0;
+    }
+    int32_t eta = -1;
+#pragma unroll 1
+    for (int it = 0; it < GROUPS; ++it) {
+        Trans t;
+        eta = divsteps_30(eta, (uint32_t)f[0], (uint32_t)g[0], t);
+        // [d, e] <- t [d, e] / 2^30 mod p, both kept in (-2p, p)
+        {
+            const int32_t sd = d[L - 1] >> 31, se = e[L - 1] >> 31;
+            int32_t md = (t.u & sd) + (t.v & se), me = (t.q & sd) + (t.r & se);
+            int64_t cd = (int64_t)t.u * d[0] + (int64_t)t.v * e[0];
+            int64_t ce = (int64_t)t.q * d[0] + (int64_t)t.r * e[0];
+            md -= (int32_t)((PINV30 * (uint32_t)cd + (uint32_t)md) & (uint32_t)M30);
+            me -= (int32_t)((PINV30 * (uint32_t)ce + (uint32_t)me) & (uint32_t)M30);
+            cd += (int64_t)(int32_t)mod30<C>(0) * md;
+            ce += (int64_t)(int32_t)mod30<C>(0) * me;
+            cd >>= 30;
+            ce >>= 30;
+#pragma unroll
+            for (int j = 1; j < L; ++j) {
+                cd += (int64_t)t.u * d[j] + (int64_t)t.v * e[j];
+                ce += (int64_t)t.q * d[j] + (int64_t)t.r * e[j];
+                cd += (int64_t)(int32_t)mod30<C>(j) * md;
+                ce += (int64_t)(int32_t)mod30<C>(j) * me;
+                d[j - 1] = (int32_t)cd & M30;
+                e[j - 1] = (int32_t)ce & M30;
+                cd >>= 30;
+                ce >>= 30;
+            }
+            d[L - 1] = (int32_t)cd;
+            e[L - 1] = (int32_t)ce;
+        }
+        // [f, g] <- t [f, g] / 2^30 (exact)
+        {
+            int64_t cf = (int64_t)t.u * f[0] + (int64_t)t.v * g[0];
+            int64_t cg = (int64_t)t.q * f[0] + (int64_t)t.r * g[0];
+            cf >>= 30;
+            cg >>= 30;
+#pragma unroll
+            for (int j = 1; j < L; ++j) {
+                cf += (int64_t)t.u * f[j] + (int64_t)t.v * g[j];
+                cg += (int64_t)t.q * f[j] + (int64_t)t.r * g[j];
+                f[j - 1] = (int32_t)cf & M30;
+                g[j - 1] = (int32_t)cg & M30;
+                cf >>= 30;
+                cg >>= 30;
+            }
+            f[L - 1] = (int32_t)cf;
+            g[L - 1] = (int32_t)cg;
+        }
+    }
+    // g = 0 and f = +-1 now: d = +-(a R)^-1.  Bring d from (-2p, p) into [0, p), negating if f = -1.
+    {
+        int32_t cond = d[L - 1] >> 31;
+#pragma unroll
+        for (int j = 0; j < L; ++j) d[j] += (int32_t)mod30<C>(j) & cond;
+        cond = f[L - 1] >> 31;
+#pragma unroll
+        for (int j = 0; j < L; ++j) d[j] = (d[j] ^ cond) - cond;
+#pragma unroll
+        for (int j = 0; j < L - 1; ++j) {
+            d[j + 1] += d[j] >> 30;
+            d[j] &= M30;
+        }
+        cond = d[L - 1] >> 31;
+#pragma unroll
+        for (int j = 0; j < L; ++j) d[j] += (int32_t)mod30<C>(j) & cond;
+#pragma unroll
+        for (int j = 0; j < L - 1; ++j) {
+            d[j + 1] += d[j] >> 30;
+            d[j] &= M30;
+        }
+    }
+    Fp<C> r;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        // bits [32 k, 32 k + 32) out of the 30-bit limbs
+        const int j = (32 * k) / 30, s = (32 * k) % 30;
+        uint64_t w = (uint64_t)(uint32_t)d[j] >> s;
+        if (j + 1 < L) w |= (uint64_t)(uint32_t)d[j + 1] << (30 - s);
+        if (j + 2 < L && 60 - s < 32) w |= (uint64_t)(uint32_t)d[j + 2] << (60 - s);
+        r.l[k] = (uint32_t)w;
+    }
+    // r = (a R)^-1 = a^-1 R^-1; one Montgomery product with R^3 puts it back in Montgomery form
+    const Fp<C> r2 = Fp<C>::r2();
+    return fp_mul(r, fp_mul(r2, r2));
+}
+
 using Fq = Fp<FqCfg>;
 using Fr = Fp<FrCfg>;
 

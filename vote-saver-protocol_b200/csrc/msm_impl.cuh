@@ -376,14 +376,24 @@ __global__ void __launch_bounds__(256) k_task_order(const Task* __restrict__ tas
 // ---------------------------------------------------------------------------------------------
 // 4. accumulate
 // ---------------------------------------------------------------------------------------------
+// lanes per thread of the batched-affine kernel (each lane keeps an affine accumulator and a prefix product in local
+// memory: 144 B in G1, 288 B in G2)
+template <class F>
+struct AffineLanes {
+    static constexpr int K = std::is_same<F, FqOps>::value ? 16 : 8;
+};
+
 template <class F>
 __global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restrict__ table, const uint32_t* __restrict__ sorted,
                                                         const Task* __restrict__ tasks,
                                                         const uint32_t* __restrict__ order,
-                                                        const uint32_t* __restrict__ n_tasks_ptr,
+                                                        const uint32_t* __restrict__ n_tasks_ptr, uint32_t max_tasks,
                                                         uint32_t* __restrict__ partial) {
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= *n_tasks_ptr) return;  // exact task count is device-resident (task_off[buckets]): no host round trip
+    // exact task count is device-resident (task_off[buckets]): no host round trip.  From max_tasks up the launch belongs
+    // to k_msm_accumulate_affine.
+    const uint32_t n_tasks = *n_tasks_ptr;
+    if (tid >= n_tasks || n_tasks >= max_tasks) return;
     const uint32_t t = order[tid];
     const Task k = tasks[t];
     XYZZ<F> acc = XYZZ<F>::inf();
@@ -395,6 +405,157 @@ __global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restri
         ec_madd<F>(acc, pt);
     }
     acc.store(partial + uint64_t(t) * (XYZZ<F>::BYTES / 4));
+}
+
+// The same sums in AFFINE coordinates on shared inversions (large launches: the H_query multiexp of a chunk of ballots,
+// any multiexp over uniform scalars).  A thread owns K lanes; a lane sums one task at a time, point after point, and
+// moves on to its next task when one is done.  In every step the thread performs one addition in each of its K lanes
+// and all K share ONE field inversion (Montgomery's trick), which the constant-time division-step inverse makes cheap
+// enough (ec.cuh: 5M + 1S + 1/K inversion per addition against the XYZZ mixed addition's 8M + 2S).
+//   lane g = thread * K + k takes tasks order[g], order[g + lanes], order[g + 2 lanes], ...: `order` lists the tasks by
+//   decreasing length, so the K lanes of a thread and the 32 threads of a warp always hold tasks of (nearly) the same
+//   length, and every lane's total is one task from each stratum of the length distribution — the lanes finish together.
+// Results land in partial[task] as XYZZ with ZZ = ZZZ = 1, so the collapse / reduction kernels do not care which kernel
+// produced them.  Exceptional additions (P + P, P - P, an infinite base) take a divergent slow path; they do not occur
+// for independent bases and only cost time in crafted inputs.
+// one shared copy of the product / square for the affine kernel: its loop bodies are then a few hundred instructions of
+// glue around calls instead of five inlined 6 KB multiplications, which is what the instruction cache wants
+template <class F>
+struct Shared {
+    using E = typename F::T;
+    static __device__ __noinline__ E mul(const E& a, const E& b) { return F::mul(a, b); }
+    static __device__ __noinline__ E sqr(const E& a) { return F::sqr(a); }
+};
+template <class F>
+VSP_DEV void affine_add_shared(typename F::T& x1, typename F::T& y1, const typename F::T& x2, const typename F::T& y2,
+                               const typename F::T& dinv) {
+    using E = typename F::T;
+    const E lam = Shared<F>::mul(F::sub(y2, y1), dinv);
+    const E x3 = F::sub(F::sub(Shared<F>::sqr(lam), x1), x2);
+    y1 = F::sub(Shared<F>::mul(lam, F::sub(x1, x3)), y1);
+    x1 = x3;
+}
+
+template <class F, int K>
+__global__ void __launch_bounds__(128, 4) k_msm_accumulate_affine(const uint32_t* __restrict__ table,
+                                                               const uint32_t* __restrict__ sorted,
+                                                               const Task* __restrict__ tasks,
+                                                               const uint32_t* __restrict__ order,
+                                                               const uint32_t* __restrict__ n_tasks_ptr, uint32_t min_tasks,
+                                                               uint32_t* __restrict__ partial) {
+    using E = typename F::T;
+    constexpr int PT_LIMBS = Affine<F>::BYTES / 4, XL = XYZZ<F>::BYTES / 4;
+    const uint32_t n_tasks = *n_tasks_ptr;
+    if (n_tasks < min_tasks) return;  // a small launch: k_msm_accumulate does it
+    const uint32_t lanes = gridDim.x * blockDim.x * K;
+    const uint32_t lane0 = (blockIdx.x * blockDim.x + threadIdx.x) * K;
+    if (lane0 >= n_tasks) return;
+    E ax[K], ay[K], pref[K];
+    uint32_t t_next[K], t_cur[K], pos[K], end[K];
+    uint32_t live = 0;  // bit k: lane k's accumulator holds a point (clear: the point at infinity)
+    uint32_t busy = 0;  // bit k: lane k has a current task
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) {
+        t_next[k] = lane0 + k;
+        pos[k] = end[k] = 0;
+        t_cur[k] = 0;
+    }
+    const E one = F::one();
+    for (;;) {
+        // ---- lanes whose task is done store it and open their next one
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            const uint32_t bit = 1u << k;
+            if (pos[k] != end[k]) continue;
+            if (busy & bit) {
+                XYZZ<F> r = (live & bit) ? XYZZ<F>{ax[k], ay[k], one, one} : XYZZ<F>::inf();
+                r.store(partial + uint64_t(t_cur[k]) * XL);
+                busy &= ~bit;
+            }
+            if (t_next[k] < n_tasks) {
+                const uint32_t t = order[t_next[k]];
+                t_next[k] += lanes;
+                const Task tk = tasks[t];
+                t_cur[k] = t;
+                pos[k] = tk.begin;
+                end[k] = tk.end;
+                busy |= bit;
+                live &= ~bit;
+                if (pos[k] < end[k]) {  // the task's first point opens the accumulator
+                    const uint32_t v = sorted[pos[k]++];
+                    Affine<F> pt = Affine<F>::load(table + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
+                    if (!pt.is_inf()) {
+                        if (v & 0x80000000u) pt.y = F::neg(pt.y);
+                        ax[k] = pt.x;
+                        ay[k] = pt.y;
+                        live |= bit;
+                    }
+                }
+            }
+        }
+        if (!busy) break;  // every lane has stored its last task
+        // ---- phase A: every lane's denominator x2 - x1 (1 where the lane has no ordinary addition this step) and the
+        // running products; the gather of lane k + 1 is issued before the product of lane k
+        E run = one;
+        uint32_t adds = 0;
+        auto denominator = [&](int k) -> E {
+            E d = one;
+            if (pos[k] < end[k] && (live & (1u << k))) {
+                const uint32_t v = sorted[pos[k]];
+                const E px = F::load(table + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
+                d = F::sub(px, ax[k]);
+                // x2 == x1 (P + P or P - P), or x2 = 0 (an all-zero base is the point at infinity): slow path in phase B
+                if (F::is_zero(d) || F::is_zero(px)) d = one;
+            }
+            return d;
+        };
+        E d_next = denominator(0);
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            const E d = d_next;
+            if (k + 1 < K) d_next = denominator(k + 1);
+            adds |= (pos[k] < end[k]) ? 1u : 0u;
+            pref[k] = run;
+            run = Shared<F>::mul(run, d);
+        }
+        if (!adds) continue;  // only single-point tasks were opened: nothing to add, go store them
+        E inv = F::inv_fast(run);
+        // ---- phase B, lanes in reverse: 1 / d_k = inv * pref_k, then inv *= d_k
+#pragma unroll 1
+        for (int k = K - 1; k >= 0; --k) {
+            const uint32_t bit = 1u << k;
+            if (pos[k] >= end[k]) continue;
+            const uint32_t v = sorted[pos[k]++];
+            Affine<F> pt = Affine<F>::load(table + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
+            if (v & 0x80000000u) pt.y = F::neg(pt.y);
+            if (!(live & bit)) {  // accumulator at infinity: the point replaces it (its d was 1)
+                if (!pt.is_inf()) {
+                    ax[k] = pt.x;
+                    ay[k] = pt.y;
+                    live |= bit;
+                }
+                continue;
+            }
+            const E d = F::sub(pt.x, ax[k]);
+            if (F::is_zero(d) || F::is_zero(pt.x)) {  // d was 1 in phase A
+                if (pt.is_inf()) continue;
+                if (F::is_zero(d)) {
+                    if (F::eq(pt.y, ay[k])) {
+                        if (!ec_affine_dbl<F>(ax[k], ay[k])) live &= ~bit;
+                    } else {
+                        live &= ~bit;  // P - P
+                    }
+                } else {  // a finite point with x = 0: one addition on its own inversion
+                    const E dinv = F::inv_fast(d);
+                    ec_affine_add_with_inverse<F>(ax[k], ay[k], pt.x, pt.y, dinv);
+                }
+                continue;
+            }
+            const E dinv = Shared<F>::mul(inv, pref[k]);
+            inv = Shared<F>::mul(inv, d);
+            affine_add_shared<F>(ax[k], ay[k], pt.x, pt.y, dinv);
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -793,12 +954,35 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_task_bin_offsets, 1, 32, 0, s, bins.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_SORT, k_task_order, order_blocks, 256, 0, s, tasks.as<Task>(), d_n_tasks, bins.as<uint32_t>(),
                  order.as<uint32_t>());
+    // Two kernels can do the accumulation.  The XYZZ one (a thread per task) is the default.  VSP_MSM_AFFINE=1 hands every
+    // launch to the batched-affine kernel instead, VSP_MSM_AFFINE=auto only launches with enough tasks to fill the GPU
+    // (the device-resident task count decides; the other kernel's threads exit at once).  Measured on B200 the affine
+    // kernel issues 29 % fewer heavy-pipe multiplies per addition but runs 1.6x SLOWER (a 256-ballot step's G1 accumulation
+    // 175 ms against 110 ms): its per-lane state lives in local memory, misses L1 (8.7 % hit rate, 600 B of DRAM traffic
+    // per addition) and leaves the warps waiting on loads and on the serial division-step chain.  Kept for that evidence
+    // and as a starting point (profiles/r02_ncu_affine_accumulate.txt); results are bit-identical either way.
+    constexpr int AK = AffineLanes<F>::K;
+    uint32_t affine_min = 0xffffffffu;
+    unsigned affine_blocks = 0;
+    if (const char* e = getenv("VSP_MSM_AFFINE")) {
+        if (e[0] == '1' || e[0] == 'a') {
+            int per_sm = 0;
+            VSP_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_msm_accumulate_affine<F, AK>, 128, 0));
+            const uint64_t resident_threads = uint64_t(ctx->sm_count) * std::max(per_sm, 1) * 128;
+            affine_min = e[0] == '1' ? 1u : (uint32_t)std::min<uint64_t>(resident_threads * AK / 2, 0xfffffffeull);
+            affine_blocks = (unsigned)std::min<uint64_t>((max_tasks + uint64_t(AK) * 128 - 1) / (uint64_t(AK) * 128),
+                                                         resident_threads / 128);
+        }
+    }
     VSP_LAUNCH_K(ctx, KC_ACC, k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
-                 sorted.as<uint32_t>(), tasks.as<Task>(), order.as<uint32_t>(), d_n_tasks, partial.as<uint32_t>());
+                 sorted.as<uint32_t>(), tasks.as<Task>(), order.as<uint32_t>(), d_n_tasks, affine_min, partial.as<uint32_t>());
     // algorithmic work of this launch for the live roofline: bucket additions scheduled (= non-zero digits,
     // offsets[buckets]) x 11 field multiplications (the reference's mixed Jacobian add) x I_mul(limbs)
     kprof_units(ctx, ctx->last_prof, 11.0 * (std::is_same<F, FqOps>::value ? 300.0 : 3.0 * 300.0),
                 offsets.as<uint32_t>() + p.buckets, s);
+    if (affine_blocks)
+        VSP_LAUNCH_K(ctx, KC_ACC, (k_msm_accumulate_affine<F, AK>), affine_blocks, 128, 0, s, bases.d_pts, sorted.as<uint32_t>(),
+                     tasks.as<Task>(), order.as<uint32_t>(), d_n_tasks, affine_min, partial.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_light<F>, (unsigned)((p.buckets + 63) / 64), 64, 0, s,
                  task_off.as<uint32_t>(), p.buckets, partial.as<uint32_t>());
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, dim3(256, COLLAPSE_SLICES), COLLAPSE_THREADS,

@@ -688,7 +688,7 @@ __global__ void k_step_div_table(uint32_t* out, uint64_t n, PowTable elt_pows, F
         fp_store(out + 8 * (base + i), run);  // prefix products, overwritten below
         e = fp_mul(e, step);
     }
-    Fr inv = fp_inv(run);
+    Fr inv = fp_inv_safegcd(run);
     for (int i = cnt - 1; i >= 0; --i) {
         Fr prev = (i > 0) ? fp_load<FrCfg>(out + 8 * (base + i - 1)) : Fr::one();
         fp_store(out + 8 * (base + i), fp_mul(inv, prev));
