@@ -254,6 +254,17 @@ VSP_API int vsp_saver_encrypt_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, const vs
 /* rnd = r | z1 | z2 */
 VSP_API int vsp_saver_rerandomize(vsp_ctx *ctx, const vsp_saver_pubkey_t *pub, const uint64_t *delta_g2, const uint64_t *rnd,
                           const uint64_t *ct_in, const uint64_t *proof_in, uint64_t *ct_out, uint64_t *proof_out);
+/* rerandomize_op<elgamal_verifiable>::process for k ballots in one call (the second half of the reference's timed vote
+ * phase, bin/cli/include/nil/vote_saver/common.hpp:1132-1145): rnd = k x (r | z1 | z2); cts k x (msg_size + 2) G1;
+ * proofs k x 48 limbs.  Key material comes from the resident handles (pk: delta_g2 and gamma_inverse_sum_s_g1 tables; sp:
+ * delta, delta_s, delta_sum_s tables), so every multiple of it is fixed-base.  The _dev variant takes and leaves the
+ * cipher texts and proofs on the device (in and out may alias), e.g. chained after vsp_saver_encrypt_batch_dev. */
+VSP_API int vsp_saver_rerandomize_batch(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pub *sp, uint64_t k,
+                                        const uint64_t *rnd, const uint64_t *cts_in, const uint64_t *proofs_in,
+                                        uint64_t *cts_out, uint64_t *proofs_out);
+VSP_API int vsp_saver_rerandomize_batch_dev(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pub *sp, uint64_t k,
+                                            const uint64_t *rnd, const uint64_t *d_cts_in, const uint64_t *d_proofs_in,
+                                            uint64_t *d_cts_out, uint64_t *d_proofs_out);
 
 /* ---- key generation: the callers that produce the keys the path consumes ------------------ */
 /* zk::generate<r1cs_gg_ppzksnark<bls12<381>, ..., proving_mode::encrypted_input>>(constraint_system)

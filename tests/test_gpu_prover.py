@@ -316,3 +316,54 @@ def test_batch_proofs_under_either_accumulate_kernel(vsp, ctx, monkeypatch, affi
         assert np.array_equal(proofs[b], cref.groth16_prove(opk, prim[b], aux[b], r, s, rsv, pub_arr["gamma_inverse_sum_s_g1"])), b
     key.close()
     pk.close()
+
+
+def test_rerandomize_batch_matches_oracle(vsp, ctx):
+    """vsp_saver_rerandomize_batch[_dev] (rerandomize_op::process, elgamal_verifiable.hpp:632-667, for k ballots): every
+    cipher text and proof equal to the oracle's per-ballot restatement and to the one-ballot entry point; the device-
+    resident variant in place on the outputs of encrypt_batch_dev"""
+    import torch
+    nc, ni, msg_size, k = 97, 30, 25, 6
+    cs, _, _ = synthetic_r1cs(nc, ni, 0, binary=True)
+    arr = synthetic_pk_arrays(cs, 81)
+    pub_arr, gamma_abc_rest = synthetic_saver_pub(msg_size, seed=82)
+    gamma_abc_rest = np.ascontiguousarray(gamma_abc_rest[:msg_size])
+    pub = vsp.SaverPublicKey(pub_arr)
+    opub = fx.fill_struct(cref.SaverPubkeyDesc(), pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    key = pub.resident(ctx, gamma_abc_rest)
+    rng = random.Random(83)
+    prim, aux, rs = [], [], []
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=200 + b, binary=True)
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4))
+    prim, aux, rs = np.stack(prim), np.stack(aux), np.stack(rs)
+    cts, proofs = pk.encrypt_batch(key, prim, aux, rs)
+    rnd = np.stack([cref.ints_to_limbs([rng.randrange(1, o.R) for _ in range(3)], 4) for _ in range(k)])
+    cts2, proofs2 = pk.rerandomize_batch(key, rnd, cts, proofs)
+    for b in range(k):
+        want_ct, want_pr = cref.saver_rerandomize(opub, arr["delta_g2"], cref.limbs_to_ints(rnd[b]), cts[b], proofs[b])
+        assert np.array_equal(cts2[b], want_ct) and np.array_equal(proofs2[b], want_pr), b
+    one_ct, one_pr = vsp.rerandomize(ctx, pub, arr["delta_g2"], cref.limbs_to_ints(rnd[2]), cts[2], proofs[2])
+    assert np.array_equal(one_ct, cts2[2]) and np.array_equal(one_pr, proofs2[2])
+    # device-resident, in place
+    assign = np.zeros((k, cs.num_variables + 1, 4), dtype=np.uint64)
+    assign[:, 0, 0] = 1
+    assign[:, 1:ni + 1] = prim
+    assign[:, ni + 1:] = aux
+    d_assign = torch.from_numpy(assign.view(np.int64)).cuda()
+    d_proofs = torch.zeros((k, 48), dtype=torch.int64, device="cuda")
+    d_cts = torch.zeros((k, msg_size + 2, 12), dtype=torch.int64, device="cuda")
+    pk.encrypt_batch_dev(key, k, d_assign.data_ptr(), rs, d_cts.data_ptr(), d_proofs.data_ptr())
+    pk.rerandomize_batch_dev(key, k, rnd, d_cts.data_ptr(), d_proofs.data_ptr())
+    ctx.synchronize()
+    assert np.array_equal(d_cts.cpu().numpy().view(np.uint64), cts2)
+    assert np.array_equal(d_proofs.cpu().numpy().view(np.uint64), proofs2)
+    bad = rnd.copy()
+    bad[1, 1] = 0  # z1 = 0 has no inverse
+    with pytest.raises(ValueError):
+        pk.rerandomize_batch(key, bad, cts, proofs)
+    key.close()
+    pk.close()

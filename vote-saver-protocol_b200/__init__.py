@@ -468,6 +468,27 @@ class ProvingKey:
         self.ctx.check(self.ctx._lib.vsp_saver_encrypt_batch_dev(self.ctx._h, self._h, key._h, k, C.c_void_p(d_assignments),
                                                                  _p(q), C.c_void_p(d_cts), C.c_void_p(d_proofs)))
 
+    def rerandomize_batch(self, key: "ResidentSaverKey", rnd, cts, proofs):
+        """rerandomize_op::process for k ballots: rnd (k, 3, 4) = (r, z1, z2), cts (k, msg_size + 2, 12), proofs (k, 48)
+        -> (cts', proofs')"""
+        q = np.ascontiguousarray(rnd, dtype=np.uint64)
+        k = q.shape[0]
+        c = np.ascontiguousarray(cts, dtype=np.uint64).reshape(k, key.msg_size + 2, 12)
+        pr = np.ascontiguousarray(proofs, dtype=np.uint64).reshape(k, 48)
+        co, po = np.zeros_like(c), np.zeros_like(pr)
+        self.ctx.check(self.ctx._lib.vsp_saver_rerandomize_batch(self.ctx._h, self._h, key._h, k, _p(q), _p(c), _p(pr), _p(co),
+                                                                 _p(po)))
+        return co, po
+
+    def rerandomize_batch_dev(self, key: "ResidentSaverKey", k: int, rnd, d_cts: int, d_proofs: int, d_cts_out: int | None = None,
+                              d_proofs_out: int | None = None):
+        """the same on device-resident cipher texts and proofs (in place unless output pointers are given)"""
+        q = np.ascontiguousarray(rnd, dtype=np.uint64)
+        self.ctx.check(self.ctx._lib.vsp_saver_rerandomize_batch_dev(
+            self.ctx._h, self._h, key._h, k, _p(q), C.c_void_p(d_cts), C.c_void_p(d_proofs),
+            C.c_void_p(d_cts_out if d_cts_out is not None else d_cts),
+            C.c_void_p(d_proofs_out if d_proofs_out is not None else d_proofs)))
+
     def encrypt(self, pubkey: SaverPublicKey, gamma_abc_rest, msg, primary, auxiliary, r_saver: int, r: int, s: int):
         """encrypt_op<elgamal_verifiable>::process -> (cipher_text (msg_size + 2, 12), proof (48,))"""
         g, mm, p, a = _a(gamma_abc_rest, 12), _a(msg, 4), _a(primary, 4), _a(auxiliary, 4)

@@ -139,6 +139,8 @@ SYMBOLS = [
     ("vsp_saver_encrypt_batch", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_saver_encrypt_batch_dev", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_saver_rerandomize", _int, [_vp, C.POINTER(SaverPubkeyDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_saver_rerandomize_batch", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_saver_rerandomize_batch_dev", _int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_groth16_generate", _int, [_vp, C.POINTER(R1CSDesc), _vp, C.POINTER(KeypairDesc)]),
     ("vsp_saver_keygen", _int, [_vp, _u64, _vp, _vp, _vp, _vp, C.POINTER(SaverKeypairDesc)]),
     ("vsp_g1_mul_batch", _int, [_vp, _u64, _vp, _vp, _vp]),

@@ -1626,3 +1626,174 @@ extern "C" int vsp_saver_encrypt_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, const
     cudaSetDevice(ctx->device);
     return saver_encrypt_batch_impl(ctx, pk, sp, k, nullptr, nullptr, d_assignments, rs, d_cts, d_proofs);
 }
+
+// ---------------------------------------------------------------------------------------------
+// rerandomize_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:632-667) for k ballots at once
+//   ct'[0] = ct[0] + r delta;  ct'[i] = ct[i] + r delta_s[i-1];  ct'[n+1] = ct[n+1] + r delta_sum_s
+//   A' = z1 A;   B' = z1^-1 B + z2 delta_g2;   C' = C + z2 A' + r gamma_inverse_sum_s_g1
+// The n + 3 multiples of key material (r delta, r delta_s, r delta_sum_s from the resident SAVER table; r gamma_inv and
+// z2 delta_g2 from the proving key's tables) are fixed-base: one warp per job, 8 doublings + 5 additions deep.  z1 A and
+// (z1 z2) A share one launch of the endomorphism-split variable-base kernel, z1^-1 B is the only 255-bit G2 walk.
+// z1^-1 comes from the host (one batched inversion for the call).
+// ---------------------------------------------------------------------------------------------
+namespace vsp {
+// pts[2 b] = pts[2 b + 1] = proofs[b].A (the two G1 variable-base jobs of ballot b);  g2[b] = proofs[b].B
+__global__ void k_rerand_gather(const uint64_t* __restrict__ proofs, unsigned k, uint64_t* __restrict__ pts, uint64_t* __restrict__ g2) {
+    const unsigned q = blockIdx.x * blockDim.x + threadIdx.x;  // (ballot, limb)
+    if (q >= k * 24) return;
+    const unsigned b = q / 24, l = q % 24;
+    const uint64_t* pr = proofs + uint64_t(b) * 48;
+    g2[uint64_t(b) * 24 + l] = pr[12 + l];
+    if (l < 12) {
+        pts[uint64_t(2 * b) * 12 + l] = pr[l];
+        pts[uint64_t(2 * b + 1) * 12 + l] = pr[l];
+    }
+}
+// thread = (ballot, slot): slots 0 .. n+1 the cipher text, n+2: A', n+3: C', n+4: B'
+__global__ void __launch_bounds__(64) k_rerand_sum(const uint64_t* __restrict__ cts_in, const uint64_t* __restrict__ proofs_in,
+                                                   const uint32_t* __restrict__ fx, const uint32_t* __restrict__ fg,
+                                                   const uint32_t* __restrict__ fd2, const uint32_t* __restrict__ v1,
+                                                   const uint32_t* __restrict__ v2, unsigned n, unsigned k,
+                                                   uint64_t* __restrict__ cts_out, uint64_t* __restrict__ proofs_out) {
+    const unsigned q = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned slots = n + 5;
+    if (q >= k * slots) return;
+    const unsigned b = q / slots, slot = q - b * slots;
+    constexpr int L1 = G1XYZZ::BYTES / 4, L2 = G2XYZZ::BYTES / 4;
+    auto mont = [](G1Affine a) {
+        if (!a.is_inf()) {
+            a.x = fp_to_mont(a.x);
+            a.y = fp_to_mont(a.y);
+        }
+        return a;
+    };
+    if (slot <= n + 1) {
+        G1XYZZ acc = G1XYZZ::load(fx + (uint64_t(b) * (n + 2) + slot) * L1);
+        ec_madd<FqOps>(acc, mont(G1Affine::load(cts_in + (uint64_t(b) * (n + 2) + slot) * 12)));
+        write_canonical<FqOps>(cts_out + (uint64_t(b) * (n + 2) + slot) * 12, acc);
+    } else if (slot == n + 2) {
+        write_canonical<FqOps>(proofs_out + uint64_t(b) * 48, G1XYZZ::load(v1 + uint64_t(2 * b) * L1));
+    } else if (slot == n + 3) {
+        G1XYZZ acc = G1XYZZ::load(v1 + uint64_t(2 * b + 1) * L1);
+        ec_add<FqOps>(acc, G1XYZZ::load(fg + uint64_t(b) * L1));
+        ec_madd<FqOps>(acc, mont(G1Affine::load(proofs_in + uint64_t(b) * 48 + 36)));
+        write_canonical<FqOps>(proofs_out + uint64_t(b) * 48 + 36, acc);
+    } else {
+        G2XYZZ acc = G2XYZZ::load(v2 + uint64_t(b) * L2);
+        ec_add<Fq2Ops>(acc, G2XYZZ::load(fd2 + uint64_t(b) * L2));
+        write_canonical<Fq2Ops>(proofs_out + uint64_t(b) * 48 + 12, acc);
+    }
+}
+
+// d_cts_in / d_cts_out: k x (n + 2) G1;  d_proofs_in / d_proofs_out: k x 48 limbs;  rnd (host): k x (r | z1 | z2).
+// Stream-ordered on ctx->stream except for the upload of the per-ballot scalars (pageable host memory: synchronous).
+static int rerandomize_batch_impl(vsp_ctx* ctx, vsp_pk* pk, const vsp_saver_pub* sp, uint64_t k, const uint64_t* rnd,
+                                  const uint64_t* d_cts_in, const uint64_t* d_proofs_in, uint64_t* d_cts_out,
+                                  uint64_t* d_proofs_out) {
+    using namespace hostfr;
+    if (k > (1u << 20)) return set_error(ctx, VSP_E_INVALID, "rerandomize: batch too large");
+    const unsigned n = sp->n, K = (unsigned)k;
+    VSP_TRY(ensure_gamma_table(ctx, pk, sp->gamma_inv));
+    cudaStream_t s = ctx->stream;
+    constexpr size_t X1 = G1XYZZ::BYTES, X2 = G2XYZZ::BYTES;
+    // per ballot: fixed-base slots r | z2, then the variable-base scalars z1 | z1 z2 (G1) and z1^-1 (G2)
+    std::vector<uint64_t> fsc(size_t(K) * 8), v1sc(size_t(K) * 8), v2sc(size_t(K) * 4);
+    std::vector<Fr4> z1s(K), pre(K);
+    for (unsigned b = 0; b < K; ++b) {
+        const uint64_t *r = rnd + 12 * b, *z1 = r + 4, *z2 = r + 8;
+        if (!fr_reduced(r) || !fr_reduced(z1) || !fr_reduced(z2)) return set_error(ctx, VSP_E_INVALID, "rnd not reduced");
+        memcpy(z1s[b].v, z1, 32);
+        if (is_zero(z1s[b])) return set_error(ctx, VSP_E_INVALID, "z1 must be invertible");
+        Fr4 fz2;
+        memcpy(fz2.v, z2, 32);
+        const Fr4 z1z2 = mul(z1s[b], fz2);
+        memcpy(&fsc[size_t(b) * 8], r, 32);
+        memcpy(&fsc[size_t(b) * 8 + 4], z2, 32);
+        memcpy(&v1sc[size_t(b) * 8], z1, 32);
+        memcpy(&v1sc[size_t(b) * 8 + 4], z1z2.v, 32);
+        pre[b] = b ? mul(pre[b - 1], z1s[b]) : z1s[b];
+    }
+    Fr4 run = inv(pre[K - 1]);  // Montgomery's trick: one field inversion for the call
+    for (unsigned b = K; b-- > 0;) {
+        const Fr4 zi = b ? mul(run, pre[b - 1]) : run;
+        run = mul(run, z1s[b]);
+        memcpy(&v2sc[size_t(b) * 4], zi.v, 32);
+    }
+    std::vector<FixedJob> spec(n + 4);
+    spec[0] = FixedJob{0, 0};
+    for (unsigned i = 0; i < n; ++i) spec[1 + i] = FixedJob{int(1 + i), 0};
+    spec[n + 1] = FixedJob{int(3 * n + 1), 0};
+    spec[n + 2] = FixedJob{1, 0};  // fx1tab: r gamma_inv
+    spec[n + 3] = FixedJob{0, 1};  // fx2tab: z2 delta_g2
+    DevBuf d_spec, d_fsc, d_v1sc, d_v2sc, fx, fg, fd2, pts, g2, v1, v2;
+    VSP_TRY(d_spec.alloc(ctx, spec.size() * sizeof(FixedJob), s));
+    VSP_TRY(d_fsc.alloc(ctx, fsc.size() * 8, s));
+    VSP_TRY(d_v1sc.alloc(ctx, v1sc.size() * 8, s));
+    VSP_TRY(d_v2sc.alloc(ctx, v2sc.size() * 8, s));
+    VSP_TRY(fx.alloc(ctx, size_t(K) * (n + 2) * X1, s));
+    VSP_TRY(fg.alloc(ctx, size_t(K) * X1, s));
+    VSP_TRY(fd2.alloc(ctx, size_t(K) * X2, s));
+    VSP_TRY(pts.alloc(ctx, size_t(K) * 2 * 96, s));
+    VSP_TRY(g2.alloc(ctx, size_t(K) * 192, s));
+    VSP_TRY(v1.alloc(ctx, size_t(K) * 2 * X1, s));
+    VSP_TRY(v2.alloc(ctx, size_t(K) * X2, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_spec.p, spec.data(), spec.size() * sizeof(FixedJob), cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc.data(), fsc.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_v1sc.p, v1sc.data(), v1sc.size() * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_v2sc.p, v2sc.data(), v2sc.size() * 8, cudaMemcpyHostToDevice, s));
+    const FixedJob* js = d_spec.as<FixedJob>();
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_rerand_gather, (K * 24 + 127) / 128, 128, 0, s, d_proofs_in, K, pts.as<uint64_t>(), g2.as<uint64_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (K * (n + 2) + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS,
+                 FIXED_WARPS * 32 * X1, s, sp->tab.d_pts, sp->tab.n, js, n + 2, K * (n + 2), d_fsc.as<uint32_t>(), 2u,
+                 (const uint32_t*)nullptr, uint64_t(0), fx.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<FqOps>, (K + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS, FIXED_WARPS * 32 * X1, s,
+                 pk->fx1tab.d_pts, pk->fx1tab.n, js + n + 2, 1u, K, d_fsc.as<uint32_t>(), 2u, (const uint32_t*)nullptr, uint64_t(0),
+                 fg.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_fixed_mul<Fq2Ops>, (K + FIXED_WARPS - 1) / FIXED_WARPS, 32 * FIXED_WARPS, FIXED_WARPS * 32 * X2, s,
+                 pk->fx2tab.d_pts, pk->fx2tab.n, js + n + 3, 1u, K, d_fsc.as<uint32_t>(), 2u, (const uint32_t*)nullptr, uint64_t(0),
+                 fd2.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<FqOps>, 2 * K, 32, 0, s, pts.as<uint64_t>(), d_v1sc.as<uint32_t>(), 2 * K, 0,
+                 v1.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_scalar_mul_batch<Fq2Ops>, K, 32, 0, s, g2.as<uint64_t>(), d_v2sc.as<uint32_t>(), K, 0,
+                 v2.as<uint32_t>());
+    VSP_LAUNCH_K(ctx, KC_FIXED, k_rerand_sum, (K * (n + 5) + 63) / 64, 64, 0, s, d_cts_in, d_proofs_in, fx.as<uint32_t>(),
+                 fg.as<uint32_t>(), fd2.as<uint32_t>(), v1.as<uint32_t>(), v2.as<uint32_t>(), n, K, d_cts_out, d_proofs_out);
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));  // the scalar uploads read host vectors of this frame
+    return VSP_OK;
+}
+}  // namespace vsp
+
+extern "C" int vsp_saver_rerandomize_batch(vsp_ctx* ctx, const vsp_pk* pk, const vsp_saver_pub* sp, uint64_t k,
+                                           const uint64_t* rnd, const uint64_t* cts_in, const uint64_t* proofs_in,
+                                           uint64_t* cts_out, uint64_t* proofs_out) {
+    if (!ctx || !pk || !sp || !rnd || !cts_in || !proofs_in || !cts_out || !proofs_out) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    if (k == 0) return VSP_OK;
+    cudaStream_t s = ctx->stream;
+    const size_t ctb = size_t(sp->n + 2) * 96 * k, prb = size_t(384) * k;
+    DevBuf ci, pi, co, po;
+    VSP_TRY(ci.alloc(ctx, ctb, s));
+    VSP_TRY(pi.alloc(ctx, prb, s));
+    VSP_TRY(co.alloc(ctx, ctb, s));
+    VSP_TRY(po.alloc(ctx, prb, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(ci.p, cts_in, ctb, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(pi.p, proofs_in, prb, cudaMemcpyHostToDevice, s));
+    VSP_TRY(rerandomize_batch_impl(ctx, const_cast<vsp_pk*>(pk), sp, k, rnd, ci.as<uint64_t>(), pi.as<uint64_t>(),
+                                   co.as<uint64_t>(), po.as<uint64_t>()));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(cts_out, co.p, ctb, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(proofs_out, po.p, prb, cudaMemcpyDeviceToHost, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(s));
+    return VSP_OK;
+}
+
+// device-resident variant: cipher texts and proofs in and out stay on the device (e.g. straight from
+// vsp_saver_encrypt_batch_dev); in and out may be the same buffers
+extern "C" int vsp_saver_rerandomize_batch_dev(vsp_ctx* ctx, const vsp_pk* pk, const vsp_saver_pub* sp, uint64_t k,
+                                               const uint64_t* rnd, const uint64_t* d_cts_in, const uint64_t* d_proofs_in,
+                                               uint64_t* d_cts_out, uint64_t* d_proofs_out) {
+    if (!ctx || !pk || !sp || !rnd || !d_cts_in || !d_proofs_in || !d_cts_out || !d_proofs_out) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    if (k == 0) return VSP_OK;
+    return rerandomize_batch_impl(ctx, const_cast<vsp_pk*>(pk), sp, k, rnd, d_cts_in, d_proofs_in, d_cts_out, d_proofs_out);
+}
