@@ -892,6 +892,7 @@ def main():
     ctx = res["ctx"]
     peaks = load_peaks()
     p_int = ctx.measure_imad_rate(4096)  # 32x32->64 multiply-adds per second, measured now on this GPU
+    p_dfma = ctx.measure_dfma_rate(4096)  # FP64 fused multiply-adds per second (the other arithmetic pipe)
     value = world * B * K / (res["ms_dev"] * 1e-3)
     e2e = world * B * K / (res["ms_e2e"] * 1e-3)
     prof = res["prof"]
@@ -924,6 +925,11 @@ def main():
                          "traffic_note": ncu.get("note", "no ncu capture of this build under profiles/: traffic unmeasured"),
                          "launches": acc["launches"], "avg_launch_ms": acc["ms"] / max(acc["launches"], 1),
                          "share_of_kernel_time": acc["ms"] / tot_ms,
+                         "fp64_fma_peak_tfma_s": p_dfma / 1e12,
+                         "fp64_note": "measured DFMA rate / IMAD.WIDE rate = %.2f: a 52-bit-limb DFMA Montgomery product needs ~3 "
+                                      "FP64 operations per 52x52 partial product (2 FMA + 1 add) x 128 partial products for Fq "
+                                      "against 300 IMAD.WIDE, so it pays only from a ratio of ~1.9 up (DESIGN.md section 4)"
+                                      % (p_dfma / p_int if p_int else 0.0),
                          "peak_source": "vsp_measure_imad_rate, measured in this run (MEASURED_PEAKS.json has no "
                                         "integer-pipe figure); HBM peak " + peaks["source"],
                          "work": "bucket additions scheduled x 11 Fq mul x 300 MAD (SURVEY.md 8d), counted on the device"},

@@ -372,6 +372,26 @@ VSP_API int vsp_saver_verify_decryption(vsp_ctx *ctx, uint64_t msg_size, const u
                                         const uint64_t *rho_g2, const uint64_t *rho_sv_g2, const uint64_t *rho_rhov_g2,
                                         const uint64_t *gamma_abc_rest, const uint64_t *proof, uint8_t *ok_out);
 
+/* ---- witness generation for the ballot circuit --------------------------------------------------
+ * Replaces the per-vote generate_r1cs_witness sequence of bin/cli (common.hpp:1110-1128) for k ballots at once.  The
+ * circuit (components::encrypted_input_voting over Pedersen-on-Jubjub hashes and an arity-2 Merkle path) lives in the
+ * un-vendored crypto3-blueprint; vote-saver-protocol_b200/voting.py restates it and produces both the R1CS and the
+ * layout tables this program is created from (parity with crypto3's wire values unpinned; every witness satisfies that
+ * R1CS).  vsp_voting_witness_batch_dev fills k assignments (1 || primary || auxiliary, canonical Fr, num_vars + 1 elements
+ * each) in device memory, the input format of vsp_saver_encrypt_batch_dev: votes / indices k u32 (the chosen option and the
+ * voter's leaf position), eid the election id bits, sks k x 4 limbs (255-bit secrets), paths k x depth x 4 limbs (sibling
+ * digests, leaf level first). */
+typedef struct vsp_voting_program vsp_voting_program;
+VSP_API int vsp_voting_program_create(vsp_ctx *ctx, const uint32_t *scalars, uint64_t n_scalars, const uint32_t *hashes,
+                                      uint64_t n_hashes, const uint32_t *in_idx, uint64_t n_in, const uint32_t *levels,
+                                      uint64_t depth, const uint64_t *tables, uint64_t n_table_rows,
+                                      vsp_voting_program **out);
+VSP_API void vsp_voting_program_destroy(vsp_voting_program *p);
+VSP_API uint64_t vsp_voting_program_num_vars(const vsp_voting_program *p);
+VSP_API int vsp_voting_witness_batch_dev(vsp_ctx *ctx, const vsp_voting_program *p, uint64_t k, const uint32_t *votes,
+                                         uint64_t eid, const uint64_t *sks, const uint32_t *indices, const uint64_t *paths,
+                                         uint64_t *d_assignments);
+
 /* ---- wire codecs: the reference's byte formats either side of the path (host only, no GPU work) ------------- */
 /* Formats (relative to libs/marshalling): big-endian fixed-width integers (Fr 32 B, Fq 48 B, size_t 8 B), sequences
  * with an 8-byte count prefix; compressed points as processing/curve_element.hpp:93-174 writes them (G1 48 B,
@@ -411,6 +431,10 @@ VSP_API int vsp_accumulate_mads_per_add(vsp_ctx *ctx, double *out);
 /* sustained 32-bit multiply-add issue rate: runs a dependent-free IMAD.WIDE carry-chain kernel on all SMs for
  * `iters` rounds and returns multiply-adds per second (the P_int roofline denominator). */
 VSP_API int vsp_measure_imad_rate(vsp_ctx *ctx, uint64_t iters, double *mads_per_second);
+/* the same for the FP64 pipe: independent chains of fused multiply-adds on every SM (the unit of a 52-bit-limb DFMA
+ * Montgomery product, two per partial product).  Reported by bench.py beside the integer peak; DESIGN.md section 4 has the
+ * go / no-go it supports. */
+VSP_API int vsp_measure_dfma_rate(vsp_ctx *ctx, uint64_t iters, double *fmas_per_second);
 
 #ifdef __cplusplus
 }

@@ -367,3 +367,21 @@ def test_rerandomize_batch_matches_oracle(vsp, ctx):
         pk.rerandomize_batch(key, bad, cts, proofs)
     key.close()
     pk.close()
+
+
+def test_plain_text_must_be_shorter_than_the_primary_input(vsp, ctx):
+    """'Primary input should be longer than plain text.' (elgamal_verifiable.hpp:325-326): msg_size == num_inputs is
+    rejected by the one-ballot and the batched entry points"""
+    nc, ni = 40, 6
+    cs, primary, aux, arr = _instance(nc, ni, seed=31, binary=True)
+    pub_arr, gamma_abc_rest = synthetic_saver_pub(ni, seed=32)
+    gamma_abc_rest = np.ascontiguousarray(gamma_abc_rest[:ni])
+    pub = vsp.SaverPublicKey(pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    with pytest.raises(ValueError):
+        pk.encrypt(pub, gamma_abc_rest, primary, primary, aux, 5, 6, 7)
+    key = pub.resident(ctx, gamma_abc_rest)
+    with pytest.raises(ValueError):
+        pk.encrypt_batch(key, primary[None], aux[None], cref.ints_to_limbs([5, 6, 7], 4)[None])
+    key.close()
+    pk.close()

@@ -135,6 +135,11 @@ class Context:
         self.check(self._lib.vsp_accumulate_mads_per_add(self._h, C.byref(out)))
         return out.value
 
+    def measure_dfma_rate(self, iters: int = 4096) -> float:
+        out = C.c_double(0)
+        self.check(self._lib.vsp_measure_dfma_rate(self._h, iters, C.byref(out)))
+        return out.value
+
     def measure_imad_rate(self, iters: int = 4096) -> float:
         out = C.c_double(0)
         self.check(self._lib.vsp_measure_imad_rate(self._h, iters, C.byref(out)))

@@ -153,6 +153,10 @@ SYMBOLS = [
                                                  _vp, _u64, _vp, _vp]),
     ("vsp_saver_decrypt", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp]),
     ("vsp_saver_verify_decryption", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    ("vsp_voting_program_create", _int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _u64, C.POINTER(_vp)]),
+    ("vsp_voting_program_destroy", None, [_vp]),
+    ("vsp_voting_program_num_vars", _u64, [_vp]),
+    ("vsp_voting_witness_batch_dev", _int, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _vp, _vp]),
     ("vsp_codec_g1_compress", _int, [_vp, _vp]),
     ("vsp_codec_g2_compress", _int, [_vp, _vp]),
     ("vsp_codec_proof_write", _int, [_vp, _vp]),
@@ -166,6 +170,7 @@ SYMBOLS = [
     ("vsp_codec_fast_pk_read", _int, [_vp, C.c_size_t, C.POINTER(ProvingKeyDesc)]),
     ("vsp_codec_fast_pk_write", _int, [C.POINTER(ProvingKeyDesc), _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
+    ("vsp_measure_dfma_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
     ("vsp_accumulate_mads_per_add", _int, [_vp, C.POINTER(C.c_double)]),
 ]
 

@@ -484,6 +484,47 @@ __global__ void __launch_bounds__(256) k_imad_rate(uint32_t* sink, uint32_t iter
     if (x == 0x12345678u) sink[0] = x;  // keep the chains live
 }
 
+// ---- the second arithmetic pipe: FP64 fused multiply-adds (the unit of a 52-bit-limb DFMA Montgomery product) --------
+__global__ void __launch_bounds__(256) k_dfma_rate(double* sink, uint32_t iters, double seed) {
+    double a = seed + threadIdx.x * 1e-9, b = 1.0 + blockIdx.x * 1e-12;
+    double acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = a + i;
+    for (uint32_t it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[i] = fma(acc[i], b, a);
+            a += 1e-7;
+        }
+    }
+    double x = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x += acc[i];
+    if (x == 0.12345) sink[0] = x;
+}
+extern "C" int vsp_measure_dfma_rate(vsp_ctx* ctx, uint64_t iters, double* fmas_per_second) {
+    if (!ctx || !fmas_per_second || iters == 0 || iters > 0xffffffffull) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    DevBuf sink;
+    VSP_TRY(sink.alloc(ctx, 16, ctx->stream));
+    const unsigned blocks = ctx->sm_count * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    VSP_CUDA_CHECK(ctx, cudaEventCreate(&e0));
+    VSP_CUDA_CHECK(ctx, cudaEventCreate(&e1));
+    VSP_LAUNCH(ctx, k_dfma_rate, blocks, threads, 0, ctx->stream, sink.as<double>(), (uint32_t)(iters / 8 + 1), 1.5);
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(e0, ctx->stream));
+    VSP_LAUNCH(ctx, k_dfma_rate, blocks, threads, 0, ctx->stream, sink.as<double>(), (uint32_t)iters, 2.5);
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(e1, ctx->stream));
+    VSP_CUDA_CHECK(ctx, cudaEventSynchronize(e1));
+    float ms = 0;
+    VSP_CUDA_CHECK(ctx, cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *fmas_per_second = (double)blocks * threads * (double)iters * 64.0 / (ms * 1e-3);
+    return VSP_OK;
+}
+
 extern "C" int vsp_accumulate_mads_per_add(vsp_ctx* ctx, double* out) {
     if (!ctx || !out) return VSP_E_INVALID;
     *out = ACC_G1_MADS_PER_ADD;

@@ -980,6 +980,20 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
     VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 2), ctx->ev_fork, 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 3), ctx->ev_fork, 0));
+    // After the fork a failure must not return before the main stream has joined the side streams: the DevBuf
+    // destructors release abc / bsc / d_fsc / jobs in main-stream order, and a side stream may still be reading them.
+    struct ForkGuard {
+        vsp_ctx* c;
+        bool armed = true;
+        ~ForkGuard() {
+            if (!armed) return;
+            for (int i = 2; i <= 3; ++i) {
+                cudaStream_t ss = side_stream(c, i);
+                if (ss == c->stream) continue;
+                if (cudaEventRecord(c->ev_join[i], ss) == cudaSuccess) cudaStreamWaitEvent(c->stream, c->ev_join[i], 0);
+            }
+        }
+    } guard{ctx};
     // side 2: A, L
     VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->A, pk->nv + 1, d_w, evA, true, B, w_stride, X1 / 8));
     VSP_TRY(msm_run(ctx, side_stream(ctx, 2), pk->L, pk->na, d_w + 8 * (pk->ni + 1), evL, true, B, w_stride, X1 / 8));
@@ -1012,6 +1026,7 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(st, ctx->ev_join[3], 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[2], 0));
     VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_join[3], 0));
+    guard.armed = false;  // joined
 
     AsmPtrs ap;
     ap.evA = reinterpret_cast<uint32_t*>(evA);
@@ -1430,7 +1445,8 @@ extern "C" int vsp_saver_encrypt(vsp_ctx* ctx, const vsp_pk* pk, const vsp_saver
                                  uint64_t* out_ct, uint64_t* out_proof) {
     if (!ctx || !pk || !pub || !msg || !primary || !out_ct || !out_proof) return VSP_E_INVALID;
     // "Plain text should be a prefix of primary input" (elgamal_verifiable.hpp:336-339)
-    if (pub->msg_size >= pk->ni + 1 || memcmp(msg, primary, pub->msg_size * 32) != 0)
+    // and "Primary input should be longer than plain text." (:325-326)
+    if (pub->msg_size >= pk->ni || memcmp(msg, primary, pub->msg_size * 32) != 0)
         return set_error(ctx, VSP_E_INVALID, "plain text should be a proper prefix of the primary input");
     VSP_TRY(vsp_saver_ciphertext(ctx, pub, gamma_abc_rest, msg, r_saver, out_ct));
     return vsp_prove(ctx, pk, primary, aux, r, s, r_saver, pub->gamma_inverse_sum_s_g1, out_proof);
@@ -1575,7 +1591,7 @@ static int saver_encrypt_batch_impl(vsp_ctx* ctx, const vsp_pk* cpk, const vsp_s
                                     const uint64_t* primary, const uint64_t* aux, const uint64_t* d_assignments,
                                     const uint64_t* rs, uint64_t* d_cts, uint64_t* d_proofs) {
     vsp_pk* pk = const_cast<vsp_pk*>(cpk);
-    if (sp->n >= pk->ni + 1)
+    if (sp->n >= pk->ni)  // "Primary input should be longer than plain text." (elgamal_verifiable.hpp:325-326)
         return set_error(ctx, VSP_E_INVALID, "plain text should be a proper prefix of the primary input");
     const uint64_t stride = pk->nv + 1;
     const unsigned chunk = batch_chunk(ctx, pk);
