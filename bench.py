@@ -45,6 +45,10 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--ballots", type=int, default=256, help="ballots per GPU per step")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--circuit", default="voting", choices=["voting", "xor"],
+                    help="voting: the restated encrypted_input ballot circuit (Pedersen/Jubjub, Merkle path); xor: round 1's "
+                         "stand-in XOR chain of --constraints constraints")
+    ap.add_argument("--tree-depth", type=int, default=16, help="voter Merkle tree depth of the ballot circuit (configs[2]: 16)")
     ap.add_argument("--constraints", type=int, default=NUM_CONSTRAINTS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the MSM 2^20 / NTT 2^20 / sharded MSM side measurements")
@@ -58,16 +62,30 @@ def parse_args():
     return ap.parse_args()
 
 
-def workload_config(args, world):
-    return {"workload": "batched encrypted-input ballot proofs (BASELINE configs[3] on the configs[2] depth-16 stand-in "
-                        "circuit), proof-per-GPU",
-            "constraints": args.constraints, "primary_inputs": NUM_INPUTS, "msg_size": MSG_SIZE,
-            "domain": "basic_radix2 2^16" if args.constraints == NUM_CONSTRAINTS else "see constraints",
-            "ballots_per_gpu_per_step": args.ballots, "ballots_per_step": args.ballots * world,
-            "witness": "all-bits XOR chain (r1cs_examples.hpp:154-210 shape), distinct per ballot",
-            "proving_key": "synthetic seeded bases k_i*G (shape-only)",
-            "l2": "inputs larger than L2: 2 MiB of witness + ~30 MiB of scratch per ballot x %d ballots per step, window "
-                  "tables ~200 MiB; every ballot's witness differs; no explicit flush" % args.ballots}
+def workload_config(args, world, circuit=None):
+    cfg = {"primary_inputs": NUM_INPUTS, "msg_size": MSG_SIZE,
+           "ballots_per_gpu_per_step": args.ballots, "ballots_per_step": args.ballots * world,
+           "proving_key": "synthetic seeded bases k_i*G (shape-only; the verify legs use keys generated on the GPU)",
+           "l2": "inputs larger than L2: ~1 MiB of witness + ~15 MiB of scratch per ballot x %d ballots per step, window "
+                 "tables ~100 MiB; every ballot's witness differs; no explicit flush" % args.ballots}
+    if args.circuit == "voting":
+        cfg.update({"workload": "batched encrypted-input ballot proofs (BASELINE configs[3]) on the ballot circuit of configs[2]: "
+                                "voter Merkle tree depth %d (2^%d voters), eid 64 bits, msg_size 25; proof-per-GPU"
+                                % (args.tree_depth, args.tree_depth),
+                    "circuit": "encrypted_input_voting restated (vote-saver-protocol_b200/voting.py: Pedersen-on-Jubjub hashes, "
+                               "arity-2 Merkle path, multipacking; crypto3-blueprint's own gadgets are un-vendored, so constraint "
+                               "count and wire values are the restatement's: parity unpinned)",
+                    "witness": "generated on the GPU (vsp_voting_witness_batch_dev): distinct voter, secret key and vote per "
+                               "ballot over one consistent voter tree"})
+        if circuit is not None:
+            cfg.update({"constraints": circuit.num_constraints, "variables": circuit.num_vars,
+                        "domain": "basic_radix2 2^15" if args.tree_depth == 16 else "see constraints"})
+    else:
+        cfg.update({"workload": "batched encrypted-input ballot proofs (BASELINE configs[3]) on round 1's stand-in XOR-chain "
+                                "circuit, proof-per-GPU", "constraints": args.constraints,
+                    "domain": "basic_radix2 2^16" if args.constraints == NUM_CONSTRAINTS else "see constraints",
+                    "witness": "all-bits XOR chain (r1cs_examples.hpp:154-210 shape), distinct per ballot"})
+    return cfg
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -154,26 +172,64 @@ def run_b200(args):
     B, K, W = args.ballots, args.steps, max(args.warmup, 3)
 
     # ---- setup (untimed): circuit, proving key, witnesses ----------------------------------------------
-    cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
-    _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
+    circuit = witness_info = None
+    if args.circuit == "voting":
+        vt = importlib.import_module("vote-saver-protocol_b200.voting")
+        circuit = vt.VotingCircuit(depth=args.tree_depth, eid_bits=64, msg_size=MSG_SIZE)
+        cs = circuit.r1cs_arrays()
+        # "Constraints number in the generated R1CS" / "Variables number ..." as common.hpp:911-912 prints them
+        sys.stderr.write("Constraints number in the generated R1CS: %d\nVariables number in the generated R1CS: %d\n"
+                         % (circuit.num_constraints, circuit.num_vars))
+    else:
+        cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
+    ni, na = cs["num_inputs"], cs["num_aux"]
+    _, m = vsp.domain_plan(cs["num_constraints"] + ni + 1)
     pk = vsp.ProvingKey(ctx, wl.proving_key_arrays(vsp, ctx, cs, m, seed=7))
     pub_arr, gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
     gabc = np.ascontiguousarray(gabc[:MSG_SIZE])
     pub = vsp.SaverPublicKey(pub_arr)
     key = pub.resident(ctx, gabc)
-    ni, na = cs["num_inputs"], cs["num_aux"]
     prim = torch.empty((B, ni, 4), dtype=torch.int64).pin_memory()
     aux = torch.empty((B, na, 4), dtype=torch.int64).pin_memory()
-    proofs_host = torch.empty((B, 48), dtype=torch.int64).pin_memory()
     prim_np, aux_np = prim.numpy().view(np.uint64), aux.numpy().view(np.uint64)
-    for b in range(B):
-        p, a = wl.ballot_witness(cs, seed=rank * 100003 + b)
-        prim_np[b], aux_np[b] = p, a
-    rs = wl.random_fr(3 * B, seed=rank + 99).reshape(B, 3, 4)
     assign = torch.zeros((B, ni + na + 1, 4), dtype=torch.int64, device="cuda")
-    assign[:, 0, 0] = 1
-    assign[:, 1:ni + 1] = prim.cuda()
-    assign[:, ni + 1:] = aux.cuda()
+    if circuit is not None:
+        # one consistent voter tree: this rank's B voters hold real keys, every other leaf the default digest
+        import random as _random
+        rng = _random.Random(1000 + rank)
+        sks = [rng.getrandbits(255) for _ in range(B)]
+        tree = vt.SparseVoterTree(args.tree_depth, sks)
+        gen = vt.WitnessGenerator(ctx, circuit)
+        lim = lambda x: np.frombuffer(int(x).to_bytes(32, "little"), dtype=np.uint64)
+        votes = np.array([rng.randrange(MSG_SIZE) for _ in range(B)], dtype=np.uint32)
+        sk_l = np.stack([lim(x) for x in sks])
+        idx = np.arange(B, dtype=np.uint32)
+        paths = np.array([[lim(d) for d in tree.path(i)] for i in range(B)], dtype=np.uint64).reshape(B, max(args.tree_depth, 1), 4) \
+            if args.tree_depth else np.zeros((B, 1, 4), dtype=np.uint64)
+        eid = rng.getrandbits(64)
+        with torch.cuda.stream(stream):
+            gen.generate_dev(B, votes, eid, sk_l, idx, paths, assign.data_ptr())  # warm-up + the step's witnesses
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            gen.generate_dev(B, votes, eid, sk_l, idx, paths, assign.data_ptr())
+            torch.cuda.synchronize()
+            gen_s = time.perf_counter() - t0
+        witness_info = {"ballots": B, "ms": gen_s * 1e3, "ballots_per_s": B / gen_s,
+                        "what": "vsp_voting_witness_batch_dev: %d full assignments (%d variables each) left in device memory; "
+                                "wall clock incl. the upload of votes / keys / copaths" % (B, circuit.num_vars)}
+        host = assign.cpu().numpy().view(np.uint64)
+        root = int.from_bytes(host[0, ni - 1].tobytes(), "little") + (int.from_bytes(host[0, ni].tobytes(), "little") << 254)
+        witness_info["root_is_the_trees"] = bool(root == tree.root)
+        prim_np[:], aux_np[:] = host[:, 1:ni + 1], host[:, ni + 1:]
+        gen.close()
+    else:
+        for b in range(B):
+            p, a = wl.ballot_witness(cs, seed=rank * 100003 + b)
+            prim_np[b], aux_np[b] = p, a
+        assign[:, 0, 0] = 1
+        assign[:, 1:ni + 1] = prim.cuda()
+        assign[:, ni + 1:] = aux.cuda()
+    rs = wl.random_fr(3 * B, seed=rank + 99).reshape(B, 3, 4)
     d_proofs = torch.zeros((B, 48), dtype=torch.int64, device="cuda")
     d_cts = torch.zeros((B, MSG_SIZE + 2, 12), dtype=torch.int64, device="cuda")
 
@@ -231,7 +287,8 @@ def run_b200(args):
     cts_dev = d_cts.cpu().numpy().view(np.uint64)
     same = bool(np.array_equal(proofs_e2e, proofs_dev) and np.array_equal(cts_e2e, cts_dev))
 
-    return dict(world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
+    return dict(circuit=circuit, witness_info=witness_info,
+                world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
                 clocks=clocks, launches=launches, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
                 proofs=proofs_dev, cts=cts_dev, gabc=gabc, key=key, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes),
                 d2h=int(B * 384 + cts_dev.nbytes), stream=stream)
@@ -336,17 +393,34 @@ def run_reference(args):
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     cref.lib().orc_set_num_threads(cores)
     vsp, ctx = _CpuKeyGen, None
-    cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
-    _, m = vsp.domain_plan(args.constraints + NUM_INPUTS + 1)
+    n = max(1, args.cpu_ballots)  # ballots per step: a bounded sample of the B-ballot batch
+    prim, aux = [], []
+    circuit = None
+    if args.circuit == "voting":
+        # the same circuit and the same kind of witnesses as the B200 arm: the circuit module's pure-Python side (its
+        # R1CS builder and host witness restatement) — the CUDA library is not loaded on this arm
+        import random as _random
+        vt = importlib.import_module("vote-saver-protocol_b200.voting")
+        circuit = vt.VotingCircuit(depth=args.tree_depth, eid_bits=64, msg_size=MSG_SIZE)
+        cs = circuit.r1cs_arrays()
+        rng = _random.Random(1000)
+        sks = [rng.getrandbits(255) for _ in range(n)]
+        tree = vt.SparseVoterTree(args.tree_depth, sks)
+        eid = rng.getrandbits(64)
+        for b in range(n):
+            p, a = circuit.witness(rng.randrange(MSG_SIZE), eid, sks[b], b, tree.path(b))
+            prim.append(vt.ints_to_fr(p))
+            aux.append(vt.ints_to_fr(a))
+    else:
+        cs = wl.ballot_r1cs(args.constraints, NUM_INPUTS, seed=0)
+        for b in range(n):
+            p, a = wl.ballot_witness(cs, seed=b)
+            prim.append(p)
+            aux.append(a)
+    _, m = vsp.domain_plan(cs["num_constraints"] + cs["num_inputs"] + 1)
     pk_arr = wl.proving_key_arrays(vsp, ctx, cs, m, seed=7)
     pub_arr, gabc = wl.saver_pubkey_arrays(vsp, ctx, MSG_SIZE, seed=11)
     gabc = np.ascontiguousarray(gabc[:MSG_SIZE])
-    n = max(1, args.cpu_ballots)  # ballots per step: a bounded sample of the B-ballot batch
-    prim, aux = [], []
-    for b in range(n):
-        p, a = wl.ballot_witness(cs, seed=b)
-        prim.append(p)
-        aux.append(a)
     rs = wl.random_fr(3 * n, seed=99).reshape(n, 3, 4)
     K, W = args.steps, args.warmup  # the same step and warm-up counts as the B200 arm
     for _ in range(W):
@@ -361,7 +435,7 @@ def run_reference(args):
     return {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": K,
             "warmup": W, "ms_per_step": total / K * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32 limbs (Fq 12x32, Fr 8x32 Montgomery)" if False else "u64 limbs (CPU)",
-            "data": "synthetic", "config": workload_config(args, world),
+            "data": "synthetic", "config": workload_config(args, world, circuit),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
@@ -909,7 +983,7 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": res["W"],
             "ms_per_step": res["ms_dev"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u32 limbs (Fq 12x32, Fr 8x32, Montgomery)", "data": "synthetic",
-            "config": workload_config(args, world),
+            "config": workload_config(args, world, res["circuit"]),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"],
                     "ms_per_step": res["ms_e2e"] / K, "proofs_equal_device_path": res["same"]},
             "gpu_launches": res["launches"], "clocks": res["clocks"],
@@ -939,6 +1013,8 @@ def main():
     line["roofline"]["whole_step_frac"] = (step_units / K) / (res["ms_dev"] / K * 1e-3) / p_int if p_int else None
     if extras_on:
         line["extras"] = run_extras(res, peaks, p_int)
+        if res["witness_info"]:
+            line["extras"]["witness_generation"] = res["witness_info"]
         if world == 1 and not args.no_sweep:
             line["extras"]["sweep"] = run_sweep(res, peaks, p_int)
         w = msm_reference_mads(1 << args.sharded_log_n)

@@ -47,14 +47,16 @@ struct Fq2Ops {
     VSP_DEV static T one() { return T{Fq::one(), Fq::zero()}; }
     VSP_DEV static T add(const T& a, const T& b) { return T{fp_add(a.c0, b.c0), fp_add(a.c1, b.c1)}; }
     VSP_DEV static T sub(const T& a, const T& b) { return T{fp_sub(a.c0, b.c0), fp_sub(a.c1, b.c1)}; }
-    // (a0 + a1 u)(b0 + b1 u), u^2 = -1, Karatsuba: 3 Fq multiplications
-    static __device__ __noinline__ T mul(const T& a, const T& b) {
+    // (a0 + a1 u)(b0 + b1 u), u^2 = -1, Karatsuba: 3 Fq multiplications.  One shared copy (28 of them inlined per mixed
+    // addition would not fit the instruction cache); operands BY VALUE so that they travel in registers — a reference
+    // parameter of a non-inlined function makes the caller spill both operands to its stack frame
+    static __device__ __noinline__ T mul(T a, T b) {
         Fq t0 = fp_mul(a.c0, b.c0);
         Fq t1 = fp_mul(a.c1, b.c1);
         Fq s = fp_mul(fp_add(a.c0, a.c1), fp_add(b.c0, b.c1));
         return T{fp_sub(t0, t1), fp_sub(fp_sub(s, t0), t1)};
     }
-    static __device__ __noinline__ T sqr(const T& a) {
+    static __device__ __noinline__ T sqr(T a) {
         Fq m = fp_mul(a.c0, a.c1);
         Fq r0 = fp_mul(fp_add(a.c0, a.c1), fp_sub(a.c0, a.c1));
         return T{r0, fp_dbl(m)};

@@ -830,7 +830,12 @@ __global__ void __launch_bounds__(64) k_table_level(uint32_t* table, uint64_t n,
     }
 }
 
-// window width minimising  (bucket additions) + (reduction: 2 full additions per bucket, ~1.4x a mixed one each)
+// window width minimising  (bucket additions) + (reduction: 2 full additions per bucket, ~1.4x a mixed one each).
+// With a window table the reduction runs once per (ballot, query) over buckets that a realistic witness fills (a third of
+// the ballot circuit's wires are full-width field elements), and its kernels — serial running sums — reach well under
+// half the accumulate kernel's pipe utilisation, so a bucket there is weighted by what it measured to cost on the ballot
+// circuit (B200, 64-ballot chunks: c = 13 beats 14, 15, 16 at 32k points: 1,139 / 1,101 / 1,092 / 965 proofs/s), not by
+// its multiplication count.
 static unsigned choose_window(uint64_t n, bool table) {
     if (const char* e = getenv("VSP_MSM_C")) {  // tuning override
         const int c = atoi(e);
@@ -839,7 +844,7 @@ static unsigned choose_window(uint64_t n, bool table) {
     double best = 1e300;
     unsigned best_c = 4;
     for (unsigned c = 4; c <= 22; ++c) {
-        const double w = 255 / c + 1, red = 2.8 * double(1u << (c - 1));
+        const double w = 255 / c + 1, red = (table ? 16.0 : 2.8) * double(1u << (c - 1));
         const double cost = table ? w * double(n) + red : w * (double(n) + red);
         if (cost < best) {
             best = cost;
@@ -991,11 +996,12 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     VSP_LAUNCH_K(ctx, KC_MSM_REDUCE, k_msm_collapse_heavy<F>, 256, COLLAPSE_THREADS, COLLAPSE_THREADS * XYZZ<F>::BYTES, s,
                  heavy.as<uint32_t>(), heavy_count.as<uint32_t>(), task_off.as<uint32_t>(), partial.as<uint32_t>(), 1);
     const unsigned n_sets = batch * p.sets;
-    // segment length: keep ~2^15 segment threads in flight (each runs a serial chain of 2 * SEG additions)
+    // segment length: keep ~2^14 segment threads in flight (each runs a serial chain of 2 * SEG additions); measured on the
+    // ballot circuit (c = 13, 64-ballot chunks): SEG = 16 beats 8 and 32 (reduction 37 / 42 / 51 ms per step)
     unsigned seg_log = 1;
     {
         const unsigned total_log = p.nb_log + floor_log2_u64(n_sets);
-        if (total_log > 15 + 1) seg_log = total_log - 15;
+        if (total_log > 14 + 1) seg_log = total_log - 14;
         if (const char* e = getenv("VSP_MSM_SEG_LOG")) seg_log = (unsigned)atoi(e);  // tuning override
         if (seg_log < 1) seg_log = 1;
         if (seg_log > SEG_LOG_MAX) seg_log = SEG_LOG_MAX;

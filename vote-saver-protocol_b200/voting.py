@@ -80,13 +80,27 @@ def ed_add(p, q):
     return ((u1 * v2 + v1 * u2) * pow(1 + t, -1, Q) % Q, (v1 * v2 + u1 * u2) * pow(1 - t, -1, Q) % Q)
 
 
+def _proj_add(p, q):
+    """projective twisted Edwards addition, a = -1 (add-2008-bbjlp): no inversion"""
+    (x1, y1, z1), (x2, y2, z2) = p, q
+    a = z1 * z2 % Q
+    b = a * a % Q
+    c = x1 * x2 % Q
+    d = y1 * y2 % Q
+    e = JUBJUB_D * c % Q * d % Q
+    f, g = (b - e) % Q, (b + e) % Q
+    return (a * f % Q * ((x1 + y1) * (x2 + y2) - c - d) % Q, a * g % Q * (d + c) % Q, f * g % Q)
+
+
 def ed_mul(k: int, p):
-    acc = (0, 1)
+    """k p by double-and-add in projective coordinates, one inversion at the end"""
+    acc, pp = (0, 1, 1), (p[0], p[1], 1)
     for bit in bin(k)[2:] if k else "":
-        acc = ed_add(acc, acc)
+        acc = _proj_add(acc, acc)
         if bit == "1":
-            acc = ed_add(acc, p)
-    return acc
+            acc = _proj_add(acc, pp)
+    zi = pow(acc[2], -1, Q)
+    return (acc[0] * zi % Q, acc[1] * zi % Q)
 
 
 def ed_neg(p):
@@ -160,6 +174,38 @@ def merkle_path_native(leaves: Sequence[int], index: int) -> List[int]:
         level = [pedersen_hash_native(digest_bits(level[i]) + digest_bits(level[i + 1])) for i in range(0, len(level), 2)]
         index >>= 1
     return path
+
+
+class SparseVoterTree:
+    """A 2^depth-leaf voter tree in which only the first len(sks) leaves hold real public keys (pk_i = PedersenHash(sk_i))
+    and every other leaf holds the same default digest: the subtrees made of defaults only collapse to one value per level,
+    so a consistent depth-16 tree costs a few hundred hashes instead of 65,535.  Gives the root and every voter's copath."""
+
+    def __init__(self, depth: int, sks: Sequence[int], default_leaf: int = 0):
+        n = len(sks)
+        assert n <= (1 << depth)
+        self.depth = depth
+        level = [pedersen_hash_native(digest_bits(s)) for s in sks]
+        self.leaves = list(level)
+        default = default_leaf
+        self.levels = []  # (real nodes of the level, the all-default node of the level)
+        for _ in range(depth):
+            self.levels.append((level, default))
+            nxt = []
+            for i in range(0, len(level), 2):
+                right = level[i + 1] if i + 1 < len(level) else default
+                nxt.append(pedersen_hash_native(digest_bits(level[i]) + digest_bits(right)))
+            default = pedersen_hash_native(digest_bits(default) * 2)
+            level = nxt
+        self.root = level[0] if level else default
+
+    def path(self, index: int) -> List[int]:
+        out = []
+        for level, default in self.levels:
+            sib = index ^ 1
+            out.append(level[sib] if sib < len(level) else default)
+            index >>= 1
+        return out
 
 
 # ---- the circuit ---------------------------------------------------------------------------------------------------
