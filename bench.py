@@ -101,7 +101,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("VSP_BENCH_SMI_MS", "100")], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("VSP_BENCH_SMI_MS", "200")], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
@@ -1000,9 +1000,10 @@ def main():
                          "launches": acc["launches"], "avg_launch_ms": acc["ms"] / max(acc["launches"], 1),
                          "share_of_kernel_time": acc["ms"] / tot_ms,
                          "fp64_fma_peak_tfma_s": p_dfma / 1e12,
-                         "fp64_note": "measured DFMA rate / IMAD.WIDE rate = %.2f: a 52-bit-limb DFMA Montgomery product needs ~3 "
-                                      "FP64 operations per 52x52 partial product (2 FMA + 1 add) x 128 partial products for Fq "
-                                      "against 300 IMAD.WIDE, so it pays only from a ratio of ~1.9 up (DESIGN.md section 4)"
+                         "fp64_note": "measured DFMA rate / IMAD.WIDE rate = %.2f.  A 52-bit-limb DFMA Montgomery product of Fq is 128 "
+                                      "partial products x (2 FMA + 1 FP64 add) = 384 FP64-pipe operations plus ~512 64-bit integer "
+                                      "additions of the raw mantissas, against 300 IMAD.WIDE + ~90 others: at this ratio the product "
+                                      "alone would gain < 1.2x before any format conversion — no-go (DESIGN.md section 4)"
                                       % (p_dfma / p_int if p_int else 0.0),
                          "peak_source": "vsp_measure_imad_rate, measured in this run (MEASURED_PEAKS.json has no "
                                         "integer-pipe figure); HBM peak " + peaks["source"],
