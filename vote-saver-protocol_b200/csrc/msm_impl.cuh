@@ -389,22 +389,30 @@ __global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restri
                                                         const uint32_t* __restrict__ order,
                                                         const uint32_t* __restrict__ n_tasks_ptr, uint32_t max_tasks,
                                                         uint32_t* __restrict__ partial) {
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     // exact task count is device-resident (task_off[buckets]): no host round trip.  From max_tasks up the launch belongs
     // to k_msm_accumulate_affine.
     const uint32_t n_tasks = *n_tasks_ptr;
-    if (tid >= n_tasks || n_tasks >= max_tasks) return;
-    const uint32_t t = order[tid];
-    const Task k = tasks[t];
-    XYZZ<F> acc = XYZZ<F>::inf();
+    if (n_tasks >= max_tasks) return;
     constexpr int PT_LIMBS = Affine<F>::BYTES / 4;
-    for (uint32_t pos = k.begin; pos < k.end; ++pos) {
-        const uint32_t v = sorted[pos];
-        Affine<F> pt = Affine<F>::load(table + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
-        if (v & 0x80000000u) pt.y = F::neg(pt.y);
-        ec_madd<F>(acc, pt);
+    // Grid-stride over the length-ordered tasks (a thread's successive tasks are `gridDim.x * blockDim.x` apart in the
+    // order, so a warp still holds equal lengths).  By default the grid covers every task with its own thread;
+    // VSP_MSM_ACC_BLOCKS = k caps it at k blocks per SM.  Measured on B200 (ballot circuit, 256-ballot steps): two blocks
+    // per SM keep the integer pipe as busy as three (accumulation alone 118 -> 124 ms per step), but leaving that room to
+    // the other streams' kernels does not shorten the step (1,161 against 1,210 ballots/s; one block per SM 1,062), and
+    // neither do two or four independent stream sets proving disjoint halves of a batch concurrently
+    // (tools/dual_pipeline_probe.py: 1,315 / 1,319 / 1,325 ballots/s): the step is the sum of its kernels' work.
+    for (uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x; tid < n_tasks; tid += gridDim.x * blockDim.x) {
+        const uint32_t t = order[tid];
+        const Task k = tasks[t];
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t pos = k.begin; pos < k.end; ++pos) {
+            const uint32_t v = sorted[pos];
+            Affine<F> pt = Affine<F>::load(table + uint64_t(v & 0x7fffffffu) * PT_LIMBS);
+            if (v & 0x80000000u) pt.y = F::neg(pt.y);
+            ec_madd<F>(acc, pt);
+        }
+        acc.store(partial + uint64_t(t) * (XYZZ<F>::BYTES / 4));
     }
-    acc.store(partial + uint64_t(t) * (XYZZ<F>::BYTES / 4));
 }
 
 // The same sums in AFFINE coordinates on shared inversions (large launches: the H_query multiexp of a chunk of ballots,
@@ -979,7 +987,19 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
                                                          resident_threads / 128);
         }
     }
-    VSP_LAUNCH_K(ctx, KC_ACC, k_msm_accumulate<F>, (unsigned)((max_tasks + 127) / 128), 128, 0, s, bases.d_pts,
+    // VSP_MSM_ACC_SMEM (bytes of unused dynamic shared memory per block) caps the kernel's resident blocks per SM from
+    // the outside: an occupancy experiment (does leaving register-file room for the other streams' kernels pay?)
+    size_t acc_smem = 0;
+    if (const char* e = getenv("VSP_MSM_ACC_SMEM")) {
+        acc_smem = (size_t)atol(e);
+        if (acc_smem > 48 * 1024)
+            VSP_CUDA_CHECK(ctx, cudaFuncSetAttribute(k_msm_accumulate<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)acc_smem));
+    }
+    unsigned acc_per_sm = 0;
+    if (const char* e = getenv("VSP_MSM_ACC_BLOCKS")) acc_per_sm = (unsigned)atoi(e);  // 0: one block per 128 tasks (uncapped)
+    uint64_t acc_blocks = (max_tasks + 127) / 128;
+    if (acc_per_sm) acc_blocks = std::min<uint64_t>(acc_blocks, uint64_t(ctx->sm_count) * acc_per_sm);
+    VSP_LAUNCH_K(ctx, KC_ACC, k_msm_accumulate<F>, (unsigned)acc_blocks, 128, acc_smem, s, bases.d_pts,
                  sorted.as<uint32_t>(), tasks.as<Task>(), order.as<uint32_t>(), d_n_tasks, affine_min, partial.as<uint32_t>());
     // algorithmic work of this launch for the live roofline: bucket additions scheduled (= non-zero digits,
     // offsets[buckets]) x 11 field multiplications (the reference's mixed Jacobian add) x I_mul(limbs)
