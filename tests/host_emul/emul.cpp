@@ -81,7 +81,28 @@ static void ecop(int op, const uint64_t* a, const uint64_t* b, uint32_t k, uint6
     st_aff<F>(out, r);
 }
 
+// op 0: redc(mul_wide(a, b)) on raw limbs (a, b any N-limb values with a b < p 2^(32N));  1: fp_mul_sub_mul(a, b, c, d)
+template <class C>
+static void wideop(int op, const uint64_t* a, const uint64_t* b, const uint64_t* c, const uint64_t* d, uint64_t* out) {
+    if (op == 0) {
+        uint32_t T[2 * C::N];
+        fp_mul_wide<C>(ld<C>(a), ld<C>(b), T);
+        st<C>(out, fp_redc<C>(T));
+    } else {
+        st<C>(out, fp_mul_sub_mul<C>(ld<C>(a), ld<C>(b), ld<C>(c), ld<C>(d)));
+    }
+}
+
 extern "C" {
+void emul_fq_wide(int op, const uint64_t* a, const uint64_t* b, const uint64_t* c, const uint64_t* d, uint64_t* out) { wideop<FqCfg>(op, a, b, c, d, out); }
+void emul_fr_wide(int op, const uint64_t* a, const uint64_t* b, const uint64_t* c, const uint64_t* d, uint64_t* out) { wideop<FrCfg>(op, a, b, c, d, out); }
+// Fq2 on raw Montgomery-domain limbs (c0 | c1): op 0 mul, 1 sqr, 2 mul_sub_mul(a, b, c, d)
+void emul_fq2_raw(int op, const uint64_t* a, const uint64_t* b, const uint64_t* c, const uint64_t* d, uint64_t* out) {
+    auto L = [](const uint64_t* p) { return Fq2{ld<FqCfg>(p), ld<FqCfg>(p + 6)}; };
+    Fq2 r = op == 0 ? Fq2Ops::mul(L(a), L(b)) : op == 1 ? Fq2Ops::sqr(L(a)) : Fq2Ops::mul_sub_mul(L(a), L(b), L(c), L(d));
+    st<FqCfg>(out, r.c0);
+    st<FqCfg>(out + 6, r.c1);
+}
 void emul_fr_op(int op, const uint64_t* a, const uint64_t* b, uint64_t* out) { binop<FrCfg>(op, a, b, out); }
 void emul_fq_op(int op, const uint64_t* a, const uint64_t* b, uint64_t* out) { binop<FqCfg>(op, a, b, out); }
 void emul_g1_op(int op, const uint64_t* a, const uint64_t* b, uint32_t k, uint64_t* out) { ecop<FqOps>(op, a, b, k, out); }

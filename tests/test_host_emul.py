@@ -111,3 +111,63 @@ def test_division_step_inverse_stress(emul, name, mod, limbs):
         A[:] = ints_to_limbs([a], limbs)
         fn(7, P(A), P(A), P(O))
         assert limbs_to_ints(O)[0] == (pow(a, -1, mod) if a else 0), hex(a)
+
+
+@pytest.mark.parametrize("name,mod,limbs", [("fr", o.R, 4), ("fq", o.P, 6)])
+def test_double_width_product_and_shared_reduction(emul, name, mod, limbs):
+    """fp_mul_wide + fp_redc (lazy reduction): operands up to 2p - 2 (an unreduced sum), limb patterns that fire every carry
+    path, and a b - c d on one reduction, against Python integers"""
+    fn = getattr(emul, "emul_%s_wide" % name)
+    rinv = pow(1 << (64 * limbs), -1, mod)
+    rng = random.Random(17 + limbs)
+    pat = [0, 0xffffffff, 1, 0x80000000]
+
+    def biased(bound):
+        while True:
+            v = sum(rng.choice(pat + [rng.getrandbits(32)]) << (32 * i) for i in range(2 * limbs))
+            v %= bound
+            if v:
+                return v
+
+    Z = np.zeros((1, limbs), np.uint64)
+    for it in range(600):
+        a, b = (biased(2 * mod - 1), biased(2 * mod - 1)) if it % 2 else (rng.randrange(mod), rng.randrange(mod))
+        O = np.zeros((1, limbs), np.uint64)
+        fn(0, P(ints_to_limbs([a], limbs)), P(ints_to_limbs([b], limbs)), P(Z), P(Z), P(O))
+        assert limbs_to_ints(O)[0] == a * b * rinv % mod, (hex(a), hex(b))
+        a, b, c, d = (biased(mod) for _ in range(4)) if it % 2 else (rng.randrange(mod) for _ in range(4))
+        fn(1, P(ints_to_limbs([a], limbs)), P(ints_to_limbs([b], limbs)), P(ints_to_limbs([c], limbs)), P(ints_to_limbs([d], limbs)), P(O))
+        assert limbs_to_ints(O)[0] == (a * b - c * d) * rinv % mod
+    for a, b, c, d in ((mod - 1, mod - 1, 0, 0), (0, 0, mod - 1, mod - 1), (mod - 1, mod - 1, mod - 1, mod - 1), (1, 1, mod - 1, mod - 1)):
+        O = np.zeros((1, limbs), np.uint64)
+        fn(1, P(ints_to_limbs([a], limbs)), P(ints_to_limbs([b], limbs)), P(ints_to_limbs([c], limbs)), P(ints_to_limbs([d], limbs)), P(O))
+        assert limbs_to_ints(O)[0] == (a * b - c * d) * rinv % mod
+
+
+def test_fq2_lazy_products(emul):
+    """Fq2Ops::mul / sqr / mul_sub_mul (three double-width products, two reductions) on raw Montgomery-domain limbs"""
+    p = o.P
+    rinv = pow(1 << 384, -1, p)
+    rng = random.Random(23)
+    edge = [0, 1, p - 1, p - 2, (1 << 384) % p]
+
+    def f2mul(x, y):
+        return ((x[0] * y[0] - x[1] * y[1]) % p, (x[0] * y[1] + x[1] * y[0]) % p)
+
+    def pack(x):
+        return np.concatenate([ints_to_limbs([x[0]], 6)[0], ints_to_limbs([x[1]], 6)[0]])
+
+    cases = [tuple((rng.choice(edge), rng.choice(edge)) for _ in range(4)) for _ in range(60)]
+    cases += [tuple((rng.randrange(p), rng.randrange(p)) for _ in range(4)) for _ in range(300)]
+    for a, b, c, d in cases:
+        O = np.zeros(12, np.uint64)
+        A, B, Cc, D = pack(a), pack(b), pack(c), pack(d)
+        emul.emul_fq2_raw(0, P(A), P(B), P(Cc), P(D), P(O))
+        want = f2mul(a, b)
+        assert tuple(limbs_to_ints(O.reshape(2, 6))) == (want[0] * rinv % p, want[1] * rinv % p)
+        emul.emul_fq2_raw(1, P(A), P(B), P(Cc), P(D), P(O))
+        want = f2mul(a, a)
+        assert tuple(limbs_to_ints(O.reshape(2, 6))) == (want[0] * rinv % p, want[1] * rinv % p)
+        emul.emul_fq2_raw(2, P(A), P(B), P(Cc), P(D), P(O))
+        ab, cd = f2mul(a, b), f2mul(c, d)
+        assert tuple(limbs_to_ints(O.reshape(2, 6))) == ((ab[0] - cd[0]) * rinv % p, (ab[1] - cd[1]) * rinv % p)

@@ -129,6 +129,7 @@ struct FqCfg {
     __host__ __device__ static constexpr uint32_t mod(int i) { return VSP_FQ_MOD(i); }
     __host__ __device__ static constexpr uint32_t r1(int i) { return VSP_FQ_R1(i); }
     __host__ __device__ static constexpr uint32_t r2(int i) { return VSP_FQ_R2(i); }
+    __host__ __device__ static constexpr uint32_t p2(int i) { return VSP_FQ_P2(i); }
 };
 struct FrCfg {
     static constexpr int N = VSP_FR_LIMBS;
@@ -136,6 +137,7 @@ struct FrCfg {
     __host__ __device__ static constexpr uint32_t mod(int i) { return VSP_FR_MOD(i); }
     __host__ __device__ static constexpr uint32_t r1(int i) { return VSP_FR_R1(i); }
     __host__ __device__ static constexpr uint32_t r2(int i) { return VSP_FR_R2(i); }
+    __host__ __device__ static constexpr uint32_t p2(int i) { return VSP_FR_P2(i); }
 };
 
 template <class C>
@@ -214,6 +216,18 @@ VSP_DEV Fp<C> fp_sub(const Fp<C>& a, const Fp<C>& b) {
 #pragma unroll
     for (int i = 1; i < N - 1; ++i) r.l[i] = ptx::addc_cc(r.l[i], C::mod(i) & mask);
     r.l[N - 1] = ptx::addc(r.l[N - 1], C::mod(N - 1) & mask);
+    return r;
+}
+
+// a + b without the conditional subtraction (< 2p < 2^(32N)): an operand for fp_mul_wide
+template <class C>
+VSP_DEV Fp<C> fp_add_raw(const Fp<C>& a, const Fp<C>& b) {
+    constexpr int N = C::N;
+    Fp<C> r;
+    r.l[0] = ptx::add_cc(a.l[0], b.l[0]);
+#pragma unroll
+    for (int i = 1; i < N - 1; ++i) r.l[i] = ptx::addc_cc(a.l[i], b.l[i]);
+    r.l[N - 1] = ptx::addc(a.l[N - 1], b.l[N - 1]);
     return r;
 }
 
@@ -316,6 +330,121 @@ VSP_DEV Fp<C> fp_mul(const Fp<C>& a, const Fp<C>& b) {
     return r;
 }
 
+// Montgomery reduction of a double-width value: T / 2^(32N) mod p for T < p 2^(32N), fully reduced.  Column by column
+// on the sliding (E, O) frame of mont_reduce_column: frame value = E + O 2^32 over limbs [i, i + N]; the frame's shift is
+// a role swap, the carry of O[0] + E[1] rides into the next column's multiply chain, and limb N + i of T enters the
+// frame's top as row i leaves.  N^2 + N multiply-adds.
+template <class C>
+VSP_DEV Fp<C> fp_redc(const uint32_t (&T)[2 * C::N]) {
+    constexpr int N = C::N;
+    uint32_t E[N], O[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        E[k] = T[k];
+        O[k] = 0u;
+    }
+    mont_reduce_column<C>(E, O);  // E[0] = 0 now
+#pragma unroll
+    for (int i = 0; i < N - 1; ++i) {
+        uint32_t nO[N];
+#pragma unroll
+        for (int k = 0; k < N - 2; ++k) nO[k] = E[k + 2];
+        nO[N - 2] = T[N + i];
+        nO[N - 1] = 0u;
+        const uint32_t e0 = ptx::add_cc(O[0], E[1]);
+#pragma unroll
+        for (int k = 1; k < N; ++k) E[k] = O[k];
+        E[0] = e0;
+#pragma unroll
+        for (int k = 0; k < N; ++k) O[k] = nO[k];
+        mont_reduce_column<C, true>(E, O);
+    }
+    Fp<C> r;
+    r.l[0] = ptx::add_cc(O[0], E[1]);
+#pragma unroll
+    for (int k = 1; k < N - 1; ++k) r.l[k] = ptx::addc_cc(O[k], E[k + 1]);
+    r.l[N - 1] = ptx::addc(O[N - 1], T[2 * N - 1]);
+    fp_reduce_once(r);
+    return r;
+}
+
+// a * b as a 2N-limb integer, no reduction (N^2 multiply-adds).  Operands may be any N-limb values (e.g. an unreduced
+// sum a0 + a1 < 2p).  Same two-accumulator discipline as fp_mul: a product landing on an even column goes to the pair
+// Ev[c], Ev[c + 1], on an odd column to Od[c - 1], Od[c]; rows in increasing order, so the limb above a row's chain has
+// only ever held carries when the chain's last carry is added to it.
+template <class C>
+VSP_DEV void fp_mul_wide(const Fp<C>& a, const Fp<C>& b, uint32_t (&T)[2 * C::N]) {
+    constexpr int N = C::N;
+    uint32_t Ev[2 * N], Od[2 * N];
+#pragma unroll
+    for (int k = 0; k < 2 * N; ++k) Ev[k] = Od[k] = 0u;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const uint32_t bi = b.l[i];
+        // columns i + j with j of i's parity are even when i is even: they go to Ev if (i + j) is even
+        {
+            const int j0 = i & 1;  // (i + j) even
+#pragma unroll
+            for (int j = j0; j < N; j += 2) {
+                const int c = i + j;
+                Ev[c] = (j == j0) ? ptx::mad_lo_cc(a.l[j], bi, Ev[c]) : ptx::madc_lo_cc(a.l[j], bi, Ev[c]);
+                Ev[c + 1] = ptx::madc_hi_cc(a.l[j], bi, Ev[c + 1]);
+            }
+            const int top = i + (N - 2 + j0) + 2;  // limb above the chain
+            if (top < 2 * N) Ev[top] = ptx::addc(Ev[top], 0u);
+        }
+        {
+            const int j0 = 1 - (i & 1);  // (i + j) odd
+#pragma unroll
+            for (int j = j0; j < N; j += 2) {
+                const int c = i + j - 1;
+                Od[c] = (j == j0) ? ptx::mad_lo_cc(a.l[j], bi, Od[c]) : ptx::madc_lo_cc(a.l[j], bi, Od[c]);
+                Od[c + 1] = ptx::madc_hi_cc(a.l[j], bi, Od[c + 1]);
+            }
+            const int top = i + (N - 2 + j0) - 1 + 2;
+            if (top < 2 * N) Od[top] = ptx::addc(Od[top], 0u);
+        }
+    }
+    T[0] = Ev[0];
+    T[1] = ptx::add_cc(Ev[1], Od[0]);
+#pragma unroll
+    for (int k = 2; k < 2 * N - 1; ++k) T[k] = ptx::addc_cc(Ev[k], Od[k - 1]);
+    T[2 * N - 1] = ptx::addc(Ev[2 * N - 1], Od[2 * N - 2]);
+}
+// double-width helpers: T += U, T -= U (no overflow / no borrow by the callers' bounds), T += p^2
+template <int M>
+VSP_DEV void wide_add(uint32_t (&T)[M], const uint32_t (&U)[M]) {
+    T[0] = ptx::add_cc(T[0], U[0]);
+#pragma unroll
+    for (int k = 1; k < M - 1; ++k) T[k] = ptx::addc_cc(T[k], U[k]);
+    T[M - 1] = ptx::addc(T[M - 1], U[M - 1]);
+}
+template <int M>
+VSP_DEV void wide_sub(uint32_t (&T)[M], const uint32_t (&U)[M]) {
+    T[0] = ptx::sub_cc(T[0], U[0]);
+#pragma unroll
+    for (int k = 1; k < M - 1; ++k) T[k] = ptx::subc_cc(T[k], U[k]);
+    T[M - 1] = ptx::subc(T[M - 1], U[M - 1]);
+}
+template <class C>
+VSP_DEV void wide_add_p2(uint32_t (&T)[2 * C::N]) {
+    constexpr int M = 2 * C::N;
+    T[0] = ptx::add_cc(T[0], C::p2(0));
+#pragma unroll
+    for (int k = 1; k < M - 1; ++k) T[k] = ptx::addc_cc(T[k], C::p2(k));
+    T[M - 1] = ptx::addc(T[M - 1], C::p2(M - 1));
+}
+// a b - c d mod p on ONE reduction: (a b - c d + p^2) / 2^(32N), all four operands fully reduced
+template <class C>
+VSP_DEV Fp<C> fp_mul_sub_mul(const Fp<C>& a, const Fp<C>& b, const Fp<C>& c, const Fp<C>& d) {
+    uint32_t T[2 * C::N], U[2 * C::N];
+    fp_mul_wide<C>(a, b, T);
+    fp_mul_wide<C>(c, d, U);
+    wide_add_p2<C>(T);
+    wide_sub(T, U);
+    return fp_redc<C>(T);
+}
+
 // Montgomery square a^2 / 2^(32N) mod p.  The N(N-1)/2 cross products a_i a_j (i < j) are formed once and doubled, so a
 // square costs N(N-1)/2 + N + N^2 + N multiply-adds (Fq: 234, Fr: 108) against the product's 2N^2 + N (300 / 136).
 // Same two-accumulator discipline as fp_mul so every lo/hi pair is one IMAD.WIDE: a product landing on an even 32-bit
@@ -374,39 +503,7 @@ VSP_DEV Fp<C> fp_sqr(const Fp<C>& a) {
     }
     T[2 * N - 2] = ptx::madc_lo_cc(a.l[N - 1], a.l[N - 1], T[2 * N - 2]);
     T[2 * N - 1] = ptx::madc_hi(a.l[N - 1], a.l[N - 1], T[2 * N - 1]);
-    // reduction: frame value = E + O 2^32 over limbs [i, i + N]
-    uint32_t E[N], O[N];
-#pragma unroll
-    for (int k = 0; k < N; ++k) {
-        E[k] = T[k];
-        O[k] = 0u;
-    }
-    mont_reduce_column<C>(E, O);  // E[0] = 0 now
-#pragma unroll
-    for (int i = 0; i < N - 1; ++i) {
-        // frame shift by one limb: the old O becomes the even accumulator, the old E >> 64 (topped up with limb N + i of
-        // T) the odd one; the carry of O[0] + E[1] belongs to column 1 of the new frame and rides into the next
-        // column's O chain (its last addc cannot overflow: the frame value stays below 2^(32 (N + 1)))
-        uint32_t nO[N];
-#pragma unroll
-        for (int k = 0; k < N - 2; ++k) nO[k] = E[k + 2];
-        nO[N - 2] = T[N + i];
-        nO[N - 1] = 0u;
-        const uint32_t e0 = ptx::add_cc(O[0], E[1]);
-#pragma unroll
-        for (int k = 1; k < N; ++k) E[k] = O[k];
-        E[0] = e0;
-#pragma unroll
-        for (int k = 0; k < N; ++k) O[k] = nO[k];
-        mont_reduce_column<C, true>(E, O);
-    }
-    Fp<C> r;
-    r.l[0] = ptx::add_cc(O[0], E[1]);
-#pragma unroll
-    for (int k = 1; k < N - 1; ++k) r.l[k] = ptx::addc_cc(O[k], E[k + 1]);
-    r.l[N - 1] = ptx::addc(O[N - 1], T[2 * N - 1]);
-    fp_reduce_once(r);
-    return r;
+    return fp_redc<C>(T);
 }
 
 template <class C>

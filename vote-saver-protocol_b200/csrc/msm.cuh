@@ -30,10 +30,11 @@ int msm_run(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64_t n_scal
             uint64_t* d_out, bool raw_xyzz = false, unsigned batch = 1, uint64_t scalar_stride = 0,
             uint64_t out_stride = 0);
 
-// 32x32->64 multiply-adds k_msm_accumulate<G1> issues per bucket addition: the XYZZ mixed addition is 8 products
-// (2 * 12^2 + 12 = 300 each) + 2 squares (12 * 11 / 2 + 12 + 12^2 + 12 = 234 each).  bench.py's roofline quotes it beside
-// the reference algorithm's 11 x 300.
-constexpr double ACC_G1_MADS_PER_ADD = 8 * 300.0 + 2 * 234.0;
+// 32x32->64 multiply-adds k_msm_accumulate<G1> issues per bucket addition: the XYZZ mixed addition is 6 products
+// (2 * 12^2 + 12 = 300 each), 2 squares (12 * 11 / 2 + 12 + 12^2 + 12 = 234 each) and Y3 = R (Q - X3) - Y1 PPP as two
+// double-width products on one reduction (2 * 144 + 156 = 444).  bench.py's roofline quotes it beside the reference
+// algorithm's 11 x 300.
+constexpr double ACC_G1_MADS_PER_ADD = 6 * 300.0 + 2 * 234.0 + 444.0;
 
 // out = sum of k affine canonical points (device pointers)
 int points_sum_dev(vsp_ctx* ctx, cudaStream_t s, bool g2, uint64_t k, const uint64_t* d_points, uint64_t* d_out);

@@ -1022,6 +1022,7 @@ static int msm_run_t(vsp_ctx* ctx, cudaStream_t s, const BasesDev& bases, uint64
     {
         const unsigned total_log = p.nb_log + floor_log2_u64(n_sets);
         if (total_log > 14 + 1) seg_log = total_log - 14;
+        if (p.sets == 1 && seg_log > 4) seg_log = 4;  // batched ballots: SEG = 16 measured best at 64, 128 and 256 per chunk
         if (const char* e = getenv("VSP_MSM_SEG_LOG")) seg_log = (unsigned)atoi(e);  // tuning override
         if (seg_log < 1) seg_log = 1;
         if (seg_log > SEG_LOG_MAX) seg_log = SEG_LOG_MAX;
