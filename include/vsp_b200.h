@@ -229,6 +229,14 @@ VSP_API int vsp_prove_partial_dev(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t
 VSP_API int vsp_prove_assemble_dev(vsp_ctx *ctx, const vsp_pk *pk, uint64_t world, const uint64_t *d_gathered,
                                    const uint64_t r[4], const uint64_t s[4], const uint64_t *r_saver,
                                    const uint64_t *gamma_inverse_sum_s_g1, uint64_t *d_proof);
+/* vsp_prove_partial_dev in two calls, with room for an exchange between them: the three coset extensions of the witness
+ * map (inverse_fft, multiply_by_coset, fft of aA, aB, aC) are independent, so G ranks can each extend the vectors of
+ * `vector_mask` (bit 0 aA, bit 1 aB, bit 2 aC) into d_abc (3 m Fr, caller-owned device memory), broadcast them to each
+ * other while the A / L / B multiexps already run on the side streams, and finish: H on the coset, its coefficients, the H
+ * multiexp.  begin with vector_mask = 7 followed by finish equals vsp_prove_partial_dev. */
+VSP_API int vsp_prove_partial_begin_dev(vsp_ctx *ctx, const vsp_pk *pk, const uint64_t *d_assignment, unsigned vector_mask,
+                                        uint64_t *d_abc, uint64_t *d_partials);
+VSP_API int vsp_prove_partial_finish_dev(vsp_ctx *ctx, const vsp_pk *pk, uint64_t *d_abc, uint64_t *d_partials);
 
 /* SAVER: ciphertext (msg_size + 2 G1) and the encrypted_input proof in one call */
 VSP_API int vsp_saver_encrypt(vsp_ctx *ctx, const vsp_pk *pk, const vsp_saver_pubkey_t *pub, const uint64_t *gamma_abc_rest,

@@ -99,3 +99,56 @@ def test_sharded_prover_over_nccl_two_gpus():
                           "--master-addr", "127.0.0.1", "--master-port", "29611", os.path.join(here, "dist_sharded_check.py")],
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "SHARDED_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_split_witness_map_begin_finish(vsp, ctx):
+    """vsp_prove_partial_begin_dev / _finish_dev: three emulated ranks each extend one of aA, aB, aC to the coset, the
+    'broadcast' is a device copy of the owner's vector into the others' buffers, and the finished shares assemble to the
+    oracle's proof (basic and step domains); begin with mask 7 + finish equals prove_partial_dev"""
+    import torch
+    sh = importlib.import_module("vote-saver-protocol_b200.sharded")
+    for nc, ni in ((97, 30), (1057, 30)):
+        world = 3
+        cs, primary, aux = synthetic_r1cs(nc, ni, seed=nc + 5)
+        arr = synthetic_pk_arrays(cs, nc + 3)
+        P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+        _, m = vsp.domain_plan(nc + ni + 1)
+        d_assign = torch.from_numpy(np.concatenate([cref.ints_to_limbs([1], 4), P, A]).view(np.int64)).cuda()
+        gathered = torch.zeros((world, sh.PARTIAL_LIMBS), dtype=torch.int64, device="cuda")
+        abc = [torch.zeros((3, m * 4), dtype=torch.int64, device="cuda") for _ in range(world)]
+        keys = []
+        owners = sh.vector_owners(world)
+        for rank in range(world):
+            sliced, rng = sh.slice_proving_key(arr, m, rank, world)
+            pk = vsp.ProvingKey(ctx, sliced, slice=rng)
+            mask = sum(1 << v for v in range(3) if owners[v] == rank)
+            pk.prove_partial_begin_dev(d_assign.data_ptr(), mask, abc[rank].data_ptr(), gathered[rank].data_ptr())
+            keys.append(pk)
+        ctx.synchronize()
+        for v in range(3):  # the exchange
+            for rank in range(world):
+                if rank != owners[v]:
+                    abc[rank][v].copy_(abc[owners[v]][v])
+        torch.cuda.synchronize()
+        for rank in range(world):
+            keys[rank].prove_partial_finish_dev(abc[rank].data_ptr(), gathered[rank].data_ptr())
+        d_proof = torch.zeros(48, dtype=torch.int64, device="cuda")
+        r, s = 0x1234, o.R - 99
+        keys[1].prove_assemble_dev(world, gathered.data_ptr(), r, s, d_proof.data_ptr())
+        ctx.synchronize()
+        opk = fx.fill_pk(cref.ProvingKeyDesc(), arr)
+        assert np.array_equal(d_proof.cpu().numpy().view(np.uint64), cref.groth16_prove(opk, P, A, r, s))
+        # mask 7 on one rank = the undivided call
+        one = torch.zeros(sh.PARTIAL_LIMBS, dtype=torch.int64, device="cuda")
+        two = torch.zeros(sh.PARTIAL_LIMBS, dtype=torch.int64, device="cuda")
+        keys[0].prove_partial_dev(d_assign.data_ptr(), one.data_ptr())
+        keys[0].prove_partial_begin_dev(d_assign.data_ptr(), 7, abc[0].data_ptr(), two.data_ptr())
+        keys[0].prove_partial_finish_dev(abc[0].data_ptr(), two.data_ptr())
+        # raw XYZZ shares are projective (their limbs depend on the order the sort left inside each bucket): compare the points
+        pa, pb = torch.zeros(48, dtype=torch.int64, device="cuda"), torch.zeros(48, dtype=torch.int64, device="cuda")
+        keys[0].prove_assemble_dev(1, one.data_ptr(), r, s, pa.data_ptr())
+        keys[0].prove_assemble_dev(1, two.data_ptr(), r, s, pb.data_ptr())
+        ctx.synchronize()
+        assert torch.equal(pa, pb)
+        for k in keys:
+            k.close()

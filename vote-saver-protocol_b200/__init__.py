@@ -422,6 +422,15 @@ class ProvingKey:
         self.ctx.check(self.ctx._lib.vsp_prove_partial_dev(self.ctx._h, self._h, C.c_void_p(d_assignment),
                                                            C.c_void_p(d_partials)))
 
+    def prove_partial_begin_dev(self, d_assignment: int, vector_mask: int, d_abc: int, d_partials: int):
+        """first half of prove_partial_dev: multiexps A / L / B started, coset extension of the vectors in vector_mask
+        (bit 0 aA, 1 aB, 2 aC) left in d_abc (3 m Fr)"""
+        self.ctx.check(self.ctx._lib.vsp_prove_partial_begin_dev(self.ctx._h, self._h, C.c_void_p(d_assignment), int(vector_mask),
+                                                                 C.c_void_p(d_abc), C.c_void_p(d_partials)))
+
+    def prove_partial_finish_dev(self, d_abc: int, d_partials: int):
+        self.ctx.check(self.ctx._lib.vsp_prove_partial_finish_dev(self.ctx._h, self._h, C.c_void_p(d_abc), C.c_void_p(d_partials)))
+
     def prove_assemble_dev(self, world: int, d_gathered: int, r: int, s: int, d_proof: int,
                            pubkey: SaverPublicKey | None = None, r_saver: int | None = None):
         """d_gathered: world x 144 limbs (the all_gather of every rank's prove_partial_dev); proof left at d_proof"""

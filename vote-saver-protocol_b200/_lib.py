@@ -125,6 +125,8 @@ SYMBOLS = [
     ("vsp_prove_partial", _int, [_vp, _vp, _vp, _vp, _vp]),
     ("vsp_prove_assemble", _int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_prove_partial_dev", _int, [_vp, _vp, _vp, _vp]),
+    ("vsp_prove_partial_begin_dev", _int, [_vp, _vp, _vp, C.c_uint, _vp, _vp]),
+    ("vsp_prove_partial_finish_dev", _int, [_vp, _vp, _vp, _vp]),
     ("vsp_prove_assemble_dev", _int, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_pk_destroy", None, [_vp]),
     ("vsp_pk_domain_size", _u64, [_vp]),

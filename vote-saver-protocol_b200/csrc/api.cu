@@ -117,6 +117,7 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
     for (int i = 0; i < 2; ++i) {
         if (ctx->tail[i].done) cudaEventDestroy(ctx->tail[i].done);
         if (ctx->tail[i].p) cudaFree(ctx->tail[i].p);
+        if (i == 0 && ctx->partial_bsc) cudaFree(ctx->partial_bsc);
     }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -67,6 +67,8 @@ struct vsp_ctx {
         bool pending = false;
     } tail[2];
     unsigned tail_next = 0;
+    void* partial_bsc = nullptr;  // gathered B-query scalars between vsp_prove_partial_begin_dev and _finish_dev
+    size_t partial_bsc_cap = 0;
     int batch_chunk = 0;  // ballots per chunk of the batched prover (0: VSP_BATCH_CHUNK or 64); vsp_ctx_set_batch_chunk
     cudaEvent_t ev_main = nullptr;
     vsp::KProf prof;

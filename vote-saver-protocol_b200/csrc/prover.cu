@@ -741,8 +741,20 @@ static int coset_lde(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, uint32_t* d
 
 // d_w: B assignments (1 || primary || aux), canonical, w_stride elements apart.  abc: 3 B m Fr of scratch; on return
 // abc[0 .. B m) holds coefficients_for_H[0..m) of every ballot (canonical).  Everything on stream s.
+// The map in two halves, so that a proof sharded over several GPUs can split the three independent coset extensions
+// (inverse_fft, multiply_by_coset, fft of aA, aB, aC) between ranks and exchange the results:
+//   witness_map_evaluate  constraint evaluation for all three, coset extension of the vectors in `mask` (bit v: vector v)
+//   witness_map_finish    H = (A o B - C) / Z on the coset, back to coefficients
+static int witness_map_evaluate(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const uint32_t* d_w, uint64_t w_stride,
+                                unsigned B, uint32_t* abc, unsigned mask);
+static int witness_map_finish(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, unsigned B, uint32_t* abc);
 static int witness_map_dev(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const uint32_t* d_w, uint64_t w_stride,
                            unsigned B, uint32_t* abc) {
+    VSP_TRY(witness_map_evaluate(ctx, s, pk, d_w, w_stride, B, abc, 7u));
+    return witness_map_finish(ctx, s, pk, B, abc);
+}
+static int witness_map_evaluate(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const uint32_t* d_w, uint64_t w_stride,
+                                unsigned B, uint32_t* abc, unsigned mask) {
     const uint64_t m = pk->m;
     CsrDev csr;
     for (int i = 0; i < 3; ++i) {
@@ -750,7 +762,6 @@ static int witness_map_dev(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const
         csr.col[i] = pk->d_col[i];
         csr.val[i] = pk->d_val[i];
     }
-    uint32_t *aA = abc, *aB = abc + 8 * (uint64_t(B) * m), *aC = abc + 8 * (uint64_t(2 * B) * m);
     if (pk->short_rows)
         VSP_LAUNCH_K(ctx, KC_QAP, k_r1cs_eval_rows, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, csr, d_w, w_stride,
                      pk->nc, pk->ni, m, abc);
@@ -766,7 +777,14 @@ static int witness_map_dev(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, const
                      m, long_part.as<uint32_t>(), abc);
     }
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
-    VSP_TRY(coset_lde(ctx, s, pk, abc, 3 * B));
+    if ((mask & 7u) == 7u) return coset_lde(ctx, s, pk, abc, 3 * B);
+    for (unsigned v = 0; v < 3; ++v)
+        if (mask & (1u << v)) VSP_TRY(coset_lde(ctx, s, pk, abc + 8 * (uint64_t(v) * B * m), B));
+    return VSP_OK;
+}
+static int witness_map_finish(vsp_ctx* ctx, cudaStream_t s, const vsp_pk* pk, unsigned B, uint32_t* abc) {
+    const uint64_t m = pk->m;
+    uint32_t *aA = abc, *aB = abc + 8 * (uint64_t(B) * m), *aC = abc + 8 * (uint64_t(2 * B) * m);
     VSP_LAUNCH_K(ctx, KC_QAP, k_h_pointwise, dim3((unsigned)((m + 127) / 128), B), 128, 0, s, aA, aB, aC, pk->d_zinv, m);
     VSP_CUDA_CHECK(ctx, cudaGetLastError());
     if (pk->kind == VSP_DOMAIN_BASIC_RADIX2) {
@@ -1298,6 +1316,63 @@ static int assemble_impl(vsp_ctx* ctx, vsp_pk* pk, const uint32_t* ev, const uin
     return VSP_OK;
 }
 }  // namespace vsp
+
+// vsp_prove_partial_dev in two calls with room for an exchange between them (sharded.ShardedProver.prove_dev):
+//   begin   the A / L / B multiexps start on the side streams; on the main stream the constraint evaluation and the coset
+//           extension of the vectors in `vector_mask` (bit 0 aA, 1 aB, 2 aC), left in d_abc (3 m Fr, caller-owned)
+//   ...     the ranks exchange the extended vectors (three broadcasts of m Fr over NCCL) while the multiexps run
+//   finish  H on the coset, its coefficients, the H multiexp; joins the side streams; d_partials complete
+extern "C" int vsp_prove_partial_begin_dev(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* d_assignment, unsigned vector_mask,
+                                           uint64_t* d_abc, uint64_t* d_partials) {
+    if (!ctx || !pk || !d_assignment || !d_abc || !d_partials) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStream_t s = ctx->stream;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(d_assignment);
+    const uint64_t stride = pk->nv + 1;
+    uint64_t* o = d_partials;
+    // the gathered B scalars must outlive this call: they live behind the three vectors' scratch in a context-owned buffer
+    if (ctx->partial_bsc_cap < (pk->B_count ? pk->B_count : 1) * 32) {
+        if (ctx->partial_bsc) cudaFree(ctx->partial_bsc);
+        ctx->partial_bsc = nullptr;
+        ctx->partial_bsc_cap = 0;
+        VSP_CUDA_CHECK(ctx, cudaMalloc(&ctx->partial_bsc, (pk->B_count ? pk->B_count : 1) * 32));
+        ctx->partial_bsc_cap = (pk->B_count ? pk->B_count : 1) * 32;
+    }
+    uint32_t* bsc = reinterpret_cast<uint32_t*>(ctx->partial_bsc);
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_fork, s));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 2), ctx->ev_fork, 0));
+    VSP_CUDA_CHECK(ctx, cudaStreamWaitEvent(side_stream(ctx, 3), ctx->ev_fork, 0));
+    int rc = msm_run(ctx, side_stream(ctx, 2), pk->A, pk->A_n, w + 8 * pk->A_lo, o, true);
+    if (rc == VSP_OK) rc = msm_run(ctx, side_stream(ctx, 2), pk->L, pk->L_n, w + 8 * (pk->ni + 1 + pk->L_lo), o + 72, true);
+    cudaEventRecord(ctx->ev_join[2], side_stream(ctx, 2));
+    cudaStream_t s3 = side_stream(ctx, 3);
+    if (rc == VSP_OK && pk->B_count)
+        VSP_LAUNCH_K(ctx, KC_QAP, k_gather_fr, dim3((unsigned)((pk->B_count + 127) / 128), 1), 128, 0, s3, w, stride, pk->d_B_idx,
+                     pk->B_count, bsc);
+    if (rc == VSP_OK) rc = msm_run(ctx, s3, pk->Bg2, pk->B_count, bsc, o + 96, true);
+    if (rc == VSP_OK) rc = msm_run(ctx, s3, pk->Bg1, pk->B_count, bsc, o + 24, true);
+    cudaEventRecord(ctx->ev_join[3], s3);
+    if (rc == VSP_OK)
+        rc = witness_map_evaluate(ctx, s, pk, w, stride, 1, reinterpret_cast<uint32_t*>(d_abc), vector_mask & 7u);
+    if (rc != VSP_OK) {  // nothing of this call may still be running when the caller releases its buffers
+        cudaStreamWaitEvent(s, ctx->ev_join[2], 0);
+        cudaStreamWaitEvent(s, ctx->ev_join[3], 0);
+    }
+    return rc;
+}
+extern "C" int vsp_prove_partial_finish_dev(vsp_ctx* ctx, const vsp_pk* pk, uint64_t* d_abc, uint64_t* d_partials) {
+    if (!ctx || !pk || !d_abc || !d_partials) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStream_t s = ctx->stream;
+    uint32_t* abc = reinterpret_cast<uint32_t*>(d_abc);
+    int rc = witness_map_finish(ctx, s, pk, 1, abc);
+    if (rc == VSP_OK) rc = msm_run(ctx, s, pk->H, pk->H_n, abc + 8 * pk->H_lo, d_partials + 48, true);
+    cudaStreamWaitEvent(s, ctx->ev_join[2], 0);
+    cudaStreamWaitEvent(s, ctx->ev_join[3], 0);
+    if (rc != VSP_OK) return rc;
+    VSP_CUDA_CHECK(ctx, cudaGetLastError());
+    return VSP_OK;
+}
 
 // out_partials: evA | evB1 | evH | evL (G1 affine) | evB2 (G2 affine) = 4 * 12 + 24 = 72 limbs, canonical
 extern "C" int vsp_prove_partial(vsp_ctx* ctx, const vsp_pk* pk, const uint64_t* primary, const uint64_t* aux,

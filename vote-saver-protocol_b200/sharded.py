@@ -177,6 +177,13 @@ def key_ranges(cs: dict, m: int, n_b: int, rank: int, world: int) -> dict:
             "H": shard_range(m - 1, rank, world), "L": shard_range(na, rank, world)}
 
 
+def vector_owners(world: int):
+    """rank that extends aA, aB, aC to the coset in a sharded proof: three different ranks from world 3 up, (0, 1, 0) at 2"""
+    if world >= 3:
+        return (0, 1, 2)
+    return (0, 1 % max(world, 1), 0)
+
+
 PARTIAL_LIMBS = 144  # raw XYZZ shares of vsp_prove_partial_dev: evA | evB1 | evH | evL (24 limbs each) | evB2 (48)
 
 
@@ -203,6 +210,13 @@ class ShardedProver:
             arrays, self.ranges = slice_proving_key(arrays, self.m, self.rank, self.world)
         self.pk = vsp.ProvingKey(ctx, arrays, slice=self.ranges)
         self._bufs = None
+        self._abc = None
+        # share the witness map's three coset extensions between ranks (prove_dev); off: every rank computes all three
+        self.split_witness_map = True
+
+    def _global_rank(self, group_rank: int) -> int:
+        dist = _dist()
+        return dist.get_global_rank(self.group, group_rank) if self.group is not None else group_rank
 
     def prove_dev(self, d_assignment, r: int, s: int, pubkey=None, r_saver=None):
         """d_assignment: torch int64 CUDA tensor holding (1 || primary || auxiliary) as canonical Fr limbs.  Returns the
@@ -214,7 +228,19 @@ class ShardedProver:
                           torch.zeros(self.world * PARTIAL_LIMBS, dtype=torch.int64, device=dev),
                           torch.zeros(48, dtype=torch.int64, device=dev))
         part, gathered, proof = self._bufs
-        self.pk.prove_partial_dev(d_assignment.data_ptr(), part.data_ptr())
+        if self.world > 1 and self.split_witness_map:
+            # the three coset extensions of the witness map go to (up to) three ranks; each owner broadcasts its vector
+            # (m Fr over NCCL / NVLink) while every rank's A / L / B multiexps already run on the side streams
+            if self._abc is None:
+                self._abc = torch.empty((3, self.m * 4), dtype=torch.int64, device=d_assignment.device)
+            owners = vector_owners(self.world)
+            mask = sum(1 << v for v in range(3) if owners[v] == self.rank)
+            self.pk.prove_partial_begin_dev(d_assignment.data_ptr(), mask, self._abc.data_ptr(), part.data_ptr())
+            for v in range(3):
+                _dist().broadcast(self._abc[v], src=self._global_rank(owners[v]), group=self.group)
+            self.pk.prove_partial_finish_dev(self._abc.data_ptr(), part.data_ptr())
+        else:
+            self.pk.prove_partial_dev(d_assignment.data_ptr(), part.data_ptr())
         if self.world > 1:
             _dist().all_gather_into_tensor(gathered, part, group=self.group)
         else:
