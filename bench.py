@@ -17,6 +17,7 @@ configs[2]: 65,505 constraints + 30 primary inputs -> evaluation domain 2^16 (to
 from __future__ import annotations
 
 import argparse
+import gc
 import importlib
 import json
 import os
@@ -96,22 +97,84 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.rows, self.proc, self.index = [], None, index
+        self.rows, self.proc, self.index, self.source, self.thread = [], None, index, "nvidia-smi", None
 
     def start(self):
+        """VSP_BENCH_CLOCKS = nvml (default: NVML polled in this process, the library nvidia-smi itself reads from; no child
+        process whose start-up and per-sample device enumeration can hold the driver), smi (the nvidia-smi loop of
+        B200_PROFILING.md), off"""
+        mode = os.environ.get("VSP_BENCH_CLOCKS", "nvml")
+        self.period = float(os.environ.get("VSP_BENCH_SMI_MS", "200")) / 1e3
+        if mode == "off":
+            return
+        if mode == "nvml" and self._start_nvml():
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("VSP_BENCH_SMI_MS", "200")], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", str(int(self.period * 1e3))],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
             self.proc = None
+
+    def _start_nvml(self) -> bool:
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            # torch's device `index` is relative to CUDA_VISIBLE_DEVICES: go through the PCI bus id
+            import torch
+            bus = torch.cuda.get_device_properties(self.index).pci_bus_id
+            dom = torch.cuda.get_device_properties(self.index).pci_domain_id
+            dev = torch.cuda.get_device_properties(self.index).pci_device_id
+            h = nv.nvmlDeviceGetHandleByPciBusId(("%08x:%02x:%02x.0" % (dom, bus, dev)).encode())
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        except Exception:
+            return False
+        bits = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
+        self.source = "nvml"
+        self._stop = threading.Event()
+
+        def poll():
+            while not self._stop.is_set():
+                try:
+                    sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                    try:
+                        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    except Exception:
+                        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    try:
+                        pw = nv.nvmlDeviceGetPowerUsage(h) / 1e3
+                    except Exception:
+                        pw = 0.0
+                    self.rows.append([str(sm), str(mx), "%.1f" % pw] + ["Active" if r & b else "Not Active" for _n, b in bits])
+                except Exception:
+                    pass
+                self._stop.wait(self.period)
+
+        self.thread = threading.Thread(target=poll, daemon=True)
+        self.thread.start()
+        return True
 
     def _pump(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
+    def wait_first(self, timeout: float = 10.0):
+        """nvidia-smi's start-up (NVML initialisation) can hold the driver for hundreds of ms: let it finish, and the first
+        sample arrive, before anything is timed"""
+        t0 = time.perf_counter()
+        while not self.rows and time.perf_counter() - t0 < timeout and \
+                ((self.proc and self.proc.poll() is None) or (self.thread and self.thread.is_alive())):
+            time.sleep(0.05)
+
+    def mark(self):
+        """drop what was sampled so far: only samples taken inside the timed region count"""
+        self.rows = []
+
     def stop(self):
+        if self.thread:
+            self._stop.set()
+            self.thread.join(timeout=2)
         if self.proc:
             self.proc.terminate()
             try:
@@ -123,7 +186,7 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower() == "active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": self.source if sm else None}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -242,21 +305,37 @@ def run_b200(args):
 
     # ---- device-resident timing ---------------------------------------------------------------------
     with torch.cuda.stream(stream):
-        for _ in range(W):
-            step_dev()
-        barrier(world)
-        launches0 = ctx.launch_count
+        # the sampler starts (and is seen to be running) before the warm-up, so that its start-up cannot land in the timed steps
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
+            sampler.wait_first()
+        for _ in range(W):
+            step_dev()
+        barrier(world)
+        # the circuit builder leaves millions of live Python objects: a full collection landing inside a timed step stalls
+        # the launching thread for hundreds of ms (seen as one ~900 ms step in ~1 run of 8), so collect now and hold the
+        # collector off until both timed regions are over
+        gc.collect()
+        gc.disable()
+        launches0 = ctx.launch_count
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier(world)
+        sampler.mark()
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(K - 1)]
         e0.record(stream)
-        for _ in range(K):
+        host_ms = []
+        for k in range(K):
+            th = time.perf_counter()
             step_dev()
+            host_ms.append((time.perf_counter() - th) * 1e3)  # the launching thread's time to enqueue the step
+            if k < K - 1:
+                marks[k].record(stream)  # per-step split, for the record only: the value is e0 -> e1 over all K steps
         e1.record(stream)
         barrier(world)
         ms_dev = e0.elapsed_time(e1)
+        edges = [e0] + marks + [e1]
+        step_ms = [edges[k].elapsed_time(edges[k + 1]) for k in range(K)]
         clocks = sampler.stop() if rank == 0 else None
         launches = ctx.launch_count - launches0
         # the same K steps once more with the library's per-launch CUDA events on (kernel classes, roofline); while
@@ -283,13 +362,14 @@ def run_b200(args):
         f1.record(stream)
         barrier(world)
         ms_e2e = max(f0.elapsed_time(f1), (time.perf_counter() - t0) * 1e3)
+    gc.enable()
     ms_e2e = max_over_ranks(ms_e2e, world)
     cts_dev = d_cts.cpu().numpy().view(np.uint64)
     same = bool(np.array_equal(proofs_e2e, proofs_dev) and np.array_equal(cts_e2e, cts_dev))
 
     return dict(circuit=circuit, witness_info=witness_info,
                 world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
-                clocks=clocks, launches=launches, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
+                clocks=clocks, launches=launches, step_ms=step_ms, host_ms=host_ms, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
                 proofs=proofs_dev, cts=cts_dev, gabc=gabc, key=key, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes),
                 d2h=int(B * 384 + cts_dev.nbytes), stream=stream)
 
@@ -982,6 +1062,8 @@ def main():
     ncu = load_ncu_evidence()
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": res["W"],
             "ms_per_step": res["ms_dev"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "step_ms": [round(x, 2) for x in res["step_ms"]],
+            "step_host_enqueue_ms": [round(x, 2) for x in res["host_ms"]],
             "dtype": "u32 limbs (Fq 12x32, Fr 8x32, Montgomery)", "data": "synthetic",
             "config": workload_config(args, world, res["circuit"]),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"],
