@@ -100,6 +100,19 @@ VSP_API int vsp_domain_plan(uint64_t min_size, int *kind, uint64_t *m);
  * basic domain zero-pads short input, the step domain's inverse_fft rejects it (VSP_E_INVALID) as the reference does. */
 VSP_API int vsp_fr_fft(vsp_ctx *ctx, uint64_t m, int inverse, const uint64_t *in, uint64_t n_in, uint64_t *out);
 VSP_API int vsp_fr_fft_dev(vsp_ctx *ctx, uint64_t m, int inverse, uint64_t *d_inout);
+/* vsp_fr_fft_dev for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Basic radix-2 domains only, 2 <= m <= VSP_NOALLOC_FFT_MAX_M = 2^16, m a power of two;
+ * anything else is rejected (VSP_E_DOMAIN for a size that is not a power of two, VSP_E_INVALID beyond the maximum,
+ * message in vsp_last_error).  Same kernels and bit-identical results as vsp_fr_fft_dev, stream-ordered on the
+ * context's stream, but the transform's ping-pong buffer and twiddle table are two file-scope __device__ arrays
+ * (2 MiB + 1 MiB, held by every GPU that loads the library until exit), so the call makes no cudaMalloc / cudaFree /
+ * cudaMallocAsync and calls no allocating library routine.  The first call on each device resolves the arrays'
+ * addresses, fills the twiddle table and synchronises the context's stream once: make it outside graph capture.
+ * Every call on a GPU shares the one scratch array, whatever context or stream it comes from: calls that overlap on
+ * the GPU race; calls on one stream are ordered.  Nothing in the scratch needs clearing between calls. */
+#define VSP_NOALLOC_FFT_MAX_M (1ull << 16)
+VSP_API int vsp_fr_fft_noalloc_dev(vsp_ctx *ctx, uint64_t m, int inverse, uint64_t *d_inout);
 VSP_API int vsp_fr_multiply_by_coset(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *a_inout);
 VSP_API int vsp_fr_multiply_by_coset_dev(vsp_ctx *ctx, uint64_t n, const uint64_t g[4], uint64_t *d_inout);
 VSP_API int vsp_fr_divide_by_z_on_coset(vsp_ctx *ctx, uint64_t m, uint64_t *a_inout);

@@ -178,6 +178,11 @@ class EvaluationDomain:
     def fft_dev(self, d_ptr: int, inverse: bool = False):
         self.ctx.check(self.ctx._lib.vsp_fr_fft_dev(self.ctx._h, self.m, int(inverse), C.c_void_p(d_ptr)))
 
+    def fft_noalloc_dev(self, d_ptr: int, inverse: bool = False):
+        """fft_dev without any allocation (static device scratch; basic radix-2 domains up to 2^16; no reference
+        counterpart, see include/vsp_b200.h).  Calls that overlap on one GPU race on the shared scratch."""
+        self.ctx.check(self.ctx._lib.vsp_fr_fft_noalloc_dev(self.ctx._h, self.m, int(inverse), C.c_void_p(d_ptr)))
+
 
 def make_evaluation_domain(ctx: Context, min_size: int) -> EvaluationDomain:
     return EvaluationDomain(ctx, min_size)

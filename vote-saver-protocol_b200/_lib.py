@@ -96,6 +96,7 @@ SYMBOLS = [
     ("vsp_domain_plan", _int, [_u64, C.POINTER(_int), C.POINTER(_u64)]),
     ("vsp_fr_fft", _int, [_vp, _u64, _int, _vp, _u64, _vp]),
     ("vsp_fr_fft_dev", _int, [_vp, _u64, _int, _vp]),
+    ("vsp_fr_fft_noalloc_dev", _int, [_vp, _u64, _int, _vp]),
     ("vsp_fr_multiply_by_coset", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_fr_multiply_by_coset_dev", _int, [_vp, _u64, _vp, _vp]),
     ("vsp_fr_divide_by_z_on_coset", _int, [_vp, _u64, _vp]),

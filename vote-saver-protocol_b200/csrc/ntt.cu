@@ -22,6 +22,7 @@
 #include "host_fr.h"
 
 #include <map>
+#include <mutex>
 
 namespace vsp {
 
@@ -764,3 +765,133 @@ int divide_by_z_on_coset_dev(vsp_ctx* ctx, cudaStream_t s, uint64_t m, uint32_t*
 }
 
 }  // namespace vsp
+
+// ---------------------------------------------------------------------------------------------
+// vsp_fr_fft_noalloc_dev: the basic radix-2 transform for callers that may not allocate.
+//
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and the
+// same pass plan as ntt_pow2 above, but the Stockham ping-pong buffer that ntt_pow2 takes from the stream-ordered
+// pool, and the twiddle table that ntt_tables_ensure cudaMallocs, live in two file-scope __device__ arrays of fixed
+// size: VSP_NOALLOC_FFT_MAX_LOG = 16, i.e. 2^16 x 32 B = 2 MiB of scratch + 2^15 x 32 B = 1 MiB of twiddles, held by
+// every GPU that loads the library until the process exits.
+//
+// In host code the arrays' names are host-side stand-ins, not device addresses: the addresses the kernels get come
+// from cudaGetSymbolAddress, called once per device with that device current (noalloc_setup).  Nothing in the scratch
+// has to start at zero: pass 0 of a two-pass transform writes all m elements before pass 1 reads any, and a one-pass
+// in-place transform writes all m before they are copied back, so the previous call's contents are never read.
+// All calls on one GPU share the one scratch array, whatever context or stream they come from: calls that overlap on
+// the GPU race.  Calls on the same stream are ordered and safe.
+// ---------------------------------------------------------------------------------------------
+#define VSP_NOALLOC_FFT_MAX_LOG 16
+static __device__ __align__(256) uint32_t g_noalloc_fft_scratch[8u << VSP_NOALLOC_FFT_MAX_LOG];
+static __device__ __align__(256) uint32_t g_noalloc_fft_twiddles[8u << (VSP_NOALLOC_FFT_MAX_LOG - 1)];
+
+namespace vsp {
+
+struct NoAllocFft {
+    uint32_t* scratch = nullptr;   // device address of g_noalloc_fft_scratch on this device
+    uint32_t* twiddles = nullptr;  // device address of g_noalloc_fft_twiddles on this device, filled
+    bool ready = false;
+};
+static const int NOALLOC_MAX_DEVICES = 64;
+static NoAllocFft g_noalloc[NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mutex;
+
+// once per device, that device current: resolve the two symbols and fill the twiddle table
+static int noalloc_setup(vsp_ctx* ctx, NoAllocFft** out) {
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+        return set_error(ctx, VSP_E_INVALID, "vsp_fr_fft_noalloc_dev: device ordinal %d out of range", ctx->device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    NoAllocFft* st = &g_noalloc[ctx->device];
+    if (!st->ready) {
+        uint32_t *scratch = nullptr, *tw = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&scratch, g_noalloc_fft_scratch);
+        if (e == cudaSuccess) e = cudaGetSymbolAddress((void**)&tw, g_noalloc_fft_twiddles);
+        if (e != cudaSuccess || !scratch || !tw)
+            return set_error(ctx, VSP_E_CUDA, "vsp_fr_fft_noalloc_dev: cudaGetSymbolAddress failed on device %d: %s", ctx->device,
+                             cudaGetErrorString(e));
+        const uint64_t half = uint64_t(1) << (VSP_NOALLOC_FFT_MAX_LOG - 1);
+        k_build_twiddles<<<(unsigned)((half + 255) / 256), 256, 0, ctx->stream>>>(tw, VSP_NOALLOC_FFT_MAX_LOG);
+        ++ctx->launches;
+        VSP_CUDA_CHECK(ctx, cudaGetLastError());
+        // other contexts and streams of this device use the table from now on: the build must be complete
+        VSP_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        st->scratch = scratch;
+        st->twiddles = tw;
+        st->ready = true;
+    }
+    *out = st;
+    return VSP_OK;
+}
+
+}  // namespace vsp
+
+extern "C" int vsp_fr_fft_noalloc_dev(vsp_ctx* ctx, uint64_t m, int inverse, uint64_t* d_inout) {
+    using namespace vsp;
+    if (!ctx || !d_inout) return VSP_E_INVALID;
+    if (m < 2 || (m & (m - 1)) != 0)
+        return set_error(ctx, VSP_E_DOMAIN, "vsp_fr_fft_noalloc_dev: m = %llu is not a basic radix-2 domain size (a power of two >= 2)",
+                         (unsigned long long)m);
+    if (m > (uint64_t(1) << VSP_NOALLOC_FFT_MAX_LOG))
+        return set_error(ctx, VSP_E_INVALID,
+                         "vsp_fr_fft_noalloc_dev: m = %llu exceeds the static scratch, maximum 2^%d = %llu elements "
+                         "(use vsp_fr_fft_dev for larger domains)",
+                         (unsigned long long)m, VSP_NOALLOC_FFT_MAX_LOG, (unsigned long long)(uint64_t(1) << VSP_NOALLOC_FFT_MAX_LOG));
+    VSP_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+    NoAllocFft* st = nullptr;
+    VSP_TRY(noalloc_setup(ctx, &st));
+    const unsigned log_n = ceil_log2_u64(m);
+    cudaStream_t s = ctx->stream;
+    uint32_t* d = reinterpret_cast<uint32_t*>(d_inout);
+    // the pass plan of ntt_pow2 for log_n <= 16: one pass up to 2^10, two above; 2^9 values per block
+    unsigned ks[2], np;
+    if (log_n <= 10) {
+        np = 1;
+        ks[0] = log_n;
+    } else {
+        np = 2;
+        ks[0] = (log_n + 1) / 2;
+        ks[1] = log_n - ks[0];
+    }
+    const unsigned block_log = 9;
+    const uint32_t* src = d;
+    unsigned ns_log = 0;
+    for (unsigned p = 0; p < np; ++p) {
+        const unsigned k = ks[p];
+        unsigned g_log = (k >= block_log) ? 0 : (block_log - k);
+        if (g_log > log_n - k) g_log = log_n - k;
+        const bool last = (p + 1 == np);
+        const bool single_block = (log_n - k - g_log) == 0;
+        // a pass never runs in place across blocks: everything but a one-block transform and the second pass goes
+        // through the static scratch
+        uint32_t* dst = (last && (np == 2 || single_block)) ? d : st->scratch;
+        PassArgs a;
+        a.in = src;
+        a.out = dst;
+        a.w = st->twiddles;
+        a.pre = nullptr;
+        a.post = nullptr;
+        a.log_w = VSP_NOALLOC_FFT_MAX_LOG;
+        a.log_n = log_n;
+        a.k = k;
+        a.ns_log = ns_log;
+        a.g_log = g_log;
+        a.in_stride = m;
+        a.out_stride = m;
+        a.inverse = inverse ? 1 : 0;
+        a.scale_log = (inverse && last) ? (int)log_n : 0;
+        const unsigned blocks = 1u << (log_n - k - g_log);
+        const size_t smem = ((size_t)32 << (k + g_log)) + ((size_t)16 << k);  // <= 48 KiB for every log_n <= 16
+        if (k >= 2)
+            k_ntt_pass4<<<dim3(blocks, 1), 1u << (k - 2 + g_log), smem, s>>>(a);
+        else
+            k_ntt_pass<<<dim3(blocks, 1), 1u << (k - 1 + g_log), smem, s>>>(a);
+        ++ctx->launches;
+        VSP_CUDA_CHECK(ctx, cudaGetLastError());
+        if (last && dst != d) VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d, dst, m * 32, cudaMemcpyDeviceToDevice, s));
+        src = dst;
+        ns_log += k;
+    }
+    return VSP_OK;
+}
