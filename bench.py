@@ -318,6 +318,7 @@ def run_b200(args):
         # collector off until both timed regions are over
         gc.collect()
         gc.disable()
+        scratch0 = ctx.scratch_stats()
         launches0 = ctx.launch_count
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier(world)
@@ -338,6 +339,10 @@ def run_b200(args):
         step_ms = [edges[k].elapsed_time(edges[k + 1]) for k in range(K)]
         clocks = sampler.stop() if rank == 0 else None
         launches = ctx.launch_count - launches0
+        scratch1 = ctx.scratch_stats()
+        scratch = {"owned_MiB": scratch1["owned_bytes"] >> 20,
+                   "driver_allocations_in_timed_steps": scratch1["driver_allocations"] - scratch0["driver_allocations"],
+                   "what": "the context's own block cache behind every temporary device buffer (vsp_ctx_scratch_stats)"}
         # the same K steps once more with the library's per-launch CUDA events on (kernel classes, roofline); while
         # they are on, the library runs its side streams' work on the main stream so launches do not overlap
         ctx.profile_enable(True)
@@ -369,7 +374,7 @@ def run_b200(args):
 
     return dict(circuit=circuit, witness_info=witness_info,
                 world=world, rank=rank, ctx=ctx, vsp=vsp, pk=pk, cs=cs, m=m, B=B, K=K, W=W, ms_dev=ms_dev, ms_e2e=ms_e2e,
-                clocks=clocks, launches=launches, step_ms=step_ms, host_ms=host_ms, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
+                clocks=clocks, launches=launches, step_ms=step_ms, host_ms=host_ms, scratch=scratch, prof=prof, same=same, prim=prim_np, aux=aux_np, rs=rs, pub_arr=pub_arr,
                 proofs=proofs_dev, cts=cts_dev, gabc=gabc, key=key, h2d=int(prim_np.nbytes + aux_np.nbytes + rs.nbytes),
                 d2h=int(B * 384 + cts_dev.nbytes), stream=stream)
 
@@ -1068,7 +1073,7 @@ def main():
             "config": workload_config(args, world, res["circuit"]),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"],
                     "ms_per_step": res["ms_e2e"] / K, "proofs_equal_device_path": res["same"]},
-            "gpu_launches": res["launches"], "clocks": res["clocks"],
+            "gpu_launches": res["launches"], "clocks": res["clocks"], "scratch": res["scratch"],
             "roofline": {"bound": "int32-mad", "kernel": "k_msm_accumulate<G1>", "achieved": ach, "peak": p_int / 1e12,
                          "unit": "TMAD/s", "frac": ach / (p_int / 1e12) if p_int else None,
                          "frac_meaning": "bucket additions x the REFERENCE algorithm's 11 Fq mul x 300 MAD each, over the measured "

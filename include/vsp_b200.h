@@ -82,6 +82,17 @@ VSP_API const char *vsp_last_warning(const vsp_ctx *ctx);
  * ballots x points x windows would pass 2^32 keys is itself run in sub-batches.  Results do not depend on it. */
 VSP_API int vsp_ctx_set_batch_chunk(vsp_ctx *ctx, int ballots);
 VSP_API int vsp_ctx_synchronize(vsp_ctx *ctx);
+/* Scratch memory.  Every temporary device buffer of a call comes from a cache of device blocks the context owns
+ * (stream-ordered like cudaMallocAsync, but dependent only on the order of the host's calls): the first run of a
+ * workload cudaMallocs its blocks, every later run of the same workload makes no driver allocation at all (the
+ * reference allocates its std::vectors per call, e.g. r1cs_gg_ppzksnark/prover.hpp:117-160; this is their device-side
+ * stand-in).  Unused blocks go back to the driver on vsp_ctx_trim, when more than VSP_SCRATCH_CACHE_GB (environment,
+ * default 64) sit unused at the moment a new block is needed, when a cudaMalloc fails, and on vsp_ctx_destroy.
+ * vsp_ctx_trim synchronises the device.  vsp_ctx_scratch_stats: bytes the cache owns, bytes of them not in use, and
+ * the number of cudaMalloc calls it has made so far (any pointer may be NULL). */
+VSP_API int vsp_ctx_trim(vsp_ctx *ctx);
+VSP_API int vsp_ctx_scratch_stats(const vsp_ctx *ctx, uint64_t *owned_bytes, uint64_t *unused_bytes,
+                                  uint64_t *driver_allocations);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 VSP_API uint64_t vsp_ctx_launch_count(const vsp_ctx *ctx);
 VSP_API const char *vsp_version(void);

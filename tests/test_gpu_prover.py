@@ -385,3 +385,36 @@ def test_plain_text_must_be_shorter_than_the_primary_input(vsp, ctx):
         pk.encrypt_batch(key, primary[None], aux[None], cref.ints_to_limbs([5, 6, 7], 4)[None])
     key.close()
     pk.close()
+
+
+def test_scratch_cache_reaches_a_steady_state_and_trims(vsp, ctx):
+    """the context's scratch cache (vsp_ctx_scratch_stats / vsp_ctx_trim): the first batch cudaMallocs its blocks, equal
+    batches after it make no driver allocation and return the same proofs; trim hands every unused block back and the
+    next batch still agrees"""
+    nc, ni, k = 97, 30, 5
+    cs, _, _ = synthetic_r1cs(nc, ni, 0)
+    arr = synthetic_pk_arrays(cs, 3)
+    pub_arr, _ = synthetic_saver_pub(25, seed=4)
+    pub = vsp.SaverPublicKey(pub_arr)
+    pk = vsp.ProvingKey(ctx, arr)
+    rng = random.Random(19)
+    prim, aux, rs = [], [], []
+    for b in range(k):
+        _, p, a = synthetic_r1cs(nc, ni, seed=b)
+        prim.append(cref.ints_to_limbs(p, 4))
+        aux.append(cref.ints_to_limbs(a, 4))
+        rs.append(cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4))
+    prim, aux, rs = np.stack(prim), np.stack(aux), np.stack(rs)
+    first = pk.prove_batch(prim, aux, rs, pub)
+    s0 = ctx.scratch_stats()
+    assert s0["driver_allocations"] > 0 and s0["owned_bytes"] >= s0["unused_bytes"] > 0
+    for _ in range(3):
+        assert np.array_equal(pk.prove_batch(prim, aux, rs, pub), first)
+    s1 = ctx.scratch_stats()
+    assert s1["driver_allocations"] == s0["driver_allocations"] and s1["owned_bytes"] == s0["owned_bytes"]
+    ctx.trim()
+    s2 = ctx.scratch_stats()
+    assert s2["unused_bytes"] == 0 and s2["owned_bytes"] == s0["owned_bytes"] - s0["unused_bytes"]
+    assert np.array_equal(pk.prove_batch(prim, aux, rs, pub), first)
+    assert ctx.scratch_stats()["driver_allocations"] > s2["driver_allocations"]
+    pk.close()

@@ -111,6 +111,16 @@ class Context:
     def synchronize(self):
         self.check(self._lib.vsp_ctx_synchronize(self._h))
 
+    def trim(self):
+        """every unused block of the context's scratch cache back to the driver (synchronises the device)"""
+        self.check(self._lib.vsp_ctx_trim(self._h))
+
+    def scratch_stats(self) -> dict:
+        """{"owned_bytes", "unused_bytes", "driver_allocations"} of the context's scratch cache"""
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self.check(self._lib.vsp_ctx_scratch_stats(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"owned_bytes": a.value, "unused_bytes": b.value, "driver_allocations": c.value}
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.vsp_ctx_launch_count(self._h))

@@ -89,6 +89,8 @@ SYMBOLS = [
     ("vsp_last_warning", C.c_char_p, [_vp]),
     ("vsp_ctx_set_batch_chunk", _int, [_vp, _int]),
     ("vsp_ctx_synchronize", _int, [_vp]),
+    ("vsp_ctx_trim", _int, [_vp]),
+    ("vsp_ctx_scratch_stats", _int, [_vp, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64)]),
     ("vsp_ctx_launch_count", _u64, [_vp]),
     ("vsp_version", C.c_char_p, []),
     ("vsp_ctx_profile_enable", _int, [_vp, _int]),

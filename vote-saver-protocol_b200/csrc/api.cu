@@ -80,12 +80,8 @@ int vsp_ctx_create(int device, void* cuda_stream, vsp_ctx** out) {
     cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming);
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->tail[i].done, cudaEventDisableTiming);
-    // keep freed scratch in the pool: repeated calls then allocate without touching the driver
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-        uint64_t thr = UINT64_MAX;
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-    }
+    // scratch comes from the context's own block cache (common.cuh), created on first use: the process's default
+    // memory pool is left as the host application configured it
     if (cudaGetLastError() != cudaSuccess) {
         delete ctx;
         return VSP_E_NO_DEVICE;
@@ -119,6 +115,11 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
         if (ctx->tail[i].p) cudaFree(ctx->tail[i].p);
         if (i == 0 && ctx->partial_bsc) cudaFree(ctx->partial_bsc);
     }
+    if (ctx->scratch) {
+        scratch_trim(ctx);
+        delete ctx->scratch;
+        ctx->scratch = nullptr;
+    }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -128,6 +129,22 @@ const char* vsp_last_warning(const vsp_ctx* ctx) { return ctx ? ctx->warn.c_str(
 int vsp_ctx_set_batch_chunk(vsp_ctx* ctx, int ballots) {
     if (!ctx || ballots < 0 || ballots > 1024) return VSP_E_INVALID;
     ctx->batch_chunk = ballots;
+    return VSP_OK;
+}
+
+int vsp_ctx_trim(vsp_ctx* ctx) {
+    if (!ctx) return VSP_E_INVALID;
+    cudaSetDevice(ctx->device);
+    scratch_trim(ctx);
+    return VSP_OK;
+}
+
+int vsp_ctx_scratch_stats(const vsp_ctx* ctx, uint64_t* owned_bytes, uint64_t* unused_bytes, uint64_t* driver_allocations) {
+    if (!ctx) return VSP_E_INVALID;
+    const ScratchCache* c = ctx->scratch;
+    if (owned_bytes) *owned_bytes = c ? c->owned_bytes : 0;
+    if (unused_bytes) *unused_bytes = c ? c->unused_bytes : 0;
+    if (driver_allocations) *driver_allocations = c ? c->driver_allocations : 0;
     return VSP_OK;
 }
 

@@ -2,10 +2,12 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -13,6 +15,7 @@
 
 namespace vsp {
 struct NttTables;
+struct ScratchCache;
 
 // kernel classes for the live per-class device timing (vsp_ctx_profile_*): bench.py's roofline leg
 enum KClass {
@@ -71,6 +74,7 @@ struct vsp_ctx {
     size_t partial_bsc_cap = 0;
     int batch_chunk = 0;  // ballots per chunk of the batched prover (0: VSP_BATCH_CHUNK or 64); vsp_ctx_set_batch_chunk
     cudaEvent_t ev_main = nullptr;
+    vsp::ScratchCache* scratch = nullptr;  // device blocks behind every DevBuf (below)
     vsp::KProf prof;
     int last_prof = -1;  // profile record of the most recent launch (for kprof_units)
 };
@@ -96,9 +100,34 @@ inline void set_warning(vsp_ctx* ctx, const char* fmt, ...) {
     if (ctx) ctx->warn = buf;
 }
 
+// VSP_HOST_TRACE=<ms>: every CUDA runtime call / kernel launch of this library that holds the calling thread for longer
+// than <ms> is reported on stderr with its source line (diagnosis of host-side stalls; off by default: one branch)
+struct HostTrace {
+    const char* what;
+    const char* file;
+    int line;
+    std::chrono::steady_clock::time_point t0;
+    static double threshold() {
+        static const double t = getenv("VSP_HOST_TRACE") ? atof(getenv("VSP_HOST_TRACE")) : -1.0;
+        return t;
+    }
+    HostTrace(const char* w, const char* f, int l) : what(w), file(f), line(l) {
+        if (threshold() >= 0) t0 = std::chrono::steady_clock::now();
+    }
+    ~HostTrace() {
+        if (threshold() < 0) return;
+        const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        if (ms > threshold()) fprintf(stderr, "[vsp host trace] %.2f ms in %s (%s:%d)\n", ms, what, file, line);
+    }
+};
+
 #define VSP_CUDA_CHECK(ctx, expr)                                                                          \
     do {                                                                                                   \
-        cudaError_t _e = (expr);                                                                           \
+        cudaError_t _e;                                                                                    \
+        {                                                                                                  \
+            ::vsp::HostTrace _ht(#expr, __FILE__, __LINE__);                                               \
+            _e = (expr);                                                                                   \
+        }                                                                                                  \
         if (_e != cudaSuccess)                                                                             \
             return ::vsp::set_error((ctx), VSP_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
                                     __FILE__, __LINE__);                                                   \
@@ -140,7 +169,10 @@ inline void kprof_units(vsp_ctx* ctx, int idx, double scale, const uint32_t* d_c
 #define VSP_LAUNCH_K(ctx, kc, kernel, grid, block, smem, strm, ...)  \
     do {                                                             \
         const int _pi = ::vsp::kprof_begin((ctx), (kc), (strm));     \
-        kernel<<<(grid), (block), (smem), (strm)>>>(__VA_ARGS__);    \
+        {                                                            \
+            ::vsp::HostTrace _ht(#kernel, __FILE__, __LINE__);       \
+            kernel<<<(grid), (block), (smem), (strm)>>>(__VA_ARGS__);\
+        }                                                            \
         ::vsp::kprof_end((ctx), _pi, (strm));                        \
         (ctx)->last_prof = _pi;                                      \
         ++(ctx)->launches;                                           \
@@ -148,29 +180,121 @@ inline void kprof_units(vsp_ctx* ctx, int idx, double scale, const uint32_t* d_c
 #define VSP_LAUNCH(ctx, kernel, grid, block, smem, strm, ...) \
     VSP_LAUNCH_K(ctx, ::vsp::KC_OTHER, kernel, grid, block, smem, strm, __VA_ARGS__)
 
-// Stream-ordered device buffer (cudaMallocAsync pool: no device synchronisation, memory reused across calls).
+// ---------------------------------------------------------------------------------------------
+// Scratch memory of a context: a cache of device blocks the context owns, in place of the driver's stream-ordered pool.
+//
+// The pool (cudaMallocAsync) was measured to hold the launching thread for 20-800 ms inside ONE allocation of the first
+// step after a device synchronisation, in about one bench run in four (its block assignment depends on which frees
+// have completed on the GPU, so the free list it finds after a synchronisation varies from run to run).  The cache
+// depends only on the order of the host's calls: a step that repeats the same allocations finds the same blocks, and
+// after the first step no driver allocation happens at all.
+//
+// A block is found by (stream, size): the smallest block last used on the SAME stream that fits with at most 1/8 of
+// slack, else a new one from cudaMalloc.  A block never moves between streams, so stream order alone makes reuse safe:
+// no events, and no dependency is ever created between the context's streams (taking a block another stream released
+// made that stream's work up to the release a prerequisite: measured 2 % on the ballot step, where the multiexps on the
+// side streams are meant to overlap).  As with cudaFreeAsync, work on other streams that reads a buffer must have been
+// joined into the buffer's stream before the release.  The price is memory: the cache holds the sum of the streams'
+// peaks rather than the peak of their sum.  Blocks are returned to the driver by scratch_trim (vsp_ctx_trim), when more
+// than VSP_SCRATCH_CACHE_GB (default 64) sit unused at the moment a new block is needed, when a cudaMalloc fails, and
+// when the context is destroyed.
+// ---------------------------------------------------------------------------------------------
+struct ScratchBlock {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaStream_t stream = nullptr;  // the one stream this block is used on
+};
+
+struct ScratchCache {
+    std::map<cudaStream_t, std::multimap<size_t, void*>> unused;  // per stream, by size
+    size_t unused_bytes = 0, owned_bytes = 0;
+    size_t limit = size_t(getenv("VSP_SCRATCH_CACHE_GB") ? atof(getenv("VSP_SCRATCH_CACHE_GB")) * 1073741824.0 : 64.0 * 1073741824.0);
+    uint64_t driver_allocations = 0;  // cudaMalloc calls so far (a steady loop stops adding to it)
+};
+
+// every unused block back to the driver (device-wide synchronisation: their last users must be done)
+inline void scratch_trim(vsp_ctx* ctx) {
+    ScratchCache* c = ctx ? ctx->scratch : nullptr;
+    if (!c || c->unused_bytes == 0) return;
+    cudaDeviceSynchronize();
+    for (auto& per_stream : c->unused)
+        for (auto& kv : per_stream.second) {
+            cudaFree(kv.second);
+            c->owned_bytes -= kv.first;
+        }
+    c->unused.clear();
+    c->unused_bytes = 0;
+}
+
+inline int scratch_acquire(vsp_ctx* ctx, size_t n, cudaStream_t stream, ScratchBlock* out) {
+    if (!ctx->scratch) ctx->scratch = new ScratchCache();
+    ScratchCache& c = *ctx->scratch;
+    n = (n + 255) & ~size_t(255);
+    auto& mine = c.unused[stream];
+    auto it = mine.lower_bound(n);
+    if (it != mine.end() && it->first <= n + n / 8) {
+        out->p = it->second;
+        out->bytes = it->first;
+        out->stream = stream;
+        c.unused_bytes -= out->bytes;
+        mine.erase(it);
+        return VSP_OK;
+    }
+    if (c.unused_bytes > c.limit) scratch_trim(ctx);
+    void* p = nullptr;
+    cudaError_t e;
+    {
+        HostTrace ht("cudaMalloc (scratch cache miss)", __FILE__, __LINE__);
+        e = cudaMalloc(&p, n);
+        if (e != cudaSuccess && c.unused_bytes) {
+            cudaGetLastError();
+            scratch_trim(ctx);
+            e = cudaMalloc(&p, n);
+        }
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_error(ctx, VSP_E_NOMEM, "cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+    }
+    out->p = p;
+    out->bytes = n;
+    out->stream = stream;
+    c.owned_bytes += n;
+    ++c.driver_allocations;
+    return VSP_OK;
+}
+
+inline void scratch_release(vsp_ctx* ctx, ScratchBlock& b) {
+    ctx->scratch->unused[b.stream].emplace(b.bytes, b.p);
+    ctx->scratch->unused_bytes += b.bytes;
+}
+
+// Stream-ordered device buffer out of the context's scratch cache: no device synchronisation and, once a workload has
+// run through once, no driver call beyond an event record.
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
     cudaStream_t s = nullptr;
+    vsp_ctx* owner = nullptr;
+    ScratchBlock blk;
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     ~DevBuf() { release(); }
     int alloc(vsp_ctx* ctx, size_t n, cudaStream_t stream) {
         release();
+        if (!ctx) return VSP_E_INVALID;
         if (n == 0) n = 16;
+        int rc = scratch_acquire(ctx, n, stream, &blk);
+        if (rc != VSP_OK) return rc;
+        owner = ctx;
         s = stream;
-        cudaError_t e = cudaMallocAsync(&p, n, stream);
-        if (e != cudaSuccess) {
-            p = nullptr;
-            return set_error(ctx, VSP_E_NOMEM, "cudaMallocAsync(%zu) failed: %s", n, cudaGetErrorString(e));
-        }
+        p = blk.p;
         bytes = n;
         return VSP_OK;
     }
     void release() {
-        if (p) cudaFreeAsync(p, s);
+        if (p) scratch_release(owner, blk);
         p = nullptr;
         bytes = 0;
     }
