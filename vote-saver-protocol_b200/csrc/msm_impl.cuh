@@ -383,8 +383,15 @@ struct AffineLanes {
     static constexpr int K = std::is_same<F, FqOps>::value ? 16 : 8;
 };
 
+// resident blocks per SM the accumulation kernel is compiled for: three in G1 (<= 168 registers per thread; the lazy
+// reductions had pushed it to 172, i.e. two blocks), two in G2 (255 registers either way)
 template <class F>
-__global__ void __launch_bounds__(128) k_msm_accumulate(const uint32_t* __restrict__ table, const uint32_t* __restrict__ sorted,
+struct AccBlocks {
+    static constexpr int MIN_BLOCKS = std::is_same<F, FqOps>::value ? 3 : 2;
+};
+
+template <class F>
+__global__ void __launch_bounds__(128, AccBlocks<F>::MIN_BLOCKS) k_msm_accumulate(const uint32_t* __restrict__ table, const uint32_t* __restrict__ sorted,
                                                         const Task* __restrict__ tasks,
                                                         const uint32_t* __restrict__ order,
                                                         const uint32_t* __restrict__ n_tasks_ptr, uint32_t max_tasks,
