@@ -894,7 +894,7 @@ def run_sharded_msm(res, log_n_total: int, p_int_holder):
 
 
 def batch_chunk_env() -> int:
-    return int(os.environ.get("VSP_BATCH_CHUNK", "128"))
+    return int(os.environ.get("VSP_BATCH_CHUNK", "256"))
 
 
 def run_sharded_prove(res, log_m: int):

@@ -77,7 +77,7 @@ VSP_API const char *vsp_last_error(const vsp_ctx *ctx);
  * device memory, multiexps over these bases run table-less" (same results, slower for small queries) */
 VSP_API const char *vsp_last_warning(const vsp_ctx *ctx);
 /* ballots per chunk of the batched entry points (vsp_prove_batch*, vsp_saver_encrypt_batch*): 0 restores the default
- * (environment VSP_BATCH_CHUNK, else 128).  The library further clamps it by the circuit's domain size m to
+ * (environment VSP_BATCH_CHUNK, else 256).  The library further clamps it by the circuit's domain size m to
  * max(1, 2^23 / m), so a batch of any size over any circuit runs in bounded scratch; inside a chunk a multiexp whose
  * ballots x points x windows would pass 2^32 keys is itself run in sub-batches.  Results do not depend on it. */
 VSP_API int vsp_ctx_set_batch_chunk(vsp_ctx *ctx, int ballots);

@@ -124,7 +124,7 @@ def test_saver_encrypt_and_rerandomize_match_oracle(vsp, ctx):
 
 @pytest.mark.parametrize("binary", [True, False])
 def test_encrypt_batch_matches_oracle(vsp, ctx, binary):
-    """vsp_saver_encrypt_batch: k ballots, chunked (VSP_BATCH_CHUNK default 128 -> one chunk; k = 7 exercises ragged
+    """vsp_saver_encrypt_batch: k ballots, chunked (VSP_BATCH_CHUNK default 256 -> one chunk; k = 7 exercises ragged
     lanes), messages with 0 / 1 and general slots, each ciphertext and proof against the oracle"""
     nc, ni, msg_size, k = 97, 30, 25, 7
     cs, _, _ = synthetic_r1cs(nc, ni, 0, binary=binary)

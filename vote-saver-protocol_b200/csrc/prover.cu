@@ -1076,15 +1076,15 @@ static int join_tails(vsp_ctx* ctx) {
     return VSP_OK;
 }
 
-// ballots per chunk: vsp_ctx_set_batch_chunk, else VSP_BATCH_CHUNK (read on every call), else 128 (measured on the ballot
-// circuit: 1,212 / 1,234 / 1,239 ballots/s at 64 / 128 / 256 per chunk); then clamped by the
+// ballots per chunk: vsp_ctx_set_batch_chunk, else VSP_BATCH_CHUNK (read on every call), else 256 (measured on the ballot
+// circuit: 1,384 / 1,417 / 1,443 ballots/s at 64 / 128 / 256 per chunk, 1,360 / 1,393 / 1,403 from host buffers); then clamped by the
 // domain size so that a chunk's scratch (about 100 B per ballot and domain element, plus the multiexp keys) stays a few
-// GB whatever the circuit: 128 ballots at m = 2^16, 8 at 2^20, 1 from 2^23 up
+// GB whatever the circuit: 256 ballots at m = 2^15, 128 at 2^16, 8 at 2^20, 1 from 2^23 up
 static unsigned batch_chunk(const vsp_ctx* ctx, const vsp_pk* pk) {
     long x = ctx->batch_chunk;
     if (x <= 0) {
         const char* e = getenv("VSP_BATCH_CHUNK");
-        x = e ? atol(e) : 128;
+        x = e ? atol(e) : 256;
     }
     x = x < 1 ? 1 : (x > 1024 ? 1024 : x);
     const uint64_t cap = std::max<uint64_t>(1, (uint64_t(1) << 23) / (pk->m ? pk->m : 1));
