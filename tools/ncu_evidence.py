@@ -53,7 +53,7 @@ def main(raw_csv: str, out_txt: str, what: str = ""):
                                     capture_output=True, text=True).stdout.strip()
         except Exception:
             commit = ""
-        ev = {"kernel": "k_msm_accumulate<FqOps>", "launch": "H_query multiexp of one 128-ballot chunk (the longest G1 accumulation launch)",
+        ev = {"kernel": "k_msm_accumulate<FqOps>", "launch": "H_query multiexp of one 256-ballot chunk (the longest G1 accumulation launch)",
               "duration_ms": float(top["gpu__time_duration.sum"].replace(",", "")),
               "dram_bytes_per_launch": to_bytes(top["dram__bytes_read.sum"], u["dram__bytes_read.sum"])
               + to_bytes(top["dram__bytes_write.sum"], u["dram__bytes_write.sum"]),

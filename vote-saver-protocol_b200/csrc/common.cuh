@@ -189,8 +189,8 @@ inline void kprof_units(vsp_ctx* ctx, int idx, double scale, const uint32_t* d_c
 // depends only on the order of the host's calls: a step that repeats the same allocations finds the same blocks, and
 // after the first step no driver allocation happens at all.
 //
-// A block is found by (stream, size): the smallest block last used on the SAME stream that fits with at most 1/8 of
-// slack, else a new one from cudaMalloc.  A block never moves between streams, so stream order alone makes reuse safe:
+// A block is found by (stream, size class): a block of the request's class last used on the SAME stream, else a new one
+// from cudaMalloc.  A block never moves between streams, so stream order alone makes reuse safe:
 // no events, and no dependency is ever created between the context's streams (taking a block another stream released
 // made that stream's work up to the release a prerequisite: measured 2 % on the ballot step, where the multiexps on the
 // side streams are meant to overlap).  As with cudaFreeAsync, work on other streams that reads a buffer must have been
@@ -226,13 +226,24 @@ inline void scratch_trim(vsp_ctx* ctx) {
     c->unused_bytes = 0;
 }
 
+// sizes are rounded up to one of sixteen classes per power of two (at most 1/8 of slack, 512 B at least) and a block serves
+// its own class only: whether a request hits then depends on nothing but the requests made before it, so the second run
+// of a workload already allocates nothing (a best-fit rule let a smaller request take the block a later one needed, and
+// took several runs to settle), while nearby batch sizes still share blocks
+inline size_t scratch_size_class(size_t n) {
+    if (n <= 512) return 512;
+    unsigned top = 63 - (unsigned)__builtin_clzll((unsigned long long)(n - 1));  // 2^top < n <= 2^(top+1)
+    const size_t step = size_t(1) << (top - 3);                                  // a sixteenth of 2^(top+1)
+    return (n + step - 1) & ~(step - 1);
+}
+
 inline int scratch_acquire(vsp_ctx* ctx, size_t n, cudaStream_t stream, ScratchBlock* out) {
     if (!ctx->scratch) ctx->scratch = new ScratchCache();
     ScratchCache& c = *ctx->scratch;
-    n = (n + 255) & ~size_t(255);
+    n = scratch_size_class(n);
     auto& mine = c.unused[stream];
-    auto it = mine.lower_bound(n);
-    if (it != mine.end() && it->first <= n + n / 8) {
+    auto it = mine.find(n);
+    if (it != mine.end()) {
         out->p = it->second;
         out->bytes = it->first;
         out->stream = stream;
