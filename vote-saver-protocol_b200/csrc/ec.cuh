@@ -218,15 +218,15 @@ VSP_DEV void ec_madd(XYZZ<F>& acc, const Affine<F>& q) {
         }
         return;
     }
+    // every value is consumed as early as the formulas allow (the products are calls, which the compiler does not
+    // reorder): PP and P die before the second half, so the G2 kernel carries one Fq2 less across it
     E PP = F::sqr(P);
-    E PPP = F::mul(P, PP);
     E Q = F::mul(acc.X, PP);
-    E X3 = F::sub(F::sub(F::sqr(R), PPP), F::dbl(Q));
-    E Y3 = F::mul_sub_mul(R, F::sub(Q, X3), acc.Y, PPP);
-    acc.X = X3;
-    acc.Y = Y3;
+    E PPP = F::mul(P, PP);
     acc.ZZ = F::mul(acc.ZZ, PP);
     acc.ZZZ = F::mul(acc.ZZZ, PPP);
+    acc.X = F::sub(F::sub(F::sqr(R), PPP), F::dbl(Q));
+    acc.Y = F::mul_sub_mul(R, F::sub(Q, acc.X), acc.Y, PPP);
 }
 
 // ---------------------------------------------------------------------------------------------
