@@ -283,11 +283,9 @@ __device__ __noinline__ void ec_add(XYZZ<F>& acc, const XYZZ<F>& q) {
         return;
     }
     E U1 = F::mul(acc.X, q.ZZ);
-    E U2 = F::mul(q.X, acc.ZZ);
+    E P = F::sub(F::mul(q.X, acc.ZZ), U1);
     E S1 = F::mul(acc.Y, q.ZZZ);
-    E S2 = F::mul(q.Y, acc.ZZZ);
-    E P = F::sub(U2, U1);
-    E R = F::sub(S2, S1);
+    E R = F::sub(F::mul(q.Y, acc.ZZZ), S1);
     if (F::is_zero(P)) {
         if (F::is_zero(R)) {
             acc = ec_dbl<F>(acc);
@@ -296,15 +294,14 @@ __device__ __noinline__ void ec_add(XYZZ<F>& acc, const XYZZ<F>& q) {
         }
         return;
     }
+    // as in ec_madd: every value consumed as early as the formulas allow, results written back to `acc` (memory) at once
     E PP = F::sqr(P);
-    E PPP = F::mul(P, PP);
     E Q = F::mul(U1, PP);
-    E X3 = F::sub(F::sub(F::sqr(R), PPP), F::dbl(Q));
-    E Y3 = F::mul_sub_mul(R, F::sub(Q, X3), S1, PPP);
-    acc.X = X3;
-    acc.Y = Y3;
+    E PPP = F::mul(P, PP);
     acc.ZZ = F::mul(F::mul(acc.ZZ, q.ZZ), PP);
     acc.ZZZ = F::mul(F::mul(acc.ZZZ, q.ZZZ), PPP);
+    acc.X = F::sub(F::sub(F::sqr(R), PPP), F::dbl(Q));
+    acc.Y = F::mul_sub_mul(R, F::sub(Q, acc.X), S1, PPP);
 }
 
 // canonical affine (Montgomery form) of an XYZZ point: one field inversion
