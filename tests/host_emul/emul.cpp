@@ -7,6 +7,7 @@
 #include <cstring>
 
 #include "../../vote-saver-protocol_b200/csrc/ec.cuh"
+#include "../../vote-saver-protocol_b200/csrc/scratch_class.h"
 
 using namespace vsp;
 
@@ -114,3 +115,6 @@ void emul_fr_montmul_raw(const uint64_t* a, const uint64_t* b, uint64_t* out) { 
 void emul_fq_montsqr_raw(const uint64_t* a, uint64_t* out) { st<FqCfg>(out, fp_sqr(ld<FqCfg>(a))); }
 void emul_fr_montsqr_raw(const uint64_t* a, uint64_t* out) { st<FrCfg>(out, fp_sqr(ld<FrCfg>(a))); }
 }
+
+// the scratch cache's size class of a request of n bytes (csrc/scratch_class.h)
+extern "C" uint64_t emul_scratch_size_class(uint64_t n) { return (uint64_t)vsp::scratch_size_class((size_t)n); }

@@ -171,3 +171,23 @@ def test_fq2_lazy_products(emul):
         emul.emul_fq2_raw(2, P(A), P(B), P(Cc), P(D), P(O))
         ab, cd = f2mul(a, b), f2mul(c, d)
         assert tuple(limbs_to_ints(O.reshape(2, 6))) == ((ab[0] - cd[0]) * rinv % p, (ab[1] - cd[1]) * rinv % p)
+
+
+def test_scratch_cache_size_classes(emul):
+    """csrc/scratch_class.h, the size classes of the context's scratch cache: a class holds its request with at most 1/8 of
+    slack, is its own class (so a released block is found again by the same request), never shrinks with the request, and
+    there are eight of them per power of two"""
+    f = emul.emul_scratch_size_class
+    f.restype, f.argtypes = C.c_uint64, [C.c_uint64]
+    rng = random.Random(5)
+    sizes = [1, 16, 511, 512, 513, 1023, 1024, 1025, (1 << 20) - 1, 1 << 20, (1 << 20) + 1, 3 << 30, (1 << 33) + 5, 1 << 40]
+    sizes += [rng.randrange(1, 1 << rng.randrange(10, 42)) for _ in range(20000)]
+    for n in sizes:
+        c = f(n)
+        assert c >= n and c >= 512 and c % 64 == 0, n
+        assert n <= 512 or c * 8 <= n * 9, (n, c)   # at most 1/8 above the request
+        assert f(c) == c, (n, c)                     # a class is a fixed point
+    assert all(f(n) <= f(n + 1) for n in range(1, 70000))
+    for top in (12, 20, 31, 36):
+        classes = {f(n) for n in range((1 << top) + 1, (1 << (top + 1)) + 1, max(1, 1 << (top - 9)))}
+        assert len(classes) == 8, top

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../../include/vsp_b200.h"
+#include "scratch_class.h"
 
 namespace vsp {
 struct NttTables;
@@ -224,17 +225,6 @@ inline void scratch_trim(vsp_ctx* ctx) {
         }
     c->unused.clear();
     c->unused_bytes = 0;
-}
-
-// sizes are rounded up to one of sixteen classes per power of two (at most 1/8 of slack, 512 B at least) and a block serves
-// its own class only: whether a request hits then depends on nothing but the requests made before it, so the second run
-// of a workload already allocates nothing (a best-fit rule let a smaller request take the block a later one needed, and
-// took several runs to settle), while nearby batch sizes still share blocks
-inline size_t scratch_size_class(size_t n) {
-    if (n <= 512) return 512;
-    unsigned top = 63 - (unsigned)__builtin_clzll((unsigned long long)(n - 1));  // 2^top < n <= 2^(top+1)
-    const size_t step = size_t(1) << (top - 3);                                  // a sixteenth of 2^(top+1)
-    return (n + step - 1) & ~(step - 1);
 }
 
 inline int scratch_acquire(vsp_ctx* ctx, size_t n, cudaStream_t stream, ScratchBlock* out) {
