@@ -115,6 +115,10 @@ void vsp_ctx_destroy(vsp_ctx* ctx) {
         if (ctx->tail[i].p) cudaFree(ctx->tail[i].p);
         if (i == 0 && ctx->partial_bsc) cudaFree(ctx->partial_bsc);
     }
+    for (int i = 0; i < 4; ++i) {
+        if (ctx->stage[i].done) cudaEventDestroy(ctx->stage[i].done);
+        if (ctx->stage[i].p) cudaFreeHost(ctx->stage[i].p);
+    }
     if (ctx->scratch) {
         scratch_trim(ctx);
         delete ctx->scratch;

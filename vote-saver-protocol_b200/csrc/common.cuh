@@ -71,6 +71,16 @@ struct vsp_ctx {
         bool pending = false;
     } tail[2];
     unsigned tail_next = 0;
+    // pinned host staging of the per-chunk scalar uploads (prover.cu): four slots in turn; a slot is refilled only after
+    // the copies that read it have completed, so the uploads are truly asynchronous and the launching thread, which runs
+    // at most a step ahead, does not wait in practice
+    struct StageSlot {
+        void* p = nullptr;
+        size_t cap = 0;
+        cudaEvent_t done = nullptr;
+        bool pending = false;
+    } stage[4];
+    unsigned stage_next = 0;
     void* partial_bsc = nullptr;  // gathered B-query scalars between vsp_prove_partial_begin_dev and _finish_dev
     size_t partial_bsc_cap = 0;
     int batch_chunk = 0;  // ballots per chunk of the batched prover (0: VSP_BATCH_CHUNK or 64); vsp_ctx_set_batch_chunk

@@ -922,6 +922,31 @@ static const FixedJob PROOF_JOBS_G1[4] = {{0, 0}, {0, 1}, {0, 2}, {1, 3}};
 static const FixedJob PROOF_JOBS_G2[1] = {{0, 1}};
 
 // One chunk of B proofs, fully asynchronous: on return everything is enqueued on ctx->stream / side streams, joined
+// pinned staging slot of at least `bytes` for host data about to be uploaded on a stream (vsp_ctx::StageSlot)
+static int stage_acquire(vsp_ctx* ctx, size_t bytes, vsp_ctx::StageSlot** out) {
+    vsp_ctx::StageSlot& sl = ctx->stage[ctx->stage_next++ & 3];
+    if (sl.pending) {
+        VSP_CUDA_CHECK(ctx, cudaEventSynchronize(sl.done));
+        sl.pending = false;
+    }
+    if (sl.cap < bytes) {
+        if (sl.p) cudaFreeHost(sl.p);
+        sl.p = nullptr;
+        sl.cap = 0;
+        VSP_CUDA_CHECK(ctx, cudaMallocHost(&sl.p, bytes));
+        sl.cap = bytes;
+    }
+    if (!sl.done) VSP_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    *out = &sl;
+    return VSP_OK;
+}
+// the copies out of the slot have been enqueued on `s`
+static int stage_commit(vsp_ctx* ctx, vsp_ctx::StageSlot* sl, cudaStream_t s) {
+    VSP_CUDA_CHECK(ctx, cudaEventRecord(sl->done, s));
+    sl->pending = true;
+    return VSP_OK;
+}
+
 // back into ctx->stream, and d_proofs (B x 48 limbs) holds the results once ctx->stream completes.
 //   d_w: B assignments, w_stride apart.  rs: B x (r, s, r_saver) host scalars.
 static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w, uint64_t w_stride, const uint64_t* rs,
@@ -934,8 +959,16 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
         return set_error(ctx, VSP_E_INVALID, "this key holds a point-range slice: use vsp_prove_partial / vsp_prove_assemble");
     if (gamma_inv) VSP_TRY(ensure_gamma_table(ctx, pk, gamma_inv));
 
-    // host scalars of the chunk: fixed-base slots (4 per ballot) and the variable-base pair (s, r)
-    std::vector<uint64_t> fsc(size_t(B) * 16), vsc(size_t(B) * 8);
+    // host scalars of the chunk: fixed-base slots (4 per ballot), the variable-base pair (s, r) and the two job tables,
+    // written straight into pinned memory
+    const size_t fsc_n = size_t(B) * 16, vsc_n = size_t(B) * 8;
+    vsp_ctx::StageSlot* stage = nullptr;
+    VSP_TRY(stage_acquire(ctx, (fsc_n + vsc_n) * 8 + sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), &stage));
+    uint64_t* fsc = static_cast<uint64_t*>(stage->p);
+    uint64_t* vsc = fsc + fsc_n;
+    char* host_jobs = reinterpret_cast<char*>(vsc + vsc_n);
+    memcpy(host_jobs, PROOF_JOBS_G1, sizeof(PROOF_JOBS_G1));
+    memcpy(host_jobs + sizeof(PROOF_JOBS_G1), PROOF_JOBS_G2, sizeof(PROOF_JOBS_G2));
     for (unsigned b = 0; b < B; ++b) {
         const uint64_t *r = rs + 12 * b, *sv = r + 4, *rsv = r + 8;
         if (!fr_reduced(r) || !fr_reduced(sv) || (gamma_inv && !fr_reduced(rsv)))
@@ -983,14 +1016,13 @@ static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w
     uint32_t* d_vsc = reinterpret_cast<uint32_t*>(tp);
     DevBuf abc, bsc, d_fsc, jobs;
     VSP_TRY(bsc.alloc(ctx, size_t(B) * (pk->B_count ? pk->B_count : 1) * 32, s));
-    VSP_TRY(d_fsc.alloc(ctx, fsc.size() * 8, s));
+    VSP_TRY(d_fsc.alloc(ctx, fsc_n * 8, s));
     VSP_TRY(jobs.alloc(ctx, sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), s));
     VSP_TRY(abc.alloc(ctx, size_t(3) * B * m * 32, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc.data(), fsc.size() * 8, cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc, vsc.data(), vsc.size() * 8, cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.p, PROOF_JOBS_G1, sizeof(PROOF_JOBS_G1), cudaMemcpyHostToDevice, s));
-    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.as<char>() + sizeof(PROOF_JOBS_G1), PROOF_JOBS_G2, sizeof(PROOF_JOBS_G2),
-                                        cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_fsc.p, fsc, fsc_n * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(d_vsc, vsc, vsc_n * 8, cudaMemcpyHostToDevice, s));
+    VSP_CUDA_CHECK(ctx, cudaMemcpyAsync(jobs.p, host_jobs, sizeof(PROOF_JOBS_G1) + sizeof(PROOF_JOBS_G2), cudaMemcpyHostToDevice, s));
+    VSP_TRY(stage_commit(ctx, stage, s));
     const FixedJob* jobs1 = jobs.as<FixedJob>();
     const FixedJob* jobs2 = jobs1 + 4;
 
