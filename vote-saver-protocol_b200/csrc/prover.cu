@@ -921,7 +921,6 @@ static cudaStream_t side_stream(vsp_ctx* ctx, int i) { return ctx->prof.on ? ctx
 static const FixedJob PROOF_JOBS_G1[4] = {{0, 0}, {0, 1}, {0, 2}, {1, 3}};
 static const FixedJob PROOF_JOBS_G2[1] = {{0, 1}};
 
-// One chunk of B proofs, fully asynchronous: on return everything is enqueued on ctx->stream / side streams, joined
 // pinned staging slot of at least `bytes` for host data about to be uploaded on a stream (vsp_ctx::StageSlot)
 static int stage_acquire(vsp_ctx* ctx, size_t bytes, vsp_ctx::StageSlot** out) {
     vsp_ctx::StageSlot& sl = ctx->stage[ctx->stage_next++ & 3];
@@ -947,6 +946,7 @@ static int stage_commit(vsp_ctx* ctx, vsp_ctx::StageSlot* sl, cudaStream_t s) {
     return VSP_OK;
 }
 
+// One chunk of B proofs, fully asynchronous: on return everything is enqueued on ctx->stream / side streams, joined
 // back into ctx->stream, and d_proofs (B x 48 limbs) holds the results once ctx->stream completes.
 //   d_w: B assignments, w_stride apart.  rs: B x (r, s, r_saver) host scalars.
 static int prove_chunk(vsp_ctx* ctx, vsp_pk* pk, unsigned B, const uint32_t* d_w, uint64_t w_stride, const uint64_t* rs,
