@@ -456,6 +456,43 @@ VSP_API int vsp_codec_fast_pk_sizes(const uint8_t *blob, size_t len, vsp_fast_pk
 VSP_API int vsp_codec_fast_pk_read(const uint8_t *blob, size_t len, vsp_proving_key_t *desc);
 VSP_API int vsp_codec_fast_pk_write(const vsp_proving_key_t *desc, uint8_t *out, size_t capacity, size_t *written);
 
+/* The inverse of vsp_codec_ciphertext_write (deserialize_ct, bin/cli/include/nil/vote_saver/common.hpp:776): *n receives
+ * the count; ct == NULL queries it; capacity in points.  VSP_E_INVALID for a truncated blob or a malformed point. */
+VSP_API int vsp_codec_ciphertext_read(const uint8_t *in, size_t len, uint64_t *n, uint64_t *ct, uint64_t capacity);
+/* elgamal_verifiable public key, the vote phase's pk_eid blob (common.hpp:691, 1002;
+ * libs/marshalling/zk/.../pubkey/types/elgamal_verifiable.hpp, elgamal_verifiable_public_key / fill_public_key):
+ * delta_g1 | delta_sum_s_g1 | gamma_inverse_sum_s_g1 | delta_s_g1[msg_size] | t_g1[msg_size] | t_g2[msg_size + 1], every
+ * point compressed, every list count-prefixed.  write: out == NULL gives the size only.  read: pub == NULL gives
+ * *msg_size only; otherwise pub->msg_size must equal it and pub's six arrays, caller-allocated for that size, are filled
+ * (the filled struct goes straight into vsp_saver_pub_load / vsp_saver_encrypt). */
+VSP_API int vsp_codec_saver_pubkey_write(const vsp_saver_pubkey_t *pub, uint8_t *out, size_t capacity, size_t *written);
+VSP_API int vsp_codec_saver_pubkey_read(const uint8_t *blob, size_t len, uint64_t *msg_size, vsp_saver_pubkey_t *pub);
+/* elgamal_verifiable verification key (same file, elgamal_verifiable_verification_key / fill_verification_key;
+ * common.hpp:706): rho_g2 | rho_sv_g2[msg_size] | rho_rhov_g2[msg_size], what vsp_saver_decrypt /
+ * vsp_saver_verify_decryption take.  read: rho_g2 == NULL gives *msg_size only; otherwise capacity must equal it. */
+VSP_API int vsp_codec_saver_vk_write(uint64_t msg_size, const uint64_t *rho_g2, const uint64_t *rho_sv_g2,
+                                     const uint64_t *rho_rhov_g2, uint8_t *out, size_t capacity, size_t *written);
+VSP_API int vsp_codec_saver_vk_read(const uint8_t *blob, size_t len, uint64_t *msg_size, uint64_t *rho_g2,
+                                    uint64_t *rho_sv_g2, uint64_t *rho_rhov_g2, uint64_t capacity);
+/* elgamal_verifiable private key (same file, fill_private_key; common.hpp:722): rho as 32 big-endian bytes; the reader
+ * rejects a value that is not reduced mod r */
+VSP_API int vsp_codec_saver_sk_write(const uint64_t rho[4], uint8_t *out32);
+VSP_API int vsp_codec_saver_sk_read(const uint8_t *in, size_t len, uint64_t rho[4]);
+/* r1cs_gg_ppzksnark_extended_verification_key, the vote and tally phases' verification key blob (common.hpp:734, 1005;
+ * libs/marshalling/zk/.../r1cs_gg_ppzksnark/verification_key.hpp:128-152): alpha_g1_beta_g2 as 12 Fq coefficients in tower
+ * order (72 limbs here, the order vsp_pairing_products writes and vsp_groth16_verify_gt_batch reads) | gamma_g2 | delta_g2 |
+ * delta_g1 | gamma_g1 | gamma_ABC_g1 = first | rest, the rest a sparse_vector (indices | values | domain_size;
+ * accumulation_vector.hpp:52-57, sparse_vector.hpp:49-58).  gamma_ABC_g1 here is dense, gamma_ABC_count = 1 + domain size
+ * points; the writer lists every position of the rest (as the reference's generator builds it), the reader leaves
+ * positions the blob does not list at infinity.  write: out == NULL gives the size only.  read: alpha_g1_beta_g2 == NULL
+ * gives *gamma_ABC_count only; otherwise capacity must equal it. */
+VSP_API int vsp_codec_groth16_vk_write(const uint64_t *alpha_g1_beta_g2, const uint64_t *gamma_g2, const uint64_t *delta_g2,
+                                       const uint64_t *delta_g1, const uint64_t *gamma_g1, uint64_t gamma_ABC_count,
+                                       const uint64_t *gamma_ABC_g1, uint8_t *out, size_t capacity, size_t *written);
+VSP_API int vsp_codec_groth16_vk_read(const uint8_t *blob, size_t len, uint64_t *gamma_ABC_count, uint64_t *alpha_g1_beta_g2,
+                                      uint64_t *gamma_g2, uint64_t *delta_g2, uint64_t *delta_g1, uint64_t *gamma_g1,
+                                      uint64_t *gamma_ABC_g1, uint64_t capacity);
+
 /* ---- measurement helpers ---------------------------------------------------------------------- */
 /* 32x32->64 multiply-adds the G1 bucket-accumulation kernel of this build issues per bucket addition (the reference
  * algorithm's mixed Jacobian addition is 11 x 300 = 3,300): lets a roofline in reference units be read as pipe use */

@@ -212,3 +212,141 @@ def test_reference_made_proof_decodes():
                            cref.g1_to_limbs([o.g1_decompress(raw[144:])]).reshape(-1)])
     assert np.array_equal(proof, want)
     assert codec.proof_bytes(proof) == raw
+
+
+# ---- the other key / cipher-text blobs of the vote and tally phases --------------------------------------------------
+# From-the-spec serialisers (struct + the oracle's point encoders; nothing of the C codec): every list is an 8-byte
+# big-endian count then the elements, every point a compressed curve_element.
+
+def _c1(limbs) -> bytes:
+    return o.g1_compress(_g1(limbs))
+
+
+def _c2(limbs) -> bytes:
+    return o.g2_compress(_g2(limbs))
+
+
+def _list1(pts) -> bytes:
+    return struct.pack(">Q", len(pts)) + b"".join(_c1(p) for p in pts)
+
+
+def _list2(pts) -> bytes:
+    return struct.pack(">Q", len(pts)) + b"".join(_c2(p) for p in pts)
+
+
+def _saver_pub(n, seed):
+    g1, g2 = random_g1(2 * n + 3, seed), random_g2(n + 1, seed + 1)
+    return {"msg_size": n, "delta_g1": g1[0:1].copy(), "delta_sum_s_g1": g1[1:2].copy(),
+            "gamma_inverse_sum_s_g1": g1[2:3].copy(), "delta_s_g1": g1[3:3 + n].copy(), "t_g1": g1[3 + n:3 + 2 * n].copy(),
+            "t_g2": g2.copy()}
+
+
+def test_ciphertext_reader_inverts_the_writer_and_rejects_bad_blobs():
+    """deserialize_ct (common.hpp:776; primary_input.hpp:91-97): count | compressed G1..."""
+    ct = random_g1(27, 31)
+    ct[5] = 0  # a point at infinity travels as 0xc0 00...
+    blob = codec.ciphertext_bytes(ct)
+    assert blob == _list1(ct)
+    assert np.array_equal(codec.ciphertext_from_bytes(blob), ct)
+    assert codec.ciphertext_from_bytes(struct.pack(">Q", 0)).shape == (0, 12)
+    for bad in (blob[:-1], blob[:7], struct.pack(">Q", 28) + blob[8:], blob[:8] + bytes([blob[8] & 0x7f]) + blob[9:]):
+        with pytest.raises(ValueError):
+            codec.ciphertext_from_bytes(bad)
+
+
+@pytest.mark.parametrize("n", [1, 25])
+def test_saver_public_key_blob(n):
+    """elgamal_verifiable_public_key (libs/marshalling/zk/.../pubkey/types/elgamal_verifiable.hpp, fill_public_key): the field
+    order on the wire is delta_g1, delta_sum_s_g1, gamma_inverse_sum_s_g1, delta_s_g1, t_g1, t_g2 — not the struct's"""
+    pub = _saver_pub(n, 40 + n)
+    want = (_c1(pub["delta_g1"]) + _c1(pub["delta_sum_s_g1"]) + _c1(pub["gamma_inverse_sum_s_g1"]) +
+            _list1(pub["delta_s_g1"]) + _list1(pub["t_g1"]) + _list2(pub["t_g2"]))
+    blob = codec.saver_pubkey_bytes(pub)
+    assert blob == want and len(blob) == 3 * 48 + 24 + 2 * n * 48 + (n + 1) * 96
+    back = codec.saver_pubkey_from_bytes(blob)
+    assert back["msg_size"] == n
+    for k in ("delta_g1", "delta_sum_s_g1", "gamma_inverse_sum_s_g1", "delta_s_g1", "t_g1", "t_g2"):
+        assert np.array_equal(np.asarray(back[k]).reshape(-1), np.asarray(pub[k]).reshape(-1)), k
+    # truncated; lists of the wrong relative lengths (t_g2 must hold msg_size + 1 points); a malformed point
+    short_t_g2 = want[:-(8 + (n + 1) * 96)] + _list2(pub["t_g2"][:n])
+    for bad in (blob[:-1], blob[:100], short_t_g2, bytes([blob[0] & 0x7f]) + blob[1:]):
+        with pytest.raises(ValueError):
+            codec.saver_pubkey_from_bytes(bad)
+
+
+def test_saver_verification_and_secret_key_blobs():
+    """elgamal_verifiable_verification_key: rho_g2 | rho_sv_g2[] | rho_rhov_g2[]; elgamal_verifiable_private_key: rho"""
+    n = 25
+    g2 = random_g2(2 * n + 1, 77)
+    blob = codec.saver_vk_bytes(g2[0], g2[1:1 + n], g2[1 + n:])
+    assert blob == _c2(g2[0]) + _list2(g2[1:1 + n]) + _list2(g2[1 + n:])
+    a, b, c = codec.saver_vk_from_bytes(blob)
+    assert np.array_equal(a, g2[0]) and np.array_equal(b, g2[1:1 + n]) and np.array_equal(c, g2[1 + n:])
+    uneven = _c2(g2[0]) + _list2(g2[1:1 + n]) + _list2(g2[1 + n:2 * n])
+    for bad in (blob[:-1], uneven):
+        with pytest.raises(ValueError):
+            codec.saver_vk_from_bytes(bad)
+    rho = random.Random(5).randrange(o.R)
+    sk = codec.saver_sk_bytes(cref.ints_to_limbs([rho], 4)[0])
+    assert sk == rho.to_bytes(32, "big")
+    assert cref.limbs_to_ints(codec.saver_sk_from_bytes(sk).reshape(1, 4))[0] == rho
+    for bad in (o.R.to_bytes(32, "big"), (o.R + 5).to_bytes(32, "big"), sk[:31]):
+        with pytest.raises(ValueError):
+            codec.saver_sk_from_bytes(bad)
+    assert cref.limbs_to_ints(codec.saver_sk_from_bytes((o.R - 1).to_bytes(32, "big")).reshape(1, 4))[0] == o.R - 1
+
+
+def _databin_vk():
+    g = golden("databin_groth16.json")
+    coeffs = [int(x, 16) for x in g["alpha_g1_beta_g2"]]
+    gamma, delta = bytes.fromhex(g["gamma_g2"]), bytes.fromhex(g["delta_g2"])
+    first = bytes.fromhex(g["gamma_ABC_first"])
+    return g, coeffs, gamma, delta, first
+
+
+def test_extended_verification_key_blob_on_the_reference_made_key():
+    """r1cs_gg_ppzksnark_extended_verification_key (verification_key.hpp:128-152) around the one crypto3-made key of the
+    tree (bin/cli/src/data.bin, which stores the same fields under the TVM blob's little-endian integers): the GT element's
+    twelve coefficients keep their tower order, each as a 48-byte big-endian integer; the points are the reference's own
+    octets; the key read back through the C codec still verifies the reference's proof in the oracle."""
+    g, coeffs, gamma, delta, first = _databin_vk()
+    extra = random_g1(5, 9)  # delta_g1, gamma_g1 and three rest points (data.bin's key has no primary input)
+    gt_limbs = cref.ints_to_limbs(coeffs, 6).reshape(-1)
+    abc = np.concatenate([codec.g1_decompress(first).reshape(1, 12), extra[2:]])
+    blob = codec.groth16_vk_bytes(gt_limbs, codec.g2_decompress(gamma), codec.g2_decompress(delta), extra[0], extra[1], abc)
+    want = (b"".join(c.to_bytes(48, "big") for c in coeffs) + gamma + delta + _c1(extra[0]) + _c1(extra[1]) + first +
+            struct.pack(">Q", 3) + struct.pack(">3Q", 0, 1, 2) + _list1(extra[2:]) + struct.pack(">Q", 3))
+    assert blob == want
+    vk = codec.groth16_vk_from_bytes(blob)
+    assert np.array_equal(vk["alpha_g1_beta_g2"], gt_limbs) and np.array_equal(vk["gamma_ABC_g1"], abc)
+    assert np.array_equal(vk["delta_g1"], extra[0]) and np.array_equal(vk["gamma_g1"], extra[1])
+    # what the codec read is the key the reference's proof verifies under (primary input 0, 0, 0 leaves acc = first)
+    pr = bytes.fromhex(g["proof"])
+    J1, J2 = o.G1.from_affine, o.G2.from_affine
+    proof = (J1(o.g1_decompress(pr[:48])), J2(o.g2_decompress(pr[48:144])), J1(o.g1_decompress(pr[144:])))
+    gt = o.gt_from_coeffs(cref.limbs_to_ints(vk["alpha_g1_beta_g2"].reshape(12, 6)))
+    rest = [_g1(p) for p in vk["gamma_ABC_g1"][1:]]
+    assert o.groth16_verify_gt(gt, _g2(vk["gamma_g2"]), _g2(vk["delta_g2"]), _g1(vk["gamma_ABC_g1"][0]), rest, [0, 0, 0], proof)
+    assert not o.groth16_verify_gt(gt, _g2(vk["gamma_g2"]), _g2(vk["delta_g2"]), _g1(vk["gamma_ABC_g1"][0]), rest, [0, 1, 0], proof)
+
+
+def test_extended_verification_key_sparse_rest_and_bad_blobs():
+    """the rest of gamma_ABC_g1 is a sparse_vector (sparse_vector.hpp:49-58): positions the blob does not list read as the
+    point at infinity; indices must increase and stay inside the domain"""
+    _, coeffs, gamma, delta, first = _databin_vk()
+    pts = random_g1(4, 12)
+    head = b"".join(c.to_bytes(48, "big") for c in coeffs) + gamma + delta + _c1(pts[0]) + _c1(pts[1]) + first
+
+    def tail(indices, values, domain):
+        return struct.pack(">Q", len(indices)) + b"".join(struct.pack(">Q", i) for i in indices) + _list1(values) + struct.pack(">Q", domain)
+
+    vk = codec.groth16_vk_from_bytes(head + tail([1, 4], pts[2:4], 6))
+    assert vk["gamma_ABC_g1"].shape == (7, 12)
+    assert np.array_equal(vk["gamma_ABC_g1"][2], pts[2]) and np.array_equal(vk["gamma_ABC_g1"][5], pts[3])
+    assert not vk["gamma_ABC_g1"][[1, 3, 4, 6]].any()
+    assert codec.groth16_vk_from_bytes(head + tail([], pts[:0], 0))["gamma_ABC_g1"].shape == (1, 12)
+    not_reduced = o.P.to_bytes(48, "big") + head[48:]
+    for bad in (head + tail([4, 1], pts[2:4], 6), head + tail([1, 1], pts[2:4], 6), head + tail([1, 6], pts[2:4], 6),
+                head + tail([1], pts[2:4], 6), (head + tail([1, 4], pts[2:4], 6))[:-1], head[:500], not_reduced + tail([], pts[:0], 0)):
+        with pytest.raises(ValueError):
+            codec.groth16_vk_from_bytes(bad)

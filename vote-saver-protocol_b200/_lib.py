@@ -174,6 +174,15 @@ SYMBOLS = [
     ("vsp_codec_fast_pk_sizes", _int, [_vp, C.c_size_t, C.POINTER(FastPkSizes)]),
     ("vsp_codec_fast_pk_read", _int, [_vp, C.c_size_t, C.POINTER(ProvingKeyDesc)]),
     ("vsp_codec_fast_pk_write", _int, [C.POINTER(ProvingKeyDesc), _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    ("vsp_codec_ciphertext_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), _vp, _u64]),
+    ("vsp_codec_saver_pubkey_write", _int, [C.POINTER(SaverPubkeyDesc), _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    ("vsp_codec_saver_pubkey_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), C.POINTER(SaverPubkeyDesc)]),
+    ("vsp_codec_saver_vk_write", _int, [_u64, _vp, _vp, _vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    ("vsp_codec_saver_vk_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), _vp, _vp, _vp, _u64]),
+    ("vsp_codec_saver_sk_write", _int, [_vp, _vp]),
+    ("vsp_codec_saver_sk_read", _int, [_vp, C.c_size_t, _vp]),
+    ("vsp_codec_groth16_vk_write", _int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    ("vsp_codec_groth16_vk_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), _vp, _vp, _vp, _vp, _vp, _vp, _u64]),
     ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
     ("vsp_measure_dfma_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
     ("vsp_accumulate_mads_per_add", _int, [_vp, C.POINTER(C.c_double)]),

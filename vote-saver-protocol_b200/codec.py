@@ -96,6 +96,113 @@ def primary_input_from_bytes(blob: bytes) -> np.ndarray:
     return out
 
 
+def ciphertext_from_bytes(blob: bytes) -> np.ndarray:
+    """ct.bin -> n x 12 limbs (deserialize_ct, common.hpp:776)"""
+    n = C.c_uint64(0)
+    buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+    lib = _lib.load()
+    _check(lib.vsp_codec_ciphertext_read(buf, len(blob), C.byref(n), None, 0), "ciphertext_read")
+    out = np.zeros((n.value, 12), dtype=np.uint64)
+    _check(lib.vsp_codec_ciphertext_read(buf, len(blob), C.byref(n), out.ctypes.data, n.value), "ciphertext_read")
+    return out
+
+
+def _two_pass_write(call) -> bytes:
+    n = C.c_size_t(0)
+    _check(call(None, 0, C.byref(n)), "size query")
+    out = _out(n.value)
+    _check(call(out, n.value, C.byref(n)), "write")
+    return bytes(out)
+
+
+def saver_pubkey_bytes(pub: dict) -> bytes:
+    """the arrays dict SaverPublicKey takes (field names of vsp_saver_pubkey_t) -> the pk_eid blob (common.hpp:357)"""
+    arr = {k: (_u64(v) if isinstance(v, np.ndarray) else v) for k, v in pub.items()}
+    desc = fill_desc(_lib.SaverPubkeyDesc(), arr)
+    lib = _lib.load()
+    return _two_pass_write(lambda out, cap, n: lib.vsp_codec_saver_pubkey_write(C.byref(desc), out, cap, n))
+
+
+def saver_pubkey_from_bytes(blob: bytes) -> dict:
+    """the pk_eid blob (deserialize_pk_eid, common.hpp:691) -> the arrays dict SaverPublicKey takes"""
+    lib = _lib.load()
+    buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+    n = C.c_uint64(0)
+    _check(lib.vsp_codec_saver_pubkey_read(buf, len(blob), C.byref(n), None), "saver_pubkey_read")
+    k = n.value
+    arr = {"msg_size": k, "delta_g1": np.zeros((1, 12), dtype=np.uint64),
+           "delta_s_g1": np.zeros((max(k, 1), 12), dtype=np.uint64), "t_g1": np.zeros((max(k, 1), 12), dtype=np.uint64),
+           "t_g2": np.zeros((k + 1, 24), dtype=np.uint64), "delta_sum_s_g1": np.zeros((1, 12), dtype=np.uint64),
+           "gamma_inverse_sum_s_g1": np.zeros((1, 12), dtype=np.uint64)}
+    desc = fill_desc(_lib.SaverPubkeyDesc(), arr)
+    _check(lib.vsp_codec_saver_pubkey_read(buf, len(blob), None, C.byref(desc)), "saver_pubkey_read")
+    arr["delta_s_g1"], arr["t_g1"] = arr["delta_s_g1"][:k], arr["t_g1"][:k]
+    return arr
+
+
+def saver_vk_bytes(rho_g2, rho_sv_g2, rho_rhov_g2) -> bytes:
+    a, b, c = _u64(rho_g2).reshape(-1), _u64(rho_sv_g2, 24), _u64(rho_rhov_g2, 24)
+    if a.shape[0] != 24 or b.shape != c.shape:
+        raise ValueError("rho_g2 is one G2 point; rho_sv_g2 and rho_rhov_g2 hold msg_size G2 points each")
+    lib = _lib.load()
+    return _two_pass_write(lambda out, cap, n: lib.vsp_codec_saver_vk_write(b.shape[0], a.ctypes.data, b.ctypes.data,
+                                                                            c.ctypes.data, out, cap, n))
+
+
+def saver_vk_from_bytes(blob: bytes):
+    """-> (rho_g2 [24], rho_sv_g2 [n, 24], rho_rhov_g2 [n, 24])   (deserialize_vk_eid, common.hpp:706)"""
+    lib = _lib.load()
+    buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+    n = C.c_uint64(0)
+    _check(lib.vsp_codec_saver_vk_read(buf, len(blob), C.byref(n), None, None, None, 0), "saver_vk_read")
+    k = n.value
+    a, b, c = (np.zeros(24, dtype=np.uint64), np.zeros((max(k, 1), 24), dtype=np.uint64),
+               np.zeros((max(k, 1), 24), dtype=np.uint64))
+    _check(lib.vsp_codec_saver_vk_read(buf, len(blob), None, a.ctypes.data, b.ctypes.data, c.ctypes.data, k), "saver_vk_read")
+    return a, b[:k], c[:k]
+
+
+def saver_sk_bytes(rho) -> bytes:
+    r, out = _u64(rho).reshape(-1), _out(32)
+    _check(_lib.load().vsp_codec_saver_sk_write(r.ctypes.data, out), "saver_sk_write")
+    return bytes(out)
+
+
+def saver_sk_from_bytes(blob: bytes) -> np.ndarray:
+    out = np.zeros(4, dtype=np.uint64)
+    _check(_lib.load().vsp_codec_saver_sk_read(bytes(blob), len(blob), out.ctypes.data), "saver_sk_read")
+    return out
+
+
+def groth16_vk_bytes(alpha_g1_beta_g2, gamma_g2, delta_g2, delta_g1, gamma_g1, gamma_ABC_g1) -> bytes:
+    """the extended verification key blob (common.hpp:351): alpha_g1_beta_g2 72 limbs (vsp_pairing_products' order),
+    gamma_ABC_g1 = first | rest as (1 + n) x 12 limbs"""
+    gt, g2a, g2b = _u64(alpha_g1_beta_g2).reshape(-1), _u64(gamma_g2).reshape(-1), _u64(delta_g2).reshape(-1)
+    g1a, g1b, abc = _u64(delta_g1).reshape(-1), _u64(gamma_g1).reshape(-1), _u64(gamma_ABC_g1, 12)
+    if gt.shape[0] != 72 or g2a.shape[0] != 24 or g2b.shape[0] != 24 or g1a.shape[0] != 12 or g1b.shape[0] != 12:
+        raise ValueError("groth16 verification key: wrong limb counts")
+    lib = _lib.load()
+    return _two_pass_write(lambda out, cap, n: lib.vsp_codec_groth16_vk_write(
+        gt.ctypes.data, g2a.ctypes.data, g2b.ctypes.data, g1a.ctypes.data, g1b.ctypes.data, abc.shape[0], abc.ctypes.data,
+        out, cap, n))
+
+
+def groth16_vk_from_bytes(blob: bytes) -> dict:
+    """deserialize_vk_crs (common.hpp:734) -> {alpha_g1_beta_g2 [72], gamma_g2, delta_g2 [24], delta_g1, gamma_g1 [12],
+    gamma_ABC_g1 [(1 + n), 12]}: the arguments of vsp_groth16_verify_gt_batch, and gamma_ABC_g1[1:] is the gamma_abc_rest
+    the SAVER entry points take"""
+    lib = _lib.load()
+    buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+    n = C.c_uint64(0)
+    _check(lib.vsp_codec_groth16_vk_read(buf, len(blob), C.byref(n), None, None, None, None, None, None, 0), "groth16_vk_read")
+    vk = {"alpha_g1_beta_g2": np.zeros(72, dtype=np.uint64), "gamma_g2": np.zeros(24, dtype=np.uint64),
+          "delta_g2": np.zeros(24, dtype=np.uint64), "delta_g1": np.zeros(12, dtype=np.uint64),
+          "gamma_g1": np.zeros(12, dtype=np.uint64), "gamma_ABC_g1": np.zeros((n.value, 12), dtype=np.uint64)}
+    _check(lib.vsp_codec_groth16_vk_read(buf, len(blob), None, *(vk[k].ctypes.data for k in (
+        "alpha_g1_beta_g2", "gamma_g2", "delta_g2", "delta_g1", "gamma_g1", "gamma_ABC_g1")), n.value), "groth16_vk_read")
+    return vk
+
+
 def read_fast_proving_key(blob: bytes) -> dict:
     """r1cs_proving_key.bin -> the arrays dict ProvingKey(ctx, arrays) takes (field names of vsp_proving_key_t)"""
     lib = _lib.load()

@@ -615,3 +615,236 @@ int vsp_codec_fast_pk_write(const vsp_proving_key_t* d, uint8_t* out, size_t cap
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The other key and cipher-text blobs of the vote and tally phases, all in compressed curve_element form:
+//   cipher text (reader)          count | G1...                                 deserialize_ct, common.hpp:776
+//   SAVER public key  pk_eid      delta_g1 | delta_sum_s_g1 | gamma_inverse_sum_s_g1 | delta_s_g1[] | t_g1[] | t_g2[]
+//                                 (zk/.../pubkey/types/elgamal_verifiable.hpp: elgamal_verifiable_public_key, fill_public_key;
+//                                  read by the vote phase, common.hpp:691, 1002)
+//   SAVER verification key        rho_g2 | rho_sv_g2[] | rho_rhov_g2[]           (same file: fill_verification_key)
+//   SAVER secret key              rho: Fr                                        (same file: fill_private_key)
+//   Groth16 extended verif. key   alpha_g1_beta_g2 (12 Fq, tower order) | gamma_g2 | delta_g2 | delta_g1 | gamma_g1 |
+//                                 gamma_ABC_g1 = first | rest as sparse_vector (indices[] | values[] | domain_size)
+//                                 (zk/.../r1cs_gg_ppzksnark/verification_key.hpp:128-152, accumulation_vector.hpp:52-57,
+//                                  sparse_vector.hpp:49-58; read by the vote phase, common.hpp:734, 1005)
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t G1_C = FQ_BYTES, G2_C = 2 * FQ_BYTES;
+
+// count-prefixed list of compressed points of `width` bytes; dst == nullptr: walk only.  `expect` != ~0: the count the
+// caller's arrays were sized for
+bool point_list(Reader& r, size_t width, uint64_t expect, uint64_t* dst, uint64_t* count) {
+    const uint64_t n = r.u64();
+    if (!r.ok || n > r.left / width) return r.ok = false;
+    if (count) *count = n;
+    if (dst && n != expect) return r.ok = false;
+    const size_t limbs = width == G1_C ? 12 : 24;
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint8_t* q = r.take(width);
+        if (!q) return false;
+        if (dst && (width == G1_C ? g1_decompress(q, dst + limbs * i) : g2_decompress(q, dst + limbs * i)) != VSP_OK)
+            return r.ok = false;
+    }
+    return true;
+}
+bool point_one(Reader& r, size_t width, uint64_t* dst) {
+    const uint8_t* q = r.take(width);
+    if (!q) return false;
+    if (dst && (width == G1_C ? g1_decompress(q, dst) : g2_decompress(q, dst)) != VSP_OK) return r.ok = false;
+    return true;
+}
+
+struct Writer {
+    uint8_t* p;
+    void g1(const uint64_t* src) { g1_compress(src, p); p += G1_C; }
+    void g2(const uint64_t* src) { g2_compress(src, p); p += G2_C; }
+    void u64(uint64_t v) { put_u64(p, v); p += 8; }
+    void g1_list(const uint64_t* src, uint64_t n) { u64(n); for (uint64_t i = 0; i < n; ++i) g1(src + 12 * i); }
+    void g2_list(const uint64_t* src, uint64_t n) { u64(n); for (uint64_t i = 0; i < n; ++i) g2(src + 24 * i); }
+};
+
+}  // namespace
+
+extern "C" {
+
+// 8 + 48 n bytes -> n cipher-text G1 points; *n receives the count; ct may be NULL to query it; capacity in points
+int vsp_codec_ciphertext_read(const uint8_t* in, size_t len, uint64_t* n, uint64_t* ct, uint64_t capacity) {
+    if (!in || !n) return VSP_E_INVALID;
+    Reader r {in, len};
+    uint64_t cnt = 0;
+    if (!point_list(r, G1_C, 0, nullptr, &cnt)) return VSP_E_INVALID;
+    *n = cnt;
+    if (!ct) return VSP_OK;
+    if (capacity < cnt) return VSP_E_INVALID;
+    Reader r2 {in, len};
+    return point_list(r2, G1_C, cnt, ct, nullptr) ? VSP_OK : VSP_E_INVALID;
+}
+
+// size of / the serialised public key: msg_size points in delta_s_g1 and t_g1, msg_size + 1 in t_g2 (what
+// generate_keypair_op builds, elgamal_verifiable.hpp:218-271)
+int vsp_codec_saver_pubkey_write(const vsp_saver_pubkey_t* pub, uint8_t* out, size_t capacity, size_t* written) {
+    if (!pub || !written) return VSP_E_INVALID;
+    const uint64_t n = pub->msg_size;
+    const size_t need = 3 * G1_C + 3 * 8 + 2 * n * G1_C + (n + 1) * G2_C;
+    *written = need;
+    if (!out) return VSP_OK;
+    if (capacity < need) return VSP_E_INVALID;
+    Writer w {out};
+    w.g1(pub->delta_g1);
+    w.g1(pub->delta_sum_s_g1);
+    w.g1(pub->gamma_inverse_sum_s_g1);
+    w.g1_list(pub->delta_s_g1, n);
+    w.g1_list(pub->t_g1, n);
+    w.g2_list(pub->t_g2, n + 1);
+    return (size_t)(w.p - out) == need ? VSP_OK : VSP_E_INVALID;
+}
+
+// pub == NULL: *msg_size receives the blob's message size (the length of its delta_s_g1 list).  Otherwise pub->msg_size
+// must equal it, pub's six arrays are caller-allocated for that size and are filled.  VSP_E_INVALID for a truncated blob,
+// a malformed point, or lists that are not msg_size | msg_size | msg_size + 1 long.
+int vsp_codec_saver_pubkey_read(const uint8_t* blob, size_t len, uint64_t* msg_size, vsp_saver_pubkey_t* pub) {
+    if (!blob || (!msg_size && !pub)) return VSP_E_INVALID;
+    Reader r {blob, len};
+    auto w = [](const uint64_t* q) { return const_cast<uint64_t*>(q); };
+    if (pub && (!pub->delta_g1 || !pub->delta_sum_s_g1 || !pub->gamma_inverse_sum_s_g1 || !pub->delta_s_g1 || !pub->t_g1 ||
+                !pub->t_g2))
+        return VSP_E_INVALID;
+    point_one(r, G1_C, pub ? w(pub->delta_g1) : nullptr);
+    point_one(r, G1_C, pub ? w(pub->delta_sum_s_g1) : nullptr);
+    point_one(r, G1_C, pub ? w(pub->gamma_inverse_sum_s_g1) : nullptr);
+    uint64_t n0 = 0, n1 = 0, n2 = 0;
+    const uint64_t n = pub ? pub->msg_size : 0;
+    if (!r.ok || !point_list(r, G1_C, n, pub ? w(pub->delta_s_g1) : nullptr, &n0)) return VSP_E_INVALID;
+    if (!point_list(r, G1_C, n, pub ? w(pub->t_g1) : nullptr, &n1)) return VSP_E_INVALID;
+    if (!point_list(r, G2_C, n + 1, pub ? w(pub->t_g2) : nullptr, &n2)) return VSP_E_INVALID;
+    if (n1 != n0 || n2 != n0 + 1) return VSP_E_INVALID;
+    if (msg_size) *msg_size = n0;
+    return VSP_OK;
+}
+
+int vsp_codec_saver_vk_write(uint64_t msg_size, const uint64_t* rho_g2, const uint64_t* rho_sv_g2,
+                             const uint64_t* rho_rhov_g2, uint8_t* out, size_t capacity, size_t* written) {
+    if (!written || !rho_g2 || (msg_size && (!rho_sv_g2 || !rho_rhov_g2))) return VSP_E_INVALID;
+    const size_t need = G2_C + 2 * 8 + 2 * msg_size * G2_C;
+    *written = need;
+    if (!out) return VSP_OK;
+    if (capacity < need) return VSP_E_INVALID;
+    Writer w {out};
+    w.g2(rho_g2);
+    w.g2_list(rho_sv_g2, msg_size);
+    w.g2_list(rho_rhov_g2, msg_size);
+    return VSP_OK;
+}
+
+// rho_g2 == NULL: *msg_size receives the length of the two lists.  Otherwise the three arrays hold 1 | capacity |
+// capacity G2 points and capacity must equal that length.
+int vsp_codec_saver_vk_read(const uint8_t* blob, size_t len, uint64_t* msg_size, uint64_t* rho_g2, uint64_t* rho_sv_g2,
+                            uint64_t* rho_rhov_g2, uint64_t capacity) {
+    if (!blob || (!msg_size && !rho_g2)) return VSP_E_INVALID;
+    if (rho_g2 && (!rho_sv_g2 || !rho_rhov_g2)) return VSP_E_INVALID;
+    Reader r {blob, len};
+    uint64_t n0 = 0, n1 = 0;
+    if (!point_one(r, G2_C, rho_g2)) return VSP_E_INVALID;
+    if (!point_list(r, G2_C, capacity, rho_g2 ? rho_sv_g2 : nullptr, &n0)) return VSP_E_INVALID;
+    if (!point_list(r, G2_C, capacity, rho_g2 ? rho_rhov_g2 : nullptr, &n1)) return VSP_E_INVALID;
+    if (n0 != n1) return VSP_E_INVALID;
+    if (msg_size) *msg_size = n0;
+    return VSP_OK;
+}
+
+// rho <-> 32 big-endian bytes; the reader rejects a value that is not reduced mod r
+int vsp_codec_saver_sk_write(const uint64_t rho[4], uint8_t* out32) {
+    if (!rho || !out32) return VSP_E_INVALID;
+    put_be(out32, rho, FR_BYTES);
+    return VSP_OK;
+}
+int vsp_codec_saver_sk_read(const uint8_t* in, size_t len, uint64_t rho[4]) {
+    static const uint64_t R[4] = {0xffffffff00000001ull, 0x53bda402fffe5bfeull, 0x3339d80809a1d805ull, 0x73eda753299d7d48ull};
+    if (!in || !rho || len < FR_BYTES) return VSP_E_INVALID;
+    get_be(in, rho, FR_BYTES);
+    for (int i = 3; i >= 0; --i) {
+        if (rho[i] < R[i]) return VSP_OK;
+        if (rho[i] > R[i]) return VSP_E_INVALID;
+    }
+    return VSP_E_INVALID;  // rho == r
+}
+
+// gamma_ABC_g1 = first | rest, gamma_ABC_count = 1 + the rest's domain size; the rest is written dense (indices
+// 0 .. count - 2), the way sparse_vector(std::vector&&) builds it (libs/containers/.../sparse_vector.hpp:81-84)
+int vsp_codec_groth16_vk_write(const uint64_t* alpha_g1_beta_g2, const uint64_t* gamma_g2, const uint64_t* delta_g2,
+                               const uint64_t* delta_g1, const uint64_t* gamma_g1, uint64_t gamma_ABC_count,
+                               const uint64_t* gamma_ABC_g1, uint8_t* out, size_t capacity, size_t* written) {
+    if (!written || !alpha_g1_beta_g2 || !gamma_g2 || !delta_g2 || !delta_g1 || !gamma_g1 || !gamma_ABC_g1 ||
+        gamma_ABC_count == 0)
+        return VSP_E_INVALID;
+    const uint64_t n = gamma_ABC_count - 1;
+    const size_t need = 12 * FQ_BYTES + 2 * G2_C + 3 * G1_C + 8 + 8 * n + 8 + n * G1_C + 8;
+    *written = need;
+    if (!out) return VSP_OK;
+    if (capacity < need) return VSP_E_INVALID;
+    Writer w {out};
+    for (int i = 0; i < 12; ++i) {
+        put_be(w.p, alpha_g1_beta_g2 + 6 * i, FQ_BYTES);
+        w.p += FQ_BYTES;
+    }
+    w.g2(gamma_g2);
+    w.g2(delta_g2);
+    w.g1(delta_g1);
+    w.g1(gamma_g1);
+    w.g1(gamma_ABC_g1);
+    w.u64(n);
+    for (uint64_t i = 0; i < n; ++i) w.u64(i);
+    w.g1_list(gamma_ABC_g1 + 12, n);
+    w.u64(n);
+    return (size_t)(w.p - out) == need ? VSP_OK : VSP_E_INVALID;
+}
+
+// alpha_g1_beta_g2 == NULL: *gamma_ABC_count receives 1 + the rest's domain size.  Otherwise every array is filled
+// (alpha_g1_beta_g2: 72 limbs in vsp_pairing_products' order; gamma_ABC_g1: capacity points, capacity == that count;
+// positions the sparse rest does not list are the point at infinity).  VSP_E_INVALID for a truncated blob, a malformed
+// point, an Fq coefficient >= p, indices that do not increase or reach the domain size.
+int vsp_codec_groth16_vk_read(const uint8_t* blob, size_t len, uint64_t* gamma_ABC_count, uint64_t* alpha_g1_beta_g2,
+                              uint64_t* gamma_g2, uint64_t* delta_g2, uint64_t* delta_g1, uint64_t* gamma_g1,
+                              uint64_t* gamma_ABC_g1, uint64_t capacity) {
+    if (!blob || (!gamma_ABC_count && !alpha_g1_beta_g2)) return VSP_E_INVALID;
+    const bool fill = alpha_g1_beta_g2 != nullptr;
+    if (fill && (!gamma_g2 || !delta_g2 || !delta_g1 || !gamma_g1 || !gamma_ABC_g1)) return VSP_E_INVALID;
+    Reader r {blob, len};
+    for (int i = 0; i < 12; ++i) {
+        const uint8_t* q = r.take(FQ_BYTES);
+        if (!q) return VSP_E_INVALID;
+        uint64_t c[6];
+        get_be(q, c, FQ_BYTES);
+        if (hfq_geq_p(c)) return VSP_E_INVALID;
+        if (fill) memcpy(alpha_g1_beta_g2 + 6 * i, c, 48);
+    }
+    if (!point_one(r, G2_C, fill ? gamma_g2 : nullptr) || !point_one(r, G2_C, fill ? delta_g2 : nullptr) ||
+        !point_one(r, G1_C, fill ? delta_g1 : nullptr) || !point_one(r, G1_C, fill ? gamma_g1 : nullptr) ||
+        !point_one(r, G1_C, fill ? gamma_ABC_g1 : nullptr))
+        return VSP_E_INVALID;
+    const uint64_t n_idx = r.u64();
+    if (!r.ok || n_idx > r.left / 8) return VSP_E_INVALID;
+    const uint8_t* idx = r.take(8 * n_idx);
+    const uint64_t n_val = r.u64();
+    if (!idx || !r.ok || n_val != n_idx || n_val > r.left / G1_C) return VSP_E_INVALID;
+    const uint8_t* val = r.take(G1_C * n_val);
+    const uint64_t domain = r.u64();
+    if (!val || !r.ok || domain == ~uint64_t(0) || n_idx > domain) return VSP_E_INVALID;
+    if (gamma_ABC_count) *gamma_ABC_count = domain + 1;
+    uint64_t prev = 0;
+    for (uint64_t i = 0; i < n_idx; ++i) {
+        const uint64_t k = get_u64(idx + 8 * i);
+        if (k >= domain || (i && k <= prev)) return VSP_E_INVALID;
+        prev = k;
+    }
+    if (!fill) return VSP_OK;
+    if (capacity != domain + 1) return VSP_E_INVALID;
+    memset(gamma_ABC_g1 + 12, 0, (size_t)domain * 96);
+    for (uint64_t i = 0; i < n_idx; ++i)
+        if (g1_decompress(val + G1_C * i, gamma_ABC_g1 + 12 * (1 + get_u64(idx + 8 * i))) != VSP_OK) return VSP_E_INVALID;
+    return VSP_OK;
+}
+
+}  // extern "C"
