@@ -493,6 +493,22 @@ VSP_API int vsp_codec_groth16_vk_read(const uint8_t *blob, size_t len, uint64_t 
                                       uint64_t *gamma_g2, uint64_t *delta_g2, uint64_t *delta_g1, uint64_t *gamma_g1,
                                       uint64_t *gamma_ABC_g1, uint64_t capacity);
 
+/* The vote phase's remaining inputs (common.hpp:996-1003), host only.
+ * serialize_bitarray / deserialize_bitarray (common.hpp:574-612): bits holds n_bits bytes of 0 / 1; bit i travels in octet
+ * i / 8, most significant bit first; the blob is exactly ceil(n_bits / 8) octets. */
+VSP_API int vsp_codec_bitarray_write(const uint8_t *bits, uint64_t n_bits, uint8_t *out);
+VSP_API int vsp_codec_bitarray_read(const uint8_t *in, size_t len, uint64_t n_bits, uint8_t *bits);
+/* get_multi_field_element_from_bits (common.hpp:543-570): ceil(n_bits / 254) canonical Fr, bit j of a chunk weighs 2^j */
+VSP_API int vsp_codec_bits_to_field_elements(const uint8_t *bits, uint64_t n_bits, uint64_t *out);
+/* deserialize_merkle_tree (common.hpp:614-636; libs/containers/include/nil/crypto3/container/merkle/tree.hpp:424-427,
+ * 492-499): 2^(depth + 1) - 1 digests of 255 bits as 32-octet bit arrays, leaves first, then row by row, the root last.
+ * digests: 4 limbs each, bit i of the integer = digest bit i. */
+VSP_API int vsp_codec_merkle_tree_write(const uint64_t *digests, uint64_t depth, uint8_t *out);
+VSP_API int vsp_codec_merkle_tree_read(const uint8_t *blob, size_t len, uint64_t depth, uint64_t *digests);
+/* containers::merkle_proof<hash, 2>(tree, index) (libs/containers/.../merkle/proof.hpp:65-91): the depth sibling digests
+ * from the leaf level up, i.e. one row of vsp_voting_witness_batch_dev's paths */
+VSP_API int vsp_codec_merkle_copath(const uint64_t *digests, uint64_t depth, uint64_t index, uint64_t *path);
+
 /* ---- measurement helpers ---------------------------------------------------------------------- */
 /* 32x32->64 multiply-adds the G1 bucket-accumulation kernel of this build issues per bucket addition (the reference
  * algorithm's mixed Jacobian addition is 11 x 300 = 3,300): lets a roofline in reference units be read as pipe use */

@@ -350,3 +350,78 @@ def test_extended_verification_key_sparse_rest_and_bad_blobs():
                 head + tail([1], pts[2:4], 6), (head + tail([1, 4], pts[2:4], 6))[:-1], head[:500], not_reduced + tail([], pts[:0], 0)):
         with pytest.raises(ValueError):
             codec.groth16_vk_from_bytes(bad)
+
+
+# ---- the vote phase's remaining inputs: bit arrays, the voters' Merkle tree, the copath, bit packing --------------------
+
+def _bits_to_octets(bits):
+    """stream_endian::big_octet_big_bit, from the definition: the bit string read as one big-endian binary number"""
+    pad = list(bits) + [0] * (-len(bits) % 8)
+    return bytes(int("".join(map(str, pad[i:i + 8])), 2) for i in range(0, len(pad), 8))
+
+
+def test_bitarray_blob():
+    """serialize_bitarray / deserialize_bitarray (common.hpp:574-612) at the sizes bin/cli uses (255-bit keys) and around
+    octet boundaries"""
+    rng = random.Random(3)
+    for n in (1, 7, 8, 9, 64, 255, 256):
+        bits = [rng.randrange(2) for _ in range(n)]
+        blob = codec.bitarray_bytes(bits)
+        assert blob == _bits_to_octets(bits) and len(blob) == (n + 7) // 8
+        assert list(codec.bitarray_from_bytes(blob, n)) == bits
+    assert codec.bitarray_bytes([1, 0, 0, 0, 0, 0, 0, 0, 1]) == b"\x80\x80"
+    with pytest.raises(ValueError):
+        codec.bitarray_from_bytes(bytes(31), 255)
+    with pytest.raises(ValueError):
+        codec.bitarray_from_bytes(bytes(33), 255)
+
+
+def test_bits_pack_into_field_elements_like_the_reference_loop():
+    """get_multi_field_element_from_bits over get_field_element_from_bits (common.hpp:543-570), restated as its loop"""
+    def field_from_bits(bits):
+        result = 0
+        for i in range(len(bits)):
+            result = (result + (result + bits[len(bits) - 1 - i])) % o.R
+        return result
+    rng = random.Random(4)
+    for n in (1, 64, 253, 254, 255, 508, 509, 600):
+        bits = [rng.randrange(2) for _ in range(n)]
+        want = [field_from_bits(bits[i:i + 254]) for i in range(0, n, 254)]
+        assert cref.limbs_to_ints(codec.bits_to_field_elements(bits)) == want
+    # the three uses in the ballot's primary input: eid (64 bits -> 1 element), sn and rt (255 bits -> 2 elements)
+    assert codec.bits_to_field_elements([1] * 64).shape == (1, 4) and codec.bits_to_field_elements([1] * 255).shape == (2, 4)
+
+
+def test_merkle_tree_blob_and_copath():
+    """deserialize_merkle_tree (common.hpp:614-636) and merkle_proof (containers/merkle/proof.hpp:65-91) on a depth-3 voter
+    tree built by the circuit module's native hash: node order leaves | rows | root, digests as 32-octet bit arrays, the
+    copath equal to an independent per-level computation, the root the one the circuit's public input packs"""
+    voting = importlib.import_module("vote-saver-protocol_b200.voting")
+    depth, rng = 3, random.Random(8)
+    sks = [rng.getrandbits(255) for _ in range(1 << depth)]
+    leaves = [voting.pedersen_hash_native(voting.digest_bits(s)) for s in sks]
+    nodes, level = list(leaves), list(leaves)
+    while len(level) > 1:
+        level = [voting.pedersen_hash_native(voting.digest_bits(level[i]) + voting.digest_bits(level[i + 1]))
+                 for i in range(0, len(level), 2)]
+        nodes += level
+    assert len(nodes) == 15 and nodes[-1] == voting.merkle_root_native(leaves)
+    limbs = cref.ints_to_limbs(nodes, 4)
+    blob = codec.merkle_tree_bytes(limbs, depth)
+    assert blob == b"".join(_bits_to_octets(voting.digest_bits(x)) for x in nodes) and len(blob) == 15 * 32
+    back = codec.merkle_tree_from_bytes(blob, depth)
+    assert np.array_equal(back, limbs)
+    tree = voting.SparseVoterTree(depth, sks)
+    for idx in range(1 << depth):
+        path = cref.limbs_to_ints(codec.merkle_copath(back, depth, idx))
+        assert path == voting.merkle_path_native(leaves, idx) == tree.path(idx)
+    assert codec.merkle_copath(limbs[:1], 0, 0).shape == (0, 4)
+    for bad in (blob[:-1], blob + bytes(32), blob[:32 * 7]):
+        with pytest.raises(ValueError):
+            codec.merkle_tree_from_bytes(bad, depth)
+    with pytest.raises(ValueError):
+        codec.merkle_copath(limbs, depth, 8)
+    too_wide = limbs.copy()
+    too_wide[3, 3] |= np.uint64(1 << 63)
+    with pytest.raises(ValueError):
+        codec.merkle_tree_bytes(too_wide, depth)

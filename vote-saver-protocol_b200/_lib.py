@@ -183,6 +183,12 @@ SYMBOLS = [
     ("vsp_codec_saver_sk_read", _int, [_vp, C.c_size_t, _vp]),
     ("vsp_codec_groth16_vk_write", _int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     ("vsp_codec_groth16_vk_read", _int, [_vp, C.c_size_t, C.POINTER(_u64), _vp, _vp, _vp, _vp, _vp, _vp, _u64]),
+    ("vsp_codec_bitarray_write", _int, [_vp, _u64, _vp]),
+    ("vsp_codec_bitarray_read", _int, [_vp, C.c_size_t, _u64, _vp]),
+    ("vsp_codec_bits_to_field_elements", _int, [_vp, _u64, _vp]),
+    ("vsp_codec_merkle_tree_write", _int, [_vp, _u64, _vp]),
+    ("vsp_codec_merkle_tree_read", _int, [_vp, C.c_size_t, _u64, _vp]),
+    ("vsp_codec_merkle_copath", _int, [_vp, _u64, _u64, _vp]),
     ("vsp_measure_imad_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
     ("vsp_measure_dfma_rate", _int, [_vp, _u64, C.POINTER(C.c_double)]),
     ("vsp_accumulate_mads_per_add", _int, [_vp, C.POINTER(C.c_double)]),

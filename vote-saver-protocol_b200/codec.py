@@ -203,6 +203,54 @@ def groth16_vk_from_bytes(blob: bytes) -> dict:
     return vk
 
 
+def bitarray_bytes(bits) -> bytes:
+    """serialize_bitarray (common.hpp:574-591): 0 / 1 values -> ceil(n / 8) octets, first bit in the top of the first octet"""
+    b = np.ascontiguousarray(bits, dtype=np.uint8).reshape(-1)
+    out = _out((b.shape[0] + 7) // 8)
+    _check(_lib.load().vsp_codec_bitarray_write(b.ctypes.data, b.shape[0], out), "bitarray_write")
+    return bytes(out)
+
+
+def bitarray_from_bytes(blob: bytes, n_bits: int) -> np.ndarray:
+    out = np.zeros(n_bits, dtype=np.uint8)
+    _check(_lib.load().vsp_codec_bitarray_read(bytes(blob), len(blob), n_bits, out.ctypes.data), "bitarray_read")
+    return out
+
+
+def bits_to_field_elements(bits) -> np.ndarray:
+    """get_multi_field_element_from_bits (common.hpp:557-570): -> ceil(n / 254) x 4 limbs"""
+    b = np.ascontiguousarray(bits, dtype=np.uint8).reshape(-1)
+    out = np.zeros(((b.shape[0] + 253) // 254, 4), dtype=np.uint64)
+    _check(_lib.load().vsp_codec_bits_to_field_elements(b.ctypes.data, b.shape[0], out.ctypes.data), "bits_to_field_elements")
+    return out
+
+
+def merkle_tree_bytes(digests, depth: int) -> bytes:
+    d = _u64(digests, 4)
+    if d.shape[0] != (2 << depth) - 1:
+        raise ValueError("a depth-%d tree holds %d digests" % (depth, (2 << depth) - 1))
+    out = _out(32 * d.shape[0])
+    _check(_lib.load().vsp_codec_merkle_tree_write(d.ctypes.data, depth, out), "merkle_tree_write")
+    return bytes(out)
+
+
+def merkle_tree_from_bytes(blob: bytes, depth: int) -> np.ndarray:
+    """deserialize_merkle_tree (common.hpp:614-636) -> (2^(depth + 1) - 1) x 4 limbs, leaves first, root last"""
+    out = np.zeros(((2 << depth) - 1, 4), dtype=np.uint64)
+    _check(_lib.load().vsp_codec_merkle_tree_read(bytes(blob), len(blob), depth, out.ctypes.data), "merkle_tree_read")
+    return out
+
+
+def merkle_copath(digests, depth: int, index: int) -> np.ndarray:
+    """merkle_proof(tree, index) for arity 2 -> depth x 4 limbs, leaf level first (a `paths` row of the witness generator)"""
+    d = _u64(digests, 4)
+    if d.shape[0] != (2 << depth) - 1:
+        raise ValueError("a depth-%d tree holds %d digests" % (depth, (2 << depth) - 1))
+    out = np.zeros((depth, 4), dtype=np.uint64)
+    _check(_lib.load().vsp_codec_merkle_copath(d.ctypes.data, depth, index, out.ctypes.data), "merkle_copath")
+    return out
+
+
 def read_fast_proving_key(blob: bytes) -> dict:
     """r1cs_proving_key.bin -> the arrays dict ProvingKey(ctx, arrays) takes (field names of vsp_proving_key_t)"""
     lib = _lib.load()

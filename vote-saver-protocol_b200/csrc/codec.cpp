@@ -848,3 +848,96 @@ int vsp_codec_groth16_vk_read(const uint8_t* blob, size_t len, uint64_t* gamma_A
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The vote phase's remaining inputs (bin/cli/include/nil/vote_saver/common.hpp:996-1003): bit arrays (the voter's secret
+// key, the voters' public keys), the voters' Merkle tree and the copath taken from it, and the packing of bit strings
+// into primary-input field elements.
+//   bit array        n bits -> ceil(n / 8) octets, bit i in octet i / 8, most significant bit first
+//                    (serialize_bitarray / deserialize_bitarray, common.hpp:574-612: stream_endian::big_octet_big_bit)
+//   Merkle tree      2^(depth + 1) - 1 digests of 255 bits, each a 32-octet bit array; leaves first, then row by row, the
+//                    root last (deserialize_merkle_tree, common.hpp:614-636; libs/containers/.../merkle/tree.hpp:424-427,
+//                    492-499).  Here a digest is the 4-limb integer whose bit i is digest bit i.
+//   copath           arity 2: the sibling of the node on the way up, leaf level first
+//                    (libs/containers/.../merkle/proof.hpp:65-91)
+//   packing          get_multi_field_element_from_bits (common.hpp:557-570): chunks of 254 bits, bit j of a chunk has
+//                    weight 2^j (get_field_element_from_bits, common.hpp:543-555)
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr uint64_t DIGEST_BITS = 255, DIGEST_OCTETS = 32, PACK_CHUNK = 254, MAX_TREE_DEPTH = 40;
+}
+
+extern "C" {
+
+int vsp_codec_bitarray_write(const uint8_t* bits, uint64_t n_bits, uint8_t* out) {
+    if ((!bits && n_bits) || !out) return VSP_E_INVALID;
+    memset(out, 0, (size_t)((n_bits + 7) / 8));
+    for (uint64_t i = 0; i < n_bits; ++i)
+        if (bits[i]) out[i / 8] |= (uint8_t)(0x80u >> (i % 8));
+    return VSP_OK;
+}
+
+// len must be exactly ceil(n_bits / 8) (the reference asserts it); padding bits are ignored, as the reference's copy_n does
+int vsp_codec_bitarray_read(const uint8_t* in, size_t len, uint64_t n_bits, uint8_t* bits) {
+    if (!in || (!bits && n_bits) || len != (size_t)((n_bits + 7) / 8)) return VSP_E_INVALID;
+    for (uint64_t i = 0; i < n_bits; ++i) bits[i] = (in[i / 8] >> (7 - i % 8)) & 1;
+    return VSP_OK;
+}
+
+// out: ceil(n_bits / 254) canonical Fr
+int vsp_codec_bits_to_field_elements(const uint8_t* bits, uint64_t n_bits, uint64_t* out) {
+    if ((!bits && n_bits) || (!out && n_bits)) return VSP_E_INVALID;
+    for (uint64_t c = 0; c * PACK_CHUNK < n_bits; ++c) {
+        uint64_t* v = out + 4 * c;
+        v[0] = v[1] = v[2] = v[3] = 0;
+        const uint64_t lo = c * PACK_CHUNK, hi = lo + PACK_CHUNK < n_bits ? lo + PACK_CHUNK : n_bits;
+        for (uint64_t i = lo; i < hi; ++i)
+            if (bits[i]) v[(i - lo) / 64] |= uint64_t(1) << ((i - lo) % 64);
+    }
+    return VSP_OK;
+}
+
+int vsp_codec_merkle_tree_write(const uint64_t* digests, uint64_t depth, uint8_t* out) {
+    if (!digests || !out || depth > MAX_TREE_DEPTH) return VSP_E_INVALID;
+    const uint64_t nodes = (uint64_t(2) << depth) - 1;
+    for (uint64_t k = 0; k < nodes; ++k) {
+        const uint64_t* d = digests + 4 * k;
+        if (d[3] >> 63) return VSP_E_INVALID;  // a digest has 255 bits
+        uint8_t* o = out + DIGEST_OCTETS * k;
+        memset(o, 0, DIGEST_OCTETS);
+        for (uint64_t i = 0; i < DIGEST_BITS; ++i)
+            if ((d[i / 64] >> (i % 64)) & 1) o[i / 8] |= (uint8_t)(0x80u >> (i % 8));
+    }
+    return VSP_OK;
+}
+
+// digests: 2^(depth + 1) - 1 entries of 4 limbs.  VSP_E_INVALID unless len is exactly that many 32-octet digests.
+int vsp_codec_merkle_tree_read(const uint8_t* blob, size_t len, uint64_t depth, uint64_t* digests) {
+    if (!blob || !digests || depth > MAX_TREE_DEPTH) return VSP_E_INVALID;
+    const uint64_t nodes = (uint64_t(2) << depth) - 1;
+    if (len / DIGEST_OCTETS != nodes || len % DIGEST_OCTETS) return VSP_E_INVALID;
+    for (uint64_t k = 0; k < nodes; ++k) {
+        uint64_t* d = digests + 4 * k;
+        d[0] = d[1] = d[2] = d[3] = 0;
+        const uint8_t* o = blob + DIGEST_OCTETS * k;
+        for (uint64_t i = 0; i < DIGEST_BITS; ++i)
+            if ((o[i / 8] >> (7 - i % 8)) & 1) d[i / 64] |= uint64_t(1) << (i % 64);
+    }
+    return VSP_OK;
+}
+
+// path: depth digests, leaf level first — one row of vsp_voting_witness_batch_dev's `paths`
+int vsp_codec_merkle_copath(const uint64_t* digests, uint64_t depth, uint64_t index, uint64_t* path) {
+    if (!digests || (!path && depth) || depth > MAX_TREE_DEPTH || index >= (uint64_t(1) << depth)) return VSP_E_INVALID;
+    uint64_t cur = index, row_len = uint64_t(1) << depth, row_begin = 0;
+    for (uint64_t level = 0; level < depth; ++level) {
+        const uint64_t sibling = (cur - row_begin) % 2 ? cur - 1 : cur + 1;
+        memcpy(path + 4 * level, digests + 4 * sibling, 32);
+        cur = row_len + row_begin + (cur - row_begin) / 2;
+        row_begin += row_len;
+        row_len /= 2;
+    }
+    return VSP_OK;
+}
+
+}  // extern "C"
