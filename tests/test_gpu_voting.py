@@ -118,3 +118,22 @@ def test_ballots_on_the_real_circuit_prove_and_verify(vsp, ctx):
     key.close()
     pk.close()
     gen.close()
+
+
+@pytest.mark.xfail(strict=False, reason="vote_phase.py's GPU half was written after the round's GPU minutes were spent and has "
+                                        "not run on hardware yet; its host half is covered by tests/test_vote_phase.py")
+def test_vote_phase_from_blobs_to_blobs():
+    """generate_vote (bin/cli/src/wasm.cpp:112-147) / process_encrypted_input_mode_vote_phase (common.hpp:985-1166) through
+    vote-saver-protocol_b200/vote_phase.py: tests/vote_phase_check.py in a process of its own (a fault there cannot reach the
+    tests collected after this one)"""
+    import json
+    import os
+    import subprocess
+    import sys
+    script = os.path.join(os.path.dirname(os.path.abspath(__file__)), "vote_phase_check.py")
+    run = subprocess.run([sys.executable, script], capture_output=True, text=True, timeout=600)
+    assert run.returncode == 0, run.stderr[-2000:]
+    res = json.loads(run.stdout.strip().splitlines()[-1])
+    for key in ("sizes_ok", "accepted", "forged_root_rejected", "sn_is_native_hash", "public_slice_is_eid_sn_rt",
+                "deterministic_given_scalars", "batch_accepted", "tally", "tally_proof", "vk_blob_round_trip"):
+        assert res[key] is True, (key, res)

@@ -1,0 +1,195 @@
+"""CPU tier: the host half of the blobs-to-blobs vote phase (vote-saver-protocol_b200/vote_phase.py) — deserialisation of what
+process_encrypted_input_mode_vote_phase reads (bin/cli/include/nil/vote_saver/common.hpp:996-1006), the reference's
+root check, the sk bit array, and the four output blobs of serialize_data (common.hpp:462-485, 1149-1160).  The GPU half is
+tests/test_gpu_voting.py."""
+import importlib
+import random
+import struct
+
+import numpy as np
+import pytest
+
+from oracle import cref, pyref as o
+
+from helpers import golden, random_g1, random_g2, synthetic_pk_arrays, synthetic_r1cs
+
+importlib.import_module("vote-saver-protocol_b200")
+codec = importlib.import_module("vote-saver-protocol_b200.codec")
+vp = importlib.import_module("vote-saver-protocol_b200.vote_phase")
+vt = importlib.import_module("vote-saver-protocol_b200.voting")
+
+
+def _tree(depth, rng):
+    sks = [rng.getrandbits(255) for _ in range(1 << depth)]
+    leaves = [vt.pedersen_hash_native(vt.digest_bits(s)) for s in sks]
+    nodes, level = list(leaves), list(leaves)
+    while len(level) > 1:
+        level = [vt.pedersen_hash_native(vt.digest_bits(level[i]) + vt.digest_bits(level[i + 1])) for i in range(0, len(level), 2)]
+        nodes += level
+    return sks, leaves, nodes
+
+
+def _blobs(depth=2, eid_bits=64, seed=5):
+    rng = random.Random(seed)
+    sks, leaves, nodes = _tree(depth, rng)
+    eid = rng.getrandbits(eid_bits)
+    g = golden("databin_groth16.json")
+    g1, g2 = random_g1(40, seed), random_g2(30, seed + 1)
+    n = 25
+    pub = {"msg_size": n, "delta_g1": g1[0:1].copy(), "delta_sum_s_g1": g1[1:2].copy(), "gamma_inverse_sum_s_g1": g1[2:3].copy(),
+           "delta_s_g1": random_g1(n, seed + 2), "t_g1": random_g1(n, seed + 3), "t_g2": g2[:n + 1].copy()}
+    cs, _, _ = synthetic_r1cs(40, 30, seed=seed, binary=True)
+    pk_arr = synthetic_pk_arrays(cs, seed)
+    gt = cref.ints_to_limbs([int(x, 16) for x in g["alpha_g1_beta_g2"]], 6).reshape(-1)
+    vk_blob = codec.groth16_vk_bytes(gt, g2[26], g2[27], g1[3], g1[4], random_g1(31, seed + 4))
+    root_bits = vt.digest_bits(nodes[-1])
+    blobs = {
+        "merkle_tree_blob": codec.merkle_tree_bytes(cref.ints_to_limbs(nodes, 4), depth),
+        "rt_blob": codec.primary_input_bytes(codec.bits_to_field_elements(root_bits)),
+        "eid_blob": codec.primary_input_bytes(cref.ints_to_limbs([eid], 4)),
+        "pk_eid_blob": codec.saver_pubkey_bytes(pub),
+        "proving_key_blob": codec.write_fast_proving_key(pk_arr),
+        "verification_key_blob": vk_blob,
+    }
+    return blobs, sks, leaves, nodes, eid, pub, pk_arr
+
+
+def test_parse_vote_inputs_reads_every_blob_and_checks_the_root():
+    blobs, sks, leaves, nodes, eid, pub, pk_arr = _blobs()
+    inp = vp.parse_vote_inputs(2, 64, **blobs)
+    assert inp.eid == eid and inp.tree.shape == (7, 4)
+    assert cref.limbs_to_ints(inp.tree) == nodes
+    assert cref.limbs_to_ints(inp.rt_packed) == [nodes[-1] & ((1 << 254) - 1), nodes[-1] >> 254]
+    assert inp.pubkey["msg_size"] == 25 and np.array_equal(inp.pubkey["t_g2"], pub["t_g2"])
+    assert int(inp.proving_key["cs"]["num_constraints"]) == 40 and np.array_equal(inp.proving_key["A_query"], pk_arr["A_query"])
+    assert inp.verification_key["gamma_ABC_g1"].shape == (31, 12)
+    # the copath the phase hands to the witness generator is the tree's
+    for idx in range(4):
+        assert cref.limbs_to_ints(codec.merkle_copath(inp.tree, 2, idx)) == vt.merkle_path_native(leaves, idx)
+    # BOOST_ASSERT(rt_field == admin_rt_field), common.hpp:1025: a tree that is not the published one is refused
+    other = dict(blobs, rt_blob=codec.primary_input_bytes(cref.ints_to_limbs([5, 0], 4)))
+    with pytest.raises(ValueError, match="published root"):
+        vp.parse_vote_inputs(2, 64, **other)
+    with pytest.raises(ValueError):
+        vp.parse_vote_inputs(3, 64, **blobs)  # 7 digests are not a depth-3 tree
+    with pytest.raises(ValueError):
+        vp.parse_vote_inputs(2, 65, **blobs)
+
+
+def test_eid_bits_come_from_the_packed_element():
+    """common.hpp:1010-1015: eid[i] = bit i of eid_field[i / 254]; bits past eid_bits are not part of the election id"""
+    blobs, *_ = _blobs(eid_bits=64, seed=6)
+    wide = dict(blobs, eid_blob=codec.primary_input_bytes(cref.ints_to_limbs([(1 << 70) | 0xabc], 4)))
+    assert vp.parse_vote_inputs(2, 12, **wide).eid == 0xabc
+    two = dict(blobs, eid_blob=codec.primary_input_bytes(cref.ints_to_limbs([1, 2], 4)))
+    with pytest.raises(ValueError, match="field elements"):
+        vp.parse_vote_inputs(2, 64, **two)
+
+
+def test_secret_key_blob_is_the_bit_array_of_the_key():
+    sk = random.Random(7).getrandbits(255) | 1 | (1 << 254)
+    blob = codec.bitarray_bytes(vt.digest_bits(sk))
+    assert len(blob) == 32 and blob[0] & 0x80 and blob[31] & 0x02  # sk[0] leads the first octet, sk[254] is bit 1 of the last
+    assert cref.limbs_to_ints(vp.secret_key_from_blob(blob).reshape(1, 4))[0] == sk
+    with pytest.raises(ValueError):
+        vp.secret_key_from_blob(blob[:31])
+
+
+def test_serialize_vote_writes_the_four_blobs_of_serialize_data():
+    """proof | primary input from the eid on | cipher text | sn  (common.hpp:1149-1160)"""
+    rng = random.Random(9)
+    primary = cref.ints_to_limbs([0] * 7 + [1] + [0] * 17 + [rng.randrange(o.R) for _ in range(5)], 4)  # m | eid | sn(2) | rt(2)
+    ct = random_g1(27, 10)
+    proof = np.concatenate([random_g1(1, 11).reshape(-1), random_g2(1, 12).reshape(-1), random_g1(1, 13).reshape(-1)])
+    proof_blob, pinput_blob, ct_blob, sn_blob = vp.serialize_vote(proof, primary, ct, 25, 1)
+    assert proof_blob == codec.proof_bytes(proof) and len(proof_blob) == 192
+    ints = cref.limbs_to_ints(primary)
+    assert pinput_blob == struct.pack(">Q", 5) + b"".join(x.to_bytes(32, "big") for x in ints[25:])
+    assert sn_blob == struct.pack(">Q", 2) + b"".join(x.to_bytes(32, "big") for x in ints[26:28])
+    assert ct_blob == codec.ciphertext_bytes(ct) and np.array_equal(codec.ciphertext_from_bytes(ct_blob), ct)
+    with pytest.raises(ValueError):
+        vp.serialize_vote(proof, primary[:-1], ct, 25, 1)
+
+
+class _HostWitness:
+    """stands in for voting.WitnessGenerator (the CUDA generator) with the circuit module's host restatement, which the GPU
+    generator equals bit for bit (tests/test_gpu_voting.py)"""
+
+    def __init__(self, circuit):
+        self.circuit, self.calls = circuit, []
+
+    def generate(self, votes, eid, sks, indices, paths):
+        self.calls.append((votes, eid, sks, indices, paths))
+        rows = []
+        for b in range(len(votes)):
+            path = cref.limbs_to_ints(np.ascontiguousarray(paths[b]))[:self.circuit.depth]
+            prim, aux = self.circuit.witness(int(votes[b]), int(eid), cref.limbs_to_ints(sks[b].reshape(1, 4))[0], int(indices[b]), path)
+            rows.append(vt.ints_to_fr([1] + prim + aux))
+        return np.stack(rows)
+
+    def close(self):
+        pass
+
+
+class _EchoProver:
+    """stands in for ProvingKey.encrypt_batch / rerandomize_batch: fixed points of the right shapes, and a record of what the
+    phase passed in"""
+
+    def __init__(self, msg_size):
+        self.msg_size, self.seen = msg_size, {}
+
+    def encrypt_batch(self, key, primary, auxiliary, rs):
+        self.seen.update(primary=primary, auxiliary=auxiliary, rs=rs)
+        k = rs.shape[0]
+        cts = np.stack([random_g1(self.msg_size + 2, 100 + b) for b in range(k)])
+        proofs = np.stack([np.concatenate([random_g1(1, 200 + b).reshape(-1), random_g2(1, 300 + b).reshape(-1),
+                                           random_g1(1, 400 + b).reshape(-1)]) for b in range(k)])
+        return cts, proofs
+
+    def rerandomize_batch(self, key, rnd, cts, proofs):
+        self.seen["rnd"] = rnd
+        return cts[:, ::-1].copy(), proofs  # visibly different cipher texts
+
+    def close(self):
+        pass
+
+
+def test_vote_phase_glue_with_host_stand_ins_for_the_three_gpu_calls():
+    """everything VotePhase.generate_votes does around the witness generator, encrypt_batch and rerandomize_batch: voter index ->
+    copath from the tree blob, sk blob -> key bits, eid element -> eid bits, the assignment split into primary | auxiliary, the
+    scalars handed through, and the four blobs.  sn and rt in the published slice equal independent native computations, so
+    every bit order on the way in is the circuit's."""
+    blobs, sks, leaves, nodes, eid, pub, pk_arr = _blobs(depth=2, eid_bits=64, seed=15)
+    inputs = vp.parse_vote_inputs(2, 64, **blobs)
+    c = vt.VotingCircuit(depth=2)
+    phase = object.__new__(vp.VotePhase)
+    phase.ctx, phase.inputs, phase.circuit, phase.msg_size = None, inputs, c, c.msg_size
+    phase.witness, phase.pk, phase.key, phase.pub = _HostWitness(c), _EchoProver(c.msg_size), None, None
+    ballots = [(2, 7, codec.bitarray_bytes(vt.digest_bits(sks[2]))), (0, 24, codec.bitarray_bytes(vt.digest_bits(sks[0])))]
+    rs = cref.ints_to_limbs(list(range(1, 7)), 4).reshape(2, 3, 4)
+    rnd = cref.ints_to_limbs(list(range(11, 17)), 4).reshape(2, 3, 4)
+    out = phase.generate_votes(ballots, rs=rs, rnd=rnd)
+    assert np.array_equal(phase.pk.seen["rs"], rs) and np.array_equal(phase.pk.seen["rnd"], rnd)
+    assert phase.pk.seen["primary"].shape == (2, c.num_inputs, 4) and phase.pk.seen["auxiliary"].shape == (2, c.num_aux, 4)
+    cs = o.R1CS(c.num_inputs, c.num_aux, c.constraints)
+    pack = lambda x: [x & ((1 << 254) - 1), x >> 254]
+    for b, (idx, vote, _) in enumerate(ballots):
+        proof_blob, pinput_blob, ct_blob, sn_blob = out[b]
+        prim = cref.limbs_to_ints(phase.pk.seen["primary"][b])
+        assert cs.is_satisfied(prim, cref.limbs_to_ints(phase.pk.seen["auxiliary"][b]))
+        assert prim[:25] == [int(i == vote) for i in range(25)]
+        sn = vt.pedersen_hash_native([(eid >> i) & 1 for i in range(64)] + vt.digest_bits(sks[idx]))
+        assert cref.limbs_to_ints(codec.primary_input_from_bytes(pinput_blob)) == [eid] + pack(sn) + pack(nodes[-1])
+        assert cref.limbs_to_ints(codec.primary_input_from_bytes(sn_blob)) == pack(sn)
+        assert np.array_equal(codec.ciphertext_from_bytes(ct_blob), random_g1(27, 100 + b)[::-1])  # the rerandomised ones
+        assert len(proof_blob) == 192
+    # without rerandomisation the encrypt step's cipher texts go out; secrets are drawn when none are given
+    out2 = phase.generate_votes(ballots[:1], rerandomize=False)
+    assert np.array_equal(codec.ciphertext_from_bytes(out2[0][2]), random_g1(27, 100))
+    drawn = cref.limbs_to_ints(phase.pk.seen["rs"].reshape(3, 4))
+    assert len(set(drawn)) == 3 and all(0 <= x < o.R for x in drawn)
+    with pytest.raises(ValueError, match="less than number of participants"):
+        phase.generate_votes([(4, 0, ballots[0][2])])
+    with pytest.raises(ValueError, match="options"):
+        phase.generate_votes([(0, 25, ballots[0][2])])
+    assert phase.generate_votes([]) == []

@@ -1,0 +1,98 @@
+"""Run by tests/test_gpu_voting.py in a process of its own: the blobs-to-blobs vote phase (vote-saver-protocol_b200/vote_phase.py)
+on the real depth-2 ballot circuit, BASELINE configs[0] — every input in the reference's byte formats (common.hpp:996-1006),
+the four output blobs parsed back and checked: the ballot is accepted by verify_encryption, a forged root is not, sn is the
+native Pedersen hash of eid || sk, the public slice is eid | sn | rt, and the tally of four voters decrypts to their votes.
+Prints one JSON line."""
+import importlib
+import json
+import os
+import random
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+
+from oracle import cref, pyref as o  # noqa: E402  (the checker)
+
+vsp = importlib.import_module("vote-saver-protocol_b200")
+codec = importlib.import_module("vote-saver-protocol_b200.codec")
+vp = importlib.import_module("vote-saver-protocol_b200.vote_phase")
+vt = importlib.import_module("vote-saver-protocol_b200.voting")
+
+
+def main():
+    rng = random.Random(21)
+    depth, eid_bits = 2, 64
+    res = {}
+    with vsp.Context(0) as ctx:
+        c = vt.VotingCircuit(depth=depth)
+        pk_arr, vk = vsp.generate(ctx, c.r1cs_arrays(), [rng.randrange(1, o.R) for _ in range(5)])
+        pub_arr, rho, svk = vsp.saver_generate_keypair(ctx, vk, c.msg_size, [rng.randrange(1, o.R) for _ in range(3 * c.msg_size + 2)])
+        gt, _ = vsp.pairing_products(ctx, vk["alpha_g1"], vk["beta_g2"])
+        sks = [rng.getrandbits(255) for _ in range(1 << depth)]
+        leaves = [vt.pedersen_hash_native(vt.digest_bits(s)) for s in sks]
+        nodes, level = list(leaves), list(leaves)
+        while len(level) > 1:
+            level = [vt.pedersen_hash_native(vt.digest_bits(level[i]) + vt.digest_bits(level[i + 1])) for i in range(0, len(level), 2)]
+            nodes += level
+        eid = rng.getrandbits(eid_bits)
+        blobs = dict(
+            merkle_tree_blob=codec.merkle_tree_bytes(cref.ints_to_limbs(nodes, 4), depth),
+            rt_blob=codec.primary_input_bytes(codec.bits_to_field_elements(vt.digest_bits(nodes[-1]))),
+            eid_blob=codec.primary_input_bytes(cref.ints_to_limbs([eid], 4)),
+            pk_eid_blob=codec.saver_pubkey_bytes(pub_arr),
+            proving_key_blob=codec.write_fast_proving_key(pk_arr),
+            verification_key_blob=codec.groth16_vk_bytes(gt[0], vk["gamma_g2"], vk["delta_g2"], vk["delta_g1"], vk["gamma_g1"],
+                                                         vk["gamma_ABC_g1"]))
+        sk_blobs = [codec.bitarray_bytes(vt.digest_bits(s)) for s in sks]
+        pub = vsp.SaverPublicKey(pub_arr)
+        gabc = np.ascontiguousarray(vk["gamma_ABC_g1"][1:1 + c.msg_size])
+
+        # one ballot through the reference's own entry point shape
+        voter, vote = 2, 7
+        proof_blob, pinput_blob, ct_blob, sn_blob = vp.generate_vote(ctx, depth, eid_bits, voter, vote, blobs["merkle_tree_blob"],
+                                                                    blobs["rt_blob"], blobs["eid_blob"], sk_blobs[voter],
+                                                                    blobs["pk_eid_blob"], blobs["proving_key_blob"],
+                                                                    blobs["verification_key_blob"])
+        proof, ct = codec.proof_from_bytes(proof_blob), codec.ciphertext_from_bytes(ct_blob)
+        rest = codec.primary_input_from_bytes(pinput_blob)
+        res["blob_sizes"] = [len(proof_blob), len(pinput_blob), len(ct_blob), len(sn_blob)]
+        res["sizes_ok"] = res["blob_sizes"] == [192, 8 + 32 * 5, 8 + 48 * (c.msg_size + 2), 8 + 32 * 2]
+        res["accepted"] = bool(vsp.verify_encryption_batch(ctx, vk, pub, ct[None], rest[None], proof[None])[0])
+        forged = rest.copy()
+        forged[3, 0] ^= np.uint64(1)
+        res["forged_root_rejected"] = not bool(vsp.verify_encryption_batch(ctx, vk, pub, ct[None], forged[None], proof[None])[0])
+        sn = vt.pedersen_hash_native([(eid >> i) & 1 for i in range(eid_bits)] + vt.digest_bits(sks[voter]))
+        pack = lambda x: [x & ((1 << 254) - 1), x >> 254]
+        res["sn_is_native_hash"] = cref.limbs_to_ints(codec.primary_input_from_bytes(sn_blob)) == pack(sn)
+        res["public_slice_is_eid_sn_rt"] = cref.limbs_to_ints(rest) == [eid] + pack(sn) + pack(nodes[-1])
+
+        # the four voters in one call on resident keys, fixed scalars: twice the same blobs; then the tally
+        inputs = vp.parse_vote_inputs(depth, eid_bits, **blobs)
+        votes = [3, 3, 7, 0]
+        ballots = [(i, votes[i], sk_blobs[i]) for i in range(4)]
+        rs = np.stack([cref.ints_to_limbs([rng.randrange(o.R) for _ in range(3)], 4) for _ in range(4)])
+        rnd = np.stack([cref.ints_to_limbs([rng.randrange(1, o.R) for _ in range(3)], 4) for _ in range(4)])
+        with vp.VotePhase(ctx, inputs) as phase:
+            out = phase.generate_votes(ballots, rs=rs, rnd=rnd)
+            res["deterministic_given_scalars"] = out == phase.generate_votes(ballots, rs=rs, rnd=rnd)
+        cts = np.stack([codec.ciphertext_from_bytes(b[2]) for b in out])
+        proofs = np.stack([codec.proof_from_bytes(b[0]) for b in out])
+        rests = np.stack([codec.primary_input_from_bytes(b[1]) for b in out])
+        res["batch_accepted"] = bool(vsp.verify_encryption_batch(ctx, vk, pub, cts, rests, proofs).all())
+        total = cts[0]
+        for b in range(1, 4):
+            total = np.stack([cref.g1_add(total[i], cts[b][i]) for i in range(c.msg_size + 2)])
+        counts, c0 = vsp.decrypt(ctx, total, rho, svk, gabc, block_bits=4)
+        res["tally"] = counts == [votes.count(i) for i in range(c.msg_size)]
+        res["tally_proof"] = bool(vsp.verify_decryption(ctx, total, counts, svk, gabc, c0))
+        # the key as the vote phase deserialised it (alpha_g1_beta_g2 in GT form) is the generated one
+        res["vk_blob_round_trip"] = bool(np.array_equal(inputs.verification_key["alpha_g1_beta_g2"], gt[0]) and
+                                         np.array_equal(inputs.verification_key["gamma_ABC_g1"], vk["gamma_ABC_g1"]))
+    print(json.dumps(res))
+
+
+if __name__ == "__main__":
+    main()
