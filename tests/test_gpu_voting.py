@@ -135,5 +135,6 @@ def test_vote_phase_from_blobs_to_blobs():
     assert run.returncode == 0, run.stderr[-2000:]
     res = json.loads(run.stdout.strip().splitlines()[-1])
     for key in ("sizes_ok", "accepted", "forged_root_rejected", "sn_is_native_hash", "public_slice_is_eid_sn_rt",
-                "deterministic_given_scalars", "batch_accepted", "tally", "tally_proof", "vk_blob_round_trip"):
+                "deterministic_given_scalars", "batch_accepted", "tally", "tally_proof", "vk_blob_round_trip", "tally_blobs",
+                "tally_blobs_verify", "wrong_result_rejected"):
         assert res[key] is True, (key, res)

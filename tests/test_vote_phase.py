@@ -193,3 +193,63 @@ def test_vote_phase_glue_with_host_stand_ins_for_the_three_gpu_calls():
     with pytest.raises(ValueError, match="options"):
         phase.generate_votes([(0, 25, ballots[0][2])])
     assert phase.generate_votes([]) == []
+
+
+def test_tally_phase_glue_with_host_stand_ins(monkeypatch):
+    """tally_phase.py around its three GPU calls (vsp_g1_sum, vsp_saver_decrypt, vsp_saver_verify_decryption), which are
+    replaced by the oracle's point addition and by recorders: blobs are read in the reference's formats, the cipher texts are
+    summed slot by slot, the keys reach decrypt / verify_decryption in the right slots, and the two output blobs are
+    serialize_tally_phase_data's (common.hpp:511-522)"""
+    tp = importlib.import_module("vote-saver-protocol_b200.tally_phase")
+    vsp = importlib.import_module("vote-saver-protocol_b200")
+    n, k = 25, 3
+    cts = np.stack([random_g1(n + 2, 500 + b) for b in range(k)])
+    g2 = random_g2(2 * n + 1, 60)
+    rho = random.Random(61).randrange(o.R)
+    g = golden("databin_groth16.json")
+    gt = cref.ints_to_limbs([int(x, 16) for x in g["alpha_g1_beta_g2"]], 6).reshape(-1)
+    gabc = random_g1(31, 62)
+    vk_blob = codec.groth16_vk_bytes(gt, g2[0], g2[1], random_g1(1, 63)[0], random_g1(1, 64)[0], gabc)
+    vk_eid_blob = codec.saver_vk_bytes(g2[0], g2[1:1 + n], g2[1 + n:])
+    sk_blob = codec.saver_sk_bytes(cref.ints_to_limbs([rho], 4)[0])
+    cts_blobs = [codec.ciphertext_bytes(c) for c in cts]
+    want_agg = np.stack([cref.g1_add(cref.g1_add(cts[0][i], cts[1][i]), cts[2][i]) for i in range(n + 2)])
+    seen = {}
+
+    def points_sum(ctx, pts):
+        acc = pts[0]
+        for p in pts[1:]:
+            acc = cref.g1_add(acc, p)
+        return np.asarray(acc, dtype=np.uint64).reshape(12)
+
+    def decrypt(ctx, ct, rho_, svk, gabc_rest, block_bits=4):
+        seen["decrypt"] = (np.array(ct), rho_, svk, np.array(gabc_rest), block_bits)
+        return [2, 0, 1] + [0] * (n - 3), random_g1(1, 65)[0]
+
+    def verify_decryption(ctx, ct, plain, svk, gabc_rest, proof):
+        seen["verify"] = (np.array(ct), list(plain), svk, np.array(gabc_rest), np.array(proof))
+        return True
+
+    monkeypatch.setattr(vsp, "points_sum", points_sum)
+    monkeypatch.setattr(vsp, "decrypt", decrypt)
+    monkeypatch.setattr(vsp, "verify_decryption", verify_decryption)
+    dec_proof_blob, voting_res_blob = tp.tally_admin_phase(None, 2, cts_blobs, sk_blob, vk_eid_blob, None, vk_blob)
+    ct, rho_, svk, rest, bits = seen["decrypt"]
+    assert np.array_equal(ct, want_agg) and rho_ == rho and bits == 4
+    assert np.array_equal(svk["rho_g2"], g2[0]) and np.array_equal(svk["rho_sv_g2"], g2[1:1 + n]) and np.array_equal(svk["rho_rhov_g2"], g2[1 + n:])
+    assert np.array_equal(rest, gabc[1:1 + n])
+    assert dec_proof_blob == o.g1_compress(o.G1.from_affine(cref.g1_from_limbs(random_g1(1, 65))[0]))
+    assert voting_res_blob == struct.pack(">Q", n) + b"".join(x.to_bytes(32, "big") for x in [2, 0, 1] + [0] * (n - 3))
+    assert tp.tally_voter_phase(None, 2, cts_blobs, vk_eid_blob, None, vk_blob, voting_res_blob, dec_proof_blob) is True
+    ct, plain, svk, rest, proof = seen["verify"]
+    assert np.array_equal(ct, want_agg) and plain == [2, 0, 1] + [0] * (n - 3) and np.array_equal(proof, random_g1(1, 65)[0])
+    assert np.array_equal(rest, gabc[1:1 + n]) and np.array_equal(svk["rho_sv_g2"], g2[1:1 + n])
+    # a result of the wrong length is refused before any GPU work; so are too many ballots and ragged cipher texts
+    short = struct.pack(">Q", n - 1) + bytes(32 * (n - 1))
+    seen.clear()
+    assert tp.tally_voter_phase(None, 2, cts_blobs, vk_eid_blob, None, vk_blob, short, dec_proof_blob) is False and not seen
+    with pytest.raises(ValueError, match="participants"):
+        tp.read_ciphertexts(1, cts_blobs)
+    with pytest.raises(ValueError, match="Wrong size"):
+        tp.read_ciphertexts(2, cts_blobs[:2] + [codec.ciphertext_bytes(cts[2][:-1])])
+    assert np.array_equal(tp.aggregate(None, cts[:1]), cts[0])

@@ -1,7 +1,8 @@
 """Run by tests/test_gpu_voting.py in a process of its own: the blobs-to-blobs vote phase (vote-saver-protocol_b200/vote_phase.py)
 on the real depth-2 ballot circuit, BASELINE configs[0] — every input in the reference's byte formats (common.hpp:996-1006),
 the four output blobs parsed back and checked: the ballot is accepted by verify_encryption, a forged root is not, sn is the
-native Pedersen hash of eid || sk, the public slice is eid | sn | rt, and the tally of four voters decrypts to their votes.
+native Pedersen hash of eid || sk, the public slice is eid | sn | rt, and the tally of four voters decrypts to their votes, directly and through
+tally_phase.py's blobs.
 Prints one JSON line."""
 import importlib
 import json
@@ -88,6 +89,19 @@ def main():
         counts, c0 = vsp.decrypt(ctx, total, rho, svk, gabc, block_bits=4)
         res["tally"] = counts == [votes.count(i) for i in range(c.msg_size)]
         res["tally_proof"] = bool(vsp.verify_decryption(ctx, total, counts, svk, gabc, c0))
+        # the tally phase on the same ballots, blobs in and out (common.hpp:1176-1296)
+        tp = importlib.import_module("vote-saver-protocol_b200.tally_phase")
+        vk_eid_blob = codec.saver_vk_bytes(svk["rho_g2"], svk["rho_sv_g2"], svk["rho_rhov_g2"])
+        sk_eid_blob = codec.saver_sk_bytes(cref.ints_to_limbs([rho], 4)[0])
+        ct_blobs = [b[2] for b in out]
+        dec_proof_blob, voting_res_blob = tp.tally_admin_phase(ctx, depth, ct_blobs, sk_eid_blob, vk_eid_blob, None,
+                                                               blobs["verification_key_blob"])
+        res["tally_blobs"] = cref.limbs_to_ints(codec.primary_input_from_bytes(voting_res_blob)) == [votes.count(i) for i in range(c.msg_size)]
+        res["tally_blobs_verify"] = tp.tally_voter_phase(ctx, depth, ct_blobs, vk_eid_blob, None, blobs["verification_key_blob"],
+                                                         voting_res_blob, dec_proof_blob)
+        wrong = codec.primary_input_bytes(cref.ints_to_limbs([votes.count(i) + (i == 5) for i in range(c.msg_size)], 4))
+        res["wrong_result_rejected"] = not tp.tally_voter_phase(ctx, depth, ct_blobs, vk_eid_blob, None,
+                                                                blobs["verification_key_blob"], wrong, dec_proof_blob)
         # the key as the vote phase deserialised it (alpha_g1_beta_g2 in GT form) is the generated one
         res["vk_blob_round_trip"] = bool(np.array_equal(inputs.verification_key["alpha_g1_beta_g2"], gt[0]) and
                                          np.array_equal(inputs.verification_key["gamma_ABC_g1"], vk["gamma_ABC_g1"]))
