@@ -253,3 +253,70 @@ def test_tally_phase_glue_with_host_stand_ins(monkeypatch):
     with pytest.raises(ValueError, match="Wrong size"):
         tp.read_ciphertexts(2, cts_blobs[:2] + [codec.ciphertext_bytes(cts[2][:-1])])
     assert np.array_equal(tp.aggregate(None, cts[:1]), cts[0])
+
+
+def test_init_voter_and_admin_data_phases_feed_the_vote_phase():
+    """init_phase.py: voter key blobs (common.hpp:824-846) and the administrator's eid / rt / merkle_tree blobs (:943-985) on
+    three voters of a depth-3 election — the unclaimed leaves are all-zero keys, as deserialize_voters_public_keys pads them —
+    then read back by the vote phase's parser, whose root check passes; the tree equals a plain full-tree computation"""
+    ip = importlib.import_module("vote-saver-protocol_b200.init_phase")
+    rng = random.Random(31)
+    sks = [rng.getrandbits(255) for _ in range(3)]
+    keys = [ip.init_voter_phase(i, sk=s) for i, s in enumerate(sks)]
+    for (pk_blob, sk_blob), s in zip(keys, sks):
+        assert len(pk_blob) == 32 and len(sk_blob) == 32
+        assert cref.limbs_to_ints(vp.secret_key_from_blob(sk_blob).reshape(1, 4))[0] == s
+        assert list(codec.bitarray_from_bytes(pk_blob, 255)) == vt.digest_bits(vt.pedersen_hash_native(vt.digest_bits(s)))
+    drawn_pk, drawn_sk = ip.init_voter_phase(0)
+    assert drawn_sk != keys[0][1] and len(drawn_pk) == 32
+    eid_blob, rt_blob, tree_blob = ip.init_admin_phase_generate_data(3, 64, [k[0] for k in keys], eid=0x1234)
+    leaves = [vt.pedersen_hash_native(vt.digest_bits(s)) for s in sks] + [0] * 5
+    nodes, level = list(leaves), list(leaves)
+    while len(level) > 1:
+        level = [vt.pedersen_hash_native(vt.digest_bits(level[i]) + vt.digest_bits(level[i + 1])) for i in range(0, len(level), 2)]
+        nodes += level
+    assert cref.limbs_to_ints(codec.merkle_tree_from_bytes(tree_blob, 3)) == nodes
+    assert cref.limbs_to_ints(codec.primary_input_from_bytes(eid_blob)) == [0x1234]
+    blobs, *_ = _blobs(depth=2, seed=33)
+    blobs.update(merkle_tree_blob=tree_blob, rt_blob=rt_blob, eid_blob=eid_blob)
+    inp = vp.parse_vote_inputs(3, 64, **blobs)
+    assert inp.eid == 0x1234 and cref.limbs_to_ints(inp.tree)[-1] == nodes[-1]
+    with pytest.raises(ValueError):
+        ip.init_admin_phase_generate_data(1, 64, [k[0] for k in keys])
+    with pytest.raises(ValueError):
+        ip.init_admin_phase_generate_data(3, 8, [], eid=256)
+
+
+def test_init_admin_keys_phase_glue_with_host_stand_ins(monkeypatch):
+    """init_admin_phase_generate_keys around its three GPU calls (vsp_groth16_generate, vsp_saver_keygen, one pairing): the
+    five blobs of serialize_initial_phase_admin_keys (common.hpp:330-366) carry what the generators returned, and the vote
+    phase's parser reads them back"""
+    ip = importlib.import_module("vote-saver-protocol_b200.init_phase")
+    vsp = importlib.import_module("vote-saver-protocol_b200")
+    cs, _, _ = synthetic_r1cs(40, 30, seed=3, binary=True)
+    pk_arr = synthetic_pk_arrays(cs, 3)
+    g1, g2 = random_g1(40, 70), random_g2(60, 71)
+    vk = {"alpha_g1": g1[0:1], "beta_g2": g2[0:1], "gamma_g2": g2[1:2], "delta_g2": g2[2:3], "gamma_g1": g1[1:2], "delta_g1": g1[2:3],
+          "gamma_ABC_g1": g1[3:34]}
+    n = 25
+    pub = {"msg_size": n, "delta_g1": g1[2:3].copy(), "delta_s_g1": random_g1(n, 72), "t_g1": random_g1(n, 73), "t_g2": g2[3:3 + n + 1].copy(),
+           "delta_sum_s_g1": g1[34:35].copy(), "gamma_inverse_sum_s_g1": g1[35:36].copy()}
+    svk = {"rho_g2": g2[30:31], "rho_sv_g2": g2[31:31 + n].copy(), "rho_rhov_g2": random_g2(n, 74)}
+    gt = cref.ints_to_limbs([int(x, 16) for x in golden("databin_groth16.json")["alpha_g1_beta_g2"]], 6).reshape(1, 72)
+    seen = {}
+    monkeypatch.setattr(vsp, "generate", lambda ctx, arrays, toxic: (seen.update(cs=arrays, toxic=toxic), (pk_arr, vk))[1])
+    monkeypatch.setattr(vsp, "saver_generate_keypair", lambda ctx, vk_, m, rnd: (seen.update(rnd=rnd, m=m), (pub, 12345, svk))[1])
+    monkeypatch.setattr(vsp, "pairing_products", lambda ctx, a, b: (seen.update(pair=(a, b)), (gt, np.array([False])))[1])
+    pk_blob, vk_blob, pub_blob, sk_blob, svk_blob = ip.init_admin_phase_generate_keys(None, 0, 8)
+    c = vt.VotingCircuit(depth=0, eid_bits=8)
+    assert int(seen["cs"]["num_constraints"]) == len(c.constraints) and int(seen["cs"]["num_inputs"]) == 30
+    assert len(seen["toxic"]) == 5 and len(seen["rnd"]) == 3 * n + 2 and all(0 < x < o.R for x in seen["toxic"] + seen["rnd"])
+    assert np.array_equal(seen["pair"][0], vk["alpha_g1"]) and np.array_equal(seen["pair"][1], vk["beta_g2"])
+    back = codec.groth16_vk_from_bytes(vk_blob)
+    assert np.array_equal(back["alpha_g1_beta_g2"], gt[0]) and np.array_equal(back["gamma_ABC_g1"], vk["gamma_ABC_g1"])
+    assert np.array_equal(back["delta_g1"], vk["delta_g1"][0]) and np.array_equal(back["gamma_g1"], vk["gamma_g1"][0])
+    assert np.array_equal(codec.read_fast_proving_key(pk_blob)["H_query"], pk_arr["H_query"])
+    assert np.array_equal(codec.saver_pubkey_from_bytes(pub_blob)["t_g2"], pub["t_g2"])
+    assert cref.limbs_to_ints(codec.saver_sk_from_bytes(sk_blob).reshape(1, 4))[0] == 12345
+    a, b, cc = codec.saver_vk_from_bytes(svk_blob)
+    assert np.array_equal(a, svk["rho_g2"][0]) and np.array_equal(b, svk["rho_sv_g2"]) and np.array_equal(cc, svk["rho_rhov_g2"])

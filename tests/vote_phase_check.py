@@ -1,6 +1,6 @@
 """Run by tests/test_gpu_voting.py in a process of its own: the blobs-to-blobs vote phase (vote-saver-protocol_b200/vote_phase.py)
 on the real depth-2 ballot circuit, BASELINE configs[0] — every input in the reference's byte formats (common.hpp:996-1006),
-the four output blobs parsed back and checked: the ballot is accepted by verify_encryption, a forged root is not, sn is the
+the blobs made by init_phase.py's three phases, the four output blobs parsed back and checked: the ballot is accepted by verify_encryption, a forged root is not, sn is the
 native Pedersen hash of eid || sk, the public slice is eid | sn | rt, and the tally of four voters decrypts to their votes, directly and through
 tally_phase.py's blobs.
 Prints one JSON line."""
@@ -28,26 +28,28 @@ def main():
     depth, eid_bits = 2, 64
     res = {}
     with vsp.Context(0) as ctx:
+        ip = importlib.import_module("vote-saver-protocol_b200.init_phase")
         c = vt.VotingCircuit(depth=depth)
-        pk_arr, vk = vsp.generate(ctx, c.r1cs_arrays(), [rng.randrange(1, o.R) for _ in range(5)])
-        pub_arr, rho, svk = vsp.saver_generate_keypair(ctx, vk, c.msg_size, [rng.randrange(1, o.R) for _ in range(3 * c.msg_size + 2)])
-        gt, _ = vsp.pairing_products(ctx, vk["alpha_g1"], vk["beta_g2"])
+        # the initial phases (common.hpp:824-985), blobs out: administrator keys, voter keys, session data
+        toxic = [rng.randrange(1, o.R) for _ in range(5)]
+        keygen_rnd = [rng.randrange(1, o.R) for _ in range(3 * c.msg_size + 2)]
+        pk_blob, vk_blob, pk_eid_blob, sk_eid_blob, vk_eid_blob = ip.init_admin_phase_generate_keys(ctx, depth, eid_bits, toxic=toxic,
+                                                                                                  rnd=keygen_rnd)
         sks = [rng.getrandbits(255) for _ in range(1 << depth)]
-        leaves = [vt.pedersen_hash_native(vt.digest_bits(s)) for s in sks]
-        nodes, level = list(leaves), list(leaves)
-        while len(level) > 1:
-            level = [vt.pedersen_hash_native(vt.digest_bits(level[i]) + vt.digest_bits(level[i + 1])) for i in range(0, len(level), 2)]
-            nodes += level
+        voter_keys = [ip.init_voter_phase(i, sk=s) for i, s in enumerate(sks)]
         eid = rng.getrandbits(eid_bits)
-        blobs = dict(
-            merkle_tree_blob=codec.merkle_tree_bytes(cref.ints_to_limbs(nodes, 4), depth),
-            rt_blob=codec.primary_input_bytes(codec.bits_to_field_elements(vt.digest_bits(nodes[-1]))),
-            eid_blob=codec.primary_input_bytes(cref.ints_to_limbs([eid], 4)),
-            pk_eid_blob=codec.saver_pubkey_bytes(pub_arr),
-            proving_key_blob=codec.write_fast_proving_key(pk_arr),
-            verification_key_blob=codec.groth16_vk_bytes(gt[0], vk["gamma_g2"], vk["delta_g2"], vk["delta_g1"], vk["gamma_g1"],
-                                                         vk["gamma_ABC_g1"]))
-        sk_blobs = [codec.bitarray_bytes(vt.digest_bits(s)) for s in sks]
+        eid_blob, rt_blob, tree_blob = ip.init_admin_phase_generate_data(depth, eid_bits, [k[0] for k in voter_keys], eid=eid)
+        blobs = dict(merkle_tree_blob=tree_blob, rt_blob=rt_blob, eid_blob=eid_blob, pk_eid_blob=pk_eid_blob,
+                     proving_key_blob=pk_blob, verification_key_blob=vk_blob)
+        sk_blobs = [k[1] for k in voter_keys]
+        nodes = cref.limbs_to_ints(codec.merkle_tree_from_bytes(tree_blob, depth))
+        # the same keys as arrays, for the verifier calls below (the generators are deterministic in their secrets)
+        pk_arr, vk = vsp.generate(ctx, c.r1cs_arrays(), toxic)
+        pub_arr, rho, svk = vsp.saver_generate_keypair(ctx, vk, c.msg_size, keygen_rnd)
+        gt, _ = vsp.pairing_products(ctx, vk["alpha_g1"], vk["beta_g2"])
+        res["key_blobs_are_the_generated_keys"] = bool(
+            pk_blob == codec.write_fast_proving_key(pk_arr) and pk_eid_blob == codec.saver_pubkey_bytes(pub_arr) and
+            sk_eid_blob == codec.saver_sk_bytes(cref.ints_to_limbs([rho], 4)[0]))
         pub = vsp.SaverPublicKey(pub_arr)
         gabc = np.ascontiguousarray(vk["gamma_ABC_g1"][1:1 + c.msg_size])
 
@@ -91,8 +93,6 @@ def main():
         res["tally_proof"] = bool(vsp.verify_decryption(ctx, total, counts, svk, gabc, c0))
         # the tally phase on the same ballots, blobs in and out (common.hpp:1176-1296)
         tp = importlib.import_module("vote-saver-protocol_b200.tally_phase")
-        vk_eid_blob = codec.saver_vk_bytes(svk["rho_g2"], svk["rho_sv_g2"], svk["rho_rhov_g2"])
-        sk_eid_blob = codec.saver_sk_bytes(cref.ints_to_limbs([rho], 4)[0])
         ct_blobs = [b[2] for b in out]
         dec_proof_blob, voting_res_blob = tp.tally_admin_phase(ctx, depth, ct_blobs, sk_eid_blob, vk_eid_blob, None,
                                                                blobs["verification_key_blob"])
