@@ -391,6 +391,15 @@ VSP_API int vsp_saver_verify_encryption_batch(vsp_ctx *ctx, const vsp_verificati
                                               uint64_t k, const uint64_t *cts, const uint64_t *unencrypted_primary,
                                               uint64_t n_unencrypted, const uint64_t *proofs, uint8_t *ok_out);
 
+/* The same with the verification key in the reference's own form, as vsp_codec_groth16_vk_read delivers it
+ * (alpha_g1_beta_g2: 72 limbs; verification_key.hpp:128-152) — what a verifier that only holds the key blobs calls
+ * (verify_encryption in the vote phase's own check, bin/cli/include/nil/vote_saver/common.hpp:1163-1169). */
+VSP_API int vsp_saver_verify_encryption_gt_batch(vsp_ctx *ctx, const uint64_t *alpha_g1_beta_g2, const uint64_t *gamma_g2,
+                                                 const uint64_t *delta_g2, uint64_t gamma_ABC_count,
+                                                 const uint64_t *gamma_ABC_g1, const vsp_saver_pubkey_t *pub, uint64_t k,
+                                                 const uint64_t *cts, const uint64_t *unencrypted_primary,
+                                                 uint64_t n_unencrypted, const uint64_t *proofs, uint8_t *ok_out);
+
 /* decrypt_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:401-441): ct = msg_size + 2 G1 (e.g. the tally's sum of
  * ballots' ciphertexts), rho the secret key, (rho_sv_g2, rho_rhov_g2) from the SAVER verification key, gamma_abc_rest the
  * first msg_size points of gamma_ABC_g1.rest.  m_out: msg_size Fr, each the discrete log found by the reference's search

@@ -136,5 +136,5 @@ def test_vote_phase_from_blobs_to_blobs():
     res = json.loads(run.stdout.strip().splitlines()[-1])
     for key in ("sizes_ok", "accepted", "forged_root_rejected", "sn_is_native_hash", "public_slice_is_eid_sn_rt",
                 "deterministic_given_scalars", "batch_accepted", "tally", "tally_proof", "vk_blob_round_trip", "tally_blobs",
-                "tally_blobs_verify", "wrong_result_rejected", "key_blobs_are_the_generated_keys"):
+                "tally_blobs_verify", "wrong_result_rejected", "key_blobs_are_the_generated_keys", "verify_votes_from_blobs"):
         assert res[key] is True, (key, res)

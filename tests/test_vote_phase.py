@@ -320,3 +320,43 @@ def test_init_admin_keys_phase_glue_with_host_stand_ins(monkeypatch):
     assert cref.limbs_to_ints(codec.saver_sk_from_bytes(sk_blob).reshape(1, 4))[0] == 12345
     a, b, cc = codec.saver_vk_from_bytes(svk_blob)
     assert np.array_equal(a, svk["rho_g2"][0]) and np.array_equal(b, svk["rho_sv_g2"]) and np.array_equal(cc, svk["rho_rhov_g2"])
+
+
+def test_verify_votes_glue_with_a_host_stand_in(monkeypatch):
+    """vote_phase.verify_votes around vsp_saver_verify_encryption_gt_batch: ballots whose blobs do not decode or do not fit the
+    keys are False without reaching the GPU, the others go in one batch with the key in its serialised (GT) form"""
+    vsp = importlib.import_module("vote-saver-protocol_b200")
+    blobs, *_ = _blobs(seed=44)
+    rng = random.Random(45)
+    seen = {}
+
+    class Pub:
+        def __init__(self, arr):
+            self.arrays, self.msg_size = arr, int(arr["msg_size"])
+
+    def verify(ctx, vk, pub, cts, rests, proofs):
+        seen.update(vk=vk, cts=np.array(cts), rests=np.array(rests), proofs=np.array(proofs))
+        return np.array([True, False][:len(proofs)] + [True] * max(0, len(proofs) - 2))
+
+    monkeypatch.setattr(vsp, "SaverPublicKey", Pub)
+    monkeypatch.setattr(vsp, "verify_encryption_gt_batch", verify)
+
+    def ballot(seed, n_ct=27, n_rest=5):
+        proof = np.concatenate([random_g1(1, seed).reshape(-1), random_g2(1, seed).reshape(-1), random_g1(1, seed + 1).reshape(-1)])
+        rest = cref.ints_to_limbs([rng.randrange(o.R) for _ in range(n_rest)], 4)
+        return codec.proof_bytes(proof), codec.primary_input_bytes(rest), codec.ciphertext_bytes(random_g1(n_ct, seed + 2))
+
+    good = [ballot(1), ballot(2), ballot(3)]
+    broken_proof = (bytes(192), good[0][1], good[0][2])
+    short_ct = ballot(4, n_ct=26)
+    long_rest = ballot(5, n_rest=6)
+    unreduced = (good[0][0], struct.pack(">Q", 5) + o.R.to_bytes(32, "big") + bytes(32 * 4), good[0][2])
+    got = vp.verify_votes(None, blobs["verification_key_blob"], blobs["pk_eid_blob"],
+                          [good[0], broken_proof, good[1], short_ct, long_rest, unreduced, good[2]])
+    assert got == [True, False, False, False, False, False, True]
+    assert seen["cts"].shape == (3, 27, 12) and seen["rests"].shape == (3, 5, 4) and seen["proofs"].shape == (3, 48)
+    assert np.array_equal(seen["proofs"][1], codec.proof_from_bytes(good[1][0]))
+    assert seen["vk"]["alpha_g1_beta_g2"].shape == (72,) and seen["vk"]["gamma_ABC_g1"].shape == (31, 12)
+    seen.clear()
+    assert vp.verify_votes(None, blobs["verification_key_blob"], blobs["pk_eid_blob"], [broken_proof]) == [False] and not seen
+    assert vp.verify_votes(None, blobs["verification_key_blob"], blobs["pk_eid_blob"], []) == []

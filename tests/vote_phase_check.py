@@ -85,6 +85,11 @@ def main():
         proofs = np.stack([codec.proof_from_bytes(b[0]) for b in out])
         rests = np.stack([codec.primary_input_from_bytes(b[1]) for b in out])
         res["batch_accepted"] = bool(vsp.verify_encryption_batch(ctx, vk, pub, cts, rests, proofs).all())
+        # the verifier that only holds blobs: the key in its serialised (GT) form, vsp_saver_verify_encryption_gt_batch
+        published = [(b[0], b[1], b[2]) for b in out]
+        tampered = (published[1][0], published[0][1], published[1][2])  # voter 1's proof and cipher text with voter 0's sn
+        res["verify_votes_from_blobs"] = vp.verify_votes(ctx, blobs["verification_key_blob"], blobs["pk_eid_blob"],
+                                                         published + [tampered]) == [True, True, True, True, False]
         total = cts[0]
         for b in range(1, 4):
             total = np.stack([cref.g1_add(total[i], cts[b][i]) for i in range(c.msg_size + 2)])

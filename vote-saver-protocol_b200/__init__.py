@@ -692,6 +692,23 @@ def verify_encryption_batch(ctx: Context, vk: dict, pubkey: SaverPublicKey, cts,
     return ok.astype(bool)
 
 
+def verify_encryption_gt_batch(ctx: Context, vk: dict, pubkey: SaverPublicKey, cts, unencrypted_primary, proofs) -> np.ndarray:
+    """verify_encryption_batch with the verification key as codec.groth16_vk_from_bytes delivers it (alpha_g1_beta_g2 as a GT
+    value): bool per ballot"""
+    gt, g2, d2 = _a(vk["alpha_g1_beta_g2"]).reshape(-1), _a(vk["gamma_g2"]).reshape(-1, 24), _a(vk["delta_g2"]).reshape(-1, 24)
+    gabc = _a(vk["gamma_ABC_g1"]).reshape(-1, 12)
+    if gt.shape[0] != 72:
+        raise ValueError("alpha_g1_beta_g2 must be 72 limbs")
+    pr = _a(proofs, 48)
+    k = pr.shape[0]
+    ct = np.ascontiguousarray(cts, dtype=np.uint64).reshape(k, pubkey.msg_size + 2, 12)
+    x = np.ascontiguousarray(unencrypted_primary, dtype=np.uint64).reshape(k, -1, 4)
+    ok = np.zeros(k, dtype=np.uint8)
+    ctx.check(ctx._lib.vsp_saver_verify_encryption_gt_batch(ctx._h, _p(gt), _p(g2), _p(d2), gabc.shape[0], _p(gabc),
+                                                            C.byref(pubkey.desc), k, _p(ct), _p(x), x.shape[1], _p(pr), _p(ok)))
+    return ok.astype(bool)
+
+
 def decrypt(ctx: Context, ct, rho: int, svk: dict, gamma_abc_rest, block_bits: int = 4):
     """decrypt_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:401-441): (message ints, verify_c0 point).
     svk: the SAVER verification-key arrays (rho_g2, rho_sv_g2, rho_rhov_g2).  ValueError("Decryption failed.") where the

@@ -156,6 +156,8 @@ SYMBOLS = [
     ("vsp_groth16_verify_gt_batch", _int, [_vp, _vp, _vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _vp]),
     ("vsp_saver_verify_encryption_batch", _int, [_vp, C.POINTER(VerificationKeyDesc), C.POINTER(SaverPubkeyDesc), _u64, _vp,
                                                  _vp, _u64, _vp, _vp]),
+    ("vsp_saver_verify_encryption_gt_batch", _int, [_vp, _vp, _vp, _vp, _u64, _vp, C.POINTER(SaverPubkeyDesc), _u64, _vp, _vp,
+                                                    _u64, _vp, _vp]),
     ("vsp_saver_decrypt", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp]),
     ("vsp_saver_verify_decryption", _int, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     ("vsp_voting_program_create", _int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _u64, C.POINTER(_vp)]),

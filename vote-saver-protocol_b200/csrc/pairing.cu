@@ -763,6 +763,32 @@ extern "C" int vsp_saver_verify_encryption_batch(vsp_ctx* ctx, const vsp_verific
     }
 }
 
+// verify_encryption with the verification key as the reference stores and serialises it (alpha_g1_beta_g2 in GT form): the
+// same two checks as vsp_saver_verify_encryption_batch, the Groth16 one compared as an Fq12 value (verify_impl's GT branch)
+extern "C" int vsp_saver_verify_encryption_gt_batch(vsp_ctx* ctx, const uint64_t* alpha_g1_beta_g2, const uint64_t* gamma_g2,
+                                                    const uint64_t* delta_g2, uint64_t gamma_ABC_count,
+                                                    const uint64_t* gamma_ABC_g1, const vsp_saver_pubkey_t* pub, uint64_t k,
+                                                    const uint64_t* cts, const uint64_t* unencrypted_primary,
+                                                    uint64_t n_unencrypted, const uint64_t* proofs, uint8_t* ok_out) {
+    if (!ctx) return VSP_E_INVALID;
+    if (!alpha_g1_beta_g2 || !gamma_g2 || !delta_g2 || !gamma_ABC_g1 || !pub || !pub->t_g2 || (k && (!cts || !proofs || !ok_out)) ||
+        (k && n_unencrypted && !unencrypted_primary))
+        return set_error(ctx, VSP_E_INVALID, "vsp_saver_verify_encryption_gt_batch: null argument");
+    cudaSetDevice(ctx->device);
+    vsp_verification_key_t vk;
+    memset(&vk, 0, sizeof(vk));
+    vk.gamma_g2 = gamma_g2;
+    vk.delta_g2 = delta_g2;
+    vk.gamma_ABC_count = gamma_ABC_count;
+    vk.gamma_ABC_g1 = gamma_ABC_g1;
+    try {
+        return verify_impl(ctx, &vk, pub->t_g2, pub->msg_size, k, cts, unencrypted_primary, n_unencrypted, proofs, ok_out,
+                           alpha_g1_beta_g2);
+    } catch (const std::bad_alloc&) {
+        return set_error(ctx, VSP_E_NOMEM, "host allocation failed");
+    }
+}
+
 extern "C" int vsp_g1_mul_batch(vsp_ctx* ctx, uint64_t n, const uint64_t* points, const uint64_t* scalars, uint64_t* out);
 
 // decrypt_op<elgamal_verifiable>::process (elgamal_verifiable.hpp:401-441).  For every message slot j:

@@ -172,6 +172,43 @@ class VotePhase:
         return [serialize_vote(proofs[b], primary[b], cts[b], self.msg_size, n_eid) for b in range(k)]
 
 
+def verify_votes(ctx, verification_key_blob: bytes, pk_eid_blob: bytes,
+                 ballots: Sequence[Tuple[bytes, bytes, bytes]]) -> List[bool]:
+    """verify_encryption<encryption_scheme_type>(cipher_text, {pk_eid, vk, proof, primary input after the message slots}) for
+    ballots given as (proof_blob, pinput_blob, ct_blob) — the vote phase's own check (common.hpp:1163-1169) and what the
+    verifier of the published ballots runs — from the key blobs alone: the verification key stays in the form it is
+    serialised in (alpha_g1_beta_g2 as a GT value; vsp_saver_verify_encryption_gt_batch).  A ballot whose blobs do not
+    decode, or whose sizes do not fit the keys, is False."""
+    import importlib
+    vsp = importlib.import_module(__package__)
+    vk = codec.groth16_vk_from_bytes(verification_key_blob)
+    pub = vsp.SaverPublicKey(codec.saver_pubkey_from_bytes(pk_eid_blob))
+    n = pub.msg_size
+    n_rest = vk["gamma_ABC_g1"].shape[0] - 1 - n
+    if n_rest < 0:
+        raise ValueError("the verification key's gamma_ABC_g1 is shorter than the public key's message size")
+    ok = [False] * len(ballots)
+    rows, proofs, cts, rests = [], [], [], []
+    for b, (proof_blob, pinput_blob, ct_blob) in enumerate(ballots):
+        try:
+            proof, ct, rest = codec.proof_from_bytes(proof_blob), codec.ciphertext_from_bytes(ct_blob), \
+                codec.primary_input_from_bytes(pinput_blob)
+        except ValueError:
+            continue
+        if ct.shape[0] != n + 2 or rest.shape[0] != n_rest or any(
+                int.from_bytes(np.ascontiguousarray(r).tobytes(), "little") >= FR_MODULUS for r in rest):
+            continue
+        rows.append(b)
+        proofs.append(proof)
+        cts.append(ct)
+        rests.append(rest)
+    if rows:
+        got = vsp.verify_encryption_gt_batch(ctx, vk, pub, np.stack(cts), np.stack(rests), np.stack(proofs))
+        for b, g in zip(rows, got):
+            ok[b] = bool(g)
+    return ok
+
+
 def generate_vote(ctx, tree_depth: int, eid_bits: int, voter_idx: int, vote: int, merkle_tree_blob: bytes, rt_blob: bytes,
                   eid_blob: bytes, sk_blob: bytes, pk_eid_blob: bytes, proving_key_blob: bytes,
                   verification_key_blob: bytes, rs: Optional[np.ndarray] = None,
