@@ -58,3 +58,20 @@ def test_domain_plan_rejects_degenerate_sizes(vsp):
     for m in (0, 1):
         with pytest.raises(ValueError):
             vsp.domain_plan(m)
+
+
+def test_header_is_plain_c_and_the_library_links_from_c(vsp, tmp_path):
+    """include/vsp_b200.h under gcc -std=c11 -pedantic, and tests/cpp/c_abi_check.c linked against the .so and run: host-only
+    entry points from C, VSP_E_NO_DEVICE (or a working context on a GPU box) from vsp_ctx_create"""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    lib_dir = os.path.dirname(vsp.library_path())
+    exe = str(tmp_path / "c_abi_check")
+    subprocess.check_call([gcc, "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                           "-o", exe, os.path.join(ROOT, "tests", "cpp", "c_abi_check.c"), "-L", lib_dir, "-lvsp_b200",
+                           "-Wl,-rpath," + lib_dir])
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert run.returncode == 0 and run.stdout.startswith("OK"), run.stdout + run.stderr
