@@ -425,3 +425,30 @@ def test_merkle_tree_blob_and_copath():
     too_wide[3, 3] |= np.uint64(1 << 63)
     with pytest.raises(ValueError):
         codec.merkle_tree_bytes(too_wide, depth)
+
+
+def test_blob_sizes_reproduce_the_readme_ballot_offsets():
+    """The reference's README.md:219 quotes a real ballot blob's offsets —
+        commit_ballot {"proof_end":193, "ct_begin":35273, "eid_begin":35721, "sn_begin":37769, "sn_end":45929}
+    — for `01 | proof | vk_crs | pk_eid | ct | eid | sn | rt` (README.md:207; bin/cli/src/protocol_exec.ipynb, voter_vote_phase:
+    ct_offset = 1 + len(proof) + len(vk_crs) + len(pk_eid), eid_offset = ct_end + 8, ...).  That run had msg_size 7 and one
+    field element per eid / sn / rt bit (64 + 255 + 255), so 581 primary inputs; the numbers then fix, to the byte, the sum of
+    the extended verification key blob and the SAVER public key blob as crypto3 serialises them: 35273 - 193 = 35080.  The
+    codec's blobs for those shapes have exactly that size (GT as 12 x 48 bytes, delta_g1 and gamma_g1 present, the sparse
+    rest with its index list and domain size, 8-byte counts, compressed points), and the other offsets follow."""
+    msg_size, n_primary = 7, 7 + 64 + 255 + 255
+    g = golden("databin_groth16.json")
+    gt = cref.ints_to_limbs([int(x, 16) for x in g["alpha_g1_beta_g2"]], 6).reshape(-1)
+    g1, g2 = random_g1(n_primary + 3, 90), random_g2(msg_size + 3, 91)
+    vk_blob = codec.groth16_vk_bytes(gt, g2[0], g2[1], g1[0], g1[1], g1[2:])
+    pub = {"msg_size": msg_size, "delta_g1": g1[0:1].copy(), "delta_sum_s_g1": g1[1:2].copy(), "gamma_inverse_sum_s_g1": g1[2:3].copy(),
+           "delta_s_g1": g1[3:3 + msg_size].copy(), "t_g1": g1[10:10 + msg_size].copy(), "t_g2": g2[2:2 + msg_size + 1].copy()}
+    pk_eid_blob = codec.saver_pubkey_bytes(pub)
+    assert len(vk_blob) + len(pk_eid_blob) == 35273 - 193
+    proof_end = 1 + 192
+    ct_begin = proof_end + len(vk_blob) + len(pk_eid_blob)
+    ct_end = ct_begin + len(codec.ciphertext_bytes(random_g1(msg_size + 2, 92)))
+    eid_begin = ct_end + 8
+    sn_begin = eid_begin + (len(codec.primary_input_bytes(np.zeros((64, 4), np.uint64))) - 8)
+    sn_end = sn_begin + (len(codec.primary_input_bytes(np.zeros((255, 4), np.uint64))) - 8)
+    assert (proof_end, ct_begin, eid_begin, sn_begin, sn_end) == (193, 35273, 35721, 37769, 45929)
