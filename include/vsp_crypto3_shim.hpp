@@ -407,6 +407,11 @@ namespace zk {
             typename CurveType::template g2_type<>::value_type gamma_g2, delta_g2;
             typename CurveType::template g1_type<>::value_type delta_g1, gamma_g1;
             accumulation_vector<typename CurveType::template g1_type<>::value_type> gamma_ABC_g1;
+            // A key that was deserialised (verification_key.hpp:128-152, vsp_codec_groth16_vk_read) has no alpha_g1 / beta_g2,
+            // only their pairing: 12 Fq coefficients in tower order, 72 limbs.  When has_alpha_g1_beta_g2 is set the verifiers
+            // below use it and ignore alpha_g1 / beta_g2.
+            std::array<std::uint64_t, 72> alpha_g1_beta_g2 {};
+            bool has_alpha_g1_beta_g2 = false;
         };
 
         template<typename CurveType, proving_mode Mode = proving_mode::basic>
@@ -697,9 +702,13 @@ namespace zk {
         std::memcpy(pr + 36, proof.g_C.l.data(), 96);
         std::uint8_t ok = 0;
         auto &dev = b200::device::instance();
-        dev.check(vsp_groth16_verify_batch(dev.ctx(), &d, 1, primary_input.empty() ? nullptr : primary_input[0].l.data(),
-                                           primary_input.size(), pr, &ok),
-                  "verify");
+        const std::uint64_t *x = primary_input.empty() ? nullptr : primary_input[0].l.data();
+        if (vk.has_alpha_g1_beta_g2)  // the key as deserialised: alpha_g1_beta_g2 in GT form
+            dev.check(vsp_groth16_verify_gt_batch(dev.ctx(), vk.alpha_g1_beta_g2.data(), d.gamma_g2, d.delta_g2, d.gamma_ABC_count,
+                                                  d.gamma_ABC_g1, 1, x, primary_input.size(), pr, &ok),
+                      "verify");
+        else
+            dev.check(vsp_groth16_verify_batch(dev.ctx(), &d, 1, x, primary_input.size(), pr, &ok), "verify");
         return ok != 0;
     }
 }    // namespace zk
@@ -884,9 +893,15 @@ namespace pubkey {
         std::uint8_t ok = 0;
         auto &d = b200::device::instance();
         const auto &x = p.unencrypted_primary_input;
-        d.check(vsp_saver_verify_encryption_batch(d.ctx(), &vk, &desc, 1, ct[0].l.data(), x.empty() ? nullptr : x[0].l.data(),
-                                                  x.size(), proof, &ok),
-                "verify_encryption");
+        if (p.gg_vk.has_alpha_g1_beta_g2)
+            d.check(vsp_saver_verify_encryption_gt_batch(d.ctx(), p.gg_vk.alpha_g1_beta_g2.data(), vk.gamma_g2, vk.delta_g2,
+                                                         vk.gamma_ABC_count, vk.gamma_ABC_g1, &desc, 1, ct[0].l.data(),
+                                                         x.empty() ? nullptr : x[0].l.data(), x.size(), proof, &ok),
+                    "verify_encryption");
+        else
+            d.check(vsp_saver_verify_encryption_batch(d.ctx(), &vk, &desc, 1, ct[0].l.data(),
+                                                      x.empty() ? nullptr : x[0].l.data(), x.size(), proof, &ok),
+                    "verify_encryption");
         return ok != 0;
     }
 
