@@ -360,3 +360,12 @@ def test_verify_votes_glue_with_a_host_stand_in(monkeypatch):
     seen.clear()
     assert vp.verify_votes(None, blobs["verification_key_blob"], blobs["pk_eid_blob"], [broken_proof]) == [False] and not seen
     assert vp.verify_votes(None, blobs["verification_key_blob"], blobs["pk_eid_blob"], []) == []
+
+
+def test_vote_phase_refuses_a_key_for_another_circuit():
+    """a proving key whose constraint system is not this package's ballot circuit (e.g. one made by the reference's own
+    generator over crypto3-blueprint's components) is rejected before anything is uploaded"""
+    blobs, *_ = _blobs(depth=2, seed=51)
+    inputs = vp.parse_vote_inputs(2, 64, **blobs)  # the synthetic 40-constraint key of _blobs
+    with pytest.raises(ValueError, match="is not the ballot circuit"):
+        vp.VotePhase(None, inputs)
