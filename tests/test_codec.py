@@ -486,3 +486,37 @@ def test_blob_readers_under_sanitizers(tmp_path):
         (tmp_path / name).write_bytes(blob)
     run = subprocess.run([exe, "120", str(tmp_path)], capture_output=True, text=True, timeout=300)
     assert run.returncode == 0 and "accepted" in run.stdout and "runtime error" not in run.stderr, run.stdout + run.stderr[-2000:]
+
+
+def test_cpp_marshalling_header_round_trips_every_blob(vsp, tmp_path):
+    """include/vsp_crypto3_marshalling.hpp (bin/cli's marshaling_policy over the shim's types): tests/cpp/marshalling_check.cpp
+    built with g++ and run on blobs this module wrote — every deserialiser, every serialiser, byte for byte, no GPU"""
+    import os
+    import shutil
+    import subprocess
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.dirname(vsp.library_path())
+    exe = str(tmp_path / "marshalling_check")
+    subprocess.check_call([gxx, "-O1", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(root, "include"),
+                           os.path.join(root, "tests", "cpp", "marshalling_check.cpp"), "-o", exe, "-L", lib_dir, "-lvsp_b200",
+                           "-Wl,-rpath," + lib_dir])
+    n = 5
+    g1, g2 = random_g1(40, 1), random_g2(20, 2)
+    pub = {"msg_size": n, "delta_g1": g1[0:1].copy(), "delta_sum_s_g1": g1[1:2].copy(), "gamma_inverse_sum_s_g1": g1[2:3].copy(),
+           "delta_s_g1": g1[3:8].copy(), "t_g1": g1[8:13].copy(), "t_g2": g2[:6].copy()}
+    gt = cref.ints_to_limbs([int(x, 16) for x in golden("databin_groth16.json")["alpha_g1_beta_g2"]], 6).reshape(-1)
+    cs, _, _ = synthetic_r1cs(12, 3, seed=1, binary=True)
+    proof = np.concatenate([g1[20], g2[10], g1[21]])
+    files = {"pub.bin": codec.saver_pubkey_bytes(pub), "svk.bin": codec.saver_vk_bytes(g2[6], g2[7:12], g2[12:17]),
+             "vk.bin": codec.groth16_vk_bytes(gt, g2[0], g2[1], g1[0], g1[1], g1[2:10]), "ct.bin": codec.ciphertext_bytes(g1[:7]),
+             "pk.bin": codec.write_fast_proving_key(synthetic_pk_arrays(cs, 1)),
+             "pi.bin": codec.primary_input_bytes(cref.ints_to_limbs([1, 2, 3], 4)),
+             "sk.bin": codec.saver_sk_bytes(cref.ints_to_limbs([o.R - 2], 4)[0]), "proof.bin": codec.proof_bytes(proof),
+             "tree.bin": codec.merkle_tree_bytes(cref.ints_to_limbs([11, 12, 13, 14, 15, 16, 17], 4), 2)}
+    for name, blob in files.items():
+        (tmp_path / name).write_bytes(blob)
+    run = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=120)
+    assert run.returncode == 0 and run.stdout.strip() == "OK", run.stdout + run.stderr
