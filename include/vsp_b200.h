@@ -494,7 +494,8 @@ VSP_API int vsp_codec_saver_sk_read(const uint8_t *in, size_t len, uint64_t rho[
  * accumulation_vector.hpp:52-57, sparse_vector.hpp:49-58).  gamma_ABC_g1 here is dense, gamma_ABC_count = 1 + domain size
  * points; the writer lists every position of the rest (as the reference's generator builds it), the reader leaves
  * positions the blob does not list at infinity.  write: out == NULL gives the size only.  read: alpha_g1_beta_g2 == NULL
- * gives *gamma_ABC_count only; otherwise capacity must equal it. */
+ * gives *gamma_ABC_count only; otherwise capacity must equal it.  A rest whose domain size exceeds 2^24 is refused
+ * (VSP_E_INVALID): the dense array it would need is not worth allocating on the word of an untrusted blob. */
 VSP_API int vsp_codec_groth16_vk_write(const uint64_t *alpha_g1_beta_g2, const uint64_t *gamma_g2, const uint64_t *delta_g2,
                                        const uint64_t *delta_g1, const uint64_t *gamma_g1, uint64_t gamma_ABC_count,
                                        const uint64_t *gamma_ABC_g1, uint8_t *out, size_t capacity, size_t *written);

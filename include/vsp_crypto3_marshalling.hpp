@@ -87,7 +87,8 @@ namespace b200 {
         // deserialize_merkle_tree (common.hpp:614-636): digests as 4-limb integers (bit i = digest bit i), leaves first, root
         // last; merkle_copath = containers::merkle_proof(tree, idx) for arity 2 (merkle/proof.hpp:65-91), leaf level first
         static std::vector<std::array<std::uint64_t, 4>> deserialize_merkle_tree(std::size_t tree_depth, const blob_type &blob) {
-            if (tree_depth > 40) throw std::invalid_argument("deserialize_merkle_tree: depth");
+            if (tree_depth > 40 || blob.size() != 32 * ((std::size_t(2) << tree_depth) - 1))
+                throw std::invalid_argument("deserialize_merkle_tree: the blob is not 2^(depth + 1) - 1 digests of 32 bytes");
             std::vector<std::array<std::uint64_t, 4>> out((std::size_t(2) << tree_depth) - 1);
             check(vsp_codec_merkle_tree_read(blob.data(), blob.size(), tree_depth, out[0].data()), "deserialize_merkle_tree");
             return out;

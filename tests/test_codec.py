@@ -520,3 +520,21 @@ def test_cpp_marshalling_header_round_trips_every_blob(vsp, tmp_path):
         (tmp_path / name).write_bytes(blob)
     run = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=120)
     assert run.returncode == 0 and run.stdout.strip() == "OK", run.stdout + run.stderr
+
+
+def test_readers_do_not_allocate_on_the_word_of_a_blob():
+    """sizes a blob merely claims are checked against its length (or a stated cap) before anything is allocated for them"""
+    _, coeffs, gamma, delta, first = _databin_vk()
+    pts = random_g1(2, 14)
+    head = b"".join(c.to_bytes(48, "big") for c in coeffs) + gamma + delta + _c1(pts[0]) + _c1(pts[1]) + first
+    huge_domain = head + struct.pack(">Q", 0) + struct.pack(">Q", 0) + struct.pack(">Q", 1 << 40)
+    with pytest.raises(ValueError):
+        codec.groth16_vk_from_bytes(huge_domain)
+    with pytest.raises(ValueError):
+        codec.merkle_tree_from_bytes(bytes(32 * 7), 40)
+    with pytest.raises(ValueError):
+        codec.ciphertext_from_bytes(struct.pack(">Q", 1 << 50) + bytes(48))
+    with pytest.raises(ValueError):
+        codec.primary_input_from_bytes(struct.pack(">Q", 1 << 50) + bytes(32))
+    with pytest.raises(ValueError):
+        codec.saver_pubkey_from_bytes(_c1(pts[0]) * 3 + struct.pack(">Q", 1 << 50))

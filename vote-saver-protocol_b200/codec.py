@@ -236,6 +236,8 @@ def merkle_tree_bytes(digests, depth: int) -> bytes:
 
 def merkle_tree_from_bytes(blob: bytes, depth: int) -> np.ndarray:
     """deserialize_merkle_tree (common.hpp:614-636) -> (2^(depth + 1) - 1) x 4 limbs, leaves first, root last"""
+    if not 0 <= depth <= 40 or len(blob) != 32 * ((2 << depth) - 1):
+        raise ValueError("a depth-%d tree blob is %d digests of 32 bytes" % (depth, (2 << depth) - 1 if 0 <= depth <= 40 else 0))
     out = np.zeros(((2 << depth) - 1, 4), dtype=np.uint64)
     _check(_lib.load().vsp_codec_merkle_tree_read(bytes(blob), len(blob), depth, out.ctypes.data), "merkle_tree_read")
     return out

@@ -831,7 +831,8 @@ int vsp_codec_groth16_vk_read(const uint8_t* blob, size_t len, uint64_t* gamma_A
     if (!idx || !r.ok || n_val != n_idx || n_val > r.left / G1_C) return VSP_E_INVALID;
     const uint8_t* val = r.take(G1_C * n_val);
     const uint64_t domain = r.u64();
-    if (!val || !r.ok || domain == ~uint64_t(0) || n_idx > domain) return VSP_E_INVALID;
+    // gamma_ABC_g1 is handed out dense: a domain past 2^24 positions (1.6 GB of points) is refused rather than allocated
+    if (!val || !r.ok || domain > (uint64_t(1) << 24) || n_idx > domain) return VSP_E_INVALID;
     if (gamma_ABC_count) *gamma_ABC_count = domain + 1;
     uint64_t prev = 0;
     for (uint64_t i = 0; i < n_idx; ++i) {
