@@ -135,3 +135,54 @@ def test_slice_proving_key_partitions_every_query_and_shares_sum_to_the_whole():
         assert seen["A"][-1][1] == cs.num_variables + 1 and seen["H"][-1][1] == m - 1
         for k in full:
             assert np.array_equal(acc[k], full[k]), (world, k)
+
+
+class _StubPhase:
+    """stands in for vote_phase.VotePhase on a GPU-less box: a ballot's "blobs" name the ballot and the scalars it was given"""
+
+    def __init__(self, rank):
+        self.rank, self.calls = rank, 0
+
+    def generate_votes(self, ballots, rs=None, rnd=None, rerandomize=True):
+        self.calls += 1
+        assert rs is None or rs.shape == (len(ballots), 3, 4)
+        return [(b"proof%d" % idx, b"vote%d" % vote, sk + b"|rs%d" % (0 if rs is None else int(rs[j, 0, 0])),
+                 b"rank%d" % self.rank) for j, (idx, vote, sk) in enumerate(ballots)]
+
+
+def _vote_worker(rank: int, world: int, port: int, out_dir: str):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import importlib
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        vp = importlib.import_module("vote-saver-protocol_b200.vote_phase")
+        k = 7
+        ballots = [(i, (3 * i) % 25, b"sk%d" % i) for i in range(k)]
+        rs = np.zeros((k, 3, 4), dtype=np.uint64)
+        rs[:, 0, 0] = np.arange(100, 100 + k)
+        out = vp.generate_votes_sharded(_StubPhase(rank), ballots, rs=rs)
+        assert len(out) == k
+        for i, (proof, pin, ct, sn) in enumerate(out):
+            # ballot order, each ballot made by rank i mod world with ITS scalars
+            assert (proof, pin, ct, sn) == (b"proof%d" % i, b"vote%d" % ((3 * i) % 25), b"sk%d|rs%d" % (i, 100 + i), b"rank%d" % (i % world))
+        assert vp.generate_votes_sharded(_StubPhase(rank), []) == []
+        with open(os.path.join(out_dir, "vote_ok%d" % rank), "w") as f:
+            f.write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_vote_phase_ballots_shard_over_ranks_world2_gloo(tmp_path):
+    """vote_phase.generate_votes_sharded: ballots i mod G per rank, blobs back in ballot order on every rank, per-ballot
+    scalars following their ballot (so the output is the same at every world size); without a process group it is the
+    single-process call"""
+    import importlib
+    world = 2
+    mp.spawn(_vote_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / ("vote_ok%d" % r)).exists() for r in range(world))
+    vp = importlib.import_module("vote-saver-protocol_b200.vote_phase")
+    single = vp.generate_votes_sharded(_StubPhase(0), [(i, i, b"s") for i in range(3)])
+    assert [b[0] for b in single] == [b"proof0", b"proof1", b"proof2"] and all(b[3] == b"rank0" for b in single)

@@ -172,6 +172,31 @@ class VotePhase:
         return [serialize_vote(proofs[b], primary[b], cts[b], self.msg_size, n_eid) for b in range(k)]
 
 
+def generate_votes_sharded(phase, ballots: Sequence[Tuple[int, int, bytes]], rs=None, rnd=None, rerandomize: bool = True,
+                           group=None) -> List[Tuple[bytes, bytes, bytes, bytes]]:
+    """proof-per-GPU sharding of a ballot list (BASELINE configs[3]): one process per GPU under torch.distributed,
+    every rank holding its own VotePhase on its own GPU; rank g takes ballots i = g (mod G) (sharded.ballot_indices), no
+    collective touches the data path, and the four blobs of every ballot come back in ballot order on every rank (one
+    all_gather_object of the ranks' blob lists).  rs / rnd, when given, are indexed by ballot, so the result does not depend
+    on the world size.  Without an initialised process group this is phase.generate_votes.  Under the NCCL backend the
+    caller has made its rank's GPU the current CUDA device (torch.cuda.set_device), as all_gather_object needs."""
+    from . import sharded
+    rank, world = sharded._world(group)
+    k = len(ballots)
+    mine = sharded.ballot_indices(k, rank, world)
+    pick = lambda a: None if a is None else np.ascontiguousarray(np.asarray(a, dtype=np.uint64).reshape(k, 3, 4)[mine])
+    local = phase.generate_votes([ballots[int(i)] for i in mine], rs=pick(rs), rnd=pick(rnd), rerandomize=rerandomize)
+    if world == 1:
+        return local
+    gathered = [None] * world
+    sharded._dist().all_gather_object(gathered, local, group=group)
+    out: List[Optional[Tuple[bytes, bytes, bytes, bytes]]] = [None] * k
+    for g in range(world):
+        for j, i in enumerate(sharded.ballot_indices(k, g, world)):
+            out[int(i)] = gathered[g][j]
+    return out  # type: ignore[return-value]
+
+
 def verify_votes(ctx, verification_key_blob: bytes, pk_eid_blob: bytes,
                  ballots: Sequence[Tuple[bytes, bytes, bytes]]) -> List[bool]:
     """verify_encryption<encryption_scheme_type>(cipher_text, {pk_eid, vk, proof, primary input after the message slots}) for
