@@ -538,3 +538,43 @@ def test_readers_do_not_allocate_on_the_word_of_a_blob():
         codec.primary_input_from_bytes(struct.pack(">Q", 1 << 50) + bytes(32))
     with pytest.raises(ValueError):
         codec.saver_pubkey_from_bytes(_c1(pts[0]) * 3 + struct.pack(">Q", 1 << 50))
+
+
+def test_empty_lists_and_random_shapes_round_trip():
+    """edge shapes: msg_size 0 (t_g2 still holds its one extra point), a verification key with no primary input, an empty
+    cipher text; then seeded random shapes, each blob read back and rewritten to the same bytes"""
+    g1, g2 = random_g1(64, 21), random_g2(40, 22)
+    pub0 = {"msg_size": 0, "delta_g1": g1[0:1].copy(), "delta_sum_s_g1": g1[1:2].copy(), "gamma_inverse_sum_s_g1": g1[2:3].copy(),
+            "delta_s_g1": np.zeros((1, 12), np.uint64), "t_g1": np.zeros((1, 12), np.uint64), "t_g2": g2[:1].copy()}
+    blob = codec.saver_pubkey_bytes(pub0)
+    assert len(blob) == 3 * 48 + 24 + 96
+    back = codec.saver_pubkey_from_bytes(blob)
+    assert back["msg_size"] == 0 and back["delta_s_g1"].shape == (0, 12) and np.array_equal(back["t_g2"], g2[:1])
+    a, b, c = codec.saver_vk_from_bytes(codec.saver_vk_bytes(g2[0], g2[:0], g2[:0]))
+    assert np.array_equal(a, g2[0]) and b.shape == (0, 24) and c.shape == (0, 24)
+    assert codec.ciphertext_bytes(g1[:0]) == struct.pack(">Q", 0)
+    gt = cref.ints_to_limbs([int(x, 16) for x in golden("databin_groth16.json")["alpha_g1_beta_g2"]], 6).reshape(-1)
+    vk0 = codec.groth16_vk_bytes(gt, g2[0], g2[1], g1[0], g1[1], g1[2:3])
+    assert codec.groth16_vk_from_bytes(vk0)["gamma_ABC_g1"].shape == (1, 12) and len(vk0) == 576 + 192 + 96 + 48 + 24
+    rng = random.Random(23)
+    for _ in range(12):
+        n = rng.randrange(0, 9)
+        pub = {"msg_size": n, "delta_g1": g1[0:1].copy(), "delta_sum_s_g1": g1[1:2].copy(), "gamma_inverse_sum_s_g1": g1[2:3].copy(),
+               "delta_s_g1": g1[3:3 + max(n, 1)].copy(), "t_g1": g1[20:20 + max(n, 1)].copy(), "t_g2": g2[:n + 1].copy()}
+        blob = codec.saver_pubkey_bytes(pub)
+        got = codec.saver_pubkey_from_bytes(blob)
+        got_full = dict(got, delta_s_g1=np.concatenate([got["delta_s_g1"], np.zeros((1, 12), np.uint64)]),
+                        t_g1=np.concatenate([got["t_g1"], np.zeros((1, 12), np.uint64)]))
+        assert codec.saver_pubkey_bytes(got_full) == blob
+        k = rng.randrange(1, 12)
+        vk_blob = codec.groth16_vk_bytes(gt, g2[2], g2[3], g1[4], g1[5], g1[6:6 + k])
+        vk = codec.groth16_vk_from_bytes(vk_blob)
+        assert codec.groth16_vk_bytes(vk["alpha_g1_beta_g2"], vk["gamma_g2"], vk["delta_g2"], vk["delta_g1"], vk["gamma_g1"],
+                                      vk["gamma_ABC_g1"]) == vk_blob
+        m = rng.randrange(0, 30)
+        ct = g1[:m].copy()
+        if m:
+            ct[rng.randrange(m)] = 0
+        assert np.array_equal(codec.ciphertext_from_bytes(codec.ciphertext_bytes(ct)), ct)
+        bits = [rng.randrange(2) for _ in range(rng.randrange(0, 600))]
+        assert list(codec.bitarray_from_bytes(codec.bitarray_bytes(bits), len(bits))) == bits
