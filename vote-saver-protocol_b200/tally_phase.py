@@ -12,7 +12,9 @@
 
 The reference also deserialises the proving key in both calls (`pk_crs_blob`, :1189-1190, :1251-1252) but uses only the
 verification key's gamma_ABC_g1.rest from the key pair (elgamal_verifiable.hpp:401-441, 548-575); the argument is accepted
-and ignored here.  The slot-by-slot sums run on the GPU (vsp_g1_sum), one call per cipher-text slot.
+and ignored here.  dec_proof_blob is written by `nil::marshalling::pack<endianness>(dec.second, status)` (:515): the
+marshalling library's type inference (in the un-vendored `marshalling` core) picks the type for a G1 value; it is taken here
+to be the one curve_element every other G1 point on this path uses, i.e. 48 compressed bytes.  The slot-by-slot sums run on the GPU (vsp_g1_sum), one call per cipher-text slot.
 """
 from __future__ import annotations
 
