@@ -31,7 +31,8 @@ from ._lib import (DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADI
 
 __all__ = ["Context", "EvaluationDomain", "make_evaluation_domain", "multiply_by_coset", "multiexp", "G1Bases",
            "G2Bases", "ProvingKey", "SaverPublicKey", "ResidentSaverKey", "domain_plan", "VspError", "library_path",
-           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_gt_batch", "verify_encryption_batch", "decrypt", "verify_decryption", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
+           "generate", "saver_generate_keypair", "pairing_products", "verify_batch", "verify_gt_batch", "verify_encryption_batch", "verify_encryption_gt_batch",
+           "decrypt", "verify_decryption", "g1_mul_batch", "g1_generator_mul_batch", "g2_generator_mul_batch"]
 
 FR_MULTIPLICATIVE_GENERATOR = 7
 
