@@ -146,6 +146,40 @@ def test_verify_encryption_batch_decides_like_the_oracle(ctx):
         vsp.verify_encryption_batch(ctx, vk, pub, cts, rest[:, :1], proofs)  # gamma_ABC count mismatch
 
 
+@pytest.mark.xfail(strict=False, reason="vsp_saver_verify_encryption_gt_batch (a host wrapper over the verifier's GT branch) was "
+                                        "added after the round's GPU minutes were spent and has not run on hardware yet")
+def test_verify_encryption_with_the_key_in_gt_form_decides_like_the_group_form(ctx):
+    """the verification key as it is serialised (alpha_g1_beta_g2 = pair_reduced(alpha_g1, beta_g2), verification_key.hpp:128-152)
+    gives the same decisions as the key with alpha_g1 and beta_g2, on honest, rerandomised and tampered ballots"""
+    nc, ni, msg_size, k = 33, 7, 4, 5
+    cs, arr, vk, pub_arr, rng = _keys_and_ballots(ctx, nc, ni, msg_size, k, seed=19)
+    pk = vsp.ProvingKey(ctx, arr)
+    pub = vsp.SaverPublicKey(pub_arr)
+    _cs, primary, aux = synthetic_r1cs(nc, ni, seed=19)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    gabc_rest = np.ascontiguousarray(vk["gamma_ABC_g1"][1:1 + msg_size])
+    cts, proofs = [], []
+    for b in range(k):
+        r_saver, r, s = (rng.randrange(o.R) for _ in range(3))
+        ct, proof = pk.encrypt(pub, gabc_rest, np.ascontiguousarray(P[:msg_size]), P, A, r_saver, r, s)
+        cts.append(ct)
+        proofs.append(proof)
+    cts[4], proofs[4] = vsp.rerandomize(ctx, pub, arr["delta_g2"], [rng.randrange(1, o.R) for _ in range(3)], cts[0], proofs[0])
+    pk.close()
+    cts, proofs = np.stack(cts), np.stack(proofs)
+    rest = np.tile(P[msg_size:], (k, 1, 1))
+    gt, _ = vsp.pairing_products(ctx, vk["alpha_g1"], vk["beta_g2"])
+    gt_vk = {"alpha_g1_beta_g2": gt[0], "gamma_g2": vk["gamma_g2"], "delta_g2": vk["delta_g2"], "gamma_ABC_g1": vk["gamma_ABC_g1"]}
+    assert vsp.verify_encryption_gt_batch(ctx, gt_vk, pub, cts, rest, proofs).all()
+    cts[1, 1] = cref.g1_add(cts[1, 1], G1L([o.g1_generator()])[0])  # tampered message slot
+    cts[2, msg_size + 1] = cts[3, msg_size + 1]                       # sum element of another ballot
+    rest[3, 0, 0] ^= np.uint64(1)                                     # wrong public part of the primary input
+    got = vsp.verify_encryption_gt_batch(ctx, gt_vk, pub, cts, rest, proofs)
+    assert got.tolist() == vsp.verify_encryption_batch(ctx, vk, pub, cts, rest, proofs).tolist() == [True, False, False, False, True]
+    wrong_gt = dict(gt_vk, alpha_g1_beta_g2=vsp.pairing_products(ctx, vk["alpha_g1"], vk["gamma_g2"])[0][0])
+    assert not vsp.verify_encryption_gt_batch(ctx, wrong_gt, pub, cts, rest, proofs).any()
+
+
 def test_tally_decrypt_and_verify_decryption(ctx):
     """the tally flow of bin/cli (common.hpp: sum the ballots' ciphertexts, decrypt_op, verify_decryption_op): keys, ballots
     and the tally on the GPU; small case cross-checked against the oracle's restatement of elgamal_verifiable.hpp:401-441,
