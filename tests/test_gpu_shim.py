@@ -130,3 +130,60 @@ def test_crypto3_shim_matches_oracle(tmp_path):
     p = subprocess.run([exe, fixture], capture_output=True, text=True)
     assert p.returncode == 0, p.stdout + p.stderr
     assert "all shim checks passed" in p.stdout
+
+
+def _build_blob_prove_check(tmp_path) -> str:
+    import importlib
+    import shutil
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    lib_dir = os.path.dirname(importlib.import_module("vote-saver-protocol_b200").library_path())
+    exe = str(tmp_path / "blob_prove_check")
+    subprocess.check_call([gxx, "-O1", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(CPP, "blob_prove_check.cpp"), "-o", exe, "-L", lib_dir, "-lvsp_b200",
+                           "-Wl,-rpath," + lib_dir])
+    return exe
+
+
+def _write_prove_blobs(tmp_path, seed=41):
+    import importlib
+    codec = importlib.import_module("vote-saver-protocol_b200.codec")
+    cs, primary, aux = synthetic_r1cs(97, 30, seed=seed, binary=True)
+    arr = synthetic_pk_arrays(cs, seed + 1)
+    P, A = cref.ints_to_limbs(primary, 4), cref.ints_to_limbs(aux, 4)
+    r, s = 0x1234567890abcdef, o.R - 5
+    (tmp_path / "pk.bin").write_bytes(codec.write_fast_proving_key(arr))
+    (tmp_path / "primary.bin").write_bytes(codec.primary_input_bytes(P))
+    (tmp_path / "aux.bin").write_bytes(codec.primary_input_bytes(A))
+    (tmp_path / "rs.bin").write_bytes(codec.primary_input_bytes(cref.ints_to_limbs([r, s], 4)))
+    return codec, arr, P, A, r, s
+
+
+def test_blob_prove_check_builds_and_refuses_to_run_without_a_gpu(tmp_path):
+    """CPU tier: the marshalling header + shim compile together under -Werror; the blobs are read on the host; without a CUDA
+    device the program stops with exit code 3 before proving anything"""
+    import torch
+    exe = _build_blob_prove_check(tmp_path)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test below")
+    _write_prove_blobs(tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 3 and "CUDA device is required" in p.stderr, p.stdout + p.stderr
+    (tmp_path / "pk.bin").write_bytes((tmp_path / "pk.bin").read_bytes()[:-3])
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 1 and "malformed blob" in p.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="tests/cpp/blob_prove_check.cpp was written after the round's GPU minutes were spent and "
+                                        "has not run on hardware yet")
+def test_cpp_host_proves_from_the_reference_blobs(tmp_path):
+    """r1cs_proving_key.bin -> proof.bin through C++ alone (vsp_crypto3_marshalling.hpp + vsp_crypto3_shim.hpp): the bytes equal
+    the oracle's proof in the reference's compressed encoding"""
+    exe = _build_blob_prove_check(tmp_path)
+    codec, arr, P, A, r, s = _write_prove_blobs(tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    want = cref.groth16_prove(fx.fill_pk(cref.ProvingKeyDesc(), arr), P, A, r, s)
+    assert p.stdout.strip() == codec.proof_bytes(want).hex()
